@@ -1,0 +1,134 @@
+"""Generate golden fixtures from the UNMODIFIED reference (build container only).
+
+Run:  PYTHONDONTWRITEBYTECODE=1 python oracle/make_golden.py
+Needs /root/reference (read-only mount); the GPU box does not have it, which
+is why the outputs are committed under tests/golden/.  The only harness-side
+accommodation is the `.cuda()` identity shim: utils.py:40 hard-codes `.cuda()`
+on the overlap-add index tensor, which raises on a CPU-only host
+(SURVEY.md §0 fact 4).  No reference file is edited or copied.
+"""
+import os
+import sys
+
+import numpy as np
+import torch
+
+REF = os.environ.get("CTN_REFERENCE", "/root/reference/src")
+OUT = os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", "tests", "golden")
+
+
+def _import_reference():
+    sys.dont_write_bytecode = True
+    if not torch.cuda.is_available():
+        torch.Tensor.cuda = lambda self, *a, **k: self  # harness shim, see docstring
+    sys.path.insert(0, REF)
+    import conv_tasnet as ref_model
+    import pit_criterion as ref_loss
+    import utils as ref_utils
+    sys.path.pop(0)
+    return ref_model, ref_loss, ref_utils
+
+
+CASES = {
+    # the reference's own demo tuple (conv_tasnet.py:360-363), float inputs
+    "demo_gln": dict(cfg=dict(N=3, L=4, B=2, H=3, P=3, X=3, R=2, C=2, norm_type="gLN",
+                              causal=False, mask_nonlinear="relu"), M=2, T=12, lengths=[12, 12]),
+    # causal cLN, T not a multiple of hop (tail zero-fill), ragged lengths
+    "causal_cln": dict(cfg=dict(N=8, L=4, B=8, H=16, P=3, X=3, R=2, C=2, norm_type="cLN",
+                                causal=True, mask_nonlinear="relu"), M=2, T=51, lengths=[51, 37]),
+    # C=3 softmax mask, gLN, ragged lengths
+    "softmax_c3": dict(cfg=dict(N=16, L=8, B=8, H=16, P=3, X=2, R=2, C=3, norm_type="gLN",
+                                causal=False, mask_nonlinear="softmax"), M=3, T=100,
+                       lengths=[100, 77, 64]),
+    # smallest shape that takes the tensor-core GEMM path (channels % 8 == 0, K > 128)
+    "tc_small": dict(cfg=dict(N=64, L=16, B=64, H=128, P=3, X=3, R=1, C=2, norm_type="gLN",
+                              causal=False, mask_nonlinear="relu"), M=2, T=1207, lengths=[1207, 900]),
+    # causal cLN on the tensor-core path
+    "tc_causal_cln": dict(cfg=dict(N=64, L=16, B=64, H=128, P=3, X=2, R=1, C=2, norm_type="cLN",
+                                   causal=True, mask_nonlinear="relu"), M=1, T=1300, lengths=[1300]),
+}
+
+
+def main():
+    ref_model, ref_loss, ref_utils = _import_reference()
+    os.makedirs(OUT, exist_ok=True)
+    torch.set_num_threads(1)  # bit-reproducible reductions
+
+    for name, case in CASES.items():
+        cfg, M, T = case["cfg"], case["M"], case["T"]
+        torch.manual_seed(123)
+        model = ref_model.ConvTasNet(**cfg)
+        init_sd = {k: v.detach().clone() for k, v in model.state_dict().items()}
+        g = torch.Generator().manual_seed(2025)
+        sources = 0.1 * torch.randn(M, cfg["C"], T, generator=g)
+        mixture = sources.sum(1) + 0.01 * torch.randn(M, T, generator=g)
+        lengths = torch.tensor(case["lengths"], dtype=torch.int64)
+
+        model.zero_grad()
+        est = model(mixture)
+        est_unmasked = est.detach().clone()
+        loss, max_snr, est_masked, reorder = ref_loss.cal_loss(sources.clone(), est, lengths)
+        loss.backward()
+        _, perms, idx = ref_loss.cal_si_snr_with_pit(sources.clone(), est_unmasked.clone(), lengths)
+
+        blob = {"mixture": mixture, "sources": sources, "lengths": lengths,
+                "est": est_unmasked, "loss": loss.detach(), "max_snr": max_snr.detach(),
+                "est_masked": est_masked.detach(), "reorder": reorder.detach(),
+                "perms": perms, "idx": idx}
+        for k, v in init_sd.items():
+            blob["w:" + k] = v
+        for k, v in model.named_parameters():
+            blob["g:" + k] = v.grad.detach()
+        np.savez_compressed(os.path.join(OUT, name + ".npz"),
+                            cfg=np.array(repr(cfg)),
+                            **{k: v.numpy() for k, v in blob.items()})
+        print(name, "loss", float(loss), "idx", idx.tolist(), "K", (T - cfg["L"]) // (cfg["L"] // 2) + 1)
+
+    # PIT-only cases: the reference demo shape (pit_criterion.py:118-126) with float data,
+    # plus a C=3 case whose best permutation is a 3-cycle (reorder quirk)
+    # and an exact tie (first permutation must win).
+    g = torch.Generator().manual_seed(7)
+    pit = {}
+    B, C, T = 2, 3, 12
+    src = torch.randn(B, C, T, generator=g)
+    est = torch.randn(B, C, T, generator=g)
+    lens = torch.tensor([T, T - 3])
+    e = est.clone()
+    loss, max_snr, est_m, reo = ref_loss.cal_loss(src, e, lens)
+    _, perms, idx = ref_loss.cal_si_snr_with_pit(src, est.clone(), lens)
+    pit.update(a_src=src, a_est=est, a_len=lens, a_loss=loss, a_max=max_snr, a_masked=est_m,
+               a_reo=reo, a_idx=idx, a_perms=perms)
+    B, C, T = 4, 3, 200
+    src = torch.randn(B, C, T, generator=g)
+    cyc = [[1, 2, 0], [2, 0, 1], [0, 2, 1], [0, 1, 2]]
+    est = torch.stack([src[b, cyc[b]] for b in range(B)]) + 0.05 * torch.randn(B, C, T, generator=g)
+    lens = torch.tensor([200, 150, 99, 200])
+    e = est.clone()
+    loss, max_snr, est_m, reo = ref_loss.cal_loss(src, e, lens)
+    _, perms, idx = ref_loss.cal_si_snr_with_pit(src, est.clone(), lens)
+    pit.update(b_src=src, b_est=est, b_len=lens, b_loss=loss, b_max=max_snr, b_masked=est_m,
+               b_reo=reo, b_idx=idx)
+    B, C, T = 1, 2, 64
+    s0 = torch.randn(1, 1, T, generator=g)
+    src = torch.cat([s0, s0], 1)           # identical targets -> both permutations tie exactly
+    est = torch.randn(B, C, T, generator=g)
+    est[:, 1] = est[:, 0]
+    lens = torch.tensor([T])
+    _, perms2, idx = ref_loss.cal_si_snr_with_pit(src, est.clone(), lens)
+    pit.update(c_src=src, c_est=est, c_len=lens, c_idx=idx)
+    np.savez_compressed(os.path.join(OUT, "pit_cases.npz"), **{k: v.numpy() for k, v in pit.items()})
+    print("pit idx", pit["a_idx"].tolist(), pit["b_idx"].tolist(), pit["c_idx"].tolist())
+
+    # overlap_and_add: the reference demo shape (utils.py:71-75) in float, plus L=20/16/odd cases
+    ola = {}
+    for tag, (M, C, K, L, step) in {"demo": (2, 2, 3, 4, 2), "l20": (1, 2, 17, 20, 10),
+                                    "l16": (2, 3, 9, 16, 8), "odd": (1, 1, 6, 5, 2)}.items():
+        sig = torch.randn(M, C, K, L, generator=g)
+        ola[tag + "_in"] = sig
+        ola[tag + "_out"] = ref_utils.overlap_and_add(sig, step)
+        ola[tag + "_step"] = torch.tensor(step)
+    np.savez_compressed(os.path.join(OUT, "ola_cases.npz"), **{k: v.numpy() for k, v in ola.items()})
+
+
+if __name__ == "__main__":
+    main()

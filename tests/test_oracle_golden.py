@@ -1,0 +1,60 @@
+"""Pins the oracle (oracle/convtasnet_oracle.py) to outputs of the unmodified
+reference recorded by oracle/make_golden.py (the reference has no
+golden vectors of its own)."""
+import pytest
+import torch
+
+from conftest import MODEL_CASES, load_golden, rel_l2
+from oracle import convtasnet_oracle as O
+
+
+@pytest.mark.parametrize("name", MODEL_CASES)
+def test_forward_loss_and_grads_match_reference(name):
+    torch.set_num_threads(1)
+    cfg, z = load_golden(name)
+    p = {k[2:]: v.clone().requires_grad_(True) for k, v in z.items() if k.startswith("w:")}
+    assert list(p) == list(O.param_shapes(*(cfg[k] for k in "NLBHPXRC"), cfg["causal"]))
+    est = O.forward(z["mixture"], p, cfg)
+    assert est.shape == z["est"].shape
+    assert rel_l2(est, z["est"]) < 2e-6
+    loss, max_snr, masked, reorder, idx = O.cal_loss(z["sources"], est, z["lengths"])
+    assert torch.equal(idx, z["idx"])                       # permutation choice: bit-exact
+    assert abs(float(loss) - float(z["loss"])) < 1e-4       # dB
+    assert torch.allclose(max_snr, z["max_snr"], atol=1e-4)
+    assert rel_l2(masked, z["est_masked"]) < 2e-6
+    assert rel_l2(reorder, z["reorder"]) < 2e-6
+    loss.backward()
+    for k, v in p.items():
+        assert rel_l2(v.grad, z["g:" + k]) < 5e-4, k
+
+
+def test_pit_cases():
+    z = load_golden("pit_cases")
+    for tag in "ab":
+        loss, max_snr, masked, reo, idx = O.cal_loss(z[tag + "_src"], z[tag + "_est"], z[tag + "_len"])
+        assert torch.equal(idx, z[tag + "_idx"])
+        assert torch.allclose(loss, z[tag + "_loss"], atol=1e-5)
+        assert torch.allclose(max_snr, z[tag + "_max"], atol=1e-5)
+        assert torch.equal(masked, z[tag + "_masked"])
+        assert torch.equal(reo, z[tag + "_reo"])
+    # exact tie -> first permutation
+    _, _, idx = O.cal_si_snr_with_pit(z["c_src"], z["c_est"], z["c_len"])
+    assert torch.equal(idx, z["c_idx"]) and int(idx[0]) == 0
+    assert torch.equal(O.cal_si_snr_with_pit(z["a_src"], z["a_est"], z["a_len"])[1], z["a_perms"])
+
+
+def test_overlap_and_add_cases():
+    z = load_golden("ola_cases")
+    for tag in ("demo", "l20", "l16", "odd"):
+        out = O.overlap_and_add(z[tag + "_in"], int(z[tag + "_step"]))
+        assert out.shape == z[tag + "_out"].shape
+        assert torch.allclose(out, z[tag + "_out"], atol=1e-6)
+
+
+def test_frame_geometry():
+    assert O.frame_geometry(32000, 20) == (10, 3199, 32000)
+    assert O.frame_geometry(32007, 20) == (10, 3199, 32000)
+    assert O.frame_geometry(480000, 20) == (10, 47999, 480000)
+    assert O.frame_geometry(32000, 16) == (8, 3999, 32000)
+    cfg = dict(N=256, L=20, B=256, H=512, P=3, X=8, R=4, C=2)
+    assert abs(O.forward_flops(cfg, 32000) / 1e9 - 55.341) < 1e-3
