@@ -1,0 +1,160 @@
+"""Drop-in for the reference's src/conv_tasnet.py: same class name, constructor,
+attributes, state_dict keys, checkpoint package and forward signature
+(conv_tasnet.py:13-94), with the computation done by hand-written sm_100a CUDA
+kernels in libctn_b200.so instead of a tree of torch.nn modules.
+
+Put this directory on PYTHONPATH in place of the reference's src/:
+    from conv_tasnet import ConvTasNet
+"""
+import math
+
+import torch
+import torch.nn as nn
+
+from ctn_b200 import _engine, _native
+from ctn_b200._layout import param_spec
+
+EPS = 1e-8
+
+
+class _Node(nn.Module):
+    """Parameter container; exists only so that state_dict keys nest exactly like the
+    reference's module tree.  It is never called."""
+
+    def forward(self, *a, **k):
+        raise RuntimeError("parameter container, not a layer; call ConvTasNet.forward")
+
+
+def _attach(root, dotted, param):
+    node = root
+    parts = dotted.split(".")
+    for name in parts[:-1]:
+        child = node._modules.get(name)
+        if child is None:
+            child = _Node()
+            node.add_module(name, child)
+        node = child
+    node.register_parameter(parts[-1], param)
+
+
+class ConvTasNet(nn.Module):
+    def __init__(self, N, L, B, H, P, X, R, C, norm_type="gLN", causal=False,
+                 mask_nonlinear='relu'):
+        """
+        Args (conv_tasnet.py:14-31):
+            N: Number of filters in autoencoder
+            L: Length of the filters (in samples)
+            B: Number of channels in bottleneck 1 x 1-conv block
+            H: Number of channels in convolutional blocks
+            P: Kernel size in convolutional blocks
+            X: Number of convolutional blocks in each repeat
+            R: Number of repeats
+            C: Number of speakers
+            norm_type: gLN or cLN (BN is not implemented)
+            causal: causal or non-causal
+            mask_nonlinear: 'relu' or 'softmax'
+        """
+        super(ConvTasNet, self).__init__()
+        self.N, self.L, self.B, self.H, self.P, self.X, self.R, self.C = N, L, B, H, P, X, R, C
+        self.norm_type = norm_type
+        self.causal = causal
+        self.mask_nonlinear = mask_nonlinear
+        _engine._check_cfg(self._cfg())
+        spec = param_spec(N, L, B, H, P, X, R, C, causal)
+        # Same RNG consumption as the reference's construction, so that the same seed gives
+        # the same initial weights: first the layers' default initialisers in creation
+        # order, then xavier_normal_ on every parameter with more than one dim (:41-43) --
+        # which includes the [1, C, 1] gamma / beta of every norm.
+        created = []
+        for key, (shape, kind) in spec.items():
+            t = torch.empty(shape)
+            if kind == "conv":
+                nn.init.kaiming_uniform_(t, a=math.sqrt(5))
+            elif kind == "ones":
+                t.fill_(1)
+            elif kind == "zeros":
+                t.zero_()
+            else:
+                t.fill_(0.25)
+            p = nn.Parameter(t)
+            _attach(self, key, p)
+            created.append(p)
+        for p in created:
+            if p.dim() > 1:
+                nn.init.xavier_normal_(p)
+        self._keys = list(spec)
+        self._engine = None
+
+    def _cfg(self):
+        return dict(N=self.N, L=self.L, B=self.B, H=self.H, P=self.P, X=self.X, R=self.R, C=self.C,
+                    norm_type=self.norm_type, causal=self.causal, mask_nonlinear=self.mask_nonlinear)
+
+    def _params(self):
+        sd = dict(self.named_parameters())
+        return {k: sd[k] for k in self._keys}
+
+    def engine(self):
+        """The per-module kernel orchestrator (workspaces, prepared weights, CUDA graphs)."""
+        eng = self.__dict__.get("_engine")
+        if eng is None:
+            eng = _engine.SeparationEngine(self._cfg())
+            self.__dict__["_engine"] = eng
+        return eng
+
+    def forward(self, mixture):
+        """
+        Args:
+            mixture: [M, T], M is batch size, T is #samples
+        Returns:
+            est_source: [M, C, T]
+        """
+        _native.require_cuda(mixture, "mixture")
+        params = self._params()
+        for k, p in params.items():
+            if not p.is_cuda or p.dtype != torch.float32 or p.device != mixture.device:
+                raise RuntimeError("parameter %s is %s on %s; float32 on %s is required (call model.cuda())"
+                                   % (k, p.dtype, p.device, mixture.device))
+        needs_grad = torch.is_grad_enabled() and (mixture.requires_grad or any(p.requires_grad for p in params.values()))
+        if needs_grad:
+            from ctn_b200 import _autograd
+            return _autograd.separate(self, mixture, params)
+        return self.engine().forward(mixture, {k: p.detach() for k, p in params.items()})
+
+    def __getstate__(self):
+        state = self.__dict__.copy()
+        state["_engine"] = None  # workspaces are per process / device
+        return state
+
+    @classmethod
+    def load_model(cls, path):
+        # Load to CPU
+        package = torch.load(path, map_location=lambda storage, loc: storage)
+        model = cls.load_model_from_package(package)
+        return model
+
+    @classmethod
+    def load_model_from_package(cls, package):
+        model = cls(package['N'], package['L'], package['B'], package['H'],
+                    package['P'], package['X'], package['R'], package['C'],
+                    norm_type=package['norm_type'], causal=package['causal'],
+                    mask_nonlinear=package['mask_nonlinear'])
+        model.load_state_dict(package['state_dict'])
+        return model
+
+    @staticmethod
+    def serialize(model, optimizer, epoch, tr_loss=None, cv_loss=None):
+        package = {
+            # hyper-parameter
+            'N': model.N, 'L': model.L, 'B': model.B, 'H': model.H,
+            'P': model.P, 'X': model.X, 'R': model.R, 'C': model.C,
+            'norm_type': model.norm_type, 'causal': model.causal,
+            'mask_nonlinear': model.mask_nonlinear,
+            # state
+            'state_dict': model.state_dict(),
+            'optim_dict': optimizer.state_dict(),
+            'epoch': epoch
+        }
+        if tr_loss is not None:
+            package['tr_loss'] = tr_loss
+            package['cv_loss'] = cv_loss
+        return package

@@ -1,0 +1,38 @@
+// Library-level plumbing of libctn_b200.so: error reporting, version, device query.
+#include <stdarg.h>
+#include <string.h>
+
+#include "common.cuh"
+
+namespace ctn {
+
+static thread_local char g_err[512] = "";
+
+void set_error(const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+
+int cuda_fail(cudaError_t e, const char* what) {
+    set_error("%s: %s (%s)", what, cudaGetErrorName(e), cudaGetErrorString(e));
+    return CTN_ERR_CUDA;
+}
+
+int sm_count() {
+    static int cached[64] = {0};  // per device ordinal; racing writers store the same value
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 148;
+    if (cached[dev] == 0) {
+        int n = 0;
+        if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) n = 148;
+        cached[dev] = n;
+    }
+    return cached[dev];
+}
+
+}  // namespace ctn
+
+extern "C" int ctn_version(void) { return 100; }
+extern "C" const char* ctn_last_error(void) { return ctn::g_err; }

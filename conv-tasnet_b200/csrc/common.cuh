@@ -1,0 +1,84 @@
+// Shared host/device helpers for libctn_b200.so.
+#pragma once
+#include <cuda_runtime.h>
+#include <cuda_bf16.h>
+#include <stdint.h>
+#include <stdio.h>
+
+#include "../../include/ctn_b200.h"
+
+namespace ctn {
+
+constexpr float kEps = 1e-8f;  // conv_tasnet.py:10, pit_criterion.py:9
+
+// ---------------------------------------------------------------- host side
+void set_error(const char* fmt, ...);
+int cuda_fail(cudaError_t e, const char* what);  // records the message, returns CTN_ERR_CUDA
+
+#define CTN_REQUIRE(cond, ...)            \
+    do {                                  \
+        if (!(cond)) {                    \
+            ::ctn::set_error(__VA_ARGS__); \
+            return CTN_ERR_INVALID;       \
+        }                                 \
+    } while (0)
+
+#define CTN_LAUNCH_CHECK(what)                                     \
+    do {                                                           \
+        cudaError_t e__ = cudaGetLastError();                      \
+        if (e__ != cudaSuccess) return ::ctn::cuda_fail(e__, what); \
+    } while (0)
+
+inline int ceil_div(int a, int b) { return (a + b - 1) / b; }
+int sm_count();  // multiprocessors of the current device (cached per device)
+
+// -------------------------------------------------------------- device side
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+__device__ __forceinline__ double warp_sum(double v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+
+__device__ __forceinline__ float prelu(float v, float slope) { return v >= 0.f ? v : slope * v; }
+
+// fp32 -> (hi, lo) bf16 pair, hi = rn(v), lo = rn(v - hi)
+__device__ __forceinline__ void split_bf16(float v, __nv_bfloat16& hi, __nv_bfloat16& lo) {
+    hi = __float2bfloat16_rn(v);
+    lo = __float2bfloat16_rn(v - __bfloat162float(hi));
+}
+__device__ __forceinline__ uint32_t pack_bf16(__nv_bfloat16 a, __nv_bfloat16 b) {
+    return static_cast<uint32_t>(__bfloat16_as_ushort(a)) | (static_cast<uint32_t>(__bfloat16_as_ushort(b)) << 16);
+}
+// split two floats, return packed hi pair and lo pair
+__device__ __forceinline__ void split_pack2(float v0, float v1, uint32_t& hi, uint32_t& lo) {
+    __nv_bfloat16 h0, l0, h1, l1;
+    split_bf16(v0, h0, l0);
+    split_bf16(v1, h1, l1);
+    hi = pack_bf16(h0, h1);
+    lo = pack_bf16(l0, l1);
+}
+
+// Whole-warp, fixed-order reduction of P (sum, sumsq) partials into (mean, rstd).
+// Every lane returns the same value.  count = number of elements the partials cover.
+__device__ __forceinline__ float2 gln_finalize_warp(const float2* __restrict__ part, int P, double count) {
+    const int lane = threadIdx.x & 31;
+    double s = 0.0, ss = 0.0;
+    for (int i = lane; i < P; i += 32) {
+        float2 v = __ldg(part + i);
+        s += static_cast<double>(v.x);
+        ss += static_cast<double>(v.y);
+    }
+    s = warp_sum(s);
+    ss = warp_sum(ss);
+    const double mean = s / count;
+    double var = ss / count - mean * mean;
+    var = var > 0.0 ? var : 0.0;
+    return make_float2(static_cast<float>(mean), static_cast<float>(1.0 / sqrt(var + 1e-8)));
+}
+
+}  // namespace ctn

@@ -1,0 +1,112 @@
+// Encoder: w[m, k, n] = relu(sum_l U[n, l] * mixture[m, k*hop + l]),  hop = L/2
+// (conv_tasnet.py:97-117), written frames-major as fp32 and as a bf16 (hi, lo)
+// pair, together with the per-frame mean / rstd over channels that the leading
+// cLN of the separator needs (conv_tasnet.py:167,326-327).  The framing gather is
+// done from a shared-memory copy of the tile's samples, so no [M, K, L] frame
+// tensor is materialised.  Memory-bound: reads 4*T, writes 8*N*K bytes per utterance.
+#include "common.cuh"
+
+namespace ctn {
+
+constexpr int kEncTile = 32;  // frames per CTA
+constexpr int kEncWarps = 8;
+
+__global__ void __launch_bounds__(kEncWarps * 32)
+encoder_fwd_kernel(const float* __restrict__ mixture, const float* __restrict__ U, int T, int N, int L, int K,
+                   float* __restrict__ w_f32, __nv_bfloat16* __restrict__ w_hi, __nv_bfloat16* __restrict__ w_lo,
+                   float2* __restrict__ rowstat) {
+    extern __shared__ float enc_smem[];
+    const int hop = L / 2;
+    float* Ut = enc_smem;       // [L][N]
+    float* xs = enc_smem + L * N;  // [(tile-1)*hop + L]
+    const int m = blockIdx.y;
+    const int k0 = blockIdx.x * kEncTile;
+    const int nk = min(kEncTile, K - k0);
+    const int nsamp = (nk - 1) * hop + L;
+    for (int i = threadIdx.x; i < N * L; i += blockDim.x) {
+        const int n = i / L, l = i - n * L;
+        Ut[l * N + n] = U[i];
+    }
+    const float* src = mixture + static_cast<long long>(m) * T + static_cast<long long>(k0) * hop;
+    for (int i = threadIdx.x; i < nsamp; i += blockDim.x) xs[i] = src[i];
+    __syncthreads();
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const bool pair = (N & 1) == 0;
+    for (int r = warp; r < nk; r += kEncWarps) {
+        const float* x = xs + r * hop;
+        const long long grow = static_cast<long long>(m) * K + k0 + r;
+        float s = 0.f, ss = 0.f;
+        if (pair) {
+            for (int n = 2 * lane; n < N; n += 64) {
+                float a0 = 0.f, a1 = 0.f;
+                for (int l = 0; l < L; ++l) {
+                    const float xv = x[l];
+                    const float2 u = *reinterpret_cast<const float2*>(Ut + l * N + n);
+                    a0 = fmaf(u.x, xv, a0);
+                    a1 = fmaf(u.y, xv, a1);
+                }
+                a0 = fmaxf(a0, 0.f), a1 = fmaxf(a1, 0.f);
+                s += a0 + a1;
+                ss = fmaf(a0, a0, fmaf(a1, a1, ss));
+                if (w_f32) *reinterpret_cast<float2*>(w_f32 + grow * N + n) = make_float2(a0, a1);
+                if (w_hi) {
+                    uint32_t h, lo;
+                    split_pack2(a0, a1, h, lo);
+                    *reinterpret_cast<uint32_t*>(w_hi + grow * N + n) = h;
+                    *reinterpret_cast<uint32_t*>(w_lo + grow * N + n) = lo;
+                }
+            }
+        } else {
+            for (int n = lane; n < N; n += 32) {
+                float a0 = 0.f;
+                for (int l = 0; l < L; ++l) a0 = fmaf(Ut[l * N + n], x[l], a0);
+                a0 = fmaxf(a0, 0.f);
+                s += a0;
+                ss = fmaf(a0, a0, ss);
+                if (w_f32) w_f32[grow * N + n] = a0;
+                if (w_hi) {
+                    __nv_bfloat16 h, lo;
+                    split_bf16(a0, h, lo);
+                    w_hi[grow * N + n] = h;
+                    w_lo[grow * N + n] = lo;
+                }
+            }
+        }
+        if (rowstat) {
+            s = warp_sum(s);
+            ss = warp_sum(ss);
+            if (lane == 0) {
+                const float mean = s / N;
+                const float var = fmaxf(ss / N - mean * mean, 0.f);
+                rowstat[grow] = make_float2(mean, rsqrtf(var + kEps));
+            }
+        }
+    }
+}
+
+}  // namespace ctn
+
+extern "C" int ctn_encoder_fwd(const float* mixture, const float* U, int M, int T, int N, int L, float* w_f32,
+                               void* w_hi, void* w_lo, void* rowstat, void* stream) {
+    using namespace ctn;
+    CTN_REQUIRE(mixture && U, "ctn_encoder_fwd: NULL input");
+    CTN_REQUIRE(M > 0 && N > 0 && L >= 2, "ctn_encoder_fwd: bad shape M=%d N=%d L=%d", M, N, L);
+    CTN_REQUIRE(T >= L, "ctn_encoder_fwd: T=%d shorter than the filter length L=%d", T, L);
+    CTN_REQUIRE((w_hi == nullptr) == (w_lo == nullptr), "ctn_encoder_fwd: w_hi/w_lo must be given together");
+    const int hop = L / 2;
+    const int K = (T - L) / hop + 1;
+    const size_t smem = (static_cast<size_t>(L) * N + (kEncTile - 1) * hop + L) * sizeof(float);
+    if (smem > 48 * 1024) {
+        CTN_REQUIRE(smem <= 200 * 1024, "ctn_encoder_fwd: N*L=%d too large for shared memory", N * L);
+        cudaError_t e = cudaFuncSetAttribute(encoder_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                             static_cast<int>(smem));
+        if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(encoder_fwd_kernel)");
+    }
+    dim3 grid(ceil_div(K, kEncTile), M);
+    encoder_fwd_kernel<<<grid, kEncWarps * 32, smem, static_cast<cudaStream_t>(stream)>>>(
+        mixture, U, T, N, L, K, w_f32, static_cast<__nv_bfloat16*>(w_hi), static_cast<__nv_bfloat16*>(w_lo),
+        static_cast<float2*>(rowstat));
+    CTN_LAUNCH_CHECK("encoder_fwd_kernel");
+    return CTN_OK;
+}

@@ -1,0 +1,495 @@
+// 1x1 convolutions of the separator as one GEMM over all frames of the batch:
+//     out[r, n] = sum_k a[r, k] * w[n, k]      r = m*K + frame, both operands K-major.
+// Reference: nn.Conv1d(.., 1, bias=False) at conv_tasnet.py:169 (bottleneck), :217
+// (TemporalBlock conv1x1), :256 (pointwise, + residual :237), :185 (mask conv).
+//
+// Tensor-core path (sm_100a): persistent, warp-specialised CTA of 6 warps
+//   warp 0    TMA producer   (cp.async.bulk.tensor, 128B-swizzled K-major tiles)
+//   warp 1    MMA issuer     (tcgen05.mma kind::f16, 128 x BN x 16, accumulators in TMEM)
+//   warps 2-5 epilogue       (tcgen05.ld 32x32b -> registers -> fused epilogue -> global)
+// Operands are bf16 (hi, lo) pairs; each k-step issues hi*hi + lo*hi + hi*lo so the
+// product carries 16 mantissa bits per operand with fp32 accumulation (plain bf16
+// fails the 1e-3 waveform tolerance).  Two TMEM accumulator
+// stages let the MMAs of tile i+1 run under the epilogue of tile i.
+//
+// The epilogue fuses: the folded input norm (scale / shift / per-channel bias, see
+// ctn_weight_prep), the residual add, the (hi, lo) split of the output and the
+// (sum, sumsq) statistics of the next gLN / cLN (after an optional PReLU).
+#include <cuda.h>
+
+#include "common.cuh"
+#include "ptx.cuh"
+
+namespace ctn {
+
+struct EpiParams {
+    int K, Cout, groups, tiles_per_utt;
+    float* out_f32;
+    __nv_bfloat16* out_hi;
+    __nv_bfloat16* out_lo;
+    const float* resid;
+    const float* col_g;
+    const float* col_bias;
+    int in_norm;
+    const float2* in_stat;
+    int in_P;
+    double in_count;
+    int out_stat;
+    float2* out_stat_buf;
+    int out_P;
+    const float* stat_prelu;
+};
+
+// One thread owns output row `grow` (valid or not) and 32 consecutive columns
+// starting at n0 whose accumulators are in v[].  VEC: Cout % 8 == 0 so 4-wide
+// groups are entirely inside or outside [0, Cout).
+template <bool VEC>
+__device__ __forceinline__ void epilogue_chunk(const EpiParams& ep, float (&v)[32], long long grow, int n0,
+                                               bool valid, float s, float t, float slope, bool use_slope,
+                                               float& ls, float& lss) {
+    if (n0 >= ep.Cout) return;
+    const int ncols = min(32, ep.Cout - n0);
+    // folded norm + bias
+    if (ep.col_g != nullptr || ep.col_bias != nullptr || ep.in_norm != CTN_NORM_NONE) {
+#pragma unroll
+        for (int j = 0; j < 32; ++j) {
+            if (j < ncols) {
+                float g = ep.col_g ? __ldg(ep.col_g + n0 + j) : 0.f;
+                float b = ep.col_bias ? __ldg(ep.col_bias + n0 + j) : 0.f;
+                v[j] = fmaf(s, v[j], fmaf(t, g, b));
+            }
+        }
+    }
+    if (!valid) return;
+    const long long base = grow * ep.Cout + n0;
+    if (ep.resid != nullptr) {
+        if (VEC) {
+#pragma unroll
+            for (int j = 0; j < 32; j += 4) {
+                if (j < ncols) {
+                    float4 r = *reinterpret_cast<const float4*>(ep.resid + base + j);
+                    v[j] += r.x, v[j + 1] += r.y, v[j + 2] += r.z, v[j + 3] += r.w;
+                }
+            }
+        } else {
+#pragma unroll
+            for (int j = 0; j < 32; ++j)
+                if (j < ncols) v[j] += ep.resid[base + j];
+        }
+    }
+    if (ep.out_stat != CTN_NORM_NONE) {
+#pragma unroll
+        for (int j = 0; j < 32; ++j) {
+            if (j < ncols) {
+                float x = use_slope ? prelu(v[j], slope) : v[j];
+                ls += x;
+                lss = fmaf(x, x, lss);
+            }
+        }
+    }
+    if (ep.out_f32 != nullptr) {
+        if (VEC) {
+#pragma unroll
+            for (int j = 0; j < 32; j += 4)
+                if (j < ncols)
+                    *reinterpret_cast<float4*>(ep.out_f32 + base + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+        } else {
+#pragma unroll
+            for (int j = 0; j < 32; ++j)
+                if (j < ncols) ep.out_f32[base + j] = v[j];
+        }
+    }
+    if (ep.out_hi != nullptr) {
+        if (VEC) {
+#pragma unroll
+            for (int j = 0; j < 32; j += 8) {
+                if (j < ncols) {
+                    uint4 h, l;
+                    split_pack2(v[j], v[j + 1], h.x, l.x);
+                    split_pack2(v[j + 2], v[j + 3], h.y, l.y);
+                    split_pack2(v[j + 4], v[j + 5], h.z, l.z);
+                    split_pack2(v[j + 6], v[j + 7], h.w, l.w);
+                    *reinterpret_cast<uint4*>(ep.out_hi + base + j) = h;
+                    *reinterpret_cast<uint4*>(ep.out_lo + base + j) = l;
+                }
+            }
+        } else {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) {
+                if (j < ncols) {
+                    __nv_bfloat16 h, l;
+                    split_bf16(v[j], h, l);
+                    ep.out_hi[base + j] = h;
+                    ep.out_lo[base + j] = l;
+                }
+            }
+        }
+    }
+}
+
+// Per-tile scale/shift of the folded input norm.  Warp-collective (gLN path).
+__device__ __forceinline__ void epilogue_row_affine(const EpiParams& ep, int m, long long grow, bool valid, float& s,
+                                                    float& t) {
+    s = 1.f, t = 0.f;
+    if (ep.in_norm == CTN_NORM_GLN) {
+        float2 st = gln_finalize_warp(ep.in_stat + static_cast<long long>(m) * ep.in_P, ep.in_P, ep.in_count);
+        s = st.y, t = -st.y * st.x;
+    } else if (ep.in_norm == CTN_NORM_CLN) {
+        if (valid) {
+            float2 st = __ldg(ep.in_stat + grow);
+            s = st.y, t = -st.y * st.x;
+        }
+    }
+}
+
+// Flush the statistics of one 128-column group.  Warp-collective (gLN path).
+__device__ __forceinline__ void epilogue_flush_stats(const EpiParams& ep, int m, int tk, int grp, int ew,
+                                                     long long grow, bool valid, float& ls, float& lss) {
+    if (ep.out_stat == CTN_NORM_GLN) {
+        float ws = warp_sum(ls), wss = warp_sum(lss);
+        if ((threadIdx.x & 31) == 0)
+            ep.out_stat_buf[static_cast<long long>(m) * ep.out_P + (tk * ep.groups + grp) * 4 + ew] =
+                make_float2(ws, wss);
+    } else if (ep.out_stat == CTN_NORM_CLN) {
+        if (valid) ep.out_stat_buf[grow * ep.groups + grp] = make_float2(ls, lss);
+    }
+    ls = 0.f, lss = 0.f;
+}
+
+// ======================================================================
+// tcgen05 kernel
+// ======================================================================
+constexpr int kBM = CTN_ROW_TILE;  // 128 rows = TMEM lanes
+constexpr int kBK = 64;            // bf16 elements per k-block = one 128B swizzle atom
+constexpr int kTcThreads = 192;
+
+template <int BN>
+struct TcCfg {
+    static constexpr int kStages = (BN == 256) ? 2 : 3;
+    static constexpr int kABytes = kBM * kBK * 2;  // one of hi / lo
+    static constexpr int kWBytes = BN * kBK * 2;
+    static constexpr int kStageBytes = 2 * kABytes + 2 * kWBytes;
+    static constexpr int kBarBytes = 256;
+    static constexpr int kSmemBytes = kStages * kStageBytes + kBarBytes + 1024;  // + alignment slack
+    static constexpr int kTmemCols = 2 * BN;
+};
+
+template <int BN>
+__global__ void __launch_bounds__(kTcThreads, 1)
+gemm_tc_kernel(const __grid_constant__ CUtensorMap tm_a_hi, const __grid_constant__ CUtensorMap tm_a_lo,
+               const __grid_constant__ CUtensorMap tm_w_hi, const __grid_constant__ CUtensorMap tm_w_lo,
+               const EpiParams ep, int Cin, int n_tiles, int total_tiles) {
+    using Cfg = TcCfg<BN>;
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + Cfg::kStages * Cfg::kStageBytes);
+    uint64_t* empty_bar = full_bar + Cfg::kStages;
+    uint64_t* tfull_bar = empty_bar + Cfg::kStages;
+    uint64_t* tempty_bar = tfull_bar + 2;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 2);
+
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+    const int nkb = (Cin + kBK - 1) / kBK;
+
+    if (warp == 0 && lane == 0) {
+        ptx::prefetch_tmap(&tm_a_hi);
+        ptx::prefetch_tmap(&tm_a_lo);
+        ptx::prefetch_tmap(&tm_w_hi);
+        ptx::prefetch_tmap(&tm_w_lo);
+        for (int i = 0; i < Cfg::kStages; ++i) {
+            ptx::mbar_init(full_bar + i, 1);
+            ptx::mbar_init(empty_bar + i, 1);
+        }
+        for (int i = 0; i < 2; ++i) {
+            ptx::mbar_init(tfull_bar + i, 1);
+            ptx::mbar_init(tempty_bar + i, 128);
+        }
+        ptx::fence_mbar_init();
+    } else if (warp == 1) {
+        ptx::tmem_alloc(tmem_slot, Cfg::kTmemCols);
+        ptx::tmem_relinquish();
+    }
+    ptx::tc_fence_before();
+    __syncthreads();
+    ptx::tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        // ------------------------------------------------ TMA producer
+        if (lane == 0) {
+            int stage = 0;
+            uint32_t phase = 0;
+            for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+                const int tn = tile % n_tiles;
+                const int rt = tile / n_tiles;
+                const int m = rt / ep.tiles_per_utt, tk = rt % ep.tiles_per_utt;
+                const int row0 = m * ep.K + tk * kBM;
+                const int n0 = tn * BN;
+                for (int kb = 0; kb < nkb; ++kb) {
+                    ptx::mbar_wait(empty_bar + stage, phase ^ 1);
+                    uint8_t* st = smem + stage * Cfg::kStageBytes;
+                    ptx::mbar_expect_tx(full_bar + stage, Cfg::kStageBytes);
+                    ptx::tma_load_2d(st, &tm_a_hi, full_bar + stage, kb * kBK, row0);
+                    ptx::tma_load_2d(st + Cfg::kABytes, &tm_a_lo, full_bar + stage, kb * kBK, row0);
+                    ptx::tma_load_2d(st + 2 * Cfg::kABytes, &tm_w_hi, full_bar + stage, kb * kBK, n0);
+                    ptx::tma_load_2d(st + 2 * Cfg::kABytes + Cfg::kWBytes, &tm_w_lo, full_bar + stage, kb * kBK, n0);
+                    if (++stage == Cfg::kStages) stage = 0, phase ^= 1;
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // -------------------------------------------------- MMA issuer
+        if (lane == 0) {
+            constexpr uint32_t idesc = ptx::make_idesc_bf16(kBM, BN, 0, 0);
+            int stage = 0;
+            uint32_t phase = 0;
+            int it = 0;
+            for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it) {
+                const int as = it & 1;
+                const uint32_t aphase = (it >> 1) & 1;
+                ptx::mbar_wait(tempty_bar + as, aphase ^ 1);
+                ptx::tc_fence_after();
+                const uint32_t d_tmem = tmem_base + as * BN;
+                for (int kb = 0; kb < nkb; ++kb) {
+                    ptx::mbar_wait(full_bar + stage, phase);
+                    ptx::tc_fence_after();
+                    const uint32_t sa = ptx::smem_u32(smem + stage * Cfg::kStageBytes);
+                    // K-major, 128B swizzle: 8-row groups are 1024 B apart (SBO); LBO unused.
+                    const uint64_t a_hi = ptx::make_smem_desc(sa, 0, 1024, ptx::kLayoutSwizzle128B);
+                    const uint64_t a_lo = ptx::make_smem_desc(sa + Cfg::kABytes, 0, 1024, ptx::kLayoutSwizzle128B);
+                    const uint64_t w_hi = ptx::make_smem_desc(sa + 2 * Cfg::kABytes, 0, 1024, ptx::kLayoutSwizzle128B);
+                    const uint64_t w_lo =
+                        ptx::make_smem_desc(sa + 2 * Cfg::kABytes + Cfg::kWBytes, 0, 1024, ptx::kLayoutSwizzle128B);
+#pragma unroll
+                    for (int k = 0; k < kBK / 16; ++k) {
+                        const uint64_t adv = static_cast<uint64_t>((k * 16 * 2) >> 4);  // +32 B per k-step
+                        ptx::umma_bf16(d_tmem, a_hi + adv, w_hi + adv, idesc, (kb | k) != 0);
+                        ptx::umma_bf16(d_tmem, a_lo + adv, w_hi + adv, idesc, 1);
+                        ptx::umma_bf16(d_tmem, a_hi + adv, w_lo + adv, idesc, 1);
+                    }
+                    ptx::umma_commit(empty_bar + stage);  // frees the smem stage when these MMAs retire
+                    if (kb == nkb - 1) ptx::umma_commit(tfull_bar + as);
+                    if (++stage == Cfg::kStages) stage = 0, phase ^= 1;
+                }
+            }
+        }
+    } else {
+        // ---------------------------------------------------- epilogue
+        const int ew = warp & 3;  // TMEM lane quarter this warp may read
+        float slope = 0.f;
+        const bool use_slope = ep.stat_prelu != nullptr;
+        if (use_slope) slope = __ldg(ep.stat_prelu);
+        int it = 0;
+        for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it) {
+            const int as = it & 1;
+            const uint32_t aphase = (it >> 1) & 1;
+            const int tn = tile % n_tiles;
+            const int rt = tile / n_tiles;
+            const int m = rt / ep.tiles_per_utt, tk = rt % ep.tiles_per_utt;
+            const int k = tk * kBM + ew * 32 + lane;
+            const bool valid = k < ep.K;
+            const long long grow = static_cast<long long>(m) * ep.K + k;
+            float s, t;
+            epilogue_row_affine(ep, m, grow, valid, s, t);
+
+            ptx::mbar_wait(tfull_bar + as, aphase);
+            ptx::tc_fence_after();
+            float ls = 0.f, lss = 0.f;
+#pragma unroll 1
+            for (int c = 0; c < BN / 32; ++c) {
+                const int n0 = tn * BN + c * 32;
+                if (n0 < ep.Cout) {
+                    uint32_t r[32];
+                    ptx::tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(ew * 32) << 16) + as * BN + c * 32, r);
+                    ptx::tmem_ld_wait();
+                    float v[32];
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
+                    epilogue_chunk<true>(ep, v, grow, n0, valid, s, t, slope, use_slope, ls, lss);
+                }
+                if ((c & 3) == 3) {
+                    const int grp = (tn * BN + c * 32) / CTN_COL_TILE;
+                    if (grp < ep.groups) epilogue_flush_stats(ep, m, tk, grp, ew, grow, valid, ls, lss);
+                }
+            }
+            ptx::tc_fence_before();
+            ptx::mbar_arrive(tempty_bar + as);
+        }
+    }
+
+    ptx::tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        ptx::tc_fence_after();
+        ptx::tmem_dealloc(tmem_base, Cfg::kTmemCols);
+    }
+}
+
+// ======================================================================
+// SIMT kernel: same tiling, statistics layout and epilogue; any Cin / Cout.
+// One thread per output row, 32 columns at a time.  Used for shapes the
+// tensor-core path does not take (channel counts not multiples of 8).
+// ======================================================================
+__global__ void __launch_bounds__(128)
+gemm_simt_kernel(const __nv_bfloat16* __restrict__ a_hi, const __nv_bfloat16* __restrict__ a_lo,
+                 const __nv_bfloat16* __restrict__ w_hi, const __nv_bfloat16* __restrict__ w_lo, const EpiParams ep,
+                 int Cin) {
+    const int rt = blockIdx.x;
+    const int m = rt / ep.tiles_per_utt, tk = rt % ep.tiles_per_utt;
+    const int ew = threadIdx.x >> 5;
+    const int k = tk * kBM + threadIdx.x;
+    const bool valid = k < ep.K;
+    const long long grow = static_cast<long long>(m) * ep.K + k;
+    float slope = 0.f;
+    const bool use_slope = ep.stat_prelu != nullptr;
+    if (use_slope) slope = __ldg(ep.stat_prelu);
+    float s, t;
+    epilogue_row_affine(ep, m, grow, valid, s, t);
+    float ls = 0.f, lss = 0.f;
+    for (int grp = 0; grp < ep.groups; ++grp) {
+        for (int c = 0; c < CTN_COL_TILE / 32; ++c) {
+            const int n0 = grp * CTN_COL_TILE + c * 32;
+            if (n0 >= ep.Cout) break;
+            float v[32];
+#pragma unroll
+            for (int j = 0; j < 32; ++j) v[j] = 0.f;
+            if (valid) {
+                for (int kk = 0; kk < Cin; ++kk) {
+                    const float a = __bfloat162float(a_hi[grow * Cin + kk]) + __bfloat162float(a_lo[grow * Cin + kk]);
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) {
+                        if (n0 + j < ep.Cout) {
+                            const long long wi = static_cast<long long>(n0 + j) * Cin + kk;
+                            v[j] = fmaf(a, __bfloat162float(w_hi[wi]) + __bfloat162float(w_lo[wi]), v[j]);
+                        }
+                    }
+                }
+            }
+            epilogue_chunk<false>(ep, v, grow, n0, valid, s, t, slope, use_slope, ls, lss);
+        }
+        epilogue_flush_stats(ep, m, tk, grp, ew, grow, valid, ls, lss);
+    }
+}
+
+// ======================================================================
+// host side
+// ======================================================================
+typedef CUresult (*PFN_encodeTiled)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                    const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                    CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static PFN_encodeTiled get_encode_fn() {
+    static PFN_encodeTiled fn = nullptr;  // benign race: every thread resolves the same pointer
+    if (fn == nullptr) {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult qres;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres) == cudaSuccess &&
+            qres == cudaDriverEntryPointSuccess)
+            fn = reinterpret_cast<PFN_encodeTiled>(p);
+    }
+    return fn;
+}
+
+// bf16 [rows, cols] row-major, box = 64 columns x box_rows rows, 128B swizzle, zero OOB fill
+int make_tmap_bf16_kmajor(CUtensorMap* tm, const void* ptr, long long rows, int cols, int box_rows) {
+    PFN_encodeTiled enc = get_encode_fn();
+    if (!enc) {
+        set_error("cuTensorMapEncodeTiled not available from the driver");
+        return CTN_ERR_CUDA;
+    }
+    cuuint64_t dims[2] = {static_cast<cuuint64_t>(cols), static_cast<cuuint64_t>(rows)};
+    cuuint64_t strides[1] = {static_cast<cuuint64_t>(cols) * 2};
+    cuuint32_t box[2] = {static_cast<cuuint32_t>(kBK), static_cast<cuuint32_t>(box_rows)};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = enc(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), dims, strides, box, estr,
+                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) {
+        set_error("cuTensorMapEncodeTiled failed (%d) ptr=%p rows=%lld cols=%d", static_cast<int>(r), ptr, rows, cols);
+        return CTN_ERR_CUDA;
+    }
+    return CTN_OK;
+}
+
+template <int BN>
+static int launch_tc(const ctn_gemm_args& a, const EpiParams& ep, cudaStream_t stream) {
+    using Cfg = TcCfg<BN>;
+    CUtensorMap ta_hi, ta_lo, tw_hi, tw_lo;
+    const long long R = static_cast<long long>(a.M) * a.K;
+    int rc;
+    if ((rc = make_tmap_bf16_kmajor(&ta_hi, a.a_hi, R, a.Cin, kBM)) != CTN_OK) return rc;
+    if ((rc = make_tmap_bf16_kmajor(&ta_lo, a.a_lo, R, a.Cin, kBM)) != CTN_OK) return rc;
+    if ((rc = make_tmap_bf16_kmajor(&tw_hi, a.w_hi, a.Cout, a.Cin, BN)) != CTN_OK) return rc;
+    if ((rc = make_tmap_bf16_kmajor(&tw_lo, a.w_lo, a.Cout, a.Cin, BN)) != CTN_OK) return rc;
+    static bool attr_set = false;  // idempotent; set once per process per instantiation
+    if (!attr_set) {
+        cudaError_t e = cudaFuncSetAttribute(gemm_tc_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                             Cfg::kSmemBytes);
+        if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(gemm_tc_kernel)");
+        attr_set = true;
+    }
+    const int n_tiles = ceil_div(a.Cout, BN);
+    const int total = a.M * ep.tiles_per_utt * n_tiles;
+    const int grid = total < sm_count() ? total : sm_count();
+    gemm_tc_kernel<BN><<<grid, kTcThreads, Cfg::kSmemBytes, stream>>>(ta_hi, ta_lo, tw_hi, tw_lo, ep, a.Cin, n_tiles,
+                                                                      total);
+    CTN_LAUNCH_CHECK("gemm_tc_kernel");
+    return CTN_OK;
+}
+
+}  // namespace ctn
+
+using namespace ctn;
+
+extern "C" int ctn_gemm_gln_partials(int K, int Cout) {
+    return ceil_div(K, CTN_ROW_TILE) * ceil_div(Cout, CTN_COL_TILE) * 4;
+}
+extern "C" int ctn_gemm_cln_groups(int Cout) { return ceil_div(Cout, CTN_COL_TILE); }
+
+extern "C" int ctn_gemm1x1(const ctn_gemm_args* args, void* stream_) {
+    CTN_REQUIRE(args != nullptr, "ctn_gemm1x1: args is NULL");
+    const ctn_gemm_args& a = *args;
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    CTN_REQUIRE(a.M > 0 && a.K > 0 && a.Cin > 0 && a.Cout > 0, "ctn_gemm1x1: non-positive shape M=%d K=%d Cin=%d Cout=%d",
+                a.M, a.K, a.Cin, a.Cout);
+    CTN_REQUIRE(static_cast<long long>(a.M) * a.K < (1ll << 31), "ctn_gemm1x1: M*K exceeds 2^31 rows");
+    CTN_REQUIRE(a.a_hi && a.a_lo && a.w_hi && a.w_lo, "ctn_gemm1x1: NULL operand");
+    CTN_REQUIRE((a.out_hi == nullptr) == (a.out_lo == nullptr), "ctn_gemm1x1: out_hi/out_lo must be given together");
+    CTN_REQUIRE(a.out_f32 || a.out_hi, "ctn_gemm1x1: no output requested");
+    CTN_REQUIRE(a.in_norm >= 0 && a.in_norm <= 2 && a.out_stat >= 0 && a.out_stat <= 2, "ctn_gemm1x1: bad norm mode");
+    CTN_REQUIRE(a.in_norm == CTN_NORM_NONE || (a.in_stat && a.col_g), "ctn_gemm1x1: in_norm needs in_stat and col_g");
+    CTN_REQUIRE(a.in_norm != CTN_NORM_GLN || (a.in_P > 0 && a.in_count > 0), "ctn_gemm1x1: gLN needs in_P, in_count");
+    CTN_REQUIRE(a.out_stat == CTN_NORM_NONE || a.out_stat_buf, "ctn_gemm1x1: out_stat needs out_stat_buf");
+
+    EpiParams ep;
+    ep.K = a.K, ep.Cout = a.Cout;
+    ep.groups = ceil_div(a.Cout, CTN_COL_TILE);
+    ep.tiles_per_utt = ceil_div(a.K, kBM);
+    ep.out_f32 = a.out_f32;
+    ep.out_hi = static_cast<__nv_bfloat16*>(a.out_hi);
+    ep.out_lo = static_cast<__nv_bfloat16*>(a.out_lo);
+    ep.resid = a.resid, ep.col_g = a.col_g, ep.col_bias = a.col_bias;
+    ep.in_norm = a.in_norm, ep.in_stat = static_cast<const float2*>(a.in_stat), ep.in_P = a.in_P;
+    ep.in_count = a.in_count;
+    ep.out_stat = a.out_stat, ep.out_stat_buf = static_cast<float2*>(a.out_stat_buf);
+    ep.out_P = ctn_gemm_gln_partials(a.K, a.Cout);
+    ep.stat_prelu = a.stat_prelu;
+
+    auto aligned16 = [](const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; };
+    const bool tc_ok = !a.force_simt && a.Cin % 8 == 0 && a.Cout % 8 == 0 && aligned16(a.a_hi) && aligned16(a.a_lo) &&
+                       aligned16(a.w_hi) && aligned16(a.w_lo) && aligned16(a.out_f32) && aligned16(a.out_hi) &&
+                       aligned16(a.out_lo) && aligned16(a.resid);
+    if (tc_ok) {
+        // 256-wide tiles halve the re-reads of the activation tile but need enough tiles to fill the SMs
+        const long long tiles256 = static_cast<long long>(a.M) * ep.tiles_per_utt * ceil_div(a.Cout, 256);
+        if (a.Cout % 256 == 0 && tiles256 >= 2ll * sm_count()) return launch_tc<256>(a, ep, stream);
+        return launch_tc<128>(a, ep, stream);
+    }
+    const int grid = a.M * ep.tiles_per_utt;
+    gemm_simt_kernel<<<grid, 128, 0, stream>>>(
+        static_cast<const __nv_bfloat16*>(a.a_hi), static_cast<const __nv_bfloat16*>(a.a_lo),
+        static_cast<const __nv_bfloat16*>(a.w_hi), static_cast<const __nv_bfloat16*>(a.w_lo), ep, a.Cin);
+    CTN_LAUNCH_CHECK("gemm_simt_kernel");
+    return CTN_OK;
+}

@@ -1,0 +1,281 @@
+"""Host-side orchestration of the separation forward pass on one GPU.
+
+PyTorch is used for device memory and streams only; every arithmetic step is a
+call into libctn_b200.so.  The sequence mirrors ConvTasNet.forward
+(conv_tasnet.py:45-60) but in fused form:
+
+  encoder (+ cLN statistics)                          ctn_encoder_fwd
+  cLN folded into the bottleneck 1x1                  ctn_gemm1x1   (in_norm = CLN)
+  per TemporalBlock (conv_tasnet.py:212-272):
+    conv1x1 (+ statistics of PReLU output)            ctn_gemm1x1   (out_stat)
+    PReLU, norm, depthwise, PReLU (+ statistics)      ctn_dwconv_fwd
+    norm folded into pointwise 1x1, + residual        ctn_gemm1x1   (in_norm, resid)
+  mask 1x1                                            ctn_gemm1x1
+  mask non-linearity, decoder, overlap-add, pad       ctn_decoder_fwd
+
+A `_Plan` owns the static workspaces for one (M, T) shape and the prebuilt
+argument structs, so a forward is a flat list of C calls on the current stream;
+it can be captured into a CUDA graph (`use_graph`) to remove launch gaps.
+"""
+import ctypes as C
+
+import torch
+
+from . import _native as nat
+from ._layout import block_keys, frame_geometry
+
+_NORM = {"gLN": nat.NORM_GLN, "cLN": nat.NORM_CLN}
+_MASK = {"relu": nat.MASK_RELU, "softmax": nat.MASK_SOFTMAX}
+
+
+def _check_cfg(cfg):
+    if cfg["norm_type"] not in _NORM:
+        # conv_tasnet.py:300-303 falls through to BatchNorm1d; batch statistics couple the
+        # utterances of a batch, which the utterance-sharded design excludes
+        raise NotImplementedError("norm_type=%r: only gLN and cLN are implemented" % (cfg["norm_type"],))
+    if cfg["mask_nonlinear"] not in _MASK:
+        raise ValueError("Unsupported mask non-linear function")  # conv_tasnet.py:208
+
+
+class _Prepared:
+    """Weight-derived buffers: bf16 (hi, lo) splits with the preceding norm's affine folded in."""
+
+    def __init__(self, cfg, device):
+        N, B, H, C = cfg["N"], cfg["B"], cfg["H"], cfg["C"]
+        bf = dict(dtype=torch.bfloat16, device=device)
+        f32 = dict(dtype=torch.float32, device=device)
+        self.bott = (torch.empty(B, N, **bf), torch.empty(B, N, **bf), torch.empty(B, **f32), torch.empty(B, **f32))
+        self.blocks = []
+        for _ in range(cfg["R"] * cfg["X"]):
+            self.blocks.append(dict(
+                w1=(torch.empty(H, B, **bf), torch.empty(H, B, **bf)),
+                w2=(torch.empty(B, H, **bf), torch.empty(B, H, **bf), torch.empty(B, **f32), torch.empty(B, **f32))))
+        self.mask = (torch.empty(C * N, B, **bf), torch.empty(C * N, B, **bf))
+        self.fingerprint = None
+
+    def refresh(self, cfg, params):
+        fp = tuple((p.data_ptr(), p._version) for p in params.values())
+        if fp == self.fingerprint:
+            return
+        lib, s = nat.lib(), nat.stream()
+        N, B, H, C = cfg["N"], cfg["B"], cfg["H"], cfg["C"]
+
+        def prep(W, rows, cols, gamma, beta, out):
+            nat.check(lib.ctn_weight_prep(nat.ptr(W), rows, cols, nat.ptr(gamma), nat.ptr(beta), 0,
+                                          nat.ptr(out[0]), nat.ptr(out[1]),
+                                          nat.ptr(out[2]) if len(out) > 2 else None,
+                                          nat.ptr(out[3]) if len(out) > 3 else None, s))
+
+        prep(params["separator.network.1.weight"], B, N, params["separator.network.0.gamma"],
+             params["separator.network.0.beta"], self.bott)
+        i = 0
+        for r in range(cfg["R"]):
+            for x in range(cfg["X"]):
+                k = block_keys(r, x, cfg["causal"])
+                prep(params[k["w1"]], H, B, None, None, self.blocks[i]["w1"])
+                prep(params[k["w2"]], B, H, params[k["g2"]], params[k["b2"]], self.blocks[i]["w2"])
+                i += 1
+        prep(params["separator.network.3.weight"], C * N, B, None, None, self.mask)
+        self.fingerprint = fp
+
+
+class _Plan:
+    """Static workspaces + call list for one (M, T) on one device."""
+
+    def __init__(self, cfg, M, T, device):
+        self.cfg, self.M, self.T, self.device = cfg, M, T, device
+        N, L, B, H, C = cfg["N"], cfg["L"], cfg["B"], cfg["H"], cfg["C"]
+        self.hop, self.K, self.T_conv = frame_geometry(T, L)
+        K = self.K
+        R_ = M * K
+        lib = nat.lib()
+        f32 = dict(dtype=torch.float32, device=device)
+        bf = dict(dtype=torch.bfloat16, device=device)
+        self.mix = torch.empty(M, T, **f32)
+        self.est = torch.empty(M, C, T, **f32)
+        self.w = torch.empty(R_, N, **f32)
+        self.w_hl = (torch.empty(R_, N, **bf), torch.empty(R_, N, **bf))
+        self.rowstat0 = torch.empty(R_, 2, **f32)
+        self.x = torch.empty(R_, B, **f32)
+        self.x_hl = (torch.empty(R_, B, **bf), torch.empty(R_, B, **bf))
+        self.a = torch.empty(R_, H, **f32)
+        self.q_hl = (torch.empty(R_, H, **bf), torch.empty(R_, H, **bf))
+        self.score = torch.empty(R_, C * N, **f32)
+        self.norm = _NORM[cfg["norm_type"]]
+        if self.norm == nat.NORM_GLN:
+            self.P1 = lib.ctn_gemm_gln_partials(K, H)
+            self.P2 = lib.ctn_dwconv_gln_partials(K)
+            self.stat1 = torch.zeros(M, self.P1, 2, **f32)
+            self.stat2 = torch.zeros(M, self.P2, 2, **f32)
+        else:
+            self.P1 = lib.ctn_gemm_cln_groups(H)
+            self.P2 = 1
+            self.stat1 = torch.zeros(R_, self.P1, 2, **f32)
+            self.stat2 = torch.zeros(R_, 2, **f32)
+        self.calls = None
+        self.param_ptrs = None
+        self.graph = None
+        self._keep = []
+
+    def _gemm(self, **kw):
+        g = nat.GemmArgs()
+        g.M, g.K = self.M, self.K
+        for k, v in kw.items():
+            setattr(g, k, v.data_ptr() if isinstance(v, torch.Tensor) else v)
+        self._keep.append(g)
+        fn = nat.lib().ctn_gemm1x1
+        ref = C.byref(g)
+        return lambda s: fn(ref, s)
+
+    def build(self, params, prep):
+        cfg = self.cfg
+        N, L, B, H, C_ = cfg["N"], cfg["L"], cfg["B"], cfg["H"], cfg["C"]
+        M, K, T = self.M, self.K, self.T
+        lib = nat.lib()
+        self._keep = []
+        calls = []
+        info = []   # (kind, algorithmic FLOPs, algorithmic bytes) per call, for profiling / roofline reports
+        Rr = M * K
+        U = params["encoder.conv1d_U.weight"]
+        V = params["decoder.basis_signals.weight"]
+        enc = lib.ctn_encoder_fwd
+        a = (self.mix.data_ptr(), U.data_ptr(), M, T, N, L, self.w.data_ptr(), self.w_hl[0].data_ptr(),
+             self.w_hl[1].data_ptr(), self.rowstat0.data_ptr())
+        calls.append(lambda s, a=a: enc(*a, s))
+        info.append(("encoder", 2.0 * Rr * N * L, 4.0 * M * T + 8.0 * Rr * N))
+        info.append(("gemm_bottleneck", 2.0 * Rr * N * B, 4.0 * Rr * N + 8.0 * Rr * B))
+        calls.append(self._gemm(Cin=N, Cout=B, a_hi=self.w_hl[0], a_lo=self.w_hl[1], w_hi=prep.bott[0],
+                                w_lo=prep.bott[1], col_g=prep.bott[2], col_bias=prep.bott[3],
+                                in_norm=nat.NORM_CLN, in_stat=self.rowstat0,
+                                out_f32=self.x, out_hi=self.x_hl[0], out_lo=self.x_hl[1]))
+        dw = lib.ctn_dwconv_fwd
+        i = 0
+        for r in range(cfg["R"]):
+            for xb in range(cfg["X"]):
+                k = block_keys(r, xb, cfg["causal"])
+                pb = prep.blocks[i]
+                i += 1
+                info.append(("gemm_conv1x1", 2.0 * Rr * B * H, 4.0 * Rr * B + 4.0 * Rr * H))
+                info.append(("dwconv", 2.0 * Rr * H * cfg["P"], 8.0 * Rr * H))
+                info.append(("gemm_pointwise", 2.0 * Rr * B * H, 4.0 * Rr * H + 12.0 * Rr * B))
+                calls.append(self._gemm(Cin=B, Cout=H, a_hi=self.x_hl[0], a_lo=self.x_hl[1], w_hi=pb["w1"][0],
+                                        w_lo=pb["w1"][1], out_f32=self.a, out_stat=self.norm,
+                                        out_stat_buf=self.stat1, stat_prelu=params[k["a1"]]))
+                d = nat.DwconvArgs()
+                d.M, d.K, d.H, d.P, d.dilation, d.causal = M, K, H, cfg["P"], 2 ** xb, int(bool(cfg["causal"]))
+                d.inp, d.prelu_in = self.a.data_ptr(), params[k["a1"]].data_ptr()
+                d.gamma_in, d.beta_in = params[k["g1"]].data_ptr(), params[k["b1"]].data_ptr()
+                d.norm, d.in_stat, d.in_P = self.norm, self.stat1.data_ptr(), self.P1
+                d.wd, d.prelu_out = params[k["wd"]].data_ptr(), params[k["a2"]].data_ptr()
+                d.out_pre = None
+                d.out_hi, d.out_lo = self.q_hl[0].data_ptr(), self.q_hl[1].data_ptr()
+                d.out_stat = self.stat2.data_ptr()
+                self._keep.append(d)
+                calls.append(lambda s, ref=C.byref(d): dw(ref, s))
+                calls.append(self._gemm(Cin=H, Cout=B, a_hi=self.q_hl[0], a_lo=self.q_hl[1], w_hi=pb["w2"][0],
+                                        w_lo=pb["w2"][1], col_g=pb["w2"][2], col_bias=pb["w2"][3],
+                                        in_norm=self.norm, in_stat=self.stat2, in_P=self.P2,
+                                        in_count=float(K) * H, resid=self.x,
+                                        out_f32=self.x, out_hi=self.x_hl[0], out_lo=self.x_hl[1]))
+        calls.append(self._gemm(Cin=B, Cout=C_ * N, a_hi=self.x_hl[0], a_lo=self.x_hl[1], w_hi=prep.mask[0],
+                                w_lo=prep.mask[1], out_f32=self.score))
+        info.append(("gemm_mask", 2.0 * Rr * B * C_ * N, 4.0 * Rr * B + 4.0 * Rr * C_ * N))
+        info.append(("decoder", 2.0 * Rr * C_ * N * L, 4.0 * Rr * N * (C_ + 1) + 4.0 * M * C_ * T))
+        dec = lib.ctn_decoder_fwd
+        a = (self.score.data_ptr(), self.w.data_ptr(), V.data_ptr(), M, K, N, L, C_, T,
+             _MASK[cfg["mask_nonlinear"]], self.est.data_ptr())
+        calls.append(lambda s, a=a: dec(*a, s))
+        self.calls = calls
+        self.call_info = info
+        assert len(info) == len(calls)
+        self.param_ptrs = tuple(p.data_ptr() for p in params.values())
+        self.graph = None
+
+    def launch(self):
+        s = nat.stream()
+        check = nat.check
+        for c in self.calls:
+            check(c(s))
+
+    def launch_timed(self):
+        """Runs the call list with a CUDA event pair around every call (profiling aid):
+        returns [(kind, flops, bytes, milliseconds)]."""
+        s = nat.stream()
+        evs = [torch.cuda.Event(enable_timing=True) for _ in range(len(self.calls) + 1)]
+        evs[0].record()
+        for i, c in enumerate(self.calls):
+            nat.check(c(s))
+            evs[i + 1].record()
+        torch.cuda.synchronize(self.device)
+        return [(k, f, b, evs[i].elapsed_time(evs[i + 1])) for i, (k, f, b) in enumerate(self.call_info)]
+
+    def run(self, use_graph):
+        if not use_graph:
+            self.launch()
+            return
+        if self.graph is None:
+            self.launch()  # warm-up outside capture (first-use attribute setup, lazy module load)
+            torch.cuda.synchronize(self.device)
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):
+                self.launch()
+            self.graph = g
+        self.graph.replay()
+
+
+class SeparationEngine:
+    """Inference forward for one ConvTasNet parameter set on one device."""
+
+    def __init__(self, cfg):
+        _check_cfg(cfg)
+        self.cfg = dict(cfg)
+        self.prepared = {}
+        self.plans = {}
+        self.micro_batch = 16
+        self.use_graph = False
+        self.launches = 0   # kernels of libctn_b200 launched by forward() so far
+
+    def num_launches(self):
+        """Kernel launches of one plan execution (encoder + bottleneck + 3 per block + mask + decoder)."""
+        return 4 + 3 * self.cfg["R"] * self.cfg["X"]
+
+    def _plan(self, params, M, T, device):
+        key = (device.index, M, T)
+        prep = self.prepared.get(device.index)
+        if prep is None:
+            prep = self.prepared[device.index] = _Prepared(self.cfg, device)
+        old_fp = prep.fingerprint
+        prep.refresh(self.cfg, params)
+        plan = self.plans.get(key)
+        if plan is None:
+            plan = self.plans[key] = _Plan(self.cfg, M, T, device)
+        ptrs = tuple(p.data_ptr() for p in params.values())
+        if plan.calls is None or plan.param_ptrs != ptrs:
+            plan.build(params, prep)
+        elif old_fp != prep.fingerprint:
+            pass  # same pointers, refreshed contents: call list and any captured graph stay valid
+        return plan
+
+    @torch.no_grad()
+    def forward(self, mixture, params):
+        nat.require_cuda(mixture, "mixture")
+        if mixture.dim() != 2:
+            raise RuntimeError("mixture must be [M, T], got shape %s" % (tuple(mixture.shape),))
+        if mixture.dtype != torch.float32:
+            raise RuntimeError("mixture must be float32, got %s" % mixture.dtype)
+        M, T = mixture.shape
+        cfg = self.cfg
+        if T < cfg["L"]:
+            raise RuntimeError("Calculated output size is too small: T=%d < L=%d" % (T, cfg["L"]))
+        device = mixture.device
+        out = torch.empty(M, cfg["C"], T, dtype=torch.float32, device=device)
+        with torch.cuda.device(device):
+            mb = max(1, int(self.micro_batch))
+            for m0 in range(0, M, mb):
+                m1 = min(M, m0 + mb)
+                plan = self._plan(params, m1 - m0, T, device)
+                plan.mix.copy_(mixture[m0:m1])
+                plan.run(self.use_graph)
+                self.launches += len(plan.calls)
+                out[m0:m1].copy_(plan.est)
+        return out

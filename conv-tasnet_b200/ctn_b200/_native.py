@@ -1,0 +1,111 @@
+"""ctypes binding of libctn_b200.so (C ABI declared in include/ctn_b200.h).
+
+There is no fallback: if the library is missing or a call fails, a RuntimeError
+(or ValueError for the reference's ValueError cases) is raised.
+"""
+import ctypes as C
+import os
+
+import torch
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB_PATH = os.path.join(os.path.dirname(_HERE), "libctn_b200.so")
+
+NORM_NONE, NORM_GLN, NORM_CLN = 0, 1, 2
+MASK_RELU, MASK_SOFTMAX = 0, 1
+ROW_TILE, COL_TILE, DW_TILE = 128, 128, 16
+
+_vp = C.c_void_p
+
+
+class GemmArgs(C.Structure):
+    """struct ctn_gemm_args"""
+    _fields_ = [
+        ("M", C.c_int), ("K", C.c_int), ("Cin", C.c_int), ("Cout", C.c_int),
+        ("a_hi", _vp), ("a_lo", _vp), ("w_hi", _vp), ("w_lo", _vp),
+        ("out_f32", _vp), ("out_hi", _vp), ("out_lo", _vp),
+        ("resid", _vp), ("col_g", _vp), ("col_bias", _vp),
+        ("in_norm", C.c_int), ("in_stat", _vp), ("in_P", C.c_int), ("in_count", C.c_double),
+        ("out_stat", C.c_int), ("out_stat_buf", _vp), ("stat_prelu", _vp),
+        ("force_simt", C.c_int),
+    ]
+
+
+class DwconvArgs(C.Structure):
+    """struct ctn_dwconv_args"""
+    _fields_ = [
+        ("M", C.c_int), ("K", C.c_int), ("H", C.c_int), ("P", C.c_int),
+        ("dilation", C.c_int), ("causal", C.c_int),
+        ("inp", _vp), ("prelu_in", _vp), ("gamma_in", _vp), ("beta_in", _vp),
+        ("norm", C.c_int), ("in_stat", _vp), ("in_P", C.c_int),
+        ("wd", _vp), ("prelu_out", _vp), ("out_pre", _vp), ("out_hi", _vp), ("out_lo", _vp),
+        ("out_stat", _vp),
+    ]
+
+
+_SIGNATURES = {
+    "ctn_version": (C.c_int, []),
+    "ctn_last_error": (C.c_char_p, []),
+    "ctn_gemm_gln_partials": (C.c_int, [C.c_int, C.c_int]),
+    "ctn_dwconv_gln_partials": (C.c_int, [C.c_int]),
+    "ctn_gemm_cln_groups": (C.c_int, [C.c_int]),
+    "ctn_weight_prep": (C.c_int, [_vp, C.c_int, C.c_int, _vp, _vp, C.c_int, _vp, _vp, _vp, _vp, _vp]),
+    "ctn_encoder_fwd": (C.c_int, [_vp, _vp, C.c_int, C.c_int, C.c_int, C.c_int, _vp, _vp, _vp, _vp, _vp]),
+    "ctn_gemm1x1": (C.c_int, [C.POINTER(GemmArgs), _vp]),
+    "ctn_dwconv_fwd": (C.c_int, [C.POINTER(DwconvArgs), _vp]),
+    "ctn_decoder_fwd": (C.c_int, [_vp, _vp, _vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
+                                  _vp, _vp]),
+    "ctn_overlap_add": (C.c_int, [_vp, C.c_int, C.c_int, C.c_int, C.c_int, _vp, _vp]),
+    "ctn_pit_workspace_doubles": (C.c_int, [C.c_int, C.c_int, C.c_int]),
+    "ctn_pit_sisnr_fwd": (C.c_int, [_vp, _vp, _vp, C.c_int, C.c_int, C.c_int, _vp, C.c_int, _vp, _vp, _vp, _vp,
+                                    _vp, _vp, _vp]),
+    "ctn_pit_reorder": (C.c_int, [_vp, _vp, _vp, C.c_int, C.c_int, C.c_int, _vp, _vp]),
+    "ctn_pit_sisnr_bwd": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, C.c_int, C.c_int, C.c_int, _vp, _vp]),
+}
+
+_lib = None
+
+
+def exported_symbols():
+    """Names include/ctn_b200.h declares (used by the CPU-side ABI test)."""
+    return sorted(_SIGNATURES)
+
+
+def lib():
+    """Loads the shared library once; raises if it has not been built."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(_LIB_PATH):
+            raise RuntimeError(
+                "libctn_b200.so not found at %s: build it with "
+                "`python conv-tasnet_b200/build_native.py` (there is no CPU or PyTorch fallback)" % _LIB_PATH)
+        handle = C.CDLL(_LIB_PATH)
+        for name, (res, args) in _SIGNATURES.items():
+            fn = getattr(handle, name)
+            fn.restype, fn.argtypes = res, args
+        _lib = handle
+    return _lib
+
+
+def check(rc):
+    """Translates a C return code into the reference's Python error conventions."""
+    if rc == 0:
+        return
+    msg = lib().ctn_last_error().decode("utf-8", "replace")
+    if "Unsupported mask non-linear function" in msg:
+        raise ValueError(msg)  # conv_tasnet.py:208
+    raise RuntimeError("libctn_b200: %s (code %d)" % (msg, rc))
+
+
+def ptr(t):
+    """Device pointer of a tensor (None -> NULL)."""
+    return None if t is None else t.data_ptr()
+
+
+def stream():
+    return torch.cuda.current_stream().cuda_stream
+
+
+def require_cuda(t, what):
+    if not (isinstance(t, torch.Tensor) and t.is_cuda):
+        raise RuntimeError("%s must be a CUDA tensor: this implementation has no CPU path" % what)

@@ -1,0 +1,175 @@
+/*
+ * ctn_b200.h -- C ABI of libctn_b200.so: the B200 (sm_100a) kernels behind the
+ * Conv-TasNet separation path.
+ *
+ * The reference (jwr1995/Conv-TasNet) has no FFI: its hot path is three Python
+ * modules (src/conv_tasnet.py, src/pit_criterion.py, src/utils.py).  The
+ * drop-in modules of the same names under conv-tasnet_b200/ keep that Python
+ * surface and call the functions below through ctypes.  Each entry point cites
+ * the reference lines whose arithmetic it replaces.
+ *
+ * Conventions
+ *  - Every pointer is a DEVICE pointer owned by the caller (PyTorch allocates);
+ *    the library owns no device memory and keeps no mutable global state.
+ *  - `stream` is a cudaStream_t passed as void*.  Calls are stream-ordered and
+ *    never synchronise the host, so a whole forward/backward can be captured
+ *    in a CUDA graph.
+ *  - Return value: 0 on success, <0 on failure (CTN_ERR_*); never throws or
+ *    exits.  ctn_last_error() returns a thread-local description.
+ *  - Internal activation layout is frames-major ("channels-last"):
+ *    act[(m*K + k)*C + c] for utterance m, frame k, channel c, where
+ *    K = (T - L)/(L/2) + 1 (conv_tasnet.py:113).  Activations that feed a 1x1
+ *    convolution are stored as a bf16 pair (hi, lo) with hi + lo ~= fp32 value
+ *    (16 mantissa bits); the tensor-core GEMM computes hi*hi + lo*hi + hi*lo
+ *    with fp32 accumulation.
+ */
+#ifndef CTN_B200_H
+#define CTN_B200_H
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define CTN_OK 0
+#define CTN_ERR_INVALID (-1)     /* bad argument */
+#define CTN_ERR_UNSUPPORTED (-2) /* shape the kernels do not cover */
+#define CTN_ERR_CUDA (-3)        /* CUDA runtime / driver error */
+
+#define CTN_NORM_NONE 0
+#define CTN_NORM_GLN 1 /* GlobalLayerNorm, conv_tasnet.py:332-355 */
+#define CTN_NORM_CLN 2 /* ChannelwiseLayerNorm, conv_tasnet.py:307-329 */
+
+#define CTN_MASK_RELU 0    /* conv_tasnet.py:205-206 */
+#define CTN_MASK_SOFTMAX 1 /* conv_tasnet.py:203-204 */
+
+/* geometry of the statistics buffers the kernels exchange */
+#define CTN_ROW_TILE 128 /* GEMM row tile (frames) */
+#define CTN_COL_TILE 128 /* statistics column group */
+#define CTN_DW_TILE 16   /* depthwise-kernel frame tile */
+
+int ctn_version(void);
+const char* ctn_last_error(void);
+
+/* Number of (sum, sumsq) float2 partials per utterance written by
+ * ctn_gemm1x1 (out_stat = GLN) and by ctn_dwconv_fwd (norm = GLN). */
+int ctn_gemm_gln_partials(int K, int Cout);
+int ctn_dwconv_gln_partials(int K);
+/* Number of per-row column-group partials written by ctn_gemm1x1 (out_stat = CLN). */
+int ctn_gemm_cln_groups(int Cout);
+
+/* Weight preparation for one 1x1 convolution W[rows, cols] (fp32, row-major;
+ * nn.Conv1d weight [rows, cols, 1], conv_tasnet.py:169,185,217,256).
+ *   Wg[r,c] = W[r,c] * gamma[c]   (gamma NULL -> 1)   -> (w_hi, w_lo) bf16 [rows, cols]
+ *   col_g[r]   = sum_c (w_hi + w_lo)[r,c]              (NULL to skip)
+ *   col_bias[r]= sum_c W[r,c] * beta[c]                (NULL to skip)
+ * This folds the norm that precedes the convolution into its weights:
+ *   W.(gamma*(y-mu)*rstd + beta) = rstd*(Wg.y) - rstd*mu*col_g + col_bias.
+ * transpose != 0 writes (w_hi, w_lo) as [cols, rows] (operand of the dgrad GEMM). */
+int ctn_weight_prep(const float* W, int rows, int cols, const float* gamma, const float* beta, int transpose,
+                    void* w_hi, void* w_lo, float* col_g, float* col_bias, void* stream);
+
+/* Encoder (conv_tasnet.py:97-117): w = relu(Conv1d(1,N,L,stride L/2)(mixture)).
+ * mixture [M,T] fp32 -> w_f32 [M*K, N], (w_hi, w_lo) bf16 [M*K, N] and the
+ * per-frame statistics of the leading cLN (conv_tasnet.py:167,326-327):
+ * rowstat[M*K] = float2(mean, 1/sqrt(var + 1e-8)).  Any of the outputs may be NULL. */
+int ctn_encoder_fwd(const float* mixture, const float* U, int M, int T, int N, int L, float* w_f32, void* w_hi,
+                    void* w_lo, void* rowstat, void* stream);
+
+typedef struct ctn_gemm_args {
+    int M, K;                /* utterances, frames per utterance                         */
+    int Cin, Cout;           /* out[r, n] = sum_k a[r, k] * w[n, k]                      */
+    const void *a_hi, *a_lo; /* bf16 [M*K, Cin]                                           */
+    const void *w_hi, *w_lo; /* bf16 [Cout, Cin] (from ctn_weight_prep)                   */
+    float* out_f32;          /* [M*K, Cout] or NULL                                       */
+    void *out_hi, *out_lo;   /* bf16 [M*K, Cout] or NULL                                  */
+    const float* resid;      /* [M*K, Cout] added to the result, or NULL (may == out_f32) */
+    const float* col_g;      /* [Cout] or NULL, see in_norm                               */
+    const float* col_bias;   /* [Cout] or NULL                                            */
+    /* Folded input normalisation: out = rstd*acc - rstd*mean*col_g + col_bias (+ resid).
+     * GLN: in_stat = float2 partials [M, in_P] (sum, sumsq) over in_count elements per utterance.
+     * CLN: in_stat = float2 [M*K] (mean, rstd) per frame. */
+    int in_norm;
+    const void* in_stat;
+    int in_P;
+    double in_count;
+    /* Statistics of the OUTPUT for the next norm (taken after an optional PReLU
+     * with slope *stat_prelu; the stored output itself is never activated):
+     * GLN: out_stat_buf = float2 [M, ctn_gemm_gln_partials(K, Cout)]
+     * CLN: out_stat_buf = float2 [M*K, ctn_gemm_cln_groups(Cout)] */
+    int out_stat;
+    void* out_stat_buf;
+    const float* stat_prelu;
+    int force_simt; /* testing: skip the tcgen05 path */
+} ctn_gemm_args;
+
+/* 1x1 convolution as a GEMM over all frames of the batch (bottleneck
+ * conv_tasnet.py:169; TemporalBlock conv1x1 :217; pointwise :256 with the
+ * residual add of :237; mask conv :185).  tcgen05/TMEM/TMA path when
+ * Cin % 8 == 0 && Cout % 8 == 0, a plain SIMT kernel otherwise. */
+int ctn_gemm1x1(const ctn_gemm_args* args, void* stream);
+
+typedef struct ctn_dwconv_args {
+    int M, K, H, P, dilation, causal;
+    const float* in;       /* a = conv1x1 output, fp32 [M*K, H]                        */
+    const float* prelu_in; /* slope of the first PReLU (device scalar), :218           */
+    const float *gamma_in, *beta_in; /* first norm affine [H], :219                    */
+    int norm;              /* CTN_NORM_GLN or CTN_NORM_CLN                             */
+    const void* in_stat;   /* GLN: float2 [M, in_P] partials; CLN: float2 [M*K, in_P]  */
+    int in_P;
+    const float* wd;        /* depthwise weight [H, P], :247-250                       */
+    const float* prelu_out; /* slope of the second PReLU, :253                         */
+    float* out_pre;         /* d = depthwise output before PReLU, fp32 [M*K,H] or NULL */
+    void *out_hi, *out_lo;  /* q = prelu(d) as bf16 pair [M*K, H]                      */
+    void* out_stat;         /* GLN: float2 [M, ctn_dwconv_gln_partials(K)] partials of q;
+                               CLN: float2 [M*K] (mean, rstd) of q                     */
+} ctn_dwconv_args;
+
+/* First PReLU + norm applied on load, zero padding AFTER normalisation, dilated
+ * depthwise cross-correlation (causal = left-only taps, i.e. pad+Chomp1d
+ * :175-176,247-252,275-289), second PReLU, statistics for the second norm. */
+int ctn_dwconv_fwd(const ctn_dwconv_args* args, void* stream);
+
+/* Mask non-linearity, mask * mixture_w, basis Linear(N -> L), overlap-add with
+ * step L/2 and right zero-fill to T (conv_tasnet.py:202-209,137-142,56-59;
+ * utils.py:9-46).  score fp32 [M*K, C*N] (channel = c*N + n), w fp32 [M*K, N],
+ * V fp32 [L, N] -> est [M, C, T].  Scatter-free: every output sample is one
+ * thread's sum of its (at most ceil(L/hop)) frame terms in ascending frame order. */
+int ctn_decoder_fwd(const float* score, const float* w, const float* V, int M, int K, int N, int L, int C, int T,
+                    int mask_nonlinear, float* est, void* stream);
+
+/* utils.py:9-46 overlap_and_add for an arbitrary frame_step <= L:
+ * frames [batch, K, L] -> out [batch, (K-1)*step + L]. */
+int ctn_overlap_add(const float* frames, int batch, int K, int L, int step, float* out, void* stream);
+
+/* ---- utterance-level PIT SI-SNR loss (pit_criterion.py) ------------------------------ */
+
+/* Number of doubles of workspace ctn_pit_sisnr_fwd needs. */
+int ctn_pit_workspace_doubles(int B, int C, int T);
+
+/* cal_si_snr_with_pit (pit_criterion.py:27-76) + the loss of cal_loss (:22).
+ * source, estimate fp32 [B, C, T]; lengths int64 [B]; perms int64 [nperm, C] in
+ * itertools.permutations order (:66).  Side effect as in the reference (:38):
+ * estimate[b, :, t >= lengths[b]] is zeroed IN PLACE.
+ * Outputs: max_snr [B] (= [B,1]), max_idx int64 [B] (first maximum on ties),
+ * loss [1] = 0 - mean(max_snr); optional pair_snr [B, C, C] (estimate i vs target j, dB)
+ * and coef [B, C, 4], the closed-form gradient coefficients ctn_pit_sisnr_bwd consumes. */
+int ctn_pit_sisnr_fwd(const float* source, float* estimate, const long long* lengths, int B, int C, int T,
+                      const long long* perms, int nperm, double* workspace, float* max_snr, long long* max_idx,
+                      float* loss, float* pair_snr, float* coef, void* stream);
+
+/* reorder_source (pit_criterion.py:79-98): out[b, c] = estimate[b, perms[max_idx[b]][c]]
+ * (applies the permutation, not its inverse -- kept as in the reference). */
+int ctn_pit_reorder(const float* estimate, const long long* perms, const long long* max_idx, int B, int C, int T,
+                    float* out, void* stream);
+
+/* d loss / d estimate for loss = 0 - mean(max_snr) (what autograd derives from
+ * pit_criterion.py:37-76): one elementwise pass.  upstream = d(total)/d(loss) [1] or NULL (= 1).
+ * estimate is the MASKED estimate that ctn_pit_sisnr_fwd left behind. */
+int ctn_pit_sisnr_bwd(const float* source, const float* estimate, const long long* lengths, const long long* perms,
+                      const long long* max_idx, const float* coef, const float* upstream, int B, int C, int T,
+                      float* grad_estimate, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* CTN_B200_H */

@@ -1,0 +1,112 @@
+"""Thin torch-tensor wrappers around the C ABI for the per-kernel parity tests."""
+import ctypes as C
+
+import torch
+
+from ctn_b200 import _native as nat
+
+
+def split_hl(x):
+    hi = x.to(torch.bfloat16)
+    lo = (x - hi.float()).to(torch.bfloat16)
+    return hi.contiguous(), lo.contiguous()
+
+
+def weight_prep(W, gamma=None, beta=None, transpose=False):
+    rows, cols = W.shape
+    shp = (cols, rows) if transpose else (rows, cols)
+    hi = torch.empty(shp, dtype=torch.bfloat16, device=W.device)
+    lo = torch.empty_like(hi)
+    g = torch.empty(rows, device=W.device)
+    b = torch.empty(rows, device=W.device)
+    nat.check(nat.lib().ctn_weight_prep(W.data_ptr(), rows, cols, nat.ptr(gamma), nat.ptr(beta), int(transpose),
+                                        hi.data_ptr(), lo.data_ptr(), g.data_ptr(), b.data_ptr(), nat.stream()))
+    return hi, lo, g, b
+
+
+def encoder(mix, U):
+    M, T = mix.shape
+    N, _, L = U.shape
+    K = (T - L) // (L // 2) + 1
+    dev = mix.device
+    w = torch.empty(M * K, N, device=dev)
+    hi = torch.empty(M * K, N, dtype=torch.bfloat16, device=dev)
+    lo = torch.empty_like(hi)
+    st = torch.empty(M * K, 2, device=dev)
+    nat.check(nat.lib().ctn_encoder_fwd(mix.data_ptr(), U.data_ptr(), M, T, N, L, w.data_ptr(), hi.data_ptr(),
+                                        lo.data_ptr(), st.data_ptr(), nat.stream()))
+    return w, hi, lo, st, K
+
+
+def gemm(M, K, a_hi, a_lo, w_hi, w_lo, out_f32=True, out_hl=False, resid=None, col_g=None, col_bias=None,
+         in_norm=0, in_stat=None, in_P=0, in_count=0.0, out_stat=0, stat_prelu=None, force_simt=False):
+    R, Cin = a_hi.shape
+    Cout = w_hi.shape[0]
+    dev = a_hi.device
+    lib = nat.lib()
+    g = nat.GemmArgs()
+    g.M, g.K, g.Cin, g.Cout = M, K, Cin, Cout
+    g.a_hi, g.a_lo, g.w_hi, g.w_lo = a_hi.data_ptr(), a_lo.data_ptr(), w_hi.data_ptr(), w_lo.data_ptr()
+    res = {}
+    if out_f32:
+        res["out"] = torch.full((R, Cout), float("nan"), device=dev)
+        g.out_f32 = res["out"].data_ptr()
+    if out_hl:
+        res["hi"] = torch.zeros(R, Cout, dtype=torch.bfloat16, device=dev)
+        res["lo"] = torch.zeros_like(res["hi"])
+        g.out_hi, g.out_lo = res["hi"].data_ptr(), res["lo"].data_ptr()
+    g.resid, g.col_g, g.col_bias = nat.ptr(resid), nat.ptr(col_g), nat.ptr(col_bias)
+    g.in_norm, g.in_stat, g.in_P, g.in_count = in_norm, nat.ptr(in_stat), in_P, in_count
+    g.out_stat = out_stat
+    if out_stat == nat.NORM_GLN:
+        res["stat"] = torch.full((M, lib.ctn_gemm_gln_partials(K, Cout), 2), float("nan"), device=dev)
+    elif out_stat == nat.NORM_CLN:
+        res["stat"] = torch.full((R, lib.ctn_gemm_cln_groups(Cout), 2), float("nan"), device=dev)
+    if out_stat:
+        g.out_stat_buf = res["stat"].data_ptr()
+    g.stat_prelu = nat.ptr(stat_prelu)
+    g.force_simt = int(force_simt)
+    nat.check(lib.ctn_gemm1x1(C.byref(g), nat.stream()))
+    return res
+
+
+def dwconv(M, K, a, a1, g1, b1, norm, in_stat, in_P, wd, a2, dilation, causal, want_pre=True):
+    R, H = a.shape
+    P = wd.shape[-1]
+    dev = a.device
+    lib = nat.lib()
+    d = nat.DwconvArgs()
+    d.M, d.K, d.H, d.P, d.dilation, d.causal = M, K, H, P, dilation, int(causal)
+    d.inp, d.prelu_in, d.gamma_in, d.beta_in = a.data_ptr(), a1.data_ptr(), g1.data_ptr(), b1.data_ptr()
+    d.norm, d.in_stat, d.in_P = norm, in_stat.data_ptr(), in_P
+    d.wd, d.prelu_out = wd.data_ptr(), a2.data_ptr()
+    pre = torch.full((R, H), float("nan"), device=dev) if want_pre else None
+    hi = torch.zeros(R, H, dtype=torch.bfloat16, device=dev)
+    lo = torch.zeros_like(hi)
+    if norm == nat.NORM_GLN:
+        st = torch.full((M, lib.ctn_dwconv_gln_partials(K), 2), float("nan"), device=dev)
+    else:
+        st = torch.full((R, 2), float("nan"), device=dev)
+    d.out_pre, d.out_hi, d.out_lo, d.out_stat = nat.ptr(pre), hi.data_ptr(), lo.data_ptr(), st.data_ptr()
+    nat.check(lib.ctn_dwconv_fwd(C.byref(d), nat.stream()))
+    return pre, hi, lo, st
+
+
+def decoder(score, w, V, M, K, C_, T, mask):
+    L, N = V.shape
+    est = torch.full((M, C_, T), float("nan"), device=score.device)
+    nat.check(nat.lib().ctn_decoder_fwd(score.data_ptr(), w.data_ptr(), V.data_ptr(), M, K, N, L, C_, T, mask,
+                                        est.data_ptr(), nat.stream()))
+    return est
+
+
+def to_rows(x):
+    """[M, C, K] -> frames-major [M*K, C]"""
+    M, C_, K = x.shape
+    return x.permute(0, 2, 1).reshape(M * K, C_).contiguous()
+
+
+def from_rows(r, M):
+    """[M*K, C] -> [M, C, K]"""
+    R, C_ = r.shape
+    return r.view(M, R // M, C_).permute(0, 2, 1).contiguous()

@@ -1,0 +1,243 @@
+"""Per-kernel parity of the CUDA path (through the C ABI) against the oracle.
+
+Tolerances: the GEMM operands carry 16 mantissa bits each (bf16 hi + lo), fp32
+accumulate, so matrix products are compared at 3e-5 rel-L2 against an fp64
+product of the SAME fp32 inputs; everything else is fp32 arithmetic in a
+different summation order and is held to 1e-5.  Integer outputs (frame counts,
+permutation indices) are bit-exact.
+"""
+import pytest
+import torch
+import torch.nn.functional as F
+
+from conftest import load_golden, rel_l2
+from oracle import convtasnet_oracle as O
+
+pytestmark = pytest.mark.gpu
+
+if torch.cuda.is_available():
+    import kernels as Kn
+    from ctn_b200 import _native as nat
+
+DEV = "cuda"
+
+
+def _rand(*shape, seed=0, scale=1.0):
+    g = torch.Generator().manual_seed(seed)
+    return (torch.randn(*shape, generator=g) * scale).to(DEV)
+
+
+# ----------------------------------------------------------------- encoder
+@pytest.mark.parametrize("M,T,N,L", [(2, 12, 3, 4), (3, 1207, 64, 16), (2, 32007, 256, 20), (1, 4000, 512, 16),
+                                     (1, 57, 5, 5)])
+def test_encoder(M, T, N, L):
+    mix = _rand(M, T, seed=1, scale=0.1)
+    U = _rand(N, 1, L, seed=2, scale=0.3)
+    w, hi, lo, st, K = Kn.encoder(mix, U)
+    assert K == O.frame_geometry(T, L)[1]
+    ref = O.encoder(mix.double(), U.double())                  # [M,N,K]
+    assert ref.shape[-1] == K
+    ref_rows = Kn.to_rows(ref)
+    assert rel_l2(w, ref_rows) < 1e-6
+    assert rel_l2(hi.float() + lo.float(), ref_rows) < 2e-5
+    mean = ref_rows.mean(1)
+    rstd = 1.0 / torch.sqrt(ref_rows.var(1, unbiased=False) + 1e-8)
+    assert rel_l2(st[:, 0], mean) < 1e-5
+    assert rel_l2(st[:, 1], rstd) < 1e-4
+
+
+# ------------------------------------------------------------- weight prep
+@pytest.mark.parametrize("rows,cols", [(3, 2), (256, 512), (1536, 128)])
+def test_weight_prep(rows, cols):
+    W = _rand(rows, cols, seed=3, scale=0.1)
+    gamma, beta = _rand(cols, seed=4), _rand(cols, seed=5)
+    hi, lo, g, b = Kn.weight_prep(W, gamma, beta)
+    Wg = W.double() * gamma.double()
+    assert rel_l2(hi.float() + lo.float(), Wg) < 1e-5
+    assert rel_l2(g, (hi.double() + lo.double()).sum(1)) < 1e-5
+    assert rel_l2(b, W.double() @ beta.double()) < 1e-5
+    hi_t, lo_t, _, _ = Kn.weight_prep(W, None, None, transpose=True)
+    assert rel_l2(hi_t.float() + lo_t.float(), W.double().t()) < 1e-5
+
+
+# -------------------------------------------------------------------- GEMM
+def _gemm_case(M, K, Cin, Cout, simt, seed=0):
+    R = M * K
+    A = _rand(R, Cin, seed=seed + 10)
+    W = _rand(Cout, Cin, seed=seed + 11, scale=0.1)
+    a_hi, a_lo = Kn.split_hl(A)
+    w_hi, w_lo = Kn.split_hl(W)
+    Ad = a_hi.double() + a_lo.double()
+    Wd = w_hi.double() + w_lo.double()
+    return A, W, a_hi, a_lo, w_hi, w_lo, Ad @ Wd.t()
+
+
+SHAPES = [(1, 5, 2, 3, True), (2, 149, 64, 128, False), (2, 149, 64, 128, True), (1, 300, 256, 512, False),
+          (3, 3199, 256, 512, False), (3, 3199, 512, 256, False), (1, 3999, 128, 1536, False),
+          (2, 130, 24, 40, False), (16, 3199, 256, 512, False)]
+
+
+@pytest.mark.parametrize("M,K,Cin,Cout,simt", SHAPES)
+def test_gemm_plain(M, K, Cin, Cout, simt):
+    A, W, a_hi, a_lo, w_hi, w_lo, ref = _gemm_case(M, K, Cin, Cout, simt)
+    res = Kn.gemm(M, K, a_hi, a_lo, w_hi, w_lo, out_f32=True, out_hl=True, force_simt=simt)
+    assert rel_l2(res["out"], ref) < 3e-5
+    assert rel_l2(res["hi"].float() + res["lo"].float(), ref) < 5e-5
+    # fp32 product of the unsplit inputs: the split itself costs < 2e-5
+    assert rel_l2(res["out"], A.double() @ W.double().t()) < 5e-5
+
+
+@pytest.mark.parametrize("M,K,Cin,Cout,simt", [(2, 5, 3, 2, True), (2, 149, 128, 64, False), (3, 3199, 512, 256, False),
+                                               (1, 300, 128, 256, True)])
+@pytest.mark.parametrize("norm", ["gLN", "cLN"])
+def test_gemm_folded_norm_residual(M, K, Cin, Cout, simt, norm):
+    """pointwise conv: W.(gamma*(q-mu)*rstd+beta) + x  (conv_tasnet.py:254-256,237)"""
+    R = M * K
+    q = _rand(R, Cin, seed=20) * 0.7 + 0.3
+    W = _rand(Cout, Cin, seed=21, scale=0.1)
+    gamma, beta = _rand(Cin, seed=22), _rand(Cin, seed=23)
+    x = _rand(R, Cout, seed=24)
+    q_hi, q_lo = Kn.split_hl(q)
+    w_hi, w_lo, col_g, col_bias = Kn.weight_prep(W, gamma, beta)
+    qd = q.double().view(M, K, Cin)
+    if norm == "gLN":
+        # statistics arrive as (sum, sumsq) partials per utterance
+        P = 7
+        parts = torch.zeros(M, P, 2, device=DEV)
+        chunks = torch.tensor_split(torch.arange(K), P)
+        for m in range(M):
+            for i, ch in enumerate(chunks):
+                if len(ch):
+                    parts[m, i, 0] = qd[m, ch].sum()
+                    parts[m, i, 1] = (qd[m, ch] ** 2).sum()
+        mean = qd.mean(dim=(1, 2), keepdim=True)
+        var = ((qd - mean) ** 2).mean(dim=(1, 2), keepdim=True)
+        kw = dict(in_norm=nat.NORM_GLN, in_stat=parts, in_P=P, in_count=float(K * Cin))
+    else:
+        mean = qd.mean(dim=2, keepdim=True)
+        var = qd.var(dim=2, unbiased=False, keepdim=True)
+        st = torch.stack([mean.flatten(), 1.0 / torch.sqrt(var.flatten() + 1e-8)], 1).float().contiguous()
+        kw = dict(in_norm=nat.NORM_CLN, in_stat=st)
+    normed = gamma.double() * (qd - mean) / torch.sqrt(var + 1e-8) + beta.double()
+    ref = normed.view(R, Cin) @ W.double().t() + x.double()
+    res = Kn.gemm(M, K, q_hi, q_lo, w_hi, w_lo, out_f32=True, out_hl=True, resid=x, col_g=col_g,
+                  col_bias=col_bias, force_simt=simt, **kw)
+    assert rel_l2(res["out"], ref) < 5e-5
+    assert rel_l2(res["hi"].float() + res["lo"].float(), ref) < 7e-5
+
+
+@pytest.mark.parametrize("M,K,Cin,Cout,simt", [(2, 5, 2, 3, True), (2, 149, 64, 128, False), (3, 3199, 256, 512, False),
+                                               (2, 140, 64, 136, False), (1, 300, 64, 384, True)])
+@pytest.mark.parametrize("norm", ["gLN", "cLN"])
+def test_gemm_output_statistics(M, K, Cin, Cout, simt, norm):
+    """conv1x1 + statistics of prelu(out) for the following norm (conv_tasnet.py:217-219)"""
+    A, W, a_hi, a_lo, w_hi, w_lo, ref = _gemm_case(M, K, Cin, Cout, simt, seed=30)
+    slope = torch.tensor([0.25], device=DEV)
+    mode = nat.NORM_GLN if norm == "gLN" else nat.NORM_CLN
+    res = Kn.gemm(M, K, a_hi, a_lo, w_hi, w_lo, out_stat=mode, stat_prelu=slope, force_simt=simt)
+    assert rel_l2(res["out"], ref) < 3e-5
+    p = F.prelu(ref, slope.double()).view(M, K, Cout)
+    st = res["stat"].double()
+    assert not torch.isnan(st).any()
+    if norm == "gLN":
+        assert rel_l2(st[..., 0].sum(1), p.sum(dim=(1, 2))) < 1e-4
+        assert rel_l2(st[..., 1].sum(1), (p ** 2).sum(dim=(1, 2))) < 1e-4
+    else:
+        assert rel_l2(st[..., 0].sum(1), p.sum(dim=2).flatten()) < 1e-4
+        assert rel_l2(st[..., 1].sum(1), (p ** 2).sum(dim=2).flatten()) < 1e-4
+
+
+# --------------------------------------------------------------- depthwise
+@pytest.mark.parametrize("H,K,M", [(3, 5, 2), (16, 24, 2), (512, 3199, 2)])
+@pytest.mark.parametrize("dil", [1, 2, 8, 128])
+@pytest.mark.parametrize("causal", [False, True])
+@pytest.mark.parametrize("norm", ["gLN", "cLN"])
+def test_dwconv(H, K, M, dil, causal, norm):
+    if H < 512 and dil > 8:
+        pytest.skip("large dilation only at the paper shape")
+    P = 3
+    a = _rand(M, H, K, seed=40)
+    a1 = torch.tensor([0.25], device=DEV)
+    a2 = torch.tensor([0.1], device=DEV)
+    g1, b1 = _rand(H, seed=41), _rand(H, seed=42)
+    wd = _rand(H, 1, P, seed=43, scale=0.5)
+    ad = a.double()
+    pa = F.prelu(ad, a1.double())
+    nfun = O.gln if norm == "gLN" else O.cln
+    n1 = nfun(pa, g1.double().view(1, H, 1), b1.double().view(1, H, 1))
+    d_ref = O.depthwise(n1, wd.double(), dil, causal)
+    q_ref = F.prelu(d_ref, a2.double())
+    rows = Kn.to_rows(a)
+    lib = nat.lib()
+    if norm == "gLN":
+        in_P = 5
+        parts = torch.zeros(M, in_P, 2, device=DEV)
+        parts[:, 0, 0] = pa.sum(dim=(1, 2))
+        parts[:, 3, 1] = (pa ** 2).sum(dim=(1, 2))
+        mode = nat.NORM_GLN
+    else:
+        in_P = 2
+        parts = torch.zeros(M * K, in_P, 2, device=DEV)
+        par = Kn.to_rows(pa)
+        parts[:, 0, 0] = par[:, : H // 2].sum(1)
+        parts[:, 1, 0] = par[:, H // 2:].sum(1)
+        parts[:, 0, 1] = (par[:, : H // 2] ** 2).sum(1)
+        parts[:, 1, 1] = (par[:, H // 2:] ** 2).sum(1)
+        mode = nat.NORM_CLN
+    pre, hi, lo, st = Kn.dwconv(M, K, rows, a1, g1, b1, mode, parts, in_P, wd, a2, dil, causal)
+    assert rel_l2(pre, Kn.to_rows(d_ref)) < 2e-5
+    qr = Kn.to_rows(q_ref)
+    assert rel_l2(hi.float() + lo.float(), qr) < 3e-5
+    assert not torch.isnan(st).any()
+    if norm == "gLN":
+        assert st.shape[1] == lib.ctn_dwconv_gln_partials(K)
+        assert rel_l2(st[..., 0].double().sum(1), q_ref.sum(dim=(1, 2))) < 1e-4
+        assert rel_l2(st[..., 1].double().sum(1), (q_ref ** 2).sum(dim=(1, 2))) < 1e-4
+    else:
+        assert rel_l2(st[:, 0], qr.mean(1)) < 1e-4
+        assert rel_l2(st[:, 1], 1.0 / torch.sqrt(qr.var(1, unbiased=False) + 1e-8)) < 1e-3
+
+
+def test_dwconv_rejects_length_changing_config():
+    """P=2 non-causal changes the length; the reference crashes at the residual add"""
+    H, K, M = 4, 10, 1
+    z = torch.zeros(M * K, H, device=DEV)
+    one = torch.ones(1, device=DEV)
+    with pytest.raises(RuntimeError):
+        Kn.dwconv(M, K, z, one, torch.ones(H, device=DEV), torch.zeros(H, device=DEV), nat.NORM_GLN,
+                  torch.zeros(M, 1, 2, device=DEV), 1, torch.zeros(H, 1, 2, device=DEV), one, 1, False)
+
+
+# ----------------------------------------------------------------- decoder
+@pytest.mark.parametrize("M,K,N,L,C,extra", [(2, 5, 3, 4, 2, 0), (2, 149, 64, 16, 2, 7), (1, 3199, 256, 20, 2, 0),
+                                             (2, 500, 512, 16, 3, 5), (1, 40, 6, 5, 2, 1)])
+@pytest.mark.parametrize("mask", ["relu", "softmax"])
+def test_decoder(M, K, N, L, C, extra, mask):
+    hop = L // 2
+    T = (K - 1) * hop + L + extra
+    score = _rand(M, C * N, K, seed=50)
+    w = _rand(M, N, K, seed=51).abs()
+    V = _rand(L, N, seed=52, scale=0.2)
+    sc = score.double().view(M, C, N, K)
+    m = F.softmax(sc, dim=1) if mask == "softmax" else F.relu(sc)
+    ref = F.pad(O.decoder(w.double(), m, V.double()), (0, extra))
+    est = Kn.decoder(Kn.to_rows(score), Kn.to_rows(w), V, M, K, C, T,
+                     nat.MASK_SOFTMAX if mask == "softmax" else nat.MASK_RELU)
+    assert est.shape == ref.shape
+    assert not torch.isnan(est).any()
+    assert rel_l2(est, ref) < 1e-5
+    if extra:
+        assert torch.count_nonzero(est[..., -extra:]) == 0
+
+
+def test_overlap_and_add_matches_reference_fixtures():
+    import utils as U
+    z = load_golden("ola_cases")
+    for tag in ("demo", "l20", "l16", "odd"):
+        out = U.overlap_and_add(z[tag + "_in"].to(DEV), int(z[tag + "_step"]))
+        ref = z[tag + "_out"].to(DEV)
+        assert out.shape == ref.shape
+        if tag != "odd":
+            assert torch.equal(out, ref)       # two commutative addends onto zero: bit-identical
+        else:
+            assert torch.allclose(out, ref, atol=1e-6)
