@@ -183,7 +183,8 @@ def test_error_conventions():
     with pytest.raises(NotImplementedError):
         conv_tasnet.ConvTasNet(8, 4, 8, 8, 3, 1, 1, 2, norm_type="BN")
     m = conv_tasnet.ConvTasNet(8, 4, 8, 8, 3, 1, 1, 2).to(DEV).eval()
-    with pytest.raises(RuntimeError):
-        m(torch.zeros(1, 3, device=DEV))          # T < L
-    with pytest.raises(RuntimeError):
-        m(torch.zeros(1, 100))                    # CPU input: no CPU path
+    with torch.no_grad():
+        with pytest.raises(RuntimeError):
+            m(torch.zeros(1, 3, device=DEV))      # T < L
+        with pytest.raises(RuntimeError):
+            m(torch.zeros(1, 100))                # CPU input: no CPU path
