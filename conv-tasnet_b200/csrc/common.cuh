@@ -54,13 +54,15 @@ __device__ __forceinline__ void split_bf16(float v, __nv_bfloat16& hi, __nv_bflo
 __device__ __forceinline__ uint32_t pack_bf16(__nv_bfloat16 a, __nv_bfloat16 b) {
     return static_cast<uint32_t>(__bfloat16_as_ushort(a)) | (static_cast<uint32_t>(__bfloat16_as_ushort(b)) << 16);
 }
-// split two floats, return packed hi pair and lo pair
+// split two floats, return packed hi pair and lo pair (v0 in the low half); 6 instructions:
+// one packed cvt.rn.bf16x2 per pair, the hi halves are recovered with a shift / mask.
 __device__ __forceinline__ void split_pack2(float v0, float v1, uint32_t& hi, uint32_t& lo) {
-    __nv_bfloat16 h0, l0, h1, l1;
-    split_bf16(v0, h0, l0);
-    split_bf16(v1, h1, l1);
-    hi = pack_bf16(h0, h1);
-    lo = pack_bf16(l0, l1);
+    const __nv_bfloat162 h = __floats2bfloat162_rn(v0, v1);
+    hi = *reinterpret_cast<const uint32_t*>(&h);
+    const float f0 = __uint_as_float(hi << 16);
+    const float f1 = __uint_as_float(hi & 0xffff0000u);
+    const __nv_bfloat162 l = __floats2bfloat162_rn(v0 - f0, v1 - f1);
+    lo = *reinterpret_cast<const uint32_t*>(&l);
 }
 
 // Whole-warp, fixed-order reduction of P (sum, sumsq) partials into (mean, rstd).

@@ -12,6 +12,7 @@
 // (taps at k +- dil re-hit L2).  Inference writes q only as the bf16 (hi, lo) pair the
 // pointwise GEMM consumes; training additionally keeps d in fp32 for the backward.
 #include "common.cuh"
+#include "dwconv_march.cuh"
 
 namespace ctn {
 
@@ -196,7 +197,16 @@ dwconv_fwd_kernel(const DwParams p) {
 
 }  // namespace ctn
 
-extern "C" int ctn_dwconv_gln_partials(int K) { return ctn::ceil_div(K, CTN_DW_TILE); }
+static bool dw_use_march(int H, int P, int norm) { return norm == CTN_NORM_GLN && P == 3 && H % 4 == 0; }
+
+extern "C" int ctn_dwconv_gln_partials(int K, int H, int P, int dilation) {
+    if (dw_use_march(H, P, CTN_NORM_GLN) && dilation > 0) {
+        int NS, items;
+        ctn::dw_march_geometry(K, H, dilation, &NS, &items);
+        return ctn::ceil_div(items, ctn::kDmWarps);
+    }
+    return ctn::ceil_div(K, CTN_DW_TILE);
+}
 
 extern "C" int ctn_dwconv_fwd(const ctn_dwconv_args* args, void* stream) {
     using namespace ctn;
@@ -221,11 +231,26 @@ extern "C" int ctn_dwconv_fwd(const ctn_dwconv_args* args, void* stream) {
     p.wd = a.wd, p.prelu_out = a.prelu_out, p.out_pre = a.out_pre;
     p.out_hi = static_cast<__nv_bfloat16*>(a.out_hi), p.out_lo = static_cast<__nv_bfloat16*>(a.out_lo);
     p.out_stat = static_cast<float2*>(a.out_stat);
-    p.out_P = ctn_dwconv_gln_partials(a.K);
+    p.out_P = ctn_dwconv_gln_partials(a.K, a.H, a.P, a.dilation);
+    auto al16 = [](const void* q) { return (reinterpret_cast<uintptr_t>(q) & 15) == 0; };
+    if (dw_use_march(a.H, a.P, a.norm) && al16(a.in) && al16(a.out_pre) && al16(a.out_hi) && al16(a.out_lo) &&
+        al16(a.gamma_in) && al16(a.beta_in) && al16(a.wd)) {
+        DwMarchParams q;
+        q.K = a.K, q.H = a.H, q.dil = a.dilation, q.c0 = a.causal ? 2 : 1, q.in_P = a.in_P;
+        dw_march_geometry(a.K, a.H, a.dilation, &q.NS, &q.items);
+        q.out_P = p.out_P;
+        q.in = a.in, q.prelu_in = a.prelu_in, q.gamma_in = a.gamma_in, q.beta_in = a.beta_in;
+        q.in_stat = p.in_stat, q.wd = a.wd, q.prelu_out = a.prelu_out, q.out_pre = a.out_pre;
+        q.out_hi = p.out_hi, q.out_lo = p.out_lo, q.out_stat = p.out_stat;
+        dim3 mgrid(q.out_P, a.M);
+        dwconv_march_kernel<<<mgrid, kDmWarps * 32, 0, static_cast<cudaStream_t>(stream)>>>(q);
+        CTN_LAUNCH_CHECK("dwconv_march_kernel");
+        return CTN_OK;
+    }
+    CTN_REQUIRE(!dw_use_march(a.H, a.P, a.norm), "ctn_dwconv_fwd: pointers must be 16-byte aligned");
     const size_t smem = (static_cast<size_t>(a.P + 2) * a.H + 2 * kDwWarps + 2) * sizeof(float);
     CTN_REQUIRE(smem <= 48 * 1024, "ctn_dwconv_fwd: H*(P+2)=%d too large for shared memory", a.H * (a.P + 2));
     dim3 grid(ceil_div(a.K, kDwTile), a.M);
-    auto al16 = [](const void* q) { return (reinterpret_cast<uintptr_t>(q) & 15) == 0; };
     const bool vec = a.H % 4 == 0 && al16(a.in) && al16(a.out_pre) && al16(a.out_hi) && al16(a.out_lo);
     if (vec)
         dwconv_fwd_kernel<4><<<grid, kDwWarps * 32, smem, static_cast<cudaStream_t>(stream)>>>(p);

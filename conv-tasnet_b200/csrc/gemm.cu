@@ -38,6 +38,12 @@ struct EpiParams {
     float2* out_stat_buf;
     int out_P;
     const float* stat_prelu;
+    // backward statistics (pointwise dgrad): see ctn_gemm_args.bw_*
+    const float* bw_pre;
+    const float* bw_gamma;
+    const float* bw_slope;
+    const float2* bw_stat;
+    int bw_P;
 };
 
 // One thread owns output row `grow` (valid or not) and 32 consecutive columns
@@ -46,7 +52,7 @@ struct EpiParams {
 template <bool VEC>
 __device__ __forceinline__ void epilogue_chunk(const EpiParams& ep, float (&v)[32], long long grow, int n0,
                                                bool valid, float s, float t, float slope, bool use_slope,
-                                               float& ls, float& lss) {
+                                               float bw_mean, float bw_rstd, float& ls, float& lss) {
     if (n0 >= ep.Cout) return;
     const int ncols = min(32, ep.Cout - n0);
     // folded norm + bias
@@ -77,7 +83,18 @@ __device__ __forceinline__ void epilogue_chunk(const EpiParams& ep, float (&v)[3
                 if (j < ncols) v[j] += ep.resid[base + j];
         }
     }
-    if (ep.out_stat != CTN_NORM_NONE) {
+    if (ep.bw_pre != nullptr) {
+        // gLN backward sums: slope = PReLU slope of the saved pre-activation, (s, t) reused as (mean, rstd)
+#pragma unroll
+        for (int j = 0; j < 32; ++j) {
+            if (j < ncols) {
+                const float qh = (prelu(ep.bw_pre[base + j], slope) - bw_mean) * bw_rstd;
+                const float gd = __ldg(ep.bw_gamma + n0 + j) * v[j];
+                ls += gd;
+                lss = fmaf(gd, qh, lss);
+            }
+        }
+    } else if (ep.out_stat != CTN_NORM_NONE) {
 #pragma unroll
         for (int j = 0; j < 32; ++j) {
             if (j < ncols) {
@@ -142,6 +159,16 @@ __device__ __forceinline__ void epilogue_row_affine(const EpiParams& ep, int m, 
     }
 }
 
+// (mean, rstd) of the forward norm whose backward sums the epilogue accumulates.  Warp-collective.
+__device__ __forceinline__ void epilogue_bw_stats(const EpiParams& ep, int m, float& mean, float& rstd) {
+    mean = 0.f, rstd = 1.f;
+    if (ep.bw_pre != nullptr) {
+        const float2 st = gln_finalize_warp(ep.bw_stat + static_cast<long long>(m) * ep.bw_P, ep.bw_P,
+                                            static_cast<double>(ep.K) * ep.Cout);
+        mean = st.x, rstd = st.y;
+    }
+}
+
 // Flush the statistics of one 128-column group.  Warp-collective (gLN path).
 __device__ __forceinline__ void epilogue_flush_stats(const EpiParams& ep, int m, int tk, int grp, int ew,
                                                      long long grow, bool valid, float& ls, float& lss) {
@@ -169,8 +196,12 @@ struct TcCfg {
     static constexpr int kABytes = kBM * kBK * 2;  // one of hi / lo
     static constexpr int kWBytes = BN * kBK * 2;
     static constexpr int kStageBytes = 2 * kABytes + 2 * kWBytes;
+    // epilogue staging per warp: fp32 block 32 x 128 B, then the hi and lo blocks 32 x 64 B each
+    static constexpr int kStgWarpBytes = 8192;
+    static constexpr int kStgBytes = 4 * kStgWarpBytes;
+    static constexpr int kColBytes = 2 * BN * 4;   // col_g, col_bias of the current column tile
     static constexpr int kBarBytes = 256;
-    static constexpr int kSmemBytes = kStages * kStageBytes + kBarBytes + 1024;  // + alignment slack
+    static constexpr int kSmemBytes = kStages * kStageBytes + kStgBytes + kColBytes + kBarBytes;
     static constexpr int kTmemCols = 2 * BN;
 };
 
@@ -178,11 +209,15 @@ template <int BN>
 __global__ void __launch_bounds__(kTcThreads, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tm_a_hi, const __grid_constant__ CUtensorMap tm_a_lo,
                const __grid_constant__ CUtensorMap tm_w_hi, const __grid_constant__ CUtensorMap tm_w_lo,
-               const EpiParams ep, int Cin, int n_tiles, int total_tiles) {
+               const __grid_constant__ CUtensorMap tm_o_f32, const __grid_constant__ CUtensorMap tm_o_hi,
+               const __grid_constant__ CUtensorMap tm_o_lo, const EpiParams ep, int Cin, int n_tiles,
+               int total_tiles) {
     using Cfg = TcCfg<BN>;
-    extern __shared__ uint8_t smem_raw[];
-    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-    uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + Cfg::kStages * Cfg::kStageBytes);
+    extern __shared__ __align__(1024) uint8_t smem[];
+    if ((ptx::smem_u32(smem) & 1023u) != 0) __trap();  // 128B-swizzled tiles need 1024 B alignment
+    uint8_t* stg = smem + Cfg::kStages * Cfg::kStageBytes;
+    float* col_s = reinterpret_cast<float*>(stg + Cfg::kStgBytes);
+    uint64_t* full_bar = reinterpret_cast<uint64_t*>(stg + Cfg::kStgBytes + Cfg::kColBytes);
     uint64_t* empty_bar = full_bar + Cfg::kStages;
     uint64_t* tfull_bar = empty_bar + Cfg::kStages;
     uint64_t* tempty_bar = tfull_bar + 2;
@@ -276,11 +311,23 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tm_a_hi, const __grid_constan
         }
     } else {
         // ---------------------------------------------------- epilogue
+        // TMEM -> registers -> fused math -> swizzled smem staging -> TMA store.  Each warp
+        // owns 32 rows and its own 8 KB staging area, so no cross-warp barrier is needed for
+        // the stores; the residual of the next chunk is prefetched under the current one.
         const int ew = warp & 3;  // TMEM lane quarter this warp may read
+        const int et = threadIdx.x - 64;  // 0..127 among the epilogue threads
         float slope = 0.f;
         const bool use_slope = ep.stat_prelu != nullptr;
         if (use_slope) slope = __ldg(ep.stat_prelu);
-        int it = 0;
+        const bool bw = ep.bw_pre != nullptr;
+        const bool affine = !bw && (ep.col_g != nullptr || ep.col_bias != nullptr || ep.in_norm != CTN_NORM_NONE);
+        const float bw_slope = bw ? __ldg(ep.bw_slope) : 0.f;
+        const float* aux = bw ? ep.bw_pre : ep.resid;  // per-element side input, prefetched one chunk ahead
+        const uint32_t stg_f32 = ptx::smem_u32(stg + ew * Cfg::kStgWarpBytes);
+        const uint32_t stg_hi = stg_f32 + 4096, stg_lo = stg_f32 + 6144;
+        const uint32_t sw128 = static_cast<uint32_t>(lane & 7);
+        const uint32_t sw64 = static_cast<uint32_t>((lane >> 1) & 3);
+        int it = 0, cur_tn = -1;
         for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it) {
             const int as = it & 1;
             const uint32_t aphase = (it >> 1) & 1;
@@ -290,23 +337,128 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tm_a_hi, const __grid_constan
             const int k = tk * kBM + ew * 32 + lane;
             const bool valid = k < ep.K;
             const long long grow = static_cast<long long>(m) * ep.K + k;
-            float s, t;
+            float s, t, bw_mean, bw_rstd;
             epilogue_row_affine(ep, m, grow, valid, s, t);
-
+            epilogue_bw_stats(ep, m, bw_mean, bw_rstd);
+            if ((affine || bw) && tn != cur_tn) {  // per-column constants of this column tile -> smem
+                ptx::named_bar_sync(1, 128);
+                for (int i = et; i < BN; i += 128) {
+                    const int n = tn * BN + i;
+                    const float* cg = bw ? ep.bw_gamma : ep.col_g;
+                    col_s[i] = (cg && n < ep.Cout) ? __ldg(cg + n) : 0.f;
+                    col_s[BN + i] = (ep.col_bias && n < ep.Cout) ? __ldg(ep.col_bias + n) : 0.f;
+                }
+                ptx::named_bar_sync(1, 128);
+                cur_tn = tn;
+            }
+            const int ncol_tile = min(BN, ep.Cout - tn * BN);  // multiple of 8
+            float4 rn[8];                                       // residual prefetch, one chunk ahead
+            auto load_resid = [&](int c) {
+                if (aux != nullptr && valid && c * 32 < ncol_tile) {
+                    const float4* rp = reinterpret_cast<const float4*>(aux + grow * ep.Cout + tn * BN + c * 32);
+                    const int nv = min(32, ncol_tile - c * 32) >> 2;
+#pragma unroll
+                    for (int j = 0; j < 8; ++j)
+                        if (j < nv) rn[j] = rp[j];
+                }
+            };
+            load_resid(0);
             ptx::mbar_wait(tfull_bar + as, aphase);
             ptx::tc_fence_after();
             float ls = 0.f, lss = 0.f;
 #pragma unroll 1
             for (int c = 0; c < BN / 32; ++c) {
                 const int n0 = tn * BN + c * 32;
-                if (n0 < ep.Cout) {
+                if (c * 32 < ncol_tile) {
+                    const int ncols = min(32, ncol_tile - c * 32);
                     uint32_t r[32];
                     ptx::tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(ew * 32) << 16) + as * BN + c * 32, r);
+                    float4 rc[8];
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) rc[j] = rn[j];
+                    load_resid(c + 1);
                     ptx::tmem_ld_wait();
                     float v[32];
 #pragma unroll
                     for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
-                    epilogue_chunk<true>(ep, v, grow, n0, valid, s, t, slope, use_slope, ls, lss);
+                    if (affine) {
+#pragma unroll
+                        for (int j = 0; j < 32; j += 4) {
+                            const float4 g = *reinterpret_cast<const float4*>(col_s + c * 32 + j);
+                            const float4 b = *reinterpret_cast<const float4*>(col_s + BN + c * 32 + j);
+                            v[j] = fmaf(s, v[j], fmaf(t, g.x, b.x));
+                            v[j + 1] = fmaf(s, v[j + 1], fmaf(t, g.y, b.y));
+                            v[j + 2] = fmaf(s, v[j + 2], fmaf(t, g.z, b.z));
+                            v[j + 3] = fmaf(s, v[j + 3], fmaf(t, g.w, b.w));
+                        }
+                    }
+                    if (ep.resid != nullptr && valid) {
+#pragma unroll
+                        for (int j = 0; j < 8; ++j)
+                            if (j * 4 < ncols) {
+                                v[4 * j] += rc[j].x, v[4 * j + 1] += rc[j].y;
+                                v[4 * j + 2] += rc[j].z, v[4 * j + 3] += rc[j].w;
+                            }
+                    }
+                    if (bw && valid) {
+#pragma unroll
+                        for (int j = 0; j < 8; ++j)
+                            if (j * 4 < ncols) {
+                                const float dv[4] = {rc[j].x, rc[j].y, rc[j].z, rc[j].w};
+                                const float4 g = *reinterpret_cast<const float4*>(col_s + c * 32 + 4 * j);
+                                const float gv[4] = {g.x, g.y, g.z, g.w};
+#pragma unroll
+                                for (int q = 0; q < 4; ++q) {
+                                    const float qh = (prelu(dv[q], bw_slope) - bw_mean) * bw_rstd;
+                                    const float gd = gv[q] * v[4 * j + q];
+                                    ls += gd;
+                                    lss = fmaf(gd, qh, lss);
+                                }
+                            }
+                    } else if (ep.out_stat != CTN_NORM_NONE && valid) {
+#pragma unroll
+                        for (int j = 0; j < 32; ++j)
+                            if (j < ncols) {
+                                const float x = use_slope ? prelu(v[j], slope) : v[j];
+                                ls += x;
+                                lss = fmaf(x, x, lss);
+                            }
+                    }
+                    // wait until the TMA engine has finished READING this warp's staging area
+                    if (lane == 0) ptx::tma_store_wait_read<0>();
+                    __syncwarp();
+                    if (ep.out_f32 != nullptr) {
+#pragma unroll
+                        for (int j = 0; j < 8; ++j)
+                            ptx::st_shared_v4(stg_f32 + lane * 128 + ((static_cast<uint32_t>(j) ^ sw128) << 4),
+                                              __float_as_uint(v[4 * j]), __float_as_uint(v[4 * j + 1]),
+                                              __float_as_uint(v[4 * j + 2]), __float_as_uint(v[4 * j + 3]));
+                    }
+                    if (ep.out_hi != nullptr) {
+#pragma unroll
+                        for (int j = 0; j < 4; ++j) {
+                            uint32_t h[4], l[4];
+#pragma unroll
+                            for (int q = 0; q < 4; ++q) split_pack2(v[8 * j + 2 * q], v[8 * j + 2 * q + 1], h[q], l[q]);
+                            const uint32_t off = lane * 64 + ((static_cast<uint32_t>(j) ^ sw64) << 4);
+                            ptx::st_shared_v4(stg_hi + off, h[0], h[1], h[2], h[3]);
+                            ptx::st_shared_v4(stg_lo + off, l[0], l[1], l[2], l[3]);
+                        }
+                    }
+                    ptx::fence_async_smem();
+                    __syncwarp();
+                    if (lane == 0) {
+                        const int krow0 = tk * kBM + ew * 32;
+                        if (krow0 < ep.K) {  // rows past K are clipped by the tensor map's K extent
+                            if (ep.out_f32 != nullptr)
+                                ptx::tma_store_3d(&tm_o_f32, stg + ew * Cfg::kStgWarpBytes, n0, krow0, m);
+                            if (ep.out_hi != nullptr) {
+                                ptx::tma_store_3d(&tm_o_hi, stg + ew * Cfg::kStgWarpBytes + 4096, n0, krow0, m);
+                                ptx::tma_store_3d(&tm_o_lo, stg + ew * Cfg::kStgWarpBytes + 6144, n0, krow0, m);
+                            }
+                        }
+                        ptx::tma_store_commit();
+                    }
                 }
                 if ((c & 3) == 3) {
                     const int grp = (tn * BN + c * 32) / CTN_COL_TILE;
@@ -316,6 +468,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tm_a_hi, const __grid_constan
             ptx::tc_fence_before();
             ptx::mbar_arrive(tempty_bar + as);
         }
+        if (lane == 0) ptx::tma_store_wait_all<0>();
     }
 
     ptx::tc_fence_before();
@@ -344,8 +497,10 @@ gemm_simt_kernel(const __nv_bfloat16* __restrict__ a_hi, const __nv_bfloat16* __
     float slope = 0.f;
     const bool use_slope = ep.stat_prelu != nullptr;
     if (use_slope) slope = __ldg(ep.stat_prelu);
-    float s, t;
+    float s, t, bw_mean, bw_rstd;
     epilogue_row_affine(ep, m, grow, valid, s, t);
+    epilogue_bw_stats(ep, m, bw_mean, bw_rstd);
+    if (ep.bw_pre != nullptr) slope = __ldg(ep.bw_slope);
     float ls = 0.f, lss = 0.f;
     for (int grp = 0; grp < ep.groups; ++grp) {
         for (int c = 0; c < CTN_COL_TILE / 32; ++c) {
@@ -366,7 +521,7 @@ gemm_simt_kernel(const __nv_bfloat16* __restrict__ a_hi, const __nv_bfloat16* __
                     }
                 }
             }
-            epilogue_chunk<false>(ep, v, grow, n0, valid, s, t, slope, use_slope, ls, lss);
+            epilogue_chunk<false>(ep, v, grow, n0, valid, s, t, slope, use_slope, bw_mean, bw_rstd, ls, lss);
         }
         epilogue_flush_stats(ep, m, tk, grp, ew, grow, valid, ls, lss);
     }
@@ -391,6 +546,16 @@ static PFN_encodeTiled get_encode_fn() {
     return fn;
 }
 
+int make_tmap_bf16_kmajor(CUtensorMap* tm, const void* ptr, long long rows, int cols, int box_rows);
+// same map, named for its use by the weight-gradient kernel (MN-major reads of the same tiles)
+int make_tmap_bf16_box(CUtensorMap* tm, const void* ptr, long long rows, int cols, int box_cols, int box_rows) {
+    if (box_cols != kBK) {
+        set_error("make_tmap_bf16_box: only 64-column boxes are supported");
+        return CTN_ERR_INVALID;
+    }
+    return make_tmap_bf16_kmajor(tm, ptr, rows, cols, box_rows);
+}
+
 // bf16 [rows, cols] row-major, box = 64 columns x box_rows rows, 128B swizzle, zero OOB fill
 int make_tmap_bf16_kmajor(CUtensorMap* tm, const void* ptr, long long rows, int cols, int box_rows) {
     PFN_encodeTiled enc = get_encode_fn();
@@ -412,6 +577,30 @@ int make_tmap_bf16_kmajor(CUtensorMap* tm, const void* ptr, long long rows, int 
     return CTN_OK;
 }
 
+// [M, K, C] row-major output, box = 32 columns x 32 frames of one utterance; rows past K are
+// clipped by the map, so a partial last row tile never touches the next utterance.
+static int make_tmap_out(CUtensorMap* tm, const void* ptr, int M, int K, int C, bool f32) {
+    PFN_encodeTiled enc = get_encode_fn();
+    if (!enc) {
+        set_error("cuTensorMapEncodeTiled not available from the driver");
+        return CTN_ERR_CUDA;
+    }
+    const cuuint64_t es = f32 ? 4 : 2;
+    cuuint64_t dims[3] = {static_cast<cuuint64_t>(C), static_cast<cuuint64_t>(K), static_cast<cuuint64_t>(M)};
+    cuuint64_t strides[2] = {static_cast<cuuint64_t>(C) * es, static_cast<cuuint64_t>(C) * es * K};
+    cuuint32_t box[3] = {32, 32, 1};
+    cuuint32_t estr[3] = {1, 1, 1};
+    CUresult r = enc(tm, f32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3,
+                     const_cast<void*>(ptr), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                     f32 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_NONE,
+                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) {
+        set_error("cuTensorMapEncodeTiled(out) failed (%d) ptr=%p M=%d K=%d C=%d", static_cast<int>(r), ptr, M, K, C);
+        return CTN_ERR_CUDA;
+    }
+    return CTN_OK;
+}
+
 template <int BN>
 static int launch_tc(const ctn_gemm_args& a, const EpiParams& ep, cudaStream_t stream) {
     using Cfg = TcCfg<BN>;
@@ -422,6 +611,14 @@ static int launch_tc(const ctn_gemm_args& a, const EpiParams& ep, cudaStream_t s
     if ((rc = make_tmap_bf16_kmajor(&ta_lo, a.a_lo, R, a.Cin, kBM)) != CTN_OK) return rc;
     if ((rc = make_tmap_bf16_kmajor(&tw_hi, a.w_hi, a.Cout, a.Cin, BN)) != CTN_OK) return rc;
     if ((rc = make_tmap_bf16_kmajor(&tw_lo, a.w_lo, a.Cout, a.Cin, BN)) != CTN_OK) return rc;
+    CUtensorMap to_f32, to_hi, to_lo;
+    // unused maps still have to be valid objects: point them at an operand
+    if ((rc = make_tmap_out(&to_f32, a.out_f32 ? a.out_f32 : a.out_hi, a.M, a.K, a.Cout, a.out_f32 != nullptr)) != CTN_OK)
+        return rc;
+    if ((rc = make_tmap_out(&to_hi, a.out_hi ? a.out_hi : a.out_f32, a.M, a.K, a.Cout, a.out_hi == nullptr)) != CTN_OK)
+        return rc;
+    if ((rc = make_tmap_out(&to_lo, a.out_lo ? a.out_lo : a.out_f32, a.M, a.K, a.Cout, a.out_lo == nullptr)) != CTN_OK)
+        return rc;
     static bool attr_set = false;  // idempotent; set once per process per instantiation
     if (!attr_set) {
         cudaError_t e = cudaFuncSetAttribute(gemm_tc_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -432,8 +629,8 @@ static int launch_tc(const ctn_gemm_args& a, const EpiParams& ep, cudaStream_t s
     const int n_tiles = ceil_div(a.Cout, BN);
     const int total = a.M * ep.tiles_per_utt * n_tiles;
     const int grid = total < sm_count() ? total : sm_count();
-    gemm_tc_kernel<BN><<<grid, kTcThreads, Cfg::kSmemBytes, stream>>>(ta_hi, ta_lo, tw_hi, tw_lo, ep, a.Cin, n_tiles,
-                                                                      total);
+    gemm_tc_kernel<BN><<<grid, kTcThreads, Cfg::kSmemBytes, stream>>>(ta_hi, ta_lo, tw_hi, tw_lo, to_f32, to_hi, to_lo,
+                                                                      ep, a.Cin, n_tiles, total);
     CTN_LAUNCH_CHECK("gemm_tc_kernel");
     return CTN_OK;
 }
@@ -475,11 +672,16 @@ extern "C" int ctn_gemm1x1(const ctn_gemm_args* args, void* stream_) {
     ep.out_stat = a.out_stat, ep.out_stat_buf = static_cast<float2*>(a.out_stat_buf);
     ep.out_P = ctn_gemm_gln_partials(a.K, a.Cout);
     ep.stat_prelu = a.stat_prelu;
+    ep.bw_pre = a.bw_pre, ep.bw_gamma = a.bw_gamma, ep.bw_slope = a.bw_slope;
+    ep.bw_stat = static_cast<const float2*>(a.bw_stat), ep.bw_P = a.bw_P;
+    CTN_REQUIRE(a.bw_pre == nullptr || (a.bw_gamma && a.bw_slope && a.bw_stat && a.bw_P > 0 &&
+                                        a.out_stat == CTN_NORM_GLN && a.resid == nullptr && a.in_norm == CTN_NORM_NONE),
+                "ctn_gemm1x1: bw_pre needs bw_gamma/bw_slope/bw_stat, out_stat = GLN and no resid / in_norm");
 
     auto aligned16 = [](const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; };
     const bool tc_ok = !a.force_simt && a.Cin % 8 == 0 && a.Cout % 8 == 0 && aligned16(a.a_hi) && aligned16(a.a_lo) &&
                        aligned16(a.w_hi) && aligned16(a.w_lo) && aligned16(a.out_f32) && aligned16(a.out_hi) &&
-                       aligned16(a.out_lo) && aligned16(a.resid);
+                       aligned16(a.out_lo) && aligned16(a.resid) && aligned16(a.bw_pre);
     if (tc_ok) {
         // 256-wide tiles halve the re-reads of the activation tile but need enough tiles to fill the SMs
         const long long tiles256 = static_cast<long long>(a.M) * ep.tiles_per_utt * ceil_div(a.Cout, 256);

@@ -104,12 +104,14 @@ class _Plan:
         self.norm = _NORM[cfg["norm_type"]]
         if self.norm == nat.NORM_GLN:
             self.P1 = lib.ctn_gemm_gln_partials(K, H)
-            self.P2 = lib.ctn_dwconv_gln_partials(K)
+            self.P2s = [lib.ctn_dwconv_gln_partials(K, H, cfg["P"], 2 ** x) for x in range(cfg["X"])]
+            self.P2 = max(self.P2s)
             self.stat1 = torch.zeros(M, self.P1, 2, **f32)
             self.stat2 = torch.zeros(M, self.P2, 2, **f32)
         else:
             self.P1 = lib.ctn_gemm_cln_groups(H)
             self.P2 = 1
+            self.P2s = [1] * cfg["X"]
             self.stat1 = torch.zeros(R_, self.P1, 2, **f32)
             self.stat2 = torch.zeros(R_, 2, **f32)
         self.calls = None
@@ -174,7 +176,7 @@ class _Plan:
                 calls.append(lambda s, ref=C.byref(d): dw(ref, s))
                 calls.append(self._gemm(Cin=H, Cout=B, a_hi=self.q_hl[0], a_lo=self.q_hl[1], w_hi=pb["w2"][0],
                                         w_lo=pb["w2"][1], col_g=pb["w2"][2], col_bias=pb["w2"][3],
-                                        in_norm=self.norm, in_stat=self.stat2, in_P=self.P2,
+                                        in_norm=self.norm, in_stat=self.stat2, in_P=self.P2s[xb],
                                         in_count=float(K) * H, resid=self.x,
                                         out_f32=self.x, out_hi=self.x_hl[0], out_lo=self.x_hl[1]))
         calls.append(self._gemm(Cin=B, Cout=C_ * N, a_hi=self.x_hl[0], a_lo=self.x_hl[1], w_hi=prep.mask[0],

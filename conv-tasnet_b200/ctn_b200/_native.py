@@ -28,6 +28,7 @@ class GemmArgs(C.Structure):
         ("in_norm", C.c_int), ("in_stat", _vp), ("in_P", C.c_int), ("in_count", C.c_double),
         ("out_stat", C.c_int), ("out_stat_buf", _vp), ("stat_prelu", _vp),
         ("force_simt", C.c_int),
+        ("bw_pre", _vp), ("bw_gamma", _vp), ("bw_slope", _vp), ("bw_stat", _vp), ("bw_P", C.c_int),
     ]
 
 
@@ -43,11 +44,37 @@ class DwconvArgs(C.Structure):
     ]
 
 
+class BwdDwArgs(C.Structure):
+    """struct ctn_bwd_dw_args"""
+    _fields_ = [
+        ("M", C.c_int), ("K", C.c_int), ("H", C.c_int), ("P", C.c_int), ("dilation", C.c_int), ("causal", C.c_int),
+        ("P1", C.c_int), ("P2", C.c_int), ("Pb", C.c_int),
+        ("du", _vp), ("d", _vp), ("a", _vp), ("stat1", _vp), ("stat2", _vp), ("bstat", _vp),
+        ("g1", _vp), ("b1", _vp), ("g2", _vp), ("wd", _vp), ("slope1", _vp), ("slope2", _vp),
+        ("dn1", _vp), ("chan_part", _vp), ("scal_part", _vp),
+    ]
+
+
+MAX_SEG = 12
+
+
+class ReduceArgs(C.Structure):
+    """struct ctn_reduce_args"""
+    _fields_ = [
+        ("part", _vp), ("n_part", C.c_int), ("part_stride", C.c_longlong), ("nseg", C.c_int),
+        ("accumulate", C.c_int),
+        ("src_off", C.c_longlong * MAX_SEG), ("len", C.c_int * MAX_SEG), ("src_stride", C.c_int * MAX_SEG),
+        ("dst", _vp * MAX_SEG), ("dst_stride", C.c_int * MAX_SEG),
+    ]
+
+
+_i, _ll = C.c_int, C.c_longlong
+
 _SIGNATURES = {
     "ctn_version": (C.c_int, []),
     "ctn_last_error": (C.c_char_p, []),
     "ctn_gemm_gln_partials": (C.c_int, [C.c_int, C.c_int]),
-    "ctn_dwconv_gln_partials": (C.c_int, [C.c_int]),
+    "ctn_dwconv_gln_partials": (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_int]),
     "ctn_gemm_cln_groups": (C.c_int, [C.c_int]),
     "ctn_weight_prep": (C.c_int, [_vp, C.c_int, C.c_int, _vp, _vp, C.c_int, _vp, _vp, _vp, _vp, _vp]),
     "ctn_encoder_fwd": (C.c_int, [_vp, _vp, C.c_int, C.c_int, C.c_int, C.c_int, _vp, _vp, _vp, _vp, _vp]),
@@ -56,6 +83,20 @@ _SIGNATURES = {
     "ctn_decoder_fwd": (C.c_int, [_vp, _vp, _vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
                                   _vp, _vp]),
     "ctn_overlap_add": (C.c_int, [_vp, C.c_int, C.c_int, C.c_int, C.c_int, _vp, _vp]),
+    "ctn_norm_split": (_i, [_vp, _vp, _vp, _vp, _i, _vp, _i, _i, _i, _i, _vp, _vp, _vp]),
+    "ctn_wgrad_splits": (_i, [_ll, _i, _i]),
+    "ctn_wgrad": (_i, [_vp, _vp, _vp, _vp, _ll, _i, _i, _vp, _i, _vp]),
+    "ctn_bwd_dw_layout": (_i, [_i, _i, C.POINTER(_i), C.POINTER(_i)]),
+    "ctn_bwd_dwconv": (_i, [C.POINTER(BwdDwArgs), _vp]),
+    "ctn_bwd_prelu_norm_tiles": (_i, [_i]),
+    "ctn_bwd_prelu_norm": (_i, [_vp, _vp, _vp, _i, _vp, _i, _vp, _vp, _i, _i, _i, _vp, _vp, _vp, _vp]),
+    "ctn_reduce_partials": (_i, [C.POINTER(ReduceArgs), _vp]),
+    "ctn_decoder_bwd_tiles": (_i, [_i]),
+    "ctn_decoder_bwd": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp]),
+    "ctn_cln_bwd_tiles": (_i, [_i]),
+    "ctn_cln_bwd": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _vp, _vp, _vp]),
+    "ctn_encoder_wgrad_tiles": (_i, [_i]),
+    "ctn_encoder_wgrad": (_i, [_vp, _vp, _i, _i, _i, _i, _vp, _vp]),
     "ctn_pit_workspace_doubles": (C.c_int, [C.c_int, C.c_int, C.c_int]),
     "ctn_pit_sisnr_fwd": (C.c_int, [_vp, _vp, _vp, C.c_int, C.c_int, C.c_int, _vp, C.c_int, _vp, _vp, _vp, _vp,
                                     _vp, _vp, _vp]),

@@ -53,7 +53,7 @@ const char* ctn_last_error(void);
 /* Number of (sum, sumsq) float2 partials per utterance written by
  * ctn_gemm1x1 (out_stat = GLN) and by ctn_dwconv_fwd (norm = GLN). */
 int ctn_gemm_gln_partials(int K, int Cout);
-int ctn_dwconv_gln_partials(int K);
+int ctn_dwconv_gln_partials(int K, int H, int P, int dilation);
 /* Number of per-row column-group partials written by ctn_gemm1x1 (out_stat = CLN). */
 int ctn_gemm_cln_groups(int Cout);
 
@@ -100,6 +100,15 @@ typedef struct ctn_gemm_args {
     void* out_stat_buf;
     const float* stat_prelu;
     int force_simt; /* testing: skip the tcgen05 path */
+    /* Backward use (pointwise dgrad): with out = du, also emit the gLN backward sums
+     * (sum g*du, sum g*du*qh), qh = (prelu(bw_pre) - mean) * rstd, as GLN-layout partials in
+     * out_stat_buf (out_stat must be CTN_NORM_GLN).  bw_pre fp32 [M*K, Cout] = saved d,
+     * bw_gamma [Cout], bw_slope device scalar, bw_stat float2 [M, bw_P] forward partials. */
+    const float* bw_pre;
+    const float* bw_gamma;
+    const float* bw_slope;
+    const void* bw_stat;
+    int bw_P;
 } ctn_gemm_args;
 
 /* 1x1 convolution as a GEMM over all frames of the batch (bottleneck
@@ -120,7 +129,7 @@ typedef struct ctn_dwconv_args {
     const float* prelu_out; /* slope of the second PReLU, :253                         */
     float* out_pre;         /* d = depthwise output before PReLU, fp32 [M*K,H] or NULL */
     void *out_hi, *out_lo;  /* q = prelu(d) as bf16 pair [M*K, H]                      */
-    void* out_stat;         /* GLN: float2 [M, ctn_dwconv_gln_partials(K)] partials of q;
+    void* out_stat;         /* GLN: float2 [M, ctn_dwconv_gln_partials(K, H, P, dilation)] partials of q;
                                CLN: float2 [M*K] (mean, rstd) of q                     */
 } ctn_dwconv_args;
 
@@ -168,6 +177,85 @@ int ctn_pit_reorder(const float* estimate, const long long* perms, const long lo
 int ctn_pit_sisnr_bwd(const float* source, const float* estimate, const long long* lengths, const long long* perms,
                       const long long* max_idx, const float* coef, const float* upstream, int B, int C, int T,
                       float* grad_estimate, void* stream);
+
+/* ---- backward of the separator (autograd of conv_tasnet.py) ------- */
+
+/* out = split_bf16(gamma * (act(in) - mean) * rstd + beta), act = PReLU(*prelu_slope) or
+ * identity (NULL).  Re-materialises a normalised activation as the (hi, lo) operand of a
+ * weight-gradient GEMM.  stat: GLN float2 [M, P] partials; CLN float2 [M*K] (mean, rstd). */
+int ctn_norm_split(const float* in, const float* prelu_slope, const float* gamma, const float* beta, int norm,
+                   const void* stat, int P, int M, int K, int C, void* out_hi, void* out_lo, void* stream);
+
+/* Weight gradient of a 1x1 convolution: G[i, j] = sum_r x[r, i] * y[r, j] over all R rows,
+ * x bf16 (hi, lo) [R, Ci], y bf16 (hi, lo) [R, Cj] -> fp32 partials [splits, Ci, Cj]
+ * (one per row split; sum them with ctn_reduce_partials).  tcgen05 path with MN-major
+ * operands when Ci % 8 == 0 && Cj % 8 == 0. */
+int ctn_wgrad_splits(long long R, int Ci, int Cj);
+int ctn_wgrad(const void* x_hi, const void* x_lo, const void* y_hi, const void* y_lo, long long R, int Ci, int Cj,
+              float* partials, int force_simt, void* stream);
+
+typedef struct ctn_bwd_dw_args {
+    int M, K, H, P, dilation, causal;
+    int P1, P2, Pb;        /* partial counts of stat1, stat2, bstat per utterance          */
+    const float* du;       /* d loss / d u from the pointwise dgrad GEMM, fp32 [M*K, H]    */
+    const float* d;        /* saved depthwise output (before PReLU)                        */
+    const float* a;        /* saved conv1x1 output (before PReLU)                          */
+    const void* stat1;     /* forward gLN partials of prelu(a)                             */
+    const void* stat2;     /* forward gLN partials of prelu(d)                             */
+    const void* bstat;     /* (sum g2*du, sum g2*du*qh) partials from the dgrad epilogue   */
+    const float *g1, *b1, *g2, *wd, *slope1, *slope2;
+    float* dn1;            /* out: d loss / d n1, fp32 [M*K, H]                            */
+    float* chan_part;      /* out: [M*tiles*row_groups][(4+P)*H]: dg2, db2, dg1, db1, dwd[j] */
+    float* scal_part;      /* out: [M*tiles][4]: sum g1*dn1, sum g1*dn1*ph, d slope2, 0     */
+} ctn_bwd_dw_args;
+
+/* gLN-2 backward + PReLU-2 backward + depthwise backward (input and weight grads) +
+ * gLN-1 parameter grads, one pass (gLN models). */
+int ctn_bwd_dw_layout(int K, int H, int* tiles, int* row_groups);
+int ctn_bwd_dwconv(const ctn_bwd_dw_args* args, void* stream);
+
+/* gLN-1 input gradient + PReLU-1 backward: da (hi, lo) [M*K, H] and per-CTA d slope1 partials
+ * [M * ctn_bwd_prelu_norm_tiles(K)]. */
+int ctn_bwd_prelu_norm_tiles(int K);
+int ctn_bwd_prelu_norm(const float* dn1, const float* a, const void* stat1, int P1, const float* scal_part,
+                       int tiles_b, const float* g1, const float* slope1, int M, int K, int H, void* da_hi,
+                       void* da_lo, float* alpha_part, void* stream);
+
+#define CTN_MAX_SEG 12
+typedef struct ctn_reduce_args {
+    const float* part;      /* [n_part] rows of partial sums                                */
+    int n_part;
+    long long part_stride;  /* floats between consecutive partial rows                      */
+    int nseg;
+    int accumulate;         /* 0: dst = sum, 1: dst += sum                                  */
+    long long src_off[CTN_MAX_SEG];
+    int len[CTN_MAX_SEG];
+    int src_stride[CTN_MAX_SEG]; /* 0 -> 1 */
+    float* dst[CTN_MAX_SEG];
+    int dst_stride[CTN_MAX_SEG]; /* 0 -> 1 */
+} ctn_reduce_args;
+
+/* dst[seg][i*dst_stride] (+)= sum_p part[p*part_stride + src_off[seg] + i*src_stride]; fixed order. */
+int ctn_reduce_partials(const ctn_reduce_args* args, void* stream);
+
+/* Backward of mask non-linearity, mask*w, basis Linear and overlap-add (conv_tasnet.py:137-142,
+ * 202-209; utils.py:9-46): d score as bf16 (hi, lo) [M*K, C*N], the decoder's direct gradient
+ * on the encoder output dw [M*K, N], and per-CTA partials of dV [M*tiles][L*N]. */
+int ctn_decoder_bwd_tiles(int K);
+int ctn_decoder_bwd(const float* grad_est, const float* score, const float* w, const float* V, int M, int K, int N,
+                    int L, int C, int T, int mask_nonlinear, void* dscore_hi, void* dscore_lo, float* dw,
+                    float* dV_part, void* stream);
+
+/* Backward of the leading cLN (conv_tasnet.py:167) + encoder ReLU, merged with dw from the decoder:
+ * dpre [M*K, N] and per-CTA partials [M*tiles][2*N] of (d gamma0, d beta0). */
+int ctn_cln_bwd_tiles(int K);
+int ctn_cln_bwd(const float* dn0, const float* w, const void* rowstat, const float* gamma0, const float* dw_dec,
+                int M, int K, int N, float* dpre, float* chan_part, void* stream);
+
+/* dU[n, l] = sum dpre[m,k,n] * mixture[m, k*hop + l] (conv_tasnet.py:106): per-CTA partials [M*tiles][N*L]. */
+int ctn_encoder_wgrad_tiles(int K);
+int ctn_encoder_wgrad(const float* dpre, const float* mixture, int M, int T, int N, int L, float* dU_part,
+                      void* stream);
 
 #ifdef __cplusplus
 }

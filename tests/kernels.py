@@ -84,7 +84,7 @@ def dwconv(M, K, a, a1, g1, b1, norm, in_stat, in_P, wd, a2, dilation, causal, w
     hi = torch.zeros(R, H, dtype=torch.bfloat16, device=dev)
     lo = torch.zeros_like(hi)
     if norm == nat.NORM_GLN:
-        st = torch.full((M, lib.ctn_dwconv_gln_partials(K), 2), float("nan"), device=dev)
+        st = torch.full((M, lib.ctn_dwconv_gln_partials(K, H, P, dilation), 2), float("nan"), device=dev)
     else:
         st = torch.full((R, 2), float("nan"), device=dev)
     d.out_pre, d.out_hi, d.out_lo, d.out_stat = nat.ptr(pre), hi.data_ptr(), lo.data_ptr(), st.data_ptr()

@@ -190,7 +190,7 @@ def test_dwconv(H, K, M, dil, causal, norm):
     assert rel_l2(hi.float() + lo.float(), qr) < 3e-5
     assert not torch.isnan(st).any()
     if norm == "gLN":
-        assert st.shape[1] == lib.ctn_dwconv_gln_partials(K)
+        assert st.shape[1] == lib.ctn_dwconv_gln_partials(K, H, P, dil)
         assert rel_l2(st[..., 0].double().sum(1), q_ref.sum(dim=(1, 2))) < 1e-4
         assert rel_l2(st[..., 1].double().sum(1), (q_ref ** 2).sum(dim=(1, 2))) < 1e-4
     else:

@@ -23,7 +23,9 @@ def test_library_exports_every_declared_symbol():
     assert lib.ctn_version() >= 100
     # pure-host geometry queries (no device work)
     assert lib.ctn_gemm_gln_partials(3199, 512) == 25 * 4 * 4
-    assert lib.ctn_dwconv_gln_partials(3199) == 200
+    assert lib.ctn_dwconv_gln_partials(3199, 512, 3, 1) == 50      # marching kernel: 4*1*100 warps / 8
+    assert lib.ctn_dwconv_gln_partials(3199, 512, 3, 128) == 64
+    assert lib.ctn_dwconv_gln_partials(3199, 510, 3, 1) == 200     # generic kernel: 16-frame tiles
     assert lib.ctn_gemm_cln_groups(512) == 4
     assert lib.ctn_pit_workspace_doubles(3, 2, 32000) == 3 * 8 * 14
 
