@@ -101,6 +101,15 @@ class ConvTasNet(nn.Module):
             self.__dict__["_engine"] = eng
         return eng
 
+    def train_engine(self):
+        """Kernel orchestrator of the training path (saved activations, backward call list)."""
+        eng = self.__dict__.get("_train_engine")
+        if eng is None:
+            from ctn_b200 import _autograd
+            eng = _autograd.TrainEngine(self._cfg())
+            self.__dict__["_train_engine"] = eng
+        return eng
+
     def forward(self, mixture):
         """
         Args:
@@ -123,6 +132,7 @@ class ConvTasNet(nn.Module):
     def __getstate__(self):
         state = self.__dict__.copy()
         state["_engine"] = None  # workspaces are per process / device
+        state.pop("_train_engine", None)
         return state
 
     @classmethod

@@ -1,0 +1,381 @@
+"""Training path: forward that keeps what backward needs + hand-written backward.
+
+The reference gets its backward from autograd over ~3000 aten ops per step
+(SURVEY.md 3.1); here ONE torch.autograd.Function wraps the whole separation
+network.  Its forward is the inference call sequence with per-block saved
+tensors (block input x as bf16 hi/lo, conv1x1 output a, depthwise output d and
+the gLN statistics); its backward is a fixed list of libctn_b200 kernels
+(csrc/backward.cu, wgrad.cu, gemm.cu) writing every parameter gradient into one
+flat fp32 buffer -- the buffer the data-parallel allreduce then reduces in one
+NCCL call (ctn_b200/_dist.py).
+"""
+import ctypes as C
+
+import torch
+
+from . import _native as nat
+from ._engine import _MASK, _NORM, _Prepared, _check_cfg
+from ._layout import block_keys, frame_geometry, param_spec
+
+
+class _PreparedBwd:
+    """Transposed bf16 (hi, lo) weight copies: operands of the data-gradient GEMMs."""
+
+    def __init__(self, cfg, device):
+        N, B, H, C_ = cfg["N"], cfg["B"], cfg["H"], cfg["C"]
+        bf = dict(dtype=torch.bfloat16, device=device)
+        self.bott_t = (torch.empty(N, B, **bf), torch.empty(N, B, **bf))
+        self.blocks = [dict(w1t=(torch.empty(B, H, **bf), torch.empty(B, H, **bf)),
+                            w2t=(torch.empty(H, B, **bf), torch.empty(H, B, **bf)))
+                       for _ in range(cfg["R"] * cfg["X"])]
+        self.mask_t = (torch.empty(B, C_ * N, **bf), torch.empty(B, C_ * N, **bf))
+
+    def refresh(self, cfg, params):
+        lib, s = nat.lib(), nat.stream()
+        N, B, H, C_ = cfg["N"], cfg["B"], cfg["H"], cfg["C"]
+
+        def prep_t(W, rows, cols, out):
+            nat.check(lib.ctn_weight_prep(W.data_ptr(), rows, cols, None, None, 1, out[0].data_ptr(),
+                                          out[1].data_ptr(), None, None, s))
+
+        prep_t(params["separator.network.1.weight"], B, N, self.bott_t)
+        i = 0
+        for r in range(cfg["R"]):
+            for x in range(cfg["X"]):
+                k = block_keys(r, x, cfg["causal"])
+                prep_t(params[k["w1"]], H, B, self.blocks[i]["w1t"])
+                prep_t(params[k["w2"]], B, H, self.blocks[i]["w2t"])
+                i += 1
+        prep_t(params["separator.network.3.weight"], C_ * N, B, self.mask_t)
+
+
+class TrainPlan:
+    """Workspaces and call lists of one (M, T) training step on one device."""
+
+    def __init__(self, cfg, M, T, device):
+        _check_cfg(cfg)
+        if cfg["norm_type"] != "gLN":
+            raise NotImplementedError("training (backward) is implemented for norm_type='gLN'; "
+                                      "cLN models run inference only")
+        self.cfg, self.M, self.T, self.device = cfg, M, T, device
+        N, L, B, H, C_ = cfg["N"], cfg["L"], cfg["B"], cfg["H"], cfg["C"]
+        self.hop, self.K, self.T_conv = frame_geometry(T, L)
+        K = self.K
+        Rr = M * K
+        self.NB = NB = cfg["R"] * cfg["X"]
+        lib = nat.lib()
+        f32 = dict(dtype=torch.float32, device=device)
+        bf = dict(dtype=torch.bfloat16, device=device)
+        z = torch.zeros
+        e = torch.empty
+        # forward
+        self.mix = e(M, T, **f32)
+        self.w = e(Rr, N, **f32)
+        self.w_hl = (e(Rr, N, **bf), e(Rr, N, **bf))
+        self.rowstat0 = e(Rr, 2, **f32)
+        self.x = e(Rr, B, **f32)
+        self.x_hl = [(e(Rr, B, **bf), e(Rr, B, **bf)) for _ in range(NB + 1)]   # input of block b / of the mask conv
+        self.a = [e(Rr, H, **f32) for _ in range(NB)]
+        self.d = [e(Rr, H, **f32) for _ in range(NB)]
+        self.q_hl = (e(Rr, H, **bf), e(Rr, H, **bf))
+        self.P1 = lib.ctn_gemm_gln_partials(K, H)
+        self.P2s = [lib.ctn_dwconv_gln_partials(K, H, cfg["P"], 2 ** x) for x in range(cfg["X"])]
+        self.stat1 = [z(M, self.P1, 2, **f32) for _ in range(NB)]
+        self.stat2 = [z(M, max(self.P2s), 2, **f32) for _ in range(NB)]
+        self.score = e(Rr, C_ * N, **f32)
+        # backward
+        self.ds_hl = (e(Rr, C_ * N, **bf), e(Rr, C_ * N, **bf))
+        self.dw_dec = e(Rr, N, **f32)
+        self.g = e(Rr, B, **f32)
+        self.g_hl = (e(Rr, B, **bf), e(Rr, B, **bf))
+        self.hl_H = (e(Rr, H, **bf), e(Rr, H, **bf))       # u (hi, lo), later da (hi, lo)
+        self.du = e(Rr, H, **f32)
+        self.dn1 = e(Rr, H, **f32)
+        self.bstat = z(M, self.P1, 2, **f32)
+        self.dn0 = e(Rr, N, **f32)
+        self.dpre = e(Rr, N, **f32)
+        tiles_b, rg = C.c_int(), C.c_int()
+        lib.ctn_bwd_dw_layout(K, H, C.byref(tiles_b), C.byref(rg))
+        self.tiles_b, self.rg = tiles_b.value, rg.value
+        self.chan_part = e(M * self.tiles_b * self.rg, (4 + cfg["P"]) * H, **f32)
+        self.scal_part = e(M * self.tiles_b, 4, **f32)
+        self.tiles_pn = lib.ctn_bwd_prelu_norm_tiles(K)
+        self.alpha_part = e(M * self.tiles_pn, **f32)
+        self.tiles_db = lib.ctn_decoder_bwd_tiles(K)
+        self.dV_part = e(M * self.tiles_db, L * N, **f32)
+        self.tiles_cb = lib.ctn_cln_bwd_tiles(K)
+        self.cb_part = e(M * self.tiles_cb, 2 * N, **f32)
+        self.tiles_ew = lib.ctn_encoder_wgrad_tiles(K)
+        self.dU_part = e(M * self.tiles_ew, N * L, **f32)
+        shapes = [(C_ * N, B), (B, H), (H, B), (B, N)]
+        self.wg_part = e(max(lib.ctn_wgrad_splits(Rr, i, j) * i * j for i, j in shapes), **f32)
+        # flat gradient buffer in state_dict order
+        self.spec = param_spec(N, L, B, H, cfg["P"], cfg["X"], cfg["R"], C_, cfg["causal"])
+        self.offsets, off = {}, 0
+        for key, (shape, _) in self.spec.items():
+            n = 1
+            for s_ in shape:
+                n *= s_
+            self.offsets[key] = (off, n, shape)
+            off += n
+        self.flat_grad = z(off, **f32)
+        self.fwd_calls = self.bwd_calls = None
+        self.param_ptrs = None
+        self._keep = []
+        self.generation = 0
+
+    # ------------------------------------------------------------------ helpers
+    def grad_ptr(self, key):
+        return self.flat_grad.data_ptr() + 4 * self.offsets[key][0]
+
+    def grad_views(self, flat):
+        return [flat[o:o + n].view(shape) for (o, n, shape) in self.offsets.values()]
+
+    def _gemm(self, **kw):
+        g = nat.GemmArgs()
+        g.M, g.K = self.M, self.K
+        for k, v in kw.items():
+            setattr(g, k, v.data_ptr() if isinstance(v, torch.Tensor) else v)
+        self._keep.append(g)
+        fn, ref = nat.lib().ctn_gemm1x1, C.byref(g)
+        return lambda s: fn(ref, s)
+
+    def _reduce(self, part, n_part, part_stride, segs, accumulate=0):
+        """segs: list of (src_off, len, src_stride, dst_ptr, dst_stride)"""
+        r = nat.ReduceArgs()
+        r.part, r.n_part, r.part_stride, r.nseg, r.accumulate = part.data_ptr(), n_part, part_stride, len(segs), accumulate
+        for i, (so, ln, ss, dp, ds) in enumerate(segs):
+            r.src_off[i], r.len[i], r.src_stride[i], r.dst[i], r.dst_stride[i] = so, ln, ss, dp, ds
+        self._keep.append(r)
+        fn, ref = nat.lib().ctn_reduce_partials, C.byref(r)
+        return lambda s: fn(ref, s)
+
+    def _wgrad(self, x_hl, y_hl, Ci, Cj, dst_key):
+        """G = x^T y over all rows -> grad of `dst_key` ([Ci, Cj] row-major)."""
+        lib = nat.lib()
+        Rr = self.M * self.K
+        S = lib.ctn_wgrad_splits(Rr, Ci, Cj)
+        a = (x_hl[0].data_ptr(), x_hl[1].data_ptr(), y_hl[0].data_ptr(), y_hl[1].data_ptr(), Rr, Ci, Cj,
+             self.wg_part.data_ptr(), 0)
+        fn = lib.ctn_wgrad
+        return [lambda s, a=a: fn(*a, s),
+                self._reduce(self.wg_part, S, Ci * Cj, [(0, Ci * Cj, 1, self.grad_ptr(dst_key), 1)])]
+
+    # ------------------------------------------------------------- call lists
+    def build(self, params, prep, prep_b):
+        cfg = self.cfg
+        N, L, B, H, C_, P = cfg["N"], cfg["L"], cfg["B"], cfg["H"], cfg["C"], cfg["P"]
+        M, K, T, NB = self.M, self.K, self.T, self.NB
+        lib = nat.lib()
+        self._keep = []
+        GLN = nat.NORM_GLN
+        causal = int(bool(cfg["causal"]))
+        U = params["encoder.conv1d_U.weight"]
+        V = params["decoder.basis_signals.weight"]
+        g0 = params["separator.network.0.gamma"]
+        b0 = params["separator.network.0.beta"]
+        count = float(K) * H
+
+        # ---------------- forward (keeps x_hl[b], a[b], d[b], stat1[b], stat2[b]) ----------------
+        fwd = []
+        enc = lib.ctn_encoder_fwd
+        ea = (self.mix.data_ptr(), U.data_ptr(), M, T, N, L, self.w.data_ptr(), self.w_hl[0].data_ptr(),
+              self.w_hl[1].data_ptr(), self.rowstat0.data_ptr())
+        fwd.append(lambda s, a=ea: enc(*a, s))
+        fwd.append(self._gemm(Cin=N, Cout=B, a_hi=self.w_hl[0], a_lo=self.w_hl[1], w_hi=prep.bott[0],
+                              w_lo=prep.bott[1], col_g=prep.bott[2], col_bias=prep.bott[3], in_norm=nat.NORM_CLN,
+                              in_stat=self.rowstat0, out_f32=self.x, out_hi=self.x_hl[0][0], out_lo=self.x_hl[0][1]))
+        dw = lib.ctn_dwconv_fwd
+        blocks = []
+        i = 0
+        for r in range(cfg["R"]):
+            for xb in range(cfg["X"]):
+                k = block_keys(r, xb, cfg["causal"])
+                blocks.append((i, xb, k))
+                pb = prep.blocks[i]
+                fwd.append(self._gemm(Cin=B, Cout=H, a_hi=self.x_hl[i][0], a_lo=self.x_hl[i][1], w_hi=pb["w1"][0],
+                                      w_lo=pb["w1"][1], out_f32=self.a[i], out_stat=GLN,
+                                      out_stat_buf=self.stat1[i], stat_prelu=params[k["a1"]]))
+                d = nat.DwconvArgs()
+                d.M, d.K, d.H, d.P, d.dilation, d.causal = M, K, H, P, 2 ** xb, causal
+                d.inp, d.prelu_in = self.a[i].data_ptr(), params[k["a1"]].data_ptr()
+                d.gamma_in, d.beta_in = params[k["g1"]].data_ptr(), params[k["b1"]].data_ptr()
+                d.norm, d.in_stat, d.in_P = GLN, self.stat1[i].data_ptr(), self.P1
+                d.wd, d.prelu_out = params[k["wd"]].data_ptr(), params[k["a2"]].data_ptr()
+                d.out_pre = self.d[i].data_ptr()
+                d.out_hi, d.out_lo = self.q_hl[0].data_ptr(), self.q_hl[1].data_ptr()
+                d.out_stat = self.stat2[i].data_ptr()
+                self._keep.append(d)
+                fwd.append(lambda s, ref=C.byref(d): dw(ref, s))
+                fwd.append(self._gemm(Cin=H, Cout=B, a_hi=self.q_hl[0], a_lo=self.q_hl[1], w_hi=pb["w2"][0],
+                                      w_lo=pb["w2"][1], col_g=pb["w2"][2], col_bias=pb["w2"][3], in_norm=GLN,
+                                      in_stat=self.stat2[i], in_P=self.P2s[xb], in_count=count, resid=self.x,
+                                      out_f32=self.x, out_hi=self.x_hl[i + 1][0], out_lo=self.x_hl[i + 1][1]))
+                i += 1
+        fwd.append(self._gemm(Cin=B, Cout=C_ * N, a_hi=self.x_hl[NB][0], a_lo=self.x_hl[NB][1], w_hi=prep.mask[0],
+                              w_lo=prep.mask[1], out_f32=self.score))
+        self.fwd_calls = fwd
+        self.dec_args = (self.score.data_ptr(), self.w.data_ptr(), V.data_ptr(), M, K, N, L, C_, T,
+                         _MASK[cfg["mask_nonlinear"]])
+
+        # ---------------- backward ----------------
+        bwd = []
+        self.dec_bwd_args = (self.score.data_ptr(), self.w.data_ptr(), V.data_ptr(), M, K, N, L, C_, T,
+                             _MASK[cfg["mask_nonlinear"]], self.ds_hl[0].data_ptr(), self.ds_hl[1].data_ptr(),
+                             self.dw_dec.data_ptr(), self.dV_part.data_ptr())
+        bwd.append(self._reduce(self.dV_part, M * self.tiles_db, L * N,
+                                [(0, L * N, 1, self.grad_ptr("decoder.basis_signals.weight"), 1)]))
+        bwd += self._wgrad(self.ds_hl, self.x_hl[NB], C_ * N, B, "separator.network.3.weight")
+        bwd.append(self._gemm(Cin=C_ * N, Cout=B, a_hi=self.ds_hl[0], a_lo=self.ds_hl[1], w_hi=prep_b.mask_t[0],
+                              w_lo=prep_b.mask_t[1], out_f32=self.g, out_hi=self.g_hl[0], out_lo=self.g_hl[1]))
+        ns, bd, pn = lib.ctn_norm_split, lib.ctn_bwd_dwconv, lib.ctn_bwd_prelu_norm
+        for (i, xb, k) in reversed(blocks):
+            pb = prep_b.blocks[i]
+            P2 = self.P2s[xb]
+            a_ = (self.d[i].data_ptr(), params[k["a2"]].data_ptr(), params[k["g2"]].data_ptr(),
+                  params[k["b2"]].data_ptr(), GLN, self.stat2[i].data_ptr(), P2, M, K, H,
+                  self.hl_H[0].data_ptr(), self.hl_H[1].data_ptr())
+            bwd.append(lambda s, a=a_: ns(*a, s))                                       # u (hi, lo)
+            bwd += self._wgrad(self.g_hl, self.hl_H, B, H, k["w2"])                      # dW2 = g^T u
+            bwd.append(self._gemm(Cin=B, Cout=H, a_hi=self.g_hl[0], a_lo=self.g_hl[1], w_hi=pb["w2t"][0],
+                                  w_lo=pb["w2t"][1], out_f32=self.du, out_stat=GLN, out_stat_buf=self.bstat,
+                                  bw_pre=self.d[i], bw_gamma=params[k["g2"]], bw_slope=params[k["a2"]],
+                                  bw_stat=self.stat2[i], bw_P=P2))                        # du = g W2 (+ S1, S2)
+            b = nat.BwdDwArgs()
+            b.M, b.K, b.H, b.P, b.dilation, b.causal = M, K, H, P, 2 ** xb, causal
+            b.P1, b.P2, b.Pb = self.P1, P2, self.P1
+            b.du, b.d, b.a = self.du.data_ptr(), self.d[i].data_ptr(), self.a[i].data_ptr()
+            b.stat1, b.stat2, b.bstat = self.stat1[i].data_ptr(), self.stat2[i].data_ptr(), self.bstat.data_ptr()
+            b.g1, b.b1, b.g2 = params[k["g1"]].data_ptr(), params[k["b1"]].data_ptr(), params[k["g2"]].data_ptr()
+            b.wd, b.slope1, b.slope2 = params[k["wd"]].data_ptr(), params[k["a1"]].data_ptr(), params[k["a2"]].data_ptr()
+            b.dn1, b.chan_part, b.scal_part = self.dn1.data_ptr(), self.chan_part.data_ptr(), self.scal_part.data_ptr()
+            self._keep.append(b)
+            bwd.append(lambda s, ref=C.byref(b): bd(ref, s))
+            a_ = (self.dn1.data_ptr(), self.a[i].data_ptr(), self.stat1[i].data_ptr(), self.P1,
+                  self.scal_part.data_ptr(), self.tiles_b, params[k["g1"]].data_ptr(), params[k["a1"]].data_ptr(),
+                  M, K, H, self.hl_H[0].data_ptr(), self.hl_H[1].data_ptr(), self.alpha_part.data_ptr())
+            bwd.append(lambda s, a=a_: pn(*a, s))                                       # da (hi, lo)
+            segs = [(0, H, 1, self.grad_ptr(k["g2"]), 1), (H, H, 1, self.grad_ptr(k["b2"]), 1),
+                    (2 * H, H, 1, self.grad_ptr(k["g1"]), 1), (3 * H, H, 1, self.grad_ptr(k["b1"]), 1)]
+            segs += [((4 + j) * H, H, 1, self.grad_ptr(k["wd"]) + 4 * j, P) for j in range(P)]
+            bwd.append(self._reduce(self.chan_part, M * self.tiles_b * self.rg, (4 + P) * H, segs))
+            bwd.append(self._reduce(self.scal_part, M * self.tiles_b, 4, [(2, 1, 1, self.grad_ptr(k["a2"]), 1)]))
+            bwd.append(self._reduce(self.alpha_part, M * self.tiles_pn, 1, [(0, 1, 1, self.grad_ptr(k["a1"]), 1)]))
+            bwd += self._wgrad(self.hl_H, self.x_hl[i], H, B, k["w1"])                   # dW1 = da^T x
+            bwd.append(self._gemm(Cin=H, Cout=B, a_hi=self.hl_H[0], a_lo=self.hl_H[1], w_hi=pb["w1t"][0],
+                                  w_lo=pb["w1t"][1], resid=self.g, out_f32=self.g, out_hi=self.g_hl[0],
+                                  out_lo=self.g_hl[1]))                                   # g = da W1 + g
+        # bottleneck + leading cLN + encoder
+        a_ = (self.w.data_ptr(), None, g0.data_ptr(), b0.data_ptr(), nat.NORM_CLN, self.rowstat0.data_ptr(), 1,
+              M, K, N, self.w_hl[0].data_ptr(), self.w_hl[1].data_ptr())
+        bwd.append(lambda s, a=a_: ns(*a, s))                                           # n0 (hi, lo) over w_hl
+        bwd += self._wgrad(self.g_hl, self.w_hl, B, N, "separator.network.1.weight")
+        bwd.append(self._gemm(Cin=B, Cout=N, a_hi=self.g_hl[0], a_lo=self.g_hl[1], w_hi=prep_b.bott_t[0],
+                              w_lo=prep_b.bott_t[1], out_f32=self.dn0))
+        cb = lib.ctn_cln_bwd
+        a_ = (self.dn0.data_ptr(), self.w.data_ptr(), self.rowstat0.data_ptr(), g0.data_ptr(),
+              self.dw_dec.data_ptr(), M, K, N, self.dpre.data_ptr(), self.cb_part.data_ptr())
+        bwd.append(lambda s, a=a_: cb(*a, s))
+        bwd.append(self._reduce(self.cb_part, M * self.tiles_cb, 2 * N,
+                                [(0, N, 1, self.grad_ptr("separator.network.0.gamma"), 1),
+                                 (N, N, 1, self.grad_ptr("separator.network.0.beta"), 1)]))
+        ew = lib.ctn_encoder_wgrad
+        a_ = (self.dpre.data_ptr(), self.mix.data_ptr(), M, T, N, L, self.dU_part.data_ptr())
+        bwd.append(lambda s, a=a_: ew(*a, s))
+        bwd.append(self._reduce(self.dU_part, M * self.tiles_ew, N * L,
+                                [(0, N * L, 1, self.grad_ptr("encoder.conv1d_U.weight"), 1)]))
+        self.bwd_calls = bwd
+        self.param_ptrs = tuple(p.data_ptr() for p in params.values())
+
+    def run_forward(self, est):
+        s, check, lib = nat.stream(), nat.check, nat.lib()
+        for c in self.fwd_calls:
+            check(c(s))
+        check(lib.ctn_decoder_fwd(*self.dec_args, est.data_ptr(), s))
+        return len(self.fwd_calls) + 1
+
+    def run_backward(self, g_est):
+        s, check, lib = nat.stream(), nat.check, nat.lib()
+        check(lib.ctn_decoder_bwd(g_est.data_ptr(), *self.dec_bwd_args, s))
+        for c in self.bwd_calls:
+            check(c(s))
+        return len(self.bwd_calls) + 1
+
+
+class TrainEngine:
+    """Per-model cache of training plans and prepared weights."""
+
+    def __init__(self, cfg):
+        self.cfg = dict(cfg)
+        self.plans, self.prep, self.prep_b = {}, {}, {}
+        self.launches = 0
+        # data parallelism: when set, every backward all-reduces (sum) the flat gradient over this
+        # torch.distributed group and divides by its size (ranks hold equal utterance shards and
+        # local mean losses, so this equals the gradient of the global mean loss)
+        self.process_group = None
+        self.last_flat_grad = None
+
+    def plan(self, params, M, T, device):
+        di = device.index
+        if di not in self.prep:
+            self.prep[di] = _Prepared(self.cfg, device)
+            self.prep_b[di] = _PreparedBwd(self.cfg, device)
+        old = self.prep[di].fingerprint
+        self.prep[di].refresh(self.cfg, params)
+        if old != self.prep[di].fingerprint:
+            self.prep_b[di].refresh(self.cfg, params)
+        key = (di, M, T)
+        plan = self.plans.get(key)
+        if plan is None:
+            plan = self.plans[key] = TrainPlan(self.cfg, M, T, device)
+        ptrs = tuple(p.data_ptr() for p in params.values())
+        if plan.fwd_calls is None or plan.param_ptrs != ptrs:
+            plan.build(params, self.prep[di], self.prep_b[di])
+        return plan
+
+
+class _Separate(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, model, mixture, *param_list):
+        keys = model._keys
+        params = {k: p.detach() for k, p in zip(keys, param_list)}
+        M, T = mixture.shape
+        dev = mixture.device
+        eng = model.train_engine()
+        with torch.cuda.device(dev):
+            plan = eng.plan(params, M, T, dev)
+            plan.mix.copy_(mixture)
+            est = torch.empty(M, model.C, T, dtype=torch.float32, device=dev)
+            eng.launches += plan.run_forward(est)
+        plan.generation += 1
+        ctx.plan, ctx.generation, ctx.engine = plan, plan.generation, eng
+        ctx.n_params = len(param_list)
+        return est
+
+    @staticmethod
+    def backward(ctx, g_est):
+        plan = ctx.plan
+        if plan.generation != ctx.generation:
+            raise RuntimeError("ConvTasNet.forward was called again with the same (batch, length) before "
+                               "backward: the saved activations of this graph were overwritten")
+        eng = ctx.engine
+        with torch.cuda.device(plan.device):
+            eng.launches += plan.run_backward(g_est.contiguous())
+            # one private copy per backward: autograd may adopt the returned views as .grad
+            flat = plan.flat_grad.clone()
+            if eng.process_group is not None:
+                import torch.distributed as dist
+                dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=eng.process_group)
+                flat.mul_(1.0 / dist.get_world_size(eng.process_group))
+        eng.last_flat_grad = flat
+        return (None, None) + tuple(plan.grad_views(flat))
+
+
+def separate(model, mixture, params):
+    if mixture.requires_grad:
+        raise NotImplementedError("gradient with respect to the mixture is not implemented")
+    if mixture.dim() != 2 or mixture.dtype != torch.float32:
+        raise RuntimeError("mixture must be float32 [M, T]")
+    if mixture.shape[1] < model.L:
+        raise RuntimeError("Calculated output size is too small: T=%d < L=%d" % (mixture.shape[1], model.L))
+    return _Separate.apply(model, mixture, *params.values())
