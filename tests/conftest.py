@@ -42,4 +42,4 @@ def rel_l2(a, b):
     return float(((a - b).norm() / b.norm().clamp_min(1e-30)).detach())
 
 
-MODEL_CASES = ["demo_gln", "causal_cln", "softmax_c3", "tc_small", "tc_causal_cln"]
+MODEL_CASES = ["demo_gln", "causal_cln", "softmax_c3", "tc_small", "tc_causal_cln", "odd_gln"]
