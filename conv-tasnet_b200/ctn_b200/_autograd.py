@@ -309,10 +309,11 @@ class TrainEngine:
         self.cfg = dict(cfg)
         self.plans, self.prep, self.prep_b = {}, {}, {}
         self.launches = 0
-        # data parallelism: when set, every backward all-reduces (sum) the flat gradient over this
-        # torch.distributed group and divides by its size (ranks hold equal utterance shards and
-        # local mean losses, so this equals the gradient of the global mean loss)
+        # data parallelism (ctn_b200/_dist.py): when set, every backward scales the flat gradient by
+        # n_local / n_global and all-reduces (sum) it over this torch.distributed group, which equals
+        # the gradient of the reference's global-mean loss
         self.process_group = None
+        self.global_batch = None       # utterances per step over all ranks (None = equal shards)
         self.last_flat_grad = None
 
     def plan(self, params, M, T, device):
@@ -364,9 +365,8 @@ class _Separate(torch.autograd.Function):
             # one private copy per backward: autograd may adopt the returned views as .grad
             flat = plan.flat_grad.clone()
             if eng.process_group is not None:
-                import torch.distributed as dist
-                dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=eng.process_group)
-                flat.mul_(1.0 / dist.get_world_size(eng.process_group))
+                from . import _dist
+                _dist.reduce_flat_grad(flat, plan.M, eng.global_batch, eng.process_group)
         eng.last_flat_grad = flat
         return (None, None) + tuple(plan.grad_views(flat))
 
