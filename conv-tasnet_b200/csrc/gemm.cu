@@ -16,11 +16,14 @@
 // ctn_weight_prep), the residual add, the (hi, lo) split of the output and the
 // (sum, sumsq) statistics of the next gLN / cLN (after an optional PReLU).
 #include <cuda.h>
+#include <stdlib.h>
 
 #include "common.cuh"
 #include "ptx.cuh"
 
 namespace ctn {
+
+__device__ __forceinline__ uint32_t r2u(float f) { return __float_as_uint(f); }
 
 struct EpiParams {
     int K, Cout, groups, tiles_per_utt;
@@ -44,6 +47,7 @@ struct EpiParams {
     const float* bw_slope;
     const float2* bw_stat;
     int bw_P;
+    int dbg;   // CTN_GEMM_DBG experiment bits (0 in production): 1 skip epilogue, 2 skip stores, 4 skip MMAs
 };
 
 // One thread owns output row `grow` (valid or not) and 32 consecutive columns
@@ -188,31 +192,46 @@ __device__ __forceinline__ void epilogue_flush_stats(const EpiParams& ep, int m,
 // ======================================================================
 constexpr int kBM = CTN_ROW_TILE;  // 128 rows = TMEM lanes
 constexpr int kBK = 64;            // bf16 elements per k-block = one 128B swizzle atom
-constexpr int kTcThreads = 192;
+// threads = TMA warp + MMA warp + epilogue warps (4 per 128 accumulator columns: a lone warp per
+// scheduler cannot hide its own instruction latencies, which made the epilogue the bottleneck)
 
-template <int BN>
+// PAIR: two CTAs of a cluster (cta_group::2) share one 256-column weight tile -- each loads half
+// of it -- and each owns a 128-row tile of its own, so the weight bytes crossing L2 -> SM halve.
+template <int BN, bool PAIR>
 struct TcCfg {
-    static constexpr int kStages = (BN == 256) ? 2 : 3;
+    static constexpr int kWRows = PAIR ? BN / 2 : BN;   // weight rows this CTA loads per k-block
+    static constexpr int kEpiWarps = 4 * (BN / 128);    // warp w: TMEM lane quarter w & 3, column group w >> 2
+    static constexpr int kThreads = 64 + 32 * kEpiWarps;
+    static constexpr int kStages = 3;
     static constexpr int kABytes = kBM * kBK * 2;  // one of hi / lo
-    static constexpr int kWBytes = BN * kBK * 2;
+    static constexpr int kWBytes = kWRows * kBK * 2;
     static constexpr int kStageBytes = 2 * kABytes + 2 * kWBytes;
-    // epilogue staging per warp: fp32 block 32 x 128 B, then the hi and lo blocks 32 x 64 B each
-    static constexpr int kStgWarpBytes = 8192;
-    static constexpr int kStgBytes = 4 * kStgWarpBytes;
+    // no epilogue staging: outputs go straight from registers to global memory
+    static constexpr int kStgWarpBytes = 0;
+    static constexpr int kStgBytes = kEpiWarps * kStgWarpBytes;
     static constexpr int kColBytes = 2 * BN * 4;   // col_g, col_bias of the current column tile
     static constexpr int kBarBytes = 256;
     static constexpr int kSmemBytes = kStages * kStageBytes + kStgBytes + kColBytes + kBarBytes;
     static constexpr int kTmemCols = 2 * BN;
 };
 
-template <int BN>
-__global__ void __launch_bounds__(kTcThreads, 1)
+constexpr int kEpiPlain = 0;    // optional PReLU statistics of the output
+constexpr int kEpiAffine = 1;   // folded input norm (scale / shift / bias) + optional residual
+constexpr int kEpiBw = 2;       // gLN backward sums against a saved pre-activation
+
+template <int BN, bool PAIR, int EPI>
+__global__ void __launch_bounds__((TcCfg<BN, PAIR>::kThreads), 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tm_a_hi, const __grid_constant__ CUtensorMap tm_a_lo,
                const __grid_constant__ CUtensorMap tm_w_hi, const __grid_constant__ CUtensorMap tm_w_lo,
                const __grid_constant__ CUtensorMap tm_o_f32, const __grid_constant__ CUtensorMap tm_o_hi,
                const __grid_constant__ CUtensorMap tm_o_lo, const EpiParams ep, int Cin, int n_tiles,
-               int total_tiles) {
-    using Cfg = TcCfg<BN>;
+               int total_tiles, int row_tiles) {
+    // Work items: `total_tiles` = (row tile or row-tile PAIR) x column tile, strided over the CTAs
+    // (or CTA pairs).  In PAIR mode CTA `rank` of the pair owns row tile 2*item_row + rank.
+    using Cfg = TcCfg<BN, PAIR>;
+    const uint32_t rank = PAIR ? ptx::cluster_ctarank() : 0u;
+    const int worker = PAIR ? static_cast<int>(blockIdx.x >> 1) : static_cast<int>(blockIdx.x);
+    const int n_workers = PAIR ? static_cast<int>(gridDim.x >> 1) : static_cast<int>(gridDim.x);
     extern __shared__ __align__(1024) uint8_t smem[];
     if ((ptx::smem_u32(smem) & 1023u) != 0) __trap();  // 128B-swizzled tiles need 1024 B alignment
     uint8_t* stg = smem + Cfg::kStages * Cfg::kStageBytes;
@@ -238,15 +257,20 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tm_a_hi, const __grid_constan
         }
         for (int i = 0; i < 2; ++i) {
             ptx::mbar_init(tfull_bar + i, 1);
-            ptx::mbar_init(tempty_bar + i, 128);
+            ptx::mbar_init(tempty_bar + i, (PAIR ? 2 : 1) * Cfg::kEpiWarps);   // one arrival per epilogue warp (of both CTAs)
         }
         ptx::fence_mbar_init();
     } else if (warp == 1) {
-        ptx::tmem_alloc(tmem_slot, Cfg::kTmemCols);
-        ptx::tmem_relinquish();
+        if (PAIR) {
+            ptx::tmem_alloc_pair(tmem_slot, Cfg::kTmemCols);
+            ptx::tmem_relinquish_pair();
+        } else {
+            ptx::tmem_alloc(tmem_slot, Cfg::kTmemCols);
+            ptx::tmem_relinquish();
+        }
     }
     ptx::tc_fence_before();
-    __syncthreads();
+    if (PAIR) ptx::cluster_sync(); else __syncthreads();
     ptx::tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
 
@@ -255,32 +279,43 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tm_a_hi, const __grid_constan
         if (lane == 0) {
             int stage = 0;
             uint32_t phase = 0;
-            for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+            for (int tile = worker; tile < total_tiles; tile += n_workers) {
                 const int tn = tile % n_tiles;
-                const int rt = tile / n_tiles;
+                const int rt = PAIR ? 2 * (tile / n_tiles) + static_cast<int>(rank) : tile / n_tiles;
                 const int m = rt / ep.tiles_per_utt, tk = rt % ep.tiles_per_utt;
-                const int row0 = m * ep.K + tk * kBM;
-                const int n0 = tn * BN;
+                // a pair's odd leftover row tile does not exist: load rows past the end (zero fill)
+                const int row0 = rt < row_tiles ? m * ep.K + tk * kBM : 0x7fffff00;
+                const int n0 = tn * BN + static_cast<int>(rank) * Cfg::kWRows;
                 for (int kb = 0; kb < nkb; ++kb) {
                     ptx::mbar_wait(empty_bar + stage, phase ^ 1);
                     uint8_t* st = smem + stage * Cfg::kStageBytes;
-                    ptx::mbar_expect_tx(full_bar + stage, Cfg::kStageBytes);
-                    ptx::tma_load_2d(st, &tm_a_hi, full_bar + stage, kb * kBK, row0);
-                    ptx::tma_load_2d(st + Cfg::kABytes, &tm_a_lo, full_bar + stage, kb * kBK, row0);
-                    ptx::tma_load_2d(st + 2 * Cfg::kABytes, &tm_w_hi, full_bar + stage, kb * kBK, n0);
-                    ptx::tma_load_2d(st + 2 * Cfg::kABytes + Cfg::kWBytes, &tm_w_lo, full_bar + stage, kb * kBK, n0);
+                    if (PAIR) {
+                        // both CTAs' bytes complete on the leader's barrier, which the MMA issuer waits on
+                        const uint32_t fb = ptx::mapa(ptx::smem_u32(full_bar + stage), 0);
+                        if (rank == 0) ptx::mbar_expect_tx(full_bar + stage, 2 * Cfg::kStageBytes);
+                        ptx::tma_load_2d_pair(st, &tm_a_hi, fb, kb * kBK, row0);
+                        ptx::tma_load_2d_pair(st + Cfg::kABytes, &tm_a_lo, fb, kb * kBK, row0);
+                        ptx::tma_load_2d_pair(st + 2 * Cfg::kABytes, &tm_w_hi, fb, kb * kBK, n0);
+                        ptx::tma_load_2d_pair(st + 2 * Cfg::kABytes + Cfg::kWBytes, &tm_w_lo, fb, kb * kBK, n0);
+                    } else {
+                        ptx::mbar_expect_tx(full_bar + stage, Cfg::kStageBytes);
+                        ptx::tma_load_2d(st, &tm_a_hi, full_bar + stage, kb * kBK, row0);
+                        ptx::tma_load_2d(st + Cfg::kABytes, &tm_a_lo, full_bar + stage, kb * kBK, row0);
+                        ptx::tma_load_2d(st + 2 * Cfg::kABytes, &tm_w_hi, full_bar + stage, kb * kBK, n0);
+                        ptx::tma_load_2d(st + 2 * Cfg::kABytes + Cfg::kWBytes, &tm_w_lo, full_bar + stage, kb * kBK, n0);
+                    }
                     if (++stage == Cfg::kStages) stage = 0, phase ^= 1;
                 }
             }
         }
     } else if (warp == 1) {
         // -------------------------------------------------- MMA issuer
-        if (lane == 0) {
-            constexpr uint32_t idesc = ptx::make_idesc_bf16(kBM, BN, 0, 0);
+        if (lane == 0 && rank == 0) {
+            constexpr uint32_t idesc = ptx::make_idesc_bf16(PAIR ? 2 * kBM : kBM, BN, 0, 0);
             int stage = 0;
             uint32_t phase = 0;
             int it = 0;
-            for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it) {
+            for (int tile = worker; tile < total_tiles; tile += n_workers, ++it) {
                 const int as = it & 1;
                 const uint32_t aphase = (it >> 1) & 1;
                 ptx::mbar_wait(tempty_bar + as, aphase ^ 1);
@@ -297,185 +332,200 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tm_a_hi, const __grid_constan
                     const uint64_t w_lo =
                         ptx::make_smem_desc(sa + 2 * Cfg::kABytes + Cfg::kWBytes, 0, 1024, ptx::kLayoutSwizzle128B);
 #pragma unroll
-                    for (int k = 0; k < kBK / 16; ++k) {
+                    for (int k = 0; k < ((ep.dbg & 4) ? 0 : kBK / 16); ++k) {
                         const uint64_t adv = static_cast<uint64_t>((k * 16 * 2) >> 4);  // +32 B per k-step
-                        ptx::umma_bf16(d_tmem, a_hi + adv, w_hi + adv, idesc, (kb | k) != 0);
-                        ptx::umma_bf16(d_tmem, a_lo + adv, w_hi + adv, idesc, 1);
-                        ptx::umma_bf16(d_tmem, a_hi + adv, w_lo + adv, idesc, 1);
+                        if (PAIR) {
+                            ptx::umma_bf16_pair(d_tmem, a_hi + adv, w_hi + adv, idesc, (kb | k) != 0);
+                            ptx::umma_bf16_pair(d_tmem, a_lo + adv, w_hi + adv, idesc, 1);
+                            ptx::umma_bf16_pair(d_tmem, a_hi + adv, w_lo + adv, idesc, 1);
+                        } else {
+                            ptx::umma_bf16(d_tmem, a_hi + adv, w_hi + adv, idesc, (kb | k) != 0);
+                            ptx::umma_bf16(d_tmem, a_lo + adv, w_hi + adv, idesc, 1);
+                            ptx::umma_bf16(d_tmem, a_hi + adv, w_lo + adv, idesc, 1);
+                        }
                     }
-                    ptx::umma_commit(empty_bar + stage);  // frees the smem stage when these MMAs retire
-                    if (kb == nkb - 1) ptx::umma_commit(tfull_bar + as);
+                    if (PAIR) {
+                        ptx::umma_commit_pair(empty_bar + stage, 3);  // frees the stage in BOTH CTAs
+                        if (kb == nkb - 1) ptx::umma_commit_pair(tfull_bar + as, 3);
+                    } else {
+                        ptx::umma_commit(empty_bar + stage);  // frees the smem stage when these MMAs retire
+                        if (kb == nkb - 1) ptx::umma_commit(tfull_bar + as);
+                    }
                     if (++stage == Cfg::kStages) stage = 0, phase ^= 1;
                 }
             }
         }
     } else {
         // ---------------------------------------------------- epilogue
-        // TMEM -> registers -> fused math -> swizzled smem staging -> TMA store.  Each warp
-        // owns 32 rows and its own 8 KB staging area, so no cross-warp barrier is needed for
-        // the stores; the residual of the next chunk is prefetched under the current one.
-        const int ew = warp & 3;  // TMEM lane quarter this warp may read
-        const int et = threadIdx.x - 64;  // 0..127 among the epilogue threads
-        float slope = 0.f;
+        // TMEM -> registers -> fused math -> swizzled smem staging -> TMA store.  A warp owns 32
+        // rows x 128 columns (4 chunks of 32, fully unrolled) and its own 8 KB staging area, so the
+        // stores need no cross-warp barrier.  EPI selects the fused math at compile time: a lone
+        // generic epilogue spent 3/4 of its issue slots on predicates and register shuffles and,
+        // not the MMAs, set the kernel's duration.
+        const int ew = warp & 3;          // TMEM lane quarter this warp may read
+        const int wq = warp - 2;          // 0 .. kEpiWarps-1: staging area
+        const int cgrp = wq >> 2;         // 128-column group of the tile this warp drains
+        const int et = threadIdx.x - 64;  // index among the epilogue threads
+        constexpr int kEpiThreads = 32 * Cfg::kEpiWarps;
+        constexpr bool kAffine = EPI == kEpiAffine;
+        constexpr bool kBw = EPI == kEpiBw;
         const bool use_slope = ep.stat_prelu != nullptr;
-        if (use_slope) slope = __ldg(ep.stat_prelu);
-        const bool bw = ep.bw_pre != nullptr;
-        const bool affine = !bw && (ep.col_g != nullptr || ep.col_bias != nullptr || ep.in_norm != CTN_NORM_NONE);
-        const float bw_slope = bw ? __ldg(ep.bw_slope) : 0.f;
-        const float* aux = bw ? ep.bw_pre : ep.resid;  // per-element side input, prefetched one chunk ahead
-        const uint32_t stg_f32 = ptx::smem_u32(stg + ew * Cfg::kStgWarpBytes);
-        const uint32_t stg_hi = stg_f32 + 4096, stg_lo = stg_f32 + 6144;
-        const uint32_t sw128 = static_cast<uint32_t>(lane & 7);
-        const uint32_t sw64 = static_cast<uint32_t>((lane >> 1) & 3);
+        const float slope = use_slope ? __ldg(ep.stat_prelu) : 1.f;   // PReLU with slope 1 = identity
+        const float bw_slope = kBw ? __ldg(ep.bw_slope) : 0.f;
+        const float* aux = kBw ? ep.bw_pre : (kAffine ? ep.resid : nullptr);  // per-element side input
+        const bool want_stat = ep.out_stat != CTN_NORM_NONE;
         int it = 0, cur_tn = -1;
-        for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it) {
+        const uint32_t tempty_remote = PAIR ? ptx::mapa(ptx::smem_u32(tempty_bar), 0) : 0u;
+        for (int tile = worker; tile < total_tiles; tile += n_workers, ++it) {
             const int as = it & 1;
             const uint32_t aphase = (it >> 1) & 1;
             const int tn = tile % n_tiles;
-            const int rt = tile / n_tiles;
-            const int m = rt / ep.tiles_per_utt, tk = rt % ep.tiles_per_utt;
+            const int rt = PAIR ? 2 * (tile / n_tiles) + static_cast<int>(rank) : tile / n_tiles;
+            const bool tile_ok = rt < row_tiles;   // false only for the leftover half of an odd pair
+            const int m = tile_ok ? rt / ep.tiles_per_utt : 0, tk = tile_ok ? rt % ep.tiles_per_utt : 0;
             const int k = tk * kBM + ew * 32 + lane;
-            const bool valid = k < ep.K;
+            const bool valid = tile_ok && k < ep.K;
             const long long grow = static_cast<long long>(m) * ep.K + k;
-            float s, t, bw_mean, bw_rstd;
-            epilogue_row_affine(ep, m, grow, valid, s, t);
-            epilogue_bw_stats(ep, m, bw_mean, bw_rstd);
-            if ((affine || bw) && tn != cur_tn) {  // per-column constants of this column tile -> smem
-                ptx::named_bar_sync(1, 128);
-                for (int i = et; i < BN; i += 128) {
+            float s = 1.f, t = 0.f, bw_mean = 0.f, bw_rstd = 1.f;
+            if (kAffine) epilogue_row_affine(ep, m, grow, valid, s, t);
+            if (kBw) epilogue_bw_stats(ep, m, bw_mean, bw_rstd);
+            if ((kAffine || kBw) && tn != cur_tn) {  // per-column constants of this column tile -> smem
+                ptx::named_bar_sync(1, kEpiThreads);
+                for (int i = et; i < BN; i += kEpiThreads) {
                     const int n = tn * BN + i;
-                    const float* cg = bw ? ep.bw_gamma : ep.col_g;
+                    const float* cg = kBw ? ep.bw_gamma : ep.col_g;
                     col_s[i] = (cg && n < ep.Cout) ? __ldg(cg + n) : 0.f;
                     col_s[BN + i] = (ep.col_bias && n < ep.Cout) ? __ldg(ep.col_bias + n) : 0.f;
                 }
-                ptx::named_bar_sync(1, 128);
+                ptx::named_bar_sync(1, kEpiThreads);
                 cur_tn = tn;
             }
-            const int ncol_tile = min(BN, ep.Cout - tn * BN);  // multiple of 8
-            float4 rn[8];                                       // residual prefetch, one chunk ahead
-            auto load_resid = [&](int c) {
-                if (aux != nullptr && valid && c * 32 < ncol_tile) {
-                    const float4* rp = reinterpret_cast<const float4*>(aux + grow * ep.Cout + tn * BN + c * 32);
-                    const int nv = min(32, ncol_tile - c * 32) >> 2;
+            const int col0 = tn * BN + cgrp * 128;           // first column of this warp's group
+            const bool grp_ok = col0 < ep.Cout;              // Cout % 32 == 0: chunks are whole or absent
+            const int krow0 = tk * kBM + ew * 32;            // first frame of this warp's 32 rows
+            const bool store_ok = tile_ok && krow0 < ep.K && !(ep.dbg & 2);  // rows past K: clipped by the map
+            float ra[4][8], rb[4][8];                        // side input of even / odd chunks
+            auto load_aux = [&](float (&dst)[4][8], int ci) {
+                if (aux != nullptr && valid && col0 + ci * 32 < ep.Cout) {
+                    const float* rp = aux + grow * ep.Cout + col0 + ci * 32;
 #pragma unroll
-                    for (int j = 0; j < 8; ++j)
-                        if (j < nv) rn[j] = rp[j];
+                    for (int j = 0; j < 4; ++j) ptx::ld_global_v8(rp + 8 * j, dst[j]);
                 }
             };
-            load_resid(0);
+            if (kAffine || kBw) load_aux(ra, 0);
             ptx::mbar_wait(tfull_bar + as, aphase);
             ptx::tc_fence_after();
-            float ls = 0.f, lss = 0.f;
-#pragma unroll 1
-            for (int c = 0; c < BN / 32; ++c) {
-                const int n0 = tn * BN + c * 32;
-                if (c * 32 < ncol_tile) {
-                    const int ncols = min(32, ncol_tile - c * 32);
-                    uint32_t r[32];
-                    ptx::tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(ew * 32) << 16) + as * BN + c * 32, r);
-                    float4 rc[8];
+            float ls[4] = {0.f, 0.f, 0.f, 0.f}, lss[4] = {0.f, 0.f, 0.f, 0.f};
+            if (!(ep.dbg & 1) && grp_ok) {
 #pragma unroll
-                    for (int j = 0; j < 8; ++j) rc[j] = rn[j];
-                    load_resid(c + 1);
-                    ptx::tmem_ld_wait();
-                    float v[32];
+                for (int ci = 0; ci < 4; ++ci) {
+                    const int n0 = col0 + ci * 32;
+                    if (n0 < ep.Cout) {
+                        uint32_t r[32];
+                        if (ep.dbg & 8) {
 #pragma unroll
-                    for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
-                    if (affine) {
-#pragma unroll
-                        for (int j = 0; j < 32; j += 4) {
-                            const float4 g = *reinterpret_cast<const float4*>(col_s + c * 32 + j);
-                            const float4 b = *reinterpret_cast<const float4*>(col_s + BN + c * 32 + j);
-                            v[j] = fmaf(s, v[j], fmaf(t, g.x, b.x));
-                            v[j + 1] = fmaf(s, v[j + 1], fmaf(t, g.y, b.y));
-                            v[j + 2] = fmaf(s, v[j + 2], fmaf(t, g.z, b.z));
-                            v[j + 3] = fmaf(s, v[j + 3], fmaf(t, g.w, b.w));
+                            for (int j = 0; j < 32; ++j) r[j] = j + lane;
+                        } else
+                        ptx::tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(ew * 32) << 16) + as * BN + cgrp * 128 + ci * 32, r);
+                        if ((kAffine || kBw) && ci < 3) {
+                            if (ci & 1) load_aux(ra, ci + 1); else load_aux(rb, ci + 1);
                         }
-                    }
-                    if (ep.resid != nullptr && valid) {
+                        ptx::tmem_ld_wait();
+                        float v[32];
 #pragma unroll
-                        for (int j = 0; j < 8; ++j)
-                            if (j * 4 < ncols) {
-                                v[4 * j] += rc[j].x, v[4 * j + 1] += rc[j].y;
-                                v[4 * j + 2] += rc[j].z, v[4 * j + 3] += rc[j].w;
+                        for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
+                        const float (&rc)[4][8] = (ci & 1) ? rb : ra;
+                        const float* cs = col_s + cgrp * 128 + ci * 32;
+                        if (kAffine) {
+#pragma unroll
+                            for (int j = 0; j < 32; j += 4) {
+                                const float4 g = *reinterpret_cast<const float4*>(cs + j);
+                                const float4 b = *reinterpret_cast<const float4*>(cs + BN + j);
+                                v[j] = fmaf(s, v[j], fmaf(t, g.x, b.x));
+                                v[j + 1] = fmaf(s, v[j + 1], fmaf(t, g.y, b.y));
+                                v[j + 2] = fmaf(s, v[j + 2], fmaf(t, g.z, b.z));
+                                v[j + 3] = fmaf(s, v[j + 3], fmaf(t, g.w, b.w));
                             }
-                    }
-                    if (bw && valid) {
+                            if (aux != nullptr && valid) {
 #pragma unroll
-                        for (int j = 0; j < 8; ++j)
-                            if (j * 4 < ncols) {
-                                const float dv[4] = {rc[j].x, rc[j].y, rc[j].z, rc[j].w};
-                                const float4 g = *reinterpret_cast<const float4*>(col_s + c * 32 + 4 * j);
-                                const float gv[4] = {g.x, g.y, g.z, g.w};
+                                for (int j = 0; j < 32; ++j) v[j] += rc[j >> 3][j & 7];
+                            }
+                        }
+                        if (kBw) {
+                            if (valid) {
 #pragma unroll
-                                for (int q = 0; q < 4; ++q) {
-                                    const float qh = (prelu(dv[q], bw_slope) - bw_mean) * bw_rstd;
-                                    const float gd = gv[q] * v[4 * j + q];
-                                    ls += gd;
-                                    lss = fmaf(gd, qh, lss);
+                                for (int j = 0; j < 8; ++j) {
+                                    const float dv[4] = {rc[j >> 1][(j & 1) * 4], rc[j >> 1][(j & 1) * 4 + 1],
+                                                         rc[j >> 1][(j & 1) * 4 + 2], rc[j >> 1][(j & 1) * 4 + 3]};
+                                    const float4 g = *reinterpret_cast<const float4*>(cs + 4 * j);
+                                    const float gv[4] = {g.x, g.y, g.z, g.w};
+#pragma unroll
+                                    for (int q = 0; q < 4; ++q) {
+                                        const float qh = (prelu(dv[q], bw_slope) - bw_mean) * bw_rstd;
+                                        const float gd = gv[q] * v[4 * j + q];
+                                        ls[q] += gd;
+                                        lss[q] = fmaf(gd, qh, lss[q]);
+                                    }
                                 }
                             }
-                    } else if (ep.out_stat != CTN_NORM_NONE && valid) {
+                        } else if (want_stat && valid && !(ep.dbg & 16)) {
 #pragma unroll
-                        for (int j = 0; j < 32; ++j)
-                            if (j < ncols) {
-                                const float x = use_slope ? prelu(v[j], slope) : v[j];
-                                ls += x;
-                                lss = fmaf(x, x, lss);
+                            for (int j = 0; j < 32; ++j) {
+                                const float x = fmaf(slope, fminf(v[j], 0.f), fmaxf(v[j], 0.f));   // prelu
+                                ls[j & 3] += x;
+                                lss[j & 3] = fmaf(x, x, lss[j & 3]);
                             }
-                    }
-                    // wait until the TMA engine has finished READING this warp's staging area
-                    if (lane == 0) ptx::tma_store_wait_read<0>();
-                    __syncwarp();
-                    if (ep.out_f32 != nullptr) {
-#pragma unroll
-                        for (int j = 0; j < 8; ++j)
-                            ptx::st_shared_v4(stg_f32 + lane * 128 + ((static_cast<uint32_t>(j) ^ sw128) << 4),
-                                              __float_as_uint(v[4 * j]), __float_as_uint(v[4 * j + 1]),
-                                              __float_as_uint(v[4 * j + 2]), __float_as_uint(v[4 * j + 3]));
-                    }
-                    if (ep.out_hi != nullptr) {
-#pragma unroll
-                        for (int j = 0; j < 4; ++j) {
-                            uint32_t h[4], l[4];
-#pragma unroll
-                            for (int q = 0; q < 4; ++q) split_pack2(v[8 * j + 2 * q], v[8 * j + 2 * q + 1], h[q], l[q]);
-                            const uint32_t off = lane * 64 + ((static_cast<uint32_t>(j) ^ sw64) << 4);
-                            ptx::st_shared_v4(stg_hi + off, h[0], h[1], h[2], h[3]);
-                            ptx::st_shared_v4(stg_lo + off, l[0], l[1], l[2], l[3]);
                         }
-                    }
-                    ptx::fence_async_smem();
-                    __syncwarp();
-                    if (lane == 0) {
-                        const int krow0 = tk * kBM + ew * 32;
-                        if (krow0 < ep.K) {  // rows past K are clipped by the tensor map's K extent
-                            if (ep.out_f32 != nullptr)
-                                ptx::tma_store_3d(&tm_o_f32, stg + ew * Cfg::kStgWarpBytes, n0, krow0, m);
+                        // Straight from registers: a thread owns 32 consecutive columns of its row, i.e.
+                        // four whole 32 B sectors of fp32 (two of bf16), written with 256-bit stores.  The
+                        // earlier smem-staged TMA stores cost 2 x 8 KB of shared-memory bandwidth per chunk,
+                        // which the MMAs' operand reads and the TMA fills already saturate.
+                        if (valid && !(ep.dbg & 2)) {
+                            if (ep.out_f32 != nullptr) {
+                                float* op = ep.out_f32 + grow * ep.Cout + n0;
+#pragma unroll
+                                for (int j = 0; j < 4; ++j)
+                                    ptx::st_global_v8(op + 8 * j, r2u(v[8 * j]), r2u(v[8 * j + 1]), r2u(v[8 * j + 2]),
+                                                      r2u(v[8 * j + 3]), r2u(v[8 * j + 4]), r2u(v[8 * j + 5]),
+                                                      r2u(v[8 * j + 6]), r2u(v[8 * j + 7]));
+                            }
                             if (ep.out_hi != nullptr) {
-                                ptx::tma_store_3d(&tm_o_hi, stg + ew * Cfg::kStgWarpBytes + 4096, n0, krow0, m);
-                                ptx::tma_store_3d(&tm_o_lo, stg + ew * Cfg::kStgWarpBytes + 6144, n0, krow0, m);
+                                uint32_t h[16], l[16];
+#pragma unroll
+                                for (int j = 0; j < 16; ++j) split_pack2(v[2 * j], v[2 * j + 1], h[j], l[j]);
+                                __nv_bfloat16* hp = ep.out_hi + grow * ep.Cout + n0;
+                                __nv_bfloat16* lp = ep.out_lo + grow * ep.Cout + n0;
+#pragma unroll
+                                for (int j = 0; j < 2; ++j) {
+                                    ptx::st_global_v8(hp + 16 * j, h[8 * j], h[8 * j + 1], h[8 * j + 2], h[8 * j + 3],
+                                                      h[8 * j + 4], h[8 * j + 5], h[8 * j + 6], h[8 * j + 7]);
+                                    ptx::st_global_v8(lp + 16 * j, l[8 * j], l[8 * j + 1], l[8 * j + 2], l[8 * j + 3],
+                                                      l[8 * j + 4], l[8 * j + 5], l[8 * j + 6], l[8 * j + 7]);
+                                }
                             }
                         }
-                        ptx::tma_store_commit();
                     }
                 }
-                if ((c & 3) == 3) {
-                    const int grp = (tn * BN + c * 32) / CTN_COL_TILE;
-                    if (grp < ep.groups) epilogue_flush_stats(ep, m, tk, grp, ew, grow, valid, ls, lss);
+                if ((want_stat || kBw) && tile_ok) {
+                    float a0 = (ls[0] + ls[1]) + (ls[2] + ls[3]), a1 = (lss[0] + lss[1]) + (lss[2] + lss[3]);
+                    epilogue_flush_stats(ep, m, tk, col0 / CTN_COL_TILE, ew, grow, valid, a0, a1);
                 }
             }
             ptx::tc_fence_before();
-            ptx::mbar_arrive(tempty_bar + as);
+            __syncwarp();
+            if (lane == 0) {
+                if (PAIR) ptx::mbar_arrive_cluster(tempty_remote + as * 8);
+                else ptx::mbar_arrive(tempty_bar + as);
+            }
         }
-        if (lane == 0) ptx::tma_store_wait_all<0>();
     }
 
     ptx::tc_fence_before();
-    __syncthreads();
+    if (PAIR) ptx::cluster_sync(); else __syncthreads();
     if (warp == 1) {
         ptx::tc_fence_after();
-        ptx::tmem_dealloc(tmem_base, Cfg::kTmemCols);
+        if (PAIR) ptx::tmem_dealloc_pair(tmem_base, Cfg::kTmemCols);
+        else ptx::tmem_dealloc(tmem_base, Cfg::kTmemCols);
     }
 }
 
@@ -601,16 +651,16 @@ static int make_tmap_out(CUtensorMap* tm, const void* ptr, int M, int K, int C, 
     return CTN_OK;
 }
 
-template <int BN>
+template <int BN, bool PAIR, int EPI>
 static int launch_tc(const ctn_gemm_args& a, const EpiParams& ep, cudaStream_t stream) {
-    using Cfg = TcCfg<BN>;
+    using Cfg = TcCfg<BN, PAIR>;
     CUtensorMap ta_hi, ta_lo, tw_hi, tw_lo;
     const long long R = static_cast<long long>(a.M) * a.K;
     int rc;
     if ((rc = make_tmap_bf16_kmajor(&ta_hi, a.a_hi, R, a.Cin, kBM)) != CTN_OK) return rc;
     if ((rc = make_tmap_bf16_kmajor(&ta_lo, a.a_lo, R, a.Cin, kBM)) != CTN_OK) return rc;
-    if ((rc = make_tmap_bf16_kmajor(&tw_hi, a.w_hi, a.Cout, a.Cin, BN)) != CTN_OK) return rc;
-    if ((rc = make_tmap_bf16_kmajor(&tw_lo, a.w_lo, a.Cout, a.Cin, BN)) != CTN_OK) return rc;
+    if ((rc = make_tmap_bf16_kmajor(&tw_hi, a.w_hi, a.Cout, a.Cin, Cfg::kWRows)) != CTN_OK) return rc;
+    if ((rc = make_tmap_bf16_kmajor(&tw_lo, a.w_lo, a.Cout, a.Cin, Cfg::kWRows)) != CTN_OK) return rc;
     CUtensorMap to_f32, to_hi, to_lo;
     // unused maps still have to be valid objects: point them at an operand
     if ((rc = make_tmap_out(&to_f32, a.out_f32 ? a.out_f32 : a.out_hi, a.M, a.K, a.Cout, a.out_f32 != nullptr)) != CTN_OK)
@@ -621,17 +671,31 @@ static int launch_tc(const ctn_gemm_args& a, const EpiParams& ep, cudaStream_t s
         return rc;
     static bool attr_set = false;  // idempotent; set once per process per instantiation
     if (!attr_set) {
-        cudaError_t e = cudaFuncSetAttribute(gemm_tc_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+        cudaError_t e = cudaFuncSetAttribute(gemm_tc_kernel<BN, PAIR, EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                              Cfg::kSmemBytes);
         if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(gemm_tc_kernel)");
         attr_set = true;
     }
     const int n_tiles = ceil_div(a.Cout, BN);
-    const int total = a.M * ep.tiles_per_utt * n_tiles;
-    const int grid = total < sm_count() ? total : sm_count();
-    gemm_tc_kernel<BN><<<grid, kTcThreads, Cfg::kSmemBytes, stream>>>(ta_hi, ta_lo, tw_hi, tw_lo, to_f32, to_hi, to_lo,
-                                                                      ep, a.Cin, n_tiles, total);
-    CTN_LAUNCH_CHECK("gemm_tc_kernel");
+    const int row_tiles = a.M * ep.tiles_per_utt;
+    const int items = (PAIR ? ceil_div(row_tiles, 2) : row_tiles) * n_tiles;
+    const int workers_max = PAIR ? sm_count() / 2 : sm_count();
+    const int workers = items < workers_max ? items : workers_max;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(PAIR ? 2 * workers : workers, 1, 1);
+    cfg.blockDim = dim3(Cfg::kThreads, 1, 1);
+    cfg.dynamicSmemBytes = Cfg::kSmemBytes;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = PAIR ? 2 : 1;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    cudaError_t e = cudaLaunchKernelEx(&cfg, gemm_tc_kernel<BN, PAIR, EPI>, ta_hi, ta_lo, tw_hi, tw_lo, to_f32, to_hi, to_lo,
+                                       ep, a.Cin, n_tiles, items, row_tiles);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaLaunchKernelEx(gemm_tc_kernel)");
     return CTN_OK;
 }
 
@@ -674,19 +738,31 @@ extern "C" int ctn_gemm1x1(const ctn_gemm_args* args, void* stream_) {
     ep.stat_prelu = a.stat_prelu;
     ep.bw_pre = a.bw_pre, ep.bw_gamma = a.bw_gamma, ep.bw_slope = a.bw_slope;
     ep.bw_stat = static_cast<const float2*>(a.bw_stat), ep.bw_P = a.bw_P;
+    {
+        const char* d = getenv("CTN_GEMM_DBG");
+        ep.dbg = d ? atoi(d) : 0;
+    }
     CTN_REQUIRE(a.bw_pre == nullptr || (a.bw_gamma && a.bw_slope && a.bw_stat && a.bw_P > 0 &&
                                         a.out_stat == CTN_NORM_GLN && a.resid == nullptr && a.in_norm == CTN_NORM_NONE),
                 "ctn_gemm1x1: bw_pre needs bw_gamma/bw_slope/bw_stat, out_stat = GLN and no resid / in_norm");
 
     auto aligned16 = [](const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; };
-    const bool tc_ok = !a.force_simt && a.Cin % 8 == 0 && a.Cout % 8 == 0 && aligned16(a.a_hi) && aligned16(a.a_lo) &&
+    const bool tc_ok = !(a.force_simt & 1) && a.Cin % 8 == 0 && a.Cout % 32 == 0 && aligned16(a.a_hi) && aligned16(a.a_lo) &&
                        aligned16(a.w_hi) && aligned16(a.w_lo) && aligned16(a.out_f32) && aligned16(a.out_hi) &&
                        aligned16(a.out_lo) && aligned16(a.resid) && aligned16(a.bw_pre);
     if (tc_ok) {
         // 256-wide tiles halve the re-reads of the activation tile but need enough tiles to fill the SMs
         const long long tiles256 = static_cast<long long>(a.M) * ep.tiles_per_utt * ceil_div(a.Cout, 256);
-        if (a.Cout % 256 == 0 && tiles256 >= 2ll * sm_count()) return launch_tc<256>(a, ep, stream);
-        return launch_tc<128>(a, ep, stream);
+        const int mode = a.force_simt >> 1;   // test hook: 1 = single-CTA kernels only, 2 = pair kernel
+        const bool pair = a.Cout % 256 == 0 && mode != 1 && (mode == 2 || tiles256 >= 2ll * sm_count());
+        const bool affine = a.col_g != nullptr || a.col_bias != nullptr || a.in_norm != CTN_NORM_NONE ||
+                            a.resid != nullptr;
+        if (a.bw_pre != nullptr)
+            return pair ? launch_tc<256, true, kEpiBw>(a, ep, stream) : launch_tc<128, false, kEpiBw>(a, ep, stream);
+        if (affine)
+            return pair ? launch_tc<256, true, kEpiAffine>(a, ep, stream)
+                        : launch_tc<128, false, kEpiAffine>(a, ep, stream);
+        return pair ? launch_tc<256, true, kEpiPlain>(a, ep, stream) : launch_tc<128, false, kEpiPlain>(a, ep, stream);
     }
     const int grid = a.M * ep.tiles_per_utt;
     gemm_simt_kernel<<<grid, 128, 0, stream>>>(
