@@ -83,4 +83,28 @@ __device__ __forceinline__ float2 gln_finalize_warp(const float2* __restrict__ p
     return make_float2(static_cast<float>(mean), static_cast<float>(1.0 / sqrt(var + 1e-8)));
 }
 
+// Block-wide variant: every thread of the CTA loads its share of the partials at once (one
+// round of memory latency instead of P/32), fixed reduction order.  red: >= 2 * (blockDim.x / 32)
+// doubles of shared memory.  Returns (mean, rstd) to every thread; contains __syncthreads().
+__device__ __forceinline__ float2 gln_finalize_block(const float2* __restrict__ part, int P, double count,
+                                                     double* red) {
+    double s = 0.0, ss = 0.0;
+    for (int i = threadIdx.x; i < P; i += blockDim.x) {
+        const float2 v = __ldg(part + i);
+        s += static_cast<double>(v.x);
+        ss += static_cast<double>(v.y);
+    }
+    s = warp_sum(s);
+    ss = warp_sum(ss);
+    const int nw = blockDim.x >> 5, w = threadIdx.x >> 5;
+    if ((threadIdx.x & 31) == 0) red[w] = s, red[nw + w] = ss;
+    __syncthreads();
+    s = 0.0, ss = 0.0;
+    for (int i = 0; i < nw; ++i) s += red[i], ss += red[nw + i];
+    const double mean = s / count;
+    double var = ss / count - mean * mean;
+    var = var > 0.0 ? var : 0.0;
+    return make_float2(static_cast<float>(mean), static_cast<float>(1.0 / sqrt(var + 1e-8)));
+}
+
 }  // namespace ctn

@@ -3,8 +3,11 @@
 // frames k = ph, ph + dil, ph + 2 dil, ...  The three taps of consecutive outputs are then
 // consecutive elements of that sequence, so every input element is loaded, PReLU'd and
 // normalised ONCE and reused from a 3-deep register window (the row-per-warp kernel does
-// that work three times).  Loads run 4 rows ahead of use.  HBM-bound: 4*H bytes read and
-// 4*H written per frame (+4*H for d in training), 2/32 halo re-reads per segment.
+// that work three times).  Loads run 8 rows ahead of use.  HBM-bound by design: 4*H bytes
+// read and 4*H written per frame (+4*H for d in training), 2/32 halo re-reads per segment --
+// so the arithmetic is written with the packed fp32x2 instructions of sm_100 (fma.rn.f32x2
+// ...): the scalar version of this loop issued 34 instructions per element and was
+// issue-bound at half the memory roofline.
 #pragma once
 #include "common.cuh"
 
@@ -12,7 +15,7 @@ namespace ctn {
 
 constexpr int kDmSeg = 32;    // outputs per warp segment
 constexpr int kDmWarps = 8;
-constexpr int kDmAhead = 4;   // rows loaded ahead of use
+constexpr int kDmAhead = 8;   // rows loaded ahead of use
 
 struct DwMarchParams {
     int K, H, dil, c0, in_P, NS, items, out_P;
@@ -29,22 +32,63 @@ struct DwMarchParams {
     float2* out_stat;
 };
 
+// ---- packed fp32x2 helpers (a 64-bit register pair holds two floats) ----
+typedef unsigned long long f2_t;
+__device__ __forceinline__ f2_t f2_pack(float lo, float hi) {
+    f2_t r;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+    return r;
+}
+__device__ __forceinline__ void f2_unpack(f2_t v, float& lo, float& hi) {
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
+__device__ __forceinline__ f2_t f2_fma(f2_t a, f2_t b, f2_t c) {
+    f2_t d;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+    return d;
+}
+__device__ __forceinline__ f2_t f2_mul(f2_t a, f2_t b) {
+    f2_t d;
+    asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+    return d;
+}
+__device__ __forceinline__ f2_t f2_add(f2_t a, f2_t b) {
+    f2_t d;
+    asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+    return d;
+}
+// (max(v, 0), min(v, 0)) of a pair: mx with two scalar FMNMX, mn = v - mx with one packed FMA
+__device__ __forceinline__ void f2_split_sign(f2_t v, f2_t neg1, f2_t& mx, f2_t& mn) {
+    float a, b;
+    f2_unpack(v, a, b);
+    mx = f2_pack(fmaxf(a, 0.f), fmaxf(b, 0.f));
+    mn = f2_fma(mx, neg1, v);
+}
+// (hi, lo) bf16 split of a pair: hi = rn(v), lo = rn(v - hi); v.lo lands in the low half-word
+__device__ __forceinline__ void f2_split_bf16(f2_t v, f2_t neg1, uint32_t& hi, uint32_t& lo) {
+    float a, b;
+    f2_unpack(v, a, b);
+    const __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
+    hi = *reinterpret_cast<const uint32_t*>(&h);
+    const f2_t hf = f2_pack(__uint_as_float(hi << 16), __uint_as_float(hi & 0xffff0000u));
+    float c, d;
+    f2_unpack(f2_fma(hf, neg1, v), c, d);
+    const __nv_bfloat162 l = __floats2bfloat162_rn(c, d);
+    lo = *reinterpret_cast<const uint32_t*>(&l);
+}
+
 __global__ void __launch_bounds__(kDmWarps * 32)
 dwconv_march_kernel(const DwMarchParams p) {
-    __shared__ float st_s[2];
+    __shared__ double fin_s[2 * kDmWarps];
     __shared__ float red_s[2 * kDmWarps];
     const int m = blockIdx.y;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int H = p.H, d = p.dil;
-    if (warp == 0) {
-        const float2 st = gln_finalize_warp(p.in_stat + static_cast<long long>(m) * p.in_P, p.in_P,
-                                            static_cast<double>(p.K) * H);
-        if (lane == 0) st_s[0] = st.x, st_s[1] = st.y;
-    }
-    __syncthreads();
-    const float mean = st_s[0], rstd = st_s[1];
+    const float2 st = gln_finalize_block(p.in_stat + static_cast<long long>(m) * p.in_P, p.in_P,
+                                         static_cast<double>(p.K) * H, fin_s);
+    const float mean = st.x, rstd = st.y;
     const float a1 = __ldg(p.prelu_in), a2 = __ldg(p.prelu_out);
-    float ls = 0.f, lss = 0.f;
+    f2_t ls[2] = {0ull, 0ull}, lss[2] = {0ull, 0ull};   // packed (0.f, 0.f)
 
     const int item = blockIdx.x * kDmWarps + warp;
     const int CG = (H + 127) / 128;
@@ -56,74 +100,102 @@ dwconv_march_kernel(const DwMarchParams p) {
     const int j0 = seg * kDmSeg;
     const int n = min(kDmSeg, J - j0);                      // outputs of this segment
     if (item < p.items && c < H && n > 0) {
-        // per-channel constants: n1 = A * prelu(a) + B
-        const float4 g = *reinterpret_cast<const float4*>(p.gamma_in + c);
-        const float4 b = *reinterpret_cast<const float4*>(p.beta_in + c);
-        const float A[4] = {g.x * rstd, g.y * rstd, g.z * rstd, g.w * rstd};
-        const float Bc[4] = {b.x - A[0] * mean, b.y - A[1] * mean, b.z - A[2] * mean, b.w - A[3] * mean};
-        float w[4][3];
+        const f2_t neg1 = f2_pack(-1.f, -1.f);
+        const f2_t a2p = f2_pack(a2, a2);
+        // per-channel constants: n1 = A * max(a, 0) + (A * a1) * min(a, 0) + B   (PReLU + gLN)
+        f2_t A[2], Aa[2], Bc[2], w0[2], w1[2], w2[2];
         {
-            const float4 w0 = *reinterpret_cast<const float4*>(p.wd + c * 3);
-            const float4 w1 = *reinterpret_cast<const float4*>(p.wd + c * 3 + 4);
-            const float4 w2 = *reinterpret_cast<const float4*>(p.wd + c * 3 + 8);
-            const float f[12] = {w0.x, w0.y, w0.z, w0.w, w1.x, w1.y, w1.z, w1.w, w2.x, w2.y, w2.z, w2.w};
+            const float4 g = *reinterpret_cast<const float4*>(p.gamma_in + c);
+            const float4 b = *reinterpret_cast<const float4*>(p.beta_in + c);
+            const float Af[4] = {g.x * rstd, g.y * rstd, g.z * rstd, g.w * rstd};
+            const float Bf[4] = {b.x - Af[0] * mean, b.y - Af[1] * mean, b.z - Af[2] * mean, b.w - Af[3] * mean};
+            const float4 t0 = *reinterpret_cast<const float4*>(p.wd + c * 3);
+            const float4 t1 = *reinterpret_cast<const float4*>(p.wd + c * 3 + 4);
+            const float4 t2 = *reinterpret_cast<const float4*>(p.wd + c * 3 + 8);
+            const float f[12] = {t0.x, t0.y, t0.z, t0.w, t1.x, t1.y, t1.z, t1.w, t2.x, t2.y, t2.z, t2.w};
 #pragma unroll
-            for (int i = 0; i < 4; ++i)
-#pragma unroll
-                for (int t = 0; t < 3; ++t) w[i][t] = f[i * 3 + t];
+            for (int i = 0; i < 2; ++i) {
+                A[i] = f2_pack(Af[2 * i], Af[2 * i + 1]);
+                Aa[i] = f2_pack(Af[2 * i] * a1, Af[2 * i + 1] * a1);
+                Bc[i] = f2_pack(Bf[2 * i], Bf[2 * i + 1]);
+                w0[i] = f2_pack(f[6 * i], f[6 * i + 3]);
+                w1[i] = f2_pack(f[6 * i + 1], f[6 * i + 4]);
+                w2[i] = f2_pack(f[6 * i + 2], f[6 * i + 5]);
+            }
         }
         const long long ubase = static_cast<long long>(m) * p.K;
         const int r0 = j0 - p.c0;   // sequence index of the first window element
         const int nrows = n + 2;
+        const long long strd = static_cast<long long>(d) * H;            // elements between rows of the phase
+        const long long in0 = (ubase + ph + static_cast<long long>(r0) * d) * H + c;   // may point before the buffer
         auto valid = [&](int s) { return s < nrows && r0 + s >= 0 && r0 + s < J; };
         auto load = [&](int s) {
             float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-            if (valid(s)) v = *reinterpret_cast<const float4*>(p.in + (ubase + ph + static_cast<long long>(r0 + s) * d) * H + c);
+            if (valid(s)) v = *reinterpret_cast<const float4*>(p.in + in0 + s * strd);
             return v;
         };
-        auto xform = [&](const float4& v, bool ok, float (&o)[4]) {
-            const float r[4] = {v.x, v.y, v.z, v.w};
+        // PReLU + norm of one loaded row; rows outside the phase are the convolution's zero padding
+        auto xform = [&](const float4& v, bool ok, f2_t (&o)[2]) {
+            if (ok) {
+                const f2_t in2[2] = {f2_pack(v.x, v.y), f2_pack(v.z, v.w)};
 #pragma unroll
-            for (int i = 0; i < 4; ++i) o[i] = ok ? fmaf(A[i], prelu(r[i], a1), Bc[i]) : 0.f;  // zero padding after the norm
+                for (int i = 0; i < 2; ++i) {
+                    f2_t mx, mn;
+                    f2_split_sign(in2[i], neg1, mx, mn);
+                    o[i] = f2_fma(A[i], mx, f2_fma(Aa[i], mn, Bc[i]));
+                }
+            } else {
+                o[0] = 0ull, o[1] = 0ull;
+            }
         };
         float4 q[kDmAhead];
 #pragma unroll
         for (int s = 0; s < kDmAhead; ++s) q[s] = load(s);
-        float x0[4], x1[4], x2[4];
+        f2_t x0[2], x1[2], x2[2];
         xform(q[0], valid(0), x0);
-        q[0] = load(4);
+        q[0] = load(kDmAhead);
         xform(q[1], valid(1), x1);
-        q[1] = load(5);
+        q[1] = load(kDmAhead + 1);
+        long long orow = (ubase + ph + static_cast<long long>(j0) * d) * H + c;
         for (int o = 0; o < n; o += kDmAhead) {
 #pragma unroll
             for (int u = 0; u < kDmAhead; ++u) {
                 if (o + u < n) {
                     const int s = o + u + 2;
-                    xform(q[(u + 2) & 3], valid(s), x2);
-                    q[(u + 2) & 3] = load(s + kDmAhead);
-                    const long long row = ubase + ph + static_cast<long long>(j0 + o + u) * d;
-                    float acc[4], qq[4];
+                    xform(q[(u + 2) & (kDmAhead - 1)], valid(s), x2);
+                    q[(u + 2) & (kDmAhead - 1)] = load(s + kDmAhead);
+                    uint2 h, l;
+                    f2_t acc[2];
 #pragma unroll
-                    for (int i = 0; i < 4; ++i) {
-                        acc[i] = fmaf(w[i][2], x2[i], fmaf(w[i][1], x1[i], w[i][0] * x0[i]));
-                        qq[i] = prelu(acc[i], a2);
-                        ls += qq[i];
-                        lss = fmaf(qq[i], qq[i], lss);
+                    for (int i = 0; i < 2; ++i) {
+                        acc[i] = f2_fma(w2[i], x2[i], f2_fma(w1[i], x1[i], f2_mul(w0[i], x0[i])));
+                        f2_t mx, mn;
+                        f2_split_sign(acc[i], neg1, mx, mn);
+                        const f2_t qq = f2_fma(a2p, mn, mx);          // PReLU
+                        ls[i] = f2_add(ls[i], qq);
+                        lss[i] = f2_fma(qq, qq, lss[i]);
+                        f2_split_bf16(qq, neg1, i == 0 ? h.x : h.y, i == 0 ? l.x : l.y);
                         x0[i] = x1[i], x1[i] = x2[i];
                     }
-                    if (p.out_pre) *reinterpret_cast<float4*>(p.out_pre + row * H + c) = make_float4(acc[0], acc[1], acc[2], acc[3]);
-                    uint2 h, l;
-                    split_pack2(qq[0], qq[1], h.x, l.x);
-                    split_pack2(qq[2], qq[3], h.y, l.y);
-                    *reinterpret_cast<uint2*>(p.out_hi + row * H + c) = h;
-                    *reinterpret_cast<uint2*>(p.out_lo + row * H + c) = l;
+                    if (p.out_pre) {
+                        float4 dv;
+                        f2_unpack(acc[0], dv.x, dv.y);
+                        f2_unpack(acc[1], dv.z, dv.w);
+                        *reinterpret_cast<float4*>(p.out_pre + orow) = dv;
+                    }
+                    *reinterpret_cast<uint2*>(p.out_hi + orow) = h;
+                    *reinterpret_cast<uint2*>(p.out_lo + orow) = l;
+                    orow += strd;
                 }
             }
         }
     }
-    ls = warp_sum(ls);
-    lss = warp_sum(lss);
-    if (lane == 0) red_s[warp] = ls, red_s[kDmWarps + warp] = lss;
+    float s0, s1, s2, s3, t0, t1, t2, t3;
+    f2_unpack(ls[0], s0, s1), f2_unpack(ls[1], s2, s3);
+    f2_unpack(lss[0], t0, t1), f2_unpack(lss[1], t2, t3);
+    const float wls = warp_sum((s0 + s1) + (s2 + s3));
+    const float wlss = warp_sum((t0 + t1) + (t2 + t3));
+    if (lane == 0) red_s[warp] = wls, red_s[kDmWarps + warp] = wlss;
     __syncthreads();
     if (threadIdx.x == 0) {
         float s = 0.f, ss = 0.f;

@@ -374,7 +374,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tm_a_hi, const __grid_constan
         const float bw_slope = kBw ? __ldg(ep.bw_slope) : 0.f;
         const float* aux = kBw ? ep.bw_pre : (kAffine ? ep.resid : nullptr);  // per-element side input
         const bool want_stat = ep.out_stat != CTN_NORM_NONE;
-        int it = 0, cur_tn = -1;
+        int it = 0, cur_tn = -1, cur_m = -1;
+        float s = 1.f, t = 0.f, bw_mean = 0.f, bw_rstd = 1.f;
         const uint32_t tempty_remote = PAIR ? ptx::mapa(ptx::smem_u32(tempty_bar), 0) : 0u;
         for (int tile = worker; tile < total_tiles; tile += n_workers, ++it) {
             const int as = it & 1;
@@ -386,9 +387,10 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tm_a_hi, const __grid_constan
             const int k = tk * kBM + ew * 32 + lane;
             const bool valid = tile_ok && k < ep.K;
             const long long grow = static_cast<long long>(m) * ep.K + k;
-            float s = 1.f, t = 0.f, bw_mean = 0.f, bw_rstd = 1.f;
-            if (kAffine) epilogue_row_affine(ep, m, grow, valid, s, t);
-            if (kBw) epilogue_bw_stats(ep, m, bw_mean, bw_rstd);
+            // gLN statistics depend on the utterance only: re-reduce the partials when m changes
+            if (kAffine && (ep.in_norm != CTN_NORM_GLN || m != cur_m)) epilogue_row_affine(ep, m, grow, valid, s, t);
+            if (kBw && m != cur_m) epilogue_bw_stats(ep, m, bw_mean, bw_rstd);
+            cur_m = m;
             if ((kAffine || kBw) && tn != cur_tn) {  // per-column constants of this column tile -> smem
                 ptx::named_bar_sync(1, kEpiThreads);
                 for (int i = et; i < BN; i += kEpiThreads) {
