@@ -268,6 +268,10 @@ def run_b200(args):
                 "share_of_step": g_ms / tot_ms, "traffic": None,
                 "how": "CUDA events around every launch of one %d-utterance micro-batch pass, 3 repeats" % mb}
 
+    train = None
+    if not args.no_train:
+        train = train_step(args, world, rank, dev, timed)
+
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:
         v, step_s, cores = oracle_cpu_throughput(cfg, T, 4, 3, 1)
@@ -293,9 +297,60 @@ def run_b200(args):
         }
         if cpu is not None:
             out["cpu_baseline"] = cpu
+        if train is not None:
+            out["train_step"] = train
         print(json.dumps(out), flush=True)
     if world > 1:
         dist.destroy_process_group()
+
+
+def train_step(args, world, rank, dev, timed):
+    """BASELINE configs[1]: paper config, batch 3 x 4 s per GPU (weak scaling), forward +
+    cal_loss + backward (ONE NCCL all-reduce of the flat gradient when world > 1) + clip(5) +
+    Adam(1e-3), as solver.py:178-186.  Host mixtures/sources are copied in every step and the
+    loss is read back (solver.py:188 does loss.item())."""
+    import conv_tasnet
+    import pit_criterion
+    from ctn_b200 import _dist
+    from oracle import convtasnet_oracle as O
+    cfg, T, M = PAPER, T_4S, 3
+    params = O.random_params(*(cfg[k] for k in "NLBHPXRC"), cfg["causal"], seed=1234)
+    model = conv_tasnet.ConvTasNet(**cfg)
+    model.load_state_dict(params)
+    model = model.to(dev).train()
+    if world > 1:
+        _dist.attach(model)
+    opt = torch.optim.Adam(model.parameters(), lr=1e-3)
+    g = torch.Generator().manual_seed(77 + rank)
+    h_src = (0.1 * torch.randn(M, cfg["C"], T, generator=g)).pin_memory()
+    h_mix = h_src.sum(1).pin_memory()
+    lengths = torch.full((M,), T, dtype=torch.int64, device=dev)
+    h_loss = torch.empty((), dtype=torch.float32).pin_memory()
+    eng = model.train_engine()
+
+    def step():
+        mix = h_mix.to(dev, non_blocking=True)
+        src = h_src.to(dev, non_blocking=True)
+        est = model(mix)
+        loss, _, _, _ = pit_criterion.cal_loss(src, est, lengths)
+        opt.zero_grad()
+        loss.backward()
+        torch.nn.utils.clip_grad_norm_(model.parameters(), 5.0)
+        opt.step()
+        h_loss.copy_(loss.detach(), non_blocking=True)
+
+    for _ in range(max(3, args.warmup)):
+        step()
+    l0 = eng.launches
+    steps = max(args.steps, 5)
+    sec = timed(step, steps)
+    return {"ms_per_step": sec / steps * 1e3, "steps": steps, "utterances_per_gpu": M, "global_batch": M * world,
+            "scaling": "weak", "audio_s_per_s": M * world * (T / SR) * steps / sec,
+            "algorithmic_tflops": 3.0 * forward_flops(cfg, T) * M * world * steps / sec / 1e12,
+            "gpu_launches_per_step": (eng.launches - l0) // steps, "loss": float(h_loss),
+            "config": "BASELINE configs[1]: paper config, 3 x 4 s per GPU, fwd + PIT SI-SNR loss + bwd + "
+                      "grad all-reduce + clip(5) + Adam, host inputs copied every step",
+            "h2d_bytes_per_step": M * T * 4 * (1 + cfg["C"]), "d2h_bytes_per_step": 4}
 
 
 def main():
@@ -307,6 +362,7 @@ def main():
     ap.add_argument("--micro-batch", type=int, default=16)
     ap.add_argument("--graph", type=int, default=1)
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-train", action="store_true", help="skip the train-step leg")
     args = ap.parse_args()
     if args.warmup < 3 and args.impl == "b200":
         args.warmup = 3

@@ -9,6 +9,7 @@
 // Every reduction is a fixed-order tree (thread -> warp -> CTA partial -> ctn_reduce_partials),
 // so gradients are bit-reproducible run to run.
 #include "common.cuh"
+#include "bwd_dw_march.cuh"
 
 namespace ctn {
 
@@ -607,12 +608,23 @@ extern "C" int ctn_norm_split(const float* in, const float* prelu_slope, const f
     return CTN_OK;
 }
 
-extern "C" int ctn_bwd_dw_layout(int K, int H, int* tiles, int* row_groups) {
+static bool bwd_use_march(int H, int P) { return P == 3 && H % 4 == 0; }
+
+extern "C" int ctn_bwd_dw_layout(int K, int H, int P, int dilation, int* ctas, int* chan_rows) {
+    if (bwd_use_march(H, P) && dilation > 0) {
+        int NS, units, groups, n_ctas;
+        bwd_march_geometry(K, H, dilation, &NS, &units, &groups, &n_ctas);
+        if (ctas) *ctas = n_ctas;
+        if (chan_rows) *chan_rows = groups;
+        return CTN_OK;
+    }
     const int vec = H % 4 == 0 ? 4 : 1;
     const int CV = ceil_div(H, vec);
     const int CVt = CV < kBwThreads ? CV : kBwThreads;
-    if (tiles) *tiles = ceil_div(K, kBdTile);
-    if (row_groups) *row_groups = kBwThreads / CVt > 0 ? kBwThreads / CVt : 1;
+    const int tiles = ceil_div(K, kBdTile);
+    const int rg = kBwThreads / CVt > 0 ? kBwThreads / CVt : 1;
+    if (ctas) *ctas = tiles;
+    if (chan_rows) *chan_rows = tiles * rg;
     return CTN_OK;
 }
 
@@ -624,6 +636,28 @@ extern "C" int ctn_bwd_dwconv(const ctn_bwd_dw_args* args, void* stream) {
     CTN_REQUIRE(a.du && a.d && a.a && a.stat1 && a.stat2 && a.bstat && a.g1 && a.b1 && a.g2 && a.wd && a.slope1 &&
                     a.slope2 && a.dn1 && a.chan_part && a.scal_part,
                 "ctn_bwd_dwconv: NULL pointer");
+    const bool aligned = al16(a.du) && al16(a.d) && al16(a.a) && al16(a.dn1) && al16(a.g1) && al16(a.b1) &&
+                         al16(a.g2) && al16(a.wd) && al16(a.chan_part);
+    if (bwd_use_march(a.H, a.P)) {
+        CTN_REQUIRE(aligned, "ctn_bwd_dwconv: pointers must be 16-byte aligned");
+        BwdMarchParams q;
+        q.K = a.K, q.H = a.H, q.dil = a.dilation, q.c0 = a.causal ? 2 : 1;
+        q.P1 = a.P1, q.P2 = a.P2, q.Pb = a.Pb;
+        bwd_march_geometry(a.K, a.H, a.dilation, &q.NS, &q.units, &q.groups, &q.ctas);
+        q.chan_rows = q.groups;
+        q.du = a.du, q.d = a.d, q.a = a.a;
+        q.stat1 = static_cast<const float2*>(a.stat1), q.stat2 = static_cast<const float2*>(a.stat2);
+        q.bstat = static_cast<const float2*>(a.bstat);
+        q.g1 = a.g1, q.b1 = a.b1, q.g2 = a.g2, q.wd = a.wd, q.slope1 = a.slope1, q.slope2 = a.slope2;
+        q.dn1 = a.dn1, q.chan_part = a.chan_part, q.scal_part = a.scal_part;
+        dim3 grid(q.ctas, a.M);
+        if (a.causal)
+            bwd_dw_march_kernel<2><<<grid, kDmWarps * 32, 0, static_cast<cudaStream_t>(stream)>>>(q);
+        else
+            bwd_dw_march_kernel<1><<<grid, kDmWarps * 32, 0, static_cast<cudaStream_t>(stream)>>>(q);
+        CTN_LAUNCH_CHECK("bwd_dw_march_kernel");
+        return CTN_OK;
+    }
     BwdDwParams p;
     p.K = a.K, p.H = a.H, p.P = a.P, p.dil = a.dilation, p.causal = a.causal;
     p.P1 = a.P1, p.P2 = a.P2, p.Pb = a.Pb;
@@ -632,12 +666,11 @@ extern "C" int ctn_bwd_dwconv(const ctn_bwd_dw_args* args, void* stream) {
     p.bstat = static_cast<const float2*>(a.bstat);
     p.g1 = a.g1, p.b1 = a.b1, p.g2 = a.g2, p.wd = a.wd, p.slope1 = a.slope1, p.slope2 = a.slope2;
     p.dn1 = a.dn1, p.chan_part = a.chan_part, p.scal_part = a.scal_part;
-    int tiles, rg;
-    ctn_bwd_dw_layout(a.K, a.H, &tiles, &rg);
-    p.RG = rg;
+    int tiles, rows;
+    ctn_bwd_dw_layout(a.K, a.H, a.P, a.dilation, &tiles, &rows);
+    p.RG = rows / tiles;
     dim3 grid(tiles, a.M);
-    const bool vec = a.H % 4 == 0 && al16(a.du) && al16(a.d) && al16(a.a) && al16(a.dn1) && al16(a.g1) &&
-                     al16(a.b1) && al16(a.g2);
+    const bool vec = a.H % 4 == 0 && aligned;
     CTN_REQUIRE(vec || a.H % 4 != 0, "ctn_bwd_dwconv: pointers must be 16-byte aligned");
     if (vec)
         bwd_dw_kernel<4><<<grid, kBwThreads, 0, static_cast<cudaStream_t>(stream)>>>(p);

@@ -94,11 +94,14 @@ class TrainPlan:
         self.bstat = z(M, self.P1, 2, **f32)
         self.dn0 = e(Rr, N, **f32)
         self.dpre = e(Rr, N, **f32)
-        tiles_b, rg = C.c_int(), C.c_int()
-        lib.ctn_bwd_dw_layout(K, H, C.byref(tiles_b), C.byref(rg))
-        self.tiles_b, self.rg = tiles_b.value, rg.value
-        self.chan_part = e(M * self.tiles_b * self.rg, (4 + cfg["P"]) * H, **f32)
-        self.scal_part = e(M * self.tiles_b, 4, **f32)
+        self.bd_ctas, self.bd_rows = [], []          # per dilation: scal_part / chan_part rows per utterance
+        for x in range(cfg["X"]):
+            ctas, rows = C.c_int(), C.c_int()
+            lib.ctn_bwd_dw_layout(K, H, cfg["P"], 2 ** x, C.byref(ctas), C.byref(rows))
+            self.bd_ctas.append(ctas.value)
+            self.bd_rows.append(rows.value)
+        self.chan_part = e(M * max(self.bd_rows), (4 + cfg["P"]) * H, **f32)
+        self.scal_part = e(M * max(self.bd_ctas), 4, **f32)
         self.tiles_pn = lib.ctn_bwd_prelu_norm_tiles(K)
         self.alpha_part = e(M * self.tiles_pn, **f32)
         self.tiles_db = lib.ctn_decoder_bwd_tiles(K)
@@ -252,14 +255,14 @@ class TrainPlan:
             self._keep.append(b)
             bwd.append(lambda s, ref=C.byref(b): bd(ref, s))
             a_ = (self.dn1.data_ptr(), self.a[i].data_ptr(), self.stat1[i].data_ptr(), self.P1,
-                  self.scal_part.data_ptr(), self.tiles_b, params[k["g1"]].data_ptr(), params[k["a1"]].data_ptr(),
+                  self.scal_part.data_ptr(), self.bd_ctas[xb], params[k["g1"]].data_ptr(), params[k["a1"]].data_ptr(),
                   M, K, H, self.hl_H[0].data_ptr(), self.hl_H[1].data_ptr(), self.alpha_part.data_ptr())
             bwd.append(lambda s, a=a_: pn(*a, s))                                       # da (hi, lo)
             segs = [(0, H, 1, self.grad_ptr(k["g2"]), 1), (H, H, 1, self.grad_ptr(k["b2"]), 1),
                     (2 * H, H, 1, self.grad_ptr(k["g1"]), 1), (3 * H, H, 1, self.grad_ptr(k["b1"]), 1)]
             segs += [((4 + j) * H, H, 1, self.grad_ptr(k["wd"]) + 4 * j, P) for j in range(P)]
-            bwd.append(self._reduce(self.chan_part, M * self.tiles_b * self.rg, (4 + P) * H, segs))
-            bwd.append(self._reduce(self.scal_part, M * self.tiles_b, 4, [(2, 1, 1, self.grad_ptr(k["a2"]), 1)]))
+            bwd.append(self._reduce(self.chan_part, M * self.bd_rows[xb], (4 + P) * H, segs))
+            bwd.append(self._reduce(self.scal_part, M * self.bd_ctas[xb], 4, [(2, 1, 1, self.grad_ptr(k["a2"]), 1)]))
             bwd.append(self._reduce(self.alpha_part, M * self.tiles_pn, 1, [(0, 1, 1, self.grad_ptr(k["a1"]), 1)]))
             bwd += self._wgrad(self.hl_H, self.x_hl[i], H, B, k["w1"])                   # dW1 = da^T x
             bwd.append(self._gemm(Cin=H, Cout=B, a_hi=self.hl_H[0], a_lo=self.hl_H[1], w_hi=pb["w1t"][0],

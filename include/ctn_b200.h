@@ -205,13 +205,15 @@ typedef struct ctn_bwd_dw_args {
     const void* bstat;     /* (sum g2*du, sum g2*du*qh) partials from the dgrad epilogue   */
     const float *g1, *b1, *g2, *wd, *slope1, *slope2;
     float* dn1;            /* out: d loss / d n1, fp32 [M*K, H]                            */
-    float* chan_part;      /* out: [M*tiles*row_groups][(4+P)*H]: dg2, db2, dg1, db1, dwd[j] */
-    float* scal_part;      /* out: [M*tiles][4]: sum g1*dn1, sum g1*dn1*ph, d slope2, 0     */
+    float* chan_part;      /* out: [M*chan_rows][(4+P)*H]: dg2, db2, dg1, db1, dwd[j]      */
+    float* scal_part;      /* out: [M*ctas][4]: sum g1*dn1, sum g1*dn1*ph, d slope2, 0     */
 } ctn_bwd_dw_args;
 
 /* gLN-2 backward + PReLU-2 backward + depthwise backward (input and weight grads) +
  * gLN-1 parameter grads, one pass (gLN models). */
-int ctn_bwd_dw_layout(int K, int H, int* tiles, int* row_groups);
+/* Partial-sum geometry per utterance for this (P, dilation): rows of scal_part (= CTAs) and
+ * rows of chan_part. */
+int ctn_bwd_dw_layout(int K, int H, int P, int dilation, int* ctas, int* chan_rows);
 int ctn_bwd_dwconv(const ctn_bwd_dw_args* args, void* stream);
 
 /* gLN-1 input gradient + PReLU-1 backward: da (hi, lo) [M*K, H] and per-CTA d slope1 partials

@@ -21,7 +21,7 @@ def _stat(t):
     return torch.stack([s, ss], -1).view(-1, 1, 2).float().contiguous()
 
 
-@pytest.mark.parametrize("H,K,M", [(3, 5, 2), (5, 37, 1), (16, 24, 2), (512, 700, 2)])
+@pytest.mark.parametrize("H,K,M", [(3, 5, 2), (5, 37, 1), (16, 24, 2), (136, 333, 2), (512, 700, 2)])
 @pytest.mark.parametrize("dil", [1, 2, 4, 128])
 @pytest.mark.parametrize("causal", [False, True])
 def test_block_backward_chain(H, K, M, dil, causal):
@@ -54,11 +54,11 @@ def test_block_backward_chain(H, K, M, dil, causal):
     bstat = torch.stack([gd.sum(dim=(1, 2)), (gd * qh).sum(dim=(1, 2))], -1).view(M, 1, 2).float().contiguous()
     stat1, stat2 = _stat(pa.detach()), _stat(q.detach())
     a_r, d_r, du_r = rows(a), rows(d), rows(du)
-    tiles, rg = C.c_int(), C.c_int()
-    lib.ctn_bwd_dw_layout(K, H, C.byref(tiles), C.byref(rg))
-    tiles, rg = tiles.value, rg.value
+    tiles, rows = C.c_int(), C.c_int()
+    lib.ctn_bwd_dw_layout(K, H, P, dil, C.byref(tiles), C.byref(rows))
+    tiles, rows = tiles.value, rows.value
     dn1 = torch.full((M * K, H), float("nan"), device=DEV)
-    chan = torch.full((M * tiles * rg, (4 + P) * H), float("nan"), device=DEV)
+    chan = torch.full((M * rows, (4 + P) * H), float("nan"), device=DEV)
     scal = torch.full((M * tiles, 4), float("nan"), device=DEV)
     prm = [f(t).view(-1) for t in (g1, b1, g2)]
     wd_f, a1_f, a2_f = f(wd).view(H, P), f(a1), f(a2)
