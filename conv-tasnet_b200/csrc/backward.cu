@@ -378,9 +378,9 @@ __global__ void __launch_bounds__(kBwThreads) bwd_prelu_norm_kernel(const BwdPnP
 // ---------------------------------------------------------------------------------------
 constexpr int kMaxSeg = 12;
 struct ReduceParams {
-    const float* part;
-    int n_part;
-    long long part_stride;
+    const float* part[kMaxSeg];
+    int n_part[kMaxSeg];
+    long long part_stride[kMaxSeg];
     int nseg;
     int accumulate;
     long long src_off[kMaxSeg];
@@ -394,16 +394,18 @@ __global__ void reduce_partials_kernel(const ReduceParams p) {
     const int seg = blockIdx.y;
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= p.len[seg]) return;
-    const float* src = p.part + p.src_off[seg] + static_cast<long long>(i) * p.src_stride[seg];
+    const float* src = p.part[seg] + p.src_off[seg] + static_cast<long long>(i) * p.src_stride[seg];
+    const int n_part = p.n_part[seg];
+    const long long ps = p.part_stride[seg];
     float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
     int q = 0;
-    for (; q + 4 <= p.n_part; q += 4) {
-        s0 += src[(q + 0) * p.part_stride];
-        s1 += src[(q + 1) * p.part_stride];
-        s2 += src[(q + 2) * p.part_stride];
-        s3 += src[(q + 3) * p.part_stride];
+    for (; q + 4 <= n_part; q += 4) {
+        s0 += src[(q + 0) * ps];
+        s1 += src[(q + 1) * ps];
+        s2 += src[(q + 2) * ps];
+        s3 += src[(q + 3) * ps];
     }
-    for (; q < p.n_part; ++q) s0 += src[q * p.part_stride];
+    for (; q < n_part; ++q) s0 += src[q * ps];
     const float s = (s0 + s1) + (s2 + s3);
     float* d = p.dst[seg] + static_cast<long long>(i) * p.dst_stride[seg];
     *d = p.accumulate ? *d + s : s;
@@ -706,12 +708,16 @@ extern "C" int ctn_bwd_prelu_norm(const float* dn1, const float* a, const void* 
 extern "C" int ctn_reduce_partials(const ctn_reduce_args* args, void* stream) {
     CTN_REQUIRE(args != nullptr, "ctn_reduce_partials: args is NULL");
     const ctn_reduce_args& a = *args;
-    CTN_REQUIRE(a.part && a.n_part > 0 && a.nseg > 0 && a.nseg <= kMaxSeg, "ctn_reduce_partials: bad arguments");
+    CTN_REQUIRE(a.nseg > 0 && a.nseg <= kMaxSeg, "ctn_reduce_partials: bad arguments");
     ReduceParams p;
-    p.part = a.part, p.n_part = a.n_part, p.part_stride = a.part_stride, p.nseg = a.nseg, p.accumulate = a.accumulate;
+    p.nseg = a.nseg, p.accumulate = a.accumulate;
     int maxlen = 0;
     for (int s = 0; s < a.nseg; ++s) {
         CTN_REQUIRE(a.dst[s] != nullptr && a.len[s] > 0, "ctn_reduce_partials: bad segment %d", s);
+        p.part[s] = a.seg_part[s] ? a.seg_part[s] : a.part;
+        p.n_part[s] = a.seg_part[s] ? a.seg_n_part[s] : a.n_part;
+        p.part_stride[s] = a.seg_part[s] ? a.seg_part_stride[s] : a.part_stride;
+        CTN_REQUIRE(p.part[s] != nullptr && p.n_part[s] > 0, "ctn_reduce_partials: segment %d has no partials", s);
         p.src_off[s] = a.src_off[s], p.len[s] = a.len[s], p.src_stride[s] = a.src_stride[s] ? a.src_stride[s] : 1;
         p.dst[s] = a.dst[s], p.dst_stride[s] = a.dst_stride[s] ? a.dst_stride[s] : 1;
         maxlen = a.len[s] > maxlen ? a.len[s] : maxlen;

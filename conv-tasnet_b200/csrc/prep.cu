@@ -34,7 +34,48 @@ __global__ void weight_prep_kernel(const float* __restrict__ W, int rows, int co
     }
 }
 
+// One launch for a whole table of weights (blockIdx.y = table entry): a training step refreshes
+// 132 prepared weights, which as separate launches cost 1 ms of a 12 ms step.
+__global__ void weight_prep_batch_kernel(const ctn_prep_item* __restrict__ items) {
+    const ctn_prep_item it = items[blockIdx.y];
+    const int r = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    const int lane = threadIdx.x & 31;
+    if (r >= it.rows) return;
+    __nv_bfloat16* w_hi = static_cast<__nv_bfloat16*>(it.w_hi);
+    __nv_bfloat16* w_lo = static_cast<__nv_bfloat16*>(it.w_lo);
+    float sg = 0.f, sb = 0.f;
+    for (int c = lane; c < it.cols; c += 32) {
+        const float w = it.W[static_cast<long long>(r) * it.cols + c];
+        const float wg = it.gamma ? w * it.gamma[c] : w;
+        __nv_bfloat16 h, l;
+        split_bf16(wg, h, l);
+        const long long o = it.transpose ? static_cast<long long>(c) * it.rows + r
+                                         : static_cast<long long>(r) * it.cols + c;
+        w_hi[o] = h;
+        w_lo[o] = l;
+        sg += __bfloat162float(h) + __bfloat162float(l);
+        if (it.beta) sb = fmaf(w, it.beta[c], sb);
+    }
+    sg = warp_sum(sg);
+    sb = warp_sum(sb);
+    if (lane == 0) {
+        if (it.col_g) it.col_g[r] = sg;
+        if (it.col_bias) it.col_bias[r] = sb;
+    }
+}
+
 }  // namespace ctn
+
+extern "C" int ctn_weight_prep_batch(const ctn_prep_item* items_dev, int n_items, int max_rows, void* stream) {
+    using namespace ctn;
+    CTN_REQUIRE(items_dev != nullptr && n_items > 0 && n_items <= 65535 && max_rows > 0,
+                "ctn_weight_prep_batch: bad arguments");
+    const int warps = 8;
+    dim3 grid(ceil_div(max_rows, warps), n_items);
+    weight_prep_batch_kernel<<<grid, warps * 32, 0, static_cast<cudaStream_t>(stream)>>>(items_dev);
+    CTN_LAUNCH_CHECK("weight_prep_batch_kernel");
+    return CTN_OK;
+}
 
 extern "C" int ctn_weight_prep(const float* W, int rows, int cols, const float* gamma, const float* beta,
                                int transpose, void* w_hi, void* w_lo, float* col_g, float* col_bias, void* stream) {

@@ -29,24 +29,24 @@ class _PreparedBwd:
                             w2t=(torch.empty(H, B, **bf), torch.empty(H, B, **bf)))
                        for _ in range(cfg["R"] * cfg["X"])]
         self.mask_t = (torch.empty(B, C_ * N, **bf), torch.empty(B, C_ * N, **bf))
+        self.table = self.table_ptrs = None
 
     def refresh(self, cfg, params):
-        lib, s = nat.lib(), nat.stream()
-        N, B, H, C_ = cfg["N"], cfg["B"], cfg["H"], cfg["C"]
-
-        def prep_t(W, rows, cols, out):
-            nat.check(lib.ctn_weight_prep(W.data_ptr(), rows, cols, None, None, 1, out[0].data_ptr(),
-                                          out[1].data_ptr(), None, None, s))
-
-        prep_t(params["separator.network.1.weight"], B, N, self.bott_t)
-        i = 0
-        for r in range(cfg["R"]):
-            for x in range(cfg["X"]):
-                k = block_keys(r, x, cfg["causal"])
-                prep_t(params[k["w1"]], H, B, self.blocks[i]["w1t"])
-                prep_t(params[k["w2"]], B, H, self.blocks[i]["w2t"])
-                i += 1
-        prep_t(params["separator.network.3.weight"], C_ * N, B, self.mask_t)
+        ptrs = tuple(p.data_ptr() for p in params.values())
+        if self.table is None or self.table_ptrs != ptrs:
+            N, B, H, C_ = cfg["N"], cfg["B"], cfg["H"], cfg["C"]
+            t = nat.PrepTable(self.bott_t[0].device)
+            t.add(params["separator.network.1.weight"], B, N, None, None, 1, self.bott_t)
+            i = 0
+            for r in range(cfg["R"]):
+                for x in range(cfg["X"]):
+                    k = block_keys(r, x, cfg["causal"])
+                    t.add(params[k["w1"]], H, B, None, None, 1, self.blocks[i]["w1t"])
+                    t.add(params[k["w2"]], B, H, None, None, 1, self.blocks[i]["w2t"])
+                    i += 1
+            t.add(params["separator.network.3.weight"], C_ * N, B, None, None, 1, self.mask_t)
+            self.table, self.table_ptrs = t, ptrs
+        self.table.run()
 
 
 class TrainPlan:
@@ -112,6 +112,7 @@ class TrainPlan:
         self.dU_part = e(M * self.tiles_ew, N * L, **f32)
         shapes = [(C_ * N, B), (B, H), (H, B), (B, N)]
         self.wg_part = e(max(lib.ctn_wgrad_splits(Rr, i, j) * i * j for i, j in shapes), **f32)
+        self.wg_part2 = e(lib.ctn_wgrad_splits(Rr, H, B) * H * B, **f32)
         # flat gradient buffer in state_dict order
         self.spec = param_spec(N, L, B, H, cfg["P"], cfg["X"], cfg["R"], C_, cfg["causal"])
         self.offsets, off = {}, 0
@@ -126,6 +127,11 @@ class TrainPlan:
         self.param_ptrs = None
         self._keep = []
         self.generation = 0
+        # static endpoints so that each direction is ONE CUDA-graph launch (at the reference's batch
+        # size of 3 the ~500 kernels of a step are latency-, not throughput-bound)
+        self.est = e(M, C_, T, **f32)
+        self.g_est = e(M, C_, T, **f32)
+        self.fwd_graph = self.bwd_graph = None
 
     # ------------------------------------------------------------------ helpers
     def grad_ptr(self, key):
@@ -144,25 +150,32 @@ class TrainPlan:
         return lambda s: fn(ref, s)
 
     def _reduce(self, part, n_part, part_stride, segs, accumulate=0):
-        """segs: list of (src_off, len, src_stride, dst_ptr, dst_stride)"""
+        """segs: list of (src_off, len, src_stride, dst_ptr, dst_stride) over ONE partial buffer"""
+        return self._reduce_multi([(part, n_part, part_stride) + tuple(sg) for sg in segs], accumulate)
+
+    def _reduce_multi(self, segs, accumulate=0):
+        """ONE launch summing the partials of several kernels.
+        segs: list of (part tensor, n_part, part_stride, src_off, len, src_stride, dst_ptr, dst_stride)"""
         r = nat.ReduceArgs()
-        r.part, r.n_part, r.part_stride, r.nseg, r.accumulate = part.data_ptr(), n_part, part_stride, len(segs), accumulate
-        for i, (so, ln, ss, dp, ds) in enumerate(segs):
+        r.nseg, r.accumulate = len(segs), accumulate
+        for i, (part, n_part, ps, so, ln, ss, dp, ds) in enumerate(segs):
+            r.seg_part[i], r.seg_n_part[i], r.seg_part_stride[i] = part.data_ptr(), n_part, ps
             r.src_off[i], r.len[i], r.src_stride[i], r.dst[i], r.dst_stride[i] = so, ln, ss, dp, ds
         self._keep.append(r)
         fn, ref = nat.lib().ctn_reduce_partials, C.byref(r)
         return lambda s: fn(ref, s)
 
-    def _wgrad(self, x_hl, y_hl, Ci, Cj, dst_key):
-        """G = x^T y over all rows -> grad of `dst_key` ([Ci, Cj] row-major)."""
+    def _wgrad(self, x_hl, y_hl, Ci, Cj, dst_key, part=None):
+        """G = x^T y over all rows -> grad of `dst_key` ([Ci, Cj] row-major).
+        Returns (launch, reduce segment); the segment is summed by a later _reduce_multi."""
         lib = nat.lib()
+        part = self.wg_part if part is None else part
         Rr = self.M * self.K
         S = lib.ctn_wgrad_splits(Rr, Ci, Cj)
         a = (x_hl[0].data_ptr(), x_hl[1].data_ptr(), y_hl[0].data_ptr(), y_hl[1].data_ptr(), Rr, Ci, Cj,
-             self.wg_part.data_ptr(), 0)
+             part.data_ptr(), 0)
         fn = lib.ctn_wgrad
-        return [lambda s, a=a: fn(*a, s),
-                self._reduce(self.wg_part, S, Ci * Cj, [(0, Ci * Cj, 1, self.grad_ptr(dst_key), 1)])]
+        return (lambda s, a=a: fn(*a, s)), (part, S, Ci * Cj, 0, Ci * Cj, 1, self.grad_ptr(dst_key), 1)
 
     # ------------------------------------------------------------- call lists
     def build(self, params, prep, prep_b):
@@ -226,9 +239,11 @@ class TrainPlan:
         self.dec_bwd_args = (self.score.data_ptr(), self.w.data_ptr(), V.data_ptr(), M, K, N, L, C_, T,
                              _MASK[cfg["mask_nonlinear"]], self.ds_hl[0].data_ptr(), self.ds_hl[1].data_ptr(),
                              self.dw_dec.data_ptr(), self.dV_part.data_ptr())
-        bwd.append(self._reduce(self.dV_part, M * self.tiles_db, L * N,
-                                [(0, L * N, 1, self.grad_ptr("decoder.basis_signals.weight"), 1)]))
-        bwd += self._wgrad(self.ds_hl, self.x_hl[NB], C_ * N, B, "separator.network.3.weight")
+        call, seg_mask = self._wgrad(self.ds_hl, self.x_hl[NB], C_ * N, B, "separator.network.3.weight")
+        bwd.append(call)
+        bwd.append(self._reduce_multi([
+            (self.dV_part, M * self.tiles_db, L * N, 0, L * N, 1, self.grad_ptr("decoder.basis_signals.weight"), 1),
+            seg_mask]))
         bwd.append(self._gemm(Cin=C_ * N, Cout=B, a_hi=self.ds_hl[0], a_lo=self.ds_hl[1], w_hi=prep_b.mask_t[0],
                               w_lo=prep_b.mask_t[1], out_f32=self.g, out_hi=self.g_hl[0], out_lo=self.g_hl[1]))
         ns, bd, pn = lib.ctn_norm_split, lib.ctn_bwd_dwconv, lib.ctn_bwd_prelu_norm
@@ -239,7 +254,8 @@ class TrainPlan:
                   params[k["b2"]].data_ptr(), GLN, self.stat2[i].data_ptr(), P2, M, K, H,
                   self.hl_H[0].data_ptr(), self.hl_H[1].data_ptr())
             bwd.append(lambda s, a=a_: ns(*a, s))                                       # u (hi, lo)
-            bwd += self._wgrad(self.g_hl, self.hl_H, B, H, k["w2"])                      # dW2 = g^T u
+            call, seg_w2 = self._wgrad(self.g_hl, self.hl_H, B, H, k["w2"])              # dW2 = g^T u
+            bwd.append(call)
             bwd.append(self._gemm(Cin=B, Cout=H, a_hi=self.g_hl[0], a_lo=self.g_hl[1], w_hi=pb["w2t"][0],
                                   w_lo=pb["w2t"][1], out_f32=self.du, out_stat=GLN, out_stat_buf=self.bstat,
                                   bw_pre=self.d[i], bw_gamma=params[k["g2"]], bw_slope=params[k["a2"]],
@@ -258,13 +274,21 @@ class TrainPlan:
                   self.scal_part.data_ptr(), self.bd_ctas[xb], params[k["g1"]].data_ptr(), params[k["a1"]].data_ptr(),
                   M, K, H, self.hl_H[0].data_ptr(), self.hl_H[1].data_ptr(), self.alpha_part.data_ptr())
             bwd.append(lambda s, a=a_: pn(*a, s))                                       # da (hi, lo)
-            segs = [(0, H, 1, self.grad_ptr(k["g2"]), 1), (H, H, 1, self.grad_ptr(k["b2"]), 1),
-                    (2 * H, H, 1, self.grad_ptr(k["g1"]), 1), (3 * H, H, 1, self.grad_ptr(k["b1"]), 1)]
-            segs += [((4 + j) * H, H, 1, self.grad_ptr(k["wd"]) + 4 * j, P) for j in range(P)]
-            bwd.append(self._reduce(self.chan_part, M * self.bd_rows[xb], (4 + P) * H, segs))
-            bwd.append(self._reduce(self.scal_part, M * self.bd_ctas[xb], 4, [(2, 1, 1, self.grad_ptr(k["a2"]), 1)]))
-            bwd.append(self._reduce(self.alpha_part, M * self.tiles_pn, 1, [(0, 1, 1, self.grad_ptr(k["a1"]), 1)]))
-            bwd += self._wgrad(self.hl_H, self.x_hl[i], H, B, k["w1"])                   # dW1 = da^T x
+            call, seg_w1 = self._wgrad(self.hl_H, self.x_hl[i], H, B, k["w1"], self.wg_part2)   # dW1 = da^T x
+            bwd.append(call)
+            # every parameter gradient of the block in ONE reduction launch
+            cp, cn, cs = self.chan_part, M * self.bd_rows[xb], (4 + P) * H
+            segs = [(cp, cn, cs, 0, H, 1, self.grad_ptr(k["g2"]), 1), (cp, cn, cs, H, H, 1, self.grad_ptr(k["b2"]), 1),
+                    (cp, cn, cs, 2 * H, H, 1, self.grad_ptr(k["g1"]), 1),
+                    (cp, cn, cs, 3 * H, H, 1, self.grad_ptr(k["b1"]), 1)]
+            segs += [(cp, cn, cs, (4 + j) * H, H, 1, self.grad_ptr(k["wd"]) + 4 * j, P) for j in range(P)]
+            segs.append((self.scal_part, M * self.bd_ctas[xb], 4, 2, 1, 1, self.grad_ptr(k["a2"]), 1))
+            segs.append((self.alpha_part, M * self.tiles_pn, 1, 0, 1, 1, self.grad_ptr(k["a1"]), 1))
+            if len(segs) + 2 <= nat.MAX_SEG:
+                bwd.append(self._reduce_multi(segs + [seg_w2, seg_w1]))
+            else:                                   # P > 3
+                bwd.append(self._reduce_multi(segs[:nat.MAX_SEG]))
+                bwd.append(self._reduce_multi(segs[nat.MAX_SEG:] + [seg_w2, seg_w1]))
             bwd.append(self._gemm(Cin=H, Cout=B, a_hi=self.hl_H[0], a_lo=self.hl_H[1], w_hi=pb["w1t"][0],
                                   w_lo=pb["w1t"][1], resid=self.g, out_f32=self.g, out_hi=self.g_hl[0],
                                   out_lo=self.g_hl[1]))                                   # g = da W1 + g
@@ -272,36 +296,65 @@ class TrainPlan:
         a_ = (self.w.data_ptr(), None, g0.data_ptr(), b0.data_ptr(), nat.NORM_CLN, self.rowstat0.data_ptr(), 1,
               M, K, N, self.w_hl[0].data_ptr(), self.w_hl[1].data_ptr())
         bwd.append(lambda s, a=a_: ns(*a, s))                                           # n0 (hi, lo) over w_hl
-        bwd += self._wgrad(self.g_hl, self.w_hl, B, N, "separator.network.1.weight")
+        call, seg_wb = self._wgrad(self.g_hl, self.w_hl, B, N, "separator.network.1.weight")
+        bwd.append(call)
         bwd.append(self._gemm(Cin=B, Cout=N, a_hi=self.g_hl[0], a_lo=self.g_hl[1], w_hi=prep_b.bott_t[0],
                               w_lo=prep_b.bott_t[1], out_f32=self.dn0))
         cb = lib.ctn_cln_bwd
         a_ = (self.dn0.data_ptr(), self.w.data_ptr(), self.rowstat0.data_ptr(), g0.data_ptr(),
               self.dw_dec.data_ptr(), M, K, N, self.dpre.data_ptr(), self.cb_part.data_ptr())
         bwd.append(lambda s, a=a_: cb(*a, s))
-        bwd.append(self._reduce(self.cb_part, M * self.tiles_cb, 2 * N,
-                                [(0, N, 1, self.grad_ptr("separator.network.0.gamma"), 1),
-                                 (N, N, 1, self.grad_ptr("separator.network.0.beta"), 1)]))
         ew = lib.ctn_encoder_wgrad
         a_ = (self.dpre.data_ptr(), self.mix.data_ptr(), M, T, N, L, self.dU_part.data_ptr())
         bwd.append(lambda s, a=a_: ew(*a, s))
-        bwd.append(self._reduce(self.dU_part, M * self.tiles_ew, N * L,
-                                [(0, N * L, 1, self.grad_ptr("encoder.conv1d_U.weight"), 1)]))
+        ncb = M * self.tiles_cb
+        bwd.append(self._reduce_multi([
+            seg_wb,
+            (self.cb_part, ncb, 2 * N, 0, N, 1, self.grad_ptr("separator.network.0.gamma"), 1),
+            (self.cb_part, ncb, 2 * N, N, N, 1, self.grad_ptr("separator.network.0.beta"), 1),
+            (self.dU_part, M * self.tiles_ew, N * L, 0, N * L, 1, self.grad_ptr("encoder.conv1d_U.weight"), 1)]))
         self.bwd_calls = bwd
         self.param_ptrs = tuple(p.data_ptr() for p in params.values())
+        self.fwd_graph = self.bwd_graph = None     # captured pointers may have changed
 
-    def run_forward(self, est):
+    def _launch_forward(self):
         s, check, lib = nat.stream(), nat.check, nat.lib()
         for c in self.fwd_calls:
             check(c(s))
-        check(lib.ctn_decoder_fwd(*self.dec_args, est.data_ptr(), s))
-        return len(self.fwd_calls) + 1
+        check(lib.ctn_decoder_fwd(*self.dec_args, self.est.data_ptr(), s))
 
-    def run_backward(self, g_est):
+    def _launch_backward(self):
         s, check, lib = nat.stream(), nat.check, nat.lib()
-        check(lib.ctn_decoder_bwd(g_est.data_ptr(), *self.dec_bwd_args, s))
+        check(lib.ctn_decoder_bwd(self.g_est.data_ptr(), *self.dec_bwd_args, s))
         for c in self.bwd_calls:
             check(c(s))
+
+    def _capture(self, launch):
+        launch()                                   # warm-up outside capture (attribute setup, lazy loading)
+        torch.cuda.synchronize(self.device)
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g, capture_error_mode="thread_local"):
+            launch()
+        return g
+
+    def run_forward(self, use_graph):
+        """mix -> est (static buffers).  Returns the number of kernels launched."""
+        if not use_graph:
+            self._launch_forward()
+        else:
+            if self.fwd_graph is None:
+                self.fwd_graph = self._capture(self._launch_forward)
+            self.fwd_graph.replay()
+        return len(self.fwd_calls) + 1
+
+    def run_backward(self, use_graph):
+        """g_est -> flat_grad (static buffers)."""
+        if not use_graph:
+            self._launch_backward()
+        else:
+            if self.bwd_graph is None:
+                self.bwd_graph = self._capture(self._launch_backward)
+            self.bwd_graph.replay()
         return len(self.bwd_calls) + 1
 
 
@@ -315,6 +368,7 @@ class TrainEngine:
         # data parallelism (ctn_b200/_dist.py): when set, every backward scales the flat gradient by
         # n_local / n_global and all-reduces (sum) it over this torch.distributed group, which equals
         # the gradient of the reference's global-mean loss
+        self.use_graph = True
         self.process_group = None
         self.global_batch = None       # utterances per step over all ranks (None = equal shards)
         self.last_flat_grad = None
@@ -349,8 +403,8 @@ class _Separate(torch.autograd.Function):
         with torch.cuda.device(dev):
             plan = eng.plan(params, M, T, dev)
             plan.mix.copy_(mixture)
-            est = torch.empty(M, model.C, T, dtype=torch.float32, device=dev)
-            eng.launches += plan.run_forward(est)
+            eng.launches += plan.run_forward(eng.use_graph)
+            est = plan.est.clone()
         plan.generation += 1
         ctx.plan, ctx.generation, ctx.engine = plan, plan.generation, eng
         ctx.n_params = len(param_list)
@@ -364,7 +418,8 @@ class _Separate(torch.autograd.Function):
                                "backward: the saved activations of this graph were overwritten")
         eng = ctx.engine
         with torch.cuda.device(plan.device):
-            eng.launches += plan.run_backward(g_est.contiguous())
+            plan.g_est.copy_(g_est)
+            eng.launches += plan.run_backward(eng.use_graph)
             # one private copy per backward: autograd may adopt the returned views as .grad
             flat = plan.flat_grad.clone()
             if eng.process_group is not None:

@@ -52,30 +52,28 @@ class _Prepared:
                 w2=(torch.empty(B, H, **bf), torch.empty(B, H, **bf), torch.empty(B, **f32), torch.empty(B, **f32))))
         self.mask = (torch.empty(C * N, B, **bf), torch.empty(C * N, B, **bf))
         self.fingerprint = None
+        self.table = self.table_ptrs = None
 
     def refresh(self, cfg, params):
         fp = tuple((p.data_ptr(), p._version) for p in params.values())
         if fp == self.fingerprint:
             return
-        lib, s = nat.lib(), nat.stream()
-        N, B, H, C = cfg["N"], cfg["B"], cfg["H"], cfg["C"]
-
-        def prep(W, rows, cols, gamma, beta, out):
-            nat.check(lib.ctn_weight_prep(nat.ptr(W), rows, cols, nat.ptr(gamma), nat.ptr(beta), 0,
-                                          nat.ptr(out[0]), nat.ptr(out[1]),
-                                          nat.ptr(out[2]) if len(out) > 2 else None,
-                                          nat.ptr(out[3]) if len(out) > 3 else None, s))
-
-        prep(params["separator.network.1.weight"], B, N, params["separator.network.0.gamma"],
-             params["separator.network.0.beta"], self.bott)
-        i = 0
-        for r in range(cfg["R"]):
-            for x in range(cfg["X"]):
-                k = block_keys(r, x, cfg["causal"])
-                prep(params[k["w1"]], H, B, None, None, self.blocks[i]["w1"])
-                prep(params[k["w2"]], B, H, params[k["g2"]], params[k["b2"]], self.blocks[i]["w2"])
-                i += 1
-        prep(params["separator.network.3.weight"], C * N, B, None, None, self.mask)
+        ptrs = tuple(p.data_ptr() for p in params.values())
+        if self.table is None or self.table_ptrs != ptrs:
+            N, B, H, C = cfg["N"], cfg["B"], cfg["H"], cfg["C"]
+            t = nat.PrepTable(self.bott[0].device)
+            t.add(params["separator.network.1.weight"], B, N, params["separator.network.0.gamma"],
+                  params["separator.network.0.beta"], 0, self.bott)
+            i = 0
+            for r in range(cfg["R"]):
+                for x in range(cfg["X"]):
+                    k = block_keys(r, x, cfg["causal"])
+                    t.add(params[k["w1"]], H, B, None, None, 0, self.blocks[i]["w1"])
+                    t.add(params[k["w2"]], B, H, params[k["g2"]], params[k["b2"]], 0, self.blocks[i]["w2"])
+                    i += 1
+            t.add(params["separator.network.3.weight"], C * N, B, None, None, 0, self.mask)
+            self.table, self.table_ptrs = t, ptrs
+        self.table.run()
         self.fingerprint = fp
 
 

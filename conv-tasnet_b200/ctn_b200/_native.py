@@ -55,6 +55,36 @@ class BwdDwArgs(C.Structure):
     ]
 
 
+class PrepItem(C.Structure):
+    """struct ctn_prep_item"""
+    _fields_ = [("W", _vp), ("gamma", _vp), ("beta", _vp), ("w_hi", _vp), ("w_lo", _vp), ("col_g", _vp),
+                ("col_bias", _vp), ("rows", C.c_int), ("cols", C.c_int), ("transpose", C.c_int),
+                ("reserved", C.c_int)]
+
+
+class PrepTable:
+    """Device-resident table of ctn_prep_item for ctn_weight_prep_batch (one launch per refresh)."""
+
+    def __init__(self, device):
+        self.device, self.items, self.dev, self.max_rows = device, [], None, 0
+
+    def add(self, W, rows, cols, gamma, beta, transpose, out):
+        it = PrepItem()
+        it.W, it.gamma, it.beta = W.data_ptr(), ptr(gamma), ptr(beta)
+        it.w_hi, it.w_lo = out[0].data_ptr(), out[1].data_ptr()
+        it.col_g = out[2].data_ptr() if len(out) > 2 else None
+        it.col_bias = out[3].data_ptr() if len(out) > 3 else None
+        it.rows, it.cols, it.transpose = rows, cols, int(transpose)
+        self.items.append(it)
+        self.max_rows = max(self.max_rows, rows)
+
+    def run(self):
+        if self.dev is None:
+            arr = (PrepItem * len(self.items))(*self.items)
+            self.dev = torch.frombuffer(bytearray(bytes(arr)), dtype=torch.uint8).to(self.device)
+        check(lib().ctn_weight_prep_batch(self.dev.data_ptr(), len(self.items), self.max_rows, stream()))
+
+
 MAX_SEG = 12
 
 
@@ -65,6 +95,7 @@ class ReduceArgs(C.Structure):
         ("accumulate", C.c_int),
         ("src_off", C.c_longlong * MAX_SEG), ("len", C.c_int * MAX_SEG), ("src_stride", C.c_int * MAX_SEG),
         ("dst", _vp * MAX_SEG), ("dst_stride", C.c_int * MAX_SEG),
+        ("seg_part", _vp * MAX_SEG), ("seg_n_part", C.c_int * MAX_SEG), ("seg_part_stride", C.c_longlong * MAX_SEG),
     ]
 
 
@@ -76,6 +107,7 @@ _SIGNATURES = {
     "ctn_gemm_gln_partials": (C.c_int, [C.c_int, C.c_int]),
     "ctn_dwconv_gln_partials": (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_int]),
     "ctn_gemm_cln_groups": (C.c_int, [C.c_int]),
+    "ctn_weight_prep_batch": (C.c_int, [_vp, C.c_int, C.c_int, _vp]),
     "ctn_weight_prep": (C.c_int, [_vp, C.c_int, C.c_int, _vp, _vp, C.c_int, _vp, _vp, _vp, _vp, _vp]),
     "ctn_encoder_fwd": (C.c_int, [_vp, _vp, C.c_int, C.c_int, C.c_int, C.c_int, _vp, _vp, _vp, _vp, _vp]),
     "ctn_gemm1x1": (C.c_int, [C.POINTER(GemmArgs), _vp]),

@@ -68,6 +68,20 @@ int ctn_gemm_cln_groups(int Cout);
 int ctn_weight_prep(const float* W, int rows, int cols, const float* gamma, const float* beta, int transpose,
                     void* w_hi, void* w_lo, float* col_g, float* col_bias, void* stream);
 
+/* The same for a table of weights in ONE launch.  `items_dev` is a DEVICE array of n_items
+ * entries (field meaning as the arguments of ctn_weight_prep); max_rows = largest `rows`. */
+typedef struct ctn_prep_item {
+    const float* W;
+    const float* gamma;
+    const float* beta;
+    void* w_hi;
+    void* w_lo;
+    float* col_g;
+    float* col_bias;
+    int rows, cols, transpose, reserved;
+} ctn_prep_item;
+int ctn_weight_prep_batch(const ctn_prep_item* items_dev, int n_items, int max_rows, void* stream);
+
 /* Encoder (conv_tasnet.py:97-117): w = relu(Conv1d(1,N,L,stride L/2)(mixture)).
  * mixture [M,T] fp32 -> w_f32 [M*K, N], (w_hi, w_lo) bf16 [M*K, N] and the
  * per-frame statistics of the leading cLN (conv_tasnet.py:167,326-327):
@@ -235,6 +249,11 @@ typedef struct ctn_reduce_args {
     int src_stride[CTN_MAX_SEG]; /* 0 -> 1 */
     float* dst[CTN_MAX_SEG];
     int dst_stride[CTN_MAX_SEG]; /* 0 -> 1 */
+    /* optional per-segment partial buffers (NULL -> part / n_part / part_stride above), so that the
+     * partials of several kernels are reduced by ONE launch */
+    const float* seg_part[CTN_MAX_SEG];
+    int seg_n_part[CTN_MAX_SEG];
+    long long seg_part_stride[CTN_MAX_SEG];
 } ctn_reduce_args;
 
 /* dst[seg][i*dst_stride] (+)= sum_p part[p*part_stride + src_off[seg] + i*src_stride]; fixed order. */
