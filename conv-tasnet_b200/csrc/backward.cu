@@ -390,25 +390,42 @@ struct ReduceParams {
     int dst_stride[kMaxSeg];
 };
 
-__global__ void reduce_partials_kernel(const ReduceParams p) {
+// 32 outputs x 8 partial slices per CTA: thread (slice, col) sums the partials p = slice, slice + 8, ...
+// (4 independent chains), then the 8 slices are added in a fixed order.  The one-thread-per-output
+// loop this replaces walked up to 2000 partial rows serially.
+constexpr int kRedCols = 32, kRedSlices = 8;
+__global__ void __launch_bounds__(kRedCols * kRedSlices) reduce_partials_kernel(const ReduceParams p) {
+    __shared__ float red[kRedSlices][kRedCols];
     const int seg = blockIdx.y;
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= p.len[seg]) return;
-    const float* src = p.part[seg] + p.src_off[seg] + static_cast<long long>(i) * p.src_stride[seg];
-    const int n_part = p.n_part[seg];
-    const long long ps = p.part_stride[seg];
-    float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
-    int q = 0;
-    for (; q + 4 <= n_part; q += 4) {
-        s0 += src[(q + 0) * ps];
-        s1 += src[(q + 1) * ps];
-        s2 += src[(q + 2) * ps];
-        s3 += src[(q + 3) * ps];
+    const int col = threadIdx.x & (kRedCols - 1), slice = threadIdx.x / kRedCols;
+    const int i = blockIdx.x * kRedCols + col;
+    const int len = p.len[seg];
+    if (blockIdx.x * kRedCols >= len) return;
+    float s = 0.f;
+    if (i < len) {
+        const float* src = p.part[seg] + p.src_off[seg] + static_cast<long long>(i) * p.src_stride[seg];
+        const int n_part = p.n_part[seg];
+        const long long ps = p.part_stride[seg];
+        float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
+        int q = slice;
+        for (; q + 3 * kRedSlices < n_part; q += 4 * kRedSlices) {
+            s0 += src[(q + 0 * kRedSlices) * ps];
+            s1 += src[(q + 1 * kRedSlices) * ps];
+            s2 += src[(q + 2 * kRedSlices) * ps];
+            s3 += src[(q + 3 * kRedSlices) * ps];
+        }
+        for (; q < n_part; q += kRedSlices) s0 += src[q * ps];
+        s = (s0 + s1) + (s2 + s3);
     }
-    for (; q < n_part; ++q) s0 += src[q * ps];
-    const float s = (s0 + s1) + (s2 + s3);
-    float* d = p.dst[seg] + static_cast<long long>(i) * p.dst_stride[seg];
-    *d = p.accumulate ? *d + s : s;
+    red[slice][col] = s;
+    __syncthreads();
+    if (slice == 0 && i < len) {
+        float t = 0.f;
+#pragma unroll
+        for (int k = 0; k < kRedSlices; ++k) t += red[k][col];
+        float* d = p.dst[seg] + static_cast<long long>(i) * p.dst_stride[seg];
+        *d = p.accumulate ? *d + t : t;
+    }
 }
 
 // ---------------------------------------------------------------------------------------
@@ -612,10 +629,10 @@ extern "C" int ctn_norm_split(const float* in, const float* prelu_slope, const f
 
 static bool bwd_use_march(int H, int P) { return P == 3 && H % 4 == 0; }
 
-extern "C" int ctn_bwd_dw_layout(int K, int H, int P, int dilation, int* ctas, int* chan_rows) {
+extern "C" int ctn_bwd_dw_layout(int M, int K, int H, int P, int dilation, int* ctas, int* chan_rows) {
     if (bwd_use_march(H, P) && dilation > 0) {
         int NS, units, groups, n_ctas;
-        bwd_march_geometry(K, H, dilation, &NS, &units, &groups, &n_ctas);
+        bwd_march_geometry(M, K, H, dilation, &NS, &units, &groups, &n_ctas);
         if (ctas) *ctas = n_ctas;
         if (chan_rows) *chan_rows = groups;
         return CTN_OK;
@@ -645,7 +662,8 @@ extern "C" int ctn_bwd_dwconv(const ctn_bwd_dw_args* args, void* stream) {
         BwdMarchParams q;
         q.K = a.K, q.H = a.H, q.dil = a.dilation, q.c0 = a.causal ? 2 : 1;
         q.P1 = a.P1, q.P2 = a.P2, q.Pb = a.Pb;
-        bwd_march_geometry(a.K, a.H, a.dilation, &q.NS, &q.units, &q.groups, &q.ctas);
+        bwd_march_geometry(a.M, a.K, a.H, a.dilation, &q.NS, &q.units, &q.groups, &q.ctas);
+        q.upw = bwd_march_units_per_warp(a.M, q.units, a.H);
         q.chan_rows = q.groups;
         q.du = a.du, q.d = a.d, q.a = a.a;
         q.stat1 = static_cast<const float2*>(a.stat1), q.stat2 = static_cast<const float2*>(a.stat2);
@@ -669,7 +687,7 @@ extern "C" int ctn_bwd_dwconv(const ctn_bwd_dw_args* args, void* stream) {
     p.g1 = a.g1, p.b1 = a.b1, p.g2 = a.g2, p.wd = a.wd, p.slope1 = a.slope1, p.slope2 = a.slope2;
     p.dn1 = a.dn1, p.chan_part = a.chan_part, p.scal_part = a.scal_part;
     int tiles, rows;
-    ctn_bwd_dw_layout(a.K, a.H, a.P, a.dilation, &tiles, &rows);
+    ctn_bwd_dw_layout(a.M, a.K, a.H, a.P, a.dilation, &tiles, &rows);
     p.RG = rows / tiles;
     dim3 grid(tiles, a.M);
     const bool vec = a.H % 4 == 0 && aligned;
@@ -722,8 +740,8 @@ extern "C" int ctn_reduce_partials(const ctn_reduce_args* args, void* stream) {
         p.dst[s] = a.dst[s], p.dst_stride[s] = a.dst_stride[s] ? a.dst_stride[s] : 1;
         maxlen = a.len[s] > maxlen ? a.len[s] : maxlen;
     }
-    dim3 grid(ceil_div(maxlen, 128), a.nseg);
-    reduce_partials_kernel<<<grid, 128, 0, static_cast<cudaStream_t>(stream)>>>(p);
+    dim3 grid(ceil_div(maxlen, kRedCols), a.nseg);
+    reduce_partials_kernel<<<grid, kRedCols * kRedSlices, 0, static_cast<cudaStream_t>(stream)>>>(p);
     CTN_LAUNCH_CHECK("reduce_partials_kernel");
     return CTN_OK;
 }

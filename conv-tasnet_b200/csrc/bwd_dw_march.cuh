@@ -20,11 +20,11 @@
 
 namespace ctn {
 
-constexpr int kBmUnits = 4;   // (phase, 32-frame segment) units a warp accumulates before writing partials
+constexpr int kBmUnits = 4;   // most (phase, 32-frame segment) units a warp accumulates before writing partials
 constexpr int kBmAhead = 4;   // rows loaded ahead of use
 
 struct BwdMarchParams {
-    int K, H, dil, c0, P1, P2, Pb, NS, units, groups, chan_rows, ctas;
+    int K, H, dil, c0, P1, P2, Pb, NS, units, groups, chan_rows, ctas, upw;
     const float* du;
     const float* d;
     const float* a;
@@ -43,11 +43,19 @@ struct BwdMarchParams {
 };
 
 // units per utterance, warp groups (= partial rows) per utterance, CTAs per utterance
-inline void bwd_march_geometry(int K, int H, int dil, int* NS, int* units, int* groups, int* ctas) {
+// units per warp: as many as kBmUnits (fewer partial rows to reduce) while the grid still fills the GPU
+inline int bwd_march_units_per_warp(int M, int units, int H) {
+    const long long warps1 = static_cast<long long>(M) * units * ((H + 127) / 128);   // warps at one unit each
+    const long long want = 2ll * 148 * kDmWarps;
+    long long u = warps1 / want;
+    return u < 1 ? 1 : (u > kBmUnits ? kBmUnits : static_cast<int>(u));
+}
+inline void bwd_march_geometry(int M, int K, int H, int dil, int* NS, int* units, int* groups, int* ctas) {
     const int Jmax = (K + dil - 1) / dil;
     *NS = (Jmax + kDmSeg - 1) / kDmSeg;
     *units = dil * (*NS);
-    *groups = (*units + kBmUnits - 1) / kBmUnits;
+    const int upw = bwd_march_units_per_warp(M, *units, H);
+    *groups = (*units + upw - 1) / upw;
     const int CG = (H + 127) / 128;
     *ctas = ((*groups) * CG + kDmWarps - 1) / kDmWarps;
 }
@@ -124,8 +132,8 @@ bwd_dw_march_kernel(const BwdMarchParams p) {
         }
         const long long ubase = static_cast<long long>(m) * p.K;
         const long long strd = static_cast<long long>(d) * H;
-        for (int uu = 0; uu < kBmUnits; ++uu) {
-            const int unit = grp * kBmUnits + uu;
+        for (int uu = 0; uu < p.upw; ++uu) {
+            const int unit = grp * p.upw + uu;
             if (unit >= p.units) break;
             const int ph = unit % d, seg = unit / d;
             const int J = ph < p.K ? (p.K - ph + d - 1) / d : 0;

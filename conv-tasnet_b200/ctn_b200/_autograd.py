@@ -97,7 +97,7 @@ class TrainPlan:
         self.bd_ctas, self.bd_rows = [], []          # per dilation: scal_part / chan_part rows per utterance
         for x in range(cfg["X"]):
             ctas, rows = C.c_int(), C.c_int()
-            lib.ctn_bwd_dw_layout(K, H, cfg["P"], 2 ** x, C.byref(ctas), C.byref(rows))
+            lib.ctn_bwd_dw_layout(M, K, H, cfg["P"], 2 ** x, C.byref(ctas), C.byref(rows))
             self.bd_ctas.append(ctas.value)
             self.bd_rows.append(rows.value)
         self.chan_part = e(M * max(self.bd_rows), (4 + cfg["P"]) * H, **f32)

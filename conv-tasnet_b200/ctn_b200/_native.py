@@ -118,7 +118,7 @@ _SIGNATURES = {
     "ctn_norm_split": (_i, [_vp, _vp, _vp, _vp, _i, _vp, _i, _i, _i, _i, _vp, _vp, _vp]),
     "ctn_wgrad_splits": (_i, [_ll, _i, _i]),
     "ctn_wgrad": (_i, [_vp, _vp, _vp, _vp, _ll, _i, _i, _vp, _i, _vp]),
-    "ctn_bwd_dw_layout": (_i, [_i, _i, _i, _i, C.POINTER(_i), C.POINTER(_i)]),
+    "ctn_bwd_dw_layout": (_i, [_i, _i, _i, _i, _i, C.POINTER(_i), C.POINTER(_i)]),
     "ctn_bwd_dwconv": (_i, [C.POINTER(BwdDwArgs), _vp]),
     "ctn_bwd_prelu_norm_tiles": (_i, [_i]),
     "ctn_bwd_prelu_norm": (_i, [_vp, _vp, _vp, _i, _vp, _i, _vp, _vp, _i, _i, _i, _vp, _vp, _vp, _vp]),

@@ -225,9 +225,9 @@ typedef struct ctn_bwd_dw_args {
 
 /* gLN-2 backward + PReLU-2 backward + depthwise backward (input and weight grads) +
  * gLN-1 parameter grads, one pass (gLN models). */
-/* Partial-sum geometry per utterance for this (P, dilation): rows of scal_part (= CTAs) and
+/* Partial-sum geometry per utterance for this (M, P, dilation): rows of scal_part (= CTAs) and
  * rows of chan_part. */
-int ctn_bwd_dw_layout(int K, int H, int P, int dilation, int* ctas, int* chan_rows);
+int ctn_bwd_dw_layout(int M, int K, int H, int P, int dilation, int* ctas, int* chan_rows);
 int ctn_bwd_dwconv(const ctn_bwd_dw_args* args, void* stream);
 
 /* gLN-1 input gradient + PReLU-1 backward: da (hi, lo) [M*K, H] and per-CTA d slope1 partials
