@@ -408,7 +408,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tm_a_hi, const __grid_constan
             const bool store_ok = tile_ok && krow0 < ep.K && !(ep.dbg & 2);  // rows past K: clipped by the map
             float ra[4][8], rb[4][8];                        // side input of even / odd chunks
             auto load_aux = [&](float (&dst)[4][8], int ci) {
-                if (aux != nullptr && valid && col0 + ci * 32 < ep.Cout) {
+                if (aux != nullptr && valid && col0 + ci * 32 < ep.Cout && !(ep.dbg & 32)) {
                     const float* rp = aux + grow * ep.Cout + col0 + ci * 32;
 #pragma unroll
                     for (int j = 0; j < 4; ++j) ptx::ld_global_v8(rp + 8 * j, dst[j]);

@@ -1,2 +1,2 @@
-timeout 900 python -m pytest tests/test_gpu_kernels.py tests/test_gpu_model.py -q -x -p no:cacheprovider > gpurun_out/tests.log 2>&1
-timeout 600 python bench.py --steps 3 --warmup 3 --no-cpu --no-train > gpurun_out/bench.log 2>&1
+export CTN_KINDS=pointwise
+for d in 0 4 6 36 38; do echo "== DBG $d"; CTN_GEMM_DBG=$d timeout 200 python tools/bench_gemm.py 16 2; done > gpurun_out/bench_gemm.log 2>&1
