@@ -138,7 +138,7 @@ constexpr int kBdTile = 128;  // frames per CTA
 constexpr int kBdMaxP = 8;
 
 struct BwdDwParams {
-    int K, H, P, dil, causal, P1, P2, Pb;
+    int K, H, P, dil, causal, P1, P2, Pb, cln;   // cln: per-frame statistics (P1 = Pb = column groups, stat2 = (mean, rstd))
     const float* du;
     const float* d;
     const float* a;
@@ -166,7 +166,7 @@ __global__ void __launch_bounds__(kBwThreads) bwd_dw_kernel(const BwdDwParams p)
     const int k0 = tile * kBdTile;
     const int nk = min(kBdTile, p.K - k0);
     const double n = static_cast<double>(p.K) * H;
-    if (threadIdx.x < 32) {
+    if (threadIdx.x < 32 && !p.cln) {
         const float2 s1 = gln_finalize_warp(p.stat1 + static_cast<long long>(m) * p.P1, p.P1, n);
         const float2 s2 = gln_finalize_warp(p.stat2 + static_cast<long long>(m) * p.P2, p.P2, n);
         // (S1, S2) / n
@@ -183,8 +183,34 @@ __global__ void __launch_bounds__(kBwThreads) bwd_dw_kernel(const BwdDwParams p)
         }
     }
     __syncthreads();
-    const float mu1 = sh[0], r1 = sh[1], mu2 = sh[2], r2 = sh[3], m1 = sh[4], m2 = sh[5];
     const float al1 = __ldg(p.slope1), al2 = __ldg(p.slope2);
+    const bool cln = p.cln != 0;
+    // statistics of one frame: gLN -> the utterance's scalars, cLN -> finalised from that frame's partials
+    auto stats1 = [&](long long row, float& mu1, float& r1) {
+        mu1 = sh[0], r1 = sh[1];
+        if (cln) {
+            float s = 0.f, ss = 0.f;
+            for (int g = 0; g < p.P1; ++g) {
+                const float2 t = __ldg(p.stat1 + row * p.P1 + g);
+                s += t.x, ss += t.y;
+            }
+            mu1 = s / H;
+            r1 = rsqrtf(fmaxf(ss / H - mu1 * mu1, 0.f) + kEps);
+        }
+    };
+    auto stats2 = [&](long long row, float& mu2, float& r2, float& m1, float& m2) {
+        mu2 = sh[2], r2 = sh[3], m1 = sh[4], m2 = sh[5];
+        if (cln) {
+            const float2 t = __ldg(p.stat2 + row);
+            mu2 = t.x, r2 = t.y;
+            float a = 0.f, b = 0.f;
+            for (int g = 0; g < p.Pb; ++g) {
+                const float2 u = __ldg(p.bstat + row * p.Pb + g);
+                a += u.x, b += u.y;
+            }
+            m1 = a / H, m2 = b / H;
+        }
+    };
     const int pad = p.causal ? (P - 1) * p.dil : ((P - 1) * p.dil) / 2;
     const long long ubase = static_cast<long long>(m) * p.K;
     const int CV = (H + VEC - 1) / VEC;
@@ -199,6 +225,8 @@ __global__ void __launch_bounds__(kBwThreads) bwd_dw_kernel(const BwdDwParams p)
         V<VEC> du, d;
         du.load(p.du + row * H + c);
         d.load(p.d + row * H + c);
+        float mu2, r2, m1, m2;
+        stats2(row, mu2, r2, m1, m2);
 #pragma unroll
         for (int i = 0; i < VEC; ++i) {
             const float qh = (prelu(d.v[i], al2) - mu2) * r2;
@@ -235,6 +263,8 @@ __global__ void __launch_bounds__(kBwThreads) bwd_dw_kernel(const BwdDwParams p)
                 {
                     V<VEC> du;
                     du.load(p.du + row * H + c);
+                    float mu2, r2, m1u, m2u;
+                    stats2(row, mu2, r2, m1u, m2u);
 #pragma unroll
                     for (int i = 0; i < VEC; ++i) {
                         const float qh = (prelu(dvc[i], al2) - mu2) * r2;
@@ -255,6 +285,8 @@ __global__ void __launch_bounds__(kBwThreads) bwd_dw_kernel(const BwdDwParams p)
                     if (kf >= 0 && kf < p.K) {
                         V<VEC> av;
                         av.load(p.a + (ubase + kf) * H + c);
+                        float mu1, r1;
+                        stats1(ubase + kf, mu1, r1);
 #pragma unroll
                         for (int i = 0; i < VEC; ++i) {
                             const float n1 = fmaf(g1v.v[i], (prelu(av.v[i], al1) - mu1) * r1, b1v.v[i]);
@@ -277,6 +309,8 @@ __global__ void __launch_bounds__(kBwThreads) bwd_dw_kernel(const BwdDwParams p)
                 }
                 V<VEC> ac, o;
                 ac.load(p.a + row * H + c);
+                float mu1, r1;
+                stats1(row, mu1, r1);
 #pragma unroll
                 for (int i = 0; i < VEC; ++i) {
                     const float ph = (prelu(ac.v[i], al1) - mu1) * r1;
@@ -367,6 +401,51 @@ __global__ void __launch_bounds__(kBwThreads) bwd_prelu_norm_kernel(const BwdPnP
             if (!(av.v[j] > 0.f)) da1[0] = fmaf(dp, av.v[j], da1[0]);
         }
         store_hl<VEC>(p.da_hi + row * H + c, p.da_lo + row * H + c, o);
+    }
+    block_sum<1>(da1, red);
+    if (threadIdx.x == 0) p.alpha_part[static_cast<long long>(m) * gridDim.x + blockIdx.x] = da1[0];
+}
+
+// ---------------------------------------------------------------------------------------
+// bwd_prelu_norm for cLN blocks: the two means of the norm backward are per frame, so one warp
+// owns a frame: pass 1 sums g1*dn1 and g1*dn1*ph over the channels, pass 2 writes da (hi, lo).
+// ---------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kBwThreads)
+bwd_prelu_norm_cln_kernel(const BwdPnParams p) {
+    __shared__ float red[8];
+    const int H = p.H;
+    const int m = blockIdx.y, k0 = blockIdx.x * kNsTile;
+    const int nk = min(kNsTile, p.K - k0);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const float al1 = __ldg(p.slope1);
+    float da1[1] = {0.f};
+    for (int r = warp; r < nk; r += kBwThreads / 32) {
+        const long long row = static_cast<long long>(m) * p.K + k0 + r;
+        float s = 0.f, ss = 0.f;
+        for (int g = 0; g < p.P1; ++g) {
+            const float2 t = __ldg(p.stat1 + row * p.P1 + g);
+            s += t.x, ss += t.y;
+        }
+        const float mu1 = s / H;
+        const float r1 = rsqrtf(fmaxf(ss / H - mu1 * mu1, 0.f) + kEps);
+        float s1 = 0.f, s2 = 0.f;
+        for (int c = lane; c < H; c += 32) {
+            const float ph = (prelu(p.a[row * H + c], al1) - mu1) * r1;
+            const float gd = p.g1[c] * p.dn1[row * H + c];
+            s1 += gd;
+            s2 = fmaf(gd, ph, s2);
+        }
+        const float m1 = warp_sum(s1) / H, m2 = warp_sum(s2) / H;
+        for (int c = lane; c < H; c += 32) {
+            const float av = p.a[row * H + c];
+            const float ph = (prelu(av, al1) - mu1) * r1;
+            const float dp = r1 * (p.g1[c] * p.dn1[row * H + c] - m1 - ph * m2);
+            const float o = av > 0.f ? dp : al1 * dp;
+            if (!(av > 0.f)) da1[0] = fmaf(dp, av, da1[0]);
+            __nv_bfloat16 h, l;
+            split_bf16(o, h, l);
+            p.da_hi[row * H + c] = h, p.da_lo[row * H + c] = l;
+        }
     }
     block_sum<1>(da1, red);
     if (threadIdx.x == 0) p.alpha_part[static_cast<long long>(m) * gridDim.x + blockIdx.x] = da1[0];
@@ -627,10 +706,10 @@ extern "C" int ctn_norm_split(const float* in, const float* prelu_slope, const f
     return CTN_OK;
 }
 
-static bool bwd_use_march(int H, int P) { return P == 3 && H % 4 == 0; }
+static bool bwd_use_march(int H, int P, int norm) { return P == 3 && H % 4 == 0 && norm != CTN_NORM_CLN; }
 
-extern "C" int ctn_bwd_dw_layout(int M, int K, int H, int P, int dilation, int* ctas, int* chan_rows) {
-    if (bwd_use_march(H, P) && dilation > 0) {
+extern "C" int ctn_bwd_dw_layout(int M, int K, int H, int P, int dilation, int norm, int* ctas, int* chan_rows) {
+    if (bwd_use_march(H, P, norm) && dilation > 0) {
         int NS, units, groups, n_ctas;
         bwd_march_geometry(M, K, H, dilation, &NS, &units, &groups, &n_ctas);
         if (ctas) *ctas = n_ctas;
@@ -657,7 +736,7 @@ extern "C" int ctn_bwd_dwconv(const ctn_bwd_dw_args* args, void* stream) {
                 "ctn_bwd_dwconv: NULL pointer");
     const bool aligned = al16(a.du) && al16(a.d) && al16(a.a) && al16(a.dn1) && al16(a.g1) && al16(a.b1) &&
                          al16(a.g2) && al16(a.wd) && al16(a.chan_part);
-    if (bwd_use_march(a.H, a.P)) {
+    if (bwd_use_march(a.H, a.P, a.norm)) {
         CTN_REQUIRE(aligned, "ctn_bwd_dwconv: pointers must be 16-byte aligned");
         BwdMarchParams q;
         q.K = a.K, q.H = a.H, q.dil = a.dilation, q.c0 = a.causal ? 2 : 1;
@@ -680,14 +759,14 @@ extern "C" int ctn_bwd_dwconv(const ctn_bwd_dw_args* args, void* stream) {
     }
     BwdDwParams p;
     p.K = a.K, p.H = a.H, p.P = a.P, p.dil = a.dilation, p.causal = a.causal;
-    p.P1 = a.P1, p.P2 = a.P2, p.Pb = a.Pb;
+    p.P1 = a.P1, p.P2 = a.P2, p.Pb = a.Pb, p.cln = a.norm == CTN_NORM_CLN;
     p.du = a.du, p.d = a.d, p.a = a.a;
     p.stat1 = static_cast<const float2*>(a.stat1), p.stat2 = static_cast<const float2*>(a.stat2);
     p.bstat = static_cast<const float2*>(a.bstat);
     p.g1 = a.g1, p.b1 = a.b1, p.g2 = a.g2, p.wd = a.wd, p.slope1 = a.slope1, p.slope2 = a.slope2;
     p.dn1 = a.dn1, p.chan_part = a.chan_part, p.scal_part = a.scal_part;
     int tiles, rows;
-    ctn_bwd_dw_layout(a.M, a.K, a.H, a.P, a.dilation, &tiles, &rows);
+    ctn_bwd_dw_layout(a.M, a.K, a.H, a.P, a.dilation, a.norm, &tiles, &rows);
     p.RG = rows / tiles;
     dim3 grid(tiles, a.M);
     const bool vec = a.H % 4 == 0 && aligned;
@@ -720,6 +799,23 @@ extern "C" int ctn_bwd_prelu_norm(const float* dn1, const float* a, const void* 
     else
         bwd_prelu_norm_kernel<1><<<grid, kBwThreads, 0, static_cast<cudaStream_t>(stream)>>>(p);
     CTN_LAUNCH_CHECK("bwd_prelu_norm_kernel");
+    return CTN_OK;
+}
+
+extern "C" int ctn_bwd_prelu_norm_cln(const float* dn1, const float* a, const void* stat1, int P1, const float* g1,
+                                      const float* slope1, int M, int K, int H, void* da_hi, void* da_lo,
+                                      float* alpha_part, void* stream) {
+    CTN_REQUIRE(dn1 && a && stat1 && g1 && slope1 && da_hi && da_lo && alpha_part, "ctn_bwd_prelu_norm_cln: NULL pointer");
+    CTN_REQUIRE(M > 0 && K > 0 && H > 0 && P1 > 0, "ctn_bwd_prelu_norm_cln: bad shape");
+    BwdPnParams p;
+    p.K = K, p.H = H, p.P1 = P1, p.tiles_b = 0;
+    p.dn1 = dn1, p.a = a, p.stat1 = static_cast<const float2*>(stat1), p.scal_part = nullptr;
+    p.g1 = g1, p.slope1 = slope1;
+    p.da_hi = static_cast<__nv_bfloat16*>(da_hi), p.da_lo = static_cast<__nv_bfloat16*>(da_lo);
+    p.alpha_part = alpha_part;
+    dim3 grid(ceil_div(K, kNsTile), M);
+    bwd_prelu_norm_cln_kernel<<<grid, kBwThreads, 0, static_cast<cudaStream_t>(stream)>>>(p);
+    CTN_LAUNCH_CHECK("bwd_prelu_norm_cln_kernel");
     return CTN_OK;
 }
 

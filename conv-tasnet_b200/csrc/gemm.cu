@@ -164,11 +164,18 @@ __device__ __forceinline__ void epilogue_row_affine(const EpiParams& ep, int m, 
 }
 
 // (mean, rstd) of the forward norm whose backward sums the epilogue accumulates.  Warp-collective.
-__device__ __forceinline__ void epilogue_bw_stats(const EpiParams& ep, int m, float& mean, float& rstd) {
+// gLN (out_stat = GLN): per utterance, from bw_P partials.  cLN (out_stat = CLN): per frame, bw_stat[row] holds
+// (mean, rstd) directly.
+__device__ __forceinline__ void epilogue_bw_stats(const EpiParams& ep, int m, long long grow, bool valid, float& mean,
+                                                  float& rstd) {
     mean = 0.f, rstd = 1.f;
-    if (ep.bw_pre != nullptr) {
+    if (ep.bw_pre == nullptr) return;
+    if (ep.out_stat == CTN_NORM_GLN) {
         const float2 st = gln_finalize_warp(ep.bw_stat + static_cast<long long>(m) * ep.bw_P, ep.bw_P,
                                             static_cast<double>(ep.K) * ep.Cout);
+        mean = st.x, rstd = st.y;
+    } else if (valid) {
+        const float2 st = __ldg(ep.bw_stat + grow);
         mean = st.x, rstd = st.y;
     }
 }
@@ -389,7 +396,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tm_a_hi, const __grid_constan
             const long long grow = static_cast<long long>(m) * ep.K + k;
             // gLN statistics depend on the utterance only: re-reduce the partials when m changes
             if (kAffine && (ep.in_norm != CTN_NORM_GLN || m != cur_m)) epilogue_row_affine(ep, m, grow, valid, s, t);
-            if (kBw && m != cur_m) epilogue_bw_stats(ep, m, bw_mean, bw_rstd);
+            if (kBw && (ep.out_stat != CTN_NORM_GLN || m != cur_m)) epilogue_bw_stats(ep, m, grow, valid, bw_mean, bw_rstd);
             cur_m = m;
             if ((kAffine || kBw) && tn != cur_tn) {  // per-column constants of this column tile -> smem
                 ptx::named_bar_sync(1, kEpiThreads);
@@ -551,7 +558,7 @@ gemm_simt_kernel(const __nv_bfloat16* __restrict__ a_hi, const __nv_bfloat16* __
     if (use_slope) slope = __ldg(ep.stat_prelu);
     float s, t, bw_mean, bw_rstd;
     epilogue_row_affine(ep, m, grow, valid, s, t);
-    epilogue_bw_stats(ep, m, bw_mean, bw_rstd);
+    epilogue_bw_stats(ep, m, grow, valid, bw_mean, bw_rstd);
     if (ep.bw_pre != nullptr) slope = __ldg(ep.bw_slope);
     float ls = 0.f, lss = 0.f;
     for (int grp = 0; grp < ep.groups; ++grp) {
@@ -744,9 +751,10 @@ extern "C" int ctn_gemm1x1(const ctn_gemm_args* args, void* stream_) {
         const char* d = getenv("CTN_GEMM_DBG");
         ep.dbg = d ? atoi(d) : 0;
     }
-    CTN_REQUIRE(a.bw_pre == nullptr || (a.bw_gamma && a.bw_slope && a.bw_stat && a.bw_P > 0 &&
-                                        a.out_stat == CTN_NORM_GLN && a.resid == nullptr && a.in_norm == CTN_NORM_NONE),
-                "ctn_gemm1x1: bw_pre needs bw_gamma/bw_slope/bw_stat, out_stat = GLN and no resid / in_norm");
+    CTN_REQUIRE(a.bw_pre == nullptr || (a.bw_gamma && a.bw_slope && a.bw_stat && a.out_stat != CTN_NORM_NONE &&
+                                        (a.out_stat != CTN_NORM_GLN || a.bw_P > 0) && a.resid == nullptr &&
+                                        a.in_norm == CTN_NORM_NONE),
+                "ctn_gemm1x1: bw_pre needs bw_gamma/bw_slope/bw_stat, an out_stat mode and no resid / in_norm");
 
     auto aligned16 = [](const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; };
     const bool tc_ok = !(a.force_simt & 1) && a.Cin % 8 == 0 && a.Cout % 32 == 0 && aligned16(a.a_hi) && aligned16(a.a_lo) &&

@@ -54,9 +54,7 @@ class TrainPlan:
 
     def __init__(self, cfg, M, T, device):
         _check_cfg(cfg)
-        if cfg["norm_type"] != "gLN":
-            raise NotImplementedError("training (backward) is implemented for norm_type='gLN'; "
-                                      "cLN models run inference only")
+        self.norm = _NORM[cfg["norm_type"]]
         self.cfg, self.M, self.T, self.device = cfg, M, T, device
         N, L, B, H, C_ = cfg["N"], cfg["L"], cfg["B"], cfg["H"], cfg["C"]
         self.hop, self.K, self.T_conv = frame_geometry(T, L)
@@ -78,10 +76,16 @@ class TrainPlan:
         self.a = [e(Rr, H, **f32) for _ in range(NB)]
         self.d = [e(Rr, H, **f32) for _ in range(NB)]
         self.q_hl = (e(Rr, H, **bf), e(Rr, H, **bf))
-        self.P1 = lib.ctn_gemm_gln_partials(K, H)
-        self.P2s = [lib.ctn_dwconv_gln_partials(K, H, cfg["P"], 2 ** x) for x in range(cfg["X"])]
-        self.stat1 = [z(M, self.P1, 2, **f32) for _ in range(NB)]
-        self.stat2 = [z(M, max(self.P2s), 2, **f32) for _ in range(NB)]
+        if self.norm == nat.NORM_GLN:       # (sum, sumsq) partials per utterance
+            self.P1 = lib.ctn_gemm_gln_partials(K, H)
+            self.P2s = [lib.ctn_dwconv_gln_partials(K, H, cfg["P"], 2 ** x) for x in range(cfg["X"])]
+            self.stat1 = [z(M, self.P1, 2, **f32) for _ in range(NB)]
+            self.stat2 = [z(M, max(self.P2s), 2, **f32) for _ in range(NB)]
+        else:                               # cLN: per frame; column-group partials / (mean, rstd)
+            self.P1 = lib.ctn_gemm_cln_groups(H)
+            self.P2s = [1] * cfg["X"]
+            self.stat1 = [z(Rr, self.P1, 2, **f32) for _ in range(NB)]
+            self.stat2 = [z(Rr, 2, **f32) for _ in range(NB)]
         self.score = e(Rr, C_ * N, **f32)
         # backward
         self.ds_hl = (e(Rr, C_ * N, **bf), e(Rr, C_ * N, **bf))
@@ -91,13 +95,13 @@ class TrainPlan:
         self.hl_H = (e(Rr, H, **bf), e(Rr, H, **bf))       # u (hi, lo), later da (hi, lo)
         self.du = e(Rr, H, **f32)
         self.dn1 = e(Rr, H, **f32)
-        self.bstat = z(M, self.P1, 2, **f32)
+        self.bstat = z(M if self.norm == nat.NORM_GLN else Rr, self.P1, 2, **f32)
         self.dn0 = e(Rr, N, **f32)
         self.dpre = e(Rr, N, **f32)
         self.bd_ctas, self.bd_rows = [], []          # per dilation: scal_part / chan_part rows per utterance
         for x in range(cfg["X"]):
             ctas, rows = C.c_int(), C.c_int()
-            lib.ctn_bwd_dw_layout(M, K, H, cfg["P"], 2 ** x, C.byref(ctas), C.byref(rows))
+            lib.ctn_bwd_dw_layout(M, K, H, cfg["P"], 2 ** x, self.norm, C.byref(ctas), C.byref(rows))
             self.bd_ctas.append(ctas.value)
             self.bd_rows.append(rows.value)
         self.chan_part = e(M * max(self.bd_rows), (4 + cfg["P"]) * H, **f32)
@@ -184,7 +188,8 @@ class TrainPlan:
         M, K, T, NB = self.M, self.K, self.T, self.NB
         lib = nat.lib()
         self._keep = []
-        GLN = nat.NORM_GLN
+        GLN = self.norm                      # the block norm (gLN or cLN)
+        is_gln = self.norm == nat.NORM_GLN
         causal = int(bool(cfg["causal"]))
         U = params["encoder.conv1d_U.weight"]
         V = params["decoder.basis_signals.weight"]
@@ -247,6 +252,7 @@ class TrainPlan:
         bwd.append(self._gemm(Cin=C_ * N, Cout=B, a_hi=self.ds_hl[0], a_lo=self.ds_hl[1], w_hi=prep_b.mask_t[0],
                               w_lo=prep_b.mask_t[1], out_f32=self.g, out_hi=self.g_hl[0], out_lo=self.g_hl[1]))
         ns, bd, pn = lib.ctn_norm_split, lib.ctn_bwd_dwconv, lib.ctn_bwd_prelu_norm
+        pn_cln = lib.ctn_bwd_prelu_norm_cln
         for (i, xb, k) in reversed(blocks):
             pb = prep_b.blocks[i]
             P2 = self.P2s[xb]
@@ -268,12 +274,20 @@ class TrainPlan:
             b.g1, b.b1, b.g2 = params[k["g1"]].data_ptr(), params[k["b1"]].data_ptr(), params[k["g2"]].data_ptr()
             b.wd, b.slope1, b.slope2 = params[k["wd"]].data_ptr(), params[k["a1"]].data_ptr(), params[k["a2"]].data_ptr()
             b.dn1, b.chan_part, b.scal_part = self.dn1.data_ptr(), self.chan_part.data_ptr(), self.scal_part.data_ptr()
+            b.norm = self.norm
             self._keep.append(b)
             bwd.append(lambda s, ref=C.byref(b): bd(ref, s))
-            a_ = (self.dn1.data_ptr(), self.a[i].data_ptr(), self.stat1[i].data_ptr(), self.P1,
-                  self.scal_part.data_ptr(), self.bd_ctas[xb], params[k["g1"]].data_ptr(), params[k["a1"]].data_ptr(),
-                  M, K, H, self.hl_H[0].data_ptr(), self.hl_H[1].data_ptr(), self.alpha_part.data_ptr())
-            bwd.append(lambda s, a=a_: pn(*a, s))                                       # da (hi, lo)
+            if is_gln:
+                a_ = (self.dn1.data_ptr(), self.a[i].data_ptr(), self.stat1[i].data_ptr(), self.P1,
+                      self.scal_part.data_ptr(), self.bd_ctas[xb], params[k["g1"]].data_ptr(),
+                      params[k["a1"]].data_ptr(), M, K, H, self.hl_H[0].data_ptr(), self.hl_H[1].data_ptr(),
+                      self.alpha_part.data_ptr())
+                bwd.append(lambda s, a=a_: pn(*a, s))                                   # da (hi, lo)
+            else:
+                a_ = (self.dn1.data_ptr(), self.a[i].data_ptr(), self.stat1[i].data_ptr(), self.P1,
+                      params[k["g1"]].data_ptr(), params[k["a1"]].data_ptr(), M, K, H,
+                      self.hl_H[0].data_ptr(), self.hl_H[1].data_ptr(), self.alpha_part.data_ptr())
+                bwd.append(lambda s, a=a_: pn_cln(*a, s))
             call, seg_w1 = self._wgrad(self.hl_H, self.x_hl[i], H, B, k["w1"], self.wg_part2)   # dW1 = da^T x
             bwd.append(call)
             # every parameter gradient of the block in ONE reduction launch

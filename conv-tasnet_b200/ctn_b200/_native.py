@@ -51,7 +51,7 @@ class BwdDwArgs(C.Structure):
         ("P1", C.c_int), ("P2", C.c_int), ("Pb", C.c_int),
         ("du", _vp), ("d", _vp), ("a", _vp), ("stat1", _vp), ("stat2", _vp), ("bstat", _vp),
         ("g1", _vp), ("b1", _vp), ("g2", _vp), ("wd", _vp), ("slope1", _vp), ("slope2", _vp),
-        ("dn1", _vp), ("chan_part", _vp), ("scal_part", _vp),
+        ("dn1", _vp), ("chan_part", _vp), ("scal_part", _vp), ("norm", C.c_int),
     ]
 
 
@@ -118,10 +118,11 @@ _SIGNATURES = {
     "ctn_norm_split": (_i, [_vp, _vp, _vp, _vp, _i, _vp, _i, _i, _i, _i, _vp, _vp, _vp]),
     "ctn_wgrad_splits": (_i, [_ll, _i, _i]),
     "ctn_wgrad": (_i, [_vp, _vp, _vp, _vp, _ll, _i, _i, _vp, _i, _vp]),
-    "ctn_bwd_dw_layout": (_i, [_i, _i, _i, _i, _i, C.POINTER(_i), C.POINTER(_i)]),
+    "ctn_bwd_dw_layout": (_i, [_i, _i, _i, _i, _i, _i, C.POINTER(_i), C.POINTER(_i)]),
     "ctn_bwd_dwconv": (_i, [C.POINTER(BwdDwArgs), _vp]),
     "ctn_bwd_prelu_norm_tiles": (_i, [_i]),
     "ctn_bwd_prelu_norm": (_i, [_vp, _vp, _vp, _i, _vp, _i, _vp, _vp, _i, _i, _i, _vp, _vp, _vp, _vp]),
+    "ctn_bwd_prelu_norm_cln": (_i, [_vp, _vp, _vp, _i, _vp, _vp, _i, _i, _i, _vp, _vp, _vp, _vp]),
     "ctn_reduce_partials": (_i, [C.POINTER(ReduceArgs), _vp]),
     "ctn_decoder_bwd_tiles": (_i, [_i]),
     "ctn_decoder_bwd": (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp]),

@@ -221,13 +221,16 @@ typedef struct ctn_bwd_dw_args {
     float* dn1;            /* out: d loss / d n1, fp32 [M*K, H]                            */
     float* chan_part;      /* out: [M*chan_rows][(4+P)*H]: dg2, db2, dg1, db1, dwd[j]      */
     float* scal_part;      /* out: [M*ctas][4]: sum g1*dn1, sum g1*dn1*ph, d slope2, 0     */
+    int norm;              /* CTN_NORM_GLN (0 is read as gLN) or CTN_NORM_CLN.  cLN: stat1 / bstat are
+                            * per-frame column-group partials [M*K, P1] / [M*K, Pb], stat2 is the
+                            * per-frame (mean, rstd) [M*K]; scal_part[.][0..1] are not produced          */
 } ctn_bwd_dw_args;
 
 /* gLN-2 backward + PReLU-2 backward + depthwise backward (input and weight grads) +
  * gLN-1 parameter grads, one pass (gLN models). */
 /* Partial-sum geometry per utterance for this (M, P, dilation): rows of scal_part (= CTAs) and
  * rows of chan_part. */
-int ctn_bwd_dw_layout(int M, int K, int H, int P, int dilation, int* ctas, int* chan_rows);
+int ctn_bwd_dw_layout(int M, int K, int H, int P, int dilation, int norm, int* ctas, int* chan_rows);
 int ctn_bwd_dwconv(const ctn_bwd_dw_args* args, void* stream);
 
 /* gLN-1 input gradient + PReLU-1 backward: da (hi, lo) [M*K, H] and per-CTA d slope1 partials
@@ -236,6 +239,11 @@ int ctn_bwd_prelu_norm_tiles(int K);
 int ctn_bwd_prelu_norm(const float* dn1, const float* a, const void* stat1, int P1, const float* scal_part,
                        int tiles_b, const float* g1, const float* slope1, int M, int K, int H, void* da_hi,
                        void* da_lo, float* alpha_part, void* stream);
+
+/* The same for cLN blocks (per-frame statistics; stat1 = column-group partials [M*K, P1]). */
+int ctn_bwd_prelu_norm_cln(const float* dn1, const float* a, const void* stat1, int P1, const float* g1,
+                           const float* slope1, int M, int K, int H, void* da_hi, void* da_lo, float* alpha_part,
+                           void* stream);
 
 #define CTN_MAX_SEG 12
 typedef struct ctn_reduce_args {

@@ -55,7 +55,7 @@ def test_block_backward_chain(H, K, M, dil, causal):
     stat1, stat2 = _stat(pa.detach()), _stat(q.detach())
     a_r, d_r, du_r = rows(a), rows(d), rows(du)
     tiles, rows = C.c_int(), C.c_int()
-    lib.ctn_bwd_dw_layout(M, K, H, P, dil, C.byref(tiles), C.byref(rows))
+    lib.ctn_bwd_dw_layout(M, K, H, P, dil, nat.NORM_GLN, C.byref(tiles), C.byref(rows))
     tiles, rows = tiles.value, rows.value
     dn1 = torch.full((M * K, H), float("nan"), device=DEV)
     chan = torch.full((M * rows, (4 + P) * H), float("nan"), device=DEV)

@@ -48,7 +48,7 @@ def _scalar_groups(named):
     return [k for k, v in named if v.numel() == 1]
 
 
-@pytest.mark.parametrize("name", ["odd_gln", "softmax_c3", "tc_small"])
+@pytest.mark.parametrize("name", ["odd_gln", "softmax_c3", "tc_small", "causal_cln", "tc_causal_cln"])
 def test_gradients_match_reference_fixture(name):
     import pit_criterion
     cfg, z = load_golden(name)
@@ -156,8 +156,18 @@ def test_training_step_reduces_loss_and_is_deterministic():
     assert torch.equal(grads[0], grads[1])
 
 
-def test_cln_training_is_rejected_loudly():
-    import conv_tasnet
-    m = conv_tasnet.ConvTasNet(8, 4, 8, 8, 3, 1, 1, 2, norm_type="cLN").to(DEV)
-    with pytest.raises(NotImplementedError):
-        m(torch.zeros(1, 64, device=DEV))
+def test_cln_training_step_runs_and_reduces_loss():
+    """Causal cLN models train too (conv_tasnet.py:298-299 + autograd in the reference)."""
+    import pit_criterion
+    cfg, z = load_golden("tc_causal_cln")
+    model = _build(cfg, {k[2:]: v for k, v in z.items() if k.startswith("w:")})
+    opt = torch.optim.Adam(model.parameters(), lr=1e-3)
+    hist = []
+    for _ in range(4):
+        opt.zero_grad()
+        est = model(z["mixture"].to(DEV))
+        loss, *_ = pit_criterion.cal_loss(z["sources"].to(DEV), est, z["lengths"].to(DEV))
+        loss.backward()
+        opt.step()
+        hist.append(float(loss.detach()))
+    assert hist[-1] < hist[0]
