@@ -1,1 +1,1 @@
-timeout 900 python -m pytest tests -m gpu -q -x -p no:cacheprovider > gpurun_out/tests.log 2>&1
+timeout 300 python bench.py --steps 2 --warmup 3 --no-cpu --no-train --micro-batch 64 > gpurun_out/bench_a.log 2>&1
