@@ -31,6 +31,8 @@ struct EpiParams {
     __nv_bfloat16* out_hi;
     __nv_bfloat16* out_lo;
     const float* resid;
+    const __nv_bfloat16* resid_hi;   // residual as a (hi, lo) pair instead of fp32
+    const __nv_bfloat16* resid_lo;
     const float* col_g;
     const float* col_bias;
     int in_norm;
@@ -72,6 +74,11 @@ __device__ __forceinline__ void epilogue_chunk(const EpiParams& ep, float (&v)[3
     }
     if (!valid) return;
     const long long base = grow * ep.Cout + n0;
+    if (ep.resid_hi != nullptr) {
+#pragma unroll
+        for (int j = 0; j < 32; ++j)
+            if (j < ncols) v[j] += __bfloat162float(ep.resid_hi[base + j]) + __bfloat162float(ep.resid_lo[base + j]);
+    }
     if (ep.resid != nullptr) {
         if (VEC) {
 #pragma unroll
@@ -380,6 +387,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tm_a_hi, const __grid_constan
         const float slope = use_slope ? __ldg(ep.stat_prelu) : 1.f;   // PReLU with slope 1 = identity
         const float bw_slope = kBw ? __ldg(ep.bw_slope) : 0.f;
         const float* aux = kBw ? ep.bw_pre : (kAffine ? ep.resid : nullptr);  // per-element side input
+        const bool aux_hl = kAffine && ep.resid_hi != nullptr;                // ... or a (hi, lo) residual
         const bool want_stat = ep.out_stat != CTN_NORM_NONE;
         int it = 0, cur_tn = -1, cur_m = -1;
         float s = 1.f, t = 0.f, bw_mean = 0.f, bw_rstd = 1.f;
@@ -415,10 +423,17 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tm_a_hi, const __grid_constan
             const bool store_ok = tile_ok && krow0 < ep.K && !(ep.dbg & 2);  // rows past K: clipped by the map
             float ra[4][8], rb[4][8];                        // side input of even / odd chunks
             auto load_aux = [&](float (&dst)[4][8], int ci) {
-                if (aux != nullptr && valid && col0 + ci * 32 < ep.Cout && !(ep.dbg & 32)) {
+                if (!valid || col0 + ci * 32 >= ep.Cout || (ep.dbg & 32)) return;
+                if (aux != nullptr) {
                     const float* rp = aux + grow * ep.Cout + col0 + ci * 32;
 #pragma unroll
                     for (int j = 0; j < 4; ++j) ptx::ld_global_v8(rp + 8 * j, dst[j]);
+                } else if (aux_hl) {   // 32 bf16 hi in dst[0..1], 32 bf16 lo in dst[2..3] (raw bits)
+                    const long long o = grow * ep.Cout + col0 + ci * 32;
+                    ptx::ld_global_v8(ep.resid_hi + o, dst[0]);
+                    ptx::ld_global_v8(ep.resid_hi + o + 16, dst[1]);
+                    ptx::ld_global_v8(ep.resid_lo + o, dst[2]);
+                    ptx::ld_global_v8(ep.resid_lo + o + 16, dst[3]);
                 }
             };
             if (kAffine || kBw) load_aux(ra, 0);
@@ -458,6 +473,14 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tm_a_hi, const __grid_constan
                             if (aux != nullptr && valid) {
 #pragma unroll
                                 for (int j = 0; j < 32; ++j) v[j] += rc[j >> 3][j & 7];
+                            } else if (aux_hl && valid) {
+#pragma unroll
+                                for (int j = 0; j < 16; ++j) {   // word j holds columns 2j (low half) and 2j + 1
+                                    const uint32_t h = __float_as_uint(rc[j >> 3][j & 7]);
+                                    const uint32_t l = __float_as_uint(rc[2 + (j >> 3)][j & 7]);
+                                    v[2 * j] += __uint_as_float(h << 16) + __uint_as_float(l << 16);
+                                    v[2 * j + 1] += __uint_as_float(h & 0xffff0000u) + __uint_as_float(l & 0xffff0000u);
+                                }
                             }
                         }
                         if (kBw) {
@@ -740,6 +763,9 @@ extern "C" int ctn_gemm1x1(const ctn_gemm_args* args, void* stream_) {
     ep.out_hi = static_cast<__nv_bfloat16*>(a.out_hi);
     ep.out_lo = static_cast<__nv_bfloat16*>(a.out_lo);
     ep.resid = a.resid, ep.col_g = a.col_g, ep.col_bias = a.col_bias;
+    ep.resid_hi = static_cast<const __nv_bfloat16*>(a.resid_hi), ep.resid_lo = static_cast<const __nv_bfloat16*>(a.resid_lo);
+    CTN_REQUIRE((a.resid_hi == nullptr) == (a.resid_lo == nullptr) && !(a.resid && a.resid_hi),
+                "ctn_gemm1x1: resid_hi/resid_lo go together and exclude resid");
     ep.in_norm = a.in_norm, ep.in_stat = static_cast<const float2*>(a.in_stat), ep.in_P = a.in_P;
     ep.in_count = a.in_count;
     ep.out_stat = a.out_stat, ep.out_stat_buf = static_cast<float2*>(a.out_stat_buf);
@@ -752,21 +778,22 @@ extern "C" int ctn_gemm1x1(const ctn_gemm_args* args, void* stream_) {
         ep.dbg = d ? atoi(d) : 0;
     }
     CTN_REQUIRE(a.bw_pre == nullptr || (a.bw_gamma && a.bw_slope && a.bw_stat && a.out_stat != CTN_NORM_NONE &&
-                                        (a.out_stat != CTN_NORM_GLN || a.bw_P > 0) && a.resid == nullptr &&
+                                        (a.out_stat != CTN_NORM_GLN || a.bw_P > 0) && a.resid == nullptr && a.resid_hi == nullptr &&
                                         a.in_norm == CTN_NORM_NONE),
                 "ctn_gemm1x1: bw_pre needs bw_gamma/bw_slope/bw_stat, an out_stat mode and no resid / in_norm");
 
     auto aligned16 = [](const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; };
     const bool tc_ok = !(a.force_simt & 1) && a.Cin % 8 == 0 && a.Cout % 32 == 0 && aligned16(a.a_hi) && aligned16(a.a_lo) &&
                        aligned16(a.w_hi) && aligned16(a.w_lo) && aligned16(a.out_f32) && aligned16(a.out_hi) &&
-                       aligned16(a.out_lo) && aligned16(a.resid) && aligned16(a.bw_pre);
+                       aligned16(a.out_lo) && aligned16(a.resid) && aligned16(a.bw_pre) && aligned16(a.resid_hi) &&
+                       aligned16(a.resid_lo);
     if (tc_ok) {
         // 256-wide tiles halve the re-reads of the activation tile but need enough tiles to fill the SMs
         const long long tiles256 = static_cast<long long>(a.M) * ep.tiles_per_utt * ceil_div(a.Cout, 256);
         const int mode = a.force_simt >> 1;   // test hook: 1 = single-CTA kernels only, 2 = pair kernel
         const bool pair = a.Cout % 256 == 0 && mode != 1 && (mode == 2 || tiles256 >= 2ll * sm_count());
         const bool affine = a.col_g != nullptr || a.col_bias != nullptr || a.in_norm != CTN_NORM_NONE ||
-                            a.resid != nullptr;
+                            a.resid != nullptr || a.resid_hi != nullptr;
         if (a.bw_pre != nullptr)
             return pair ? launch_tc<256, true, kEpiBw>(a, ep, stream) : launch_tc<128, false, kEpiBw>(a, ep, stream);
         if (affine)

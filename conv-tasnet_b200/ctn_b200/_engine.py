@@ -9,7 +9,7 @@ call into libctn_b200.so.  The sequence mirrors ConvTasNet.forward
   per TemporalBlock (conv_tasnet.py:212-272):
     conv1x1 (+ statistics of PReLU output)            ctn_gemm1x1   (out_stat)
     PReLU, norm, depthwise, PReLU (+ statistics)      ctn_dwconv_fwd
-    norm folded into pointwise 1x1, + residual        ctn_gemm1x1   (in_norm, resid)
+    norm folded into pointwise 1x1, + residual        ctn_gemm1x1   (in_norm, resid_hi/lo)
   mask 1x1                                            ctn_gemm1x1
   mask non-linearity, decoder, overlap-add, pad       ctn_decoder_fwd
 
@@ -94,7 +94,6 @@ class _Plan:
         self.w = torch.empty(R_, N, **f32)
         self.w_hl = (torch.empty(R_, N, **bf), torch.empty(R_, N, **bf))
         self.rowstat0 = torch.empty(R_, 2, **f32)
-        self.x = torch.empty(R_, B, **f32)
         self.x_hl = (torch.empty(R_, B, **bf), torch.empty(R_, B, **bf))
         self.a = torch.empty(R_, H, **f32)
         self.q_hl = (torch.empty(R_, H, **bf), torch.empty(R_, H, **bf))
@@ -143,11 +142,11 @@ class _Plan:
              self.w_hl[1].data_ptr(), self.rowstat0.data_ptr())
         calls.append(lambda s, a=a: enc(*a, s))
         info.append(("encoder", 2.0 * Rr * N * L, 4.0 * M * T + 8.0 * Rr * N))
-        info.append(("gemm_bottleneck", 2.0 * Rr * N * B, 4.0 * Rr * N + 8.0 * Rr * B))
+        info.append(("gemm_bottleneck", 2.0 * Rr * N * B, 4.0 * Rr * N + 4.0 * Rr * B))
         calls.append(self._gemm(Cin=N, Cout=B, a_hi=self.w_hl[0], a_lo=self.w_hl[1], w_hi=prep.bott[0],
                                 w_lo=prep.bott[1], col_g=prep.bott[2], col_bias=prep.bott[3],
                                 in_norm=nat.NORM_CLN, in_stat=self.rowstat0,
-                                out_f32=self.x, out_hi=self.x_hl[0], out_lo=self.x_hl[1]))
+                                out_hi=self.x_hl[0], out_lo=self.x_hl[1]))
         dw = lib.ctn_dwconv_fwd
         i = 0
         for r in range(cfg["R"]):
@@ -157,7 +156,7 @@ class _Plan:
                 i += 1
                 info.append(("gemm_conv1x1", 2.0 * Rr * B * H, 4.0 * Rr * B + 4.0 * Rr * H))
                 info.append(("dwconv", 2.0 * Rr * H * cfg["P"], 8.0 * Rr * H))
-                info.append(("gemm_pointwise", 2.0 * Rr * B * H, 4.0 * Rr * H + 12.0 * Rr * B))
+                info.append(("gemm_pointwise", 2.0 * Rr * B * H, 4.0 * Rr * H + 8.0 * Rr * B))
                 calls.append(self._gemm(Cin=B, Cout=H, a_hi=self.x_hl[0], a_lo=self.x_hl[1], w_hi=pb["w1"][0],
                                         w_lo=pb["w1"][1], out_f32=self.a, out_stat=self.norm,
                                         out_stat_buf=self.stat1, stat_prelu=params[k["a1"]]))
@@ -175,8 +174,8 @@ class _Plan:
                 calls.append(self._gemm(Cin=H, Cout=B, a_hi=self.q_hl[0], a_lo=self.q_hl[1], w_hi=pb["w2"][0],
                                         w_lo=pb["w2"][1], col_g=pb["w2"][2], col_bias=pb["w2"][3],
                                         in_norm=self.norm, in_stat=self.stat2, in_P=self.P2s[xb],
-                                        in_count=float(K) * H, resid=self.x,
-                                        out_f32=self.x, out_hi=self.x_hl[0], out_lo=self.x_hl[1]))
+                                        in_count=float(K) * H, resid_hi=self.x_hl[0], resid_lo=self.x_hl[1],
+                                        out_hi=self.x_hl[0], out_lo=self.x_hl[1]))
         calls.append(self._gemm(Cin=B, Cout=C_ * N, a_hi=self.x_hl[0], a_lo=self.x_hl[1], w_hi=prep.mask[0],
                                 w_lo=prep.mask[1], out_f32=self.score))
         info.append(("gemm_mask", 2.0 * Rr * B * C_ * N, 4.0 * Rr * B + 4.0 * Rr * C_ * N))

@@ -123,6 +123,9 @@ typedef struct ctn_gemm_args {
     const float* bw_slope;
     const void* bw_stat;
     int bw_P;
+    /* residual given as a bf16 (hi, lo) pair [M*K, Cout] instead of fp32 (both or neither; exclusive with
+     * resid; may alias out_hi / out_lo): inference keeps the block input only in that form */
+    const void *resid_hi, *resid_lo;
 } ctn_gemm_args;
 
 /* 1x1 convolution as a GEMM over all frames of the batch (bottleneck
