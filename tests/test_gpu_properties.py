@@ -1,0 +1,121 @@
+"""Size-independent properties of the path at BASELINE.json's full sizes, where the
+oracle is too slow to be the checker: linearity of overlap-and-add (utils.py:9-46),
+permutation / scale invariance of the PIT SI-SNR (pit_criterion.py:27-76), the length
+mask (pit_criterion.py:101-113), and the homogeneity of the relu-mask network in the
+mixture gain for gLN (every op between encoder and decoder is scale-equivariant or
+scale-invariant once EPS is negligible).
+"""
+import itertools
+
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda"
+
+
+def _rel(a, b):
+    return float((a.double() - b.double()).norm() / b.double().norm())
+
+
+@pytest.mark.parametrize("shape,step", [((64, 2, 3199, 20), 10), ((3, 3, 5999, 16), 8), ((1, 1, 7, 2), 1),
+                                        ((2, 2, 100, 20), 20)])
+def test_overlap_and_add_is_linear_and_conserves_mass(shape, step):
+    import utils
+    g = torch.Generator().manual_seed(11)
+    a = torch.randn(*shape, generator=g).to(DEV)
+    b = torch.randn(*shape, generator=g).to(DEV)
+    oa, ob = utils.overlap_and_add(a, step), utils.overlap_and_add(b, step)
+    K, L = shape[-2], shape[-1]
+    assert oa.shape == shape[:-2] + ((K - 1) * step + L,)
+    lin = utils.overlap_and_add(2.0 * a - 3.0 * b, step)
+    assert _rel(lin, 2.0 * oa - 3.0 * ob) < 1e-6
+    # every frame sample lands in exactly one output sample: totals agree
+    assert torch.allclose(oa.double().sum(-1), a.double().sum((-1, -2)), rtol=1e-5, atol=1e-3)
+    # a single non-zero frame lands at k * step, untouched
+    z = torch.zeros(*shape, device=DEV)
+    k = K // 2
+    z[..., k, :] = a[..., k, :]
+    oz = utils.overlap_and_add(z, step)
+    assert torch.equal(oz[..., k * step:k * step + L], a[..., k, :])
+    oz[..., k * step:k * step + L] = 0
+    assert float(oz.abs().max()) == 0.0
+
+
+@pytest.mark.parametrize("B,C,T", [(64, 2, 32000), (16, 3, 32000), (4, 4, 8001)])
+def test_pit_is_invariant_to_speaker_order_and_estimate_scale(B, C, T):
+    import pit_criterion
+    g = torch.Generator().manual_seed(12)
+    src = torch.randn(B, C, T, generator=g).to(DEV)
+    est = src[:, torch.randperm(C, generator=g)] + 0.5 * torch.randn(B, C, T, generator=g).to(DEV)
+    lens = torch.randint(T // 2, T + 1, (B,), generator=g).to(DEV)
+    lens[0] = T
+    base, perms, idx0 = pit_criterion.cal_si_snr_with_pit(src, est.clone(), lens)
+    assert perms.tolist() == [list(p) for p in itertools.permutations(range(C))]
+    for p in list(itertools.permutations(range(C)))[1:4]:
+        m, _, idx = pit_criterion.cal_si_snr_with_pit(src, est[:, list(p)].clone(), lens)
+        assert torch.allclose(m, base, atol=1e-4)
+        # estimate i of the shuffled batch is estimate p[i]: its target is perm0[p[i]]
+        for b in (0, B - 1):
+            perm0 = perms[int(idx0[b])].tolist()
+            assert perms[int(idx[b])].tolist() == [perm0[p[i]] for i in range(C)]
+    # SI-SNR does not see a per-speaker gain on the estimate
+    gains = (0.1 + 5.0 * torch.rand(1, C, 1, generator=g)).to(DEV)
+    m, _, idx = pit_criterion.cal_si_snr_with_pit(src, (est * gains).clone(), lens)
+    assert torch.allclose(m, base, atol=2e-4) and torch.equal(idx, idx0)
+    # nor a common gain on the sources
+    m, _, idx = pit_criterion.cal_si_snr_with_pit(7.0 * src, est.clone(), lens)
+    assert torch.allclose(m, base, atol=2e-4) and torch.equal(idx, idx0)
+
+
+def test_pit_ignores_samples_beyond_the_length_and_masks_them_in_place():
+    import pit_criterion
+    g = torch.Generator().manual_seed(13)
+    B, C, T = 8, 2, 32000
+    src = torch.randn(B, C, T, generator=g).to(DEV)
+    est = src + 0.3 * torch.randn(B, C, T, generator=g).to(DEV)
+    lens = torch.tensor([T, T - 1, 20000, 16001, 16000, 9, 3, 2], device=DEV)
+    mask = pit_criterion.get_mask(src, lens)
+    assert mask.shape == (B, 1, T) and mask.dtype == src.dtype
+    assert torch.equal(mask[:, 0].sum(-1).long(), lens)
+    e1 = est.clone()
+    base, _, idx0 = pit_criterion.cal_si_snr_with_pit(src, e1, lens)
+    assert torch.equal(e1, est * mask)                       # pit_criterion.py:38 side effect
+    junk = est + (1 - mask) * 100.0 * torch.randn(B, C, T, generator=g).to(DEV)
+    m, _, idx = pit_criterion.cal_si_snr_with_pit(src, junk.clone(), lens)
+    assert torch.equal(m, base) and torch.equal(idx, idx0)
+    # truncating to the longest length changes nothing either
+    m, _, idx = pit_criterion.cal_si_snr_with_pit(src[:2], est[:2].clone(), lens[:2])
+    assert torch.equal(m, base[:2])
+
+
+def test_relu_mask_gln_network_is_homogeneous_in_the_mixture_gain():
+    """Paper configuration, 4 s: separate(g * x) == g * separate(x) up to EPS effects."""
+    import conv_tasnet
+    torch.manual_seed(14)
+    model = conv_tasnet.ConvTasNet(256, 20, 256, 512, 3, 8, 4, 2, norm_type="gLN", causal=False,
+                                   mask_nonlinear="relu").to(DEV).eval()
+    g = torch.Generator().manual_seed(15)
+    mix = (0.1 * torch.randn(4, 32000, generator=g)).to(DEV)
+    with torch.no_grad():
+        y1 = model(mix)
+        y4 = model(4.0 * mix)
+        again = model(mix)
+    assert torch.equal(y1, again)                            # run-to-run bit-reproducible
+    assert _rel(y4, 4.0 * y1) < 1e-3
+
+
+def test_ragged_input_length_is_zero_padded_back():
+    """T not a multiple of the hop: output has the input's length (conv_tasnet.py:56-59)."""
+    import conv_tasnet
+    torch.manual_seed(16)
+    model = conv_tasnet.ConvTasNet(64, 16, 64, 128, 3, 3, 2, 2).to(DEV).eval()
+    g = torch.Generator().manual_seed(17)
+    for T in (16, 17, 4001, 4007):
+        mix = (0.1 * torch.randn(2, T, generator=g)).to(DEV)
+        with torch.no_grad():
+            y = model(mix)
+        assert y.shape == (2, 2, T)
+        K = (T - 16) // 8 + 1
+        covered = (K - 1) * 8 + 16
+        assert float(y[..., covered:].abs().sum()) == 0.0
