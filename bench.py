@@ -184,6 +184,7 @@ def run_b200(args):
     model = model.to(dev).eval()
     eng = model.engine()
     eng.micro_batch = args.micro_batch
+    eng.fuse_max_dilation = args.fuse
     eng.use_graph = bool(args.graph)
 
     g = torch.Generator().manual_seed(2025 + rank)
@@ -360,6 +361,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--micro-batch", type=int, default=64)
+    ap.add_argument("--fuse", type=int, default=32,
+                    help="blocks with dilation <= this use the fused depthwise+pointwise kernel (0 = off)")
     ap.add_argument("--graph", type=int, default=1)
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-train", action="store_true", help="skip the train-step leg")

@@ -1,0 +1,583 @@
+// Depthwise stage of a TemporalBlock fused into the pointwise 1x1 convolution (inference):
+//     a -> PReLU -> gLN-1 -> depthwise conv (P = 3, dilation d) -> PReLU -> q     conv_tasnet.py:218-253
+//     y = (W2 diag(gamma2)) q                                                    conv_tasnet.py:254-256
+// q never reaches HBM: SIMT producer warps compute 128 frames x 64 channels of q, split it
+// into the bf16 (hi, lo) pair and store it 128B-swizzled, K-major into the shared-memory
+// stage the tcgen05 MMAs read as their A operand (the layout a TMA load would have written).
+//
+// gLN-2 normalises q with the statistics of the WHOLE utterance, which exist only when every
+// tile of q has been produced.  The normalisation is already an epilogue affine of the folded
+// weight (ctn_weight_prep: W(gamma (q - mu) r + beta) = r (W gamma) q - r mu rowsum + W beta), so
+// it is deferred: this kernel writes the raw product y and the (sum, sumsq) partials of q, and
+// ctn_resid_update applies  x += r y - r mu rowsum + W beta  once the partials are complete.
+//
+// Tiles are not runs of consecutive frames.  Thread (quad, s) of a producer group owns four
+// channels and tile rows 16 s .. 16 s + 15, which are the frames  ph + d (j0 + jj)  of ONE
+// dilation phase: the three taps of consecutive outputs are consecutive elements of that
+// sequence, so each input row is loaded, PReLU'd and normalised once and reused from a 3-deep
+// register window (18 loads per 16 outputs, for every dilation).  A GEMM row may be any frame:
+// the epilogue thread that owns TMEM lane r simply stores to the row of frame(r).
+//
+// CTA pair (cta_group::2) as in gemm.cu: each CTA owns a 128-row tile and loads half of the
+// 256-column weight tile.  Warps: 0 TMA (weights), 1 MMA issuer, 2-5 epilogue, 6-13 producers
+// (two groups of four warps working on alternate k-blocks).
+#include <cuda.h>
+#include <stdlib.h>
+
+#include <type_traits>
+
+#include "common.cuh"
+#include "f32x2.cuh"
+#include "ptx.cuh"
+
+namespace ctn {
+
+int make_tmap_bf16_kmajor(CUtensorMap* tm, const void* ptr, long long rows, int cols, int box_rows);  // gemm.cu
+
+namespace fb {
+
+constexpr int kBM = 128;             // tile rows = TMEM lanes
+constexpr int kBN = 256;             // output channels (B) per tile = whole pointwise output
+constexpr int kBK = 64;              // channels per k-block = one 128 B swizzle atom of bf16
+constexpr int kStages = 3;
+constexpr int kABytes = kBM * kBK * 2;           // one of hi / lo
+constexpr int kWBytes = (kBN / 2) * kBK * 2;     // this CTA's half of the weight tile, one of hi / lo
+constexpr int kStageBytes = 2 * kABytes + 2 * kWBytes;
+constexpr int kEpiWarps = 4;
+constexpr int kProdWarps = 8;        // 256 threads = 32 channel pairs x 8 row segments of a k-block
+constexpr int kThreads = 64 + 32 * (kEpiWarps + kProdWarps);
+constexpr int kBarBytes = 256;
+constexpr int kStgRowBytes = 128 + 16;   // one 32-column fp32 chunk of a row; the pad spreads the rows over the banks
+constexpr int kStgBytes = kEpiWarps * 32 * kStgRowBytes;
+constexpr int kSmemFixed = kStages * kStageBytes + kBarBytes + kStgBytes;   // + 20 H bytes of per-channel constants
+constexpr int kSmemMax = 232448;
+constexpr int kRowsPerThread = 16;   // outputs a producer thread marches per k-block
+constexpr int kPartialsPerTile = kProdWarps;
+
+struct Params {
+    int K, H, d, c0;                 // frames, channels, dilation, taps before the output frame
+    int w, w_log2, jspan, n_ig, tiles_per_utt, row_tiles, items;
+    int in_P, out_P;
+    const float* a;
+    const float* prelu_in;
+    const float* gamma_in;
+    const float* beta_in;
+    const float2* in_stat;
+    const float* wd;
+    const float* prelu_out;
+    float* y;
+    float2* out_stat;
+    int dbg;
+};
+
+// frame of tile row r of tile tt (may be >= K: the row does not exist)
+__device__ __forceinline__ int tile_phase(const Params& p, int tt, int s) {
+    return (tt % p.n_ig) * p.w + (s & (p.w - 1));
+}
+__device__ __forceinline__ int tile_j0(const Params& p, int tt, int s) {
+    return (tt / p.n_ig) * p.jspan + (s >> p.w_log2) * kRowsPerThread;
+}
+
+__global__ void __launch_bounds__(kThreads, 1)
+dwpw_kernel(const __grid_constant__ CUtensorMap tm_w_hi, const __grid_constant__ CUtensorMap tm_w_lo, const Params p) {
+    const uint32_t rank = ptx::cluster_ctarank();
+    const int worker = static_cast<int>(blockIdx.x >> 1);
+    const int n_workers = static_cast<int>(gridDim.x >> 1);
+    extern __shared__ __align__(1024) uint8_t smem[];
+    if ((ptx::smem_u32(smem) & 1023u) != 0) __trap();
+    uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + kStages * kStageBytes);
+    uint64_t* empty_bar = full_bar + kStages;
+    uint64_t* tfull_bar = empty_bar + kStages;
+    uint64_t* tempty_bar = tfull_bar + 2;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 2);
+
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+    const int nkb = p.H / kBK;
+    // per-channel constants of the producers: gamma, beta and the three taps, [5][H]
+    float* cst = reinterpret_cast<float*>(smem + kStages * kStageBytes + kBarBytes + kStgBytes);
+    for (int i = threadIdx.x; i < p.H; i += kThreads) {
+        cst[i] = __ldg(p.gamma_in + i);
+        cst[p.H + i] = __ldg(p.beta_in + i);
+        cst[2 * p.H + i] = __ldg(p.wd + 3 * i);
+        cst[3 * p.H + i] = __ldg(p.wd + 3 * i + 1);
+        cst[4 * p.H + i] = __ldg(p.wd + 3 * i + 2);
+    }
+
+    if (warp == 0 && lane == 0) {
+        ptx::prefetch_tmap(&tm_w_hi);
+        ptx::prefetch_tmap(&tm_w_lo);
+        for (int i = 0; i < kStages; ++i) {
+            // leader: weight bytes of both CTAs (one expect_tx arrival) + one arrival per producer warp
+            // of the group that fills the stage, from both CTAs
+            ptx::mbar_init(full_bar + i, 1 + 2 * (kProdWarps / 2));
+            ptx::mbar_init(empty_bar + i, 1);
+        }
+        for (int i = 0; i < 2; ++i) {
+            ptx::mbar_init(tfull_bar + i, 1);
+            ptx::mbar_init(tempty_bar + i, 2 * kEpiWarps);
+        }
+        ptx::fence_mbar_init();
+    } else if (warp == 1) {
+        ptx::tmem_alloc_pair(tmem_slot, 2 * kBN);
+        ptx::tmem_relinquish_pair();
+    }
+    ptx::tc_fence_before();
+    ptx::cluster_sync();
+    ptx::tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        // ------------------------------------------------ TMA producer (weights only)
+        if (lane == 0) {
+            int stage = 0;
+            uint32_t phase = 0;
+            const uint32_t fb0 = ptx::mapa(ptx::smem_u32(full_bar), 0);
+            for (int item = worker; item < p.items; item += n_workers) {
+                for (int kb = 0; kb < nkb; ++kb) {
+                    ptx::mbar_wait(empty_bar + stage, phase ^ 1);
+                    uint8_t* st = smem + stage * kStageBytes + 2 * kABytes;
+                    if (rank == 0) ptx::mbar_expect_tx(full_bar + stage, 4 * kWBytes);
+                    ptx::tma_load_2d_pair(st, &tm_w_hi, fb0 + stage * 8, kb * kBK, static_cast<int>(rank) * (kBN / 2));
+                    ptx::tma_load_2d_pair(st + kWBytes, &tm_w_lo, fb0 + stage * 8, kb * kBK,
+                                          static_cast<int>(rank) * (kBN / 2));
+                    if (++stage == kStages) stage = 0, phase ^= 1;
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // -------------------------------------------------- MMA issuer (leader CTA)
+        if (lane == 0 && rank == 0) {
+            constexpr uint32_t idesc = ptx::make_idesc_bf16(2 * kBM, kBN, 0, 0);
+            int stage = 0;
+            uint32_t phase = 0;
+            int it = 0;
+            for (int item = worker; item < p.items; item += n_workers, ++it) {
+                const int as = it & 1;
+                const uint32_t aphase = (it >> 1) & 1;
+                ptx::mbar_wait(tempty_bar + as, aphase ^ 1);
+                ptx::tc_fence_after();
+                const uint32_t d_tmem = tmem_base + as * kBN;
+                for (int kb = 0; kb < nkb; ++kb) {
+                    ptx::mbar_wait(full_bar + stage, phase);
+                    ptx::tc_fence_after();
+                    const uint32_t sa = ptx::smem_u32(smem + stage * kStageBytes);
+                    const uint64_t a_hi = ptx::make_smem_desc(sa, 0, 1024, ptx::kLayoutSwizzle128B);
+                    const uint64_t a_lo = ptx::make_smem_desc(sa + kABytes, 0, 1024, ptx::kLayoutSwizzle128B);
+                    const uint64_t w_hi = ptx::make_smem_desc(sa + 2 * kABytes, 0, 1024, ptx::kLayoutSwizzle128B);
+                    const uint64_t w_lo = ptx::make_smem_desc(sa + 2 * kABytes + kWBytes, 0, 1024, ptx::kLayoutSwizzle128B);
+#pragma unroll
+                    for (int k = 0; k < ((p.dbg & 4) ? 0 : kBK / 16); ++k) {
+                        const uint64_t adv = static_cast<uint64_t>((k * 16 * 2) >> 4);
+                        ptx::umma_bf16_pair(d_tmem, a_hi + adv, w_hi + adv, idesc, (kb | k) != 0);
+                        ptx::umma_bf16_pair(d_tmem, a_lo + adv, w_hi + adv, idesc, 1);
+                        ptx::umma_bf16_pair(d_tmem, a_hi + adv, w_lo + adv, idesc, 1);
+                    }
+                    ptx::umma_commit_pair(empty_bar + stage, 3);
+                    if (kb == nkb - 1) ptx::umma_commit_pair(tfull_bar + as, 3);
+                    if (++stage == kStages) stage = 0, phase ^= 1;
+                }
+            }
+        }
+    } else if (warp < 2 + kEpiWarps) {
+        // ---------------------------------------------------- epilogue: TMEM -> y rows
+        const int ew = warp & 3;
+        const uint32_t tempty_remote = ptx::mapa(ptx::smem_u32(tempty_bar), 0);
+        const uint32_t stg_base = ptx::smem_u32(smem + kStages * kStageBytes + kBarBytes) + (warp - 2) * 32 * kStgRowBytes;
+        int it = 0;
+        for (int item = worker; item < p.items; item += n_workers, ++it) {
+            const int as = it & 1;
+            const uint32_t aphase = (it >> 1) & 1;
+            const int rt = 2 * item + static_cast<int>(rank);
+            const bool tile_ok = rt < p.row_tiles;
+            const int m = tile_ok ? rt / p.tiles_per_utt : 0, tt = tile_ok ? rt % p.tiles_per_utt : 0;
+            const int r = ew * 32 + lane;
+            const int s = r >> 4;
+            const int frame = tile_phase(p, tt, s) + p.d * (tile_j0(p, tt, s) + (r & 15));
+            const bool valid = tile_ok && frame < p.K;
+            float* yrow = p.y + (static_cast<long long>(m) * p.K + frame) * kBN;
+            ptx::mbar_wait(tfull_bar + as, aphase);
+            ptx::tc_fence_after();
+            if (!(p.dbg & 1)) {
+                // A lane owns one output row.  Its 32 columns of a chunk go to a private 128 B row of the
+                // warp's staging area and from there to global memory with ONE bulk copy by the async
+                // proxy: 256-bit stores straight from registers put 32 different lines per instruction
+                // through the LSU, which the producers' loads and stores need.
+                const uint32_t srow = stg_base + static_cast<uint32_t>(lane) * kStgRowBytes;
+#pragma unroll
+                for (int ci = 0; ci < kBN / 32; ++ci) {
+                    uint32_t v[32];
+                    ptx::tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(ew * 32) << 16) + as * kBN + ci * 32, v);
+                    if (p.dbg & 64) {   // experiment: 256-bit stores straight from registers
+                        ptx::tmem_ld_wait();
+                        if (valid) {
+#pragma unroll
+                            for (int j = 0; j < 4; ++j)
+                                ptx::st_global_v8(yrow + ci * 32 + 8 * j, v[8 * j], v[8 * j + 1], v[8 * j + 2], v[8 * j + 3],
+                                                  v[8 * j + 4], v[8 * j + 5], v[8 * j + 6], v[8 * j + 7]);
+                        }
+                        continue;
+                    }
+                    ptx::tma_store_wait_read<0>();          // the previous chunk's copy has read the staging row
+                    ptx::tmem_ld_wait();
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) ptx::st_shared_v4(srow + 16 * j, v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+                    ptx::fence_async_smem();
+                    if (valid && !(p.dbg & 2)) ptx::bulk_store(yrow + ci * 32, srow, 128);
+                    ptx::tma_store_commit();
+                }
+            }
+            ptx::tc_fence_before();
+            __syncwarp();
+            if (lane == 0) ptx::mbar_arrive_cluster(tempty_remote + as * 8);
+        }
+        ptx::tma_store_wait_all<0>();   // shared memory must outlive the copies that read it
+    } else {
+        // ---------------------------------------------------- q producers
+        // Two groups of four warps work on alternate k-blocks.  Thread (quad, s) of a group owns four
+        // channels and tile rows 16 s .. 16 s + 15 of the group's k-block ("unit"): 18 input rows,
+        // 16 outputs.  Input rows stream through a 9-deep register ring that runs ahead across unit
+        // and tile boundaries, so loads are in flight all the time.  Interior units (all 18 rows
+        // inside the utterance) take a path without any predicate.
+        const int pw = warp - 2 - kEpiWarps;                   // 0 .. 7
+        const int grp = pw >> 2;                               // k-blocks kb = grp, grp + 2, ...
+        const int pt = (pw & 3) * 32 + lane;                   // 0 .. 127 within the group
+        const int quad = pt & 15, s = pt >> 4;
+        const uint32_t full_remote = ptx::mapa(ptx::smem_u32(full_bar), 0);
+        const float a1 = __ldg(p.prelu_in), a2 = __ldg(p.prelu_out);
+        const f2_t a1m1 = f2_pack(a1 - 1.f, a1 - 1.f), a2m1 = f2_pack(a2 - 1.f, a2 - 1.f);
+        const f2_t neg1 = f2_pack(-1.f, -1.f), one2 = f2_pack(1.f, 1.f);
+        // byte offset of this thread's 8 bytes inside a [128 x 64] bf16 tile, for row 16 s + jj:
+        // 128 B rows, 16 B chunks XOR-swizzled with (row & 7)
+        const uint32_t row_off0 = static_cast<uint32_t>(s * kRowsPerThread) * 128u;
+        const uint32_t cs = static_cast<uint32_t>(quad >> 1) * 16u + static_cast<uint32_t>(quad & 1) * 8u;
+        const long long strd = static_cast<long long>(p.d) * p.H;
+        constexpr int kRing = (kRowsPerThread + 2) / 2;        // 9
+
+        struct Tile {          // this thread's view of one tile
+            const float* base; // row t = 0 of k-block 0 (may point before the buffer)
+            int lo, hi;        // rows t in [lo, hi) exist (inside the utterance and needed)
+            int n;             // outputs
+        };
+        auto tile_setup = [&](int item, int& m, int& tt) {
+            Tile T;
+            const int rt = 2 * item + static_cast<int>(rank);
+            const bool ok = item < p.items && rt < p.row_tiles;
+            m = ok ? rt / p.tiles_per_utt : 0;
+            tt = ok ? rt % p.tiles_per_utt : -1;
+            const int ph = tile_phase(p, max(tt, 0), s);
+            const int j0 = tile_j0(p, max(tt, 0), s);
+            const int J = ph < p.K ? (p.K - ph + p.d - 1) / p.d : 0;   // frames of this phase
+            T.n = ok ? max(0, min(kRowsPerThread, J - j0)) : 0;
+            const int r0 = j0 - p.c0;                                  // sequence index of window row t = 0
+            T.lo = max(0, -r0);
+            T.hi = T.n > 0 ? min(T.n + 2, J - r0) : 0;
+            T.base = p.a + (static_cast<long long>(m) * p.K + ph + static_cast<long long>(r0) * p.d) * p.H + quad * 4;
+            return T;
+        };
+        // volatile: ptxas otherwise sinks the ring refills down to their first use to save registers,
+        // which turns the prefetch ring into synchronous loads
+        auto ld_row = [](const float* ptr) {
+            float4 v;
+            asm volatile("ld.volatile.global.v4.f32 {%0, %1, %2, %3}, [%4];"
+                         : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+                         : "l"(ptr)
+                         : "memory");
+            return v;
+        };
+        auto is_full = [](const Tile& T) { return T.lo == 0 && T.hi == kRowsPerThread + 2; };
+
+        int cur_m = -1, m, tt;
+        float mean = 0.f, rstd = 1.f;
+        Tile T = tile_setup(worker, m, tt);
+        float4 q[kRing];
+        {
+            const float* b0 = T.base + grp * kBK;
+#pragma unroll
+            for (int t = 0; t < kRing; ++t) {
+                q[t] = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (t >= T.lo && t < T.hi) q[t] = ld_row(b0 + t * strd);
+            }
+        }
+        int it = 0;
+        for (int item = worker; item < p.items; item += n_workers, ++it) {
+            if (m != cur_m) {
+                const float2 st = gln_finalize_warp(p.in_stat + static_cast<long long>(m) * p.in_P, p.in_P,
+                                                    static_cast<double>(p.K) * p.H);
+                mean = st.x, rstd = st.y;
+                cur_m = m;
+            }
+            Tile Tn = T;
+            int mn_ = m, ttn = tt;
+            f2_t ls[2] = {0ull, 0ull}, lss[2] = {0ull, 0ull};
+            for (int kb = grp; kb < nkb; kb += 2) {
+                const int nblk = it * nkb + kb;                        // k-blocks this CTA has consumed so far
+                const int stage = nblk % kStages;
+                const uint32_t phase = (nblk / kStages) & 1;
+                const bool last_kb = kb + 2 >= nkb;
+                if (last_kb) Tn = tile_setup(item + n_workers, mn_, ttn);
+                // rows kRing .. 17 of this unit, then rows 0 .. kRing-1 of the thread's next unit
+                const float* pc = T.base + kb * kBK + kRing * strd;
+                const float* pn = Tn.base + (last_kb ? grp : kb + 2) * kBK;
+                const int c = kb * kBK + quad * 4;
+                const bool fast = is_full(T) && is_full(Tn);
+                // per-channel constants.  Interior units fold the norm into the taps:
+                //   d = sum_t w_t (A pv_t + B) = sum_t (w_t A) pv_t + B (w_0 + w_1 + w_2),  pv = PReLU(v)
+                // boundary units keep n1 = A pv + B explicit, because the zero padding applies to n1.
+                f2_t A[2], Bc[2], w0[2], w1[2], w2[2];
+                {
+                    const float4 g = *reinterpret_cast<const float4*>(cst + c);
+                    const float4 b = *reinterpret_cast<const float4*>(cst + p.H + c);
+                    const float4 u0 = *reinterpret_cast<const float4*>(cst + 2 * p.H + c);
+                    const float4 u1 = *reinterpret_cast<const float4*>(cst + 3 * p.H + c);
+                    const float4 u2 = *reinterpret_cast<const float4*>(cst + 4 * p.H + c);
+                    const float Af[4] = {g.x * rstd, g.y * rstd, g.z * rstd, g.w * rstd};
+                    const float Bf[4] = {b.x - Af[0] * mean, b.y - Af[1] * mean, b.z - Af[2] * mean, b.w - Af[3] * mean};
+                    // f[3 ch + t]: tap t of channel ch
+                    const float f[12] = {u0.x, u1.x, u2.x, u0.y, u1.y, u2.y, u0.z, u1.z, u2.z, u0.w, u1.w, u2.w};
+#pragma unroll
+                    for (int i = 0; i < 2; ++i) {
+                        A[i] = f2_pack(Af[2 * i], Af[2 * i + 1]);
+                        const f2_t Bp = f2_pack(Bf[2 * i], Bf[2 * i + 1]);
+                        const f2_t r0 = f2_pack(f[6 * i], f[6 * i + 3]), r1 = f2_pack(f[6 * i + 1], f[6 * i + 4]);
+                        const f2_t r2 = f2_pack(f[6 * i + 2], f[6 * i + 5]);
+                        // products of packed multiplies are born as register pairs (packing loaded scalars at
+                        // every use costs two moves per operand)
+                        const f2_t sc = fast ? A[i] : one2;
+                        w0[i] = f2_mul(r0, sc), w1[i] = f2_mul(r1, sc), w2[i] = f2_mul(r2, sc);
+                        Bc[i] = fast ? f2_mul(Bp, f2_add(f2_add(r0, r1), r2)) : f2_mul(Bp, one2);
+                    }
+                }
+                ptx::mbar_wait(empty_bar + stage, phase ^ 1);
+                const uint32_t hi_base = ptx::smem_u32(smem + stage * kStageBytes) + row_off0;
+
+                auto unit = [&](auto fast_tag) {
+                    constexpr bool kFast = decltype(fast_tag)::value;
+                    // row t -> pv = PReLU(v) (interior) or n1 = A pv + B, zero outside the utterance
+                    // (boundary); then the ring slot is refilled
+                    auto xform = [&](int t, f2_t (&o)[2]) {
+                        const float4 v = q[t % kRing];
+                        const f2_t v2[2] = {f2_pack(v.x, v.y), f2_pack(v.z, v.w)};
+                        const f2_t mn[2] = {f2_pack(fminf(v.x, 0.f), fminf(v.y, 0.f)), f2_pack(fminf(v.z, 0.f), fminf(v.w, 0.f))};
+#pragma unroll
+                        for (int i = 0; i < 2; ++i) {
+                            o[i] = f2_fma(a1m1, mn[i], v2[i]);
+                            if (!kFast) o[i] = (t >= T.lo && t < T.hi) ? f2_fma(A[i], o[i], Bc[i]) : 0ull;
+                        }
+                        if (t < kRing) {
+                            if (kFast || (t + kRing >= T.lo && t + kRing < T.hi)) q[t % kRing] = ld_row(pc);
+                            pc += strd;
+                        } else {
+                            if (kFast || (t - kRing >= Tn.lo && t - kRing < Tn.hi))
+                                q[t % kRing] = ld_row(pn);
+                            else
+                                q[t % kRing] = make_float4(0.f, 0.f, 0.f, 0.f);
+                            pn += strd;
+                        }
+                    };
+                    f2_t x0[2], x1[2], x2[2];
+                    xform(0, x0);
+                    xform(1, x1);
+#pragma unroll
+                    for (int o = 0; o < kRowsPerThread; ++o) {
+                        xform(o + 2, x2);
+                        uint32_t h[2], l[2];
+#pragma unroll
+                        for (int i = 0; i < 2; ++i) {
+                            const f2_t acc = kFast ? f2_fma(w2[i], x2[i], f2_fma(w1[i], x1[i], f2_fma(w0[i], x0[i], Bc[i])))
+                                                   : f2_fma(w2[i], x2[i], f2_fma(w1[i], x1[i], f2_mul(w0[i], x0[i])));
+                            float c0, c1;
+                            f2_unpack(acc, c0, c1);
+                            f2_t qq = f2_fma(a2m1, f2_pack(fminf(c0, 0.f), fminf(c1, 0.f)), acc);   // PReLU
+                            if (!kFast && o >= T.n) qq = 0ull;
+                            ls[i] = f2_add(ls[i], qq);
+                            lss[i] = f2_fma(qq, qq, lss[i]);
+                            f2_split_bf16(qq, neg1, h[i], l[i]);
+                            x0[i] = x1[i], x1[i] = x2[i];
+                        }
+                        // row 16 s + o of the tile: 128 B rows, the 16 B chunk index XOR (row & 7) = XOR (o & 7).
+                        // hi_base is 1024-aligned, so the XOR can be applied to the whole address.
+                        const uint32_t ad = ((hi_base + cs) ^ (static_cast<uint32_t>(o & 7) << 4)) + static_cast<uint32_t>(o) * 128u;
+                        asm volatile("st.volatile.shared.v2.b32 [%0], {%1, %2};" ::"r"(ad), "r"(h[0]), "r"(h[1]) : "memory");
+                        asm volatile("st.volatile.shared.v2.b32 [%0], {%1, %2};" ::"r"(ad + kABytes), "r"(l[0]), "r"(l[1]) : "memory");
+                    }
+                };
+                if (fast) unit(std::true_type{});
+                else unit(std::false_type{});
+                ptx::fence_async_smem();      // generic-proxy stores -> visible to the tensor core (async proxy)
+                __syncwarp();
+                if (lane == 0) ptx::mbar_arrive_cluster(full_remote + stage * 8);
+            }
+            // (sum, sumsq) of this warp's share of the tile, all k-blocks of its group
+            float s0, s1, s2, s3, t0, t1, t2, t3;
+            f2_unpack(ls[0], s0, s1), f2_unpack(ls[1], s2, s3);
+            f2_unpack(lss[0], t0, t1), f2_unpack(lss[1], t2, t3);
+            const float wls = warp_sum((s0 + s1) + (s2 + s3));
+            const float wlss = warp_sum((t0 + t1) + (t2 + t3));
+            if (lane == 0 && tt >= 0)
+                p.out_stat[static_cast<long long>(m) * p.out_P + tt * kPartialsPerTile + pw] = make_float2(wls, wlss);
+            T = Tn, m = mn_, tt = ttn;
+        }
+    }
+
+    ptx::tc_fence_before();
+    ptx::cluster_sync();
+    if (warp == 1) {
+        ptx::tc_fence_after();
+        ptx::tmem_dealloc_pair(tmem_base, 2 * kBN);
+    }
+}
+
+// x += r y - r mu rowsum + W beta  (the deferred gLN-2 + residual, conv_tasnet.py:254-256, :237) on
+// the (hi, lo) residual stream, in place.  One thread owns 8 channels of a row.
+constexpr int kUpdThreads = 256;
+constexpr int kUpdRows = 64;   // rows per CTA
+
+__global__ void __launch_bounds__(kUpdThreads)
+resid_update_kernel(__nv_bfloat16* __restrict__ x_hi, __nv_bfloat16* __restrict__ x_lo, const float* __restrict__ y,
+                    const float2* __restrict__ stat, int P, double count, const float* __restrict__ col_g,
+                    const float* __restrict__ col_bias, int K, int B) {
+    __shared__ double red[2 * (kUpdThreads / 32)];
+    const int m = blockIdx.y;
+    const float2 st = gln_finalize_block(stat + static_cast<long long>(m) * P, P, count, red);
+    const float sc = st.y, sh = -st.y * st.x;
+    const int tpr = B / 8;                       // threads per row
+    const int rpp = kUpdThreads / tpr;           // rows per pass
+    const int c = (threadIdx.x % tpr) * 8;
+    float cc[8];
+    {
+        const float4 g0 = __ldg(reinterpret_cast<const float4*>(col_g + c)), g1 = __ldg(reinterpret_cast<const float4*>(col_g + c + 4));
+        const float4 b0 = __ldg(reinterpret_cast<const float4*>(col_bias + c)), b1 = __ldg(reinterpret_cast<const float4*>(col_bias + c + 4));
+        cc[0] = fmaf(sh, g0.x, b0.x), cc[1] = fmaf(sh, g0.y, b0.y), cc[2] = fmaf(sh, g0.z, b0.z), cc[3] = fmaf(sh, g0.w, b0.w);
+        cc[4] = fmaf(sh, g1.x, b1.x), cc[5] = fmaf(sh, g1.y, b1.y), cc[6] = fmaf(sh, g1.z, b1.z), cc[7] = fmaf(sh, g1.w, b1.w);
+    }
+    const int k0 = blockIdx.x * kUpdRows;
+    const int k1 = min(K, k0 + kUpdRows);
+    for (int k = k0 + threadIdx.x / tpr; k < k1; k += rpp) {
+        const long long o = (static_cast<long long>(m) * K + k) * B + c;
+        const uint4 h = *reinterpret_cast<const uint4*>(x_hi + o);
+        const uint4 l = *reinterpret_cast<const uint4*>(x_lo + o);
+        float yv[8];
+        ptx::ld_global_v8(y + o, yv);
+        const uint32_t hw[4] = {h.x, h.y, h.z, h.w}, lw[4] = {l.x, l.y, l.z, l.w};
+        uint32_t oh[4], ol[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const float x0 = __uint_as_float(hw[j] << 16) + __uint_as_float(lw[j] << 16);
+            const float x1 = __uint_as_float(hw[j] & 0xffff0000u) + __uint_as_float(lw[j] & 0xffff0000u);
+            const float v0 = fmaf(sc, yv[2 * j], cc[2 * j]) + x0;
+            const float v1 = fmaf(sc, yv[2 * j + 1], cc[2 * j + 1]) + x1;
+            split_pack2(v0, v1, oh[j], ol[j]);
+        }
+        *reinterpret_cast<uint4*>(x_hi + o) = make_uint4(oh[0], oh[1], oh[2], oh[3]);
+        *reinterpret_cast<uint4*>(x_lo + o) = make_uint4(ol[0], ol[1], ol[2], ol[3]);
+    }
+}
+
+struct Geometry {
+    int w, w_log2, jspan, n_ig, tiles_per_utt;
+};
+
+static Geometry geometry(int K, int d) {
+    Geometry g;
+    g.w = d < 8 ? d : 8;
+    g.w_log2 = 0;
+    while ((1 << g.w_log2) < g.w) ++g.w_log2;
+    g.jspan = kRowsPerThread * (8 / g.w);
+    g.n_ig = d / g.w;
+    const int Jtot = ceil_div(K, d);
+    g.tiles_per_utt = g.n_ig * ceil_div(Jtot, g.jspan);
+    return g;
+}
+
+}  // namespace fb
+}  // namespace ctn
+
+using namespace ctn;
+
+extern "C" int ctn_dwpw_partials(int K, int dilation) {
+    if (K <= 0 || dilation <= 0 || (dilation & (dilation - 1)) != 0) return 0;
+    return fb::geometry(K, dilation).tiles_per_utt * fb::kPartialsPerTile;
+}
+
+extern "C" int ctn_dwpw_supported(int H, int B, int P, int dilation, int norm) {
+    return norm == CTN_NORM_GLN && P == 3 && B == fb::kBN && H % fb::kBK == 0 && H >= fb::kBK &&
+           fb::kSmemFixed + 20 * H <= fb::kSmemMax && dilation > 0 &&
+           (dilation & (dilation - 1)) == 0;
+}
+
+extern "C" int ctn_dwpw_fwd(const ctn_dwpw_args* args, void* stream_) {
+    CTN_REQUIRE(args != nullptr, "ctn_dwpw_fwd: args is NULL");
+    const ctn_dwpw_args& a = *args;
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    CTN_REQUIRE(a.M > 0 && a.K > 0, "ctn_dwpw_fwd: non-positive shape M=%d K=%d", a.M, a.K);
+    CTN_REQUIRE(ctn_dwpw_supported(a.H, a.B, 3, a.dilation, CTN_NORM_GLN),
+                "ctn_dwpw_fwd: needs B == 256, H %% 64 == 0 and a power-of-two dilation (H=%d B=%d dilation=%d)", a.H, a.B,
+                a.dilation);
+    CTN_REQUIRE(static_cast<long long>(a.M) * a.K < (1ll << 31), "ctn_dwpw_fwd: M*K exceeds 2^31 rows");
+    CTN_REQUIRE(a.a && a.prelu_in && a.gamma_in && a.beta_in && a.in_stat && a.in_P > 0 && a.wd && a.prelu_out && a.w_hi &&
+                    a.w_lo && a.y && a.out_stat,
+                "ctn_dwpw_fwd: NULL argument");
+    auto aligned16 = [](const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; };
+    CTN_REQUIRE(aligned16(a.a) && aligned16(a.gamma_in) && aligned16(a.beta_in) && aligned16(a.wd) && aligned16(a.w_hi) &&
+                    aligned16(a.w_lo) && (reinterpret_cast<uintptr_t>(a.y) & 31) == 0,
+                "ctn_dwpw_fwd: buffers must be 16-byte aligned (y: 32)");
+    const fb::Geometry g = fb::geometry(a.K, a.dilation);
+    fb::Params p;
+    p.K = a.K, p.H = a.H, p.d = a.dilation, p.c0 = a.causal ? 2 : 1;
+    p.w = g.w, p.w_log2 = g.w_log2, p.jspan = g.jspan, p.n_ig = g.n_ig, p.tiles_per_utt = g.tiles_per_utt;
+    p.row_tiles = a.M * g.tiles_per_utt;
+    p.items = ceil_div(p.row_tiles, 2);
+    p.in_P = a.in_P, p.out_P = g.tiles_per_utt * fb::kPartialsPerTile;
+    p.a = a.a, p.prelu_in = a.prelu_in, p.gamma_in = a.gamma_in, p.beta_in = a.beta_in;
+    p.in_stat = static_cast<const float2*>(a.in_stat);
+    p.wd = a.wd, p.prelu_out = a.prelu_out, p.y = a.y, p.out_stat = static_cast<float2*>(a.out_stat);
+    {
+        const char* d = getenv("CTN_GEMM_DBG");
+        p.dbg = d ? atoi(d) : 0;
+    }
+    CUtensorMap tw_hi, tw_lo;
+    int rc;
+    if ((rc = make_tmap_bf16_kmajor(&tw_hi, a.w_hi, a.B, a.H, fb::kBN / 2)) != CTN_OK) return rc;
+    if ((rc = make_tmap_bf16_kmajor(&tw_lo, a.w_lo, a.B, a.H, fb::kBN / 2)) != CTN_OK) return rc;
+    static bool attr_set = false;
+    if (!attr_set) {
+        cudaError_t e = cudaFuncSetAttribute(fb::dwpw_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, fb::kSmemMax);
+        if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(dwpw_kernel)");
+        attr_set = true;
+    }
+    const int workers_max = sm_count() / 2;
+    const int workers = p.items < workers_max ? p.items : workers_max;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(2 * workers, 1, 1);
+    cfg.blockDim = dim3(fb::kThreads, 1, 1);
+    cfg.dynamicSmemBytes = (fb::kSmemFixed + 20 * a.H);
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 2;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    cudaError_t e = cudaLaunchKernelEx(&cfg, fb::dwpw_kernel, tw_hi, tw_lo, p);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaLaunchKernelEx(dwpw_kernel)");
+    return CTN_OK;
+}
+
+extern "C" int ctn_resid_update(void* x_hi, void* x_lo, const float* y, const void* stat, int P, double count,
+                                const float* col_g, const float* col_bias, int M, int K, int B, void* stream_) {
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    CTN_REQUIRE(M > 0 && K > 0 && B > 0 && B % 8 == 0 && B <= 8 * fb::kUpdThreads && (8 * fb::kUpdThreads) % B == 0,
+                "ctn_resid_update: bad shape M=%d K=%d B=%d (B must divide 2048 and be a multiple of 8)", M, K, B);
+    CTN_REQUIRE(x_hi && x_lo && y && stat && P > 0 && count > 0 && col_g && col_bias, "ctn_resid_update: NULL argument");
+    auto aligned = [](const void* p, int n) { return (reinterpret_cast<uintptr_t>(p) & (n - 1)) == 0; };
+    CTN_REQUIRE(aligned(x_hi, 16) && aligned(x_lo, 16) && aligned(y, 32) && aligned(col_g, 16) && aligned(col_bias, 16),
+                "ctn_resid_update: buffers must be 16-byte aligned (y: 32)");
+    dim3 grid(ceil_div(K, fb::kUpdRows), M);
+    fb::resid_update_kernel<<<grid, fb::kUpdThreads, 0, stream>>>(
+        static_cast<__nv_bfloat16*>(x_hi), static_cast<__nv_bfloat16*>(x_lo), y, static_cast<const float2*>(stat), P, count,
+        col_g, col_bias, K, B);
+    CTN_LAUNCH_CHECK("resid_update_kernel");
+    return CTN_OK;
+}

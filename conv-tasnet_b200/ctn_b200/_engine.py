@@ -80,8 +80,9 @@ class _Prepared:
 class _Plan:
     """Static workspaces + call list for one (M, T) on one device."""
 
-    def __init__(self, cfg, M, T, device):
+    def __init__(self, cfg, M, T, device, fuse_max_dilation=0):
         self.cfg, self.M, self.T, self.device = cfg, M, T, device
+        self.fuse_max_dilation = fuse_max_dilation
         N, L, B, H, C = cfg["N"], cfg["L"], cfg["B"], cfg["H"], cfg["C"]
         self.hop, self.K, self.T_conv = frame_geometry(T, L)
         K = self.K
@@ -111,6 +112,16 @@ class _Plan:
             self.P2s = [1] * cfg["X"]
             self.stat1 = torch.zeros(R_, self.P1, 2, **f32)
             self.stat2 = torch.zeros(R_, 2, **f32)
+        # fused depthwise + pointwise path (ctn_dwpw_fwd + ctn_resid_update) for blocks with dilation <=
+        # fuse_max_dilation, where the configuration allows it
+        self.fused = [False] * cfg["X"]
+        if self.norm == nat.NORM_GLN and fuse_max_dilation > 0:
+            self.fused = [2 ** x <= fuse_max_dilation and bool(lib.ctn_dwpw_supported(H, B, cfg["P"], 2 ** x, self.norm))
+                          for x in range(cfg["X"])]
+        if any(self.fused):
+            self.y = torch.empty(R_, B, **f32)
+            self.P2f = [lib.ctn_dwpw_partials(K, 2 ** x) for x in range(cfg["X"])]
+            self.stat2f = torch.zeros(M, max(self.P2f), 2, **f32)
         self.calls = None
         self.param_ptrs = None
         self.graph = None
@@ -155,11 +166,31 @@ class _Plan:
                 pb = prep.blocks[i]
                 i += 1
                 info.append(("gemm_conv1x1", 2.0 * Rr * B * H, 4.0 * Rr * B + 4.0 * Rr * H))
-                info.append(("dwconv", 2.0 * Rr * H * cfg["P"], 8.0 * Rr * H))
-                info.append(("gemm_pointwise", 2.0 * Rr * B * H, 4.0 * Rr * H + 8.0 * Rr * B))
+                if self.fused[xb]:
+                    info.append(("gemm_dwpw_fused", 2.0 * Rr * B * H + 2.0 * Rr * H * cfg["P"], 4.0 * Rr * H + 4.0 * Rr * B))
+                    info.append(("resid_update", 2.0 * Rr * B, 12.0 * Rr * B))
+                else:
+                    info.append(("dwconv", 2.0 * Rr * H * cfg["P"], 8.0 * Rr * H))
+                    info.append(("gemm_pointwise", 2.0 * Rr * B * H, 4.0 * Rr * H + 8.0 * Rr * B))
                 calls.append(self._gemm(Cin=B, Cout=H, a_hi=self.x_hl[0], a_lo=self.x_hl[1], w_hi=pb["w1"][0],
                                         w_lo=pb["w1"][1], out_f32=self.a, out_stat=self.norm,
                                         out_stat_buf=self.stat1, stat_prelu=params[k["a1"]]))
+                if self.fused[xb]:
+                    f = nat.DwpwArgs()
+                    f.M, f.K, f.H, f.B, f.dilation, f.causal = M, K, H, B, 2 ** xb, int(bool(cfg["causal"]))
+                    f.a, f.prelu_in = self.a.data_ptr(), params[k["a1"]].data_ptr()
+                    f.gamma_in, f.beta_in = params[k["g1"]].data_ptr(), params[k["b1"]].data_ptr()
+                    f.in_stat, f.in_P = self.stat1.data_ptr(), self.P1
+                    f.wd, f.prelu_out = params[k["wd"]].data_ptr(), params[k["a2"]].data_ptr()
+                    f.w_hi, f.w_lo = pb["w2"][0].data_ptr(), pb["w2"][1].data_ptr()
+                    f.y, f.out_stat = self.y.data_ptr(), self.stat2f.data_ptr()
+                    self._keep.append(f)
+                    fw, upd = lib.ctn_dwpw_fwd, lib.ctn_resid_update
+                    calls.append(lambda s, ref=C.byref(f): fw(ref, s))
+                    u = (self.x_hl[0].data_ptr(), self.x_hl[1].data_ptr(), self.y.data_ptr(), self.stat2f.data_ptr(),
+                         self.P2f[xb], float(K) * H, pb["w2"][2].data_ptr(), pb["w2"][3].data_ptr(), M, K, B)
+                    calls.append(lambda s, u=u: upd(*u, s))
+                    continue
                 d = nat.DwconvArgs()
                 d.M, d.K, d.H, d.P, d.dilation, d.causal = M, K, H, cfg["P"], 2 ** xb, int(bool(cfg["causal"]))
                 d.inp, d.prelu_in = self.a.data_ptr(), params[k["a1"]].data_ptr()
@@ -232,14 +263,19 @@ class SeparationEngine:
         self.plans = {}
         self.micro_batch = 16
         self.use_graph = False
+        # blocks with dilation <= this take the fused depthwise + pointwise kernel where the configuration
+        # allows it (0 = never).  Beyond 32 every producer unit touches an utterance boundary and the
+        # unfused pair is faster.
+        self.fuse_max_dilation = 32
         self.launches = 0   # kernels of libctn_b200 launched by forward() so far
 
     def num_launches(self):
-        """Kernel launches of one plan execution (encoder + bottleneck + 3 per block + mask + decoder)."""
+        """Kernel launches of one plan execution (encoder + bottleneck + 3 per block + mask + decoder;
+        the fused path also has 3 per block: conv1x1, depthwise+pointwise, residual update)."""
         return 4 + 3 * self.cfg["R"] * self.cfg["X"]
 
     def _plan(self, params, M, T, device):
-        key = (device.index, M, T)
+        key = (device.index, M, T, self.fuse_max_dilation)
         prep = self.prepared.get(device.index)
         if prep is None:
             prep = self.prepared[device.index] = _Prepared(self.cfg, device)
@@ -247,7 +283,7 @@ class SeparationEngine:
         prep.refresh(self.cfg, params)
         plan = self.plans.get(key)
         if plan is None:
-            plan = self.plans[key] = _Plan(self.cfg, M, T, device)
+            plan = self.plans[key] = _Plan(self.cfg, M, T, device, self.fuse_max_dilation)
         ptrs = tuple(p.data_ptr() for p in params.values())
         if plan.calls is None or plan.param_ptrs != ptrs:
             plan.build(params, prep)

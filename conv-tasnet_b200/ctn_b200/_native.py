@@ -45,6 +45,15 @@ class DwconvArgs(C.Structure):
     ]
 
 
+class DwpwArgs(C.Structure):
+    """struct ctn_dwpw_args"""
+    _fields_ = [
+        ("M", C.c_int), ("K", C.c_int), ("H", C.c_int), ("B", C.c_int), ("dilation", C.c_int), ("causal", C.c_int),
+        ("a", _vp), ("prelu_in", _vp), ("gamma_in", _vp), ("beta_in", _vp), ("in_stat", _vp), ("in_P", C.c_int),
+        ("wd", _vp), ("prelu_out", _vp), ("w_hi", _vp), ("w_lo", _vp), ("y", _vp), ("out_stat", _vp),
+    ]
+
+
 class BwdDwArgs(C.Structure):
     """struct ctn_bwd_dw_args"""
     _fields_ = [
@@ -113,6 +122,10 @@ _SIGNATURES = {
     "ctn_encoder_fwd": (C.c_int, [_vp, _vp, C.c_int, C.c_int, C.c_int, C.c_int, _vp, _vp, _vp, _vp, _vp]),
     "ctn_gemm1x1": (C.c_int, [C.POINTER(GemmArgs), _vp]),
     "ctn_dwconv_fwd": (C.c_int, [C.POINTER(DwconvArgs), _vp]),
+    "ctn_dwpw_supported": (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_int, C.c_int]),
+    "ctn_dwpw_partials": (C.c_int, [C.c_int, C.c_int]),
+    "ctn_dwpw_fwd": (C.c_int, [C.POINTER(DwpwArgs), _vp]),
+    "ctn_resid_update": (C.c_int, [_vp, _vp, _vp, _vp, C.c_int, C.c_double, _vp, _vp, C.c_int, C.c_int, C.c_int, _vp]),
     "ctn_decoder_fwd": (C.c_int, [_vp, _vp, _vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
                                   _vp, _vp]),
     "ctn_overlap_add": (C.c_int, [_vp, C.c_int, C.c_int, C.c_int, C.c_int, _vp, _vp]),

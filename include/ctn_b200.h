@@ -155,6 +155,38 @@ typedef struct ctn_dwconv_args {
  * :175-176,247-252,275-289), second PReLU, statistics for the second norm. */
 int ctn_dwconv_fwd(const ctn_dwconv_args* args, void* stream);
 
+typedef struct ctn_dwpw_args {
+    int M, K, H, B;         /* a is [M*K, H], y is [M*K, B]; B == 256, H % 64 == 0              */
+    int dilation, causal;   /* power-of-two dilation, P = 3                                    */
+    const float* a;         /* conv1x1 output, fp32 [M*K, H]                                   */
+    const float* prelu_in;  /* slope of the first PReLU (device scalar), conv_tasnet.py:218    */
+    const float *gamma_in, *beta_in; /* gLN-1 affine [H], :219                                 */
+    const void* in_stat;    /* float2 [M, in_P]: gLN-1 partials (ctn_gemm1x1 out_stat)         */
+    int in_P;
+    const float* wd;        /* depthwise weight [H, 3], :247-250                               */
+    const float* prelu_out; /* slope of the second PReLU, :253                                 */
+    const void *w_hi, *w_lo;/* pointwise weight with gamma-2 folded (ctn_weight_prep), [B, H]  */
+    float* y;               /* out: (W2 diag gamma2) q, fp32 [M*K, B]: NOT yet normalised      */
+    void* out_stat;         /* out: float2 [M, ctn_dwpw_partials(K, dilation)] partials of q   */
+} ctn_dwpw_args;
+
+/* Inference fast path of one TemporalBlock's middle: first PReLU + gLN-1 + depthwise conv +
+ * second PReLU (conv_tasnet.py:218-253) computed by producer warps straight into the tensor-core
+ * operand of the pointwise convolution (:256); q never reaches memory.  gLN-2 (:254) needs the
+ * statistics of the whole utterance, so its scale/shift and the residual add (:237) are applied
+ * afterwards by ctn_resid_update.  ctn_dwpw_supported() != 0 says whether a configuration can
+ * take this path (gLN, P == 3, B == 256, H % 64 == 0, power-of-two dilation); otherwise use
+ * ctn_dwconv_fwd + ctn_gemm1x1. */
+int ctn_dwpw_supported(int H, int B, int P, int dilation, int norm);
+int ctn_dwpw_partials(int K, int dilation);
+int ctn_dwpw_fwd(const ctn_dwpw_args* args, void* stream);
+
+/* x += r * y - r * mu * col_g + col_bias on the bf16 (hi, lo) residual stream [M*K, B], in place:
+ * (mu, r) = gLN-2 statistics from the P partials per utterance over `count` elements; col_g /
+ * col_bias as produced by ctn_weight_prep (conv_tasnet.py:254-256 folded, residual :237). */
+int ctn_resid_update(void* x_hi, void* x_lo, const float* y, const void* stat, int P, double count,
+                     const float* col_g, const float* col_bias, int M, int K, int B, void* stream);
+
 /* Mask non-linearity, mask * mixture_w, basis Linear(N -> L), overlap-add with
  * step L/2 and right zero-fill to T (conv_tasnet.py:202-209,137-142,56-59;
  * utils.py:9-46).  score fp32 [M*K, C*N] (channel = c*N + n), w fp32 [M*K, N],

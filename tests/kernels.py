@@ -92,6 +92,30 @@ def dwconv(M, K, a, a1, g1, b1, norm, in_stat, in_P, wd, a2, dilation, causal, w
     return pre, hi, lo, st
 
 
+def dwpw(M, K, a, a1, g1, b1, in_stat, in_P, wd, a2, w_hi, w_lo, dilation, causal):
+    """ctn_dwpw_fwd: returns (y [M*K, B] raw product, gLN-2 partials [M, P, 2])"""
+    R, H = a.shape
+    B = w_hi.shape[0]
+    dev = a.device
+    lib = nat.lib()
+    d = nat.DwpwArgs()
+    d.M, d.K, d.H, d.B, d.dilation, d.causal = M, K, H, B, dilation, int(causal)
+    d.a, d.prelu_in, d.gamma_in, d.beta_in = a.data_ptr(), a1.data_ptr(), g1.data_ptr(), b1.data_ptr()
+    d.in_stat, d.in_P = in_stat.data_ptr(), in_P
+    d.wd, d.prelu_out, d.w_hi, d.w_lo = wd.data_ptr(), a2.data_ptr(), w_hi.data_ptr(), w_lo.data_ptr()
+    y = torch.full((R, B), float("nan"), device=dev)
+    st = torch.full((M, lib.ctn_dwpw_partials(K, dilation), 2), float("nan"), device=dev)
+    d.y, d.out_stat = y.data_ptr(), st.data_ptr()
+    nat.check(lib.ctn_dwpw_fwd(C.byref(d), nat.stream()))
+    return y, st
+
+
+def resid_update(x_hi, x_lo, y, stat, count, col_g, col_bias, M, K):
+    B = y.shape[1]
+    nat.check(nat.lib().ctn_resid_update(x_hi.data_ptr(), x_lo.data_ptr(), y.data_ptr(), stat.data_ptr(), stat.shape[1],
+                                         float(count), col_g.data_ptr(), col_bias.data_ptr(), M, K, B, nat.stream()))
+
+
 def decoder(score, w, V, M, K, C_, T, mask):
     L, N = V.shape
     est = torch.full((M, C_, T), float("nan"), device=score.device)

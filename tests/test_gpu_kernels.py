@@ -198,6 +198,46 @@ def test_dwconv(H, K, M, dil, causal, norm):
         assert rel_l2(st[:, 1], 1.0 / torch.sqrt(qr.var(1, unbiased=False) + 1e-8)) < 1e-3
 
 
+@pytest.mark.parametrize("H,K,M", [(64, 40, 3), (128, 700, 2), (512, 3199, 3)])
+@pytest.mark.parametrize("dil", [1, 2, 4, 8, 16, 32, 64, 128])
+@pytest.mark.parametrize("causal", [False, True])
+def test_fused_depthwise_pointwise(H, K, M, dil, causal):
+    """ctn_dwpw_fwd + ctn_resid_update == PReLU, gLN, depthwise, PReLU, gLN, pointwise, residual
+    (conv_tasnet.py:218-256, :237) of the oracle."""
+    B, P = 256, 3
+    a = _rand(M, H, K, seed=50)
+    a1 = torch.tensor([0.25], device=DEV)
+    a2 = torch.tensor([0.1], device=DEV)
+    g1, b1 = 1.0 + 0.3 * _rand(H, seed=51), _rand(H, seed=52)
+    g2, b2 = 1.0 + 0.3 * _rand(H, seed=53), _rand(H, seed=54)
+    wd = _rand(H, 1, P, seed=55, scale=0.5)
+    W2 = _rand(B, H, seed=56, scale=0.05)
+    x = _rand(M, B, K, seed=57)
+    ad = a.double()
+    pa = F.prelu(ad, a1.double())
+    n1 = O.gln(pa, g1.double().view(1, H, 1), b1.double().view(1, H, 1))
+    q_ref = F.prelu(O.depthwise(n1, wd.double(), dil, causal), a2.double())
+    n2 = O.gln(q_ref, g2.double().view(1, H, 1), b2.double().view(1, H, 1))
+    xr_hi, xr_lo = Kn.split_hl(Kn.to_rows(x))
+    x_in = (xr_hi.double() + xr_lo.double())
+    out_ref = torch.einsum("bh,mhk->mbk", W2.double(), n2) + Kn.from_rows(x_in, M)
+    in_P = 5
+    parts = torch.zeros(M, in_P, 2, device=DEV)
+    parts[:, 1, 0] = pa.sum(dim=(1, 2))
+    parts[:, 4, 1] = (pa ** 2).sum(dim=(1, 2))
+    w_hi, w_lo, col_g, col_bias = Kn.weight_prep(W2, g2, b2)
+    y, st = Kn.dwpw(M, K, Kn.to_rows(a), a1, g1, b1, parts, in_P, wd, a2, w_hi, w_lo, dil, causal)
+    assert not torch.isnan(st).any()
+    assert rel_l2(st[..., 0].double().sum(1), q_ref.sum(dim=(1, 2))) < 1e-4
+    assert rel_l2(st[..., 1].double().sum(1), (q_ref ** 2).sum(dim=(1, 2))) < 1e-4
+    assert not torch.isnan(y).any()                # every frame of every utterance was written
+    y_ref = torch.einsum("bh,mhk->mbk", (w_hi.double() + w_lo.double()), q_ref)
+    assert rel_l2(y, Kn.to_rows(y_ref)) < 2e-5
+    Kn.resid_update(xr_hi, xr_lo, y, st, float(K) * H, col_g, col_bias, M, K)
+    got = Kn.from_rows(xr_hi.double() + xr_lo.double(), M)
+    assert rel_l2(got, out_ref) < 2e-5
+
+
 def test_dwconv_rejects_length_changing_config():
     """P=2 non-causal changes the length; the reference crashes at the residual add"""
     H, K, M = 4, 10, 1

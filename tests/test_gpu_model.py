@@ -143,6 +143,34 @@ def test_forward_matches_oracle_at_baseline_configs(name):
     assert float(d) < DB_TOL
 
 
+@pytest.mark.parametrize("fuse", [4, 128])
+def test_fused_depthwise_pointwise_path_matches_unfused(fuse):
+    """engine.fuse_max_dilation routes blocks through ctn_dwpw_fwd + ctn_resid_update: same waveforms
+    as the unfused kernels (to rounding) and within tolerance of the oracle."""
+    cfg, M, T = CONFIGS["cfg1_paper_gln"]
+    p32 = O.random_params(*(cfg[k] for k in "NLBHPXRC"), cfg["causal"], seed=77)
+    model = _build(cfg, p32)
+    g = torch.Generator().manual_seed(78)
+    mix = (0.1 * torch.randn(3, T, generator=g)).to(DEV)
+    eng = model.engine()
+    default = eng.fuse_max_dilation
+    with torch.no_grad():
+        eng.fuse_max_dilation = 0
+        base = model(mix)
+        assert not any(eng._plan(model._params(), 3, T, mix.device).fused)
+        eng.fuse_max_dilation = fuse
+        fused = model(mix)
+        assert sum(eng._plan(model._params(), 3, T, mix.device).fused) == {4: 3, 128: 8}[fuse]
+        eng.use_graph = True
+        fused_g = model(mix)
+        eng.use_graph = False
+        eng.fuse_max_dilation = default
+        ref = O.forward(mix[:1].double(), {k: v.to(DEV).double() for k, v in p32.items()}, cfg)
+    assert rel_l2(fused, base) < 2e-5
+    assert torch.equal(fused, fused_g)
+    assert rel_l2(fused[:1], ref) < WAVE_TOL / 10
+
+
 def test_batched_equals_single_and_micro_batching():
     """Utterances are independent (gLN statistics are per utterance): a batch gives the same
     waveforms as one-by-one, whatever the micro-batch split."""

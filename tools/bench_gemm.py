@@ -25,7 +25,7 @@ def make(kind, mode):
     keep = {}
     if kind == "conv1x1":
         Cin, Cout = B, H
-    else:
+    else:   # "pointwise" = training form (fp32 residual in, fp32 + hi/lo out); "pw_inf" = inference form
         Cin, Cout = H, B
     A = torch.randn(R, Cin, device=dev)
     W = torch.randn(Cout, Cin, device=dev) * 0.05
@@ -53,7 +53,16 @@ def make(kind, mode):
         cg = torch.randn(Cout, device=dev)
         cb = torch.randn(Cout, device=dev)
         keep.update(resid=resid, hi=hi, lo=lo, ist=ist, cg=cg, cb=cb)
-        g.resid, g.out_hi, g.out_lo = resid.data_ptr(), hi.data_ptr(), lo.data_ptr()
+        if kind == "pw_inf":   # residual read from the (hi, lo) pair the result overwrites
+            r_hi, r_lo = Kn.split_hl(resid)
+            resid = r_hi.float() + r_lo.float()
+            hi.copy_(r_hi), lo.copy_(r_lo)
+            keep.update(r_hi=r_hi, r_lo=r_lo)
+            g.out_f32 = 0
+            g.resid_hi, g.resid_lo = r_hi.data_ptr(), r_lo.data_ptr()
+            g.out_hi, g.out_lo = hi.data_ptr(), lo.data_ptr()
+        else:
+            g.resid, g.out_hi, g.out_lo = resid.data_ptr(), hi.data_ptr(), lo.data_ptr()
         g.col_g, g.col_bias = cg.data_ptr(), cb.data_ptr()
         g.in_norm, g.in_stat, g.in_P, g.in_count = nat.NORM_GLN, ist.data_ptr(), P, float(K) * Cin
         s = ist.double().sum(1)
@@ -66,25 +75,8 @@ def make(kind, mode):
     return g, keep, ref
 
 
-KINDS = os.environ.get("CTN_KINDS", "conv1x1,pointwise").split(",")
-NITER = int(os.environ.get("CTN_NITER", "30"))
-for kind in KINDS:
-    for mode in modes:
-        g, keep, ref = make(kind, mode)
-        s = nat.stream()
-        nat.check(lib.ctn_gemm1x1(C.byref(g), s))
-        torch.cuda.synchronize()
-        out = keep["out"][:min(4, M) * K].double()
-        err = float((out - ref).norm() / ref.norm())
-        extra = ""
-        if kind == "pointwise":
-            hl = keep["hi"][:min(4, M) * K].double() + keep["lo"][:min(4, M) * K].double()
-            extra = " hl %.2e" % float((hl - ref).norm() / ref.norm())
-        else:
-            x = torch.where(ref >= 0, ref, 0.25 * ref)
-            st = keep["st"][:min(4, M)].double().sum(1)
-            extra = " stat %.2e %.2e" % (float(((st[:, 0] - x.view(min(4, M), -1).sum(1)) / x.view(min(4, M), -1).abs().sum(1)).abs().max()),
-                                          float(((st[:, 1] - (x * x).view(min(4, M), -1).sum(1)) / (x * x).view(min(4, M), -1).sum(1)).abs().max()))
+def bench(kind, mode, g, s, dbg, err, extra):
+    if True:
         for _ in range(5):
             lib.ctn_gemm1x1(C.byref(g), s)
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -96,4 +88,31 @@ for kind in KINDS:
         torch.cuda.synchronize()
         us = e0.elapsed_time(e1) / n * 1e3
         fl = 2.0 * R * g.Cin * g.Cout
-        print("%-9s mode %d M=%d: %.1f us  %.1f TFLOP/s (algorithmic)  rel err %.2e%s" % (kind, mode, M, us, fl / us / 1e6, err, extra))
+        print("%-9s mode %d dbg %2d M=%d: %.1f us  %.1f TFLOP/s (algorithmic)  rel err %.2e%s" % (kind, mode, dbg, M, us, fl / us / 1e6, err, extra))
+
+
+KINDS = os.environ.get("CTN_KINDS", "conv1x1,pointwise").split(",")
+NITER = int(os.environ.get("CTN_NITER", "30"))
+DBGS = [int(x) for x in os.environ.get("CTN_DBGS", "0").split(",")]
+for kind in KINDS:
+    for mode in modes:
+        g, keep, ref = make(kind, mode)
+        s = nat.stream()
+        nat.check(lib.ctn_gemm1x1(C.byref(g), s))
+        torch.cuda.synchronize()
+        out = keep["out"][:min(4, M) * K].double()
+        err = float((out - ref).norm() / ref.norm()) if kind != "pw_inf" else float("nan")
+        extra = ""
+        if kind != "conv1x1":
+            hl = keep["hi"][:min(4, M) * K].double() + keep["lo"][:min(4, M) * K].double()
+            extra = " hl %.2e" % float((hl - ref).norm() / ref.norm())
+        else:
+            x = torch.where(ref >= 0, ref, 0.25 * ref)
+            st = keep["st"][:min(4, M)].double().sum(1)
+            extra = " stat %.2e %.2e" % (float(((st[:, 0] - x.view(min(4, M), -1).sum(1)) / x.view(min(4, M), -1).abs().sum(1)).abs().max()),
+                                          float(((st[:, 1] - (x * x).view(min(4, M), -1).sum(1)) / (x * x).view(min(4, M), -1).sum(1)).abs().max()))
+        for dbg in DBGS:
+            os.environ["CTN_GEMM_DBG"] = str(dbg)
+            bench(kind, mode, g, s, dbg, err, extra)
+        os.environ["CTN_GEMM_DBG"] = "0"
+
