@@ -14,13 +14,14 @@
 // Tiles are not runs of consecutive frames.  Thread (quad, s) of a producer group owns four
 // channels and tile rows 16 s .. 16 s + 15, which are the frames  ph + d (j0 + jj)  of ONE
 // dilation phase: the three taps of consecutive outputs are consecutive elements of that
-// sequence, so each input row is loaded, PReLU'd and normalised once and reused from a 3-deep
-// register window (18 loads per 16 outputs, for every dilation).  A GEMM row may be any frame:
-// the epilogue thread that owns TMEM lane r simply stores to the row of frame(r).
+// sequence, so each input row is loaded and activated once and reused from a 3-deep register
+// window (18 loads per 16 outputs, for every dilation).  A GEMM row may be any frame: the
+// epilogue thread that owns TMEM lane r simply stores to the row of frame(r).
 //
 // CTA pair (cta_group::2) as in gemm.cu: each CTA owns a 128-row tile and loads half of the
 // 256-column weight tile.  Warps: 0 TMA (weights), 1 MMA issuer, 2-5 epilogue, 6-13 producers
-// (two groups of four warps working on alternate k-blocks).
+// (two groups of four warps working on alternate k-blocks).  14 warps = 4 per scheduler
+// partition = 128 registers per thread, which the producers' load ring needs.
 #include <cuda.h>
 #include <stdlib.h>
 
