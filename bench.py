@@ -259,15 +259,48 @@ def run_b200(args):
         tot_ms = sum(a[2] for a in acc.values())
         breakdown = {k: {"launches": a[3] // 3, "ms": a[2] / 3, "share": a[2] / tot_ms,
                          "tflops": a[0] / a[2] / 1e9, "gbs": a[1] / a[2] / 1e6} for k, a in acc.items()}
-        gem = [a for k, a in acc.items() if k.startswith("gemm")]
-        g_fl, g_ms, g_n = sum(a[0] for a in gem), sum(a[2] for a in gem), sum(a[3] for a in gem)
-        achieved = g_fl / g_ms / 1e9
-        roof = {"bound": "tensor", "kernel": "gemm_tc_kernel (1x1-conv GEMM, bf16 hi/lo split = 3 MMAs per product)",
-                "achieved": achieved, "peak": pk["tf_sustained"], "unit": "TFLOP/s",
-                "frac": achieved / pk["tf_sustained"], "peak_source": pk["source"] + " (sustained bf16)",
-                "avg_launch_ms": g_ms / g_n, "algorithmic_flops_per_launch": g_fl / g_n,
-                "share_of_step": g_ms / tot_ms, "traffic": None,
-                "how": "CUDA events around every launch of one %d-utterance micro-batch pass, 3 repeats" % mb}
+        # one roofline entry per kernel kind: tensor-bound kinds against the sustained bf16 peak
+        # (algorithmic FLOPs = ONE product; the hi/lo split executes three MMAs per product, reported
+        # as executed_*), HBM-bound kinds against the measured copy bandwidth.  traffic = DRAM bytes per
+        # launch from the committed ncu --set full capture (valid at the captured micro-batch only).
+        traffic = {}
+        try:
+            with open(os.path.join(ROOT, "profiles", "r1", "ncu_traffic_v4.json")) as f:
+                tj = json.load(f)
+            if tj.get("micro_batch") == mb:
+                traffic = {k: v["traffic_bytes"] for k, v in tj["kernels"].items()}
+        except Exception:
+            traffic = {}
+        names = {"gemm_conv1x1": "gemm_tc_kernel<256,pair,plain> (conv1x1 + PReLU statistics)",
+                 "gemm_pointwise": "gemm_tc_kernel<256,pair,affine> (pointwise + folded gLN + residual)",
+                 "gemm_dwpw_fused": "fb::dwpw_kernel (depthwise producers + pointwise GEMM)",
+                 "gemm_bottleneck": "gemm_tc_kernel (bottleneck)", "gemm_mask": "gemm_tc_kernel (mask conv)",
+                 "dwconv": "dwconv_march_kernel", "resid_update": "fb::resid_update_kernel",
+                 "encoder": "encoder_fwd_kernel", "decoder": "decoder_fwd_blocked_kernel"}
+        roofs = {}
+        for k, a in acc.items():
+            n = a[3]
+            ms = a[2] / n
+            tensor = k.startswith("gemm")
+            if tensor:
+                ach = a[0] / a[2] / 1e9
+                r = {"bound": "tensor", "achieved": ach, "peak": pk["tf_sustained"], "unit": "TFLOP/s",
+                     "frac": ach / pk["tf_sustained"], "executed_tflops": 3.0 * ach,
+                     "executed_frac": 3.0 * ach / pk["tf_sustained"],
+                     "peak_source": pk["source"] + " (sustained bf16)", "algorithmic_flops_per_launch": a[0] / n,
+                     "hbm_gbs": a[1] / a[2] / 1e6, "hbm_frac": a[1] / a[2] / 1e6 / pk["hbm"]}
+            else:
+                ach = a[1] / a[2] / 1e6
+                r = {"bound": "hbm", "achieved": ach, "peak": pk["hbm"], "unit": "GB/s", "frac": ach / pk["hbm"],
+                     "peak_source": pk["source"] + " (copy bandwidth)"}
+            r.update({"kernel": names.get(k, k), "avg_launch_ms": ms, "algorithmic_bytes_per_launch": a[1] / n,
+                      "share_of_step": a[2] / tot_ms, "traffic": traffic.get(k)})
+            roofs[k] = r
+        dom = max(roofs, key=lambda k: roofs[k]["share_of_step"])
+        roof = dict(roofs[dom])
+        roof["how"] = ("dominant kernel by share of the step; CUDA events around every launch of one %d-utterance "
+                       "micro-batch pass, 3 repeats; traffic from profiles/r1/ncu_traffic_v4.json" % mb)
+        roof["all_kernels"] = roofs
 
     train = None
     if not args.no_train:

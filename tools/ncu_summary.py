@@ -27,7 +27,7 @@ rows = list(csv.reader(io.StringIO(raw)))
 hdr, units, data = rows[0], rows[1], rows[2:]
 idx = {h: i for i, h in enumerate(hdr)}
 print("# " + (sys.argv[2] if len(sys.argv) > 2 else sys.argv[1]))
-names = [r[idx["Kernel Name"]].split("(")[0] for r in data]
+names = [r[idx["Kernel Name"]].split("(")[0].replace(", ", " ") for r in data]
 print("metric,unit," + ",".join("%s#%d" % (n, i) for i, n in enumerate(names)))
 for w in WANT:
     if w in idx:
