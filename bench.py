@@ -305,6 +305,7 @@ def run_b200(args):
     train = None
     if not args.no_train:
         train = train_step(args, world, rank, dev, timed)
+        train["ms_per_step_torch_optimizer"] = train_step(args, world, rank, dev, timed, fused_optim=False)["ms_per_step"]
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:
@@ -338,7 +339,7 @@ def run_b200(args):
         dist.destroy_process_group()
 
 
-def train_step(args, world, rank, dev, timed):
+def train_step(args, world, rank, dev, timed, fused_optim=True):
     """BASELINE configs[1]: paper config, batch 3 x 4 s per GPU (weak scaling), forward +
     cal_loss + backward (ONE NCCL all-reduce of the flat gradient when world > 1) + clip(5) +
     Adam(1e-3), as solver.py:178-186.  Host mixtures/sources are copied in every step and the
@@ -354,7 +355,11 @@ def train_step(args, world, rank, dev, timed):
     model = model.to(dev).train()
     if world > 1:
         _dist.attach(model)
-    opt = torch.optim.Adam(model.parameters(), lr=1e-3)
+    if fused_optim:   # clip(5) + Adam in two launches (ctn_clip_adam)
+        from ctn_b200.optim import FusedAdam
+        opt = FusedAdam(model.parameters(), lr=1e-3, max_norm=5.0)
+    else:
+        opt = torch.optim.Adam(model.parameters(), lr=1e-3)
     g = torch.Generator().manual_seed(77 + rank)
     h_src = (0.1 * torch.randn(M, cfg["C"], T, generator=g)).pin_memory()
     h_mix = h_src.sum(1).pin_memory()
@@ -369,7 +374,8 @@ def train_step(args, world, rank, dev, timed):
         loss, _, _, _ = pit_criterion.cal_loss(src, est, lengths)
         opt.zero_grad()
         loss.backward()
-        torch.nn.utils.clip_grad_norm_(model.parameters(), 5.0)
+        if not fused_optim:
+            torch.nn.utils.clip_grad_norm_(model.parameters(), 5.0)
         opt.step()
         h_loss.copy_(loss.detach(), non_blocking=True)
 
@@ -382,6 +388,8 @@ def train_step(args, world, rank, dev, timed):
             "scaling": "weak", "audio_s_per_s": M * world * (T / SR) * steps / sec,
             "algorithmic_tflops": 3.0 * forward_flops(cfg, T) * M * world * steps / sec / 1e12,
             "gpu_launches_per_step": (eng.launches - l0) // steps, "loss": float(h_loss),
+            "optimizer": "ctn_b200.optim.FusedAdam (clip + Adam, 2 launches)" if fused_optim
+                         else "torch clip_grad_norm_ + torch.optim.Adam",
             "config": "BASELINE configs[1]: paper config, 3 x 4 s per GPU, fwd + PIT SI-SNR loss + bwd + "
                       "grad all-reduce + clip(5) + Adam, host inputs copied every step",
             "h2d_bytes_per_step": M * T * 4 * (1 + cfg["C"]), "d2h_bytes_per_step": 4}

@@ -54,6 +54,11 @@ class DwpwArgs(C.Structure):
     ]
 
 
+class OptChunk(C.Structure):
+    """struct ctn_opt_chunk"""
+    _fields_ = [("param", _vp), ("grad", _vp), ("exp_avg", _vp), ("exp_avg_sq", _vp), ("n", C.c_int), ("pad_", C.c_int)]
+
+
 class BwdDwArgs(C.Structure):
     """struct ctn_bwd_dw_args"""
     _fields_ = [
@@ -122,6 +127,8 @@ _SIGNATURES = {
     "ctn_encoder_fwd": (C.c_int, [_vp, _vp, C.c_int, C.c_int, C.c_int, C.c_int, _vp, _vp, _vp, _vp, _vp]),
     "ctn_gemm1x1": (C.c_int, [C.POINTER(GemmArgs), _vp]),
     "ctn_dwconv_fwd": (C.c_int, [C.POINTER(DwconvArgs), _vp]),
+    "ctn_clip_adam": (C.c_int, [_vp, C.c_int, _vp, C.c_float, C.c_float, C.c_double, C.c_double, C.c_float, C.c_float,
+                                C.c_float, C.c_int, _vp, _vp]),
     "ctn_dwpw_supported": (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_int, C.c_int]),
     "ctn_dwpw_partials": (C.c_int, [C.c_int, C.c_int]),
     "ctn_dwpw_fwd": (C.c_int, [C.POINTER(DwpwArgs), _vp]),

@@ -321,6 +321,25 @@ int ctn_encoder_wgrad_tiles(int K);
 int ctn_encoder_wgrad(const float* dpre, const float* mixture, int M, int T, int N, int L, float* dU_part,
                       void* stream);
 
+/* ---- training-step tail: clip_grad_norm_ + Adam (solver.py:184-186, train.py:129-131) ---- */
+typedef struct ctn_opt_chunk {
+    float* param;       /* n parameters                                   */
+    float* grad;        /* their gradient (written only if write_grad)    */
+    float* exp_avg;     /* Adam first moment                              */
+    float* exp_avg_sq;  /* Adam second moment                             */
+    int n;
+    int pad_;
+} ctn_opt_chunk;
+
+/* torch.nn.utils.clip_grad_norm_(params, max_norm) followed by torch.optim.Adam.step() (L2 weight
+ * decay, amsgrad off) over a device table of chunks covering every parameter tensor, in two launches.
+ * betas are doubles so that 1 - beta is rounded once, as torch does.  step_size = lr / (1 - beta1^t), inv_sqrt_bias2 = 1 / sqrt(1 - beta2^t) for the step count t (host).
+ * partials: n_chunks doubles of workspace.  max_norm <= 0 disables clipping.  norm_out (may be NULL)
+ * receives the total gradient norm before clipping, like clip_grad_norm_'s return value. */
+int ctn_clip_adam(const ctn_opt_chunk* chunks_dev, int n_chunks, double* partials, float max_norm, float step_size,
+                  double beta1, double beta2, float inv_sqrt_bias2, float eps, float weight_decay, int write_grad,
+                  float* norm_out, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
