@@ -79,6 +79,8 @@ __device__ __forceinline__ int tile_j0(const Params& p, int tt, int s) {
     return (tt / p.n_ig) * p.jspan + (s >> p.w_log2) * kRowsPerThread;
 }
 
+// kPreact: the input is already PReLU(conv1x1 output) (ctn_gemm1x1 with store_prelu), prelu_in is unused
+template <bool kPreact>
 __global__ void __launch_bounds__(kThreads, 1)
 dwpw_kernel(const __grid_constant__ CUtensorMap tm_w_hi, const __grid_constant__ CUtensorMap tm_w_lo, const Params p) {
     const uint32_t rank = ptx::cluster_ctarank();
@@ -245,7 +247,7 @@ dwpw_kernel(const __grid_constant__ CUtensorMap tm_w_hi, const __grid_constant__
         const int pt = (pw & 3) * 32 + lane;                   // 0 .. 127 within the group
         const int quad = pt & 15, s = pt >> 4;
         const uint32_t full_remote = ptx::mapa(ptx::smem_u32(full_bar), 0);
-        const float a1 = __ldg(p.prelu_in), a2 = __ldg(p.prelu_out);
+        const float a1 = kPreact ? 1.f : __ldg(p.prelu_in), a2 = __ldg(p.prelu_out);
         const f2_t a1m1 = f2_pack(a1 - 1.f, a1 - 1.f), a2m1 = f2_pack(a2 - 1.f, a2 - 1.f);
         const f2_t neg1 = f2_pack(-1.f, -1.f), one2 = f2_pack(1.f, 1.f);
         // byte offset of this thread's 8 bytes inside a [128 x 64] bf16 tile, for row 16 s + jj:
@@ -359,10 +361,15 @@ dwpw_kernel(const __grid_constant__ CUtensorMap tm_w_hi, const __grid_constant__
                     auto xform = [&](int t, f2_t (&o)[2]) {
                         const float4 v = q[t % kRing];
                         const f2_t v2[2] = {f2_pack(v.x, v.y), f2_pack(v.z, v.w)};
-                        const f2_t mn[2] = {f2_pack(fminf(v.x, 0.f), fminf(v.y, 0.f)), f2_pack(fminf(v.z, 0.f), fminf(v.w, 0.f))};
 #pragma unroll
                         for (int i = 0; i < 2; ++i) {
-                            o[i] = f2_fma(a1m1, mn[i], v2[i]);
+                            if (kPreact) {
+                                o[i] = v2[i];
+                            } else {
+                                const f2_t mn = i == 0 ? f2_pack(fminf(v.x, 0.f), fminf(v.y, 0.f))
+                                                       : f2_pack(fminf(v.z, 0.f), fminf(v.w, 0.f));
+                                o[i] = f2_fma(a1m1, mn, v2[i]);
+                            }
                             if (!kFast) o[i] = (t >= T.lo && t < T.hi) ? f2_fma(A[i], o[i], Bc[i]) : 0ull;
                         }
                         if (t < kRing) {
@@ -516,7 +523,7 @@ extern "C" int ctn_dwpw_fwd(const ctn_dwpw_args* args, void* stream_) {
                 "ctn_dwpw_fwd: needs B == 256, H %% 64 == 0 and a power-of-two dilation (H=%d B=%d dilation=%d)", a.H, a.B,
                 a.dilation);
     CTN_REQUIRE(static_cast<long long>(a.M) * a.K < (1ll << 31), "ctn_dwpw_fwd: M*K exceeds 2^31 rows");
-    CTN_REQUIRE(a.a && a.prelu_in && a.gamma_in && a.beta_in && a.in_stat && a.in_P > 0 && a.wd && a.prelu_out && a.w_hi &&
+    CTN_REQUIRE(a.a && a.gamma_in && a.beta_in && a.in_stat && a.in_P > 0 && a.wd && a.prelu_out && a.w_hi &&
                     a.w_lo && a.y && a.out_stat,
                 "ctn_dwpw_fwd: NULL argument");
     auto aligned16 = [](const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; };
@@ -541,11 +548,13 @@ extern "C" int ctn_dwpw_fwd(const ctn_dwpw_args* args, void* stream_) {
     int rc;
     if ((rc = make_tmap_bf16_kmajor(&tw_hi, a.w_hi, a.B, a.H, fb::kBN / 2)) != CTN_OK) return rc;
     if ((rc = make_tmap_bf16_kmajor(&tw_lo, a.w_lo, a.B, a.H, fb::kBN / 2)) != CTN_OK) return rc;
-    static bool attr_set = false;
-    if (!attr_set) {
-        cudaError_t e = cudaFuncSetAttribute(fb::dwpw_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, fb::kSmemMax);
+    const bool preact = a.prelu_in == nullptr;
+    auto kern = preact ? fb::dwpw_kernel<true> : fb::dwpw_kernel<false>;
+    static bool attr_set[2] = {false, false};
+    if (!attr_set[preact]) {
+        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, fb::kSmemMax);
         if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(dwpw_kernel)");
-        attr_set = true;
+        attr_set[preact] = true;
     }
     const int workers_max = sm_count() / 2;
     const int workers = p.items < workers_max ? p.items : workers_max;
@@ -561,7 +570,7 @@ extern "C" int ctn_dwpw_fwd(const ctn_dwpw_args* args, void* stream_) {
     attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
-    cudaError_t e = cudaLaunchKernelEx(&cfg, fb::dwpw_kernel, tw_hi, tw_lo, p);
+    cudaError_t e = cudaLaunchKernelEx(&cfg, kern, tw_hi, tw_lo, p);
     if (e != cudaSuccess) return cuda_fail(e, "cudaLaunchKernelEx(dwpw_kernel)");
     return CTN_OK;
 }

@@ -49,6 +49,7 @@ struct EpiParams {
     const float* bw_slope;
     const float2* bw_stat;
     int bw_P;
+    int store_prelu;   // the stored output is PReLU(out) (slope *stat_prelu), not only the statistics
     int dbg;   // CTN_GEMM_DBG experiment bits (0 in production): 1 skip epilogue, 2 skip stores, 4 skip MMAs
 };
 
@@ -112,6 +113,7 @@ __device__ __forceinline__ void epilogue_chunk(const EpiParams& ep, float (&v)[3
                 float x = use_slope ? prelu(v[j], slope) : v[j];
                 ls += x;
                 lss = fmaf(x, x, lss);
+                if (ep.store_prelu) v[j] = x;
             }
         }
     }
@@ -506,6 +508,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tm_a_hi, const __grid_constan
                                 const float x = fmaf(slope, fminf(v[j], 0.f), fmaxf(v[j], 0.f));   // prelu
                                 ls[j & 3] += x;
                                 lss[j & 3] = fmaf(x, x, lss[j & 3]);
+                                if (ep.store_prelu) v[j] = x;
                             }
                         }
                         // Straight from registers: a thread owns 32 consecutive columns of its row, i.e.
@@ -771,6 +774,9 @@ extern "C" int ctn_gemm1x1(const ctn_gemm_args* args, void* stream_) {
     ep.out_stat = a.out_stat, ep.out_stat_buf = static_cast<float2*>(a.out_stat_buf);
     ep.out_P = ctn_gemm_gln_partials(a.K, a.Cout);
     ep.stat_prelu = a.stat_prelu;
+    ep.store_prelu = a.store_prelu;
+    CTN_REQUIRE(!a.store_prelu || (a.stat_prelu != nullptr && a.out_stat != CTN_NORM_NONE && a.bw_pre == nullptr),
+                "ctn_gemm1x1: store_prelu needs stat_prelu and an out_stat mode");
     ep.bw_pre = a.bw_pre, ep.bw_gamma = a.bw_gamma, ep.bw_slope = a.bw_slope;
     ep.bw_stat = static_cast<const float2*>(a.bw_stat), ep.bw_P = a.bw_P;
     {

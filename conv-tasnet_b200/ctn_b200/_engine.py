@@ -99,6 +99,7 @@ class _Plan:
         self.a = torch.empty(R_, H, **f32)
         self.q_hl = (torch.empty(R_, H, **bf), torch.empty(R_, H, **bf))
         self.score = torch.empty(R_, C * N, **f32)
+        self.one = torch.ones(1, **f32)
         self.norm = _NORM[cfg["norm_type"]]
         if self.norm == nat.NORM_GLN:
             self.P1 = lib.ctn_gemm_gln_partials(K, H)
@@ -172,13 +173,14 @@ class _Plan:
                 else:
                     info.append(("dwconv", 2.0 * Rr * H * cfg["P"], 8.0 * Rr * H))
                     info.append(("gemm_pointwise", 2.0 * Rr * B * H, 4.0 * Rr * H + 8.0 * Rr * B))
+                # self.a holds PReLU(conv1x1 output): the consumers skip the first PReLU (identity slope)
                 calls.append(self._gemm(Cin=B, Cout=H, a_hi=self.x_hl[0], a_lo=self.x_hl[1], w_hi=pb["w1"][0],
                                         w_lo=pb["w1"][1], out_f32=self.a, out_stat=self.norm,
-                                        out_stat_buf=self.stat1, stat_prelu=params[k["a1"]]))
+                                        out_stat_buf=self.stat1, stat_prelu=params[k["a1"]], store_prelu=1))
                 if self.fused[xb]:
                     f = nat.DwpwArgs()
                     f.M, f.K, f.H, f.B, f.dilation, f.causal = M, K, H, B, 2 ** xb, int(bool(cfg["causal"]))
-                    f.a, f.prelu_in = self.a.data_ptr(), params[k["a1"]].data_ptr()
+                    f.a, f.prelu_in = self.a.data_ptr(), None
                     f.gamma_in, f.beta_in = params[k["g1"]].data_ptr(), params[k["b1"]].data_ptr()
                     f.in_stat, f.in_P = self.stat1.data_ptr(), self.P1
                     f.wd, f.prelu_out = params[k["wd"]].data_ptr(), params[k["a2"]].data_ptr()
@@ -193,7 +195,7 @@ class _Plan:
                     continue
                 d = nat.DwconvArgs()
                 d.M, d.K, d.H, d.P, d.dilation, d.causal = M, K, H, cfg["P"], 2 ** xb, int(bool(cfg["causal"]))
-                d.inp, d.prelu_in = self.a.data_ptr(), params[k["a1"]].data_ptr()
+                d.inp, d.prelu_in = self.a.data_ptr(), self.one.data_ptr()
                 d.gamma_in, d.beta_in = params[k["g1"]].data_ptr(), params[k["b1"]].data_ptr()
                 d.norm, d.in_stat, d.in_P = self.norm, self.stat1.data_ptr(), self.P1
                 d.wd, d.prelu_out = params[k["wd"]].data_ptr(), params[k["a2"]].data_ptr()

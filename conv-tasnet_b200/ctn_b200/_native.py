@@ -29,7 +29,7 @@ class GemmArgs(C.Structure):
         ("out_stat", C.c_int), ("out_stat_buf", _vp), ("stat_prelu", _vp),
         ("force_simt", C.c_int),
         ("bw_pre", _vp), ("bw_gamma", _vp), ("bw_slope", _vp), ("bw_stat", _vp), ("bw_P", C.c_int),
-        ("resid_hi", _vp), ("resid_lo", _vp),
+        ("resid_hi", _vp), ("resid_lo", _vp), ("store_prelu", C.c_int),
     ]
 
 

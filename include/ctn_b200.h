@@ -126,6 +126,9 @@ typedef struct ctn_gemm_args {
     /* residual given as a bf16 (hi, lo) pair [M*K, Cout] instead of fp32 (both or neither; exclusive with
      * resid; may alias out_hi / out_lo): inference keeps the block input only in that form */
     const void *resid_hi, *resid_lo;
+    /* nonzero (needs stat_prelu): the STORED output is PReLU(out) too, not only the statistics.
+     * Inference stores PReLU(conv1x1 output) so that the consumers skip the first PReLU. */
+    int store_prelu;
 } ctn_gemm_args;
 
 /* 1x1 convolution as a GEMM over all frames of the batch (bottleneck
@@ -159,7 +162,8 @@ typedef struct ctn_dwpw_args {
     int M, K, H, B;         /* a is [M*K, H], y is [M*K, B]; B == 256, H % 64 == 0              */
     int dilation, causal;   /* power-of-two dilation, P = 3                                    */
     const float* a;         /* conv1x1 output, fp32 [M*K, H]                                   */
-    const float* prelu_in;  /* slope of the first PReLU (device scalar), conv_tasnet.py:218    */
+    const float* prelu_in;  /* slope of the first PReLU (device scalar), conv_tasnet.py:218;
+                               NULL: `a` is already PReLU(conv1x1 output) (ctn_gemm1x1 store_prelu) */
     const float *gamma_in, *beta_in; /* gLN-1 affine [H], :219                                 */
     const void* in_stat;    /* float2 [M, in_P]: gLN-1 partials (ctn_gemm1x1 out_stat)         */
     int in_P;

@@ -39,7 +39,7 @@ def encoder(mix, U):
 
 
 def gemm(M, K, a_hi, a_lo, w_hi, w_lo, out_f32=True, out_hl=False, resid=None, col_g=None, col_bias=None,
-         in_norm=0, in_stat=None, in_P=0, in_count=0.0, out_stat=0, stat_prelu=None, force_simt=False):
+         in_norm=0, in_stat=None, in_P=0, in_count=0.0, out_stat=0, stat_prelu=None, force_simt=False, store_prelu=False):
     R, Cin = a_hi.shape
     Cout = w_hi.shape[0]
     dev = a_hi.device
@@ -65,6 +65,7 @@ def gemm(M, K, a_hi, a_lo, w_hi, w_lo, out_f32=True, out_hl=False, resid=None, c
     if out_stat:
         g.out_stat_buf = res["stat"].data_ptr()
     g.stat_prelu = nat.ptr(stat_prelu)
+    g.store_prelu = int(store_prelu)
     g.force_simt = int(force_simt)
     nat.check(lib.ctn_gemm1x1(C.byref(g), nat.stream()))
     return res
@@ -100,7 +101,7 @@ def dwpw(M, K, a, a1, g1, b1, in_stat, in_P, wd, a2, w_hi, w_lo, dilation, causa
     lib = nat.lib()
     d = nat.DwpwArgs()
     d.M, d.K, d.H, d.B, d.dilation, d.causal = M, K, H, B, dilation, int(causal)
-    d.a, d.prelu_in, d.gamma_in, d.beta_in = a.data_ptr(), a1.data_ptr(), g1.data_ptr(), b1.data_ptr()
+    d.a, d.prelu_in, d.gamma_in, d.beta_in = a.data_ptr(), nat.ptr(a1), g1.data_ptr(), b1.data_ptr()
     d.in_stat, d.in_P = in_stat.data_ptr(), in_P
     d.wd, d.prelu_out, d.w_hi, d.w_lo = wd.data_ptr(), a2.data_ptr(), w_hi.data_ptr(), w_lo.data_ptr()
     y = torch.full((R, B), float("nan"), device=dev)

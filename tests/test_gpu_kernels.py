@@ -145,6 +145,10 @@ def test_gemm_output_statistics(M, K, Cin, Cout, simt, norm):
     else:
         assert rel_l2(st[..., 0].sum(1), p.sum(dim=2).flatten()) < 1e-4
         assert rel_l2(st[..., 1].sum(1), (p ** 2).sum(dim=2).flatten()) < 1e-4
+    # store_prelu: the stored output is activated too (inference), statistics unchanged
+    res2 = Kn.gemm(M, K, a_hi, a_lo, w_hi, w_lo, out_stat=mode, stat_prelu=slope, force_simt=simt, store_prelu=True)
+    assert rel_l2(res2["out"], p.reshape(M * K, Cout)) < 3e-5
+    assert torch.equal(res2["stat"], res["stat"])
 
 
 # --------------------------------------------------------------- depthwise
@@ -201,7 +205,8 @@ def test_dwconv(H, K, M, dil, causal, norm):
 @pytest.mark.parametrize("H,K,M", [(64, 40, 3), (128, 700, 2), (512, 3199, 3)])
 @pytest.mark.parametrize("dil", [1, 2, 4, 8, 16, 32, 64, 128])
 @pytest.mark.parametrize("causal", [False, True])
-def test_fused_depthwise_pointwise(H, K, M, dil, causal):
+@pytest.mark.parametrize("preact", [False, True])
+def test_fused_depthwise_pointwise(H, K, M, dil, causal, preact):
     """ctn_dwpw_fwd + ctn_resid_update == PReLU, gLN, depthwise, PReLU, gLN, pointwise, residual
     (conv_tasnet.py:218-256, :237) of the oracle."""
     B, P = 256, 3
@@ -226,7 +231,10 @@ def test_fused_depthwise_pointwise(H, K, M, dil, causal):
     parts[:, 1, 0] = pa.sum(dim=(1, 2))
     parts[:, 4, 1] = (pa ** 2).sum(dim=(1, 2))
     w_hi, w_lo, col_g, col_bias = Kn.weight_prep(W2, g2, b2)
-    y, st = Kn.dwpw(M, K, Kn.to_rows(a), a1, g1, b1, parts, in_P, wd, a2, w_hi, w_lo, dil, causal)
+    if preact:   # the kernel is handed PReLU(a) (what ctn_gemm1x1 stores with store_prelu) and no slope
+        y, st = Kn.dwpw(M, K, Kn.to_rows(pa.float()), None, g1, b1, parts, in_P, wd, a2, w_hi, w_lo, dil, causal)
+    else:
+        y, st = Kn.dwpw(M, K, Kn.to_rows(a), a1, g1, b1, parts, in_P, wd, a2, w_hi, w_lo, dil, causal)
     assert not torch.isnan(st).any()
     assert rel_l2(st[..., 0].double().sum(1), q_ref.sum(dim=(1, 2))) < 1e-4
     assert rel_l2(st[..., 1].double().sum(1), (q_ref ** 2).sum(dim=(1, 2))) < 1e-4
