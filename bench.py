@@ -402,7 +402,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--micro-batch", type=int, default=64)
-    ap.add_argument("--fuse", type=int, default=32,
+    ap.add_argument("--fuse", type=int, default=1 << 30,
                     help="blocks with dilation <= this use the fused depthwise+pointwise kernel (0 = off)")
     ap.add_argument("--graph", type=int, default=1)
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")

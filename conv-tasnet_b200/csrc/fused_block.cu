@@ -19,9 +19,10 @@
 // epilogue thread that owns TMEM lane r simply stores to the row of frame(r).
 //
 // CTA pair (cta_group::2) as in gemm.cu: each CTA owns a 128-row tile and loads half of the
-// 256-column weight tile.  Warps: 0 TMA (weights), 1 MMA issuer, 2-5 epilogue, 6-13 producers
-// (two groups of four warps working on alternate k-blocks).  14 warps = 4 per scheduler
-// partition = 128 registers per thread, which the producers' load ring needs.
+// 256-column weight tile.  Warps: 0 TMA (weights), 1 MMA issuer, 2-13 producers (three groups of
+// four warps; group g fills stage g and drains the TMEM accumulators of tiles g, g + 3, ...: there
+// are no dedicated epilogue warps).  14 warps = at most 4 per scheduler partition = 128 registers
+// per thread, which the producers' load ring needs.
 #include <cuda.h>
 #include <stdlib.h>
 
@@ -44,12 +45,10 @@ constexpr int kStages = 3;
 constexpr int kABytes = kBM * kBK * 2;           // one of hi / lo
 constexpr int kWBytes = (kBN / 2) * kBK * 2;     // this CTA's half of the weight tile, one of hi / lo
 constexpr int kStageBytes = 2 * kABytes + 2 * kWBytes;
-constexpr int kEpiWarps = 4;
-constexpr int kProdWarps = 8;        // 256 threads = 32 channel pairs x 8 row segments of a k-block
-constexpr int kThreads = 64 + 32 * (kEpiWarps + kProdWarps);
+constexpr int kProdWarps = 12;       // three groups of four warps; they also drain TMEM
+constexpr int kThreads = 64 + 32 * kProdWarps;
 constexpr int kBarBytes = 256;
-constexpr int kStgRowBytes = 128 + 16;   // one 32-column fp32 chunk of a row; the pad spreads the rows over the banks
-constexpr int kStgBytes = kEpiWarps * 32 * kStgRowBytes;
+constexpr int kStgBytes = 0;
 constexpr int kSmemFixed = kStages * kStageBytes + kBarBytes + kStgBytes;   // + 20 H bytes of per-channel constants
 constexpr int kSmemMax = 232448;
 constexpr int kRowsPerThread = 16;   // outputs a producer thread marches per k-block
@@ -113,12 +112,12 @@ dwpw_kernel(const __grid_constant__ CUtensorMap tm_w_hi, const __grid_constant__
         for (int i = 0; i < kStages; ++i) {
             // leader: weight bytes of both CTAs (one expect_tx arrival) + one arrival per producer warp
             // of the group that fills the stage, from both CTAs
-            ptx::mbar_init(full_bar + i, 1 + 2 * (kProdWarps / 2));
+            ptx::mbar_init(full_bar + i, 1 + 2 * 4);
             ptx::mbar_init(empty_bar + i, 1);
         }
         for (int i = 0; i < 2; ++i) {
             ptx::mbar_init(tfull_bar + i, 1);
-            ptx::mbar_init(tempty_bar + i, 2 * kEpiWarps);
+            ptx::mbar_init(tempty_bar + i, 2 * 4);
         }
         ptx::fence_mbar_init();
     } else if (warp == 1) {
@@ -182,71 +181,22 @@ dwpw_kernel(const __grid_constant__ CUtensorMap tm_w_hi, const __grid_constant__
                 }
             }
         }
-    } else if (warp < 2 + kEpiWarps) {
-        // ---------------------------------------------------- epilogue: TMEM -> y rows
-        const int ew = warp & 3;
-        const uint32_t tempty_remote = ptx::mapa(ptx::smem_u32(tempty_bar), 0);
-        const uint32_t stg_base = ptx::smem_u32(smem + kStages * kStageBytes + kBarBytes) + (warp - 2) * 32 * kStgRowBytes;
-        int it = 0;
-        for (int item = worker; item < p.items; item += n_workers, ++it) {
-            const int as = it & 1;
-            const uint32_t aphase = (it >> 1) & 1;
-            const int rt = 2 * item + static_cast<int>(rank);
-            const bool tile_ok = rt < p.row_tiles;
-            const int m = tile_ok ? rt / p.tiles_per_utt : 0, tt = tile_ok ? rt % p.tiles_per_utt : 0;
-            const int r = ew * 32 + lane;
-            const int s = r >> 4;
-            const int frame = tile_phase(p, tt, s) + p.d * (tile_j0(p, tt, s) + (r & 15));
-            const bool valid = tile_ok && frame < p.K;
-            float* yrow = p.y + (static_cast<long long>(m) * p.K + frame) * kBN;
-            ptx::mbar_wait(tfull_bar + as, aphase);
-            ptx::tc_fence_after();
-            if (!(p.dbg & 1)) {
-                // A lane owns one output row.  Its 32 columns of a chunk go to a private 128 B row of the
-                // warp's staging area and from there to global memory with ONE bulk copy by the async
-                // proxy: 256-bit stores straight from registers put 32 different lines per instruction
-                // through the LSU, which the producers' loads and stores need.
-                const uint32_t srow = stg_base + static_cast<uint32_t>(lane) * kStgRowBytes;
-#pragma unroll
-                for (int ci = 0; ci < kBN / 32; ++ci) {
-                    uint32_t v[32];
-                    ptx::tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(ew * 32) << 16) + as * kBN + ci * 32, v);
-                    if (p.dbg & 64) {   // experiment: 256-bit stores straight from registers
-                        ptx::tmem_ld_wait();
-                        if (valid) {
-#pragma unroll
-                            for (int j = 0; j < 4; ++j)
-                                ptx::st_global_v8(yrow + ci * 32 + 8 * j, v[8 * j], v[8 * j + 1], v[8 * j + 2], v[8 * j + 3],
-                                                  v[8 * j + 4], v[8 * j + 5], v[8 * j + 6], v[8 * j + 7]);
-                        }
-                        continue;
-                    }
-                    ptx::tma_store_wait_read<0>();          // the previous chunk's copy has read the staging row
-                    ptx::tmem_ld_wait();
-#pragma unroll
-                    for (int j = 0; j < 8; ++j) ptx::st_shared_v4(srow + 16 * j, v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
-                    ptx::fence_async_smem();
-                    if (valid && !(p.dbg & 2)) ptx::bulk_store(yrow + ci * 32, srow, 128);
-                    ptx::tma_store_commit();
-                }
-            }
-            ptx::tc_fence_before();
-            __syncwarp();
-            if (lane == 0) ptx::mbar_arrive_cluster(tempty_remote + as * 8);
-        }
-        ptx::tma_store_wait_all<0>();   // shared memory must outlive the copies that read it
     } else {
-        // ---------------------------------------------------- q producers
-        // Two groups of four warps work on alternate k-blocks.  Thread (quad, s) of a group owns four
-        // channels and tile rows 16 s .. 16 s + 15 of the group's k-block ("unit"): 18 input rows,
-        // 16 outputs.  Input rows stream through a 9-deep register ring that runs ahead across unit
-        // and tile boundaries, so loads are in flight all the time.  Interior units (all 18 rows
-        // inside the utterance) take a path without any predicate.
-        const int pw = warp - 2 - kEpiWarps;                   // 0 .. 7
-        const int grp = pw >> 2;                               // k-blocks kb = grp, grp + 2, ...
+        // ---------------------------------------------------- q producers (which also drain TMEM)
+        // Three groups of four warps; the CTA's units (tile, k-block) are dealt round-robin, unit u to
+        // group u % 3, which therefore always fills stage u % 3.  Thread (quad, s) of a group owns four
+        // channels and tile rows 16 s .. 16 s + 15 of the unit: 18 input rows, 16 outputs.  Input rows
+        // stream through a 9-deep register ring that runs ahead across unit and tile boundaries, so
+        // loads are in flight all the time.  Interior units (all 18 rows inside the utterance) take a
+        // path without any predicate.  There are no epilogue warps: the four warps of group d % 3
+        // (one per TMEM lane quarter) drain the accumulator of tile d between two of their units.
+        const int pw = warp - 2;                               // 0 .. 11
+        const int grp = pw >> 2;
         const int pt = (pw & 3) * 32 + lane;                   // 0 .. 127 within the group
         const int quad = pt & 15, s = pt >> 4;
+        const int ew = warp & 3;                               // TMEM lane quarter this warp may read
         const uint32_t full_remote = ptx::mapa(ptx::smem_u32(full_bar), 0);
+        const uint32_t tempty_remote = ptx::mapa(ptx::smem_u32(tempty_bar), 0);
         const float a1 = kPreact ? 1.f : __ldg(p.prelu_in), a2 = __ldg(p.prelu_out);
         const f2_t a1m1 = f2_pack(a1 - 1.f, a1 - 1.f), a2m1 = f2_pack(a2 - 1.f, a2 - 1.f);
         const f2_t neg1 = f2_pack(-1.f, -1.f), one2 = f2_pack(1.f, 1.f);
@@ -290,133 +240,60 @@ dwpw_kernel(const __grid_constant__ CUtensorMap tm_w_hi, const __grid_constant__
         };
         auto is_full = [](const Tile& T) { return T.lo == 0 && T.hi == kRowsPerThread + 2; };
 
-        int cur_m = -1, m, tt;
-        float mean = 0.f, rstd = 1.f;
-        Tile T = tile_setup(worker, m, tt);
-        float4 q[kRing];
-        {
-            const float* b0 = T.base + grp * kBK;
+        // TMEM accumulator of the CTA's tile number d -> y.  A lane owns one output row and writes its 32
+        // columns of a chunk with four 256-bit stores straight from registers.  (Staging the chunk in
+        // shared memory and letting the async proxy copy it out relieves the LSU, which paid off while
+        // dedicated epilogue warps could wait for the copies; a producer group must not wait.)
+        auto drain = [&](int d) {
+            const int as = d & 1;
+            const uint32_t aphase = (d >> 1) & 1;
+            const int rt = 2 * (worker + d * n_workers) + static_cast<int>(rank);
+            const bool tile_ok = rt < p.row_tiles;
+            const int m = tile_ok ? rt / p.tiles_per_utt : 0, tt = tile_ok ? rt % p.tiles_per_utt : 0;
+            const int r = ew * 32 + lane;
+            const int sr = r >> 4;
+            const int frame = tile_phase(p, tt, sr) + p.d * (tile_j0(p, tt, sr) + (r & 15));
+            const bool valid = tile_ok && frame < p.K;
+            float* yrow = p.y + (static_cast<long long>(m) * p.K + frame) * kBN;
+            ptx::mbar_wait(tfull_bar + as, aphase);
+            ptx::tc_fence_after();
+            if (!(p.dbg & 1)) {
+#pragma unroll 1
+                for (int ci = 0; ci < kBN / 32; ++ci) {
+                    uint32_t v[32];
+                    ptx::tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(ew * 32) << 16) + as * kBN + ci * 32, v);
+                    ptx::tmem_ld_wait();
+                    if (valid && !(p.dbg & 2)) {
 #pragma unroll
-            for (int t = 0; t < kRing; ++t) {
-                q[t] = make_float4(0.f, 0.f, 0.f, 0.f);
-                if (t >= T.lo && t < T.hi) q[t] = ld_row(b0 + t * strd);
-            }
-        }
-        int it = 0;
-        for (int item = worker; item < p.items; item += n_workers, ++it) {
-            if (m != cur_m) {
-                const float2 st = gln_finalize_warp(p.in_stat + static_cast<long long>(m) * p.in_P, p.in_P,
-                                                    static_cast<double>(p.K) * p.H);
-                mean = st.x, rstd = st.y;
-                cur_m = m;
-            }
-            Tile Tn = T;
-            int mn_ = m, ttn = tt;
-            f2_t ls[2] = {0ull, 0ull}, lss[2] = {0ull, 0ull};
-            for (int kb = grp; kb < nkb; kb += 2) {
-                const int nblk = it * nkb + kb;                        // k-blocks this CTA has consumed so far
-                const int stage = nblk % kStages;
-                const uint32_t phase = (nblk / kStages) & 1;
-                const bool last_kb = kb + 2 >= nkb;
-                if (last_kb) Tn = tile_setup(item + n_workers, mn_, ttn);
-                // rows kRing .. 17 of this unit, then rows 0 .. kRing-1 of the thread's next unit
-                const float* pc = T.base + kb * kBK + kRing * strd;
-                const float* pn = Tn.base + (last_kb ? grp : kb + 2) * kBK;
-                const int c = kb * kBK + quad * 4;
-                const bool fast = is_full(T) && is_full(Tn);
-                // per-channel constants.  Interior units fold the norm into the taps:
-                //   d = sum_t w_t (A pv_t + B) = sum_t (w_t A) pv_t + B (w_0 + w_1 + w_2),  pv = PReLU(v)
-                // boundary units keep n1 = A pv + B explicit, because the zero padding applies to n1.
-                f2_t A[2], Bc[2], w0[2], w1[2], w2[2];
-                {
-                    const float4 g = *reinterpret_cast<const float4*>(cst + c);
-                    const float4 b = *reinterpret_cast<const float4*>(cst + p.H + c);
-                    const float4 u0 = *reinterpret_cast<const float4*>(cst + 2 * p.H + c);
-                    const float4 u1 = *reinterpret_cast<const float4*>(cst + 3 * p.H + c);
-                    const float4 u2 = *reinterpret_cast<const float4*>(cst + 4 * p.H + c);
-                    const float Af[4] = {g.x * rstd, g.y * rstd, g.z * rstd, g.w * rstd};
-                    const float Bf[4] = {b.x - Af[0] * mean, b.y - Af[1] * mean, b.z - Af[2] * mean, b.w - Af[3] * mean};
-                    // f[3 ch + t]: tap t of channel ch
-                    const float f[12] = {u0.x, u1.x, u2.x, u0.y, u1.y, u2.y, u0.z, u1.z, u2.z, u0.w, u1.w, u2.w};
-#pragma unroll
-                    for (int i = 0; i < 2; ++i) {
-                        A[i] = f2_pack(Af[2 * i], Af[2 * i + 1]);
-                        const f2_t Bp = f2_pack(Bf[2 * i], Bf[2 * i + 1]);
-                        const f2_t r0 = f2_pack(f[6 * i], f[6 * i + 3]), r1 = f2_pack(f[6 * i + 1], f[6 * i + 4]);
-                        const f2_t r2 = f2_pack(f[6 * i + 2], f[6 * i + 5]);
-                        // products of packed multiplies are born as register pairs (packing loaded scalars at
-                        // every use costs two moves per operand)
-                        const f2_t sc = fast ? A[i] : one2;
-                        w0[i] = f2_mul(r0, sc), w1[i] = f2_mul(r1, sc), w2[i] = f2_mul(r2, sc);
-                        Bc[i] = fast ? f2_mul(Bp, f2_add(f2_add(r0, r1), r2)) : f2_mul(Bp, one2);
+                        for (int j = 0; j < 4; ++j)
+                            ptx::st_global_v8(yrow + ci * 32 + 8 * j, v[8 * j], v[8 * j + 1], v[8 * j + 2], v[8 * j + 3],
+                                              v[8 * j + 4], v[8 * j + 5], v[8 * j + 6], v[8 * j + 7]);
                     }
                 }
-                ptx::mbar_wait(empty_bar + stage, phase ^ 1);
-                const uint32_t hi_base = ptx::smem_u32(smem + stage * kStageBytes) + row_off0;
-
-                auto unit = [&](auto fast_tag) {
-                    constexpr bool kFast = decltype(fast_tag)::value;
-                    // row t -> pv = PReLU(v) (interior) or n1 = A pv + B, zero outside the utterance
-                    // (boundary); then the ring slot is refilled
-                    auto xform = [&](int t, f2_t (&o)[2]) {
-                        const float4 v = q[t % kRing];
-                        const f2_t v2[2] = {f2_pack(v.x, v.y), f2_pack(v.z, v.w)};
-#pragma unroll
-                        for (int i = 0; i < 2; ++i) {
-                            if (kPreact) {
-                                o[i] = v2[i];
-                            } else {
-                                const f2_t mn = i == 0 ? f2_pack(fminf(v.x, 0.f), fminf(v.y, 0.f))
-                                                       : f2_pack(fminf(v.z, 0.f), fminf(v.w, 0.f));
-                                o[i] = f2_fma(a1m1, mn, v2[i]);
-                            }
-                            if (!kFast) o[i] = (t >= T.lo && t < T.hi) ? f2_fma(A[i], o[i], Bc[i]) : 0ull;
-                        }
-                        if (t < kRing) {
-                            if (kFast || (t + kRing >= T.lo && t + kRing < T.hi)) q[t % kRing] = ld_row(pc);
-                            pc += strd;
-                        } else {
-                            if (kFast || (t - kRing >= Tn.lo && t - kRing < Tn.hi))
-                                q[t % kRing] = ld_row(pn);
-                            else
-                                q[t % kRing] = make_float4(0.f, 0.f, 0.f, 0.f);
-                            pn += strd;
-                        }
-                    };
-                    f2_t x0[2], x1[2], x2[2];
-                    xform(0, x0);
-                    xform(1, x1);
-#pragma unroll
-                    for (int o = 0; o < kRowsPerThread; ++o) {
-                        xform(o + 2, x2);
-                        uint32_t h[2], l[2];
-#pragma unroll
-                        for (int i = 0; i < 2; ++i) {
-                            const f2_t acc = kFast ? f2_fma(w2[i], x2[i], f2_fma(w1[i], x1[i], f2_fma(w0[i], x0[i], Bc[i])))
-                                                   : f2_fma(w2[i], x2[i], f2_fma(w1[i], x1[i], f2_mul(w0[i], x0[i])));
-                            float c0, c1;
-                            f2_unpack(acc, c0, c1);
-                            f2_t qq = f2_fma(a2m1, f2_pack(fminf(c0, 0.f), fminf(c1, 0.f)), acc);   // PReLU
-                            if (!kFast && o >= T.n) qq = 0ull;
-                            ls[i] = f2_add(ls[i], qq);
-                            lss[i] = f2_fma(qq, qq, lss[i]);
-                            f2_split_bf16(qq, neg1, h[i], l[i]);
-                            x0[i] = x1[i], x1[i] = x2[i];
-                        }
-                        // row 16 s + o of the tile: 128 B rows, the 16 B chunk index XOR (row & 7) = XOR (o & 7).
-                        // hi_base is 1024-aligned, so the XOR can be applied to the whole address.
-                        const uint32_t ad = ((hi_base + cs) ^ (static_cast<uint32_t>(o & 7) << 4)) + static_cast<uint32_t>(o) * 128u;
-                        asm volatile("st.volatile.shared.v2.b32 [%0], {%1, %2};" ::"r"(ad), "r"(h[0]), "r"(h[1]) : "memory");
-                        asm volatile("st.volatile.shared.v2.b32 [%0], {%1, %2};" ::"r"(ad + kABytes), "r"(l[0]), "r"(l[1]) : "memory");
-                    }
-                };
-                if (fast) unit(std::true_type{});
-                else unit(std::false_type{});
-                ptx::fence_async_smem();      // generic-proxy stores -> visible to the tensor core (async proxy)
-                __syncwarp();
-                if (lane == 0) ptx::mbar_arrive_cluster(full_remote + stage * 8);
             }
-            // (sum, sumsq) of this warp's share of the tile, all k-blocks of its group
+            ptx::tc_fence_before();
+            __syncwarp();
+            if (lane == 0) ptx::mbar_arrive_cluster(tempty_remote + as * 8);
+        };
+
+        const int n_tiles = worker < p.items ? (p.items - worker + n_workers - 1) / n_workers : 0;   // of this CTA
+        const int n_units = n_tiles * nkb;
+        int next_drain = grp;                                  // this group drains tiles grp, grp + 3, ...
+        int cur_it = -1, cur_m = -1, m = 0, tt = -1;
+        float mean = 0.f, rstd = 1.f;
+        Tile T = {nullptr, 0, 0, 0};
+        f2_t ls[2] = {0ull, 0ull}, lss[2] = {0ull, 0ull};
+        // every (tile, warp) slot of the partials is written exactly once: tiles in which the group had
+        // no unit (only possible when H / 64 < 3) get zeros
+        auto zero_stats = [&](int it_lo, int it_hi) {
+            for (int t = it_lo; t < it_hi; ++t) {
+                const int rt = 2 * (worker + t * n_workers) + static_cast<int>(rank);
+                if (lane == 0 && rt < p.row_tiles)
+                    p.out_stat[static_cast<long long>(rt / p.tiles_per_utt) * p.out_P + (rt % p.tiles_per_utt) * kPartialsPerTile + pw] =
+                        make_float2(0.f, 0.f);
+            }
+        };
+        auto flush_stats = [&]() {   // (sum, sumsq) of this warp's share of the tile it has just left
             float s0, s1, s2, s3, t0, t1, t2, t3;
             f2_unpack(ls[0], s0, s1), f2_unpack(ls[1], s2, s3);
             f2_unpack(lss[0], t0, t1), f2_unpack(lss[1], t2, t3);
@@ -424,7 +301,149 @@ dwpw_kernel(const __grid_constant__ CUtensorMap tm_w_hi, const __grid_constant__
             const float wlss = warp_sum((t0 + t1) + (t2 + t3));
             if (lane == 0 && tt >= 0)
                 p.out_stat[static_cast<long long>(m) * p.out_P + tt * kPartialsPerTile + pw] = make_float2(wls, wlss);
-            T = Tn, m = mn_, tt = ttn;
+            ls[0] = ls[1] = lss[0] = lss[1] = 0ull;
+        };
+        float4 q[kRing];
+        if (grp < n_units) {   // rows 0 .. 8 of the group's first unit
+            int m0, tt0;
+            const Tile T0 = tile_setup(worker + (grp / nkb) * n_workers, m0, tt0);
+            const float* b0 = T0.base + (grp % nkb) * kBK;
+#pragma unroll
+            for (int t = 0; t < kRing; ++t) {
+                q[t] = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (t >= T0.lo && t < T0.hi) q[t] = ld_row(b0 + t * strd);
+            }
+        }
+        for (int u = grp; u < n_units; u += 3) {
+            const int it = u / nkb, kb = u - it * nkb;
+            if (it != cur_it) {
+                if (cur_it >= 0) flush_stats();
+                zero_stats(cur_it + 1, it);
+                T = tile_setup(worker + it * n_workers, m, tt);
+                cur_it = it;
+                if (m != cur_m) {
+                    const float2 st = gln_finalize_warp(p.in_stat + static_cast<long long>(m) * p.in_P, p.in_P,
+                                                        static_cast<double>(p.K) * p.H);
+                    mean = st.x, rstd = st.y;
+                    cur_m = m;
+                }
+            }
+            const uint32_t phase = static_cast<uint32_t>(u / 3) & 1u;     // this group always fills stage grp
+            // the unit whose first rows replace this one's in the ring as they are consumed
+            const int un = u + 3;
+            const int itn = un / nkb, kbn = un - itn * nkb;
+            Tile Tn = T;
+            if (itn != it) {
+                int mn_, ttn;
+                Tn = tile_setup(un < n_units ? worker + itn * n_workers : p.items, mn_, ttn);
+            }
+            // rows kRing .. 17 of this unit, then rows 0 .. kRing-1 of the next one
+            const float* pc = T.base + kb * kBK + kRing * strd;
+            const float* pn = Tn.base + kbn * kBK;
+            const int c = kb * kBK + quad * 4;
+            const bool fast = is_full(T) && is_full(Tn);
+            // per-channel constants.  Interior units fold the norm into the taps:
+            //   d = sum_t w_t (A pv_t + B) = sum_t (w_t A) pv_t + B (w_0 + w_1 + w_2),  pv = PReLU(v)
+            // boundary units keep n1 = A pv + B explicit, because the zero padding applies to n1.
+            f2_t A[2], Bc[2], w0[2], w1[2], w2[2];
+            {
+                const float4 g = *reinterpret_cast<const float4*>(cst + c);
+                const float4 b = *reinterpret_cast<const float4*>(cst + p.H + c);
+                const float4 u0 = *reinterpret_cast<const float4*>(cst + 2 * p.H + c);
+                const float4 u1 = *reinterpret_cast<const float4*>(cst + 3 * p.H + c);
+                const float4 u2 = *reinterpret_cast<const float4*>(cst + 4 * p.H + c);
+                const float Af[4] = {g.x * rstd, g.y * rstd, g.z * rstd, g.w * rstd};
+                const float Bf[4] = {b.x - Af[0] * mean, b.y - Af[1] * mean, b.z - Af[2] * mean, b.w - Af[3] * mean};
+                // f[3 ch + t]: tap t of channel ch
+                const float f[12] = {u0.x, u1.x, u2.x, u0.y, u1.y, u2.y, u0.z, u1.z, u2.z, u0.w, u1.w, u2.w};
+#pragma unroll
+                for (int i = 0; i < 2; ++i) {
+                    A[i] = f2_pack(Af[2 * i], Af[2 * i + 1]);
+                    const f2_t Bp = f2_pack(Bf[2 * i], Bf[2 * i + 1]);
+                    const f2_t r0 = f2_pack(f[6 * i], f[6 * i + 3]), r1 = f2_pack(f[6 * i + 1], f[6 * i + 4]);
+                    const f2_t r2 = f2_pack(f[6 * i + 2], f[6 * i + 5]);
+                    // products of packed multiplies are born as register pairs (packing loaded scalars at
+                    // every use costs two moves per operand)
+                    const f2_t sc = fast ? A[i] : one2;
+                    w0[i] = f2_mul(r0, sc), w1[i] = f2_mul(r1, sc), w2[i] = f2_mul(r2, sc);
+                    Bc[i] = fast ? f2_mul(Bp, f2_add(f2_add(r0, r1), r2)) : f2_mul(Bp, one2);
+                }
+            }
+            ptx::mbar_wait(empty_bar + grp, phase ^ 1);
+            const uint32_t hi_base = ptx::smem_u32(smem + grp * kStageBytes) + row_off0;
+
+            auto unit = [&](auto fast_tag) {
+                constexpr bool kFast = decltype(fast_tag)::value;
+                // row t -> pv = PReLU(v) (interior) or n1 = A pv + B, zero outside the utterance
+                // (boundary); then the ring slot is refilled
+                auto xform = [&](int t, f2_t (&o)[2]) {
+                    const float4 v = q[t % kRing];
+                    const f2_t v2[2] = {f2_pack(v.x, v.y), f2_pack(v.z, v.w)};
+#pragma unroll
+                    for (int i = 0; i < 2; ++i) {
+                        if (kPreact) {
+                            o[i] = v2[i];
+                        } else {
+                            const f2_t mn = i == 0 ? f2_pack(fminf(v.x, 0.f), fminf(v.y, 0.f))
+                                                   : f2_pack(fminf(v.z, 0.f), fminf(v.w, 0.f));
+                            o[i] = f2_fma(a1m1, mn, v2[i]);
+                        }
+                        if (!kFast) o[i] = (t >= T.lo && t < T.hi) ? f2_fma(A[i], o[i], Bc[i]) : 0ull;
+                    }
+                    if (t < kRing) {
+                        if (kFast || (t + kRing >= T.lo && t + kRing < T.hi)) q[t % kRing] = ld_row(pc);
+                        pc += strd;
+                    } else {
+                        if (kFast || (t - kRing >= Tn.lo && t - kRing < Tn.hi))
+                            q[t % kRing] = ld_row(pn);
+                        else
+                            q[t % kRing] = make_float4(0.f, 0.f, 0.f, 0.f);
+                        pn += strd;
+                    }
+                };
+                f2_t x0[2], x1[2], x2[2];
+                xform(0, x0);
+                xform(1, x1);
+#pragma unroll
+                for (int o = 0; o < kRowsPerThread; ++o) {
+                    xform(o + 2, x2);
+                    uint32_t h[2], l[2];
+#pragma unroll
+                    for (int i = 0; i < 2; ++i) {
+                        const f2_t acc = kFast ? f2_fma(w2[i], x2[i], f2_fma(w1[i], x1[i], f2_fma(w0[i], x0[i], Bc[i])))
+                                               : f2_fma(w2[i], x2[i], f2_fma(w1[i], x1[i], f2_mul(w0[i], x0[i])));
+                        float c0, c1;
+                        f2_unpack(acc, c0, c1);
+                        f2_t qq = f2_fma(a2m1, f2_pack(fminf(c0, 0.f), fminf(c1, 0.f)), acc);   // PReLU
+                        if (!kFast && o >= T.n) qq = 0ull;
+                        ls[i] = f2_add(ls[i], qq);
+                        lss[i] = f2_fma(qq, qq, lss[i]);
+                        f2_split_bf16(qq, neg1, h[i], l[i]);
+                        x0[i] = x1[i], x1[i] = x2[i];
+                    }
+                    // row 16 s + o of the tile: 128 B rows, the 16 B chunk index XOR (row & 7) = XOR (o & 7).
+                    // hi_base is 1024-aligned, so the XOR can be applied to the whole address.
+                    const uint32_t ad = ((hi_base + cs) ^ (static_cast<uint32_t>(o & 7) << 4)) + static_cast<uint32_t>(o) * 128u;
+                    asm volatile("st.volatile.shared.v2.b32 [%0], {%1, %2};" ::"r"(ad), "r"(h[0]), "r"(h[1]) : "memory");
+                    asm volatile("st.volatile.shared.v2.b32 [%0], {%1, %2};" ::"r"(ad + kABytes), "r"(l[0]), "r"(l[1]) : "memory");
+                }
+            };
+            if (fast) unit(std::true_type{});
+            else unit(std::false_type{});
+            ptx::fence_async_smem();      // generic-proxy stores -> visible to the tensor core (async proxy)
+            __syncwarp();
+            if (lane == 0) ptx::mbar_arrive_cluster(full_remote + grp * 8);
+            // drain duty: tiles before the current one whose accumulators are this group's
+            while (next_drain < it) {
+                drain(next_drain);
+                next_drain += 3;
+            }
+        }
+        if (cur_it >= 0) flush_stats();
+        zero_stats(cur_it + 1, n_tiles);
+        while (next_drain < n_tiles) {
+            drain(next_drain);
+            next_drain += 3;
         }
     }
 

@@ -266,9 +266,8 @@ class SeparationEngine:
         self.micro_batch = 16
         self.use_graph = False
         # blocks with dilation <= this take the fused depthwise + pointwise kernel where the configuration
-        # allows it (0 = never).  Beyond 32 every producer unit touches an utterance boundary and the
-        # unfused pair is faster.
-        self.fuse_max_dilation = 32
+        # allows it (0 = never; the default covers every dilation)
+        self.fuse_max_dilation = 1 << 30
         self.launches = 0   # kernels of libctn_b200 launched by forward() so far
 
     def num_launches(self):
