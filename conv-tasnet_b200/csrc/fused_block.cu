@@ -41,15 +41,19 @@ namespace fb {
 constexpr int kBM = 128;             // tile rows = TMEM lanes
 constexpr int kBN = 256;             // output channels (B) per tile = whole pointwise output
 constexpr int kBK = 64;              // channels per k-block = one 128 B swizzle atom of bf16
-constexpr int kStages = 3;
+constexpr int kASlots = 4;           // produced A units in flight: more than producer groups, so a group never
+                                     // waits for the MMAs to consume its own previous unit
+constexpr int kWSlots = 2;           // weight k-blocks in flight (TMA, L2-resident)
 constexpr int kABytes = kBM * kBK * 2;           // one of hi / lo
 constexpr int kWBytes = (kBN / 2) * kBK * 2;     // this CTA's half of the weight tile, one of hi / lo
-constexpr int kStageBytes = 2 * kABytes + 2 * kWBytes;
+constexpr int kASlotBytes = 2 * kABytes;
+constexpr int kWSlotBytes = 2 * kWBytes;
+constexpr int kTileBytes = kASlots * kASlotBytes + kWSlots * kWSlotBytes;
 constexpr int kProdWarps = 12;       // three groups of four warps; they also drain TMEM
 constexpr int kThreads = 64 + 32 * kProdWarps;
 constexpr int kBarBytes = 256;
 constexpr int kStgBytes = 0;
-constexpr int kSmemFixed = kStages * kStageBytes + kBarBytes + kStgBytes;   // + 20 H bytes of per-channel constants
+constexpr int kSmemFixed = kTileBytes + kBarBytes + kStgBytes;   // + 20 H bytes of per-channel constants
 constexpr int kSmemMax = 232448;
 constexpr int kRowsPerThread = 16;   // outputs a producer thread marches per k-block
 constexpr int kPartialsPerTile = kProdWarps;
@@ -87,9 +91,12 @@ dwpw_kernel(const __grid_constant__ CUtensorMap tm_w_hi, const __grid_constant__
     const int n_workers = static_cast<int>(gridDim.x >> 1);
     extern __shared__ __align__(1024) uint8_t smem[];
     if ((ptx::smem_u32(smem) & 1023u) != 0) __trap();
-    uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + kStages * kStageBytes);
-    uint64_t* empty_bar = full_bar + kStages;
-    uint64_t* tfull_bar = empty_bar + kStages;
+    uint8_t* wsm = smem + kASlots * kASlotBytes;                // weight slots follow the A slots
+    uint64_t* afull_bar = reinterpret_cast<uint64_t*>(smem + kTileBytes);
+    uint64_t* aempty_bar = afull_bar + kASlots;
+    uint64_t* wfull_bar = aempty_bar + kASlots;
+    uint64_t* wempty_bar = wfull_bar + kWSlots;
+    uint64_t* tfull_bar = wempty_bar + kWSlots;
     uint64_t* tempty_bar = tfull_bar + 2;
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 2);
 
@@ -97,7 +104,7 @@ dwpw_kernel(const __grid_constant__ CUtensorMap tm_w_hi, const __grid_constant__
     const int lane = threadIdx.x & 31;
     const int nkb = p.H / kBK;
     // per-channel constants of the producers: gamma, beta and the three taps, [5][H]
-    float* cst = reinterpret_cast<float*>(smem + kStages * kStageBytes + kBarBytes + kStgBytes);
+    float* cst = reinterpret_cast<float*>(smem + kTileBytes + kBarBytes + kStgBytes);
     for (int i = threadIdx.x; i < p.H; i += kThreads) {
         cst[i] = __ldg(p.gamma_in + i);
         cst[p.H + i] = __ldg(p.beta_in + i);
@@ -109,11 +116,13 @@ dwpw_kernel(const __grid_constant__ CUtensorMap tm_w_hi, const __grid_constant__
     if (warp == 0 && lane == 0) {
         ptx::prefetch_tmap(&tm_w_hi);
         ptx::prefetch_tmap(&tm_w_lo);
-        for (int i = 0; i < kStages; ++i) {
-            // leader: weight bytes of both CTAs (one expect_tx arrival) + one arrival per producer warp
-            // of the group that fills the stage, from both CTAs
-            ptx::mbar_init(full_bar + i, 1 + 2 * 4);
-            ptx::mbar_init(empty_bar + i, 1);
+        for (int i = 0; i < kASlots; ++i) {
+            ptx::mbar_init(afull_bar + i, 2 * 4);   // one arrival per producer warp of the filling group, both CTAs
+            ptx::mbar_init(aempty_bar + i, 1);
+        }
+        for (int i = 0; i < kWSlots; ++i) {
+            ptx::mbar_init(wfull_bar + i, 1);       // leader: weight bytes of both CTAs (one expect_tx arrival)
+            ptx::mbar_init(wempty_bar + i, 1);
         }
         for (int i = 0; i < 2; ++i) {
             ptx::mbar_init(tfull_bar + i, 1);
@@ -132,18 +141,18 @@ dwpw_kernel(const __grid_constant__ CUtensorMap tm_w_hi, const __grid_constant__
     if (warp == 0) {
         // ------------------------------------------------ TMA producer (weights only)
         if (lane == 0) {
-            int stage = 0;
+            int slot = 0;
             uint32_t phase = 0;
-            const uint32_t fb0 = ptx::mapa(ptx::smem_u32(full_bar), 0);
+            const uint32_t fb0 = ptx::mapa(ptx::smem_u32(wfull_bar), 0);
             for (int item = worker; item < p.items; item += n_workers) {
                 for (int kb = 0; kb < nkb; ++kb) {
-                    ptx::mbar_wait(empty_bar + stage, phase ^ 1);
-                    uint8_t* st = smem + stage * kStageBytes + 2 * kABytes;
-                    if (rank == 0) ptx::mbar_expect_tx(full_bar + stage, 4 * kWBytes);
-                    ptx::tma_load_2d_pair(st, &tm_w_hi, fb0 + stage * 8, kb * kBK, static_cast<int>(rank) * (kBN / 2));
-                    ptx::tma_load_2d_pair(st + kWBytes, &tm_w_lo, fb0 + stage * 8, kb * kBK,
+                    ptx::mbar_wait(wempty_bar + slot, phase ^ 1);
+                    uint8_t* st = wsm + slot * kWSlotBytes;
+                    if (rank == 0) ptx::mbar_expect_tx(wfull_bar + slot, 4 * kWBytes);
+                    ptx::tma_load_2d_pair(st, &tm_w_hi, fb0 + slot * 8, kb * kBK, static_cast<int>(rank) * (kBN / 2));
+                    ptx::tma_load_2d_pair(st + kWBytes, &tm_w_lo, fb0 + slot * 8, kb * kBK,
                                           static_cast<int>(rank) * (kBN / 2));
-                    if (++stage == kStages) stage = 0, phase ^= 1;
+                    if (++slot == kWSlots) slot = 0, phase ^= 1;
                 }
             }
         }
@@ -151,8 +160,8 @@ dwpw_kernel(const __grid_constant__ CUtensorMap tm_w_hi, const __grid_constant__
         // -------------------------------------------------- MMA issuer (leader CTA)
         if (lane == 0 && rank == 0) {
             constexpr uint32_t idesc = ptx::make_idesc_bf16(2 * kBM, kBN, 0, 0);
-            int stage = 0;
-            uint32_t phase = 0;
+            int aslot = 0, wslot = 0;
+            uint32_t aph = 0, wph = 0;
             int it = 0;
             for (int item = worker; item < p.items; item += n_workers, ++it) {
                 const int as = it & 1;
@@ -161,13 +170,15 @@ dwpw_kernel(const __grid_constant__ CUtensorMap tm_w_hi, const __grid_constant__
                 ptx::tc_fence_after();
                 const uint32_t d_tmem = tmem_base + as * kBN;
                 for (int kb = 0; kb < nkb; ++kb) {
-                    ptx::mbar_wait(full_bar + stage, phase);
+                    ptx::mbar_wait(wfull_bar + wslot, wph);
+                    ptx::mbar_wait(afull_bar + aslot, aph);
                     ptx::tc_fence_after();
-                    const uint32_t sa = ptx::smem_u32(smem + stage * kStageBytes);
+                    const uint32_t sa = ptx::smem_u32(smem + aslot * kASlotBytes);
+                    const uint32_t sw = ptx::smem_u32(wsm + wslot * kWSlotBytes);
                     const uint64_t a_hi = ptx::make_smem_desc(sa, 0, 1024, ptx::kLayoutSwizzle128B);
                     const uint64_t a_lo = ptx::make_smem_desc(sa + kABytes, 0, 1024, ptx::kLayoutSwizzle128B);
-                    const uint64_t w_hi = ptx::make_smem_desc(sa + 2 * kABytes, 0, 1024, ptx::kLayoutSwizzle128B);
-                    const uint64_t w_lo = ptx::make_smem_desc(sa + 2 * kABytes + kWBytes, 0, 1024, ptx::kLayoutSwizzle128B);
+                    const uint64_t w_hi = ptx::make_smem_desc(sw, 0, 1024, ptx::kLayoutSwizzle128B);
+                    const uint64_t w_lo = ptx::make_smem_desc(sw + kWBytes, 0, 1024, ptx::kLayoutSwizzle128B);
 #pragma unroll
                     for (int k = 0; k < ((p.dbg & 4) ? 0 : kBK / 16); ++k) {
                         const uint64_t adv = static_cast<uint64_t>((k * 16 * 2) >> 4);
@@ -175,9 +186,11 @@ dwpw_kernel(const __grid_constant__ CUtensorMap tm_w_hi, const __grid_constant__
                         ptx::umma_bf16_pair(d_tmem, a_lo + adv, w_hi + adv, idesc, 1);
                         ptx::umma_bf16_pair(d_tmem, a_hi + adv, w_lo + adv, idesc, 1);
                     }
-                    ptx::umma_commit_pair(empty_bar + stage, 3);
+                    ptx::umma_commit_pair(aempty_bar + aslot, 3);   // frees the slots in BOTH CTAs
+                    ptx::umma_commit_pair(wempty_bar + wslot, 3);
                     if (kb == nkb - 1) ptx::umma_commit_pair(tfull_bar + as, 3);
-                    if (++stage == kStages) stage = 0, phase ^= 1;
+                    if (++aslot == ((p.dbg & 256) ? 3 : kASlots)) aslot = 0, aph ^= 1;
+                    if (++wslot == kWSlots) wslot = 0, wph ^= 1;
                 }
             }
         }
@@ -195,7 +208,7 @@ dwpw_kernel(const __grid_constant__ CUtensorMap tm_w_hi, const __grid_constant__
         const int pt = (pw & 3) * 32 + lane;                   // 0 .. 127 within the group
         const int quad = pt & 15, s = pt >> 4;
         const int ew = warp & 3;                               // TMEM lane quarter this warp may read
-        const uint32_t full_remote = ptx::mapa(ptx::smem_u32(full_bar), 0);
+        const uint32_t full_remote = ptx::mapa(ptx::smem_u32(afull_bar), 0);
         const uint32_t tempty_remote = ptx::mapa(ptx::smem_u32(tempty_bar), 0);
         const float a1 = kPreact ? 1.f : __ldg(p.prelu_in), a2 = __ldg(p.prelu_out);
         const f2_t a1m1 = f2_pack(a1 - 1.f, a1 - 1.f), a2m1 = f2_pack(a2 - 1.f, a2 - 1.f);
@@ -328,7 +341,9 @@ dwpw_kernel(const __grid_constant__ CUtensorMap tm_w_hi, const __grid_constant__
                     cur_m = m;
                 }
             }
-            const uint32_t phase = static_cast<uint32_t>(u / 3) & 1u;     // this group always fills stage grp
+            const int nslots = (p.dbg & 256) ? 3 : kASlots;               // (experiment: one slot per group)
+            const int aslot = u % nslots;                                 // units are consumed in order
+            const uint32_t phase = static_cast<uint32_t>(u / nslots) & 1u;
             // the unit whose first rows replace this one's in the ring as they are consumed
             const int un = u + 3;
             const int itn = un / nkb, kbn = un - itn * nkb;
@@ -369,8 +384,8 @@ dwpw_kernel(const __grid_constant__ CUtensorMap tm_w_hi, const __grid_constant__
                     Bc[i] = fast ? f2_mul(Bp, f2_add(f2_add(r0, r1), r2)) : f2_mul(Bp, one2);
                 }
             }
-            ptx::mbar_wait(empty_bar + grp, phase ^ 1);
-            const uint32_t hi_base = ptx::smem_u32(smem + grp * kStageBytes) + row_off0;
+            ptx::mbar_wait(aempty_bar + aslot, phase ^ 1);
+            const uint32_t hi_base = ptx::smem_u32(smem + aslot * kASlotBytes) + row_off0;
 
             auto unit = [&](auto fast_tag) {
                 constexpr bool kFast = decltype(fast_tag)::value;
@@ -432,7 +447,7 @@ dwpw_kernel(const __grid_constant__ CUtensorMap tm_w_hi, const __grid_constant__
             else unit(std::false_type{});
             ptx::fence_async_smem();      // generic-proxy stores -> visible to the tensor core (async proxy)
             __syncwarp();
-            if (lane == 0) ptx::mbar_arrive_cluster(full_remote + grp * 8);
+            if (lane == 0) ptx::mbar_arrive_cluster(full_remote + aslot * 8);
             // drain duty: tiles before the current one whose accumulators are this group's
             while (next_drain < it) {
                 drain(next_drain);
