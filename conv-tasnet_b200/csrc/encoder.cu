@@ -85,6 +85,80 @@ encoder_fwd_kernel(const float* __restrict__ mixture, const float* __restrict__ 
     }
 }
 
+
+// Register-blocked variant for the usual filter lengths: a thread keeps the L taps of its two
+// channels in registers and walks over the frames of the tile, reading the samples as shared-memory
+// broadcasts (L/2 LDS.64 + 2 L FMAs per frame instead of L LDS + L LDS.64 + 2 L FMAs).  N even,
+// N / 2 <= 512 threads.  The per-frame channel sums for the cLN statistics go through shared memory
+// in a fixed order.
+constexpr int kEncTileR = 64;
+
+template <int L>
+__global__ void __launch_bounds__(512)
+encoder_fwd_reg_kernel(const float* __restrict__ mixture, const float* __restrict__ U, int T, int N, int K,
+                       float* __restrict__ w_f32, __nv_bfloat16* __restrict__ w_hi, __nv_bfloat16* __restrict__ w_lo,
+                       float2* __restrict__ rowstat) {
+    constexpr int hop = L / 2;
+    constexpr int kSamp = (kEncTileR - 1) * hop + L;
+    __shared__ __align__(16) float xs[kSamp + 2];
+    __shared__ float2 red[kEncTileR][16];   // [frame][warp]
+    const int m = blockIdx.y;
+    const int k0 = blockIdx.x * kEncTileR;
+    const int nk = min(kEncTileR, K - k0);
+    const int nsamp = (nk - 1) * hop + L;
+    const float* src = mixture + static_cast<long long>(m) * T + static_cast<long long>(k0) * hop;
+    for (int i = threadIdx.x; i < kSamp + 2; i += blockDim.x) xs[i] = i < nsamp ? src[i] : 0.f;
+    const int n = 2 * threadIdx.x;
+    const bool act = n < N;
+    float u0[L], u1[L];
+#pragma unroll
+    for (int l = 0; l < L; ++l) {
+        u0[l] = act ? __ldg(U + static_cast<long long>(n) * L + l) : 0.f;
+        u1[l] = act ? __ldg(U + static_cast<long long>(n + 1) * L + l) : 0.f;
+    }
+    __syncthreads();
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int nwarps = (blockDim.x + 31) >> 5;
+    for (int r = 0; r < nk; ++r) {
+        const float2* x2 = reinterpret_cast<const float2*>(xs + r * hop);   // hop is even: 8-byte aligned
+        float a0 = 0.f, a1 = 0.f;
+#pragma unroll
+        for (int l = 0; l < L / 2; ++l) {
+            const float2 xv = x2[l];
+            a0 = fmaf(u0[2 * l], xv.x, a0);
+            a1 = fmaf(u1[2 * l], xv.x, a1);
+            a0 = fmaf(u0[2 * l + 1], xv.y, a0);
+            a1 = fmaf(u1[2 * l + 1], xv.y, a1);
+        }
+        a0 = fmaxf(a0, 0.f), a1 = fmaxf(a1, 0.f);
+        const long long o = (static_cast<long long>(m) * K + k0 + r) * N + n;
+        if (act) {
+            if (w_f32) *reinterpret_cast<float2*>(w_f32 + o) = make_float2(a0, a1);
+            if (w_hi) {
+                uint32_t h, lo;
+                split_pack2(a0, a1, h, lo);
+                *reinterpret_cast<uint32_t*>(w_hi + o) = h;
+                *reinterpret_cast<uint32_t*>(w_lo + o) = lo;
+            }
+        }
+        if (rowstat) {
+            const float s = warp_sum(a0 + a1);
+            const float ss = warp_sum(fmaf(a0, a0, a1 * a1));
+            if (lane == 0) red[r][warp] = make_float2(s, ss);
+        }
+    }
+    if (rowstat) {
+        __syncthreads();
+        for (int r = threadIdx.x; r < nk; r += blockDim.x) {
+            float s = 0.f, ss = 0.f;
+            for (int w = 0; w < nwarps; ++w) s += red[r][w].x, ss += red[r][w].y;
+            const float mean = s / N;
+            const float var = fmaxf(ss / N - mean * mean, 0.f);
+            rowstat[static_cast<long long>(m) * K + k0 + r] = make_float2(mean, rsqrtf(var + kEps));
+        }
+    }
+}
+
 }  // namespace ctn
 
 extern "C" int ctn_encoder_fwd(const float* mixture, const float* U, int M, int T, int N, int L, float* w_f32,
@@ -96,6 +170,20 @@ extern "C" int ctn_encoder_fwd(const float* mixture, const float* U, int M, int 
     CTN_REQUIRE((w_hi == nullptr) == (w_lo == nullptr), "ctn_encoder_fwd: w_hi/w_lo must be given together");
     const int hop = L / 2;
     const int K = (T - L) / hop + 1;
+    auto aligned = [](const void* p, int a) { return (reinterpret_cast<uintptr_t>(p) & (a - 1)) == 0; };
+    if ((L == 16 || L == 20) && N % 2 == 0 && N <= 1024 && aligned(w_f32, 8) && aligned(w_hi, 4) && aligned(w_lo, 4)) {
+        dim3 grid(ceil_div(K, kEncTileR), M);
+        const int threads = ceil_div(N / 2, 32) * 32;
+        cudaStream_t st = static_cast<cudaStream_t>(stream);
+        if (L == 20)
+            encoder_fwd_reg_kernel<20><<<grid, threads, 0, st>>>(mixture, U, T, N, K, w_f32, static_cast<__nv_bfloat16*>(w_hi),
+                                                                static_cast<__nv_bfloat16*>(w_lo), static_cast<float2*>(rowstat));
+        else
+            encoder_fwd_reg_kernel<16><<<grid, threads, 0, st>>>(mixture, U, T, N, K, w_f32, static_cast<__nv_bfloat16*>(w_hi),
+                                                                static_cast<__nv_bfloat16*>(w_lo), static_cast<float2*>(rowstat));
+        CTN_LAUNCH_CHECK("encoder_fwd_reg_kernel");
+        return CTN_OK;
+    }
     const size_t smem = (static_cast<size_t>(L) * N + (kEncTile - 1) * hop + L) * sizeof(float);
     if (smem > 48 * 1024) {
         CTN_REQUIRE(smem <= 200 * 1024, "ctn_encoder_fwd: N*L=%d too large for shared memory", N * L);

@@ -29,7 +29,7 @@ def _rand(*shape, seed=0, scale=1.0):
 
 # ----------------------------------------------------------------- encoder
 @pytest.mark.parametrize("M,T,N,L", [(2, 12, 3, 4), (3, 1207, 64, 16), (2, 32007, 256, 20), (1, 4000, 512, 16),
-                                     (1, 57, 5, 5)])
+                                     (1, 57, 5, 5), (2, 997, 30, 20), (1, 16, 6, 16), (2, 5000, 1024, 20)])
 def test_encoder(M, T, N, L):
     mix = _rand(M, T, seed=1, scale=0.1)
     U = _rand(N, 1, L, seed=2, scale=0.3)
