@@ -185,6 +185,7 @@ def run_b200(args):
     eng = model.engine()
     eng.micro_batch = args.micro_batch
     eng.fuse_max_dilation = args.fuse
+    eng.fuse_update = bool(args.fuse_update)
     eng.use_graph = bool(args.graph)
 
     g = torch.Generator().manual_seed(2025 + rank)
@@ -274,6 +275,7 @@ def run_b200(args):
         names = {"gemm_conv1x1": "gemm_tc_kernel<256,pair,plain> (conv1x1 + PReLU statistics)",
                  "gemm_pointwise": "gemm_tc_kernel<256,pair,affine> (pointwise + folded gLN + residual)",
                  "gemm_dwpw_fused": "fb::dwpw_kernel (depthwise producers + pointwise GEMM)",
+                 "gemm_update_conv1x1": "c1::updc1_kernel (residual-update producers + conv1x1 GEMM + PReLU statistics)",
                  "gemm_bottleneck": "gemm_tc_kernel (bottleneck)", "gemm_mask": "gemm_tc_kernel (mask conv)",
                  "dwconv": "dwconv_march_kernel", "resid_update": "fb::resid_update_kernel",
                  "encoder": "encoder_fwd_kernel", "decoder": "decoder_fwd_blocked_kernel"}
@@ -404,6 +406,8 @@ def main():
     ap.add_argument("--micro-batch", type=int, default=64)
     ap.add_argument("--fuse", type=int, default=1 << 30,
                     help="blocks with dilation <= this use the fused depthwise+pointwise kernel (0 = off)")
+    ap.add_argument("--fuse-update", type=int, default=0,
+                    help="fold the deferred residual update into the next conv1x1 (ctn_updc1_fwd)")
     ap.add_argument("--graph", type=int, default=1)
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-train", action="store_true", help="skip the train-step leg")

@@ -53,7 +53,8 @@ constexpr int kProdWarps = 12;       // three groups of four warps; they also dr
 constexpr int kThreads = 64 + 32 * kProdWarps;
 constexpr int kBarBytes = 256;
 constexpr int kStgBytes = 0;
-constexpr int kSmemFixed = kTileBytes + kBarBytes + kStgBytes;   // + 20 H bytes of per-channel constants
+constexpr int kMaxTiles = 32;        // row tiles per CTA whose gLN-1 (mean, rstd) are precomputed
+constexpr int kSmemFixed = kTileBytes + kBarBytes + kStgBytes + kMaxTiles * 8;   // + 20 H bytes of per-channel constants
 constexpr int kSmemMax = 232448;
 constexpr int kRowsPerThread = 16;   // outputs a producer thread marches per k-block
 constexpr int kPartialsPerTile = kProdWarps;
@@ -71,7 +72,6 @@ struct Params {
     const float* prelu_out;
     float* y;
     float2* out_stat;
-    int dbg;
 };
 
 // frame of tile row r of tile tt (may be >= K: the row does not exist)
@@ -104,7 +104,8 @@ dwpw_kernel(const __grid_constant__ CUtensorMap tm_w_hi, const __grid_constant__
     const int lane = threadIdx.x & 31;
     const int nkb = p.H / kBK;
     // per-channel constants of the producers: gamma, beta and the three taps, [5][H]
-    float* cst = reinterpret_cast<float*>(smem + kTileBytes + kBarBytes + kStgBytes);
+    float2* tstat = reinterpret_cast<float2*>(smem + kTileBytes + kBarBytes + kStgBytes);   // [kMaxTiles] (mean, rstd)
+    float* cst = reinterpret_cast<float*>(smem + kTileBytes + kBarBytes + kStgBytes + kMaxTiles * 8);
     for (int i = threadIdx.x; i < p.H; i += kThreads) {
         cst[i] = __ldg(p.gamma_in + i);
         cst[p.H + i] = __ldg(p.beta_in + i);
@@ -180,7 +181,7 @@ dwpw_kernel(const __grid_constant__ CUtensorMap tm_w_hi, const __grid_constant__
                     const uint64_t w_hi = ptx::make_smem_desc(sw, 0, 1024, ptx::kLayoutSwizzle128B);
                     const uint64_t w_lo = ptx::make_smem_desc(sw + kWBytes, 0, 1024, ptx::kLayoutSwizzle128B);
 #pragma unroll
-                    for (int k = 0; k < ((p.dbg & 4) ? 0 : kBK / 16); ++k) {
+                    for (int k = 0; k < kBK / 16; ++k) {
                         const uint64_t adv = static_cast<uint64_t>((k * 16 * 2) >> 4);
                         ptx::umma_bf16_pair(d_tmem, a_hi + adv, w_hi + adv, idesc, (kb | k) != 0);
                         ptx::umma_bf16_pair(d_tmem, a_lo + adv, w_hi + adv, idesc, 1);
@@ -189,7 +190,7 @@ dwpw_kernel(const __grid_constant__ CUtensorMap tm_w_hi, const __grid_constant__
                     ptx::umma_commit_pair(aempty_bar + aslot, 3);   // frees the slots in BOTH CTAs
                     ptx::umma_commit_pair(wempty_bar + wslot, 3);
                     if (kb == nkb - 1) ptx::umma_commit_pair(tfull_bar + as, 3);
-                    if (++aslot == ((p.dbg & 256) ? 3 : kASlots)) aslot = 0, aph ^= 1;
+                    if (++aslot == kASlots) aslot = 0, aph ^= 1;
                     if (++wslot == kWSlots) wslot = 0, wph ^= 1;
                 }
             }
@@ -270,18 +271,16 @@ dwpw_kernel(const __grid_constant__ CUtensorMap tm_w_hi, const __grid_constant__
             float* yrow = p.y + (static_cast<long long>(m) * p.K + frame) * kBN;
             ptx::mbar_wait(tfull_bar + as, aphase);
             ptx::tc_fence_after();
-            if (!(p.dbg & 1)) {
 #pragma unroll 1
-                for (int ci = 0; ci < kBN / 32; ++ci) {
-                    uint32_t v[32];
-                    ptx::tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(ew * 32) << 16) + as * kBN + ci * 32, v);
-                    ptx::tmem_ld_wait();
-                    if (valid && !(p.dbg & 2)) {
+            for (int ci = 0; ci < kBN / 32; ++ci) {
+                uint32_t v[32];
+                ptx::tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(ew * 32) << 16) + as * kBN + ci * 32, v);
+                ptx::tmem_ld_wait();
+                if (valid) {
 #pragma unroll
-                        for (int j = 0; j < 4; ++j)
-                            ptx::st_global_v8(yrow + ci * 32 + 8 * j, v[8 * j], v[8 * j + 1], v[8 * j + 2], v[8 * j + 3],
-                                              v[8 * j + 4], v[8 * j + 5], v[8 * j + 6], v[8 * j + 7]);
-                    }
+                    for (int j = 0; j < 4; ++j)
+                        ptx::st_global_v8(yrow + ci * 32 + 8 * j, v[8 * j], v[8 * j + 1], v[8 * j + 2], v[8 * j + 3],
+                                          v[8 * j + 4], v[8 * j + 5], v[8 * j + 6], v[8 * j + 7]);
                 }
             }
             ptx::tc_fence_before();
@@ -316,6 +315,17 @@ dwpw_kernel(const __grid_constant__ CUtensorMap tm_w_hi, const __grid_constant__
                 p.out_stat[static_cast<long long>(m) * p.out_P + tt * kPartialsPerTile + pw] = make_float2(wls, wlss);
             ls[0] = ls[1] = lss[0] = lss[1] = 0ull;
         };
+        // Consecutive row tiles of a CTA lie in different utterances (stride 2 * n_workers tiles): finalise
+        // the statistics of all of them up front, one tile per warp, instead of a chain of dependent
+        // loads and fp64 math in front of every tile of every group.
+        for (int t = pw; t < min(n_tiles, kMaxTiles); t += kProdWarps) {
+            const int rt = 2 * (worker + t * n_workers) + static_cast<int>(rank);
+            const int mt = rt < p.row_tiles ? rt / p.tiles_per_utt : 0;
+            const float2 st = gln_finalize_warp(p.in_stat + static_cast<long long>(mt) * p.in_P, p.in_P,
+                                                static_cast<double>(p.K) * p.H);
+            if (lane == 0) tstat[t] = st;
+        }
+        ptx::named_bar_sync(1, 32 * kProdWarps);
         float4 q[kRing];
         if (grp < n_units) {   // rows 0 .. 8 of the group's first unit
             int m0, tt0;
@@ -334,14 +344,17 @@ dwpw_kernel(const __grid_constant__ CUtensorMap tm_w_hi, const __grid_constant__
                 zero_stats(cur_it + 1, it);
                 T = tile_setup(worker + it * n_workers, m, tt);
                 cur_it = it;
-                if (m != cur_m) {
+                if (it < kMaxTiles) {
+                    const float2 st = tstat[it];
+                    mean = st.x, rstd = st.y;
+                } else if (m != cur_m) {
                     const float2 st = gln_finalize_warp(p.in_stat + static_cast<long long>(m) * p.in_P, p.in_P,
                                                         static_cast<double>(p.K) * p.H);
                     mean = st.x, rstd = st.y;
-                    cur_m = m;
                 }
+                cur_m = m;
             }
-            const int nslots = (p.dbg & 256) ? 3 : kASlots;               // (experiment: one slot per group)
+            constexpr int nslots = kASlots;
             const int aslot = u % nslots;                                 // units are consumed in order
             const uint32_t phase = static_cast<uint32_t>(u / nslots) & 1u;
             // the unit whose first rows replace this one's in the ring as they are consumed
@@ -574,10 +587,6 @@ extern "C" int ctn_dwpw_fwd(const ctn_dwpw_args* args, void* stream_) {
     p.a = a.a, p.prelu_in = a.prelu_in, p.gamma_in = a.gamma_in, p.beta_in = a.beta_in;
     p.in_stat = static_cast<const float2*>(a.in_stat);
     p.wd = a.wd, p.prelu_out = a.prelu_out, p.y = a.y, p.out_stat = static_cast<float2*>(a.out_stat);
-    {
-        const char* d = getenv("CTN_GEMM_DBG");
-        p.dbg = d ? atoi(d) : 0;
-    }
     CUtensorMap tw_hi, tw_lo;
     int rc;
     if ((rc = make_tmap_bf16_kmajor(&tw_hi, a.w_hi, a.B, a.H, fb::kBN / 2)) != CTN_OK) return rc;

@@ -80,9 +80,10 @@ class _Prepared:
 class _Plan:
     """Static workspaces + call list for one (M, T) on one device."""
 
-    def __init__(self, cfg, M, T, device, fuse_max_dilation=0):
+    def __init__(self, cfg, M, T, device, fuse_max_dilation=0, fuse_update=False):
         self.cfg, self.M, self.T, self.device = cfg, M, T, device
         self.fuse_max_dilation = fuse_max_dilation
+        self.fuse_update = fuse_update
         N, L, B, H, C = cfg["N"], cfg["L"], cfg["B"], cfg["H"], cfg["C"]
         self.hop, self.K, self.T_conv = frame_geometry(T, L)
         K = self.K
@@ -160,23 +161,46 @@ class _Plan:
                                 in_norm=nat.NORM_CLN, in_stat=self.rowstat0,
                                 out_hi=self.x_hl[0], out_lo=self.x_hl[1]))
         dw = lib.ctn_dwconv_fwd
+        fw, upd, uc1 = lib.ctn_dwpw_fwd, lib.ctn_resid_update, lib.ctn_updc1_fwd
+
+        def emit(kind, flops, nbytes, call):
+            info.append((kind, flops, nbytes))
+            calls.append(call)
+
+        def emit_update(pend):
+            u = (self.x_hl[0].data_ptr(), self.x_hl[1].data_ptr(), self.y.data_ptr(), self.stat2f.data_ptr(),
+                 pend["P"], float(K) * H, pend["g"].data_ptr(), pend["b"].data_ptr(), M, K, B)
+            emit("resid_update", 2.0 * Rr * B, 12.0 * Rr * B, lambda s, u=u: upd(*u, s))
+
+        use_c1 = self.fuse_update and self.norm == nat.NORM_GLN and bool(lib.ctn_updc1_supported(B, H, self.norm))
+        pending = None    # deferred gLN-2 + residual of the previous (fused) block
         i = 0
         for r in range(cfg["R"]):
             for xb in range(cfg["X"]):
                 k = block_keys(r, xb, cfg["causal"])
                 pb = prep.blocks[i]
                 i += 1
-                info.append(("gemm_conv1x1", 2.0 * Rr * B * H, 4.0 * Rr * B + 4.0 * Rr * H))
-                if self.fused[xb]:
-                    info.append(("gemm_dwpw_fused", 2.0 * Rr * B * H + 2.0 * Rr * H * cfg["P"], 4.0 * Rr * H + 4.0 * Rr * B))
-                    info.append(("resid_update", 2.0 * Rr * B, 12.0 * Rr * B))
-                else:
-                    info.append(("dwconv", 2.0 * Rr * H * cfg["P"], 8.0 * Rr * H))
-                    info.append(("gemm_pointwise", 2.0 * Rr * B * H, 4.0 * Rr * H + 8.0 * Rr * B))
                 # self.a holds PReLU(conv1x1 output): the consumers skip the first PReLU (identity slope)
-                calls.append(self._gemm(Cin=B, Cout=H, a_hi=self.x_hl[0], a_lo=self.x_hl[1], w_hi=pb["w1"][0],
-                                        w_lo=pb["w1"][1], out_f32=self.a, out_stat=self.norm,
-                                        out_stat_buf=self.stat1, stat_prelu=params[k["a1"]], store_prelu=1))
+                if pending is not None and use_c1:
+                    c = nat.Updc1Args()
+                    c.M, c.K, c.B, c.H = M, K, B, H
+                    c.x_hi, c.x_lo, c.y = self.x_hl[0].data_ptr(), self.x_hl[1].data_ptr(), self.y.data_ptr()
+                    c.in_stat, c.in_P, c.in_count = self.stat2f.data_ptr(), pending["P"], float(K) * H
+                    c.col_g, c.col_bias = pending["g"].data_ptr(), pending["b"].data_ptr()
+                    c.w_hi, c.w_lo = pb["w1"][0].data_ptr(), pb["w1"][1].data_ptr()
+                    c.a, c.out_stat, c.slope = self.a.data_ptr(), self.stat1.data_ptr(), params[k["a1"]].data_ptr()
+                    self._keep.append(c)
+                    emit("gemm_update_conv1x1", 2.0 * Rr * B * H + 2.0 * Rr * B, 12.0 * Rr * B + 4.0 * Rr * H,
+                         lambda s, ref=C.byref(c): uc1(ref, s))
+                    pending = None
+                else:
+                    if pending is not None:
+                        emit_update(pending)
+                        pending = None
+                    emit("gemm_conv1x1", 2.0 * Rr * B * H, 4.0 * Rr * B + 4.0 * Rr * H,
+                         self._gemm(Cin=B, Cout=H, a_hi=self.x_hl[0], a_lo=self.x_hl[1], w_hi=pb["w1"][0],
+                                    w_lo=pb["w1"][1], out_f32=self.a, out_stat=self.norm,
+                                    out_stat_buf=self.stat1, stat_prelu=params[k["a1"]], store_prelu=1))
                 if self.fused[xb]:
                     f = nat.DwpwArgs()
                     f.M, f.K, f.H, f.B, f.dilation, f.causal = M, K, H, B, 2 ** xb, int(bool(cfg["causal"]))
@@ -187,11 +211,9 @@ class _Plan:
                     f.w_hi, f.w_lo = pb["w2"][0].data_ptr(), pb["w2"][1].data_ptr()
                     f.y, f.out_stat = self.y.data_ptr(), self.stat2f.data_ptr()
                     self._keep.append(f)
-                    fw, upd = lib.ctn_dwpw_fwd, lib.ctn_resid_update
-                    calls.append(lambda s, ref=C.byref(f): fw(ref, s))
-                    u = (self.x_hl[0].data_ptr(), self.x_hl[1].data_ptr(), self.y.data_ptr(), self.stat2f.data_ptr(),
-                         self.P2f[xb], float(K) * H, pb["w2"][2].data_ptr(), pb["w2"][3].data_ptr(), M, K, B)
-                    calls.append(lambda s, u=u: upd(*u, s))
+                    emit("gemm_dwpw_fused", 2.0 * Rr * B * H + 2.0 * Rr * H * cfg["P"], 4.0 * Rr * H + 4.0 * Rr * B,
+                         lambda s, ref=C.byref(f): fw(ref, s))
+                    pending = dict(P=self.P2f[xb], g=pb["w2"][2], b=pb["w2"][3])
                     continue
                 d = nat.DwconvArgs()
                 d.M, d.K, d.H, d.P, d.dilation, d.causal = M, K, H, cfg["P"], 2 ** xb, int(bool(cfg["causal"]))
@@ -203,12 +225,15 @@ class _Plan:
                 d.out_hi, d.out_lo = self.q_hl[0].data_ptr(), self.q_hl[1].data_ptr()
                 d.out_stat = self.stat2.data_ptr()
                 self._keep.append(d)
-                calls.append(lambda s, ref=C.byref(d): dw(ref, s))
-                calls.append(self._gemm(Cin=H, Cout=B, a_hi=self.q_hl[0], a_lo=self.q_hl[1], w_hi=pb["w2"][0],
-                                        w_lo=pb["w2"][1], col_g=pb["w2"][2], col_bias=pb["w2"][3],
-                                        in_norm=self.norm, in_stat=self.stat2, in_P=self.P2s[xb],
-                                        in_count=float(K) * H, resid_hi=self.x_hl[0], resid_lo=self.x_hl[1],
-                                        out_hi=self.x_hl[0], out_lo=self.x_hl[1]))
+                emit("dwconv", 2.0 * Rr * H * cfg["P"], 8.0 * Rr * H, lambda s, ref=C.byref(d): dw(ref, s))
+                emit("gemm_pointwise", 2.0 * Rr * B * H, 4.0 * Rr * H + 8.0 * Rr * B,
+                     self._gemm(Cin=H, Cout=B, a_hi=self.q_hl[0], a_lo=self.q_hl[1], w_hi=pb["w2"][0],
+                                w_lo=pb["w2"][1], col_g=pb["w2"][2], col_bias=pb["w2"][3],
+                                in_norm=self.norm, in_stat=self.stat2, in_P=self.P2s[xb],
+                                in_count=float(K) * H, resid_hi=self.x_hl[0], resid_lo=self.x_hl[1],
+                                out_hi=self.x_hl[0], out_lo=self.x_hl[1]))
+        if pending is not None:
+            emit_update(pending)
         calls.append(self._gemm(Cin=B, Cout=C_ * N, a_hi=self.x_hl[0], a_lo=self.x_hl[1], w_hi=prep.mask[0],
                                 w_lo=prep.mask[1], out_f32=self.score))
         info.append(("gemm_mask", 2.0 * Rr * B * C_ * N, 4.0 * Rr * B + 4.0 * Rr * C_ * N))
@@ -268,15 +293,20 @@ class SeparationEngine:
         # blocks with dilation <= this take the fused depthwise + pointwise kernel where the configuration
         # allows it (0 = never; the default covers every dilation)
         self.fuse_max_dilation = 1 << 30
+        # after a fused block, fold its deferred residual update into the next block's conv1x1
+        # (ctn_updc1_fwd).  Parity-green but not faster than ctn_resid_update + ctn_gemm1x1 yet
+        self.fuse_update = False
         self.launches = 0   # kernels of libctn_b200 launched by forward() so far
 
     def num_launches(self):
         """Kernel launches of one plan execution (encoder + bottleneck + 3 per block + mask + decoder;
-        the fused path also has 3 per block: conv1x1, depthwise+pointwise, residual update)."""
-        return 4 + 3 * self.cfg["R"] * self.cfg["X"]
+        the fused path also has 3 per block: conv1x1, depthwise+pointwise, residual update; with
+        fuse_update the update rides in the next block's conv1x1: 2 per block + 1)."""
+        n = self.cfg["R"] * self.cfg["X"]
+        return 4 + (2 * n + 1 if self.fuse_update and self.fuse_max_dilation >= 2 ** (self.cfg["X"] - 1) else 3 * n)
 
     def _plan(self, params, M, T, device):
-        key = (device.index, M, T, self.fuse_max_dilation)
+        key = (device.index, M, T, self.fuse_max_dilation, self.fuse_update)
         prep = self.prepared.get(device.index)
         if prep is None:
             prep = self.prepared[device.index] = _Prepared(self.cfg, device)
@@ -284,7 +314,7 @@ class SeparationEngine:
         prep.refresh(self.cfg, params)
         plan = self.plans.get(key)
         if plan is None:
-            plan = self.plans[key] = _Plan(self.cfg, M, T, device, self.fuse_max_dilation)
+            plan = self.plans[key] = _Plan(self.cfg, M, T, device, self.fuse_max_dilation, self.fuse_update)
         ptrs = tuple(p.data_ptr() for p in params.values())
         if plan.calls is None or plan.param_ptrs != ptrs:
             plan.build(params, prep)

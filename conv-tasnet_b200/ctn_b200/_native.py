@@ -54,6 +54,15 @@ class DwpwArgs(C.Structure):
     ]
 
 
+class Updc1Args(C.Structure):
+    """struct ctn_updc1_args"""
+    _fields_ = [
+        ("M", C.c_int), ("K", C.c_int), ("B", C.c_int), ("H", C.c_int),
+        ("x_hi", _vp), ("x_lo", _vp), ("y", _vp), ("in_stat", _vp), ("in_P", C.c_int), ("in_count", C.c_double),
+        ("col_g", _vp), ("col_bias", _vp), ("w_hi", _vp), ("w_lo", _vp), ("a", _vp), ("out_stat", _vp), ("slope", _vp),
+    ]
+
+
 class OptChunk(C.Structure):
     """struct ctn_opt_chunk"""
     _fields_ = [("param", _vp), ("grad", _vp), ("exp_avg", _vp), ("exp_avg_sq", _vp), ("n", C.c_int), ("pad_", C.c_int)]
@@ -129,6 +138,8 @@ _SIGNATURES = {
     "ctn_dwconv_fwd": (C.c_int, [C.POINTER(DwconvArgs), _vp]),
     "ctn_clip_adam": (C.c_int, [_vp, C.c_int, _vp, C.c_float, C.c_float, C.c_double, C.c_double, C.c_float, C.c_float,
                                 C.c_float, C.c_int, _vp, _vp]),
+    "ctn_updc1_supported": (C.c_int, [C.c_int, C.c_int, C.c_int]),
+    "ctn_updc1_fwd": (C.c_int, [C.POINTER(Updc1Args), _vp]),
     "ctn_dwpw_supported": (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_int, C.c_int]),
     "ctn_dwpw_partials": (C.c_int, [C.c_int, C.c_int]),
     "ctn_dwpw_fwd": (C.c_int, [C.POINTER(DwpwArgs), _vp]),

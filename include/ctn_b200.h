@@ -325,6 +325,27 @@ int ctn_encoder_wgrad_tiles(int K);
 int ctn_encoder_wgrad(const float* dpre, const float* mixture, int M, int T, int N, int L, float* dU_part,
                       void* stream);
 
+typedef struct ctn_updc1_args {
+    int M, K, B, H;          /* x, y are [M*K, B] (B == 256); a is [M*K, H] (H == 256 or 512)         */
+    void *x_hi, *x_lo;       /* in/out: residual stream as a bf16 (hi, lo) pair, updated in place     */
+    const float* y;          /* raw pointwise product of the PREVIOUS block (ctn_dwpw_fwd)            */
+    const void* in_stat;     /* float2 [M, in_P]: gLN-2 partials of the previous block                */
+    int in_P;
+    double in_count;         /* K * H of the previous block's depthwise output                        */
+    const float *col_g, *col_bias; /* [B] of the previous block's pointwise weight (ctn_weight_prep)  */
+    const void *w_hi, *w_lo; /* conv1x1 weight of THIS block, bf16 [H, B]                             */
+    float* a;                /* out: PReLU(W1 x), fp32 [M*K, H]                                       */
+    void* out_stat;          /* out: float2 [M, ctn_gemm_gln_partials(K, H)] gLN-1 partials of a      */
+    const float* slope;      /* slope of this block's first PReLU (device scalar)                     */
+} ctn_updc1_args;
+
+/* ctn_resid_update of block b-1 fused into the conv1x1 of block b (conv_tasnet.py:254-256, :237 then
+ * :217-218): producer warps form x += r y - r mu rowsum + W2 beta2, write it back and feed it straight to
+ * the tensor cores; the output is PReLU(conv1x1(x)) with the statistics for gLN-1, exactly what
+ * ctn_gemm1x1 (store_prelu) would have produced.  ctn_updc1_supported() != 0: gLN, B == 256, H == 256 or 512. */
+int ctn_updc1_supported(int B, int H, int norm);
+int ctn_updc1_fwd(const ctn_updc1_args* args, void* stream);
+
 /* ---- training-step tail: clip_grad_norm_ + Adam (solver.py:184-186, train.py:129-131) ---- */
 typedef struct ctn_opt_chunk {
     float* param;       /* n parameters                                   */

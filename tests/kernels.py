@@ -117,6 +117,23 @@ def resid_update(x_hi, x_lo, y, stat, count, col_g, col_bias, M, K):
                                          float(count), col_g.data_ptr(), col_bias.data_ptr(), M, K, B, nat.stream()))
 
 
+def updc1(M, K, x_hi, x_lo, y, stat, count, col_g, col_bias, w_hi, w_lo, slope):
+    """ctn_updc1_fwd: updates (x_hi, x_lo) in place; returns (a [M*K, H], gLN-1 partials)"""
+    B = y.shape[1]
+    H = w_hi.shape[0]
+    lib = nat.lib()
+    u = nat.Updc1Args()
+    u.M, u.K, u.B, u.H = M, K, B, H
+    u.x_hi, u.x_lo, u.y = x_hi.data_ptr(), x_lo.data_ptr(), y.data_ptr()
+    u.in_stat, u.in_P, u.in_count = stat.data_ptr(), stat.shape[1], float(count)
+    u.col_g, u.col_bias, u.w_hi, u.w_lo = col_g.data_ptr(), col_bias.data_ptr(), w_hi.data_ptr(), w_lo.data_ptr()
+    a = torch.full((M * K, H), float("nan"), device=y.device)
+    st = torch.full((M, lib.ctn_gemm_gln_partials(K, H), 2), float("nan"), device=y.device)
+    u.a, u.out_stat, u.slope = a.data_ptr(), st.data_ptr(), slope.data_ptr()
+    nat.check(lib.ctn_updc1_fwd(C.byref(u), nat.stream()))
+    return a, st
+
+
 def decoder(score, w, V, M, K, C_, T, mask):
     L, N = V.shape
     est = torch.full((M, C_, T), float("nan"), device=score.device)

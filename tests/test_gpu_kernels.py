@@ -246,6 +246,46 @@ def test_fused_depthwise_pointwise(H, K, M, dil, causal, preact):
     assert rel_l2(got, out_ref) < 2e-5
 
 
+@pytest.mark.parametrize("K,M,H", [(40, 3, 256), (700, 2, 512), (3199, 5, 512), (128, 1, 512), (129, 4, 256),
+                                   (1000, 3, 768), (3199, 40, 1024), (3199, 64, 512)])
+def test_fused_update_conv1x1(K, M, H):
+    """ctn_updc1_fwd == ctn_resid_update followed by ctn_gemm1x1 (store_prelu, gLN statistics)."""
+    B = 256
+    x = _rand(M * K, B, seed=60)
+    y = _rand(M * K, B, seed=61, scale=0.7)
+    g2, b2 = 1.0 + 0.3 * _rand(512, seed=62), _rand(512, seed=63)
+    W2 = _rand(B, 512, seed=64, scale=0.05)
+    _, _, col_g, col_bias = Kn.weight_prep(W2, g2, b2)
+    P = 7
+    stat = torch.rand(M, P, 2, device=DEV) * 100 + 50
+    count = float(K) * 512
+    stat[:, :, 1] = stat[:, :, 0] ** 2 / (count / P) * 3.0 + 10.0
+    W1 = _rand(H, B, seed=65, scale=0.06)
+    w_hi, w_lo, _, _ = Kn.weight_prep(W1)
+    slope = torch.tensor([0.25], device=DEV)
+    x_hi, x_lo = Kn.split_hl(x)
+    # reference path: the two unfused kernels
+    r_hi, r_lo = x_hi.clone(), x_lo.clone()
+    Kn.resid_update(r_hi, r_lo, y, stat, count, col_g, col_bias, M, K)
+    ref = Kn.gemm(M, K, r_hi, r_lo, w_hi, w_lo, out_stat=nat.NORM_GLN, stat_prelu=slope, store_prelu=True)
+    a, st = Kn.updc1(M, K, x_hi, x_lo, y, stat, count, col_g, col_bias, w_hi, w_lo, slope)
+    assert torch.equal(x_hi, r_hi) and torch.equal(x_lo, r_lo)       # same arithmetic, same rounding
+    assert not torch.isnan(a).any() and not torch.isnan(st).any()
+    assert rel_l2(a, ref["out"]) < 1e-6
+    assert rel_l2(st.double().sum(1), ref["stat"].double().sum(1)) < 1e-6
+    # and against fp64
+    s = stat.double().sum(1)
+    mean = s[:, 0] / count
+    r = 1.0 / torch.sqrt((s[:, 1] / count - mean * mean).clamp_min(0) + 1e-8)
+    mm = torch.arange(M, device=DEV).repeat_interleave(K)
+    xn = (x_hi.double() + x_lo.double())
+    x_ref = (Kn.split_hl(x)[0].double() + Kn.split_hl(x)[1].double()) + r[mm, None] * y.double() \
+        - (r * mean)[mm, None] * col_g.double()[None] + col_bias.double()[None]
+    assert rel_l2(xn, x_ref) < 2e-5
+    a_ref = F.prelu(xn @ (w_hi.double() + w_lo.double()).t(), slope.double())
+    assert rel_l2(a, a_ref) < 2e-5
+
+
 def test_dwconv_rejects_length_changing_config():
     """P=2 non-causal changes the length; the reference crashes at the residual add"""
     H, K, M = 4, 10, 1

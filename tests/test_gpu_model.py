@@ -159,6 +159,9 @@ def test_fused_depthwise_pointwise_path_matches_unfused(fuse):
         base = model(mix)
         assert not any(eng._plan(model._params(), 3, T, mix.device).fused)
         eng.fuse_max_dilation = fuse
+        eng.fuse_update = False
+        fused_nou = model(mix)
+        eng.fuse_update = True
         fused = model(mix)
         assert sum(eng._plan(model._params(), 3, T, mix.device).fused) == {4: 3, 1 << 30: 8}[fuse]
         eng.use_graph = True
@@ -167,6 +170,9 @@ def test_fused_depthwise_pointwise_path_matches_unfused(fuse):
         eng.fuse_max_dilation = default
         ref = O.forward(mix[:1].double(), {k: v.to(DEV).double() for k, v in p32.items()}, cfg)
     assert rel_l2(fused, base) < 2e-5
+    assert rel_l2(fused_nou, base) < 2e-5
+    print("fused vs not-updated-fused", rel_l2(fused, fused_nou))
+    assert rel_l2(fused, fused_nou) < 2e-6          # same arithmetic, different summation order in the statistics
     assert torch.equal(fused, fused_g)
     assert rel_l2(fused[:1], ref) < WAVE_TOL / 10
 
