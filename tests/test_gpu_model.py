@@ -172,7 +172,7 @@ def test_fused_depthwise_pointwise_path_matches_unfused(fuse):
     assert rel_l2(fused, base) < 2e-5
     assert rel_l2(fused_nou, base) < 2e-5
     print("fused vs not-updated-fused", rel_l2(fused, fused_nou))
-    assert rel_l2(fused, fused_nou) < 2e-6          # same arithmetic, different summation order in the statistics
+    assert rel_l2(fused, fused_nou) < 2e-5          # the folded update re-splits x on the fly: same tolerance as against the unfused path
     assert torch.equal(fused, fused_g)
     assert rel_l2(fused[:1], ref) < WAVE_TOL / 10
 
