@@ -110,6 +110,12 @@ class ConvTasNet(nn.Module):
             self.__dict__["_train_engine"] = eng
         return eng
 
+    def streaming(self, chunk_frames=256, use_graph=True):
+        """Chunked separation of one audio stream with bounded latency (causal cLN models only; an
+        addition to the reference's surface): see ctn_b200/_stream.py."""
+        from ctn_b200 import _stream
+        return _stream.StreamingSeparator(self, chunk_frames, use_graph)
+
     def forward(self, mixture):
         """
         Args:

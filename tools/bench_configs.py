@@ -105,6 +105,34 @@ def train(name, cfg, M, T, steps=10, warm=4):
             "timed": "host inputs -> device, fwd + PIT SI-SNR loss + bwd + clip(5) + Adam, loss -> host"}
 
 
+def stream_latency(name, cfg, chunk, seconds=60, warm_chunks=8):
+    """Chunked causal separation (model.streaming): per-chunk latency = host chunk -> device, one
+    steady-state chunk (CUDA graph), separated chunk -> host."""
+    model = build(cfg)
+    hop = cfg["L"] // 2
+    n = chunk * hop
+    sep = model.streaming(chunk_frames=chunk)
+    g = torch.Generator().manual_seed(2025)
+    total = seconds * SR // n
+    h_in = (0.1 * torch.randn(total + warm_chunks + 2, n, generator=g)).pin_memory()
+    h_out = torch.empty(cfg["C"], n).pin_memory()
+    state = {"i": 0}
+    sep.feed(h_in[0, :hop].cuda())      # the one extra hop the first chunk needs
+
+    def step():
+        out = sep.feed(h_in[state["i"]].cuda(non_blocking=True))
+        h_out.copy_(out, non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+        state["i"] += 1
+
+    ms = timed(step, total, warm_chunks)
+    audio = n / SR
+    return {"config": name, "chunk_frames": chunk, "chunk_audio_ms": audio * 1e3, "ms_per_chunk": ms,
+            "algorithmic_latency_ms": (n + hop) / SR * 1e3, "x_realtime_one_stream": audio / (ms / 1e3),
+            "launches_per_chunk": len(sep.body_steady) + 1, "chunks_timed": total,
+            "timed": "host chunk -> device, steady-state chunk (CUDA graph), separated chunk -> host"}
+
+
 PAPER = dict(N=256, L=20, B=256, H=512, P=3, X=8, R=4, C=2, norm_type="gLN", causal=False, mask_nonlinear="relu")
 CAUSAL = dict(PAPER, norm_type="cLN", causal=True)
 BEST = dict(N=512, L=16, B=128, H=512, P=3, X=8, R=3, C=3, norm_type="gLN", causal=False, mask_nonlinear="softmax")
@@ -117,6 +145,9 @@ def main():
         print(json.dumps(latency("cfg1 (no CUDA graph)", PAPER, 32000, graph=False)), flush=True)
     if "cfg3" in which:
         print(json.dumps(latency("cfg3: causal cLN, 1 x 60 s stream", CAUSAL, 480000, steps=10, warm=3)), flush=True)
+        for chunk in (16, 64, 256, 1024):
+            print(json.dumps(stream_latency("cfg3 streaming: causal cLN, chunks of %d frames" % chunk, CAUSAL, chunk,
+                                            seconds=20)), flush=True)
     if "cfg5" in which:
         print(json.dumps(train("cfg5: N512 L16 B128 H512 X8 R3 C3 softmax, train batch 8 x 4 s", BEST, 8, 32000)),
               flush=True)
