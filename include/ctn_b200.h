@@ -365,6 +365,17 @@ int ctn_clip_adam(const ctn_opt_chunk* chunks_dev, int n_chunks, double* partial
                   double beta1, double beta2, float inv_sqrt_bias2, float eps, float weight_decay, int write_grad,
                   float* norm_out, void* stream);
 
+/* SI-SNR improvement of a batch on the device (evaluate.py:108-144, called per utterance on host
+ * numpy arrays at evaluate.py:66-80 after remove_pad): for utterance b with n = lengths[b] valid
+ * samples (lengths NULL -> T) and source c,
+ *   sisnr[b, c, 0] = SI-SNR(ref[b,c,:n], est[b,c,:n]),  sisnr[b, c, 1] = SI-SNR(ref[b,c,:n], mix[b,:n]),
+ *   sisnri[b] = mean_c (sisnr[b,c,0] - sisnr[b,c,1])   (the reference hard-codes c = 0, 1)
+ * with both signals made zero-mean over the n samples and eps = 1e-8 placed as in cal_SISNR (:128-144).
+ * ref, est fp32 [B, C, T] (est already reordered by the best PIT permutation), mix fp32 [B, T],
+ * lengths int64 [B]; outputs fp32, sisnri may be NULL.  fp64 accumulation, deterministic. */
+int ctn_sisnri(const float* ref, const float* est, const float* mix, const long long* lengths, int B, int C, int T,
+               float* sisnr, float* sisnri, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

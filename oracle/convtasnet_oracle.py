@@ -261,6 +261,27 @@ def cal_loss(source, estimate, lengths):
 # ----------------------------------------------------------------------------
 # shape arithmetic (bit-exact integer outputs; SURVEY.md §8 notation)
 # ----------------------------------------------------------------------------
+def cal_SISNR(ref_sig, out_sig, eps=1e-8):
+    """SI-SNR of out_sig against ref_sig in dB (evaluate.py:128-144); 1-D numpy arrays of equal
+    length, arithmetic in the arrays' dtype like the reference."""
+    import numpy as np
+    assert len(ref_sig) == len(out_sig)
+    ref_zm = ref_sig - np.mean(ref_sig)                     # :134
+    out_zm = out_sig - np.mean(out_sig)                     # :135
+    energy = np.sum(ref_zm ** 2) + eps                      # :136
+    proj = np.sum(ref_zm * out_zm) * ref_zm / energy        # :137
+    noise = out_zm - proj                                   # :138
+    ratio = np.sum(proj ** 2) / (np.sum(noise ** 2) + eps)  # :139
+    return 10 * np.log(ratio + eps) / np.log(10.0)          # :140
+
+
+def cal_SISNRi(src_ref, src_est, mix):
+    """Average SI-SNR improvement over the sources (evaluate.py:108-125; the reference hard-codes
+    sources 0 and 1, this averages over all rows, identical for C = 2)."""
+    C = src_ref.shape[0]
+    return sum(cal_SISNR(src_ref[c], src_est[c]) - cal_SISNR(src_ref[c], mix) for c in range(C)) / C
+
+
 def frame_geometry(T, L):
     hop = L // 2
     K = (T - L) // hop + 1

@@ -140,5 +140,44 @@ def main():
     np.savez_compressed(os.path.join(OUT, "ola_cases.npz"), **{k: v.numpy() for k, v in ola.items()})
 
 
+    make_sisnri_cases()
+
+
+def _reference_functions(path, names):
+    """Compiles the named top-level functions of a reference file WITHOUT importing the module
+    (evaluate.py imports librosa / mir_eval, which are not installed): the definitions are taken
+    from the file's AST at generation time; nothing is copied into this repository."""
+    import ast
+    with open(path) as f:
+        tree = ast.parse(f.read())
+    body = [n for n in tree.body if isinstance(n, ast.FunctionDef) and n.name in names]
+    assert sorted(n.name for n in body) == sorted(names)
+    ns = {"np": np}
+    exec(compile(ast.Module(body=body, type_ignores=[]), path, "exec"), ns)
+    return [ns[n] for n in names]
+
+
+def make_sisnri_cases():
+    """SI-SNRi fixtures from the reference's own evaluate.cal_SISNRi / cal_SISNR (evaluate.py:108-144)."""
+    cal_SISNRi, cal_SISNR = _reference_functions(os.path.join(REF, "evaluate.py"), ["cal_SISNRi", "cal_SISNR"])
+    rng = np.random.RandomState(11)
+    out = {}
+    # (T, noise level of the estimate): low, medium and very high SNR, short and long, a DC offset
+    for i, (T, noise, dc) in enumerate([(12, 0.5, 0.0), (4000, 0.1, 0.0), (32000, 1e-3, 0.3), (16001, 1.0, -0.2),
+                                        (8000, 1e-5, 0.0)]):
+        ref = (0.1 * rng.randn(2, T) + dc).astype(np.float32)
+        est = (ref * rng.uniform(0.5, 2.0) + noise * 0.1 * rng.randn(2, T)).astype(np.float32)
+        mix = (ref.sum(0) + 0.01 * rng.randn(T)).astype(np.float32)
+        out["ref%d" % i], out["est%d" % i], out["mix%d" % i] = ref, est, mix
+        out["sisnri%d" % i] = np.float64(cal_SISNRi(ref, est, mix))
+        out["sisnr%d" % i] = np.array([[cal_SISNR(ref[c], est[c]), cal_SISNR(ref[c], mix)] for c in range(2)],
+                                      dtype=np.float64)
+        print("sisnri case", i, out["sisnri%d" % i], out["sisnr%d" % i].tolist())
+    np.savez_compressed(os.path.join(OUT, "sisnri_cases.npz"), **out)
+
+
 if __name__ == "__main__":
-    main()
+    if sys.argv[1:] == ["sisnri"]:
+        make_sisnri_cases()
+    else:
+        main()

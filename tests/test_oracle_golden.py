@@ -58,3 +58,15 @@ def test_frame_geometry():
     assert O.frame_geometry(32000, 16) == (8, 3999, 32000)
     cfg = dict(N=256, L=20, B=256, H=512, P=3, X=8, R=4, C=2)
     assert abs(O.forward_flops(cfg, 32000) / 1e9 - 55.341) < 1e-3
+
+
+def test_sisnri_cases():
+    """oracle cal_SISNR / cal_SISNRi against values recorded from the reference's evaluate.py:108-144."""
+    z = load_golden("sisnri_cases")
+    for i in range(5):
+        ref, est, mix = (z[k + str(i)].numpy() for k in ("ref", "est", "mix"))
+        tol = 1e-4 if i < 4 else 1e-2      # case 4 sits at 102 dB: float32 rounding of the reference itself
+        assert abs(O.cal_SISNRi(ref, est, mix) - float(z["sisnri%d" % i])) < tol
+        for c in range(2):
+            assert abs(O.cal_SISNR(ref[c], est[c]) - float(z["sisnr%d" % i][c, 0])) < tol
+            assert abs(O.cal_SISNR(ref[c], mix) - float(z["sisnr%d" % i][c, 1])) < tol
