@@ -12,7 +12,7 @@ import torch
 import torch.nn as nn
 
 from ctn_b200 import _engine, _native
-from ctn_b200._layout import param_spec
+from ctn_b200._layout import is_bn, param_spec
 
 EPS = 1e-8
 
@@ -34,7 +34,10 @@ def _attach(root, dotted, param):
             child = _Node()
             node.add_module(name, child)
         node = child
-    node.register_parameter(parts[-1], param)
+    if isinstance(param, nn.Parameter):
+        node.register_parameter(parts[-1], param)
+    else:
+        node.register_buffer(parts[-1], param)
 
 
 class ConvTasNet(nn.Module):
@@ -50,7 +53,7 @@ class ConvTasNet(nn.Module):
             X: Number of convolutional blocks in each repeat
             R: Number of repeats
             C: Number of speakers
-            norm_type: gLN or cLN (BN is not implemented)
+            norm_type: BN, gLN, cLN (BN: inference with running statistics only)
             causal: causal or non-causal
             mask_nonlinear: 'relu' or 'softmax'
         """
@@ -60,13 +63,17 @@ class ConvTasNet(nn.Module):
         self.causal = causal
         self.mask_nonlinear = mask_nonlinear
         _engine._check_cfg(self._cfg())
-        spec = param_spec(N, L, B, H, P, X, R, C, causal)
+        spec = param_spec(N, L, B, H, P, X, R, C, causal, norm_type)
         # Same RNG consumption as the reference's construction, so that the same seed gives
         # the same initial weights: first the layers' default initialisers in creation
         # order, then xavier_normal_ on every parameter with more than one dim (:41-43) --
         # which includes the [1, C, 1] gamma / beta of every norm.
         created = []
         for key, (shape, kind) in spec.items():
+            if kind.startswith("buf_"):   # BatchNorm1d buffers: running_mean 0, running_var 1, count 0
+                _attach(self, key, torch.zeros(shape, dtype=torch.long) if kind == "buf_count" else
+                        torch.full(shape, 1.0 if kind == "buf_ones" else 0.0))
+                continue
             t = torch.empty(shape)
             if kind == "conv":
                 nn.init.kaiming_uniform_(t, a=math.sqrt(5))
@@ -82,7 +89,8 @@ class ConvTasNet(nn.Module):
         for p in created:
             if p.dim() > 1:
                 nn.init.xavier_normal_(p)
-        self._keys = list(spec)
+        self._keys = [k for k, (_, kind) in spec.items() if not kind.startswith("buf_")]
+        self._buffer_keys = [k for k, (_, kind) in spec.items() if kind in ("buf_zeros", "buf_ones")]
         self._engine = None
 
     def _cfg(self):
@@ -91,7 +99,11 @@ class ConvTasNet(nn.Module):
 
     def _params(self):
         sd = dict(self.named_parameters())
-        return {k: sd[k] for k in self._keys}
+        out = {k: sd[k] for k in self._keys}
+        if self._buffer_keys:   # BatchNorm running statistics ride along (the engine folds them)
+            bd = dict(self.named_buffers())
+            out.update((k, bd[k]) for k in self._buffer_keys)
+        return out
 
     def engine(self):
         """The per-module kernel orchestrator (workspaces, prepared weights, CUDA graphs)."""
@@ -130,6 +142,11 @@ class ConvTasNet(nn.Module):
                 raise RuntimeError("parameter %s is %s on %s; float32 on %s is required (call model.cuda())"
                                    % (k, p.dtype, p.device, mixture.device))
         needs_grad = torch.is_grad_enabled() and (mixture.requires_grad or any(p.requires_grad for p in params.values()))
+        if is_bn(self.norm_type) and (self.training or needs_grad):
+            # nn.BatchNorm1d in training mode normalises with statistics over the whole batch and updates
+            # its running buffers (conv_tasnet.py:300-303); only the inference form is implemented
+            raise NotImplementedError("norm_type=%r (BatchNorm1d) is implemented for inference only: call "
+                                      "model.eval() and run under torch.no_grad()" % (self.norm_type,))
         if needs_grad:
             from ctn_b200 import _autograd
             return _autograd.separate(self, mixture, params)

@@ -89,3 +89,31 @@ extern "C" int ctn_weight_prep(const float* W, int rows, int cols, const float* 
     CTN_LAUNCH_CHECK("weight_prep_kernel");
     return CTN_OK;
 }
+
+// nn.BatchNorm1d in inference mode (conv_tasnet.py:300-303 -> torch's batch_norm with running
+// statistics): y = (x - running_mean) / sqrt(running_var + eps) * weight + bias, a per-channel affine
+//   scale[c] = weight[c] / sqrt(running_var[c] + eps),  shift[c] = bias[c] - running_mean[c] * scale[c].
+// The engine passes (scale, shift) wherever the gLN kernels take (gamma, beta) together with unit
+// statistics (mean 0, rstd 1), so BN blocks run through the same fused kernels.
+namespace ctn {
+__global__ void bn_fold_kernel(const float* __restrict__ weight, const float* __restrict__ bias,
+                               const float* __restrict__ mean, const float* __restrict__ var, float eps, int C,
+                               float* __restrict__ scale, float* __restrict__ shift) {
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= C) return;
+    const float s = (weight ? weight[c] : 1.f) / sqrtf(var[c] + eps);
+    scale[c] = s;
+    shift[c] = (bias ? bias[c] : 0.f) - mean[c] * s;
+}
+}  // namespace ctn
+
+extern "C" int ctn_bn_fold(const float* weight, const float* bias, const float* running_mean, const float* running_var,
+                           float eps, int C, float* scale, float* shift, void* stream) {
+    using namespace ctn;
+    CTN_REQUIRE(running_mean && running_var && scale && shift, "ctn_bn_fold: NULL pointer");
+    CTN_REQUIRE(C > 0 && eps >= 0.f, "ctn_bn_fold: bad arguments");
+    bn_fold_kernel<<<ceil_div(C, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(weight, bias, running_mean,
+                                                                                    running_var, eps, C, scale, shift);
+    CTN_LAUNCH_CHECK("bn_fold_kernel");
+    return CTN_OK;
+}

@@ -53,7 +53,7 @@ class TrainPlan:
     """Workspaces and call lists of one (M, T) training step on one device."""
 
     def __init__(self, cfg, M, T, device):
-        _check_cfg(cfg)
+        _check_cfg(cfg, training=True)
         self.norm = _NORM[cfg["norm_type"]]
         self.cfg, self.M, self.T, self.device = cfg, M, T, device
         N, L, B, H, C_ = cfg["N"], cfg["L"], cfg["B"], cfg["H"], cfg["C"]

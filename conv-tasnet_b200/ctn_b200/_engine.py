@@ -22,17 +22,22 @@ import ctypes as C
 import torch
 
 from . import _native as nat
-from ._layout import block_keys, frame_geometry
+from ._layout import block_keys, frame_geometry, is_bn
 
 _NORM = {"gLN": nat.NORM_GLN, "cLN": nat.NORM_CLN}
 _MASK = {"relu": nat.MASK_RELU, "softmax": nat.MASK_SOFTMAX}
 
 
-def _check_cfg(cfg):
-    if cfg["norm_type"] not in _NORM:
-        # conv_tasnet.py:300-303 falls through to BatchNorm1d; batch statistics couple the
-        # utterances of a batch, which the utterance-sharded design excludes
-        raise NotImplementedError("norm_type=%r: only gLN and cLN are implemented" % (cfg["norm_type"],))
+BN_EPS = 1e-5   # nn.BatchNorm1d default (conv_tasnet.py:303 passes no eps)
+
+
+def _check_cfg(cfg, training=False):
+    if training and is_bn(cfg["norm_type"]):
+        # conv_tasnet.py:300-303 falls through to BatchNorm1d; its training-mode batch statistics couple
+        # the utterances of a batch, which the utterance-sharded design excludes.
+        # Inference with the running statistics is a per-channel affine and IS implemented (_Plan).
+        raise NotImplementedError("norm_type=%r (BatchNorm1d): training is not implemented, only inference"
+                                  % (cfg["norm_type"],))
     if cfg["mask_nonlinear"] not in _MASK:
         raise ValueError("Unsupported mask non-linear function")  # conv_tasnet.py:208
 
@@ -51,6 +56,10 @@ class _Prepared:
                 w1=(torch.empty(H, B, **bf), torch.empty(H, B, **bf)),
                 w2=(torch.empty(B, H, **bf), torch.empty(B, H, **bf), torch.empty(B, **f32), torch.empty(B, **f32))))
         self.mask = (torch.empty(C * N, B, **bf), torch.empty(C * N, B, **bf))
+        if is_bn(cfg["norm_type"]):     # per block: (scale, shift) of both BatchNorm1d layers, folded from the
+            for blk in self.blocks:     # running statistics by ctn_bn_fold
+                blk["bn1"] = (torch.empty(H, **f32), torch.empty(H, **f32))
+                blk["bn2"] = (torch.empty(H, **f32), torch.empty(H, **f32))
         self.fingerprint = None
         self.table = self.table_ptrs = None
 
@@ -59,6 +68,17 @@ class _Prepared:
         if fp == self.fingerprint:
             return
         ptrs = tuple(p.data_ptr() for p in params.values())
+        bn = is_bn(cfg["norm_type"])
+        if bn:
+            lib, st, i = nat.lib(), nat.stream(), 0
+            for r in range(cfg["R"]):
+                for x in range(cfg["X"]):
+                    k = block_keys(r, x, cfg["causal"], cfg["norm_type"])
+                    for tag, out in (("1", self.blocks[i]["bn1"]), ("2", self.blocks[i]["bn2"])):
+                        nat.check(lib.ctn_bn_fold(params[k["g" + tag]].data_ptr(), params[k["b" + tag]].data_ptr(),
+                                                  params[k["rm" + tag]].data_ptr(), params[k["rv" + tag]].data_ptr(),
+                                                  BN_EPS, cfg["H"], out[0].data_ptr(), out[1].data_ptr(), st))
+                    i += 1
         if self.table is None or self.table_ptrs != ptrs:
             N, B, H, C = cfg["N"], cfg["B"], cfg["H"], cfg["C"]
             t = nat.PrepTable(self.bott[0].device)
@@ -67,9 +87,10 @@ class _Prepared:
             i = 0
             for r in range(cfg["R"]):
                 for x in range(cfg["X"]):
-                    k = block_keys(r, x, cfg["causal"])
+                    k = block_keys(r, x, cfg["causal"], cfg["norm_type"])
+                    g2, b2 = self.blocks[i]["bn2"] if bn else (params[k["g2"]], params[k["b2"]])
                     t.add(params[k["w1"]], H, B, None, None, 0, self.blocks[i]["w1"])
-                    t.add(params[k["w2"]], B, H, params[k["g2"]], params[k["b2"]], 0, self.blocks[i]["w2"])
+                    t.add(params[k["w2"]], B, H, g2, b2, 0, self.blocks[i]["w2"])
                     i += 1
             t.add(params["separator.network.3.weight"], C * N, B, None, None, 0, self.mask)
             self.table, self.table_ptrs = t, ptrs
@@ -101,7 +122,13 @@ class _Plan:
         self.q_hl = (torch.empty(R_, H, **bf), torch.empty(R_, H, **bf))
         self.score = torch.empty(R_, C * N, **f32)
         self.one = torch.ones(1, **f32)
-        self.norm = _NORM[cfg["norm_type"]]
+        # BatchNorm1d blocks (inference) run through the gLN kernels: per-channel (scale, shift) in place of
+        # (gamma, beta) and unit statistics (mean 0, rstd 1) in place of the utterance statistics
+        self.bn = is_bn(cfg["norm_type"])
+        self.norm = nat.NORM_GLN if self.bn else _NORM[cfg["norm_type"]]
+        if self.bn:
+            self.unit = torch.zeros(M, 1, 2, **f32)
+            self.unit[:, 0, 1] = float(K * H)       # (sum, sumsq) = (0, count): mean 0, var 1
         if self.norm == nat.NORM_GLN:
             self.P1 = lib.ctn_gemm_gln_partials(K, H)
             self.P2s = [lib.ctn_dwconv_gln_partials(K, H, cfg["P"], 2 ** x) for x in range(cfg["X"])]
@@ -168,7 +195,7 @@ class _Plan:
             calls.append(call)
 
         def emit_update(pend):
-            u = (self.x_hl[0].data_ptr(), self.x_hl[1].data_ptr(), self.y.data_ptr(), self.stat2f.data_ptr(),
+            u = (self.x_hl[0].data_ptr(), self.x_hl[1].data_ptr(), self.y.data_ptr(), pend["stat"].data_ptr(),
                  pend["P"], float(K) * H, pend["g"].data_ptr(), pend["b"].data_ptr(), M, K, B)
             emit("resid_update", 2.0 * Rr * B, 12.0 * Rr * B, lambda s, u=u: upd(*u, s))
 
@@ -177,15 +204,17 @@ class _Plan:
         i = 0
         for r in range(cfg["R"]):
             for xb in range(cfg["X"]):
-                k = block_keys(r, xb, cfg["causal"])
+                k = block_keys(r, xb, cfg["causal"], cfg["norm_type"])
                 pb = prep.blocks[i]
                 i += 1
+                g1, b1 = pb["bn1"] if self.bn else (params[k["g1"]], params[k["b1"]])
+                st1, st1_P = (self.unit, 1) if self.bn else (self.stat1, self.P1)
                 # self.a holds PReLU(conv1x1 output): the consumers skip the first PReLU (identity slope)
                 if pending is not None and use_c1:
                     c = nat.Updc1Args()
                     c.M, c.K, c.B, c.H = M, K, B, H
                     c.x_hi, c.x_lo, c.y = self.x_hl[0].data_ptr(), self.x_hl[1].data_ptr(), self.y.data_ptr()
-                    c.in_stat, c.in_P, c.in_count = self.stat2f.data_ptr(), pending["P"], float(K) * H
+                    c.in_stat, c.in_P, c.in_count = pending["stat"].data_ptr(), pending["P"], float(K) * H
                     c.col_g, c.col_bias = pending["g"].data_ptr(), pending["b"].data_ptr()
                     c.w_hi, c.w_lo = pb["w1"][0].data_ptr(), pb["w1"][1].data_ptr()
                     c.a, c.out_stat, c.slope = self.a.data_ptr(), self.stat1.data_ptr(), params[k["a1"]].data_ptr()
@@ -205,21 +234,22 @@ class _Plan:
                     f = nat.DwpwArgs()
                     f.M, f.K, f.H, f.B, f.dilation, f.causal = M, K, H, B, 2 ** xb, int(bool(cfg["causal"]))
                     f.a, f.prelu_in = self.a.data_ptr(), None
-                    f.gamma_in, f.beta_in = params[k["g1"]].data_ptr(), params[k["b1"]].data_ptr()
-                    f.in_stat, f.in_P = self.stat1.data_ptr(), self.P1
+                    f.gamma_in, f.beta_in = g1.data_ptr(), b1.data_ptr()
+                    f.in_stat, f.in_P = st1.data_ptr(), st1_P
                     f.wd, f.prelu_out = params[k["wd"]].data_ptr(), params[k["a2"]].data_ptr()
                     f.w_hi, f.w_lo = pb["w2"][0].data_ptr(), pb["w2"][1].data_ptr()
                     f.y, f.out_stat = self.y.data_ptr(), self.stat2f.data_ptr()
                     self._keep.append(f)
                     emit("gemm_dwpw_fused", 2.0 * Rr * B * H + 2.0 * Rr * H * cfg["P"], 4.0 * Rr * H + 4.0 * Rr * B,
                          lambda s, ref=C.byref(f): fw(ref, s))
-                    pending = dict(P=self.P2f[xb], g=pb["w2"][2], b=pb["w2"][3])
+                    pending = dict(P=1 if self.bn else self.P2f[xb], stat=self.unit if self.bn else self.stat2f,
+                                   g=pb["w2"][2], b=pb["w2"][3])
                     continue
                 d = nat.DwconvArgs()
                 d.M, d.K, d.H, d.P, d.dilation, d.causal = M, K, H, cfg["P"], 2 ** xb, int(bool(cfg["causal"]))
                 d.inp, d.prelu_in = self.a.data_ptr(), self.one.data_ptr()
-                d.gamma_in, d.beta_in = params[k["g1"]].data_ptr(), params[k["b1"]].data_ptr()
-                d.norm, d.in_stat, d.in_P = self.norm, self.stat1.data_ptr(), self.P1
+                d.gamma_in, d.beta_in = g1.data_ptr(), b1.data_ptr()
+                d.norm, d.in_stat, d.in_P = self.norm, st1.data_ptr(), st1_P
                 d.wd, d.prelu_out = params[k["wd"]].data_ptr(), params[k["a2"]].data_ptr()
                 d.out_pre = None
                 d.out_hi, d.out_lo = self.q_hl[0].data_ptr(), self.q_hl[1].data_ptr()
@@ -229,7 +259,8 @@ class _Plan:
                 emit("gemm_pointwise", 2.0 * Rr * B * H, 4.0 * Rr * H + 8.0 * Rr * B,
                      self._gemm(Cin=H, Cout=B, a_hi=self.q_hl[0], a_lo=self.q_hl[1], w_hi=pb["w2"][0],
                                 w_lo=pb["w2"][1], col_g=pb["w2"][2], col_bias=pb["w2"][3],
-                                in_norm=self.norm, in_stat=self.stat2, in_P=self.P2s[xb],
+                                in_norm=self.norm, in_stat=self.unit if self.bn else self.stat2,
+                                in_P=1 if self.bn else self.P2s[xb],
                                 in_count=float(K) * H, resid_hi=self.x_hl[0], resid_lo=self.x_hl[1],
                                 out_hi=self.x_hl[0], out_lo=self.x_hl[1]))
         if pending is not None:

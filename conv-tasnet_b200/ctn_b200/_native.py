@@ -166,6 +166,7 @@ _SIGNATURES = {
     "ctn_pit_sisnr_fwd": (C.c_int, [_vp, _vp, _vp, C.c_int, C.c_int, C.c_int, _vp, C.c_int, _vp, _vp, _vp, _vp,
                                     _vp, _vp, _vp]),
     "ctn_pit_reorder": (C.c_int, [_vp, _vp, _vp, C.c_int, C.c_int, C.c_int, _vp, _vp]),
+    "ctn_bn_fold": (C.c_int, [_vp, _vp, _vp, _vp, C.c_float, C.c_int, _vp, _vp, _vp]),
     "ctn_sisnri": (C.c_int, [_vp, _vp, _vp, _vp, C.c_int, C.c_int, C.c_int, _vp, _vp, _vp]),
     "ctn_pit_sisnr_bwd": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, C.c_int, C.c_int, C.c_int, _vp, _vp]),
 }

@@ -365,6 +365,14 @@ int ctn_clip_adam(const ctn_opt_chunk* chunks_dev, int n_chunks, double* partial
                   double beta1, double beta2, float inv_sqrt_bias2, float eps, float weight_decay, int write_grad,
                   float* norm_out, void* stream);
 
+/* nn.BatchNorm1d in inference mode (conv_tasnet.py:300-303, reached for any norm_type other than
+ * "gLN" / "cLN"): folds (weight, bias, running_mean, running_var, eps) [C] into the per-channel affine
+ *   scale = weight / sqrt(running_var + eps),  shift = bias - running_mean * scale
+ * (weight / bias NULL -> 1 / 0).  The engine hands (scale, shift) to the kernels in place of a gLN's
+ * (gamma, beta), with unit statistics. */
+int ctn_bn_fold(const float* weight, const float* bias, const float* running_mean, const float* running_var, float eps,
+                int C, float* scale, float* shift, void* stream);
+
 /* SI-SNR improvement of a batch on the device (evaluate.py:108-144, called per utterance on host
  * numpy arrays at evaluate.py:66-80 after remove_pad): for utterance b with n = lengths[b] valid
  * samples (lengths NULL -> T) and source c,

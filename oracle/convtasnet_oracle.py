@@ -33,12 +33,29 @@ EPS = 1e-8  # conv_tasnet.py:10, pit_criterion.py:9
 # ----------------------------------------------------------------------------
 # state_dict key helpers (conv_tasnet.py:167-185, 217-263)
 # ----------------------------------------------------------------------------
-def block_keys(r, x, causal):
+def is_bn(norm_type):
+    """chose_norm (conv_tasnet.py:292-303): every norm_type but "gLN" / "cLN" is nn.BatchNorm1d."""
+    return norm_type not in ("gLN", "cLN")
+
+
+def block_keys(r, x, causal, norm_type="gLN"):
     """Key names of one TemporalBlock.  Causal models have a Chomp1d at
     dsconv index 1, which shifts the later indices by one
-    (conv_tasnet.py:258-263)."""
+    (conv_tasnet.py:258-263).  BatchNorm1d blocks (:300-303) name their affine
+    weight / bias and add running_mean / running_var / num_batches_tracked buffers."""
     base = "separator.network.2.%d.%d.net." % (r, x)
     o = 1 if causal else 0
+    if is_bn(norm_type):
+        n1, n2 = base + "2.", base + "3.net.%d." % (2 + o)
+        return {
+            "w1": base + "0.weight", "a1": base + "1.weight",
+            "g1": n1 + "weight", "b1": n1 + "bias", "rm1": n1 + "running_mean", "rv1": n1 + "running_var",
+            "nb1": n1 + "num_batches_tracked",
+            "wd": base + "3.net.0.weight", "a2": base + "3.net.%d.weight" % (1 + o),
+            "g2": n2 + "weight", "b2": n2 + "bias", "rm2": n2 + "running_mean", "rv2": n2 + "running_var",
+            "nb2": n2 + "num_batches_tracked",
+            "w2": base + "3.net.%d.weight" % (3 + o),
+        }
     return {
         "w1": base + "0.weight",              # [H,B,1]
         "a1": base + "1.weight",              # [1]
@@ -50,23 +67,29 @@ def block_keys(r, x, causal):
     }
 
 
-def param_shapes(N, L, B, H, P, X, R, C, causal=False):
-    """Ordered {key: shape} in the reference's parameter registration order."""
+def param_shapes(N, L, B, H, P, X, R, C, causal=False, norm_type="gLN"):
+    """Ordered {key: shape} in the reference's state_dict order (BatchNorm1d buffers included)."""
     shapes = {"encoder.conv1d_U.weight": (N, 1, L),
               "separator.network.0.gamma": (1, N, 1),
               "separator.network.0.beta": (1, N, 1),
               "separator.network.1.weight": (B, N, 1)}
     for r in range(R):
         for x in range(X):
-            k = block_keys(r, x, causal)
+            k = block_keys(r, x, causal, norm_type)
+            bn = is_bn(norm_type)
+            nshape = (H,) if bn else (1, H, 1)
             shapes[k["w1"]] = (H, B, 1)
             shapes[k["a1"]] = (1,)
-            shapes[k["g1"]] = (1, H, 1)
-            shapes[k["b1"]] = (1, H, 1)
+            shapes[k["g1"]] = nshape
+            shapes[k["b1"]] = nshape
+            if bn:
+                shapes[k["rm1"]], shapes[k["rv1"]], shapes[k["nb1"]] = (H,), (H,), ()
             shapes[k["wd"]] = (H, 1, P)
             shapes[k["a2"]] = (1,)
-            shapes[k["g2"]] = (1, H, 1)
-            shapes[k["b2"]] = (1, H, 1)
+            shapes[k["g2"]] = nshape
+            shapes[k["b2"]] = nshape
+            if bn:
+                shapes[k["rm2"]], shapes[k["rv2"]], shapes[k["nb2"]] = (H,), (H,), ()
             shapes[k["w2"]] = (B, H, 1)
     shapes["separator.network.3.weight"] = (C * N, B, 1)
     shapes["decoder.basis_signals.weight"] = (L, N)
@@ -74,14 +97,27 @@ def param_shapes(N, L, B, H, P, X, R, C, causal=False):
 
 
 def random_params(N, L, B, H, P, X, R, C, causal=False, seed=0, dtype=torch.float32,
-                  scale_norm=True):
+                  scale_norm=True, norm_type="gLN"):
     """Seeded synthetic weights with the reference's init *distribution*
     (xavier-normal for dim>1 incl. gamma/beta, PReLU 0.25; conv_tasnet.py:41-43).
     Not bit-identical to a same-seed reference construction; golden fixtures
     carry the reference's actual weights."""
     g = torch.Generator().manual_seed(seed)
     out = {}
-    for k, shp in param_shapes(N, L, B, H, P, X, R, C, causal).items():
+    for k, shp in param_shapes(N, L, B, H, P, X, R, C, causal, norm_type).items():
+        if is_bn(norm_type) and k.split(".")[-1] in ("bias", "running_mean", "running_var", "num_batches_tracked") \
+                or (is_bn(norm_type) and shp == (H,)):
+            # BatchNorm1d tensors: non-trivial affine and running statistics (as after some training)
+            leaf = k.split(".")[-1]
+            if leaf == "num_batches_tracked":
+                out[k] = torch.tensor(100, dtype=torch.long)
+            elif leaf == "running_var":
+                out[k] = (0.5 + torch.rand(shp, generator=g, dtype=torch.float64)).to(dtype)
+            elif leaf == "weight":
+                out[k] = (1.0 + 0.2 * torch.randn(shp, generator=g, dtype=torch.float64)).to(dtype)
+            else:
+                out[k] = (0.1 * torch.randn(shp, generator=g, dtype=torch.float64)).to(dtype)
+            continue
         if len(shp) == 1:
             out[k] = torch.full(shp, 0.25, dtype=dtype)
             continue
@@ -117,12 +153,23 @@ def gln(y, gamma, beta):
     return gamma * (y - mean) / torch.pow(var + EPS, 0.5) + beta
 
 
-def _norm(norm_type, y, gamma, beta):
+BN_EPS = 1e-5  # nn.BatchNorm1d default; conv_tasnet.py:303 passes none
+
+
+def bn_eval(y, weight, bias, running_mean, running_var):
+    """nn.BatchNorm1d in eval mode (conv_tasnet.py:300-303): running statistics per channel."""
+    inv = 1.0 / torch.sqrt(running_var + BN_EPS)
+    return (y - running_mean[None, :, None]) * inv[None, :, None] * weight[None, :, None] + bias[None, :, None]
+
+
+def _norm(norm_type, y, gamma, beta, stats=None):
     if norm_type == "gLN":
         return gln(y, gamma, beta)
     if norm_type == "cLN":
         return cln(y, gamma, beta)
-    raise NotImplementedError("oracle covers gLN and cLN (SURVEY.md §8a row 5)")
+    if stats is None:
+        raise NotImplementedError("BatchNorm1d: the oracle covers inference (running statistics) only")
+    return bn_eval(y, gamma, beta, stats[0], stats[1])
 
 
 def depthwise(x, wd, dilation, causal):
@@ -141,10 +188,11 @@ def temporal_block(x, p, k, dilation, norm_type, causal, taps=None):
     intermediates for per-kernel parity tests."""
     a = F.conv1d(x, p[k["w1"]])
     pa = F.prelu(a, p[k["a1"]])
-    n1 = _norm(norm_type, pa, p[k["g1"]], p[k["b1"]])
+    bn = is_bn(norm_type)
+    n1 = _norm(norm_type, pa, p[k["g1"]], p[k["b1"]], (p[k["rm1"]], p[k["rv1"]]) if bn else None)
     d = depthwise(n1, p[k["wd"]], dilation, causal)
     q = F.prelu(d, p[k["a2"]])
-    n2 = _norm(norm_type, q, p[k["g2"]], p[k["b2"]])
+    n2 = _norm(norm_type, q, p[k["g2"]], p[k["b2"]], (p[k["rm2"]], p[k["rv2"]]) if bn else None)
     out = F.conv1d(n2, p[k["w2"]]) + x
     if taps is not None:
         taps.update(a=a, pa=pa, n1=n1, d=d, q=q, n2=n2, out=out)
@@ -160,7 +208,7 @@ def separator(w, p, cfg, taps=None):
         taps["bottleneck"] = y
     for r in range(cfg["R"]):
         for x in range(cfg["X"]):
-            k = block_keys(r, x, cfg["causal"])
+            k = block_keys(r, x, cfg["causal"], cfg["norm_type"])
             y = temporal_block(y, p, k, 2 ** x, cfg["norm_type"], cfg["causal"])
             if taps is not None:
                 taps["block_%d_%d" % (r, x)] = y

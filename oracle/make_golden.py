@@ -49,6 +49,12 @@ CASES = {
     # odd channel counts (SIMT GEMM / scalar backward kernels), ragged lengths.  Gradient fixture for
     # that path: demo_gln's own gradients sit on a PReLU kink (one depthwise output is 5e-8, so fp32
     # rounding decides the branch) and cannot be held to a tight tolerance.
+    # BatchNorm1d blocks (conv_tasnet.py:300-303) in INFERENCE mode on the tensor-core path: running statistics
+    # come from three training-mode forwards of the reference, the affine is perturbed; no gradients stored
+    "tc_bn_eval": dict(cfg=dict(N=64, L=16, B=64, H=128, P=3, X=3, R=1, C=2, norm_type="BN",
+                                causal=False, mask_nonlinear="relu"), M=2, T=1207, lengths=[1207, 900], bn_eval=True),
+    "bn_eval_causal": dict(cfg=dict(N=8, L=4, B=8, H=16, P=3, X=2, R=2, C=2, norm_type="BN",
+                                    causal=True, mask_nonlinear="relu"), M=2, T=51, lengths=[51, 37], bn_eval=True),
     "odd_gln": dict(cfg=dict(N=5, L=4, B=6, H=7, P=3, X=3, R=1, C=2, norm_type="gLN",
                              causal=False, mask_nonlinear="relu"), M=2, T=60, lengths=[60, 41]),
 }
@@ -66,8 +72,17 @@ def main():
         cfg, M, T = case["cfg"], case["M"], case["T"]
         torch.manual_seed(123)
         model = ref_model.ConvTasNet(**cfg)
-        init_sd = {k: v.detach().clone() for k, v in model.state_dict().items()}
         g = torch.Generator().manual_seed(2025)
+        if case.get("bn_eval"):
+            with torch.no_grad():
+                model.train()
+                for _ in range(3):
+                    model(0.1 * torch.randn(M, T, generator=g))
+                for k, v in model.named_parameters():
+                    if v.dim() == 1 and v.numel() > 1:      # BatchNorm1d weight / bias
+                        v.add_(0.2 * torch.randn(v.shape, generator=g))
+            model.eval()
+        init_sd = {k: v.detach().clone() for k, v in model.state_dict().items()}
         sources = 0.1 * torch.randn(M, cfg["C"], T, generator=g)
         mixture = sources.sum(1) + 0.01 * torch.randn(M, T, generator=g)
         lengths = torch.tensor(case["lengths"], dtype=torch.int64)
@@ -76,7 +91,8 @@ def main():
         est = model(mixture)
         est_unmasked = est.detach().clone()
         loss, max_snr, est_masked, reorder = ref_loss.cal_loss(sources.clone(), est, lengths)
-        loss.backward()
+        if not case.get("bn_eval"):
+            loss.backward()
         _, perms, idx = ref_loss.cal_si_snr_with_pit(sources.clone(), est_unmasked.clone(), lengths)
 
         blob = {"mixture": mixture, "sources": sources, "lengths": lengths,
@@ -86,7 +102,8 @@ def main():
         for k, v in init_sd.items():
             blob["w:" + k] = v
         for k, v in model.named_parameters():
-            blob["g:" + k] = v.grad.detach()
+            if v.grad is not None:
+                blob["g:" + k] = v.grad.detach()
         np.savez_compressed(os.path.join(OUT, name + ".npz"),
                             cfg=np.array(repr(cfg)),
                             **{k: v.numpy() for k, v in blob.items()})

@@ -214,8 +214,9 @@ def test_error_conventions():
     import conv_tasnet
     with pytest.raises(ValueError):
         conv_tasnet.ConvTasNet(8, 4, 8, 8, 3, 1, 1, 2, mask_nonlinear="tanh")
+    bn = conv_tasnet.ConvTasNet(8, 4, 8, 8, 3, 1, 1, 2, norm_type="BN").to(DEV)   # BatchNorm1d: inference only
     with pytest.raises(NotImplementedError):
-        conv_tasnet.ConvTasNet(8, 4, 8, 8, 3, 1, 1, 2, norm_type="BN")
+        bn.train()(torch.zeros(1, 100, device=DEV))
     m = conv_tasnet.ConvTasNet(8, 4, 8, 8, 3, 1, 1, 2).to(DEV).eval()
     with torch.no_grad():
         with pytest.raises(RuntimeError):

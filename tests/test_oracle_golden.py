@@ -70,3 +70,18 @@ def test_sisnri_cases():
         for c in range(2):
             assert abs(O.cal_SISNR(ref[c], est[c]) - float(z["sisnr%d" % i][c, 0])) < tol
             assert abs(O.cal_SISNR(ref[c], mix) - float(z["sisnr%d" % i][c, 1])) < tol
+
+
+@pytest.mark.parametrize("name", ["tc_bn_eval", "bn_eval_causal"])
+def test_batchnorm_inference_matches_reference(name):
+    """norm_type="BN" (conv_tasnet.py:300-303) in eval mode: state_dict layout incl. the running-statistics
+    buffers, forward and loss against the reference's recorded outputs."""
+    torch.set_num_threads(1)
+    cfg, z = load_golden(name)
+    p = {k[2:]: v for k, v in z.items() if k.startswith("w:")}
+    assert list(p) == list(O.param_shapes(*(cfg[k] for k in "NLBHPXRC"), cfg["causal"], cfg["norm_type"]))
+    est = O.forward(z["mixture"], p, cfg)
+    assert rel_l2(est, z["est"]) < 2e-6
+    loss, max_snr, masked, reorder, idx = O.cal_loss(z["sources"], est, z["lengths"])
+    assert torch.equal(idx, z["idx"])
+    assert abs(float(loss) - float(z["loss"])) < 1e-4
