@@ -187,6 +187,7 @@ def run_b200(args):
     eng.fuse_max_dilation = args.fuse
     eng.fuse_update = bool(args.fuse_update)
     eng.use_graph = bool(args.graph)
+    eng.n_streams = args.streams
 
     g = torch.Generator().manual_seed(2025 + rank)
     host_mix = (0.1 * torch.randn(n_local, T, generator=g)).pin_memory()
@@ -325,7 +326,7 @@ def run_b200(args):
             "config": {"workload": "bulk separation of %d x 4 s @ 8 kHz mixtures, paper config "
                                    "(BASELINE configs[3]), sharded by utterance" % GLOBAL_BATCH,
                        "global_batch": GLOBAL_BATCH, "per_gpu": n_local, "micro_batch": args.micro_batch,
-                       "cuda_graph": bool(args.graph), "parallelism": "utterance-sharded x%d, no collective" % world,
+                       "cuda_graph": bool(args.graph), "streams": args.streams, "parallelism": "utterance-sharded x%d, no collective" % world,
                        "l2": "activation working set per step (%.1f GB) >> 126 MB L2" % (n_local * 33e6 / 1e9),
                        "x_realtime_per_gpu": value / world},
             "clocks": clocks, "e2e": e2e, "gpu_launches": launches,
@@ -409,6 +410,8 @@ def main():
     ap.add_argument("--fuse-update", type=int, default=0,
                     help="fold the deferred residual update into the next conv1x1 (ctn_updc1_fwd)")
     ap.add_argument("--graph", type=int, default=1)
+    ap.add_argument("--streams", type=int, default=1,
+                    help="micro-batches in flight on separate streams (engine.n_streams)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-train", action="store_true", help="skip the train-step leg")
     args = ap.parse_args()

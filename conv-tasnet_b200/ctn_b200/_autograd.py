@@ -52,10 +52,12 @@ class _PreparedBwd:
 class TrainPlan:
     """Workspaces and call lists of one (M, T) training step on one device."""
 
-    def __init__(self, cfg, M, T, device):
+    def __init__(self, cfg, M, T, device, overlap=True):
         _check_cfg(cfg, training=True)
         self.norm = _NORM[cfg["norm_type"]]
         self.cfg, self.M, self.T, self.device = cfg, M, T, device
+        self.overlap = bool(overlap)                 # weight gradients on a side stream (see _launch_backward)
+        self.side_stream = torch.cuda.Stream(device=device) if overlap else None
         N, L, B, H, C_ = cfg["N"], cfg["L"], cfg["B"], cfg["H"], cfg["C"]
         self.hop, self.K, self.T_conv = frame_geometry(T, L)
         K = self.K
@@ -259,9 +261,11 @@ class TrainPlan:
             a_ = (self.d[i].data_ptr(), params[k["a2"]].data_ptr(), params[k["g2"]].data_ptr(),
                   params[k["b2"]].data_ptr(), GLN, self.stat2[i].data_ptr(), P2, M, K, H,
                   self.hl_H[0].data_ptr(), self.hl_H[1].data_ptr())
+            bwd.append(_JOIN)     # the previous block's weight gradients read hl_H and the partial buffers
             bwd.append(lambda s, a=a_: ns(*a, s))                                       # u (hi, lo)
             call, seg_w2 = self._wgrad(self.g_hl, self.hl_H, B, H, k["w2"])              # dW2 = g^T u
-            bwd.append(call)
+            bwd.append(_FORK)
+            bwd.append((_SIDE, call))
             bwd.append(self._gemm(Cin=B, Cout=H, a_hi=self.g_hl[0], a_lo=self.g_hl[1], w_hi=pb["w2t"][0],
                                   w_lo=pb["w2t"][1], out_f32=self.du, out_stat=GLN, out_stat_buf=self.bstat,
                                   bw_pre=self.d[i], bw_gamma=params[k["g2"]], bw_slope=params[k["a2"]],
@@ -277,6 +281,7 @@ class TrainPlan:
             b.norm = self.norm
             self._keep.append(b)
             bwd.append(lambda s, ref=C.byref(b): bd(ref, s))
+            bwd.append(_JOIN)     # dW2 has consumed u before da overwrites hl_H
             if is_gln:
                 a_ = (self.dn1.data_ptr(), self.a[i].data_ptr(), self.stat1[i].data_ptr(), self.P1,
                       self.scal_part.data_ptr(), self.bd_ctas[xb], params[k["g1"]].data_ptr(),
@@ -289,7 +294,8 @@ class TrainPlan:
                       self.hl_H[0].data_ptr(), self.hl_H[1].data_ptr(), self.alpha_part.data_ptr())
                 bwd.append(lambda s, a=a_: pn_cln(*a, s))
             call, seg_w1 = self._wgrad(self.hl_H, self.x_hl[i], H, B, k["w1"], self.wg_part2)   # dW1 = da^T x
-            bwd.append(call)
+            bwd.append(_FORK)
+            bwd.append((_SIDE, call))
             # every parameter gradient of the block in ONE reduction launch
             cp, cn, cs = self.chan_part, M * self.bd_rows[xb], (4 + P) * H
             segs = [(cp, cn, cs, 0, H, 1, self.grad_ptr(k["g2"]), 1), (cp, cn, cs, H, H, 1, self.grad_ptr(k["b2"]), 1),
@@ -299,14 +305,15 @@ class TrainPlan:
             segs.append((self.scal_part, M * self.bd_ctas[xb], 4, 2, 1, 1, self.grad_ptr(k["a2"]), 1))
             segs.append((self.alpha_part, M * self.tiles_pn, 1, 0, 1, 1, self.grad_ptr(k["a1"]), 1))
             if len(segs) + 2 <= nat.MAX_SEG:
-                bwd.append(self._reduce_multi(segs + [seg_w2, seg_w1]))
+                bwd.append((_SIDE, self._reduce_multi(segs + [seg_w2, seg_w1])))
             else:                                   # P > 3
-                bwd.append(self._reduce_multi(segs[:nat.MAX_SEG]))
-                bwd.append(self._reduce_multi(segs[nat.MAX_SEG:] + [seg_w2, seg_w1]))
+                bwd.append((_SIDE, self._reduce_multi(segs[:nat.MAX_SEG])))
+                bwd.append((_SIDE, self._reduce_multi(segs[nat.MAX_SEG:] + [seg_w2, seg_w1])))
             bwd.append(self._gemm(Cin=H, Cout=B, a_hi=self.hl_H[0], a_lo=self.hl_H[1], w_hi=pb["w1t"][0],
                                   w_lo=pb["w1t"][1], resid=self.g, out_f32=self.g, out_hi=self.g_hl[0],
                                   out_lo=self.g_hl[1]))                                   # g = da W1 + g
         # bottleneck + leading cLN + encoder
+        bwd.append(_JOIN)
         a_ = (self.w.data_ptr(), None, g0.data_ptr(), b0.data_ptr(), nat.NORM_CLN, self.rowstat0.data_ptr(), 1,
               M, K, N, self.w_hl[0].data_ptr(), self.w_hl[1].data_ptr())
         bwd.append(lambda s, a=a_: ns(*a, s))                                           # n0 (hi, lo) over w_hl
@@ -338,10 +345,39 @@ class TrainPlan:
         check(lib.ctn_decoder_fwd(*self.dec_args, self.est.data_ptr(), s))
 
     def _launch_backward(self):
+        """The dgrad chain runs on the current stream; weight-gradient GEMMs and the per-block parameter
+        reduction (results needed only at the end of the step) run on a side stream between _FORK (side
+        waits for main) and _JOIN (main waits for side) markers, so they fill the SMs the chain's
+        kernels leave idle at small batch.  With overlap off everything runs in list order on one stream."""
         s, check, lib = nat.stream(), nat.check, nat.lib()
         check(lib.ctn_decoder_bwd(self.g_est.data_ptr(), *self.dec_bwd_args, s))
+        if not self.overlap:
+            for c in self.bwd_calls:
+                if c is _FORK or c is _JOIN:
+                    continue
+                check((c[1] if isinstance(c, tuple) else c)(s))
+            return
+        main = torch.cuda.current_stream(self.device)
+        side = self.side_stream
+        side_ptr = side.cuda_stream
+        pending = False     # side work issued since the last join
         for c in self.bwd_calls:
-            check(c(s))
+            if c is _FORK:
+                ev = torch.cuda.Event()
+                ev.record(main)
+                side.wait_event(ev)
+            elif c is _JOIN:
+                if pending:
+                    ev = torch.cuda.Event()
+                    ev.record(side)
+                    main.wait_event(ev)
+                    pending = False
+            elif isinstance(c, tuple):
+                check(c[1](side_ptr))
+                pending = True
+            else:
+                check(c(s))
+        assert not pending
 
     def _capture(self, launch):
         launch()                                   # warm-up outside capture (attribute setup, lazy loading)
@@ -369,7 +405,10 @@ class TrainPlan:
             if self.bwd_graph is None:
                 self.bwd_graph = self._capture(self._launch_backward)
             self.bwd_graph.replay()
-        return len(self.bwd_calls) + 1
+        return sum(1 for c in self.bwd_calls if c is not _FORK and c is not _JOIN) + 1
+
+
+_FORK, _JOIN, _SIDE = "fork", "join", "side"   # markers in TrainPlan.bwd_calls
 
 
 class TrainEngine:
@@ -383,6 +422,7 @@ class TrainEngine:
         # n_local / n_global and all-reduces (sum) it over this torch.distributed group, which equals
         # the gradient of the reference's global-mean loss
         self.use_graph = True
+        self.overlap_wgrad = True      # backward: weight-gradient GEMMs + reductions on a side stream
         self.process_group = None
         self.global_batch = None       # utterances per step over all ranks (None = equal shards)
         self.last_flat_grad = None
@@ -396,10 +436,10 @@ class TrainEngine:
         self.prep[di].refresh(self.cfg, params)
         if old != self.prep[di].fingerprint:
             self.prep_b[di].refresh(self.cfg, params)
-        key = (di, M, T)
+        key = (di, M, T, bool(self.overlap_wgrad))
         plan = self.plans.get(key)
         if plan is None:
-            plan = self.plans[key] = TrainPlan(self.cfg, M, T, device)
+            plan = self.plans[key] = TrainPlan(self.cfg, M, T, device, self.overlap_wgrad)
         ptrs = tuple(p.data_ptr() for p in params.values())
         if plan.fwd_calls is None or plan.param_ptrs != ptrs:
             plan.build(params, self.prep[di], self.prep_b[di])

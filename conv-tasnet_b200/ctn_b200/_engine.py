@@ -327,6 +327,11 @@ class SeparationEngine:
         # after a fused block, fold its deferred residual update into the next block's conv1x1
         # (ctn_updc1_fwd).  Parity-green but not faster than ctn_resid_update + ctn_gemm1x1 yet
         self.fuse_update = False
+        # micro-batches in flight: with n > 1, consecutive micro-batches (independent utterances, separate
+        # workspaces) are issued round-robin on n side streams, so one chain's HBM-bound kernels
+        # (residual update, decoder) and kernel tails overlap the other chain's tensor-bound GEMMs
+        self.n_streams = 1
+        self._streams = {}
         self.launches = 0   # kernels of libctn_b200 launched by forward() so far
 
     def num_launches(self):
@@ -336,8 +341,8 @@ class SeparationEngine:
         n = self.cfg["R"] * self.cfg["X"]
         return 4 + (2 * n + 1 if self.fuse_update and self.fuse_max_dilation >= 2 ** (self.cfg["X"] - 1) else 3 * n)
 
-    def _plan(self, params, M, T, device):
-        key = (device.index, M, T, self.fuse_max_dilation, self.fuse_update)
+    def _plan(self, params, M, T, device, slot=0):
+        key = (device.index, M, T, self.fuse_max_dilation, self.fuse_update, slot)
         prep = self.prepared.get(device.index)
         if prep is None:
             prep = self.prepared[device.index] = _Prepared(self.cfg, device)
@@ -368,11 +373,38 @@ class SeparationEngine:
         out = torch.empty(M, cfg["C"], T, dtype=torch.float32, device=device)
         with torch.cuda.device(device):
             mb = max(1, int(self.micro_batch))
-            for m0 in range(0, M, mb):
-                m1 = min(M, m0 + mb)
-                plan = self._plan(params, m1 - m0, T, device)
-                plan.mix.copy_(mixture[m0:m1])
-                plan.run(self.use_graph)
+            n_str = max(1, min(int(self.n_streams), (M + mb - 1) // mb))
+            if n_str == 1:
+                for m0 in range(0, M, mb):
+                    m1 = min(M, m0 + mb)
+                    plan = self._plan(params, m1 - m0, T, device)
+                    plan.mix.copy_(mixture[m0:m1])
+                    plan.run(self.use_graph)
+                    self.launches += len(plan.calls)
+                    out[m0:m1].copy_(plan.est)
+                return out
+            # several chains in flight: plans (and their CUDA graphs) are built on the caller's stream first,
+            # then each micro-batch runs on its slot's side stream; the caller's stream joins at the end
+            chunks = [(m0, min(M, m0 + mb)) for m0 in range(0, M, mb)]
+            plans = [self._plan(params, m1 - m0, T, device, slot=i % n_str) for i, (m0, m1) in enumerate(chunks)]
+            side = self._streams.setdefault(device.index, [])
+            while len(side) < n_str:
+                side.append(torch.cuda.Stream(device=device))
+            cur = torch.cuda.current_stream(device)
+            if self.use_graph:
+                for plan in plans:
+                    if plan.graph is None:
+                        plan.run(True)      # capture (and one replay) on the caller's stream
+            ready = cur.record_event()
+            for i, ((m0, m1), plan) in enumerate(zip(chunks, plans)):
+                st = side[i % n_str]
+                if i < n_str:
+                    st.wait_event(ready)
+                with torch.cuda.stream(st):
+                    plan.mix.copy_(mixture[m0:m1])
+                    plan.run(self.use_graph)
+                    out[m0:m1].copy_(plan.est)
                 self.launches += len(plan.calls)
-                out[m0:m1].copy_(plan.est)
+            for st in side[:n_str]:
+                cur.wait_stream(st)
         return out

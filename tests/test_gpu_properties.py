@@ -119,3 +119,25 @@ def test_ragged_input_length_is_zero_padded_back():
         K = (T - 16) // 8 + 1
         covered = (K - 1) * 8 + 16
         assert float(y[..., covered:].abs().sum()) == 0.0
+
+
+def test_micro_batches_on_side_streams_are_bit_identical():
+    """engine.n_streams > 1 issues consecutive micro-batches on separate streams (separate workspaces):
+    the result must not depend on it."""
+    import conv_tasnet
+    from conftest import load_golden
+    cfg, z = load_golden("tc_small")
+    model = conv_tasnet.ConvTasNet(**cfg)
+    model.load_state_dict({k[2:]: v for k, v in z.items() if k.startswith("w:")})
+    model = model.to("cuda").eval()
+    g = torch.Generator().manual_seed(4)
+    mix = (0.1 * torch.randn(7, 1207, generator=g)).to("cuda")
+    eng = model.engine()
+    eng.micro_batch = 2
+    outs = []
+    with torch.no_grad():
+        for n, graph in ((1, False), (2, False), (3, True), (2, True)):
+            eng.n_streams, eng.use_graph = n, graph
+            outs.append(model(mix).clone())
+    for o in outs[1:]:
+        assert torch.equal(o, outs[0])

@@ -8,6 +8,7 @@ M = int(sys.argv[1]) if len(sys.argv) > 1 else 3
 cfg = dict(N=256, L=20, B=256, H=512, P=3, X=8, R=4, C=2, norm_type="gLN", causal=False, mask_nonlinear="relu")
 torch.manual_seed(0)
 model = conv_tasnet.ConvTasNet(**cfg).cuda().train()
+model.train_engine().overlap_wgrad = bool(int(os.environ.get("CTN_OVERLAP", "1")))
 opt = torch.optim.Adam(model.parameters(), lr=1e-3)
 src = 0.1 * torch.randn(M, 2, 32000, device="cuda"); mix = src.sum(1)
 lengths = torch.full((M,), 32000, device="cuda")
