@@ -2,6 +2,8 @@
 #include <stdarg.h>
 #include <string.h>
 
+#include <stdlib.h>
+
 #include "common.cuh"
 
 namespace ctn {
@@ -18,6 +20,15 @@ void set_error(const char* fmt, ...) {
 int cuda_fail(cudaError_t e, const char* what) {
     set_error("%s: %s (%s)", what, cudaGetErrorName(e), cudaGetErrorString(e));
     return CTN_ERR_CUDA;
+}
+
+int pdl_enabled() {
+    static int cached = -1;   // racing writers store the same value
+    if (cached < 0) {
+        const char* e = getenv("CTN_PDL");
+        cached = (e != nullptr && e[0] == '0') ? 0 : 1;
+    }
+    return cached;
 }
 
 int sm_count() {

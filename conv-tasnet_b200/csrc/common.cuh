@@ -30,6 +30,38 @@ int cuda_fail(cudaError_t e, const char* what);  // records the message, returns
     } while (0)
 
 inline int ceil_div(int a, int b) { return (a + b - 1) / b; }
+int pdl_enabled();  // 1 unless the environment says CTN_PDL=0 (read once)
+// PDL is used for plain stream launches of SMALL problems only (rows = M * K frames): it hides the
+// launch latency and prologue of latency-bound kernels (one 4 s utterance, eager: 2.08 -> 1.81 ms), but
+// measured 3-7 % slower from 8 utterances up, and inside a CUDA-graph capture kernel-to-kernel edges
+// have no launch latency to hide (programmatic edges: 2-4 % slower).  DESIGN.md 3.10.
+constexpr long long kPdlMaxRows = 8192;
+inline int pdl_allowed(cudaStream_t stream, long long rows) {
+    if (!pdl_enabled() || rows > kPdlMaxRows) return 0;
+    cudaStreamCaptureStatus st = cudaStreamCaptureStatusNone;
+    if (cudaStreamIsCapturing(stream, &st) != cudaSuccess) return 0;
+    return st == cudaStreamCaptureStatusNone ? 1 : 0;
+}
+
+// Launch with the programmatic-dependent-launch attribute: the kernel may be scheduled while its
+// predecessor in the stream drains (it must call ptx::grid_dep_wait() before touching anything the
+// predecessor wrote).  Also valid under stream capture (becomes a programmatic graph edge).
+template <typename... P, typename... A>
+inline cudaError_t launch_pdl(long long rows, void (*kernel)(P...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream,
+                              A... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid, cfg.blockDim = block, cfg.dynamicSmemBytes = smem, cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = pdl_allowed(stream, rows);
+    cfg.attrs = attr, cfg.numAttrs = 1;
+    return cudaLaunchKernelEx(&cfg, kernel, static_cast<P>(args)...);
+}
+#define CTN_LAUNCH_PDL(what, ...)                                   \
+    do {                                                            \
+        cudaError_t e__ = ::ctn::launch_pdl(__VA_ARGS__);           \
+        if (e__ != cudaSuccess) return ::ctn::cuda_fail(e__, what); \
+    } while (0)
 int sm_count();  // multiprocessors of the current device (cached per device)
 
 // -------------------------------------------------------------- device side

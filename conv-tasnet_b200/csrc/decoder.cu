@@ -10,6 +10,7 @@
 // reference's index_add_ for even L (two commutative addends onto zero).
 // Memory-bound: reads 4*(C+1)*N bytes per frame, writes 4*C*hop.
 #include "common.cuh"
+#include "ptx.cuh"
 
 namespace ctn {
 
@@ -20,6 +21,7 @@ constexpr int kDecMaxC = 8;
 __global__ void __launch_bounds__(kDecWarps * 32)
 decoder_fwd_kernel(const float* __restrict__ score, const float* __restrict__ w, const float* __restrict__ V, int K,
                    int N, int L, int C, int T, int softmax, float* __restrict__ est) {
+    ptx::grid_dep_sync();   // PDL: predecessor complete; let the next kernel be scheduled
     extern __shared__ float dec_smem[];
     const int hop = L / 2;
     const int halo = (L - 1) / hop;            // frames before the tile that reach into it
@@ -116,6 +118,7 @@ template <int C, int LPT>
 __global__ void __launch_bounds__(256)
 decoder_fwd_blocked_kernel(const float* __restrict__ score, const float* __restrict__ w, const float* __restrict__ V,
                            int K, int N, int L, int T, int softmax, float* __restrict__ est) {
+    ptx::grid_dep_sync();   // PDL: predecessor complete; let the next kernel be scheduled
     extern __shared__ float dec_smem[];
     const int hop = L / 2;
     const int halo = (L - 1) / hop;
@@ -241,7 +244,7 @@ static int launch_decoder_blocked(const float* score, const float* w, const floa
                                          static_cast<int>(smem));
     if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(decoder_fwd_blocked_kernel)");
     dim3 grid(ceil_div(K, kDecRows - halo), M);
-    decoder_fwd_blocked_kernel<C, LPT><<<grid, 256, smem, stream>>>(score, w, V, K, N, L, T, softmax, est);
+    CTN_LAUNCH_PDL("decoder_fwd_blocked_kernel", static_cast<long long>(M) * K, decoder_fwd_blocked_kernel<C, LPT>, grid, 256, smem, stream, score, w, V, K, N, L, T, softmax, est);
     CTN_LAUNCH_CHECK("decoder_fwd_blocked_kernel");
     return CTN_OK;
 }
@@ -302,8 +305,7 @@ extern "C" int ctn_decoder_fwd(const float* score, const float* w, const float* 
         if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(decoder_fwd_kernel)");
     }
     dim3 grid(ceil_div(K, kDecTile), M);
-    decoder_fwd_kernel<<<grid, kDecWarps * 32, smem, static_cast<cudaStream_t>(stream)>>>(
-        score, w, V, K, N, L, C, T, mask_nonlinear == CTN_MASK_SOFTMAX, est);
+    CTN_LAUNCH_PDL("decoder_fwd_kernel", static_cast<long long>(M) * K, decoder_fwd_kernel, grid, kDecWarps * 32, smem, static_cast<cudaStream_t>(stream), score, w, V, K, N, L, C, T, mask_nonlinear == CTN_MASK_SOFTMAX, est);
     CTN_LAUNCH_CHECK("decoder_fwd_kernel");
     return CTN_OK;
 }

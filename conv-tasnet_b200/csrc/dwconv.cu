@@ -12,6 +12,7 @@
 // (taps at k +- dil re-hit L2).  Inference writes q only as the bf16 (hi, lo) pair the
 // pointwise GEMM consumes; training additionally keeps d in fp32 for the backward.
 #include "common.cuh"
+#include "ptx.cuh"
 #include "dwconv_march.cuh"
 
 namespace ctn {
@@ -75,6 +76,7 @@ __device__ __forceinline__ void store_split(__nv_bfloat16* hi, __nv_bfloat16* lo
 template <int VEC>
 __global__ void __launch_bounds__(kDwWarps * 32)
 dwconv_fwd_kernel(const DwParams p) {
+    ptx::grid_dep_sync();   // PDL: predecessor complete; let the next kernel be scheduled
     extern __shared__ float dw_smem[];
     const int H = p.H, P = p.P;
     float* wd_s = dw_smem;        // [P][H]  tap-major
@@ -243,7 +245,7 @@ extern "C" int ctn_dwconv_fwd(const ctn_dwconv_args* args, void* stream) {
         q.in_stat = p.in_stat, q.wd = a.wd, q.prelu_out = a.prelu_out, q.out_pre = a.out_pre;
         q.out_hi = p.out_hi, q.out_lo = p.out_lo, q.out_stat = p.out_stat;
         dim3 mgrid(q.out_P, a.M);
-        dwconv_march_kernel<<<mgrid, kDmWarps * 32, 0, static_cast<cudaStream_t>(stream)>>>(q);
+        CTN_LAUNCH_PDL("dwconv_march_kernel", static_cast<long long>(a.M) * a.K, dwconv_march_kernel, mgrid, kDmWarps * 32, 0, static_cast<cudaStream_t>(stream), q);
         CTN_LAUNCH_CHECK("dwconv_march_kernel");
         return CTN_OK;
     }
@@ -253,9 +255,9 @@ extern "C" int ctn_dwconv_fwd(const ctn_dwconv_args* args, void* stream) {
     dim3 grid(ceil_div(a.K, kDwTile), a.M);
     const bool vec = a.H % 4 == 0 && al16(a.in) && al16(a.out_pre) && al16(a.out_hi) && al16(a.out_lo);
     if (vec)
-        dwconv_fwd_kernel<4><<<grid, kDwWarps * 32, smem, static_cast<cudaStream_t>(stream)>>>(p);
+        CTN_LAUNCH_PDL("dwconv_fwd_kernel", static_cast<long long>(a.M) * a.K, dwconv_fwd_kernel<4>, grid, kDwWarps * 32, smem, static_cast<cudaStream_t>(stream), p);
     else
-        dwconv_fwd_kernel<1><<<grid, kDwWarps * 32, smem, static_cast<cudaStream_t>(stream)>>>(p);
+        CTN_LAUNCH_PDL("dwconv_fwd_kernel", static_cast<long long>(a.M) * a.K, dwconv_fwd_kernel<1>, grid, kDwWarps * 32, smem, static_cast<cudaStream_t>(stream), p);
     CTN_LAUNCH_CHECK("dwconv_fwd_kernel");
     return CTN_OK;
 }

@@ -10,6 +10,7 @@
 // issue-bound at half the memory roofline.
 #pragma once
 #include "common.cuh"
+#include "ptx.cuh"
 #include "f32x2.cuh"
 
 namespace ctn {
@@ -33,6 +34,7 @@ struct DwMarchParams {
 
 __global__ void __launch_bounds__(kDmWarps * 32)
 dwconv_march_kernel(const DwMarchParams p) {
+    ptx::grid_dep_sync();   // PDL: predecessor complete; let the next kernel be scheduled
     __shared__ double fin_s[2 * kDmWarps];
     __shared__ float red_s[2 * kDmWarps];
     const int m = blockIdx.y;

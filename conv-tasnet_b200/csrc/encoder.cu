@@ -5,6 +5,7 @@
 // done from a shared-memory copy of the tile's samples, so no [M, K, L] frame
 // tensor is materialised.  Memory-bound: reads 4*T, writes 8*N*K bytes per utterance.
 #include "common.cuh"
+#include "ptx.cuh"
 
 namespace ctn {
 
@@ -15,6 +16,7 @@ __global__ void __launch_bounds__(kEncWarps * 32)
 encoder_fwd_kernel(const float* __restrict__ mixture, const float* __restrict__ U, int T, int N, int L, int K,
                    float* __restrict__ w_f32, __nv_bfloat16* __restrict__ w_hi, __nv_bfloat16* __restrict__ w_lo,
                    float2* __restrict__ rowstat) {
+    ptx::grid_dep_sync();   // PDL: predecessor complete; let the next kernel be scheduled
     extern __shared__ float enc_smem[];
     const int hop = L / 2;
     float* Ut = enc_smem;       // [L][N]
@@ -98,6 +100,7 @@ __global__ void __launch_bounds__(512)
 encoder_fwd_reg_kernel(const float* __restrict__ mixture, const float* __restrict__ U, int T, int N, int K,
                        float* __restrict__ w_f32, __nv_bfloat16* __restrict__ w_hi, __nv_bfloat16* __restrict__ w_lo,
                        float2* __restrict__ rowstat) {
+    ptx::grid_dep_sync();   // PDL: predecessor complete; let the next kernel be scheduled
     constexpr int hop = L / 2;
     constexpr int kSamp = (kEncTileR - 1) * hop + L;
     __shared__ __align__(16) float xs[kSamp + 2];
@@ -176,11 +179,9 @@ extern "C" int ctn_encoder_fwd(const float* mixture, const float* U, int M, int 
         const int threads = ceil_div(N / 2, 32) * 32;
         cudaStream_t st = static_cast<cudaStream_t>(stream);
         if (L == 20)
-            encoder_fwd_reg_kernel<20><<<grid, threads, 0, st>>>(mixture, U, T, N, K, w_f32, static_cast<__nv_bfloat16*>(w_hi),
-                                                                static_cast<__nv_bfloat16*>(w_lo), static_cast<float2*>(rowstat));
+            CTN_LAUNCH_PDL("encoder_fwd_reg_kernel", static_cast<long long>(M) * K, encoder_fwd_reg_kernel<20>, grid, threads, 0, st, mixture, U, T, N, K, w_f32, static_cast<__nv_bfloat16*>(w_hi), static_cast<__nv_bfloat16*>(w_lo), static_cast<float2*>(rowstat));
         else
-            encoder_fwd_reg_kernel<16><<<grid, threads, 0, st>>>(mixture, U, T, N, K, w_f32, static_cast<__nv_bfloat16*>(w_hi),
-                                                                static_cast<__nv_bfloat16*>(w_lo), static_cast<float2*>(rowstat));
+            CTN_LAUNCH_PDL("encoder_fwd_reg_kernel", static_cast<long long>(M) * K, encoder_fwd_reg_kernel<16>, grid, threads, 0, st, mixture, U, T, N, K, w_f32, static_cast<__nv_bfloat16*>(w_hi), static_cast<__nv_bfloat16*>(w_lo), static_cast<float2*>(rowstat));
         CTN_LAUNCH_CHECK("encoder_fwd_reg_kernel");
         return CTN_OK;
     }
@@ -192,9 +193,7 @@ extern "C" int ctn_encoder_fwd(const float* mixture, const float* U, int M, int 
         if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(encoder_fwd_kernel)");
     }
     dim3 grid(ceil_div(K, kEncTile), M);
-    encoder_fwd_kernel<<<grid, kEncWarps * 32, smem, static_cast<cudaStream_t>(stream)>>>(
-        mixture, U, T, N, L, K, w_f32, static_cast<__nv_bfloat16*>(w_hi), static_cast<__nv_bfloat16*>(w_lo),
-        static_cast<float2*>(rowstat));
+    CTN_LAUNCH_PDL("encoder_fwd_kernel", static_cast<long long>(M) * K, encoder_fwd_kernel, grid, kEncWarps * 32, smem, static_cast<cudaStream_t>(stream), mixture, U, T, N, L, K, w_f32, static_cast<__nv_bfloat16*>(w_hi), static_cast<__nv_bfloat16*>(w_lo), static_cast<float2*>(rowstat));
     CTN_LAUNCH_CHECK("encoder_fwd_kernel");
     return CTN_OK;
 }

@@ -138,6 +138,9 @@ dwpw_kernel(const __grid_constant__ CUtensorMap tm_w_hi, const __grid_constant__
     ptx::cluster_sync();
     ptx::tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    // PDL: everything above touched shared memory, TMEM and model parameters only (the predecessor, a
+    // conv1x1 GEMM, writes activations and statistics); wait for it before reading those
+    ptx::grid_dep_sync();
 
     if (warp == 0) {
         // ------------------------------------------------ TMA producer (weights only)
@@ -492,6 +495,7 @@ __global__ void __launch_bounds__(kUpdThreads)
 resid_update_kernel(__nv_bfloat16* __restrict__ x_hi, __nv_bfloat16* __restrict__ x_lo, const float* __restrict__ y,
                     const float2* __restrict__ stat, int P, double count, const float* __restrict__ col_g,
                     const float* __restrict__ col_bias, int K, int B) {
+    ptx::grid_dep_sync();   // PDL: predecessor complete; let the next kernel be scheduled
     __shared__ double red[2 * (kUpdThreads / 32)];
     const int m = blockIdx.y;
     const float2 st = gln_finalize_block(stat + static_cast<long long>(m) * P, P, count, red);
@@ -606,13 +610,15 @@ extern "C" int ctn_dwpw_fwd(const ctn_dwpw_args* args, void* stream_) {
     cfg.blockDim = dim3(fb::kThreads, 1, 1);
     cfg.dynamicSmemBytes = (fb::kSmemFixed + 20 * a.H);
     cfg.stream = stream;
-    cudaLaunchAttribute attr[1];
+    cudaLaunchAttribute attr[2];
     attr[0].id = cudaLaunchAttributeClusterDimension;
     attr[0].val.clusterDim.x = 2;
     attr[0].val.clusterDim.y = 1;
     attr[0].val.clusterDim.z = 1;
+    attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[1].val.programmaticStreamSerializationAllowed = pdl_allowed(stream, static_cast<long long>(a.M) * a.K);
     cfg.attrs = attr;
-    cfg.numAttrs = 1;
+    cfg.numAttrs = 2;
     cudaError_t e = cudaLaunchKernelEx(&cfg, kern, tw_hi, tw_lo, p);
     if (e != cudaSuccess) return cuda_fail(e, "cudaLaunchKernelEx(dwpw_kernel)");
     return CTN_OK;
@@ -628,9 +634,7 @@ extern "C" int ctn_resid_update(void* x_hi, void* x_lo, const float* y, const vo
     CTN_REQUIRE(aligned(x_hi, 16) && aligned(x_lo, 16) && aligned(y, 32) && aligned(col_g, 16) && aligned(col_bias, 16),
                 "ctn_resid_update: buffers must be 16-byte aligned (y: 32)");
     dim3 grid(ceil_div(K, fb::kUpdRows), M);
-    fb::resid_update_kernel<<<grid, fb::kUpdThreads, 0, stream>>>(
-        static_cast<__nv_bfloat16*>(x_hi), static_cast<__nv_bfloat16*>(x_lo), y, static_cast<const float2*>(stat), P, count,
-        col_g, col_bias, K, B);
+    CTN_LAUNCH_PDL("resid_update_kernel", static_cast<long long>(M) * K, fb::resid_update_kernel, grid, fb::kUpdThreads, 0, stream, static_cast<__nv_bfloat16*>(x_hi), static_cast<__nv_bfloat16*>(x_lo), y, static_cast<const float2*>(stat), P, count, col_g, col_bias, K, B);
     CTN_LAUNCH_CHECK("resid_update_kernel");
     return CTN_OK;
 }

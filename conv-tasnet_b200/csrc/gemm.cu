@@ -289,6 +289,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tm_a_hi, const __grid_constan
     if (PAIR) ptx::cluster_sync(); else __syncthreads();
     ptx::tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    // PDL: barrier init, TMEM allocation and descriptor prefetch above overlapped the predecessor's tail;
+    // from here on the kernel reads what the predecessor wrote
+    ptx::grid_dep_sync();
 
     if (warp == 0) {
         // ------------------------------------------------ TMA producer
@@ -573,6 +576,7 @@ __global__ void __launch_bounds__(128)
 gemm_simt_kernel(const __nv_bfloat16* __restrict__ a_hi, const __nv_bfloat16* __restrict__ a_lo,
                  const __nv_bfloat16* __restrict__ w_hi, const __nv_bfloat16* __restrict__ w_lo, const EpiParams ep,
                  int Cin) {
+    ptx::grid_dep_sync();   // PDL: predecessor complete; let the next kernel be scheduled
     const int rt = blockIdx.x;
     const int m = rt / ep.tiles_per_utt, tk = rt % ep.tiles_per_utt;
     const int ew = threadIdx.x >> 5;
@@ -721,13 +725,15 @@ static int launch_tc(const ctn_gemm_args& a, const EpiParams& ep, cudaStream_t s
     cfg.blockDim = dim3(Cfg::kThreads, 1, 1);
     cfg.dynamicSmemBytes = Cfg::kSmemBytes;
     cfg.stream = stream;
-    cudaLaunchAttribute attr[1];
+    cudaLaunchAttribute attr[2];
     attr[0].id = cudaLaunchAttributeClusterDimension;
     attr[0].val.clusterDim.x = PAIR ? 2 : 1;
     attr[0].val.clusterDim.y = 1;
     attr[0].val.clusterDim.z = 1;
+    attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[1].val.programmaticStreamSerializationAllowed = pdl_allowed(stream, static_cast<long long>(a.M) * a.K);
     cfg.attrs = attr;
-    cfg.numAttrs = 1;
+    cfg.numAttrs = 2;
     cudaError_t e = cudaLaunchKernelEx(&cfg, gemm_tc_kernel<BN, PAIR, EPI>, ta_hi, ta_lo, tw_hi, tw_lo, to_f32, to_hi, to_lo,
                                        ep, a.Cin, n_tiles, items, row_tiles);
     if (e != cudaSuccess) return cuda_fail(e, "cudaLaunchKernelEx(gemm_tc_kernel)");
@@ -808,9 +814,7 @@ extern "C" int ctn_gemm1x1(const ctn_gemm_args* args, void* stream_) {
         return pair ? launch_tc<256, true, kEpiPlain>(a, ep, stream) : launch_tc<128, false, kEpiPlain>(a, ep, stream);
     }
     const int grid = a.M * ep.tiles_per_utt;
-    gemm_simt_kernel<<<grid, 128, 0, stream>>>(
-        static_cast<const __nv_bfloat16*>(a.a_hi), static_cast<const __nv_bfloat16*>(a.a_lo),
-        static_cast<const __nv_bfloat16*>(a.w_hi), static_cast<const __nv_bfloat16*>(a.w_lo), ep, a.Cin);
+    CTN_LAUNCH_PDL("gemm_simt_kernel", static_cast<long long>(a.M) * a.K, gemm_simt_kernel, grid, 128, 0, stream, static_cast<const __nv_bfloat16*>(a.a_hi), static_cast<const __nv_bfloat16*>(a.a_lo), static_cast<const __nv_bfloat16*>(a.w_hi), static_cast<const __nv_bfloat16*>(a.w_lo), ep, a.Cin);
     CTN_LAUNCH_CHECK("gemm_simt_kernel");
     return CTN_OK;
 }

@@ -96,6 +96,18 @@ __device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t ncols) {
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols) : "memory");
 }
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+// Programmatic dependent launch (PDL).  A kernel launched with the programmatic-stream-serialization
+// attribute may start while its predecessor in the stream still runs; grid_dep_wait() blocks until the
+// predecessor grid has completed and its writes are visible (a no-op for a normal launch).
+// grid_dep_launch() lets the NEXT kernel's CTAs be scheduled early.  Every kernel calls wait before
+// launch, so when a kernel's prologue runs everything up to its pre-predecessor is complete.
+__device__ __forceinline__ void grid_dep_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void grid_dep_launch() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void grid_dep_sync() {
+    grid_dep_wait();
+    grid_dep_launch();
+}
+
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
 
 // D[tmem] (+)= A[smem] * B[smem], bf16 x bf16 -> f32, one CTA.
