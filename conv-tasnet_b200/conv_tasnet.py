@@ -91,18 +91,27 @@ class ConvTasNet(nn.Module):
                 nn.init.xavier_normal_(p)
         self._keys = [k for k, (_, kind) in spec.items() if not kind.startswith("buf_")]
         self._buffer_keys = [k for k, (_, kind) in spec.items() if kind in ("buf_zeros", "buf_ones")]
-        self._engine = None
+        # created eagerly (no CUDA work) so that DataParallel replicas, whose __dict__ is a shallow copy of
+        # this module's, share one orchestrator with per-device plans instead of rebuilding it per call
+        self.__dict__["_engine"] = _engine.SeparationEngine(self._cfg())
+        from ctn_b200 import _autograd
+        self.__dict__["_train_engine"] = _autograd.TrainEngine(self._cfg())
 
     def _cfg(self):
         return dict(N=self.N, L=self.L, B=self.B, H=self.H, P=self.P, X=self.X, R=self.R, C=self.C,
                     norm_type=self.norm_type, causal=self.causal, mask_nonlinear=self.mask_nonlinear)
 
     def _params(self):
-        sd = dict(self.named_parameters())
-        out = {k: sd[k] for k in self._keys}
-        if self._buffer_keys:   # BatchNorm running statistics ride along (the engine folds them)
-            bd = dict(self.named_buffers())
-            out.update((k, bd[k]) for k in self._buffer_keys)
+        """{state_dict key: tensor} of the parameters (and BatchNorm running statistics) in registration
+        order.  Resolved attribute by attribute rather than through named_parameters(): the replicas that
+        torch.nn.DataParallel builds (train.py:121, separate.py:45) hold their parameter copies as plain
+        attributes, not in _parameters."""
+        out = {}
+        for key in self._keys + self._buffer_keys:
+            node = self
+            for part in key.split("."):
+                node = getattr(node, part)
+            out[key] = node
         return out
 
     def engine(self):

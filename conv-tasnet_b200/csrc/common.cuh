@@ -63,6 +63,15 @@ inline cudaError_t launch_pdl(long long rows, void (*kernel)(P...), dim3 grid, d
         if (e__ != cudaSuccess) return ::ctn::cuda_fail(e__, what); \
     } while (0)
 int sm_count();  // multiprocessors of the current device (cached per device)
+// Function attributes (dynamic shared-memory limit) are per DEVICE: a process that drives several GPUs
+// (torch.nn.DataParallel, train.py:121) must set them on each.  Slot of the current device in a
+// per-kernel `static bool done[kMaxDevices]` cache.
+constexpr int kMaxDevices = 64;
+inline int device_slot() {
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= kMaxDevices) return 0;
+    return dev;
+}
 
 // -------------------------------------------------------------- device side
 __device__ __forceinline__ float warp_sum(float v) {

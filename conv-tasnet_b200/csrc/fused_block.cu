@@ -597,7 +597,8 @@ extern "C" int ctn_dwpw_fwd(const ctn_dwpw_args* args, void* stream_) {
     if ((rc = make_tmap_bf16_kmajor(&tw_lo, a.w_lo, a.B, a.H, fb::kBN / 2)) != CTN_OK) return rc;
     const bool preact = a.prelu_in == nullptr;
     auto kern = preact ? fb::dwpw_kernel<true> : fb::dwpw_kernel<false>;
-    static bool attr_set[2] = {false, false};
+    static bool attr_done[kMaxDevices][2] = {};
+    bool* attr_set = attr_done[device_slot()];
     if (!attr_set[preact]) {
         cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, fb::kSmemMax);
         if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(dwpw_kernel)");

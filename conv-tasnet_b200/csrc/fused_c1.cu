@@ -387,7 +387,8 @@ extern "C" int ctn_updc1_fwd(const ctn_updc1_args* args, void* stream_) {
     int rc;
     if ((rc = make_tmap_bf16_kmajor(&tw_hi, a.w_hi, a.H, a.B, c1::kBN / 2)) != CTN_OK) return rc;
     if ((rc = make_tmap_bf16_kmajor(&tw_lo, a.w_lo, a.H, a.B, c1::kBN / 2)) != CTN_OK) return rc;
-    static bool attr_set = false;
+    static bool attr_done[kMaxDevices] = {};
+    bool& attr_set = attr_done[device_slot()];
     if (!attr_set) {
         cudaError_t e = cudaFuncSetAttribute(c1::updc1_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, c1::kSmemBytes);
         if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(updc1_kernel)");

@@ -708,7 +708,8 @@ static int launch_tc(const ctn_gemm_args& a, const EpiParams& ep, cudaStream_t s
         return rc;
     if ((rc = make_tmap_out(&to_lo, a.out_lo ? a.out_lo : a.out_f32, a.M, a.K, a.Cout, a.out_lo == nullptr)) != CTN_OK)
         return rc;
-    static bool attr_set = false;  // idempotent; set once per process per instantiation
+    static bool attr_done[kMaxDevices] = {};  // idempotent; set once per device per instantiation
+    bool& attr_set = attr_done[device_slot()];
     if (!attr_set) {
         cudaError_t e = cudaFuncSetAttribute(gemm_tc_kernel<BN, PAIR, EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                              Cfg::kSmemBytes);

@@ -208,7 +208,8 @@ static int launch_wgrad(const void* x_hi, const void* x_lo, const void* y_hi, co
     if ((rc = make_tmap_bf16_box(&tx_lo, x_lo, R, Ci, 64, kWgBR)) != CTN_OK) return rc;
     if ((rc = make_tmap_bf16_box(&ty_hi, y_hi, R, Cj, 64, kWgBR)) != CTN_OK) return rc;
     if ((rc = make_tmap_bf16_box(&ty_lo, y_lo, R, Cj, 64, kWgBR)) != CTN_OK) return rc;
-    static bool attr_set = false;
+    static bool attr_done[kMaxDevices] = {};
+    bool& attr_set = attr_done[device_slot()];
     if (!attr_set) {
         cudaError_t e = cudaFuncSetAttribute(wgrad_tc_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                              Cfg::kSmemBytes);

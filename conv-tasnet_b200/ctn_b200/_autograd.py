@@ -14,7 +14,7 @@ import ctypes as C
 import torch
 
 from . import _native as nat
-from ._engine import _MASK, _NORM, _Prepared, _check_cfg
+from ._engine import _MASK, _NORM, _Prepared, _check_cfg, aligned_params
 from ._layout import block_keys, frame_geometry, param_spec
 
 
@@ -383,7 +383,7 @@ class TrainPlan:
         launch()                                   # warm-up outside capture (attribute setup, lazy loading)
         torch.cuda.synchronize(self.device)
         g = torch.cuda.CUDAGraph()
-        with torch.cuda.graph(g, capture_error_mode="thread_local"):
+        with torch.cuda.graph(g, stream=nat.capture_stream(self.device), capture_error_mode="thread_local"):
             launch()
         return g
 
@@ -426,6 +426,7 @@ class TrainEngine:
         self.process_group = None
         self.global_batch = None       # utterances per step over all ranks (None = equal shards)
         self.last_flat_grad = None
+        self._staged = {}              # per device: aligned copies of DataParallel replica parameters
 
     def plan(self, params, M, T, device):
         di = device.index
@@ -455,6 +456,7 @@ class _Separate(torch.autograd.Function):
         dev = mixture.device
         eng = model.train_engine()
         with torch.cuda.device(dev):
+            params = aligned_params(eng._staged, params, dev)
             plan = eng.plan(params, M, T, dev)
             plan.mix.copy_(mixture)
             eng.launches += plan.run_forward(eng.use_graph)

@@ -42,6 +42,21 @@ def _check_cfg(cfg, training=False):
         raise ValueError("Unsupported mask non-linear function")  # conv_tasnet.py:208
 
 
+def aligned_params(store, params, device):
+    """The kernels read parameter vectors with 16-byte loads.  Parameters of an ordinary module are
+    separate allocations (256-byte aligned); the replicas torch.nn.DataParallel builds (train.py:121) are
+    views into one coalesced broadcast buffer and generally are not.  In that case the values are copied
+    (device-to-device, one foreach copy) into engine-owned buffers with stable addresses, so plans and
+    CUDA graphs built on them stay valid from call to call."""
+    if all(p.data_ptr() % 16 == 0 for p in params.values()):
+        return params
+    bufs = store.get(device.index)
+    if bufs is None or list(bufs) != list(params) or any(bufs[k].shape != p.shape for k, p in params.items()):
+        bufs = store[device.index] = {k: torch.empty(p.shape, dtype=p.dtype, device=device) for k, p in params.items()}
+    torch._foreach_copy_(list(bufs.values()), [p.detach() for p in params.values()])
+    return bufs
+
+
 class _Prepared:
     """Weight-derived buffers: bf16 (hi, lo) splits with the preceding norm's affine folded in."""
 
@@ -305,7 +320,7 @@ class _Plan:
             self.launch()  # warm-up outside capture (first-use attribute setup, lazy module load)
             torch.cuda.synchronize(self.device)
             g = torch.cuda.CUDAGraph()
-            with torch.cuda.graph(g):
+            with torch.cuda.graph(g, stream=nat.capture_stream(self.device)):
                 self.launch()
             self.graph = g
         self.graph.replay()
@@ -332,6 +347,7 @@ class SeparationEngine:
         # (residual update, decoder) and kernel tails overlap the other chain's tensor-bound GEMMs
         self.n_streams = 1
         self._streams = {}
+        self._staged = {}   # per device: aligned copies of unaligned (DataParallel replica) parameters
         self.launches = 0   # kernels of libctn_b200 launched by forward() so far
 
     def num_launches(self):
@@ -372,6 +388,7 @@ class SeparationEngine:
         device = mixture.device
         out = torch.empty(M, cfg["C"], T, dtype=torch.float32, device=device)
         with torch.cuda.device(device):
+            params = aligned_params(self._staged, params, device)
             mb = max(1, int(self.micro_batch))
             n_str = max(1, min(int(self.n_streams), (M + mb - 1) // mb))
             if n_str == 1:

@@ -214,6 +214,19 @@ def stream():
     return torch.cuda.current_stream().cuda_stream
 
 
+_capture_streams = {}
+
+
+def capture_stream(device):
+    """A capture stream that belongs to `device`.  torch.cuda.graph's default capture stream is created
+    once per process on whatever device was current then, which breaks captures on any other GPU of a
+    process that drives several (torch.nn.DataParallel)."""
+    st = _capture_streams.get(device.index)
+    if st is None:
+        st = _capture_streams[device.index] = torch.cuda.Stream(device=device)
+    return st
+
+
 def require_cuda(t, what):
     if not (isinstance(t, torch.Tensor) and t.is_cuda):
         raise RuntimeError("%s must be a CUDA tensor: this implementation has no CPU path" % what)

@@ -247,7 +247,7 @@ class StreamingSeparator:
             torch.cuda.synchronize(self.device)
             g = torch.cuda.CUDAGraph()
             n = self.launches
-            with torch.cuda.graph(g):       # capture only records; the replay below executes
+            with torch.cuda.graph(g, stream=nat.capture_stream(self.device)):   # records only; replayed below
                 self._chunk_steady()
             self.launches = n
             self.graph_steady = g

@@ -82,3 +82,37 @@ def test_two_rank_gradient_equals_single_process(M):
         err, dl = out[r]
         assert err < 2e-5, (r, err)      # fp32 summation order differs between 1 and 2 shards
         assert dl < 1e-4
+
+
+def test_reference_dataparallel_wrapper():
+    """train.py:120-122 / separate.py:43-46 wrap the model in torch.nn.DataParallel: one process, the
+    batch scattered over the GPUs, replicas called from one Python thread per GPU.  The drop-in must
+    give the single-GPU result (inference) and the single-GPU gradients (training) through it."""
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    import conv_tasnet
+    import pit_criterion
+    torch.manual_seed(5)
+    model = conv_tasnet.ConvTasNet(**CFG).cuda(0)
+    g = torch.Generator().manual_seed(12)
+    src = (0.1 * torch.randn(4, 2, 2400, generator=g)).cuda(0)
+    mix = src.sum(1)
+    lengths = torch.tensor([2400, 2000, 2400, 1700], device="cuda:0")
+    dp = torch.nn.DataParallel(model, device_ids=[0, 1])
+    model.eval()
+    with torch.no_grad():
+        single = model(mix)
+        multi = dp(mix)
+    assert multi.device == single.device and torch.equal(single, multi)   # utterances are independent
+    model.train()
+    model.zero_grad()
+    loss, *_ = pit_criterion.cal_loss(src, model(mix), lengths)
+    loss.backward()
+    want = torch.cat([p.grad.flatten() for p in model.parameters()]).clone()
+    model.zero_grad()
+    loss2, *_ = pit_criterion.cal_loss(src, dp(mix), lengths)
+    loss2.backward()
+    got = torch.cat([p.grad.flatten() for p in model.parameters()])
+    assert abs(float(loss) - float(loss2)) < 1e-4
+    err = float((got.double() - want.double()).norm() / want.double().norm())
+    assert err < 2e-5, err
