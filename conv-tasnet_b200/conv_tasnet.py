@@ -131,6 +131,22 @@ class ConvTasNet(nn.Module):
             self.__dict__["_train_engine"] = eng
         return eng
 
+    @torch.no_grad()
+    def separate(self, mixture, out=None):
+        """Inference from host memory to host memory (the loop of separate.py:60-71 moves every batch to
+        the GPU and every estimate back with blocking copies): mixture is a CPU float32 [M, T] tensor,
+        ideally pinned; returns a pinned CPU [M, C, T] tensor (or fills `out`).  Host-device copies of
+        neighbouring micro-batches overlap the kernels.  The call returns after the result has arrived."""
+        params = {k: p.detach() for k, p in self._params().items()}
+        if is_bn(self.norm_type) and self.training:
+            raise NotImplementedError("norm_type=%r (BatchNorm1d) is implemented for inference only" % (self.norm_type,))
+        dev = next(iter(params.values())).device
+        if dev.type != "cuda":
+            raise RuntimeError("the model must be on a CUDA device: this implementation has no CPU path")
+        res = self.engine().forward_host(mixture, params, out)
+        torch.cuda.current_stream(dev).synchronize()
+        return res
+
     def streaming(self, chunk_frames=256, use_graph=True):
         """Chunked separation of one audio stream with bounded latency (causal cLN models only; an
         addition to the reference's surface): see ctn_b200/_stream.py."""

@@ -375,6 +375,63 @@ class SeparationEngine:
         return plan
 
     @torch.no_grad()
+    def forward_host(self, mixture, params, out=None):
+        """Bulk separation from HOST memory to HOST memory (BASELINE configs[3]): mixture is a CPU
+        float32 [M, T] tensor (pinned for asynchronous copies), the result a pinned CPU [M, C, T] tensor.
+        Micro-batch i+1 is copied in and micro-batch i-1 copied out on two copy streams while micro-batch
+        i computes (two workspace slots), so PCIe time disappears behind the kernels instead of adding
+        to them.  Stream-ordered on the current stream: synchronise it before reading `out`."""
+        if mixture.is_cuda or mixture.dim() != 2 or mixture.dtype != torch.float32:
+            raise RuntimeError("mixture must be a CPU float32 [M, T] tensor (use forward() for CUDA tensors)")
+        M, T = mixture.shape
+        cfg = self.cfg
+        if T < cfg["L"]:
+            raise RuntimeError("Calculated output size is too small: T=%d < L=%d" % (T, cfg["L"]))
+        device = next(iter(params.values())).device
+        if out is None:
+            out = torch.empty(M, cfg["C"], T, dtype=torch.float32).pin_memory()
+        elif out.is_cuda or tuple(out.shape) != (M, cfg["C"], T) or out.dtype != torch.float32 or not out.is_contiguous():
+            raise RuntimeError("out must be a contiguous CPU float32 [M, C, T] tensor")
+        with torch.cuda.device(device):
+            params = aligned_params(self._staged, params, device)
+            mb = max(1, int(self.micro_batch))
+            chunks = [(m0, min(M, m0 + mb)) for m0 in range(0, M, mb)]
+            plans = [self._plan(params, m1 - m0, T, device, slot=i % 2) for i, (m0, m1) in enumerate(chunks)]
+            cur = torch.cuda.current_stream(device)
+            if self.use_graph:
+                for plan in plans:
+                    if plan.graph is None:
+                        plan.run(True)      # capture (and one replay) before the pipeline starts
+            side = self._streams.setdefault(("io", device.index), [])
+            while len(side) < 2:
+                side.append(torch.cuda.Stream(device=device))
+            s_in, s_out = side
+            start = cur.record_event()
+            s_in.wait_event(start)
+            s_out.wait_event(start)
+            computed = {}    # plan -> event: its last compute has finished (mix may be overwritten)
+            drained = {}     # plan -> event: its last result has left the device (est may be overwritten)
+            for (m0, m1), plan in zip(chunks, plans):
+                with torch.cuda.stream(s_in):
+                    if plan in computed:
+                        s_in.wait_event(computed[plan])
+                    plan.mix.copy_(mixture[m0:m1], non_blocking=True)
+                    loaded = s_in.record_event()
+                cur.wait_event(loaded)
+                if plan in drained:
+                    cur.wait_event(drained[plan])
+                plan.run(self.use_graph)
+                self.launches += len(plan.calls)
+                computed[plan] = cur.record_event()
+                with torch.cuda.stream(s_out):
+                    s_out.wait_event(computed[plan])
+                    out[m0:m1].copy_(plan.est, non_blocking=True)
+                    drained[plan] = s_out.record_event()
+            cur.wait_stream(s_out)
+            cur.wait_stream(s_in)
+        return out
+
+    @torch.no_grad()
     def forward(self, mixture, params):
         nat.require_cuda(mixture, "mixture")
         if mixture.dim() != 2:

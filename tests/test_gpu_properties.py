@@ -141,3 +141,28 @@ def test_micro_batches_on_side_streams_are_bit_identical():
             outs.append(model(mix).clone())
     for o in outs[1:]:
         assert torch.equal(o, outs[0])
+
+
+def test_host_to_host_separation_equals_device_forward():
+    """ConvTasNet.separate (pinned host in / out, double-buffered copies on side streams) must return
+    exactly what forward() returns, for ragged micro-batch splits, with and without CUDA graphs."""
+    import conv_tasnet
+    from conftest import load_golden
+    cfg, z = load_golden("tc_small")
+    model = conv_tasnet.ConvTasNet(**cfg)
+    model.load_state_dict({k[2:]: v for k, v in z.items() if k.startswith("w:")})
+    model = model.to("cuda").eval()
+    g = torch.Generator().manual_seed(8)
+    mix = 0.1 * torch.randn(7, 1207, generator=g)
+    eng = model.engine()
+    with torch.no_grad():
+        want = model(mix.cuda()).cpu()
+    for mb, graph, pinned in ((2, False, True), (3, True, True), (16, False, False), (2, True, False)):
+        eng.micro_batch, eng.use_graph = mb, graph
+        src = mix.pin_memory() if pinned else mix.clone()
+        got = model.separate(src)
+        assert got.device.type == "cpu" and torch.equal(got, want)
+        out = torch.empty(7, cfg["C"], 1207).pin_memory()
+        assert model.separate(src, out=out) is out and torch.equal(out, want)
+    with pytest.raises(RuntimeError):
+        model.separate(mix.cuda())
