@@ -105,17 +105,21 @@ decoder_fwd_kernel(const float* __restrict__ score, const float* __restrict__ w,
     }
 }
 
-// Register-blocked variant for the usual shapes (C <= 3, L <= 24, N % 4 == 0).  The CTA stages the
-// masked mixture weights sw[r, c, n] of 32 frames (the first `halo` of them belong to the previous
-// tile) in shared memory, then thread (r = tid / 8, g = tid % 8) computes the outputs l = g, g + 8,
-// g + 16 of all C speakers of frame r with float4 reads along n: C + LPT shared loads (all
-// broadcasts or conflict-free) per 4 * C * LPT FMAs.  The generic kernel above does one output per
-// lane with scalar loads and 8 of 32 lanes idle in its second pass.
-constexpr int kDecRows = 32;     // frames per CTA including the halo
+// Row-blocked variant for the usual shapes (C <= 3, L <= 24, N % 4 == 0).  The CTA stages the masked
+// mixture weights sw[r, c, n] of 32 frames (the first `halo` of them belong to the previous tile) and
+// the basis V in shared memory.  Lane r of warp q then computes ALL L outputs of ALL C speakers of frame
+// r over the q-th eighth of the n range: per 4 n it loads C float4 of its own row (conflict-free: the
+// row stride is 4 banks off a multiple of 32) and LT float4 of V that are the same address for the
+// whole warp (one-wavefront broadcasts) for 4*C*LT FMAs -- FMA-issue-bound, where the previous layout
+// (thread = frame x 3 outputs, C + 3 four-wavefront loads per 24 FMAs) was bound by the shared-memory
+// pipe at 0.20 of the HBM roofline.  The 8 partial sums per output are added in a fixed order, so
+// a frame's value does not depend on its position in the tile or the batch.
+constexpr int kDecRows = 32;     // frames per CTA including the halo (= lanes of a warp)
 constexpr int kDecPad = 4;       // floats of padding per shared-memory row (bank spread)
+constexpr int kDecSlices = 8;    // n-range slices = warps per CTA
 
-template <int C, int LPT>
-__global__ void __launch_bounds__(256)
+template <int C, int LT>
+__global__ void __launch_bounds__(32 * kDecSlices)
 decoder_fwd_blocked_kernel(const float* __restrict__ score, const float* __restrict__ w, const float* __restrict__ V,
                            int K, int N, int L, int T, int softmax, float* __restrict__ est) {
     ptx::grid_dep_sync();   // PDL: predecessor complete; let the next kernel be scheduled
@@ -124,37 +128,53 @@ decoder_fwd_blocked_kernel(const float* __restrict__ score, const float* __restr
     const int halo = (L - 1) / hop;
     const int tile = kDecRows - halo;          // frames this CTA owns
     const int NS = N + kDecPad;
-    const int CL = C * L;
-    float* Vt = dec_smem;                      // [L][NS]   (V is [L, N] row-major already)
-    float* sw = Vt + L * NS;                   // [kDecRows][C][NS]
-    float* fr = sw + kDecRows * C * NS;        // [kDecRows][C][L]
+    float* Vt = dec_smem;                      // [LT][NS]   (V is [L, N] row-major already; rows >= L are zero)
+    float* sw = Vt + LT * NS;                  // [kDecRows][C][NS]; later reused as part[kDecSlices][kDecRows][C][LT]
     const int m = blockIdx.y;
     const int k0 = blockIdx.x * tile;          // first owned frame
     const int nk = min(tile, K - k0);
     const int rows = halo + nk;                // staged frames: k0 - halo .. k0 + nk - 1
     const int N4 = N >> 2;
-    for (int i = threadIdx.x; i < L * N4; i += blockDim.x) {
+    // basis -> shared memory with asynchronous copies, in flight together with the row loads below
+    for (int i = threadIdx.x; i < LT * N4; i += blockDim.x) {
         const int l = i / N4, n4 = i - l * N4;
-        *reinterpret_cast<float4*>(Vt + l * NS + 4 * n4) = *reinterpret_cast<const float4*>(V + l * N + 4 * n4);
+        if (l < L)
+            ptx::cp_async_16(Vt + l * NS + 4 * n4, V + l * N + 4 * n4);
+        else
+            *reinterpret_cast<float4*>(Vt + l * NS + 4 * n4) = make_float4(0.f, 0.f, 0.f, 0.f);
     }
-    for (int i = threadIdx.x; i < rows * N4; i += blockDim.x) {
-        const int r = i / N4, n4 = i - r * N4;
-        const int k = k0 - halo + r;
-        float4 o[C];
-        if (k < 0) {
+    // masked mixture weights -> shared memory, kDecUnroll items per thread and step with all global loads
+    // of a step issued before the first use (the one-item loop was a chain of 8 DRAM round trips per CTA)
+    constexpr int kDecUnroll = 4;
+    for (int base = threadIdx.x; base < kDecRows * N4; base += kDecUnroll * blockDim.x) {
+        float4 wv[kDecUnroll], sc[kDecUnroll][C];
+        int dst[kDecUnroll];
 #pragma unroll
-            for (int c = 0; c < C; ++c) o[c] = make_float4(0.f, 0.f, 0.f, 0.f);
-        } else {
-            const long long grow = static_cast<long long>(m) * K + k;
-            const float4 wv = *reinterpret_cast<const float4*>(w + grow * N + 4 * n4);
-            float4 sc[C];
+        for (int u = 0; u < kDecUnroll; ++u) {
+            const int i = base + u * blockDim.x;
+            const int r = i / N4, n4 = i - r * N4;
+            const int k = k0 - halo + r;
+            dst[u] = i < kDecRows * N4 ? r * C * NS + 4 * n4 : -1;
+            const bool live = i < kDecRows * N4 && k >= 0 && r < rows;
+            wv[u] = make_float4(0.f, 0.f, 0.f, 0.f);     // w = 0 zeroes the row (frames before the utterance / past the tile)
 #pragma unroll
-            for (int c = 0; c < C; ++c)
-                sc[c] = *reinterpret_cast<const float4*>(score + grow * (static_cast<long long>(C) * N) + c * N + 4 * n4);
+            for (int c = 0; c < C; ++c) sc[u][c] = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (live) {
+                const long long grow = static_cast<long long>(m) * K + k;
+                wv[u] = *reinterpret_cast<const float4*>(w + grow * N + 4 * n4);
+#pragma unroll
+                for (int c = 0; c < C; ++c)
+                    sc[u][c] = *reinterpret_cast<const float4*>(score + grow * (static_cast<long long>(C) * N) + c * N + 4 * n4);
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < kDecUnroll; ++u) {
+            if (dst[u] < 0) continue;
+            float4 o[C];
             if (softmax) {
                 float* f[C];
 #pragma unroll
-                for (int c = 0; c < C; ++c) f[c] = reinterpret_cast<float*>(&sc[c]);
+                for (int c = 0; c < C; ++c) f[c] = reinterpret_cast<float*>(&sc[u][c]);
 #pragma unroll
                 for (int e = 0; e < 4; ++e) {
                     float mx = -INFINITY;
@@ -169,57 +189,58 @@ decoder_fwd_blocked_kernel(const float* __restrict__ score, const float* __restr
                 }
 #pragma unroll
                 for (int c = 0; c < C; ++c)
-                    o[c] = make_float4(sc[c].x * wv.x, sc[c].y * wv.y, sc[c].z * wv.z, sc[c].w * wv.w);
+                    o[c] = make_float4(sc[u][c].x * wv[u].x, sc[u][c].y * wv[u].y, sc[u][c].z * wv[u].z, sc[u][c].w * wv[u].w);
             } else {
 #pragma unroll
                 for (int c = 0; c < C; ++c)
-                    o[c] = make_float4(fmaxf(sc[c].x, 0.f) * wv.x, fmaxf(sc[c].y, 0.f) * wv.y,
-                                       fmaxf(sc[c].z, 0.f) * wv.z, fmaxf(sc[c].w, 0.f) * wv.w);
-            }
-        }
-#pragma unroll
-        for (int c = 0; c < C; ++c) *reinterpret_cast<float4*>(sw + (r * C + c) * NS + 4 * n4) = o[c];
-    }
-    __syncthreads();
-
-    {   // f[r, c, l] = sum_n sw[r, c, n] * V[l, n]
-        const int r = threadIdx.x >> 3, g = threadIdx.x & 7;
-        if (r < rows) {
-            float acc[C][LPT];
-#pragma unroll
-            for (int c = 0; c < C; ++c)
-#pragma unroll
-                for (int j = 0; j < LPT; ++j) acc[c][j] = 0.f;
-            const float* vrow[LPT];
-#pragma unroll
-            for (int j = 0; j < LPT; ++j) vrow[j] = Vt + min(g + 8 * j, L - 1) * NS;
-            const float* srow = sw + r * C * NS;
-            for (int n = 0; n < N; n += 4) {
-                float4 sv[C], vv[LPT];
-#pragma unroll
-                for (int c = 0; c < C; ++c) sv[c] = *reinterpret_cast<const float4*>(srow + c * NS + n);
-#pragma unroll
-                for (int j = 0; j < LPT; ++j) vv[j] = *reinterpret_cast<const float4*>(vrow[j] + n);
-#pragma unroll
-                for (int c = 0; c < C; ++c)
-#pragma unroll
-                    for (int j = 0; j < LPT; ++j) {
-                        acc[c][j] = fmaf(sv[c].x, vv[j].x, acc[c][j]);
-                        acc[c][j] = fmaf(sv[c].y, vv[j].y, acc[c][j]);
-                        acc[c][j] = fmaf(sv[c].z, vv[j].z, acc[c][j]);
-                        acc[c][j] = fmaf(sv[c].w, vv[j].w, acc[c][j]);
-                    }
+                    o[c] = make_float4(fmaxf(sc[u][c].x, 0.f) * wv[u].x, fmaxf(sc[u][c].y, 0.f) * wv[u].y,
+                                       fmaxf(sc[u][c].z, 0.f) * wv[u].z, fmaxf(sc[u][c].w, 0.f) * wv[u].w);
             }
 #pragma unroll
-            for (int c = 0; c < C; ++c)
-#pragma unroll
-                for (int j = 0; j < LPT; ++j)
-                    if (g + 8 * j < L) fr[r * CL + c * L + g + 8 * j] = acc[c][j];
+            for (int c = 0; c < C; ++c) *reinterpret_cast<float4*>(sw + dst[u] + c * NS) = o[c];
         }
     }
+    ptx::cp_async_wait_all();
     __syncthreads();
 
-    // samples this tile owns: [k0*hop, (k0+nk)*hop), the last tile runs to T
+    // partial f[q][r, c, l] = sum over the q-th slice of n of sw[r, c, n] * V[l, n]
+    const int r = threadIdx.x & 31, q = threadIdx.x >> 5;
+    float acc[C][LT];
+#pragma unroll
+    for (int c = 0; c < C; ++c)
+#pragma unroll
+        for (int l = 0; l < LT; ++l) acc[c][l] = 0.f;
+    {
+        const int n4_lo = (q * N4) / kDecSlices, n4_hi = ((q + 1) * N4) / kDecSlices;
+        const float* srow = sw + r * C * NS;
+        for (int n4 = n4_lo; n4 < n4_hi; ++n4) {
+            float4 sv[C];
+#pragma unroll
+            for (int c = 0; c < C; ++c) sv[c] = *reinterpret_cast<const float4*>(srow + c * NS + 4 * n4);
+#pragma unroll
+            for (int l = 0; l < LT; ++l) {
+                const float4 vv = *reinterpret_cast<const float4*>(Vt + l * NS + 4 * n4);   // warp-wide broadcast
+#pragma unroll
+                for (int c = 0; c < C; ++c) {
+                    acc[c][l] = fmaf(sv[c].x, vv.x, acc[c][l]);
+                    acc[c][l] = fmaf(sv[c].y, vv.y, acc[c][l]);
+                    acc[c][l] = fmaf(sv[c].z, vv.z, acc[c][l]);
+                    acc[c][l] = fmaf(sv[c].w, vv.w, acc[c][l]);
+                }
+            }
+        }
+    }
+    __syncthreads();                           // every warp is done with sw: reuse it for the partials
+    float* part = sw;                          // [kDecSlices][kDecRows][C * LT + 1]  (+1: bank spread over rows)
+    constexpr int PR = C * LT + 1;
+#pragma unroll
+    for (int c = 0; c < C; ++c)
+#pragma unroll
+        for (int l = 0; l < LT; ++l) part[(q * kDecRows + r) * PR + c * LT + l] = acc[c][l];
+    __syncthreads();
+
+    // samples this tile owns: [k0*hop, (k0+nk)*hop), the last tile runs to T.  Each sample is the sum of
+    // the frames covering it (ascending), each frame value the sum of its slices (ascending).
     const bool last = (k0 + nk == K);
     const int t0 = k0 * hop;
     const int t1 = last ? T : (k0 + nk) * hop;
@@ -228,24 +249,41 @@ decoder_fwd_blocked_kernel(const float* __restrict__ score, const float* __restr
         int klo = (t - L + hop) / hop;  // ceil((t - L + 1) / hop) for t - L + 1 >= 0
         if (t - L + 1 <= 0) klo = 0;
         const int khi = min(t / hop, K - 1);
-        float acc = 0.f;
-        for (int k = klo; k <= khi; ++k) acc += fr[(k - (k0 - halo)) * CL + c * L + (t - k * hop)];
-        est[(static_cast<long long>(m) * C + c) * T + t] = acc;
+        float out = 0.f;
+        for (int k = klo; k <= khi; ++k) {
+            const float* pp = part + (k - (k0 - halo)) * PR + c * LT + (t - k * hop);
+            float f = 0.f;
+#pragma unroll
+            for (int s = 0; s < kDecSlices; ++s) f += pp[s * kDecRows * PR];
+            out += f;
+        }
+        est[(static_cast<long long>(m) * C + c) * T + t] = out;
     }
 }
 
-template <int C, int LPT>
+// shared memory of the row-blocked kernel: V, then the staged rows or (later, same region) the partial sums
+static size_t decoder_blocked_smem(int C, int LT, int N) {
+    const size_t rows = static_cast<size_t>(kDecRows) * C * (N + kDecPad);
+    const size_t part = static_cast<size_t>(kDecSlices) * kDecRows * (C * LT + 1);
+    return (static_cast<size_t>(LT) * (N + kDecPad) + (rows > part ? rows : part)) * sizeof(float);
+}
+
+template <int C, int LT>
 static int launch_decoder_blocked(const float* score, const float* w, const float* V, int M, int K, int N, int L, int T,
                                   int softmax, float* est, cudaStream_t stream) {
     const int hop = L / 2, halo = (L - 1) / hop;
-    const size_t smem = (static_cast<size_t>(L) * (N + kDecPad) + static_cast<size_t>(kDecRows) * C * (N + kDecPad) +
-                         static_cast<size_t>(kDecRows) * C * L) * sizeof(float);
-    cudaError_t e = cudaFuncSetAttribute(decoder_fwd_blocked_kernel<C, LPT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                         static_cast<int>(smem));
-    if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(decoder_fwd_blocked_kernel)");
+    const size_t smem = decoder_blocked_smem(C, LT, N);
+    static bool attr_done[kMaxDevices] = {};
+    bool& attr_set = attr_done[device_slot()];
+    if (!attr_set) {
+        cudaError_t e = cudaFuncSetAttribute(decoder_fwd_blocked_kernel<C, LT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                             200 * 1024);
+        if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(decoder_fwd_blocked_kernel)");
+        attr_set = true;
+    }
     dim3 grid(ceil_div(K, kDecRows - halo), M);
-    CTN_LAUNCH_PDL("decoder_fwd_blocked_kernel", static_cast<long long>(M) * K, decoder_fwd_blocked_kernel<C, LPT>, grid, 256, smem, stream, score, w, V, K, N, L, T, softmax, est);
-    CTN_LAUNCH_CHECK("decoder_fwd_blocked_kernel");
+    CTN_LAUNCH_PDL("decoder_fwd_blocked_kernel", static_cast<long long>(M) * K, decoder_fwd_blocked_kernel<C, LT>, grid,
+                   32 * kDecSlices, smem, stream, score, w, V, K, N, L, T, softmax, est);
     return CTN_OK;
 }
 
@@ -276,23 +314,22 @@ extern "C" int ctn_decoder_fwd(const float* score, const float* w, const float* 
     CTN_REQUIRE(T >= (K - 1) * hop + L, "ctn_decoder_fwd: T=%d shorter than the overlap-added length", T);
     const int halo = (L - 1) / hop;
     {
-        const size_t bsmem = (static_cast<size_t>(L) * (N + kDecPad) + static_cast<size_t>(kDecRows) * C * (N + kDecPad) +
-                              static_cast<size_t>(kDecRows) * C * L) * sizeof(float);
+        const int LT = L <= 16 ? 16 : (L <= 20 ? 20 : 24);
+        const size_t bsmem = decoder_blocked_smem(C, LT, N);
         auto al16 = [](const void* q) { return (reinterpret_cast<uintptr_t>(q) & 15) == 0; };
         if (C <= 3 && L <= 24 && N % 4 == 0 && halo < 8 && bsmem <= 200 * 1024 && al16(score) && al16(w) && al16(V)) {
             cudaStream_t st = static_cast<cudaStream_t>(stream);
             const int sm = mask_nonlinear == CTN_MASK_SOFTMAX;
-            const int lpt = ceil_div(L, 8);
 #define CTN_DEC(CC, LL) return launch_decoder_blocked<CC, LL>(score, w, V, M, K, N, L, T, sm, est, st)
-            if (C == 1 && lpt == 1) CTN_DEC(1, 1);
-            if (C == 1 && lpt == 2) CTN_DEC(1, 2);
-            if (C == 1 && lpt == 3) CTN_DEC(1, 3);
-            if (C == 2 && lpt == 1) CTN_DEC(2, 1);
-            if (C == 2 && lpt == 2) CTN_DEC(2, 2);
-            if (C == 2 && lpt == 3) CTN_DEC(2, 3);
-            if (C == 3 && lpt == 1) CTN_DEC(3, 1);
-            if (C == 3 && lpt == 2) CTN_DEC(3, 2);
-            if (C == 3 && lpt == 3) CTN_DEC(3, 3);
+            if (C == 1 && LT == 16) CTN_DEC(1, 16);
+            if (C == 1 && LT == 20) CTN_DEC(1, 20);
+            if (C == 1 && LT == 24) CTN_DEC(1, 24);
+            if (C == 2 && LT == 16) CTN_DEC(2, 16);
+            if (C == 2 && LT == 20) CTN_DEC(2, 20);
+            if (C == 2 && LT == 24) CTN_DEC(2, 24);
+            if (C == 3 && LT == 16) CTN_DEC(3, 16);
+            if (C == 3 && LT == 20) CTN_DEC(3, 20);
+            if (C == 3 && LT == 24) CTN_DEC(3, 24);
 #undef CTN_DEC
         }
     }
