@@ -467,27 +467,63 @@ struct ReduceParams {
     int src_stride[kMaxSeg];
     float* dst[kMaxSeg];
     int dst_stride[kMaxSeg];
-    int blk_off[kMaxSeg + 1];   // first CTA of each segment (prefix sum of ceil(len / kRedSpan))
+    int blk_off[kMaxSeg + 1];   // first CTA of each segment (prefix sum of ceil(len / red_span(n_part)))
 };
 
-// One CTA sums 128 outputs of one segment: thread (slice, col) owns columns col, col + 32, col + 64, col + 96
-// and sums the partials p = slice, slice + 8, ... of each (four independent loads per step, each warp
-// reading 128 contiguous bytes), then the 8 slices are added in a fixed order.  The grid is ONE
-// dimension over the (segment, column block) pairs that exist (blk_off = prefix sum of blocks per
-// segment): the 2-D grid (longest segment x segments) this replaces launched 45 000 CTAs per block of
-// the paper model, 37 000 of them for columns the short segments do not have (37 us per launch).
+// One launch sums the partials of up to kMaxSeg segments; the grid is ONE dimension over the (segment,
+// column block) pairs that exist (blk_off = prefix sum of blocks per segment) -- the 2-D grid (longest
+// segment x segments) this replaces launched 45 000 CTAs per block of the paper model, 37 000 of them
+// for columns the short segments do not have.  Two layouts of the 256 threads, chosen per segment:
+//  * wide (few partials, long rows: weight-gradient splits): 32 columns x 8 slices, four column groups
+//    per thread, i.e. 128 outputs per CTA, each warp reading 128 contiguous bytes per partial;
+//  * tall (more than kRedTall partials, short rows: per-CTA channel sums of the depthwise backward,
+//    up to ~2000 rows of 512): 8 columns x 32 slices, so the serial chain per thread is n_part / 32
+//    instead of n_part / 8 and a 512-column segment spreads over 64 CTAs instead of 4 (67 -> 20 us at
+//    batch 8 of BASELINE configs[4]).
+// Slices are added in a fixed order: deterministic.
+constexpr int kRedThreads = 256;
 constexpr int kRedCols = 32, kRedSlices = 8, kRedGroups = 4, kRedSpan = kRedCols * kRedGroups;
-__global__ void __launch_bounds__(kRedCols * kRedSlices) reduce_partials_kernel(const ReduceParams p) {
-    __shared__ float red[kRedSlices][kRedSpan];
+constexpr int kRedTall = 128, kRedTallCols = 8, kRedTallSlices = kRedThreads / kRedTallCols;
+__host__ __device__ inline int red_span(int n_part) { return n_part > kRedTall ? kRedTallCols : kRedSpan; }
+
+__global__ void __launch_bounds__(kRedThreads) reduce_partials_kernel(const ReduceParams p) {
+    __shared__ float red[kRedThreads * kRedGroups];
     int seg = 0;
     while (seg + 1 < p.nseg && static_cast<int>(blockIdx.x) >= p.blk_off[seg + 1]) ++seg;
-    const int col = threadIdx.x & (kRedCols - 1), slice = threadIdx.x / kRedCols;
-    const int i0 = (blockIdx.x - p.blk_off[seg]) * kRedSpan + col;
     const int len = p.len[seg];
     const int n_part = p.n_part[seg];
     const long long ps = p.part_stride[seg];
     const int sstr = p.src_stride[seg];
     const float* base = p.part[seg] + p.src_off[seg];
+    const int blk = blockIdx.x - p.blk_off[seg];
+    if (n_part > kRedTall) {
+        const int col = threadIdx.x & (kRedTallCols - 1), slice = threadIdx.x / kRedTallCols;
+        const int i = blk * kRedTallCols + col;
+        float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
+        if (i < len) {
+            const float* src = base + static_cast<long long>(i) * sstr;
+            int q = slice;
+            for (; q + 3 * kRedTallSlices < n_part; q += 4 * kRedTallSlices) {
+                s0 += src[(q + 0 * kRedTallSlices) * ps];
+                s1 += src[(q + 1 * kRedTallSlices) * ps];
+                s2 += src[(q + 2 * kRedTallSlices) * ps];
+                s3 += src[(q + 3 * kRedTallSlices) * ps];
+            }
+            for (; q < n_part; q += kRedTallSlices) s0 += src[q * ps];
+        }
+        red[slice * kRedTallCols + col] = (s0 + s1) + (s2 + s3);
+        __syncthreads();
+        if (threadIdx.x < kRedTallCols && i < len) {
+            float t = 0.f;
+#pragma unroll
+            for (int k = 0; k < kRedTallSlices; ++k) t += red[k * kRedTallCols + threadIdx.x];
+            float* d = p.dst[seg] + static_cast<long long>(i) * p.dst_stride[seg];
+            *d = p.accumulate ? *d + t : t;
+        }
+        return;
+    }
+    const int col = threadIdx.x & (kRedCols - 1), slice = threadIdx.x / kRedCols;
+    const int i0 = blk * kRedSpan + col;
     float s[kRedGroups];
     const float* src[kRedGroups];
     bool ok[kRedGroups];
@@ -506,14 +542,14 @@ __global__ void __launch_bounds__(kRedCols * kRedSlices) reduce_partials_kernel(
         for (int g = 0; g < kRedGroups; ++g) s[g] += v[g];
     }
 #pragma unroll
-    for (int g = 0; g < kRedGroups; ++g) red[slice][g * kRedCols + col] = s[g];
+    for (int g = 0; g < kRedGroups; ++g) red[slice * kRedSpan + g * kRedCols + col] = s[g];
     __syncthreads();
     if (threadIdx.x < kRedSpan) {
-        const int i = (blockIdx.x - p.blk_off[seg]) * kRedSpan + threadIdx.x;
+        const int i = blk * kRedSpan + threadIdx.x;
         if (i < len) {
             float t = 0.f;
 #pragma unroll
-            for (int k = 0; k < kRedSlices; ++k) t += red[k][threadIdx.x];
+            for (int k = 0; k < kRedSlices; ++k) t += red[k * kRedSpan + threadIdx.x];
             float* d = p.dst[seg] + static_cast<long long>(i) * p.dst_stride[seg];
             *d = p.accumulate ? *d + t : t;
         }
@@ -848,10 +884,10 @@ extern "C" int ctn_reduce_partials(const ctn_reduce_args* args, void* stream) {
         p.src_off[s] = a.src_off[s], p.len[s] = a.len[s], p.src_stride[s] = a.src_stride[s] ? a.src_stride[s] : 1;
         p.dst[s] = a.dst[s], p.dst_stride[s] = a.dst_stride[s] ? a.dst_stride[s] : 1;
         p.blk_off[s] = blocks;
-        blocks += ceil_div(a.len[s], kRedSpan);
+        blocks += ceil_div(a.len[s], red_span(p.n_part[s]));
     }
     p.blk_off[a.nseg] = blocks;
-    reduce_partials_kernel<<<blocks, kRedCols * kRedSlices, 0, static_cast<cudaStream_t>(stream)>>>(p);
+    reduce_partials_kernel<<<blocks, kRedThreads, 0, static_cast<cudaStream_t>(stream)>>>(p);
     CTN_LAUNCH_CHECK("reduce_partials_kernel");
     return CTN_OK;
 }

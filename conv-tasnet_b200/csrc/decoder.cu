@@ -121,25 +121,35 @@ constexpr int kDecSlices = 8;    // n-range slices = warps per CTA
 template <int C, int LT>
 __global__ void __launch_bounds__(32 * kDecSlices)
 decoder_fwd_blocked_kernel(const float* __restrict__ score, const float* __restrict__ w, const float* __restrict__ V,
-                           int K, int N, int L, int T, int softmax, float* __restrict__ est) {
+                           int K, int N, int Np, int L, int T, int softmax, float* __restrict__ est) {
+    // Np = channels staged per pass (divides N, multiple of 4): wide models (N = 512, C = 3) walk the n
+    // range in several passes so that the staged rows fit in shared memory; accumulators stay in registers
     ptx::grid_dep_sync();   // PDL: predecessor complete; let the next kernel be scheduled
     extern __shared__ float dec_smem[];
     const int hop = L / 2;
     const int halo = (L - 1) / hop;
     const int tile = kDecRows - halo;          // frames this CTA owns
-    const int NS = N + kDecPad;
+    const int NS = Np + kDecPad;
     float* Vt = dec_smem;                      // [LT][NS]   (V is [L, N] row-major already; rows >= L are zero)
     float* sw = Vt + LT * NS;                  // [kDecRows][C][NS]; later reused as part[kDecSlices][kDecRows][C][LT]
     const int m = blockIdx.y;
     const int k0 = blockIdx.x * tile;          // first owned frame
     const int nk = min(tile, K - k0);
     const int rows = halo + nk;                // staged frames: k0 - halo .. k0 + nk - 1
-    const int N4 = N >> 2;
+    const int N4 = Np >> 2;
+    const int r = threadIdx.x & 31, q = threadIdx.x >> 5;
+    float acc[C][LT];
+#pragma unroll
+    for (int c = 0; c < C; ++c)
+#pragma unroll
+        for (int l = 0; l < LT; ++l) acc[c][l] = 0.f;
+    for (int nb = 0; nb < N; nb += Np) {       // one pass per Np channels
+    if (nb > 0) __syncthreads();               // the previous pass is done with Vt / sw
     // basis -> shared memory with asynchronous copies, in flight together with the row loads below
     for (int i = threadIdx.x; i < LT * N4; i += blockDim.x) {
         const int l = i / N4, n4 = i - l * N4;
         if (l < L)
-            ptx::cp_async_16(Vt + l * NS + 4 * n4, V + l * N + 4 * n4);
+            ptx::cp_async_16(Vt + l * NS + 4 * n4, V + l * N + nb + 4 * n4);
         else
             *reinterpret_cast<float4*>(Vt + l * NS + 4 * n4) = make_float4(0.f, 0.f, 0.f, 0.f);
     }
@@ -161,10 +171,10 @@ decoder_fwd_blocked_kernel(const float* __restrict__ score, const float* __restr
             for (int c = 0; c < C; ++c) sc[u][c] = make_float4(0.f, 0.f, 0.f, 0.f);
             if (live) {
                 const long long grow = static_cast<long long>(m) * K + k;
-                wv[u] = *reinterpret_cast<const float4*>(w + grow * N + 4 * n4);
+                wv[u] = *reinterpret_cast<const float4*>(w + grow * N + nb + 4 * n4);
 #pragma unroll
                 for (int c = 0; c < C; ++c)
-                    sc[u][c] = *reinterpret_cast<const float4*>(score + grow * (static_cast<long long>(C) * N) + c * N + 4 * n4);
+                    sc[u][c] = *reinterpret_cast<const float4*>(score + grow * (static_cast<long long>(C) * N) + c * N + nb + 4 * n4);
             }
         }
 #pragma unroll
@@ -203,13 +213,7 @@ decoder_fwd_blocked_kernel(const float* __restrict__ score, const float* __restr
     ptx::cp_async_wait_all();
     __syncthreads();
 
-    // partial f[q][r, c, l] = sum over the q-th slice of n of sw[r, c, n] * V[l, n]
-    const int r = threadIdx.x & 31, q = threadIdx.x >> 5;
-    float acc[C][LT];
-#pragma unroll
-    for (int c = 0; c < C; ++c)
-#pragma unroll
-        for (int l = 0; l < LT; ++l) acc[c][l] = 0.f;
+    // partial f[q][r, c, l] += sum over the q-th slice of this pass's n of sw[r, c, n] * V[l, n]
     {
         const int n4_lo = (q * N4) / kDecSlices, n4_hi = ((q + 1) * N4) / kDecSlices;
         const float* srow = sw + r * C * NS;
@@ -230,6 +234,7 @@ decoder_fwd_blocked_kernel(const float* __restrict__ score, const float* __restr
             }
         }
     }
+    }                                          // passes
     __syncthreads();                           // every warp is done with sw: reuse it for the partials
     float* part = sw;                          // [kDecSlices][kDecRows][C * LT + 1]  (+1: bank spread over rows)
     constexpr int PR = C * LT + 1;
@@ -262,17 +267,25 @@ decoder_fwd_blocked_kernel(const float* __restrict__ score, const float* __restr
 }
 
 // shared memory of the row-blocked kernel: V, then the staged rows or (later, same region) the partial sums
-static size_t decoder_blocked_smem(int C, int LT, int N) {
-    const size_t rows = static_cast<size_t>(kDecRows) * C * (N + kDecPad);
+static size_t decoder_blocked_smem(int C, int LT, int Np) {
+    const size_t rows = static_cast<size_t>(kDecRows) * C * (Np + kDecPad);
     const size_t part = static_cast<size_t>(kDecSlices) * kDecRows * (C * LT + 1);
-    return (static_cast<size_t>(LT) * (N + kDecPad) + (rows > part ? rows : part)) * sizeof(float);
+    return (static_cast<size_t>(LT) * (Np + kDecPad) + (rows > part ? rows : part)) * sizeof(float);
+}
+// channels per pass: the whole row if it fits in ~100 KB (two CTAs per SM), else the largest power-of-two
+// fraction of N (>= 32 channels, multiple of 4) that does
+static int decoder_blocked_np(int C, int LT, int N) {
+    int Np = N;
+    while (decoder_blocked_smem(C, LT, Np) > 100 * 1024 && Np % 8 == 0 && Np / 2 >= 32) Np /= 2;
+    return Np;
 }
 
 template <int C, int LT>
 static int launch_decoder_blocked(const float* score, const float* w, const float* V, int M, int K, int N, int L, int T,
                                   int softmax, float* est, cudaStream_t stream) {
     const int hop = L / 2, halo = (L - 1) / hop;
-    const size_t smem = decoder_blocked_smem(C, LT, N);
+    const int Np = decoder_blocked_np(C, LT, N);
+    const size_t smem = decoder_blocked_smem(C, LT, Np);
     static bool attr_done[kMaxDevices] = {};
     bool& attr_set = attr_done[device_slot()];
     if (!attr_set) {
@@ -283,7 +296,7 @@ static int launch_decoder_blocked(const float* score, const float* w, const floa
     }
     dim3 grid(ceil_div(K, kDecRows - halo), M);
     CTN_LAUNCH_PDL("decoder_fwd_blocked_kernel", static_cast<long long>(M) * K, decoder_fwd_blocked_kernel<C, LT>, grid,
-                   32 * kDecSlices, smem, stream, score, w, V, K, N, L, T, softmax, est);
+                   32 * kDecSlices, smem, stream, score, w, V, K, N, Np, L, T, softmax, est);
     return CTN_OK;
 }
 
@@ -315,7 +328,7 @@ extern "C" int ctn_decoder_fwd(const float* score, const float* w, const float* 
     const int halo = (L - 1) / hop;
     {
         const int LT = L <= 16 ? 16 : (L <= 20 ? 20 : 24);
-        const size_t bsmem = decoder_blocked_smem(C, LT, N);
+        const size_t bsmem = decoder_blocked_smem(C, LT, decoder_blocked_np(C, LT, N));
         auto al16 = [](const void* q) { return (reinterpret_cast<uintptr_t>(q) & 15) == 0; };
         if (C <= 3 && L <= 24 && N % 4 == 0 && halo < 8 && bsmem <= 200 * 1024 && al16(score) && al16(w) && al16(V)) {
             cudaStream_t st = static_cast<cudaStream_t>(stream);
