@@ -103,16 +103,30 @@ class ConvTasNet(nn.Module):
 
     def _params(self):
         """{state_dict key: tensor} of the parameters (and BatchNorm running statistics) in registration
-        order.  Resolved attribute by attribute rather than through named_parameters(): the replicas that
+        order.  The owning container and leaf name of every key are resolved once; a forward then costs
+        one dict lookup per tensor (the single-utterance latency is host-bound).  The replicas that
         torch.nn.DataParallel builds (train.py:121, separate.py:45) hold their parameter copies as plain
-        attributes, not in _parameters."""
-        out = {}
-        for key in self._keys + self._buffer_keys:
-            node = self
-            for part in key.split("."):
-                node = getattr(node, part)
-            out[key] = node
-        return out
+        attributes of replicated containers, not in _parameters, so they walk the tree by attribute."""
+        if getattr(self, "_is_replica", False):
+            out = {}
+            for key in self._keys + self._buffer_keys:
+                node = self
+                for part in key.split("."):
+                    node = getattr(node, part)
+                out[key] = node
+            return out
+        slots = self.__dict__.get("_param_slots")
+        if slots is None:
+            slots = []
+            for key in self._keys + self._buffer_keys:
+                node = self
+                parts = key.split(".")
+                for part in parts[:-1]:
+                    node = node._modules[part]
+                store = node._parameters if parts[-1] in node._parameters else node._buffers
+                slots.append((key, store, parts[-1]))
+            self.__dict__["_param_slots"] = slots
+        return {key: store[leaf] for key, store, leaf in slots}
 
     def engine(self):
         """The per-module kernel orchestrator (workspaces, prepared weights, CUDA graphs)."""
@@ -137,7 +151,7 @@ class ConvTasNet(nn.Module):
         the GPU and every estimate back with blocking copies): mixture is a CPU float32 [M, T] tensor,
         ideally pinned; returns a pinned CPU [M, C, T] tensor (or fills `out`).  Host-device copies of
         neighbouring micro-batches overlap the kernels.  The call returns after the result has arrived."""
-        params = {k: p.detach() for k, p in self._params().items()}
+        params = self._params()
         if is_bn(self.norm_type) and self.training:
             raise NotImplementedError("norm_type=%r (BatchNorm1d) is implemented for inference only" % (self.norm_type,))
         dev = next(iter(params.values())).device
@@ -175,11 +189,13 @@ class ConvTasNet(nn.Module):
         if needs_grad:
             from ctn_b200 import _autograd
             return _autograd.separate(self, mixture, params)
-        return self.engine().forward(mixture, {k: p.detach() for k, p in params.items()})
+        # the engine only takes addresses and version counters of the parameters (under no_grad): no detach
+        return self.engine().forward(mixture, params)
 
     def __getstate__(self):
         state = self.__dict__.copy()
         state["_engine"] = None  # workspaces are per process / device
+        state.pop("_param_slots", None)
         state.pop("_train_engine", None)
         return state
 
