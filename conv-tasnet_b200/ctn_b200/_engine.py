@@ -392,6 +392,8 @@ class SeparationEngine:
             out = torch.empty(M, cfg["C"], T, dtype=torch.float32).pin_memory()
         elif out.is_cuda or tuple(out.shape) != (M, cfg["C"], T) or out.dtype != torch.float32 or not out.is_contiguous():
             raise RuntimeError("out must be a contiguous CPU float32 [M, C, T] tensor")
+        if M == 0:
+            return out
         with torch.cuda.device(device):
             params = aligned_params(self._staged, params, device)
             mb = max(1, int(self.micro_batch))
@@ -444,6 +446,8 @@ class SeparationEngine:
             raise RuntimeError("Calculated output size is too small: T=%d < L=%d" % (T, cfg["L"]))
         device = mixture.device
         out = torch.empty(M, cfg["C"], T, dtype=torch.float32, device=device)
+        if M == 0:      # empty batch: the reference's modules return an empty [0, C, T] tensor
+            return out
         with torch.cuda.device(device):
             params = aligned_params(self._staged, params, device)
             mb = max(1, int(self.micro_batch))

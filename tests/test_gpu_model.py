@@ -219,6 +219,8 @@ def test_error_conventions():
         bn.train()(torch.zeros(1, 100, device=DEV))
     m = conv_tasnet.ConvTasNet(8, 4, 8, 8, 3, 1, 1, 2).to(DEV).eval()
     with torch.no_grad():
+        assert tuple(m(torch.zeros(0, 100, device=DEV)).shape) == (0, 2, 100)     # empty batch, as the reference
+        assert tuple(m.separate(torch.zeros(0, 100)).shape) == (0, 2, 100)
         with pytest.raises(RuntimeError):
             m(torch.zeros(1, 3, device=DEV))      # T < L
         with pytest.raises(RuntimeError):
