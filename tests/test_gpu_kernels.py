@@ -16,6 +16,8 @@ from oracle import convtasnet_oracle as O
 pytestmark = pytest.mark.gpu
 
 if torch.cuda.is_available():
+    import ctypes as C
+
     import kernels as Kn
     from ctn_b200 import _native as nat
 
@@ -329,3 +331,59 @@ def test_overlap_and_add_matches_reference_fixtures():
             assert torch.equal(out, ref)       # two commutative addends onto zero: bit-identical
         else:
             assert torch.allclose(out, ref, atol=1e-6)
+
+
+# ------------------------------------------------- partial reduction, BatchNorm fold
+def test_reduce_partials_wide_tall_and_strided_segments():
+    """ctn_reduce_partials: one launch over segments of both layouts -- wide (37 partials x 70 001 outputs,
+    the weight-gradient shape), tall (1 500 and 129 partials x 512 / 7 outputs, the channel sums of the
+    depthwise backward), strided source / destination (the [H, 1, P] depthwise weight) -- and accumulation."""
+    g = torch.Generator().manual_seed(60)
+    wide = torch.randn(37, 70001, generator=g).to(DEV)
+    tall = torch.randn(1500, 7 * 512, generator=g).to(DEV)
+    tall2 = torch.randn(129, 40, generator=g).to(DEV)
+    P = 3
+    d_wide = torch.zeros(70001, device=DEV)
+    d_t0 = torch.zeros(512, device=DEV)
+    d_wd = torch.zeros(512, P, device=DEV)
+    d_s = torch.zeros(7, device=DEV)
+    r = nat.ReduceArgs()
+    segs = [(wide, 37, 70001, 0, 70001, 1, d_wide.data_ptr(), 1),
+            (tall, 1500, 7 * 512, 2 * 512, 512, 1, d_t0.data_ptr(), 1)]
+    segs += [(tall, 1500, 7 * 512, (4 + j) * 512, 512, 1, d_wd.data_ptr() + 4 * j, P) for j in range(P)]
+    segs.append((tall2, 129, 40, 3, 7, 5, d_s.data_ptr(), 1))          # source stride 5
+    r.nseg = len(segs)
+    for i, (part, n_part, ps, so, ln, ss, dp, ds) in enumerate(segs):
+        r.seg_part[i], r.seg_n_part[i], r.seg_part_stride[i] = part.data_ptr(), n_part, ps
+        r.src_off[i], r.len[i], r.src_stride[i], r.dst[i], r.dst_stride[i] = so, ln, ss, dp, ds
+    for accumulate in (0, 1):
+        r.accumulate = accumulate
+        nat.check(nat.lib().ctn_reduce_partials(C.byref(r), nat.stream()))
+        f = 1.0 + accumulate
+        assert rel_l2(d_wide, f * wide.double().sum(0)) < 1e-6
+        assert rel_l2(d_t0, f * tall.double().sum(0)[2 * 512:3 * 512]) < 1e-6
+        for j in range(P):
+            assert rel_l2(d_wd[:, j], f * tall.double().sum(0)[(4 + j) * 512:(5 + j) * 512]) < 1e-6
+        assert rel_l2(d_s, f * tall2.double().sum(0)[3:3 + 7 * 5:5]) < 1e-6
+
+
+def test_bn_fold():
+    """ctn_bn_fold against nn.BatchNorm1d in eval mode (conv_tasnet.py:300-303)."""
+    Cn = 515
+    bn = torch.nn.BatchNorm1d(Cn).to(DEV)
+    g = torch.Generator().manual_seed(61)
+    with torch.no_grad():
+        bn.weight.copy_(1 + 0.3 * torch.randn(Cn, generator=g))
+        bn.bias.copy_(0.2 * torch.randn(Cn, generator=g))
+        bn.running_mean.copy_(torch.randn(Cn, generator=g))
+        bn.running_var.copy_(0.1 + torch.rand(Cn, generator=g))
+    bn.eval()
+    scale, shift = torch.empty(Cn, device=DEV), torch.empty(Cn, device=DEV)
+    nat.check(nat.lib().ctn_bn_fold(bn.weight.data_ptr(), bn.bias.data_ptr(), bn.running_mean.data_ptr(),
+                                    bn.running_var.data_ptr(), bn.eps, Cn, scale.data_ptr(), shift.data_ptr(),
+                                    nat.stream()))
+    x = torch.randn(3, Cn, 50, generator=g).to(DEV)
+    with torch.no_grad():
+        want = bn(x)
+    got = x * scale[None, :, None] + shift[None, :, None]
+    assert rel_l2(got, want) < 1e-6
