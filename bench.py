@@ -265,7 +265,7 @@ def run_b200(args):
         # launch from the committed ncu --set full capture (valid at the captured micro-batch only).
         traffic = {}
         try:
-            with open(os.path.join(ROOT, "profiles", "r1", "ncu_traffic_v6.json")) as f:
+            with open(os.path.join(ROOT, "profiles", "r1", "ncu_traffic_v7.json")) as f:
                 tj = json.load(f)
             if tj.get("micro_batch") == mb:
                 traffic = {k: v["traffic_bytes"] for k, v in tj["kernels"].items()}
@@ -300,7 +300,7 @@ def run_b200(args):
         dom = max(roofs, key=lambda k: roofs[k]["share_of_step"])
         roof = dict(roofs[dom])
         roof["how"] = ("dominant kernel by share of the step; CUDA events around every launch of one %d-utterance "
-                       "micro-batch pass, 3 repeats; traffic from profiles/r1/ncu_traffic_v6.json" % mb)
+                       "micro-batch pass, 3 repeats; traffic from profiles/r1/ncu_traffic_v7.json" % mb)
         roof["all_kernels"] = roofs
 
     train = None
