@@ -166,3 +166,35 @@ def test_host_to_host_separation_equals_device_forward():
         assert model.separate(src, out=out) is out and torch.equal(out, want)
     with pytest.raises(RuntimeError):
         model.separate(mix.cuda())
+
+
+def test_full_size_config4_bulk_separation_is_batch_independent():
+    """BASELINE configs[3] at full size (512 x 4 s, paper configuration) through the host-to-host call:
+    utterance m of the bulk result equals the same utterance separated alone, whatever micro-batch it
+    fell into.  With the unfused kernels that is bit-exact.  The fused depthwise + pointwise kernel hands
+    its k-blocks to producer groups round-robin ACROSS the tiles of a CTA pair, so from 6 utterances per
+    micro-batch on (a pair owns more than one tile) the float partial sums of the gLN statistics are
+    grouped differently than for a lone utterance: deterministic, and equal to rounding (~1e-5, the size
+    of the error against the fp64 oracle; tolerance 1e-3)."""
+    import conv_tasnet
+    from oracle import convtasnet_oracle as O
+    cfg = dict(N=256, L=20, B=256, H=512, P=3, X=8, R=4, C=2, norm_type="gLN", causal=False, mask_nonlinear="relu")
+    model = conv_tasnet.ConvTasNet(**cfg)
+    model.load_state_dict(O.random_params(*(cfg[k] for k in "NLBHPXRC"), cfg["causal"], seed=1234))
+    model = model.to("cuda").eval()
+    eng = model.engine()
+    g = torch.Generator().manual_seed(2025)
+    mix = (0.1 * torch.randn(512, 32000, generator=g)).pin_memory()
+    for fuse, tol in ((1 << 30, 5e-5), (0, 0.0)):
+        eng.fuse_max_dilation = fuse
+        eng.micro_batch, eng.use_graph = 64, True
+        est = model.separate(mix)
+        assert tuple(est.shape) == (512, 2, 32000) and bool(torch.isfinite(est).all())
+        again = model.separate(mix)
+        assert torch.equal(est, again)                      # run-to-run: bit-identical either way
+        eng.use_graph = False
+        with torch.no_grad():
+            for m in (0, 63, 64, 300, 511):
+                alone = model(mix[m:m + 1].cuda()).cpu()[0]
+                err = float((alone.double() - est[m].double()).norm() / alone.double().norm())
+                assert err <= tol, (fuse, m, err)

@@ -103,3 +103,18 @@ def test_stream_paper_causal_config(chunk):
     if chunk == 256:
         ref = O.forward(mix[None].double(), {k: v.to(DEV).double() for k, v in p32.items()}, cfg)[0]
         assert rel_l2(got, ref) < 1e-3
+
+
+def test_stream_full_size_config3():
+    """BASELINE configs[2] at full size: one 60 s stream (480 000 samples, 47 999 frames) separated in
+    1.28 s chunks is bit-identical to the whole-stream forward."""
+    cfg = dict(N=256, L=20, B=256, H=512, P=3, X=8, R=4, C=2, norm_type="cLN", causal=True, mask_nonlinear="relu")
+    p32 = O.random_params(*(cfg[k] for k in "NLBHPXRC"), cfg["causal"], seed=1234)
+    model = _build(cfg, p32)
+    g = torch.Generator().manual_seed(10)
+    mix = (0.1 * torch.randn(480000, generator=g)).to(DEV)
+    with torch.no_grad():
+        whole = model(mix[None])[0]
+    sep = model.streaming(chunk_frames=1024)
+    got = _stream(sep, mix, [100000, 200000, 7])
+    assert got.shape == whole.shape and torch.equal(got, whole)
