@@ -117,3 +117,35 @@ extern "C" int ctn_bn_fold(const float* weight, const float* bias, const float* 
     CTN_LAUNCH_CHECK("bn_fold_kernel");
     return CTN_OK;
 }
+
+// Table-driven device-to-device copies in ONE launch: the state shift of the streaming separator
+// (ctn_b200/_stream.py) moves ~70 small row ranges per chunk, which as individual memcpy nodes cost
+// more than the data movement.  Source and destination ranges of one table must not overlap each other.
+namespace ctn {
+__global__ void __launch_bounds__(256) copy_table_kernel(const ctn_copy_item* __restrict__ items) {
+    const ctn_copy_item it = items[blockIdx.y];
+    const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+    const long long t = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+    const uintptr_t both = reinterpret_cast<uintptr_t>(it.dst) | reinterpret_cast<uintptr_t>(it.src) |
+                           static_cast<uintptr_t>(it.bytes);
+    if ((both & 15) == 0) {
+        const uint4* s = static_cast<const uint4*>(it.src);
+        uint4* d = static_cast<uint4*>(it.dst);
+        for (long long i = t; i < it.bytes / 16; i += stride) d[i] = s[i];
+    } else {   // 4-byte granularity (float buffers)
+        const uint32_t* s = static_cast<const uint32_t*>(it.src);
+        uint32_t* d = static_cast<uint32_t*>(it.dst);
+        for (long long i = t; i < it.bytes / 4; i += stride) d[i] = s[i];
+    }
+}
+}  // namespace ctn
+
+extern "C" int ctn_copy_table(const ctn_copy_item* items_dev, int n_items, long long max_bytes, void* stream) {
+    using namespace ctn;
+    CTN_REQUIRE(items_dev != nullptr && n_items > 0 && n_items <= 65535 && max_bytes > 0, "ctn_copy_table: bad arguments");
+    int bx = static_cast<int>((max_bytes / 16 + 255) / 256);
+    bx = bx < 1 ? 1 : (bx > 64 ? 64 : bx);
+    copy_table_kernel<<<dim3(bx, n_items), 256, 0, static_cast<cudaStream_t>(stream)>>>(items_dev);
+    CTN_LAUNCH_CHECK("copy_table_kernel");
+    return CTN_OK;
+}

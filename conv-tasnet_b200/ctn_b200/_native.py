@@ -79,6 +79,34 @@ class BwdDwArgs(C.Structure):
     ]
 
 
+class CopyItem(C.Structure):
+    """struct ctn_copy_item"""
+    _fields_ = [("dst", _vp), ("src", _vp), ("bytes", C.c_longlong)]
+
+
+class CopyTable:
+    """Device-resident table of ctn_copy_item for ctn_copy_table (one launch per run)."""
+
+    def __init__(self, device, pairs):
+        """pairs: list of (dst tensor view, src tensor view), both contiguous, same number of bytes."""
+        items = []
+        self.max_bytes = 0
+        for dst, src in pairs:
+            assert dst.is_contiguous() and src.is_contiguous()
+            n = dst.numel() * dst.element_size()
+            assert n == src.numel() * src.element_size() and n % 4 == 0
+            it = CopyItem()
+            it.dst, it.src, it.bytes = dst.data_ptr(), src.data_ptr(), n
+            items.append(it)
+            self.max_bytes = max(self.max_bytes, n)
+        self.n = len(items)
+        arr = (CopyItem * self.n)(*items)
+        self.dev = torch.frombuffer(bytearray(bytes(arr)), dtype=torch.uint8).to(device)
+
+    def run(self):
+        check(lib().ctn_copy_table(self.dev.data_ptr(), self.n, self.max_bytes, stream()))
+
+
 class PrepItem(C.Structure):
     """struct ctn_prep_item"""
     _fields_ = [("W", _vp), ("gamma", _vp), ("beta", _vp), ("w_hi", _vp), ("w_lo", _vp), ("col_g", _vp),
@@ -167,6 +195,7 @@ _SIGNATURES = {
                                     _vp, _vp, _vp]),
     "ctn_pit_reorder": (C.c_int, [_vp, _vp, _vp, C.c_int, C.c_int, C.c_int, _vp, _vp]),
     "ctn_bn_fold": (C.c_int, [_vp, _vp, _vp, _vp, C.c_float, C.c_int, _vp, _vp, _vp]),
+    "ctn_copy_table": (C.c_int, [_vp, C.c_int, C.c_longlong, _vp]),
     "ctn_sisnri": (C.c_int, [_vp, _vp, _vp, _vp, C.c_int, C.c_int, C.c_int, _vp, _vp, _vp]),
     "ctn_pit_sisnr_bwd": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, C.c_int, C.c_int, C.c_int, _vp, _vp]),
 }

@@ -18,7 +18,7 @@ at a row offset (they are pointwise in time), the depthwise kernel runs over
 ctx_b + chunk rows and its first ctx_b output rows are never read.  The first chunk of a
 stream has no context: the reference zero-pads the NORMALISED depthwise input, so the
 first chunk runs the depthwise kernel on the chunk rows alone.  Steady-state chunks are
-one CUDA graph: state shifts (device-to-device copies), encoder, 3 kernels per block,
+one CUDA graph: state shift (two table-driven copy launches), encoder, 3 kernels per block,
 mask GEMM, decoder.
 """
 import ctypes as C
@@ -91,9 +91,6 @@ class StreamingSeparator:
         self.est_first = torch.empty(C_, (Kc + 1) * hop, **f32)
         self.est = torch.empty(C_, (Kc + 2) * hop, **f32)
         self.one = torch.ones(1, **f32)
-        # scratch for state shifts whose source and destination rows overlap (chunk shorter than the context)
-        self.tmp_a = torch.empty(cmax, H, **f32)
-        self.tmp_s = torch.empty(cmax, self.P1, 2, **f32)
 
     def _gemm(self, rows, keep, **kw):
         g = nat.GemmArgs()
@@ -182,6 +179,7 @@ class StreamingSeparator:
         self.body_steady, self._keep2 = self._body(max(self.ctx))
         self.dec_first = self._decoder(True, Kc, (Kc + 1) * hop, self.est_first)
         self.dec_steady = self._decoder(False, Kc + 1, (Kc + 2) * hop, self.est)
+        self._build_shift()
         self.graph_steady = None
         self._steady_warm = False
 
@@ -195,22 +193,33 @@ class StreamingSeparator:
         self.consumed = 0       # samples of the stream copied into chunks so far
         self.emitted = 0        # samples of the stream returned so far
 
-    def _shift_state(self):
-        """Moves what the next chunk needs from the end of the previous chunk's buffers to their
-        fronts: one hop of mixture, one frame of encoder output and score, ctx_b rows per block."""
+    def _build_shift(self):
+        """Copy tables (ctn_copy_table: one launch each) that move what the next chunk needs from the end
+        of the previous chunk's buffers to their fronts: one hop of mixture, one frame of encoder output
+        and score, ctx_b rows of conv1x1 output and statistics per block.  Where the chunk is shorter
+        than a block's context the two ranges overlap, so those go through a scratch buffer: table 1 =
+        direct moves + moves into scratch, table 2 = moves out of scratch + the chunk's new samples (which
+        land where table 1 read the old hop from)."""
         Kc, hop = self.Kc, self.hop
-        self.inbuf[:hop].copy_(self.inbuf[Kc * hop:])
-        self.w[0].copy_(self.w[Kc])
-        self.score[0].copy_(self.score[Kc])
+        t1 = [(self.inbuf[:hop], self.inbuf[Kc * hop:]), (self.w[0], self.w[Kc]), (self.score[0], self.score[Kc])]
+        t2 = [(self.inbuf[hop:], self.new)]
+        self._scratch = []
         for ab, sb, c in zip(self.a, self.stat1, self.ctx):
-            if Kc >= c:
-                ab[:c].copy_(ab[Kc:])
-                sb[:c].copy_(sb[Kc:])
-            else:
-                self.tmp_a[:c].copy_(ab[Kc:])
-                ab[:c].copy_(self.tmp_a[:c])
-                self.tmp_s[:c].copy_(sb[Kc:])
-                sb[:c].copy_(self.tmp_s[:c])
+            for buf in (ab, sb):
+                if Kc >= c:
+                    t1.append((buf[:c], buf[Kc:]))
+                else:
+                    tmp = torch.empty_like(buf[:c])
+                    self._scratch.append(tmp)
+                    t1.append((tmp, buf[Kc:]))
+                    t2.append((buf[:c], tmp))
+        self.shift1 = nat.CopyTable(self.device, t1)
+        self.shift2 = nat.CopyTable(self.device, t2)
+
+    def _shift_state(self):
+        self.shift1.run()
+        self.shift2.run()
+        self.launches += 2
 
     def _launch(self, calls):
         s = nat.stream()
@@ -223,7 +232,6 @@ class StreamingSeparator:
 
     def _chunk_steady(self, with_decoder=True):
         self._shift_state()
-        self.inbuf[self.hop:].copy_(self.new)
         body = self.body_steady
         if self.hist < max(self.ctx):     # ramp-up: some block's context still reaches before the stream start
             body, self._keep3 = self._body(self.hist)
@@ -252,7 +260,7 @@ class StreamingSeparator:
             self.launches = n
             self.graph_steady = g
         self.graph_steady.replay()
-        self.launches += len(self.body_steady) + 1
+        self.launches += len(self.body_steady) + 3       # two copy tables, the body, the decoder
 
     def _take(self, n, dst):
         """Moves the next n fed samples into dst[:n] (device-to-device copies)."""

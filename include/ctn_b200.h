@@ -373,6 +373,17 @@ int ctn_clip_adam(const ctn_opt_chunk* chunks_dev, int n_chunks, double* partial
 int ctn_bn_fold(const float* weight, const float* bias, const float* running_mean, const float* running_var, float eps,
                 int C, float* scale, float* shift, void* stream);
 
+/* Table-driven device-to-device copies in one launch (state shift of the streaming separator,
+ * ctn_b200/_stream.py: the frames a causal model's next chunk reaches back to).  items_dev: DEVICE array;
+ * bytes must be a multiple of 4 and the pointers 4-byte aligned (16-byte aligned ranges move as 128-bit
+ * words); the ranges of one table must not overlap one another.  max_bytes = largest item (grid sizing). */
+typedef struct ctn_copy_item {
+    void* dst;
+    const void* src;
+    long long bytes;
+} ctn_copy_item;
+int ctn_copy_table(const ctn_copy_item* items_dev, int n_items, long long max_bytes, void* stream);
+
 /* SI-SNR improvement of a batch on the device (evaluate.py:108-144, called per utterance on host
  * numpy arrays at evaluate.py:66-80 after remove_pad): for utterance b with n = lengths[b] valid
  * samples (lengths NULL -> T) and source c,

@@ -129,7 +129,7 @@ def stream_latency(name, cfg, chunk, seconds=60, warm_chunks=8):
     audio = n / SR
     return {"config": name, "chunk_frames": chunk, "chunk_audio_ms": audio * 1e3, "ms_per_chunk": ms,
             "algorithmic_latency_ms": (n + hop) / SR * 1e3, "x_realtime_one_stream": audio / (ms / 1e3),
-            "launches_per_chunk": len(sep.body_steady) + 1, "chunks_timed": total,
+            "launches_per_chunk": len(sep.body_steady) + 3, "chunks_timed": total,
             "timed": "host chunk -> device, steady-state chunk (CUDA graph), separated chunk -> host"}
 
 
