@@ -800,9 +800,9 @@ extern "C" int ctn_bwd_dwconv(const ctn_bwd_dw_args* args, void* stream) {
         q.dn1 = a.dn1, q.chan_part = a.chan_part, q.scal_part = a.scal_part;
         dim3 grid(q.ctas, a.M);
         if (a.causal)
-            bwd_dw_march_kernel<2><<<grid, kDmWarps * 32, 0, static_cast<cudaStream_t>(stream)>>>(q);
+            bwd_dw_march_kernel<2><<<grid, kBmWarps * 32, 0, static_cast<cudaStream_t>(stream)>>>(q);
         else
-            bwd_dw_march_kernel<1><<<grid, kDmWarps * 32, 0, static_cast<cudaStream_t>(stream)>>>(q);
+            bwd_dw_march_kernel<1><<<grid, kBmWarps * 32, 0, static_cast<cudaStream_t>(stream)>>>(q);
         CTN_LAUNCH_CHECK("bwd_dw_march_kernel");
         return CTN_OK;
     }

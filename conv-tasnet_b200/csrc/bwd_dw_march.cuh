@@ -22,6 +22,13 @@ namespace ctn {
 
 constexpr int kBmUnits = 4;   // most (phase, 32-frame segment) units a warp accumulates before writing partials
 constexpr int kBmAhead = 4;   // rows loaded ahead of use
+// CTA shape: 4 warps, 3 CTAs per SM (168 registers per thread under that bound, a few spilled values).
+// The 8-warp, one-per-SM shape (204 registers) it replaces left a third of the register file idle and,
+// worse, quantised badly: at the reference's batch of 3 x 4 s the 1200 warps of work made 150 CTAs for
+// 148 SMs, i.e. two rounds (51 us per launch for 25 us of work).  Small CTAs fill the 1776 warp slots
+// evenly: backward 6.0 -> 5.2 ms at batch 3, 18.6 -> 16.5 ms at batch 16.
+constexpr int kBmWarps = 4;
+constexpr int kBmCtasPerSm = 3;
 
 struct BwdMarchParams {
     int K, H, dil, c0, P1, P2, Pb, NS, units, groups, chan_rows, ctas, upw;
@@ -46,7 +53,7 @@ struct BwdMarchParams {
 // units per warp: as many as kBmUnits (fewer partial rows to reduce) while the grid still fills the GPU
 inline int bwd_march_units_per_warp(int M, int units, int H) {
     const long long warps1 = static_cast<long long>(M) * units * ((H + 127) / 128);   // warps at one unit each
-    const long long want = 2ll * 148 * kDmWarps;
+    const long long want = 2ll * 148 * kBmWarps;
     long long u = warps1 / want;
     return u < 1 ? 1 : (u > kBmUnits ? kBmUnits : static_cast<int>(u));
 }
@@ -57,7 +64,7 @@ inline void bwd_march_geometry(int M, int K, int H, int dil, int* NS, int* units
     const int upw = bwd_march_units_per_warp(M, *units, H);
     *groups = (*units + upw - 1) / upw;
     const int CG = (H + 127) / 128;
-    *ctas = ((*groups) * CG + kDmWarps - 1) / kDmWarps;
+    *ctas = ((*groups) * CG + kBmWarps - 1) / kBmWarps;
 }
 
 // block-wide sum of two doubles in a fixed order; every thread gets the result.  red: 2 * warps doubles.
@@ -72,10 +79,10 @@ __device__ __forceinline__ void block_sum2_double(double& s, double& ss, double*
 }
 
 template <int C0>
-__global__ void __launch_bounds__(kDmWarps * 32, 1)
+__global__ void __launch_bounds__(kBmWarps * 32, kBmCtasPerSm)
 bwd_dw_march_kernel(const BwdMarchParams p) {
-    __shared__ double fin_s[2 * kDmWarps];
-    __shared__ float red_s[3 * kDmWarps];
+    __shared__ double fin_s[2 * kBmWarps];
+    __shared__ float red_s[3 * kBmWarps];
     const int m = blockIdx.y;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int H = p.H, d = p.dil;
@@ -94,7 +101,7 @@ bwd_dw_march_kernel(const BwdMarchParams p) {
     const float m1 = static_cast<float>(bs / cnt), m2 = static_cast<float>(bss / cnt);
     const float al1 = __ldg(p.slope1), al2 = __ldg(p.slope2);
 
-    const int item = blockIdx.x * kDmWarps + warp;
+    const int item = blockIdx.x * kBmWarps + warp;
     const int CG = (H + 127) / 128;
     const int cg = item % CG;
     const int grp = item / CG;
@@ -254,11 +261,11 @@ bwd_dw_march_kernel(const BwdMarchParams p) {
         f2_unpack(sA2[0], a, b), f2_unpack(sA2[1], c2, d2);
         sc[2] = warp_sum((a + b) + (c2 + d2));
     }
-    if (lane == 0) red_s[warp] = sc[0], red_s[kDmWarps + warp] = sc[1], red_s[2 * kDmWarps + warp] = sc[2];
+    if (lane == 0) red_s[warp] = sc[0], red_s[kBmWarps + warp] = sc[1], red_s[2 * kBmWarps + warp] = sc[2];
     __syncthreads();
     if (threadIdx.x == 0) {
         float t0 = 0.f, t1 = 0.f, t2 = 0.f;
-        for (int i = 0; i < kDmWarps; ++i) t0 += red_s[i], t1 += red_s[kDmWarps + i], t2 += red_s[2 * kDmWarps + i];
+        for (int i = 0; i < kBmWarps; ++i) t0 += red_s[i], t1 += red_s[kBmWarps + i], t2 += red_s[2 * kBmWarps + i];
         float* s = p.scal_part + (static_cast<long long>(m) * p.ctas + blockIdx.x) * 4;
         s[0] = t0, s[1] = t1, s[2] = t2, s[3] = 0.f;
     }

@@ -58,6 +58,9 @@ class _PitSiSnr(torch.autograd.Function):
                                             idx.data_ptr(), loss.data_ptr(), None, coef.data_ptr(), nat.stream()))
         ctx.mark_dirty(estimate)
         ctx.mark_non_differentiable(idx)
+        # unused outputs (max_snr, the masked estimate) arrive as None in backward instead of as
+        # zero tensors, so the usual loss.backward() neither allocates them nor has to look at them
+        ctx.set_materialize_grads(False)
         ctx.save_for_backward(src, estimate, lengths, perms, idx, coef)
         return loss, max_snr, idx, estimate
 

@@ -121,3 +121,33 @@ def test_training_loop_with_fused_adam_reduces_loss():
         losses.append(float(loss))
     assert losses[-1] < losses[0] - 0.5
     assert float(opt.total_norm) > 0
+
+
+def test_gradients_as_views_of_a_moving_flat_buffer():
+    """The training engine hands back all gradients as views of one flat buffer that lives at a new
+    address every step: the optimizer then shifts the gradient column of its chunk table on the device
+    instead of rebuilding it.  Same result as torch's clip + Adam; a step where the layout itself
+    changes (separate tensors again) falls back to a rebuild."""
+    from ctn_b200.optim import FusedAdam
+    ours = _params(5, SHAPES)
+    ref = [torch.nn.Parameter(p.detach().clone()) for p in ours]
+    o1 = FusedAdam(ours, lr=1e-3, max_norm=5.0)
+    o2 = torch.optim.Adam(ref, lr=1e-3)
+    g = torch.Generator().manual_seed(6)
+    total = sum(p.numel() for p in ours)
+    keep = []
+    for it in range(6):
+        flat = torch.randn(total + 64 * it, generator=g).to(DEV)
+        keep.append(flat)            # keep earlier buffers alive so that every step sees a new address
+        off = 0
+        for a, b in zip(ours, ref):
+            k = a.numel()
+            view = flat[off:off + k].view_as(a)
+            a.grad = view if it != 4 else view.clone()
+            b.grad = view.clone()
+            off += k
+        torch.nn.utils.clip_grad_norm_(ref, 5.0)
+        o2.step()
+        o1.step()
+        for a, b in zip(ours, ref):
+            assert torch.allclose(a, b, rtol=2e-6, atol=2e-7), (it, a.shape, float((a - b).abs().max()))
