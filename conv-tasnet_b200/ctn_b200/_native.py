@@ -196,6 +196,8 @@ _SIGNATURES = {
     "ctn_pit_reorder": (C.c_int, [_vp, _vp, _vp, C.c_int, C.c_int, C.c_int, _vp, _vp]),
     "ctn_bn_fold": (C.c_int, [_vp, _vp, _vp, _vp, C.c_float, C.c_int, _vp, _vp, _vp]),
     "ctn_copy_table": (C.c_int, [_vp, C.c_int, C.c_longlong, _vp]),
+    "ctn_pad_batch": (C.c_int, [_vp, _vp, _vp, C.c_int, C.c_int, C.c_int, C.c_float, _vp, _vp, _vp]),
+    "ctn_remove_pad": (C.c_int, [_vp, _vp, C.c_int, C.c_int, C.c_int, _vp, _vp]),
     "ctn_sisnri": (C.c_int, [_vp, _vp, _vp, _vp, C.c_int, C.c_int, C.c_int, _vp, _vp, _vp]),
     "ctn_pit_sisnr_bwd": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, C.c_int, C.c_int, C.c_int, _vp, _vp]),
 }

@@ -36,14 +36,18 @@ def remove_pad(inputs, inputs_lengths):
         inputs_lengths: torch.Tensor, [B]
     Returns:
         results: a list containing B items, each item is [C, T] (or [T]) numpy, T varies
-    Host-side post-processing (utils.py:49-66): one device-to-host copy for the whole
-    batch, then per-utterance slicing on the host.
+    utils.py:49-66.  CUDA inputs: the valid samples are compacted on the device (ctn_remove_pad) and
+    cross to the host in one copy (ctn_b200/batch.py); the reference copies utterance by utterance.
+    Host inputs are only sliced.
     """
     dim = inputs.dim()
     if dim not in (2, 3):
         raise ValueError("inputs must be [B, C, T] or [B, T]")
+    if inputs.is_cuda and inputs.dtype == torch.float32:
+        from ctn_b200 import batch
+        return batch.remove_pad(inputs, inputs_lengths)
     host = inputs.detach().cpu().numpy()
-    lengths = [int(n) for n in inputs_lengths.detach().cpu().tolist()]
+    lengths = [int(n) for n in torch.as_tensor(inputs_lengths).detach().cpu().tolist()]
     results = []
     for row, length in zip(host, lengths):
         results.append(row[:, :length].copy() if dim == 3 else row[:length].copy())

@@ -395,6 +395,24 @@ int ctn_copy_table(const ctn_copy_item* items_dev, int n_items, long long max_by
 int ctn_sisnri(const float* ref, const float* est, const float* mix, const long long* lengths, int B, int C, int T,
                float* sisnr, float* sisnri, void* stream);
 
+/* Batch assembly on the device: ragged utterances arrive PACKED (valid samples only, one upload) and are
+ * laid out padded as the model and the loss expect them.  Replaces pad_list (data.py:295-301) as called by
+ * the collate functions (data.py:146-154, :222-225) plus the permute to [B, C, T] (data.py:153-154) and the
+ * upload of the padded tensors (solver.py:173-176).
+ *   offsets     int64 [B + 1] DEVICE: exclusive prefix sum of the utterance lengths, offsets[B] = total
+ *   mix_packed  fp32 [total]          -> mix_pad fp32 [B, T]     (both NULL: skip the mixtures)
+ *   src_packed  fp32 [total, C] (T x C per utterance, as load_mixtures_and_sources returns them, data.py:252)
+ *                                     -> src_pad fp32 [B, C, T]  (both NULL: skip the sources)
+ * Samples at t >= len_b get pad_value (the reference uses 0); lengths above T are cut at T. */
+int ctn_pad_batch(const float* mix_packed, const float* src_packed, const long long* offsets, int B, int C, int T,
+                  float pad_value, float* mix_pad, float* src_pad, void* stream);
+
+/* Inverse for results (utils.py:49-66 remove_pad, which copies every utterance to the host separately):
+ * packed[C * offsets[b] + c * len_b + t] = in[b, c, t] for t < len_b; in fp32 [B, C, T] (C = 1 for [B, T]),
+ * packed fp32 [C * total] so that utterance b is one contiguous [C, len_b] block and the valid samples go
+ * to the host in one copy. */
+int ctn_remove_pad(const float* in, const long long* offsets, int B, int C, int T, float* packed, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

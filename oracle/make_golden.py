@@ -158,6 +158,7 @@ def main():
 
 
     make_sisnri_cases()
+    make_data_cases()
 
 
 def _reference_functions(path, names):
@@ -193,8 +194,68 @@ def make_sisnri_cases():
     np.savez_compressed(os.path.join(OUT, "sisnri_cases.npz"), **out)
 
 
+def make_data_cases():
+    """Batching / segmenting / padding fixtures from the reference's own data.py (AudioDataset,
+    EvalDataset and both collate functions, data.py:32-232), imported unmodified.  Its two absent
+    third-party imports are stubbed in the harness: `librosa.load` serves the synthetic waveforms of
+    oracle/synth_audio.py (keyed by the fake path), `preprocess.preprocess_one_dir` is never reached
+    (mix_json is given)."""
+    import json
+    import tempfile
+    import types
+    sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+    import synth_audio as sa
+    sys.dont_write_bytecode = True
+    librosa = types.ModuleType("librosa")
+    librosa.load = lambda path, sr=None: (sa.synth(path), sr)
+    preprocess = types.ModuleType("preprocess")
+    preprocess.preprocess_one_dir = lambda *a, **k: (_ for _ in ()).throw(AssertionError("not expected"))
+    sys.modules["librosa"], sys.modules["preprocess"] = librosa, preprocess
+    sys.path.insert(0, REF)
+    import data as ref_data
+    sys.path.pop(0)
+    del sys.modules["librosa"], sys.modules["preprocess"]
+
+    plan, arrays = {}, {}
+    for name, case in sa.DATA_CASES.items():
+        infos = sa.make_infos(case["lengths"], case["shuffle"])
+        with tempfile.TemporaryDirectory() as d:
+            for kind, lst in zip(("mix", "s1", "s2"), infos):
+                with open(os.path.join(d, kind + ".json"), "w") as f:
+                    json.dump(lst, f)
+            ds = ref_data.AudioDataset(d, **case["kw"])
+        plan[name] = [[[i[0] for i in part] for part in mb[:3]] + [mb[3], mb[4]] for mb in ds.minibatch]
+        for b, mb in enumerate(ds.minibatch):
+            mix_pad, ilens, src_pad = ref_data._collate_fn([mb])
+            arrays["%s.%d.mix" % (name, b)] = mix_pad.numpy()
+            arrays["%s.%d.ilens" % (name, b)] = ilens.numpy()
+            arrays["%s.%d.src" % (name, b)] = src_pad.numpy()
+        print(name, [[os.path.basename(p) for p in mb[0]] for mb in plan[name]])
+    for name, case in sa.EVAL_CASES.items():
+        infos = sa.make_infos(case["lengths"], case["shuffle"])[0]
+        with tempfile.TemporaryDirectory() as d:
+            with open(os.path.join(d, "mix.json"), "w") as f:
+                json.dump(infos, f)
+            ds = ref_data.EvalDataset(None, os.path.join(d, "mix.json"), **case["kw"])
+        plan[name] = [[[i[0] for i in mb[0]], mb[1]] for mb in ds.minibatch]
+        for b, mb in enumerate(ds.minibatch):
+            mix_pad, ilens, names = ref_data._collate_fn_eval([mb])
+            assert names == plan[name][b][0]
+            arrays["%s.%d.mix" % (name, b)] = mix_pad.numpy()
+            arrays["%s.%d.ilens" % (name, b)] = ilens.numpy()
+        print(name, [[os.path.basename(p) for p in mb[0]] for mb in plan[name]])
+    # pad_list with a non-zero pad value and 2-D items (data.py:295-301)
+    xs = [torch.arange(6.).view(3, 2), torch.arange(10.).view(5, 2), torch.arange(2.).view(1, 2)]
+    arrays["pad_list.out"] = ref_data.pad_list(xs, -1.5).numpy()
+    with open(os.path.join(OUT, "data_cases.json"), "w") as f:
+        json.dump(plan, f, indent=1, sort_keys=True)
+    np.savez_compressed(os.path.join(OUT, "data_cases.npz"), **arrays)
+
+
 if __name__ == "__main__":
     if sys.argv[1:] == ["sisnri"]:
         make_sisnri_cases()
+    elif sys.argv[1:] == ["data"]:
+        make_data_cases()
     else:
         main()
