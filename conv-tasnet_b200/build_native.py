@@ -12,7 +12,7 @@ import sys
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
-LIB = os.path.join(HERE, "libctn_b200.so")
+LIB = os.path.join(HERE, os.environ.get("CTN_LIB_NAME", "libctn_b200.so"))   # CTN_LIB_NAME / NVCC_FLAGS: experiment builds
 ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
 
 
@@ -37,9 +37,9 @@ def build(force=False, verbose=False):
     procs = []
     os.makedirs(os.path.join(HERE, "build"), exist_ok=True)
     for src in sources():
-        obj = os.path.join(HERE, "build", os.path.basename(src)[:-3] + ".o")
+        obj = os.path.join(HERE, "build", os.path.basename(LIB)[:-3] + "." + os.path.basename(src)[:-3] + ".o")
         cmd = [nvcc, *ARCH, "-O3", "-lineinfo", "-std=c++17", "-Xcompiler", "-fPIC",
-               "--expt-relaxed-constexpr", "-c", src, "-o", obj]
+               "--expt-relaxed-constexpr", *os.environ.get("NVCC_FLAGS", "").split(), "-c", src, "-o", obj]
         if verbose:
             cmd.insert(1, "-Xptxas=-v")
         procs.append((src, subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)))

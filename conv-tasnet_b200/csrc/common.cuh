@@ -87,6 +87,14 @@ __device__ __forceinline__ double warp_sum(double v) {
 
 __device__ __forceinline__ float prelu(float v, float slope) { return v >= 0.f ? v : slope * v; }
 
+// Products per GEMM term on the tensor cores: 3 = a_hi w_hi + a_lo w_hi + a_hi w_lo (the product; fp32-grade
+// results), 1 = a_hi w_hi only.  1 exists ONLY as a speed probe of single-MMA operand formats for the forward
+// GEMMs (tools/precision_study.py: fp16 operands would keep 6e-4 rel-L2; with the bf16 operands of this
+// build the result is 5e-3 and fails parity) - build with NVCC_FLAGS=-DCTN_MMA_TERMS=1, never shipped.
+#ifndef CTN_MMA_TERMS
+#define CTN_MMA_TERMS 3
+#endif
+
 // fp32 -> (hi, lo) bf16 pair, hi = rn(v), lo = rn(v - hi)
 __device__ __forceinline__ void split_bf16(float v, __nv_bfloat16& hi, __nv_bfloat16& lo) {
     hi = __float2bfloat16_rn(v);

@@ -152,10 +152,11 @@ dwpw_kernel(const __grid_constant__ CUtensorMap tm_w_hi, const __grid_constant__
                 for (int kb = 0; kb < nkb; ++kb) {
                     ptx::mbar_wait(wempty_bar + slot, phase ^ 1);
                     uint8_t* st = wsm + slot * kWSlotBytes;
-                    if (rank == 0) ptx::mbar_expect_tx(wfull_bar + slot, 4 * kWBytes);
+                    if (rank == 0) ptx::mbar_expect_tx(wfull_bar + slot, (CTN_MMA_TERMS == 3 ? 4 : 2) * kWBytes);
                     ptx::tma_load_2d_pair(st, &tm_w_hi, fb0 + slot * 8, kb * kBK, static_cast<int>(rank) * (kBN / 2));
-                    ptx::tma_load_2d_pair(st + kWBytes, &tm_w_lo, fb0 + slot * 8, kb * kBK,
-                                          static_cast<int>(rank) * (kBN / 2));
+                    if (CTN_MMA_TERMS == 3)
+                        ptx::tma_load_2d_pair(st + kWBytes, &tm_w_lo, fb0 + slot * 8, kb * kBK,
+                                              static_cast<int>(rank) * (kBN / 2));
                     if (++slot == kWSlots) slot = 0, phase ^= 1;
                 }
             }
@@ -187,8 +188,10 @@ dwpw_kernel(const __grid_constant__ CUtensorMap tm_w_hi, const __grid_constant__
                     for (int k = 0; k < kBK / 16; ++k) {
                         const uint64_t adv = static_cast<uint64_t>((k * 16 * 2) >> 4);
                         ptx::umma_bf16_pair(d_tmem, a_hi + adv, w_hi + adv, idesc, (kb | k) != 0);
-                        ptx::umma_bf16_pair(d_tmem, a_lo + adv, w_hi + adv, idesc, 1);
-                        ptx::umma_bf16_pair(d_tmem, a_hi + adv, w_lo + adv, idesc, 1);
+                        if (CTN_MMA_TERMS == 3) {
+                            ptx::umma_bf16_pair(d_tmem, a_lo + adv, w_hi + adv, idesc, 1);
+                            ptx::umma_bf16_pair(d_tmem, a_hi + adv, w_lo + adv, idesc, 1);
+                        }
                     }
                     ptx::umma_commit_pair(aempty_bar + aslot, 3);   // frees the slots in BOTH CTAs
                     ptx::umma_commit_pair(wempty_bar + wslot, 3);
@@ -456,7 +459,8 @@ dwpw_kernel(const __grid_constant__ CUtensorMap tm_w_hi, const __grid_constant__
                     // hi_base is 1024-aligned, so the XOR can be applied to the whole address.
                     const uint32_t ad = ((hi_base + cs) ^ (static_cast<uint32_t>(o & 7) << 4)) + static_cast<uint32_t>(o) * 128u;
                     asm volatile("st.volatile.shared.v2.b32 [%0], {%1, %2};" ::"r"(ad), "r"(h[0]), "r"(h[1]) : "memory");
-                    asm volatile("st.volatile.shared.v2.b32 [%0], {%1, %2};" ::"r"(ad + kABytes), "r"(l[0]), "r"(l[1]) : "memory");
+                    if (CTN_MMA_TERMS == 3)
+                        asm volatile("st.volatile.shared.v2.b32 [%0], {%1, %2};" ::"r"(ad + kABytes), "r"(l[0]), "r"(l[1]) : "memory");
                 }
             };
             if (fast) unit(std::true_type{});

@@ -298,6 +298,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tm_a_hi, const __grid_constan
         if (lane == 0) {
             int stage = 0;
             uint32_t phase = 0;
+            constexpr bool kLoTerms = CTN_MMA_TERMS == 3;   // the (a_lo, w_lo) tiles are only read by the correction MMAs
+            constexpr uint32_t kStageTx = kLoTerms ? Cfg::kStageBytes : Cfg::kStageBytes / 2;
             for (int tile = worker; tile < total_tiles; tile += n_workers) {
                 const int tn = tile % n_tiles;
                 const int rt = PAIR ? 2 * (tile / n_tiles) + static_cast<int>(rank) : tile / n_tiles;
@@ -311,17 +313,17 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tm_a_hi, const __grid_constan
                     if (PAIR) {
                         // both CTAs' bytes complete on the leader's barrier, which the MMA issuer waits on
                         const uint32_t fb = ptx::mapa(ptx::smem_u32(full_bar + stage), 0);
-                        if (rank == 0) ptx::mbar_expect_tx(full_bar + stage, 2 * Cfg::kStageBytes);
+                        if (rank == 0) ptx::mbar_expect_tx(full_bar + stage, 2 * kStageTx);
                         ptx::tma_load_2d_pair(st, &tm_a_hi, fb, kb * kBK, row0);
-                        ptx::tma_load_2d_pair(st + Cfg::kABytes, &tm_a_lo, fb, kb * kBK, row0);
+                        if (kLoTerms) ptx::tma_load_2d_pair(st + Cfg::kABytes, &tm_a_lo, fb, kb * kBK, row0);
                         ptx::tma_load_2d_pair(st + 2 * Cfg::kABytes, &tm_w_hi, fb, kb * kBK, n0);
-                        ptx::tma_load_2d_pair(st + 2 * Cfg::kABytes + Cfg::kWBytes, &tm_w_lo, fb, kb * kBK, n0);
+                        if (kLoTerms) ptx::tma_load_2d_pair(st + 2 * Cfg::kABytes + Cfg::kWBytes, &tm_w_lo, fb, kb * kBK, n0);
                     } else {
-                        ptx::mbar_expect_tx(full_bar + stage, Cfg::kStageBytes);
+                        ptx::mbar_expect_tx(full_bar + stage, kStageTx);
                         ptx::tma_load_2d(st, &tm_a_hi, full_bar + stage, kb * kBK, row0);
-                        ptx::tma_load_2d(st + Cfg::kABytes, &tm_a_lo, full_bar + stage, kb * kBK, row0);
+                        if (kLoTerms) ptx::tma_load_2d(st + Cfg::kABytes, &tm_a_lo, full_bar + stage, kb * kBK, row0);
                         ptx::tma_load_2d(st + 2 * Cfg::kABytes, &tm_w_hi, full_bar + stage, kb * kBK, n0);
-                        ptx::tma_load_2d(st + 2 * Cfg::kABytes + Cfg::kWBytes, &tm_w_lo, full_bar + stage, kb * kBK, n0);
+                        if (kLoTerms) ptx::tma_load_2d(st + 2 * Cfg::kABytes + Cfg::kWBytes, &tm_w_lo, full_bar + stage, kb * kBK, n0);
                     }
                     if (++stage == Cfg::kStages) stage = 0, phase ^= 1;
                 }
@@ -355,12 +357,16 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tm_a_hi, const __grid_constan
                         const uint64_t adv = static_cast<uint64_t>((k * 16 * 2) >> 4);  // +32 B per k-step
                         if (PAIR) {
                             ptx::umma_bf16_pair(d_tmem, a_hi + adv, w_hi + adv, idesc, (kb | k) != 0);
-                            ptx::umma_bf16_pair(d_tmem, a_lo + adv, w_hi + adv, idesc, 1);
-                            ptx::umma_bf16_pair(d_tmem, a_hi + adv, w_lo + adv, idesc, 1);
+                            if (CTN_MMA_TERMS == 3) {
+                                ptx::umma_bf16_pair(d_tmem, a_lo + adv, w_hi + adv, idesc, 1);
+                                ptx::umma_bf16_pair(d_tmem, a_hi + adv, w_lo + adv, idesc, 1);
+                            }
                         } else {
                             ptx::umma_bf16(d_tmem, a_hi + adv, w_hi + adv, idesc, (kb | k) != 0);
-                            ptx::umma_bf16(d_tmem, a_lo + adv, w_hi + adv, idesc, 1);
-                            ptx::umma_bf16(d_tmem, a_hi + adv, w_lo + adv, idesc, 1);
+                            if (CTN_MMA_TERMS == 3) {
+                                ptx::umma_bf16(d_tmem, a_lo + adv, w_hi + adv, idesc, 1);
+                                ptx::umma_bf16(d_tmem, a_hi + adv, w_lo + adv, idesc, 1);
+                            }
                         }
                     }
                     if (PAIR) {
