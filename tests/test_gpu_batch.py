@@ -103,3 +103,43 @@ def test_errors():
     mix, lengths, _ = batch.assemble(torch.zeros(0), torch.zeros(0, dtype=torch.int64), None, DEV)
     assert mix.shape == (0, 0) and lengths.numel() == 0
     assert batch.remove_pad(torch.zeros(0, 2, 5, device=DEV), torch.zeros(0, dtype=torch.int64)) == []
+
+
+def test_separate_script_end_to_end(tmp_path):
+    """The drop-in separate.py on a directory of ragged wav files: every output file holds what the model
+    gives for the batch padded on the host (separate.py:60-80), as PCM16."""
+    import wave
+    import data
+    import separate as sep
+    from conv_tasnet import ConvTasNet
+    torch.manual_seed(3)
+    model = ConvTasNet(64, 16, 32, 64, 3, 3, 2, 2).to(DEV).eval()
+    torch.save(ConvTasNet.serialize(model, torch.optim.Adam(model.parameters()), 1), tmp_path / "model.pth.tar")
+    rng = np.random.RandomState(4)
+    mix_dir = tmp_path / "mix"
+    mix_dir.mkdir()
+    lens = {"u1.wav": 4000, "b.wav": 2777, "c.wav": 3500}
+    for name, n in lens.items():
+        sep.write_wav(0.2 * rng.randn(n), str(mix_dir / name), 8000)
+    args = sep.parser.parse_args(["--model_path", str(tmp_path / "model.pth.tar"), "--mix_dir", str(mix_dir),
+                                  "--out_dir", str(tmp_path / "out"), "--batch_size", "2"])
+    sep.separate(args)
+    # expected: batches of 2 in length order (u1, c), (b); padded on the host
+    def read(path):
+        return data._load_wav(str(path), 8000)
+    for group in (["u1.wav", "c.wav"], ["b.wav"]):
+        waves = [read(mix_dir / n) for n in group]
+        T = max(len(w) for w in waves)
+        host = torch.zeros(len(group), T)
+        for i, w in enumerate(waves):
+            host[i, :len(w)] = torch.from_numpy(w)
+        with torch.no_grad():
+            est = model(host.to(DEV)).cpu().numpy()
+        for i, n in enumerate(group):
+            stem = n.strip('.wav')     # the reference's way of dropping the suffix (separate.py:73)
+            assert np.array_equal(read(tmp_path / "out" / (stem + ".wav")),
+                                  np.clip(np.rint(waves[i].astype(np.float64) * 32767), -32768, 32767).astype(np.float32) / 32768)
+            for c in range(2):
+                got = read(tmp_path / "out" / ("%s_s%d.wav" % (stem, c + 1)))
+                want = np.clip(np.rint(est[i, c, :len(waves[i])].astype(np.float64) * 32767), -32768, 32767) / 32768
+                assert got.shape == (len(waves[i]),) and np.array_equal(got, want.astype(np.float32))

@@ -44,6 +44,15 @@ def test_invalid_arguments_return_error_codes_without_a_gpu():
     assert lib.ctn_decoder_fwd(1, 1, 1, 1, 5, 8, 4, 2, 100, 7, 1, None) == -1          # bad mask id
     with pytest.raises(ValueError):                                                     # conv_tasnet.py:208
         nat.check(-1)
+    # batch assembly: mixture / source pointers come in pairs, something must be asked for
+    assert lib.ctn_pad_batch(None, None, None, 1, 2, 8, 0.0, None, None, None) == -1
+    assert b"offsets" in lib.ctn_last_error()
+    assert lib.ctn_pad_batch(8, None, 8, 1, 2, 8, 0.0, None, None, None) == -1
+    assert b"together" in lib.ctn_last_error()
+    assert lib.ctn_pad_batch(None, None, 8, 1, 2, 8, 0.0, None, None, None) == -1
+    assert lib.ctn_remove_pad(None, None, 1, 2, 8, None, None) == -1
+    assert lib.ctn_remove_pad(8, 8, 70000, 2, 8, 8, None) == -1                         # grid limit
+    assert lib.ctn_pad_batch(8, None, 8, 0, 0, 8, 0.0, 8, None, None) == 0              # empty batch: no launch
 
 
 @pytest.mark.parametrize("name", MODEL_CASES)
