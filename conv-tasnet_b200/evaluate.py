@@ -93,3 +93,56 @@ def evaluate_batch(model, padded_mixture, mixture_lengths, padded_source):
     sisnri, sisnr = batch_SISNRi(padded_source, reorder_estimate_source, padded_mixture, mixture_lengths)
     return {"loss": loss, "max_snr": max_snr, "reorder_estimate_source": reorder_estimate_source,
             "sisnri": sisnri, "sisnr": sisnr}
+
+
+def _parser():
+    import argparse
+    parser = argparse.ArgumentParser('Evaluate separation performance using Conv-TasNet')
+    parser.add_argument('--model_path', type=str, required=True, help='Path to model file created by training')
+    parser.add_argument('--data_dir', type=str, required=True,
+                        help='directory including mix.json, s1.json and s2.json')
+    parser.add_argument('--cal_sdr', type=int, default=0,
+                        help='SDR needs mir_eval (third-party, host): must stay 0 here')
+    parser.add_argument('--use_cuda', type=int, default=0,
+                        help='Accepted for compatibility; the model always runs on the GPU (evaluate.py:41-43)')
+    parser.add_argument('--sample_rate', default=8000, type=int, help='Sample rate')
+    parser.add_argument('--batch_size', default=1, type=int, help='Batch size')
+    return parser
+
+
+def evaluate(args, verbose=True):
+    """The reference's evaluation script (evaluate.py:33-84, same command line and printed lines): whole
+    utterances of data_dir, forward, PIT reordering, SI-SNRi per utterance and its average.  Batches arrive
+    packed and are padded on the device; the metric is formed on the device for the padded batch
+    (ctn_sisnri) and only B floats per batch come back, instead of remove_pad of three tensors and numpy
+    arithmetic per utterance.  Returns the average SI-SNRi."""
+    from conv_tasnet import ConvTasNet
+    from ctn_b200 import batch as _batch
+    from data import AudioDataLoader, AudioDataset
+    if args.cal_sdr:
+        cal_SDRi(None, None, None)
+    model = ConvTasNet.load_model(args.model_path)
+    if verbose:
+        print(model)
+    model.eval()
+    model.cuda()
+    dataset = AudioDataset(args.data_dir, args.batch_size, sample_rate=args.sample_rate, segment=-1)
+    data_loader = AudioDataLoader(dataset, batch_size=1, num_workers=2, packed=True, pin_memory=True)
+    total_SISNRi, total_cnt = 0.0, 0
+    for mix_packed, ilens, src_packed in data_loader:
+        padded_mixture, mixture_lengths, padded_source = _batch.assemble(mix_packed, ilens, src_packed, "cuda")
+        out = evaluate_batch(model, padded_mixture, mixture_lengths, padded_source)
+        for avg_SISNRi in out["sisnri"].tolist():
+            if verbose:
+                print("Utt", total_cnt + 1)
+                print("\tSI-SNRi={0:.2f}".format(avg_SISNRi))
+            total_SISNRi += avg_SISNRi
+            total_cnt += 1
+    print("Average SISNR improvement: {0:.2f}".format(total_SISNRi / total_cnt))
+    return total_SISNRi / total_cnt
+
+
+if __name__ == '__main__':
+    args = _parser().parse_args()
+    print(args)
+    evaluate(args)

@@ -143,3 +143,45 @@ def test_separate_script_end_to_end(tmp_path):
                 got = read(tmp_path / "out" / ("%s_s%d.wav" % (stem, c + 1)))
                 want = np.clip(np.rint(est[i, c, :len(waves[i])].astype(np.float64) * 32767), -32768, 32767) / 32768
                 assert got.shape == (len(waves[i]),) and np.array_equal(got, want.astype(np.float32))
+
+
+def test_evaluate_script_matches_per_utterance_numpy_metric(tmp_path, capsys):
+    """The drop-in evaluate.py on ragged wav triples = the reference's loop: forward on the padded batch,
+    PIT reordering, remove_pad, the oracle's cal_SISNRi (pinned to the reference's evaluate.py) per
+    utterance."""
+    import json
+    import data
+    import evaluate as ev
+    import separate as sep
+    from conv_tasnet import ConvTasNet
+    from pit_criterion import cal_loss
+    from oracle import convtasnet_oracle as O
+    torch.manual_seed(5)
+    model = ConvTasNet(64, 16, 32, 64, 3, 3, 2, 2).to(DEV).eval()
+    torch.save(ConvTasNet.serialize(model, torch.optim.Adam(model.parameters()), 1), tmp_path / "model.pth.tar")
+    rng = np.random.RandomState(6)
+    lens = [4000, 2777, 3500, 3100, 1200]
+    infos = {"mix": [], "s1": [], "s2": []}
+    for i, n in enumerate(lens):
+        s = 0.2 * rng.randn(2, n)
+        for kind, x in (("s1", s[0]), ("s2", s[1]), ("mix", s.sum(0))):
+            (tmp_path / kind).mkdir(exist_ok=True)
+            path = str(tmp_path / kind / ("u%d.wav" % i))
+            sep.write_wav(x, path, 8000)
+            infos[kind].append([path, n])
+    for kind, lst in infos.items():
+        json.dump(lst, open(tmp_path / (kind + ".json"), "w"))
+    args = ev._parser().parse_args(["--model_path", str(tmp_path / "model.pth.tar"), "--data_dir", str(tmp_path),
+                                    "--batch_size", "2"])
+    avg = ev.evaluate(args, verbose=False)
+    assert "Average SISNR improvement" in capsys.readouterr().out
+    # reference loop, host padding, numpy metric
+    ds = data.AudioDataset(str(tmp_path), 2, sample_rate=8000, segment=-1)
+    vals = []
+    for mix, ilens, src in data.AudioDataLoader(ds, batch_size=1):
+        with torch.no_grad():
+            est = model(mix.to(DEV))
+            _, _, _, reorder = cal_loss(src.to(DEV), est, ilens.to(DEV))
+        for b, n in enumerate(ilens.tolist()):
+            vals.append(O.cal_SISNRi(src[b, :, :n].numpy(), reorder[b, :, :n].cpu().numpy(), mix[b, :n].numpy()))
+    assert len(vals) == len(lens) and abs(avg - float(np.mean(vals))) < 1e-3
