@@ -262,9 +262,11 @@ class TrainPlan:
                   params[k["b2"]].data_ptr(), GLN, self.stat2[i].data_ptr(), P2, M, K, H,
                   self.hl_H[0].data_ptr(), self.hl_H[1].data_ptr())
             bwd.append(_JOIN)     # the previous block's weight gradients read hl_H and the partial buffers
-            bwd.append(lambda s, a=a_: ns(*a, s))                                       # u (hi, lo)
+            # u is read by the weight-gradient GEMM only, so it is formed on the side stream as well: the fork
+            # orders it behind the previous block's last dgrad GEMM, which reads hl_H (as da)
             call, seg_w2 = self._wgrad(self.g_hl, self.hl_H, B, H, k["w2"])              # dW2 = g^T u
             bwd.append(_FORK)
+            bwd.append((_SIDE, lambda s, a=a_: ns(*a, s)))                              # u (hi, lo)
             bwd.append((_SIDE, call))
             bwd.append(self._gemm(Cin=B, Cout=H, a_hi=self.g_hl[0], a_lo=self.g_hl[1], w_hi=pb["w2t"][0],
                                   w_lo=pb["w2t"][1], out_f32=self.du, out_stat=GLN, out_stat_buf=self.bstat,
