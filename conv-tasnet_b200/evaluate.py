@@ -110,7 +110,7 @@ def _parser():
     return parser
 
 
-def evaluate(args, verbose=True):
+def evaluate(args, verbose=True, num_workers=2):
     """The reference's evaluation script (evaluate.py:33-84, same command line and printed lines): whole
     utterances of data_dir, forward, PIT reordering, SI-SNRi per utterance and its average.  Batches arrive
     packed and are padded on the device; the metric is formed on the device for the padded batch
@@ -127,7 +127,7 @@ def evaluate(args, verbose=True):
     model.eval()
     model.cuda()
     dataset = AudioDataset(args.data_dir, args.batch_size, sample_rate=args.sample_rate, segment=-1)
-    data_loader = AudioDataLoader(dataset, batch_size=1, num_workers=2, packed=True, pin_memory=True)
+    data_loader = AudioDataLoader(dataset, batch_size=1, num_workers=num_workers, packed=True, pin_memory=True)
     total_SISNRi, total_cnt = 0.0, 0
     for mix_packed, ilens, src_packed in data_loader:
         padded_mixture, mixture_lengths, padded_source = _batch.assemble(mix_packed, ilens, src_packed, "cuda")

@@ -56,7 +56,7 @@ def separate_batches(model, loader, device="cuda"):
             yield filenames, [host[off[i]:off[i + 1]] for i in range(len(filenames))], flat_estimate
 
 
-def separate(args):
+def separate(args, num_workers=1):
     if args.mix_dir is None and args.mix_json is None:
         print("Must provide mix_dir or mix_json! When providing mix_dir, mix_json is ignored.")
     model = ConvTasNet.load_model(args.model_path)
@@ -64,7 +64,7 @@ def separate(args):
     model.eval()
     model.cuda()
     eval_dataset = EvalDataset(args.mix_dir, args.mix_json, batch_size=args.batch_size, sample_rate=args.sample_rate)
-    eval_loader = EvalDataLoader(eval_dataset, batch_size=1, packed=True, pin_memory=True, num_workers=1)
+    eval_loader = EvalDataLoader(eval_dataset, batch_size=1, packed=True, pin_memory=True, num_workers=num_workers)
     os.makedirs(args.out_dir, exist_ok=True)
     for filenames, mixtures, estimates in separate_batches(model, eval_loader):
         for filename, mixture, estimate in zip(filenames, mixtures, estimates):

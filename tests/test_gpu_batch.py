@@ -123,7 +123,7 @@ def test_separate_script_end_to_end(tmp_path):
         sep.write_wav(0.2 * rng.randn(n), str(mix_dir / name), 8000)
     args = sep.parser.parse_args(["--model_path", str(tmp_path / "model.pth.tar"), "--mix_dir", str(mix_dir),
                                   "--out_dir", str(tmp_path / "out"), "--batch_size", "2"])
-    sep.separate(args)
+    sep.separate(args, num_workers=0)    # no forked loader workers inside the test process
     # expected: batches of 2 in length order (u1, c), (b); padded on the host
     def read(path):
         return data._load_wav(str(path), 8000)
@@ -173,7 +173,7 @@ def test_evaluate_script_matches_per_utterance_numpy_metric(tmp_path, capsys):
         json.dump(lst, open(tmp_path / (kind + ".json"), "w"))
     args = ev._parser().parse_args(["--model_path", str(tmp_path / "model.pth.tar"), "--data_dir", str(tmp_path),
                                     "--batch_size", "2"])
-    avg = ev.evaluate(args, verbose=False)
+    avg = ev.evaluate(args, verbose=False, num_workers=0)
     assert "Average SISNR improvement" in capsys.readouterr().out
     # reference loop, host padding, numpy metric
     ds = data.AudioDataset(str(tmp_path), 2, sample_rate=8000, segment=-1)
