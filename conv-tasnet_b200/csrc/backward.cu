@@ -90,7 +90,13 @@ struct NormSplitParams {
     __nv_bfloat16* out_hi;
     __nv_bfloat16* out_lo;
 };
-constexpr int kNsTile = 32;
+// Frames per CTA of the row-wise elementwise kernels below (norm_split, bwd_prelu_norm).  They are latency-bound
+// at training batch sizes (20 MB in, 20 MB out per launch): A/B on one box, two alternating rounds, train step
+// at batch 3 / batch 8: 32 frames 7.84 / 11.43 ms, 16 frames 7.56 / 11.37 ms, 8 frames 7.54 / 11.53 ms.
+#ifndef CTN_NS_TILE
+#define CTN_NS_TILE 16
+#endif
+constexpr int kNsTile = CTN_NS_TILE;
 
 template <int VEC>
 __global__ void __launch_bounds__(kBwThreads) norm_split_kernel(const NormSplitParams p) {
