@@ -5,7 +5,10 @@
 
 namespace ctn {
 
-constexpr int kDmSeg = 32;    // frames per (phase, segment) unit of the marching kernels
+#ifndef CTN_DM_SEG
+#define CTN_DM_SEG 32
+#endif
+constexpr int kDmSeg = CTN_DM_SEG;    // frames per (phase, segment) unit of the marching kernels
 constexpr int kDmWarps = 8;   // warps per CTA of the marching kernels
 
 // ---- packed fp32x2 helpers (a 64-bit register pair holds two floats) ----
