@@ -15,7 +15,10 @@
 
 namespace ctn {
 
-constexpr int kDmAhead = 8;   // rows loaded ahead of use
+#ifndef CTN_DM_AHEAD
+#define CTN_DM_AHEAD 8
+#endif
+constexpr int kDmAhead = CTN_DM_AHEAD;   // rows loaded ahead of use (a power of two)
 
 struct DwMarchParams {
     int K, H, dil, c0, in_P, NS, items, out_P;

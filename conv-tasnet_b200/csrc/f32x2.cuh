@@ -9,7 +9,10 @@ namespace ctn {
 #define CTN_DM_SEG 32
 #endif
 constexpr int kDmSeg = CTN_DM_SEG;    // frames per (phase, segment) unit of the marching kernels
-constexpr int kDmWarps = 8;   // warps per CTA of the marching kernels
+#ifndef CTN_DM_WARPS
+#define CTN_DM_WARPS 8
+#endif
+constexpr int kDmWarps = CTN_DM_WARPS;   // warps per CTA of the marching kernels
 
 // ---- packed fp32x2 helpers (a 64-bit register pair holds two floats) ----
 typedef unsigned long long f2_t;
