@@ -91,20 +91,61 @@ __device__ __forceinline__ float prelu(float v, float slope) { return v >= 0.f ?
 // results), 1 = a_hi w_hi only.  1 exists ONLY as a speed probe of single-MMA operand formats for the forward
 // GEMMs (tools/precision_study.py: fp16 operands would keep 6e-4 rel-L2; with the bf16 operands of this
 // build the result is 5e-3 and fails parity) - build with NVCC_FLAGS=-DCTN_MMA_TERMS=1, never shipped.
+// CTN_OPERAND_FP16=1 (experiment build, implies one term): the 16-bit containers hold IEEE fp16 instead of bf16 -
+// 11 significant bits per operand, 22 for a (hi, lo) pair such as the residual stream; tools/precision_study.py
+// predicts 5.6e-4 rel-L2 for the forward.  Every site that forms or decodes a pair is switched below / in place;
+// the default build is textually unchanged (#else branches).
+#ifndef CTN_OPERAND_FP16
+#define CTN_OPERAND_FP16 0
+#endif
 #ifndef CTN_MMA_TERMS
+#if CTN_OPERAND_FP16
+#define CTN_MMA_TERMS 1
+#else
 #define CTN_MMA_TERMS 3
+#endif
+#endif
+#if CTN_OPERAND_FP16
+#include <cuda_fp16.h>
+static_assert(CTN_MMA_TERMS == 1, "fp16 operands are used with a single MMA per product");
 #endif
 
 // fp32 -> (hi, lo) bf16 pair, hi = rn(v), lo = rn(v - hi)
+#if CTN_OPERAND_FP16
+// value of one 16-bit container / of the two containers packed in a word (element 0 in the low half)
+__device__ __forceinline__ float op16_value(__nv_bfloat16 v) {
+    return __half2float(__ushort_as_half(__bfloat16_as_ushort(v)));
+}
+__device__ __forceinline__ void op16_value2(uint32_t w, float& v0, float& v1) {
+    const float2 f = __half22float2(*reinterpret_cast<const __half2*>(&w));
+    v0 = f.x, v1 = f.y;
+}
+__device__ __forceinline__ void split_bf16(float v, __nv_bfloat16& hi, __nv_bfloat16& lo) {
+    const __half h = __float2half_rn(v);
+    const __half l = __float2half_rn(v - __half2float(h));
+    hi = __ushort_as_bfloat16(__half_as_ushort(h));
+    lo = __ushort_as_bfloat16(__half_as_ushort(l));
+}
+#else
 __device__ __forceinline__ void split_bf16(float v, __nv_bfloat16& hi, __nv_bfloat16& lo) {
     hi = __float2bfloat16_rn(v);
     lo = __float2bfloat16_rn(v - __bfloat162float(hi));
 }
+#endif
 __device__ __forceinline__ uint32_t pack_bf16(__nv_bfloat16 a, __nv_bfloat16 b) {
     return static_cast<uint32_t>(__bfloat16_as_ushort(a)) | (static_cast<uint32_t>(__bfloat16_as_ushort(b)) << 16);
 }
 // split two floats, return packed hi pair and lo pair (v0 in the low half); 6 instructions:
 // one packed cvt.rn.bf16x2 per pair, the hi halves are recovered with a shift / mask.
+#if CTN_OPERAND_FP16
+__device__ __forceinline__ void split_pack2(float v0, float v1, uint32_t& hi, uint32_t& lo) {
+    const __half2 h = __floats2half2_rn(v0, v1);
+    hi = *reinterpret_cast<const uint32_t*>(&h);
+    const float2 hf = __half22float2(h);
+    const __half2 l = __floats2half2_rn(v0 - hf.x, v1 - hf.y);
+    lo = *reinterpret_cast<const uint32_t*>(&l);
+}
+#else
 __device__ __forceinline__ void split_pack2(float v0, float v1, uint32_t& hi, uint32_t& lo) {
     const __nv_bfloat162 h = __floats2bfloat162_rn(v0, v1);
     hi = *reinterpret_cast<const uint32_t*>(&h);
@@ -113,6 +154,7 @@ __device__ __forceinline__ void split_pack2(float v0, float v1, uint32_t& hi, ui
     const __nv_bfloat162 l = __floats2bfloat162_rn(v0 - f0, v1 - f1);
     lo = *reinterpret_cast<const uint32_t*>(&l);
 }
+#endif
 
 // Whole-warp, fixed-order reduction of P (sum, sumsq) partials into (mean, rstd).
 // Every lane returns the same value.  count = number of elements the partials cover.

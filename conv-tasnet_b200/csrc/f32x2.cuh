@@ -50,6 +50,11 @@ __device__ __forceinline__ void f2_split_sign(f2_t v, f2_t neg1, f2_t& mx, f2_t&
 __device__ __forceinline__ void f2_split_bf16(f2_t v, f2_t neg1, uint32_t& hi, uint32_t& lo) {
     float a, b;
     f2_unpack(v, a, b);
+#if CTN_OPERAND_FP16
+    (void)neg1;
+    split_pack2(a, b, hi, lo);
+    return;
+#endif
     const __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
     hi = *reinterpret_cast<const uint32_t*>(&h);
     const f2_t hf = f2_pack(__uint_as_float(hi << 16), __uint_as_float(hi & 0xffff0000u));

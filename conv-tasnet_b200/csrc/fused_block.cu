@@ -526,8 +526,14 @@ resid_update_kernel(__nv_bfloat16* __restrict__ x_hi, __nv_bfloat16* __restrict_
         uint32_t oh[4], ol[4];
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
+#if CTN_OPERAND_FP16
+            float xh0, xh1, xl0, xl1;
+            op16_value2(hw[j], xh0, xh1), op16_value2(lw[j], xl0, xl1);
+            const float x0 = xh0 + xl0, x1 = xh1 + xl1;
+#else
             const float x0 = __uint_as_float(hw[j] << 16) + __uint_as_float(lw[j] << 16);
             const float x1 = __uint_as_float(hw[j] & 0xffff0000u) + __uint_as_float(lw[j] & 0xffff0000u);
+#endif
             const float v0 = fmaf(sc, yv[2 * j], cc[2 * j]) + x0;
             const float v1 = fmaf(sc, yv[2 * j + 1], cc[2 * j + 1]) + x1;
             split_pack2(v0, v1, oh[j], ol[j]);

@@ -316,10 +316,16 @@ updc1_kernel(const __grid_constant__ CUtensorMap tm_w_hi, const __grid_constant_
                 const Row r = q[o];
                 q[o] = ld_row(nx.ox + static_cast<long long>(o) * kCin, o < nx.nrows);
                 // x = hi + lo (exact in fp32), x' = x + sc * y + cc
+#if CTN_OPERAND_FP16
+                float e0, e1, e2, e3, e4, e5, e6, e7;
+                op16_value2(r.hi.x, e0, e1), op16_value2(r.hi.y, e2, e3), op16_value2(r.lo.x, e4, e5), op16_value2(r.lo.y, e6, e7);
+                const f2_t h0 = f2_pack(e0, e1), h1 = f2_pack(e2, e3), l0 = f2_pack(e4, e5), l1 = f2_pack(e6, e7);
+#else
                 const f2_t h0 = f2_pack(__uint_as_float(r.hi.x << 16), __uint_as_float(r.hi.x & 0xffff0000u));
                 const f2_t h1 = f2_pack(__uint_as_float(r.hi.y << 16), __uint_as_float(r.hi.y & 0xffff0000u));
                 const f2_t l0 = f2_pack(__uint_as_float(r.lo.x << 16), __uint_as_float(r.lo.x & 0xffff0000u));
                 const f2_t l1 = f2_pack(__uint_as_float(r.lo.y << 16), __uint_as_float(r.lo.y & 0xffff0000u));
+#endif
                 f2_t v0 = f2_add(f2_fma(sc2, f2_pack(r.y.x, r.y.y), cc0), f2_add(h0, l0));
                 f2_t v1 = f2_add(f2_fma(sc2, f2_pack(r.y.z, r.y.w), cc1), f2_add(h1, l1));
                 uint32_t nh[2] = {0u, 0u}, nl[2] = {0u, 0u};

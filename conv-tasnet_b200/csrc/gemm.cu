@@ -78,7 +78,11 @@ __device__ __forceinline__ void epilogue_chunk(const EpiParams& ep, float (&v)[3
     if (ep.resid_hi != nullptr) {
 #pragma unroll
         for (int j = 0; j < 32; ++j)
+#if CTN_OPERAND_FP16
+            if (j < ncols) v[j] += op16_value(ep.resid_hi[base + j]) + op16_value(ep.resid_lo[base + j]);
+#else
             if (j < ncols) v[j] += __bfloat162float(ep.resid_hi[base + j]) + __bfloat162float(ep.resid_lo[base + j]);
+#endif
     }
     if (ep.resid != nullptr) {
         if (VEC) {
@@ -489,8 +493,15 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tm_a_hi, const __grid_constan
                                 for (int j = 0; j < 16; ++j) {   // word j holds columns 2j (low half) and 2j + 1
                                     const uint32_t h = __float_as_uint(rc[j >> 3][j & 7]);
                                     const uint32_t l = __float_as_uint(rc[2 + (j >> 3)][j & 7]);
+#if CTN_OPERAND_FP16
+                                    float h0, h1, l0, l1;
+                                    op16_value2(h, h0, h1), op16_value2(l, l0, l1);
+                                    v[2 * j] += h0 + l0;
+                                    v[2 * j + 1] += h1 + l1;
+#else
                                     v[2 * j] += __uint_as_float(h << 16) + __uint_as_float(l << 16);
                                     v[2 * j + 1] += __uint_as_float(h & 0xffff0000u) + __uint_as_float(l & 0xffff0000u);
+#endif
                                 }
                             }
                         }
@@ -606,12 +617,20 @@ gemm_simt_kernel(const __nv_bfloat16* __restrict__ a_hi, const __nv_bfloat16* __
             for (int j = 0; j < 32; ++j) v[j] = 0.f;
             if (valid) {
                 for (int kk = 0; kk < Cin; ++kk) {
+#if CTN_OPERAND_FP16
+                    const float a = op16_value(a_hi[grow * Cin + kk]);     // as the tensor-core path: hi only
+#else
                     const float a = __bfloat162float(a_hi[grow * Cin + kk]) + __bfloat162float(a_lo[grow * Cin + kk]);
+#endif
 #pragma unroll
                     for (int j = 0; j < 32; ++j) {
                         if (n0 + j < ep.Cout) {
                             const long long wi = static_cast<long long>(n0 + j) * Cin + kk;
+#if CTN_OPERAND_FP16
+                            v[j] = fmaf(a, op16_value(w_hi[wi]), v[j]);
+#else
                             v[j] = fmaf(a, __bfloat162float(w_hi[wi]) + __bfloat162float(w_lo[wi]), v[j]);
+#endif
                         }
                     }
                 }

@@ -23,7 +23,13 @@ __global__ void weight_prep_kernel(const float* __restrict__ W, int rows, int co
         const long long o = transpose ? static_cast<long long>(c) * rows + r : static_cast<long long>(r) * cols + c;
         w_hi[o] = h;
         w_lo[o] = l;
+#if CTN_OPERAND_FP16
+        sg += op16_value(h);   // the GEMM multiplies by w_hi only: the mean correction must use the same row sums
+#elif CTN_MMA_TERMS == 1
+        sg += __bfloat162float(h);
+#else
         sg += __bfloat162float(h) + __bfloat162float(l);
+#endif
         if (beta) sb = fmaf(w, beta[c], sb);
     }
     sg = warp_sum(sg);
@@ -53,7 +59,13 @@ __global__ void weight_prep_batch_kernel(const ctn_prep_item* __restrict__ items
                                          : static_cast<long long>(r) * it.cols + c;
         w_hi[o] = h;
         w_lo[o] = l;
+#if CTN_OPERAND_FP16
+        sg += op16_value(h);   // the GEMM multiplies by w_hi only: the mean correction must use the same row sums
+#elif CTN_MMA_TERMS == 1
+        sg += __bfloat162float(h);
+#else
         sg += __bfloat162float(h) + __bfloat162float(l);
+#endif
         if (it.beta) sb = fmaf(w, it.beta[c], sb);
     }
     sg = warp_sum(sg);

@@ -177,8 +177,13 @@ __global__ void wgrad_simt_kernel(const __nv_bfloat16* __restrict__ x_hi, const 
     if (r1 > R) r1 = R;
     float acc = 0.f;
     for (long long r = r0; r < r1; ++r) {
+#if CTN_OPERAND_FP16
+        const float xv = op16_value(x_hi[r * Ci + i]) + op16_value(x_lo[r * Ci + i]);   // the weight gradients keep 3 terms
+        const float yv = op16_value(y_hi[r * Cj + j]) + op16_value(y_lo[r * Cj + j]);
+#else
         const float xv = __bfloat162float(x_hi[r * Ci + i]) + __bfloat162float(x_lo[r * Ci + i]);
         const float yv = __bfloat162float(y_hi[r * Cj + j]) + __bfloat162float(y_lo[r * Cj + j]);
+#endif
         acc = fmaf(xv, yv, acc);
     }
     partials[static_cast<long long>(blockIdx.y) * Ci * Cj + e] = acc;
