@@ -46,4 +46,5 @@ int sm_count() {
 }  // namespace ctn
 
 extern "C" int ctn_version(void) { return 100; }
+extern "C" int ctn_operand_format(void) { return CTN_MMA_TERMS + (CTN_OPERAND_FP16 ? 100 : 0); }
 extern "C" const char* ctn_last_error(void) { return ctn::g_err; }

@@ -155,6 +155,7 @@ _i, _ll = C.c_int, C.c_longlong
 
 _SIGNATURES = {
     "ctn_version": (C.c_int, []),
+    "ctn_operand_format": (C.c_int, []),
     "ctn_last_error": (C.c_char_p, []),
     "ctn_gemm_gln_partials": (C.c_int, [C.c_int, C.c_int]),
     "ctn_dwconv_gln_partials": (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_int]),
@@ -222,6 +223,12 @@ def lib():
         for name, (res, args) in _SIGNATURES.items():
             fn = getattr(handle, name)
             fn.restype, fn.argtypes = res, args
+        fmt = handle.ctn_operand_format()
+        if fmt != 3 and os.environ.get("CTN_ALLOW_EXPERIMENT_BUILD") != "1":
+            raise RuntimeError(
+                "%s is an experiment build (operand format %d: reduced-precision GEMM operands, see DESIGN.md "
+                "section 8); rebuild with `python conv-tasnet_b200/build_native.py --force` or set "
+                "CTN_ALLOW_EXPERIMENT_BUILD=1" % (_LIB_PATH, fmt))
         _lib = handle
     return _lib
 

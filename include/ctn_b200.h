@@ -48,6 +48,10 @@ extern "C" {
 #define CTN_DW_TILE 16   /* depthwise-kernel frame tile */
 
 int ctn_version(void);
+/* Operand format the library was built with: 3 = bf16 (hi, lo) pairs, three MMAs per product (the product);
+ * 1 = bf16, one MMA and 101 = fp16, one MMA (experiment builds).  The Python layer
+ * refuses anything but 3 unless CTN_ALLOW_EXPERIMENT_BUILD=1. */
+int ctn_operand_format(void);
 const char* ctn_last_error(void);
 
 /* Number of (sum, sumsq) float2 partials per utterance written by

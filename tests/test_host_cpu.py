@@ -21,6 +21,7 @@ def test_library_exports_every_declared_symbol():
         assert hasattr(lib, name), name
     assert declared == nat.exported_symbols()
     assert lib.ctn_version() >= 100
+    assert lib.ctn_operand_format() == 3      # the product build: bf16 (hi, lo) operands, three MMAs per product
     # pure-host geometry queries (no device work)
     assert lib.ctn_gemm_gln_partials(3199, 512) == 25 * 4 * 4
     assert lib.ctn_dwconv_gln_partials(3199, 512, 3, 1) == 50      # marching kernel: 4*1*100 warps / 8

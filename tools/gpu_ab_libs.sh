@@ -1,6 +1,7 @@
 # A/B of experiment builds of the library on one box: for each conv-tasnet_b200/libctn_b200_<tag>.so named in $@
 # (and the product build) run the command in $CMD; the swap happens only in the box's scratch copy
 set -x
+export CTN_ALLOW_EXPERIMENT_BUILD=1   # the Python layer refuses non-product operand formats otherwise
 mkdir -p gpurun_out
 CMD=${CMD:-python tools/bench_configs.py cfg2 cfg5}
 cp conv-tasnet_b200/libctn_b200.so /tmp/product.so

@@ -1,6 +1,7 @@
 # Experiment build -DCTN_OPERAND_FP16=1 (fp16 operands, one MMA per product): forward accuracy against the fp64
 # oracle and bench throughput.  The swap happens only in the GPU box's scratch copy of the repo.
 set -x
+export CTN_ALLOW_EXPERIMENT_BUILD=1   # the Python layer refuses non-product operand formats otherwise
 mkdir -p gpurun_out
 cp conv-tasnet_b200/libctn_b200_fp16.so conv-tasnet_b200/libctn_b200.so
 timeout 60 python - > gpurun_out/fp16_error.log 2>&1 <<'PY'

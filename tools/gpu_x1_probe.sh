@@ -1,6 +1,7 @@
 # Speed probe: the forward with ONE MMA per product (build -DCTN_MMA_TERMS=1) against the shipped three.
 # The probe library replaces the product library ONLY in the GPU box's scratch copy of the repo.
 set -x
+export CTN_ALLOW_EXPERIMENT_BUILD=1   # the Python layer refuses non-product operand formats otherwise
 mkdir -p gpurun_out
 timeout 300 python bench.py --no-cpu --no-train > gpurun_out/bench_x3.json 2> gpurun_out/bench_x3.err
 cp conv-tasnet_b200/libctn_b200.so /tmp/libctn_b200_x3.so
