@@ -34,6 +34,17 @@ def shard(tensor, group=None):
     return tensor[lo:hi]
 
 
+def shard_minibatch(minibatch, world, rank):
+    """This rank's part of one dataset item (data.py: AudioDataset / EvalDataset items are whole minibatches,
+    [mix_infos, s1_infos, s2_infos, sample_rate, segment_len] or [mix_infos, sample_rate]): the utterance lists
+    are cut with shard_bounds, everything else is passed through, so each rank loads and pads only its own
+    utterances.  Shards differ in size when the minibatch does not divide (and, with segmenting, in their number
+    of segments): pass the global segment count to attach(global_batch=...) / reduce_flat_grad(n_global=...)."""
+    n = len(minibatch[0])
+    lo, hi = shard_bounds(n, world, rank)
+    return [part[lo:hi] if isinstance(part, (list, tuple)) and len(part) == n else part for part in minibatch]
+
+
 def reduce_flat_grad(flat, n_local, n_global=None, group=None):
     """In place: flat <- sum over ranks of (n_local / n_global) * flat.  ONE all-reduce.
     n_global None = equal shards (scale 1 / world)."""

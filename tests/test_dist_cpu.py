@@ -83,3 +83,21 @@ def test_shard_bounds_cover_and_balance():
             assert max(sizes) - min(sizes) <= 1
     with pytest.raises(ValueError):
         _dist.shard_bounds(4, 2, 2)
+
+
+def test_shard_minibatch_partitions_dataset_items():
+    """Every utterance of a minibatch goes to exactly one rank, in order, with the non-list fields intact."""
+    from ctn_b200 import _dist
+    mix = [["mix/u%d.wav" % i, 100 - i] for i in range(5)]
+    s1 = [["s1/u%d.wav" % i, 100 - i] for i in range(5)]
+    s2 = [["s2/u%d.wav" % i, 100 - i] for i in range(5)]
+    item = [mix, s1, s2, 8000, 32000]
+    for world in (1, 2, 3, 8):
+        parts = [_dist.shard_minibatch(item, world, r) for r in range(world)]
+        assert sum((p[0] for p in parts), []) == mix and sum((p[2] for p in parts), []) == s2
+        assert all(p[3:] == [8000, 32000] for p in parts)
+        assert all(len(p[0]) == len(p[1]) == len(p[2]) for p in parts)
+        sizes = [len(p[0]) for p in parts]
+        assert max(sizes) - min(sizes) <= 1
+    ev = _dist.shard_minibatch([mix, 8000], 2, 1)
+    assert ev == [mix[3:], 8000]
