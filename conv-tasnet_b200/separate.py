@@ -20,16 +20,20 @@ from ctn_b200 import batch as _batch
 from data import EvalDataLoader, EvalDataset
 from utils import remove_pad
 
-parser = argparse.ArgumentParser('Separate speech using Conv-TasNet')
-parser.add_argument('--model_path', type=str, required=True, help='Path to model file created by training')
-parser.add_argument('--mix_dir', type=str, default=None, help='Directory including mixture wav files')
-parser.add_argument('--mix_json', type=str, default=None, help='Json file including mixture wav files')
-parser.add_argument('--out_dir', type=str, default='exp/result', help='Directory putting separated wav files')
-parser.add_argument('--use_cuda', type=int, default=0,
-                    help='Accepted for compatibility; the model always runs on the GPU (as in this fork of the '
-                         'reference, separate.py:44-46)')
-parser.add_argument('--sample_rate', default=8000, type=int, help='Sample rate')
-parser.add_argument('--batch_size', default=1, type=int, help='Batch size')
+# the reference's options (separate.py:18-32), kept name for name
+_OPTIONS = [
+    ("--model_path", dict(type=str, required=True, help="model package written by training (ConvTasNet.serialize)")),
+    ("--mix_dir", dict(type=str, default=None, help="directory of mixture wav files (wins over --mix_json)")),
+    ("--mix_json", dict(type=str, default=None, help="json list of [wav path, samples] pairs")),
+    ("--out_dir", dict(type=str, default="exp/result", help="where the separated wav files go")),
+    ("--use_cuda", dict(type=int, default=0, help="accepted for compatibility: the model always runs on the GPU, "
+                                                  "as in this fork of the reference (separate.py:44-46)")),
+    ("--sample_rate", dict(type=int, default=8000, help="sample rate of the files")),
+    ("--batch_size", dict(type=int, default=1, help="mixtures per forward pass")),
+]
+parser = argparse.ArgumentParser("Separate speech using Conv-TasNet")
+for _flag, _kw in _OPTIONS:
+    parser.add_argument(_flag, **_kw)
 
 
 def write_wav(samples, filename, sample_rate):
