@@ -162,13 +162,32 @@ def bn_eval(y, weight, bias, running_mean, running_var):
     return (y - running_mean[None, :, None]) * inv[None, :, None] * weight[None, :, None] + bias[None, :, None]
 
 
+BN_MOMENTUM = 0.1  # nn.BatchNorm1d default
+
+
+def bn_train(y, weight, bias, running_mean, running_var, num_batches_tracked):
+    """nn.BatchNorm1d in training mode (conv_tasnet.py:300-303 builds it with defaults): per channel, mean and
+    BIASED variance over the batch and time dims normalise the output; the running statistics move by
+    momentum 0.1 towards the batch mean and the UNBIASED variance; num_batches_tracked counts the call.
+    Returns (out, (new_running_mean, new_running_var, new_num_batches_tracked)).  Utterances of a batch
+    are coupled through the statistics, so an utterance-sharded run needs them summed over ranks."""
+    n = y.shape[0] * y.shape[2]
+    mean = y.mean(dim=(0, 2))
+    var = ((y - mean[None, :, None]) ** 2).mean(dim=(0, 2))
+    out = (y - mean[None, :, None]) / torch.sqrt(var[None, :, None] + BN_EPS) * weight[None, :, None] + bias[None, :, None]
+    unbiased = var * (n / max(n - 1, 1))
+    new = ((1 - BN_MOMENTUM) * running_mean + BN_MOMENTUM * mean.detach(),
+           (1 - BN_MOMENTUM) * running_var + BN_MOMENTUM * unbiased.detach(), num_batches_tracked + 1)
+    return out, new
+
+
 def _norm(norm_type, y, gamma, beta, stats=None):
     if norm_type == "gLN":
         return gln(y, gamma, beta)
     if norm_type == "cLN":
         return cln(y, gamma, beta)
     if stats is None:
-        raise NotImplementedError("BatchNorm1d: the oracle covers inference (running statistics) only")
+        raise NotImplementedError("BatchNorm1d needs its running statistics")
     return bn_eval(y, gamma, beta, stats[0], stats[1])
 
 
@@ -183,23 +202,35 @@ def depthwise(x, wd, dilation, causal):
     return y
 
 
-def temporal_block(x, p, k, dilation, norm_type, causal, taps=None):
+def temporal_block(x, p, k, dilation, norm_type, causal, taps=None, new_stats=None):
     """conv_tasnet.py:227-237 + 259-272.  `taps` (optional dict) collects
-    intermediates for per-kernel parity tests."""
+    intermediates for per-kernel parity tests.  `new_stats` (a dict) switches BatchNorm1d blocks to
+    training mode: batch statistics normalise, the updated buffers are stored in it under their keys."""
     a = F.conv1d(x, p[k["w1"]])
     pa = F.prelu(a, p[k["a1"]])
     bn = is_bn(norm_type)
-    n1 = _norm(norm_type, pa, p[k["g1"]], p[k["b1"]], (p[k["rm1"]], p[k["rv1"]]) if bn else None)
+
+    def norm(y, i):
+        g, b = p[k["g%d" % i]], p[k["b%d" % i]]
+        if not bn:
+            return _norm(norm_type, y, g, b)
+        if new_stats is None:
+            return _norm(norm_type, y, g, b, (p[k["rm%d" % i]], p[k["rv%d" % i]]))
+        out, (rm, rv, nb) = bn_train(y, g, b, p[k["rm%d" % i]], p[k["rv%d" % i]], p[k["nb%d" % i]])
+        new_stats[k["rm%d" % i]], new_stats[k["rv%d" % i]], new_stats[k["nb%d" % i]] = rm, rv, nb
+        return out
+
+    n1 = norm(pa, 1)
     d = depthwise(n1, p[k["wd"]], dilation, causal)
     q = F.prelu(d, p[k["a2"]])
-    n2 = _norm(norm_type, q, p[k["g2"]], p[k["b2"]], (p[k["rm2"]], p[k["rv2"]]) if bn else None)
+    n2 = norm(q, 2)
     out = F.conv1d(n2, p[k["w2"]]) + x
     if taps is not None:
         taps.update(a=a, pa=pa, n1=n1, d=d, q=q, n2=n2, out=out)
     return out
 
 
-def separator(w, p, cfg, taps=None):
+def separator(w, p, cfg, taps=None, new_stats=None):
     """conv_tasnet.py:192-209.  [M,N,K] -> mask [M,C,N,K]."""
     M, N, K = w.shape
     y = cln(w, p["separator.network.0.gamma"], p["separator.network.0.beta"])
@@ -209,7 +240,7 @@ def separator(w, p, cfg, taps=None):
     for r in range(cfg["R"]):
         for x in range(cfg["X"]):
             k = block_keys(r, x, cfg["causal"], cfg["norm_type"])
-            y = temporal_block(y, p, k, 2 ** x, cfg["norm_type"], cfg["causal"])
+            y = temporal_block(y, p, k, 2 ** x, cfg["norm_type"], cfg["causal"], new_stats=new_stats)
             if taps is not None:
                 taps["block_%d_%d" % (r, x)] = y
     score = F.conv1d(y, p["separator.network.3.weight"]).view(M, cfg["C"], N, K)
@@ -239,12 +270,13 @@ def decoder(w, mask, V):
     return overlap_and_add(frames, L // 2)
 
 
-def forward(mixture, p, cfg, taps=None):
-    """ConvTasNet.forward (conv_tasnet.py:45-60).  [M,T] -> [M,C,T]."""
+def forward(mixture, p, cfg, taps=None, new_stats=None):
+    """ConvTasNet.forward (conv_tasnet.py:45-60).  [M,T] -> [M,C,T].  new_stats: see temporal_block
+    (model.train() with norm_type="BN")."""
     w = encoder(mixture, p["encoder.conv1d_U.weight"])
     if taps is not None:
         taps["mixture_w"] = w
-    mask = separator(w, p, cfg, taps)
+    mask = separator(w, p, cfg, taps, new_stats)
     est = decoder(w, mask, p["decoder.basis_signals.weight"])
     T = mixture.shape[-1]
     return F.pad(est, (0, T - est.shape[-1]))

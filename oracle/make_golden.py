@@ -53,6 +53,10 @@ CASES = {
     # come from three training-mode forwards of the reference, the affine is perturbed; no gradients stored
     "tc_bn_eval": dict(cfg=dict(N=64, L=16, B=64, H=128, P=3, X=3, R=1, C=2, norm_type="BN",
                                 causal=False, mask_nonlinear="relu"), M=2, T=1207, lengths=[1207, 900], bn_eval=True),
+    # BatchNorm1d in TRAINING mode: batch statistics, running-statistics update, gradients (the product raises
+    # for this mode; the fixture pins the oracle for it)
+    "bn_train": dict(cfg=dict(N=8, L=4, B=8, H=16, P=3, X=2, R=2, C=2, norm_type="BN",
+                              causal=False, mask_nonlinear="relu"), M=3, T=61, lengths=[61, 61, 40], bn_train=True),
     "bn_eval_causal": dict(cfg=dict(N=8, L=4, B=8, H=16, P=3, X=2, R=2, C=2, norm_type="BN",
                                     causal=True, mask_nonlinear="relu"), M=2, T=51, lengths=[51, 37], bn_eval=True),
     "odd_gln": dict(cfg=dict(N=5, L=4, B=6, H=7, P=3, X=3, R=1, C=2, norm_type="gLN",
@@ -82,6 +86,13 @@ def main():
                     if v.dim() == 1 and v.numel() > 1:      # BatchNorm1d weight / bias
                         v.add_(0.2 * torch.randn(v.shape, generator=g))
             model.eval()
+        if case.get("bn_train"):
+            with torch.no_grad():
+                model.train()
+                model(0.1 * torch.randn(M, T, generator=g))      # buffers away from their initial 0 / 1 / 0
+                for k, v in model.named_parameters():
+                    if v.dim() == 1 and v.numel() > 1:
+                        v.add_(0.2 * torch.randn(v.shape, generator=g))
         init_sd = {k: v.detach().clone() for k, v in model.state_dict().items()}
         sources = 0.1 * torch.randn(M, cfg["C"], T, generator=g)
         mixture = sources.sum(1) + 0.01 * torch.randn(M, T, generator=g)
@@ -101,6 +112,10 @@ def main():
                 "perms": perms, "idx": idx}
         for k, v in init_sd.items():
             blob["w:" + k] = v
+        if case.get("bn_train"):
+            for k, v in model.state_dict().items():                # buffers after the training-mode forward
+                if "running_" in k or "num_batches" in k:
+                    blob["u:" + k] = v.detach().clone()
         for k, v in model.named_parameters():
             if v.grad is not None:
                 blob["g:" + k] = v.grad.detach()

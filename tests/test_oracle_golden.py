@@ -85,3 +85,36 @@ def test_batchnorm_inference_matches_reference(name):
     loss, max_snr, masked, reorder, idx = O.cal_loss(z["sources"], est, z["lengths"])
     assert torch.equal(idx, z["idx"])
     assert abs(float(loss) - float(z["loss"])) < 1e-4
+
+
+def test_batchnorm_training_mode_matches_reference():
+    """norm_type="BN" in train() mode (conv_tasnet.py:300-303 with nn.BatchNorm1d's defaults): batch statistics in
+    the forward, the running-statistics / num_batches_tracked update, and the gradients of every parameter,
+    against the reference's recorded training-mode forward + backward.  (The product implements BN for inference
+    and raises in training mode; this pins the oracle for the remaining SURVEY 8(f) row.)"""
+    torch.set_num_threads(1)
+    cfg, z = load_golden("bn_train")
+    p = {k[2:]: v.clone() for k, v in z.items() if k.startswith("w:")}
+    buffers = [k for k in p if "running_" in k or "num_batches" in k]
+    for k, v in p.items():
+        if k not in buffers:
+            v.requires_grad_(True)
+    new_stats = {}
+    est = O.forward(z["mixture"], p, cfg, new_stats=new_stats)
+    assert rel_l2(est, z["est"]) < 2e-6
+    loss, max_snr, masked, reorder, idx = O.cal_loss(z["sources"], est, z["lengths"])
+    assert torch.equal(idx, z["idx"]) and abs(float(loss.detach()) - float(z["loss"])) < 1e-4
+    updated = {k[2:]: v for k, v in z.items() if k.startswith("u:")}
+    assert sorted(updated) == sorted(new_stats) and len(updated) == 3 * 2 * cfg["R"] * cfg["X"]
+    for k, v in updated.items():
+        if v.is_floating_point():
+            assert torch.allclose(new_stats[k], v, rtol=1e-5, atol=1e-7), k
+        else:
+            assert int(new_stats[k]) == int(v), k
+    loss.backward()
+    grads = {k[2:]: v for k, v in z.items() if k.startswith("g:")}
+    assert sorted(grads) == sorted(k for k in p if k not in buffers)
+    for k, g in grads.items():
+        assert rel_l2(p[k].grad, g) < 2e-4, (k, rel_l2(p[k].grad, g))
+    # the same weights in eval mode use the running statistics instead: a different result
+    assert rel_l2(O.forward(z["mixture"], {k: v.detach() for k, v in p.items()}, cfg), z["est"]) > 1e-3
