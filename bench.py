@@ -304,7 +304,7 @@ def run_b200(args):
         roof["all_kernels"] = roofs
 
     train = None
-    if not args.no_train:
+    if not args.no_train and _precision() == "bf16x3":     # the fp16 inference precision has no training path
         train = train_step(args, world, rank, dev, timed)
         train["ms_per_step_torch_optimizer"] = train_step(args, world, rank, dev, timed, fused_optim=False)["ms_per_step"]
 
@@ -319,7 +319,8 @@ def run_b200(args):
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": sec / args.steps * 1e3, "higher_is_better": True,
             "scaling": "strong", "vs_baseline": None,
-            "dtype": "bf16 hi+lo split operands (3 MMAs), fp32 accumulate; fp32 elsewhere",
+            "dtype": ("bf16 hi+lo split operands (3 MMAs), fp32 accumulate; fp32 elsewhere" if _precision() == "bf16x3"
+                      else "fp16 operands (1 MMA), fp32 accumulate; fp32 elsewhere (CTN_PRECISION=fp16, opt-in)"),
             "data": "synthetic",
             "config": {"workload": "bulk separation of %d x 4 s @ 8 kHz mixtures, paper config "
                                    "(BASELINE configs[3]), sharded by utterance" % GLOBAL_BATCH,
@@ -338,6 +339,11 @@ def run_b200(args):
         print(json.dumps(out), flush=True)
     if world > 1:
         dist.destroy_process_group()
+
+
+def _precision():
+    from ctn_b200 import _native as nat
+    return nat.PRECISION
 
 
 def train_step(args, world, rank, dev, timed, fused_optim=True):

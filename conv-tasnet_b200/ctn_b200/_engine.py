@@ -32,6 +32,9 @@ BN_EPS = 1e-5   # nn.BatchNorm1d default (conv_tasnet.py:303 passes no eps)
 
 
 def _check_cfg(cfg, training=False):
+    if training and nat.PRECISION != "bf16x3":
+        raise RuntimeError("CTN_PRECISION=%s is an inference-only precision: gradients need the bf16 (hi, lo) "
+                           "operands of the default mode" % nat.PRECISION)
     if training and is_bn(cfg["norm_type"]):
         # conv_tasnet.py:300-303 falls through to BatchNorm1d; its training-mode batch statistics couple
         # the utterances of a batch, which the utterance-sharded design excludes.

@@ -9,7 +9,17 @@ import os
 import torch
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-_LIB_PATH = os.path.join(os.path.dirname(_HERE), "libctn_b200.so")
+# Precision of the tensor-core GEMM operands, chosen once per process (CTN_PRECISION):
+#   "bf16x3" (default)  bf16 (hi, lo) pairs, three MMAs per product: 1.5e-5 rel-L2 at the paper configuration,
+#                       the only mode training supports
+#   "fp16"              fp16 operands, one MMA per product: inference only, 4.9e-4 rel-L2 (tolerance 1e-3),
+#                       +14-19 % throughput.  Same sources compiled with
+#                       -DCTN_OPERAND_FP16=1 into a second library (build_native.py --fp16).
+_FORMATS = {"bf16x3": ("libctn_b200.so", 3), "fp16": ("libctn_b200_fp16.so", 101)}
+PRECISION = os.environ.get("CTN_PRECISION", "bf16x3")
+if PRECISION not in _FORMATS:
+    raise RuntimeError("CTN_PRECISION=%r: expected one of %s" % (PRECISION, sorted(_FORMATS)))
+_LIB_PATH = os.path.join(os.path.dirname(_HERE), _FORMATS[PRECISION][0])
 
 NORM_NONE, NORM_GLN, NORM_CLN = 0, 1, 2
 MASK_RELU, MASK_SOFTMAX = 0, 1
@@ -217,18 +227,18 @@ def lib():
     if _lib is None:
         if not os.path.exists(_LIB_PATH):
             raise RuntimeError(
-                "libctn_b200.so not found at %s: build it with "
-                "`python conv-tasnet_b200/build_native.py` (there is no CPU or PyTorch fallback)" % _LIB_PATH)
+                "%s not found: build it with `python conv-tasnet_b200/build_native.py%s` (there is no CPU or "
+                "PyTorch fallback)" % (_LIB_PATH, "" if PRECISION == "bf16x3" else " --fp16"))
         handle = C.CDLL(_LIB_PATH)
         for name, (res, args) in _SIGNATURES.items():
             fn = getattr(handle, name)
             fn.restype, fn.argtypes = res, args
         fmt = handle.ctn_operand_format()
-        if fmt != 3 and os.environ.get("CTN_ALLOW_EXPERIMENT_BUILD") != "1":
+        if fmt != _FORMATS[PRECISION][1] and os.environ.get("CTN_ALLOW_EXPERIMENT_BUILD") != "1":
             raise RuntimeError(
-                "%s is an experiment build (operand format %d: reduced-precision GEMM operands, see DESIGN.md "
-                "section 8); rebuild with `python conv-tasnet_b200/build_native.py --force` or set "
-                "CTN_ALLOW_EXPERIMENT_BUILD=1" % (_LIB_PATH, fmt))
+                "%s was built with operand format %d, CTN_PRECISION=%s needs %d (see DESIGN.md section 8); rebuild "
+                "with `python conv-tasnet_b200/build_native.py --all --force` or set CTN_ALLOW_EXPERIMENT_BUILD=1"
+                % (_LIB_PATH, fmt, PRECISION, _FORMATS[PRECISION][1]))
         _lib = handle
     return _lib
 

@@ -14,6 +14,18 @@ for p in (ROOT, PKG):
         sys.path.insert(0, p)
 
 
+def pytest_sessionstart(session):
+    """The libraries are built in-tree by __graft_entry__.build(); a checkout without them (a fresh machine)
+    builds them here once instead of failing every test.  Existing libraries are left alone."""
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("ctn_build_native", os.path.join(PKG, "build_native.py"))
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    for variant, (name, _) in mod.VARIANTS.items():
+        if not os.path.exists(os.path.join(PKG, name)):
+            mod.build(variant=variant)
+
+
 def pytest_configure(config):
     config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box)")
 

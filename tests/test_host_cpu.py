@@ -9,7 +9,7 @@ import re
 import pytest
 import torch
 
-from conftest import MODEL_CASES, ROOT, load_golden
+from conftest import MODEL_CASES, PKG, ROOT, load_golden
 
 
 def test_library_exports_every_declared_symbol():
@@ -137,3 +137,25 @@ def test_product_path_never_imports_the_oracle():
             if f.endswith((".py", ".cu", ".cuh", ".h")):
                 text = open(os.path.join(dirpath, f)).read()
                 assert "oracle" not in text.lower() or f == "never", (dirpath, f)
+
+
+def test_precision_variants_of_the_library():
+    """CTN_PRECISION picks the library per process; each library states its operand format and exports the
+    whole ABI; a mismatch or an unknown precision is refused."""
+    import ctypes as C
+    import subprocess
+    import sys
+    from ctn_b200 import _native as nat
+    assert nat.PRECISION == "bf16x3"
+    fp16 = os.path.join(PKG, "libctn_b200_fp16.so")
+    assert os.path.exists(fp16), "python conv-tasnet_b200/build_native.py --fp16 (done by __graft_entry__.build())"
+    h = C.CDLL(fp16)
+    assert h.ctn_operand_format() == 101
+    for name in nat.exported_symbols():
+        assert hasattr(h, name), name
+    code = "from ctn_b200 import _native as n; n.lib(); print(n.PRECISION, n.lib().ctn_operand_format())"
+    env = dict(os.environ, PYTHONPATH=PKG, CTN_PRECISION="fp16")
+    r = subprocess.run([sys.executable, "-c", code], env=env, capture_output=True, text=True)
+    assert r.returncode == 0 and r.stdout.split() == ["fp16", "101"], r.stderr[-500:]
+    r = subprocess.run([sys.executable, "-c", code], env=dict(env, CTN_PRECISION="fp8"), capture_output=True, text=True)
+    assert r.returncode != 0 and "CTN_PRECISION" in r.stderr
