@@ -1,5 +1,11 @@
+"""Quick check of the opt-in inference precision on a GPU box (a few seconds):
+    CTN_PRECISION=fp16 python tools/fp16_mode_check.py
+small causal cLN model against the fp64 oracle, chunked streaming against the whole forward, training refused.
+The full check is tests/test_gpu_zz_precision.py."""
 import sys, torch
-sys.path[:0] = ["/root/repo", "/root/repo/conv-tasnet_b200"]
+import os
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path[:0] = [ROOT, os.path.join(ROOT, "conv-tasnet_b200")]
 import conv_tasnet
 from ctn_b200 import _native as nat
 from oracle import convtasnet_oracle as O
