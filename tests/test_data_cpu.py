@@ -132,3 +132,32 @@ def test_pack_rejects_mismatched_sources():
         batch.pack([np.zeros(5, np.float32)], [], pin=False)
     mix, ilens, src = batch.pack([], None, pin=False)
     assert mix.numel() == 0 and ilens.numel() == 0 and src is None
+
+
+def test_preprocess_lists_the_directory_tree(tmp_path):
+    """preprocess.py:12-36: one json per set and speaker with (absolute path, samples); the result feeds
+    AudioDataset directly."""
+    import types
+    import data
+    import preprocess
+    rng = np.random.RandomState(1)
+    lens = [300, 500, 410]
+    for s in preprocess.SETS:
+        for spk in preprocess.SPEAKERS:
+            d = tmp_path / "wav" / s / spk
+            d.mkdir(parents=True)
+            for i, n in enumerate(lens):
+                with wave.open(str(d / ("u%d.wav" % i)), "wb") as w:
+                    w.setnchannels(1), w.setsampwidth(2), w.setframerate(8000)
+                    w.writeframes((rng.randn(n) * 3000).astype("<i2").tobytes())
+    preprocess.preprocess(types.SimpleNamespace(in_dir=str(tmp_path / "wav"), out_dir=str(tmp_path / "json"),
+                                                sample_rate=8000))
+    for s in preprocess.SETS:
+        for spk in preprocess.SPEAKERS:
+            infos = json.load(open(tmp_path / "json" / s / (spk + ".json")))
+            assert [n for _, n in infos] == lens
+            assert all(os.path.isabs(p) and p.endswith("u%d.wav" % i) and ("/%s/%s/" % (s, spk)) in p
+                       for i, (p, _) in enumerate(infos))
+    ds = data.AudioDataset(str(tmp_path / "json" / "tr"), batch_size=2, sample_rate=8000, segment=-1)
+    mix, ilens, src = next(iter(data.AudioDataLoader(ds, batch_size=1)))
+    assert ilens.tolist() == [500, 410] and mix.shape == (2, 500) and src.shape == (2, 2, 500)
