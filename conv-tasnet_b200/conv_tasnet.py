@@ -146,17 +146,22 @@ class ConvTasNet(nn.Module):
         return eng
 
     @torch.no_grad()
-    def separate(self, mixture, out=None):
+    def separate(self, mixture, out=None, wait=True):
         """Inference from host memory to host memory (the loop of separate.py:60-71 moves every batch to
         the GPU and every estimate back with blocking copies): mixture is a CPU float32 [M, T] tensor,
         ideally pinned; returns a pinned CPU [M, C, T] tensor (or fills `out`).  Host-device copies of
-        neighbouring micro-batches overlap the kernels.  The call returns after the result has arrived."""
+        neighbouring micro-batches overlap the kernels.  The call returns after the result has arrived.
+        wait=False returns (out, event) at once instead: `out` is complete when `event.synchronize()`
+        returns (event is None for an empty batch), and consecutive calls pipeline -- one call's copy-out
+        runs under the next call's kernels.  Neither `mixture` nor `out` may be touched before that."""
         params = self._params()
         if is_bn(self.norm_type) and self.training:
             raise NotImplementedError("norm_type=%r (BatchNorm1d) is implemented for inference only" % (self.norm_type,))
         dev = next(iter(params.values())).device
         if dev.type != "cuda":
             raise RuntimeError("the model must be on a CUDA device: this implementation has no CPU path")
+        if not wait:
+            return self.engine().forward_host(mixture, params, out, join=False)
         res = self.engine().forward_host(mixture, params, out)
         torch.cuda.current_stream(dev).synchronize()
         return res

@@ -10,11 +10,12 @@ flat fp32 buffer -- the buffer the data-parallel allreduce then reduces in one
 NCCL call (ctn_b200/_dist.py).
 """
 import ctypes as C
+import weakref
 
 import torch
 
 from . import _native as nat
-from ._engine import _MASK, _NORM, _Prepared, _check_cfg, aligned_params
+from ._engine import _MASK, _NORM, PlanCache, _Prepared, _check_cfg, aligned_params
 from ._layout import block_keys, frame_geometry, param_spec
 
 
@@ -138,6 +139,8 @@ class TrainPlan:
         self.est = e(M, C_, T, **f32)
         self.g_est = e(M, C_, T, **f32)
         self.fwd_graph = self.bwd_graph = None
+        self.fwd_runs = self.bwd_runs = 0
+        self.owner, self.done = None, True      # weakref to the autograd ctx whose activations are saved here
 
     # ------------------------------------------------------------------ helpers
     def grad_ptr(self, key):
@@ -169,7 +172,8 @@ class TrainPlan:
             r.src_off[i], r.len[i], r.src_stride[i], r.dst[i], r.dst_stride[i] = so, ln, ss, dp, ds
         self._keep.append(r)
         fn, ref = nat.lib().ctn_reduce_partials, C.byref(r)
-        return lambda s: fn(ref, s)
+        nbytes = sum(4.0 * n_part * ln for (_, n_part, _, _, ln, _, _, _) in segs)
+        return self._tag(lambda s: fn(ref, s), "bwd_reduce_partials", 0.0, nbytes)
 
     def _wgrad(self, x_hl, y_hl, Ci, Cj, dst_key, part=None):
         """G = x^T y over all rows -> grad of `dst_key` ([Ci, Cj] row-major).
@@ -181,7 +185,13 @@ class TrainPlan:
         a = (x_hl[0].data_ptr(), x_hl[1].data_ptr(), y_hl[0].data_ptr(), y_hl[1].data_ptr(), Rr, Ci, Cj,
              part.data_ptr(), 0)
         fn = lib.ctn_wgrad
-        return (lambda s, a=a: fn(*a, s)), (part, S, Ci * Cj, 0, Ci * Cj, 1, self.grad_ptr(dst_key), 1)
+        call = self._tag(lambda s, a=a: fn(*a, s), "bwd_wgrad", 2.0 * Rr * Ci * Cj, 4.0 * Rr * (Ci + Cj))
+        return call, (part, S, Ci * Cj, 0, Ci * Cj, 1, self.grad_ptr(dst_key), 1)
+
+    def _tag(self, call, kind, flops, nbytes):
+        """Registers (kind, algorithmic FLOPs, algorithmic HBM bytes) of one launch for launch_timed()."""
+        self.meta[call] = (kind, float(flops), float(nbytes))
+        return call
 
     # ------------------------------------------------------------- call lists
     def build(self, params, prep, prep_b):
@@ -190,6 +200,8 @@ class TrainPlan:
         M, K, T, NB = self.M, self.K, self.T, self.NB
         lib = nat.lib()
         self._keep = []
+        self.meta = {}
+        tag, Rr = self._tag, M * K
         GLN = self.norm                      # the block norm (gLN or cLN)
         is_gln = self.norm == nat.NORM_GLN
         causal = int(bool(cfg["causal"]))
@@ -204,10 +216,11 @@ class TrainPlan:
         enc = lib.ctn_encoder_fwd
         ea = (self.mix.data_ptr(), U.data_ptr(), M, T, N, L, self.w.data_ptr(), self.w_hl[0].data_ptr(),
               self.w_hl[1].data_ptr(), self.rowstat0.data_ptr())
-        fwd.append(lambda s, a=ea: enc(*a, s))
-        fwd.append(self._gemm(Cin=N, Cout=B, a_hi=self.w_hl[0], a_lo=self.w_hl[1], w_hi=prep.bott[0],
-                              w_lo=prep.bott[1], col_g=prep.bott[2], col_bias=prep.bott[3], in_norm=nat.NORM_CLN,
-                              in_stat=self.rowstat0, out_f32=self.x, out_hi=self.x_hl[0][0], out_lo=self.x_hl[0][1]))
+        fwd.append(tag(lambda s, a=ea: enc(*a, s), "fwd_encoder", 2.0 * Rr * N * L, 4.0 * M * T + 8.0 * Rr * N))
+        fwd.append(tag(self._gemm(Cin=N, Cout=B, a_hi=self.w_hl[0], a_lo=self.w_hl[1], w_hi=prep.bott[0],
+                                  w_lo=prep.bott[1], col_g=prep.bott[2], col_bias=prep.bott[3], in_norm=nat.NORM_CLN,
+                                  in_stat=self.rowstat0, out_f32=self.x, out_hi=self.x_hl[0][0],
+                                  out_lo=self.x_hl[0][1]), "fwd_gemm_bottleneck", 2.0 * Rr * N * B, Rr * (4.0 * N + 8.0 * B)))
         dw = lib.ctn_dwconv_fwd
         blocks = []
         i = 0
@@ -216,9 +229,10 @@ class TrainPlan:
                 k = block_keys(r, xb, cfg["causal"])
                 blocks.append((i, xb, k))
                 pb = prep.blocks[i]
-                fwd.append(self._gemm(Cin=B, Cout=H, a_hi=self.x_hl[i][0], a_lo=self.x_hl[i][1], w_hi=pb["w1"][0],
-                                      w_lo=pb["w1"][1], out_f32=self.a[i], out_stat=GLN,
-                                      out_stat_buf=self.stat1[i], stat_prelu=params[k["a1"]]))
+                fwd.append(tag(self._gemm(Cin=B, Cout=H, a_hi=self.x_hl[i][0], a_lo=self.x_hl[i][1], w_hi=pb["w1"][0],
+                                          w_lo=pb["w1"][1], out_f32=self.a[i], out_stat=GLN,
+                                          out_stat_buf=self.stat1[i], stat_prelu=params[k["a1"]]),
+                               "fwd_gemm_conv1x1", 2.0 * Rr * B * H, Rr * (4.0 * B + 4.0 * H)))
                 d = nat.DwconvArgs()
                 d.M, d.K, d.H, d.P, d.dilation, d.causal = M, K, H, P, 2 ** xb, causal
                 d.inp, d.prelu_in = self.a[i].data_ptr(), params[k["a1"]].data_ptr()
@@ -229,14 +243,16 @@ class TrainPlan:
                 d.out_hi, d.out_lo = self.q_hl[0].data_ptr(), self.q_hl[1].data_ptr()
                 d.out_stat = self.stat2[i].data_ptr()
                 self._keep.append(d)
-                fwd.append(lambda s, ref=C.byref(d): dw(ref, s))
-                fwd.append(self._gemm(Cin=H, Cout=B, a_hi=self.q_hl[0], a_lo=self.q_hl[1], w_hi=pb["w2"][0],
-                                      w_lo=pb["w2"][1], col_g=pb["w2"][2], col_bias=pb["w2"][3], in_norm=GLN,
-                                      in_stat=self.stat2[i], in_P=self.P2s[xb], in_count=count, resid=self.x,
-                                      out_f32=self.x, out_hi=self.x_hl[i + 1][0], out_lo=self.x_hl[i + 1][1]))
+                fwd.append(tag(lambda s, ref=C.byref(d): dw(ref, s), "fwd_dwconv", 2.0 * Rr * H * P, 12.0 * Rr * H))
+                fwd.append(tag(self._gemm(Cin=H, Cout=B, a_hi=self.q_hl[0], a_lo=self.q_hl[1], w_hi=pb["w2"][0],
+                                          w_lo=pb["w2"][1], col_g=pb["w2"][2], col_bias=pb["w2"][3], in_norm=GLN,
+                                          in_stat=self.stat2[i], in_P=self.P2s[xb], in_count=count, resid=self.x,
+                                          out_f32=self.x, out_hi=self.x_hl[i + 1][0], out_lo=self.x_hl[i + 1][1]),
+                               "fwd_gemm_pointwise", 2.0 * Rr * B * H, Rr * (4.0 * H + 12.0 * B)))
                 i += 1
-        fwd.append(self._gemm(Cin=B, Cout=C_ * N, a_hi=self.x_hl[NB][0], a_lo=self.x_hl[NB][1], w_hi=prep.mask[0],
-                              w_lo=prep.mask[1], out_f32=self.score))
+        fwd.append(tag(self._gemm(Cin=B, Cout=C_ * N, a_hi=self.x_hl[NB][0], a_lo=self.x_hl[NB][1], w_hi=prep.mask[0],
+                                  w_lo=prep.mask[1], out_f32=self.score),
+                       "fwd_gemm_mask", 2.0 * Rr * B * C_ * N, Rr * (4.0 * B + 4.0 * C_ * N)))
         self.fwd_calls = fwd
         self.dec_args = (self.score.data_ptr(), self.w.data_ptr(), V.data_ptr(), M, K, N, L, C_, T,
                          _MASK[cfg["mask_nonlinear"]])
@@ -251,8 +267,9 @@ class TrainPlan:
         bwd.append(self._reduce_multi([
             (self.dV_part, M * self.tiles_db, L * N, 0, L * N, 1, self.grad_ptr("decoder.basis_signals.weight"), 1),
             seg_mask]))
-        bwd.append(self._gemm(Cin=C_ * N, Cout=B, a_hi=self.ds_hl[0], a_lo=self.ds_hl[1], w_hi=prep_b.mask_t[0],
-                              w_lo=prep_b.mask_t[1], out_f32=self.g, out_hi=self.g_hl[0], out_lo=self.g_hl[1]))
+        bwd.append(tag(self._gemm(Cin=C_ * N, Cout=B, a_hi=self.ds_hl[0], a_lo=self.ds_hl[1], w_hi=prep_b.mask_t[0],
+                                  w_lo=prep_b.mask_t[1], out_f32=self.g, out_hi=self.g_hl[0], out_lo=self.g_hl[1]),
+                       "bwd_gemm_mask_dgrad", 2.0 * Rr * B * C_ * N, Rr * (4.0 * C_ * N + 8.0 * B)))
         ns, bd, pn = lib.ctn_norm_split, lib.ctn_bwd_dwconv, lib.ctn_bwd_prelu_norm
         pn_cln = lib.ctn_bwd_prelu_norm_cln
         for (i, xb, k) in reversed(blocks):
@@ -266,12 +283,13 @@ class TrainPlan:
             # orders it behind the previous block's last dgrad GEMM, which reads hl_H (as da)
             call, seg_w2 = self._wgrad(self.g_hl, self.hl_H, B, H, k["w2"])              # dW2 = g^T u
             bwd.append(_FORK)
-            bwd.append((_SIDE, lambda s, a=a_: ns(*a, s)))                              # u (hi, lo)
+            bwd.append((_SIDE, tag(lambda s, a=a_: ns(*a, s), "bwd_norm_split", 4.0 * Rr * H, 8.0 * Rr * H)))   # u (hi, lo)
             bwd.append((_SIDE, call))
-            bwd.append(self._gemm(Cin=B, Cout=H, a_hi=self.g_hl[0], a_lo=self.g_hl[1], w_hi=pb["w2t"][0],
-                                  w_lo=pb["w2t"][1], out_f32=self.du, out_stat=GLN, out_stat_buf=self.bstat,
-                                  bw_pre=self.d[i], bw_gamma=params[k["g2"]], bw_slope=params[k["a2"]],
-                                  bw_stat=self.stat2[i], bw_P=P2))                        # du = g W2 (+ S1, S2)
+            bwd.append(tag(self._gemm(Cin=B, Cout=H, a_hi=self.g_hl[0], a_lo=self.g_hl[1], w_hi=pb["w2t"][0],
+                                      w_lo=pb["w2t"][1], out_f32=self.du, out_stat=GLN, out_stat_buf=self.bstat,
+                                      bw_pre=self.d[i], bw_gamma=params[k["g2"]], bw_slope=params[k["a2"]],
+                                      bw_stat=self.stat2[i], bw_P=P2),                    # du = g W2 (+ S1, S2)
+                           "bwd_gemm_dgrad_pointwise", 2.0 * Rr * B * H, Rr * (4.0 * B + 8.0 * H)))
             b = nat.BwdDwArgs()
             b.M, b.K, b.H, b.P, b.dilation, b.causal = M, K, H, P, 2 ** xb, causal
             b.P1, b.P2, b.Pb = self.P1, P2, self.P1
@@ -282,19 +300,19 @@ class TrainPlan:
             b.dn1, b.chan_part, b.scal_part = self.dn1.data_ptr(), self.chan_part.data_ptr(), self.scal_part.data_ptr()
             b.norm = self.norm
             self._keep.append(b)
-            bwd.append(lambda s, ref=C.byref(b): bd(ref, s))
+            bwd.append(tag(lambda s, ref=C.byref(b): bd(ref, s), "bwd_dwconv", 4.0 * Rr * H * P, 16.0 * Rr * H))
             bwd.append(_JOIN)     # dW2 has consumed u before da overwrites hl_H
             if is_gln:
                 a_ = (self.dn1.data_ptr(), self.a[i].data_ptr(), self.stat1[i].data_ptr(), self.P1,
                       self.scal_part.data_ptr(), self.bd_ctas[xb], params[k["g1"]].data_ptr(),
                       params[k["a1"]].data_ptr(), M, K, H, self.hl_H[0].data_ptr(), self.hl_H[1].data_ptr(),
                       self.alpha_part.data_ptr())
-                bwd.append(lambda s, a=a_: pn(*a, s))                                   # da (hi, lo)
+                bwd.append(tag(lambda s, a=a_: pn(*a, s), "bwd_prelu_norm", 6.0 * Rr * H, 12.0 * Rr * H))   # da (hi, lo)
             else:
                 a_ = (self.dn1.data_ptr(), self.a[i].data_ptr(), self.stat1[i].data_ptr(), self.P1,
                       params[k["g1"]].data_ptr(), params[k["a1"]].data_ptr(), M, K, H,
                       self.hl_H[0].data_ptr(), self.hl_H[1].data_ptr(), self.alpha_part.data_ptr())
-                bwd.append(lambda s, a=a_: pn_cln(*a, s))
+                bwd.append(tag(lambda s, a=a_: pn_cln(*a, s), "bwd_prelu_norm", 6.0 * Rr * H, 12.0 * Rr * H))
             call, seg_w1 = self._wgrad(self.hl_H, self.x_hl[i], H, B, k["w1"], self.wg_part2)   # dW1 = da^T x
             bwd.append(_FORK)
             bwd.append((_SIDE, call))
@@ -311,25 +329,27 @@ class TrainPlan:
             else:                                   # P > 3
                 bwd.append((_SIDE, self._reduce_multi(segs[:nat.MAX_SEG])))
                 bwd.append((_SIDE, self._reduce_multi(segs[nat.MAX_SEG:] + [seg_w2, seg_w1])))
-            bwd.append(self._gemm(Cin=H, Cout=B, a_hi=self.hl_H[0], a_lo=self.hl_H[1], w_hi=pb["w1t"][0],
-                                  w_lo=pb["w1t"][1], resid=self.g, out_f32=self.g, out_hi=self.g_hl[0],
-                                  out_lo=self.g_hl[1]))                                   # g = da W1 + g
+            bwd.append(tag(self._gemm(Cin=H, Cout=B, a_hi=self.hl_H[0], a_lo=self.hl_H[1], w_hi=pb["w1t"][0],
+                                      w_lo=pb["w1t"][1], resid=self.g, out_f32=self.g, out_hi=self.g_hl[0],
+                                      out_lo=self.g_hl[1]),                               # g = da W1 + g
+                           "bwd_gemm_dgrad_conv1x1", 2.0 * Rr * B * H, Rr * (4.0 * H + 12.0 * B)))
         # bottleneck + leading cLN + encoder
         bwd.append(_JOIN)
         a_ = (self.w.data_ptr(), None, g0.data_ptr(), b0.data_ptr(), nat.NORM_CLN, self.rowstat0.data_ptr(), 1,
               M, K, N, self.w_hl[0].data_ptr(), self.w_hl[1].data_ptr())
-        bwd.append(lambda s, a=a_: ns(*a, s))                                           # n0 (hi, lo) over w_hl
+        bwd.append(tag(lambda s, a=a_: ns(*a, s), "bwd_norm_split", 4.0 * Rr * N, 8.0 * Rr * N))   # n0 (hi, lo) over w_hl
         call, seg_wb = self._wgrad(self.g_hl, self.w_hl, B, N, "separator.network.1.weight")
         bwd.append(call)
-        bwd.append(self._gemm(Cin=B, Cout=N, a_hi=self.g_hl[0], a_lo=self.g_hl[1], w_hi=prep_b.bott_t[0],
-                              w_lo=prep_b.bott_t[1], out_f32=self.dn0))
+        bwd.append(tag(self._gemm(Cin=B, Cout=N, a_hi=self.g_hl[0], a_lo=self.g_hl[1], w_hi=prep_b.bott_t[0],
+                                  w_lo=prep_b.bott_t[1], out_f32=self.dn0),
+                       "bwd_gemm_dgrad_bottleneck", 2.0 * Rr * B * N, Rr * (4.0 * B + 4.0 * N)))
         cb = lib.ctn_cln_bwd
         a_ = (self.dn0.data_ptr(), self.w.data_ptr(), self.rowstat0.data_ptr(), g0.data_ptr(),
               self.dw_dec.data_ptr(), M, K, N, self.dpre.data_ptr(), self.cb_part.data_ptr())
-        bwd.append(lambda s, a=a_: cb(*a, s))
+        bwd.append(tag(lambda s, a=a_: cb(*a, s), "bwd_cln", 8.0 * Rr * N, 16.0 * Rr * N))
         ew = lib.ctn_encoder_wgrad
         a_ = (self.dpre.data_ptr(), self.mix.data_ptr(), M, T, N, L, self.dU_part.data_ptr())
-        bwd.append(lambda s, a=a_: ew(*a, s))
+        bwd.append(tag(lambda s, a=a_: ew(*a, s), "bwd_encoder_wgrad", 2.0 * Rr * N * L, 4.0 * Rr * N + 4.0 * M * T))
         ncb = M * self.tiles_cb
         bwd.append(self._reduce_multi([
             seg_wb,
@@ -381,6 +401,32 @@ class TrainPlan:
                 check(c(s))
         assert not pending
 
+    def launch_timed(self):
+        """Profiling aid: one forward + backward on ONE stream (no side-stream overlap) with a CUDA event pair
+        around every launch.  Returns [(kind, algorithmic FLOPs, algorithmic bytes, milliseconds)]; est is
+        fed back as its own gradient (the timing does not depend on the values)."""
+        s, lib = nat.stream(), nat.lib()
+        cfg, M, K, T = self.cfg, self.M, self.K, self.T
+        N, L, C_ = cfg["N"], cfg["L"], cfg["C"]
+        Rr = M * K
+        dec_meta = ("fwd_decoder", 2.0 * Rr * C_ * N * L, 4.0 * Rr * N * (C_ + 1) + 4.0 * M * C_ * T)
+        decb_meta = ("bwd_decoder", 6.0 * Rr * C_ * N * L, Rr * N * (4.0 * (C_ + 1) + 4.0 * C_ + 4.0) + 4.0 * M * C_ * T)
+        seq = [(c, self.meta.get(c, ("other", 0.0, 0.0))) for c in self.fwd_calls]
+        seq.append((lambda st: lib.ctn_decoder_fwd(*self.dec_args, self.est.data_ptr(), st), dec_meta))
+        seq.append((lambda st: lib.ctn_decoder_bwd(self.est.data_ptr(), *self.dec_bwd_args, st), decb_meta))
+        for c in self.bwd_calls:
+            if c is _FORK or c is _JOIN:
+                continue
+            c = c[1] if isinstance(c, tuple) else c
+            seq.append((c, self.meta.get(c, ("other", 0.0, 0.0))))
+        evs = [torch.cuda.Event(enable_timing=True) for _ in range(len(seq) + 1)]
+        evs[0].record()
+        for i, (c, _) in enumerate(seq):
+            nat.check(c(s))
+            evs[i + 1].record()
+        torch.cuda.synchronize(self.device)
+        return [(m[0], m[1], m[2], evs[i].elapsed_time(evs[i + 1])) for i, (_, m) in enumerate(seq)]
+
     def _capture(self, launch):
         launch()                                   # warm-up outside capture (attribute setup, lazy loading)
         torch.cuda.synchronize(self.device)
@@ -391,8 +437,9 @@ class TrainPlan:
 
     def run_forward(self, use_graph):
         """mix -> est (static buffers).  Returns the number of kernels launched."""
-        if not use_graph:
-            self._launch_forward()
+        self.fwd_runs += 1
+        if not use_graph or (self.fwd_graph is None and self.fwd_runs < 2):
+            self._launch_forward()     # a shape is captured the second time it is seen (see _engine._Plan.run)
         else:
             if self.fwd_graph is None:
                 self.fwd_graph = self._capture(self._launch_forward)
@@ -401,7 +448,8 @@ class TrainPlan:
 
     def run_backward(self, use_graph):
         """g_est -> flat_grad (static buffers)."""
-        if not use_graph:
+        self.bwd_runs += 1
+        if not use_graph or (self.bwd_graph is None and self.bwd_runs < 2):
             self._launch_backward()
         else:
             if self.bwd_graph is None:
@@ -418,7 +466,8 @@ class TrainEngine:
 
     def __init__(self, cfg):
         self.cfg = dict(cfg)
-        self.plans, self.prep, self.prep_b = {}, {}, {}
+        # bounded: solver.py:96-97 validates with gradients enabled, one new (M, T) per minibatch
+        self.plans, self.prep, self.prep_b = PlanCache(keep=2), {}, {}
         self.launches = 0
         # data parallelism (ctn_b200/_dist.py): when set, every backward scales the flat gradient by
         # n_local / n_global and all-reduces (sum) it over this torch.distributed group, which equals
@@ -428,9 +477,23 @@ class TrainEngine:
         self.process_group = None
         self.global_batch = None       # utterances per step over all ranks (None = equal shards)
         self.last_flat_grad = None
+        self.max_pending = 4           # activation sets per shape that may await their backward at one time
         self._staged = {}              # per device: aligned copies of DataParallel replica parameters
 
     def plan(self, params, M, T, device):
+        """The plan of the first activation set of this shape that no live autograd graph is waiting on: a
+        second forward before the first one's backward (two micro-batches whose losses are summed, or a
+        train-mode forward whose graph is kept) gets its own saved activations, as autograd gives the
+        reference; sets whose graph was dropped without a backward are reused."""
+        for slot in range(self.max_pending):
+            plan = self._plan(params, M, T, device, slot)
+            owner = plan.owner() if plan.owner is not None else None
+            if owner is None or plan.done:
+                return plan
+        raise RuntimeError("ConvTasNet.forward: %d forwards of shape (%d, %d) are awaiting backward; free their "
+                           "graphs or raise train_engine().max_pending" % (self.max_pending, M, T))
+
+    def _plan(self, params, M, T, device, slot=0):
         di = device.index
         if di not in self.prep:
             self.prep[di] = _Prepared(self.cfg, device)
@@ -439,10 +502,10 @@ class TrainEngine:
         self.prep[di].refresh(self.cfg, params)
         if old != self.prep[di].fingerprint:
             self.prep_b[di].refresh(self.cfg, params)
-        key = (di, M, T, bool(self.overlap_wgrad))
+        key = (di, M, T, bool(self.overlap_wgrad), slot)
         plan = self.plans.get(key)
         if plan is None:
-            plan = self.plans[key] = TrainPlan(self.cfg, M, T, device, self.overlap_wgrad)
+            plan = self.plans.put(key, TrainPlan(self.cfg, M, T, device, self.overlap_wgrad), device)
         ptrs = tuple(p.data_ptr() for p in params.values())
         if plan.fwd_calls is None or plan.param_ptrs != ptrs:
             plan.build(params, self.prep[di], self.prep_b[di])
@@ -464,6 +527,7 @@ class _Separate(torch.autograd.Function):
             eng.launches += plan.run_forward(eng.use_graph)
             est = plan.est.clone()
         plan.generation += 1
+        plan.owner, plan.done = weakref.ref(ctx), False
         ctx.plan, ctx.generation, ctx.engine = plan, plan.generation, eng
         ctx.n_params = len(param_list)
         return est
@@ -472,14 +536,15 @@ class _Separate(torch.autograd.Function):
     def backward(ctx, g_est):
         plan = ctx.plan
         if plan.generation != ctx.generation:
-            raise RuntimeError("ConvTasNet.forward was called again with the same (batch, length) before "
-                               "backward: the saved activations of this graph were overwritten")
+            raise RuntimeError("backward through a ConvTasNet graph whose saved activations were released "
+                               "(a second backward through the same graph)")
         eng = ctx.engine
         with torch.cuda.device(plan.device):
             plan.g_est.copy_(g_est)
             eng.launches += plan.run_backward(eng.use_graph)
             # one private copy per backward: autograd may adopt the returned views as .grad
             flat = plan.flat_grad.clone()
+            plan.done = True           # the activation set is free for the next forward of this shape
             if eng.process_group is not None:
                 from . import _dist
                 _dist.reduce_flat_grad(flat, plan.M, eng.global_batch, eng.process_group)

@@ -55,6 +55,21 @@ def reduce_flat_grad(flat, n_local, n_global=None, group=None):
     return flat
 
 
+def empty_shard_step(model, group=None):
+    """The step of a rank whose shard of the minibatch is EMPTY (fewer utterances than ranks: shard_bounds gives
+    lo == hi).  Such a rank has no forward and no backward, so it would never reach the all-reduce the other
+    ranks wait in; it calls this instead: it contributes a zero flat gradient to the same collective and
+    receives the global gradient as .grad of its parameters, so its optimizer step keeps the replica in sync."""
+    ps = [p for p in model.parameters() if p.requires_grad]
+    flat = torch.zeros(sum(p.numel() for p in ps), dtype=torch.float32, device=ps[0].device)
+    dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=group)
+    off = 0
+    for p in ps:
+        p.grad = flat[off:off + p.numel()].view_as(p)
+        off += p.numel()
+    return flat
+
+
 def global_loss(local_loss, n_local, n_global=None, group=None):
     """The reference's batch-mean loss from the ranks' local means (reporting only; one
     scalar all-reduce, not on the gradient path)."""
@@ -70,6 +85,10 @@ def broadcast_parameters(model, src=0, group=None):
             dist.broadcast(p.data, src=src, group=group)
         for b in model.buffers():
             dist.broadcast(b.data, src=src, group=group)
+        # `.data` writes do not advance the version counters the engines key their prepared weights on
+        ts = list(model.parameters()) + list(model.buffers())
+        if ts:
+            torch.autograd.graph.increment_version(ts)
 
 
 def attach(model, group=None, global_batch=None, broadcast=True):

@@ -60,6 +60,73 @@ def aligned_params(store, params, device):
     return bufs
 
 
+def _tensor_bytes(obj, seen):
+    if isinstance(obj, torch.Tensor):
+        st = obj.untyped_storage()
+        if st.data_ptr() in seen:
+            return 0
+        seen.add(st.data_ptr())
+        return st.nbytes()
+    if isinstance(obj, (list, tuple)):
+        return sum(_tensor_bytes(o, seen) for o in obj)
+    if isinstance(obj, dict):
+        return sum(_tensor_bytes(o, seen) for o in obj.values())
+    return 0
+
+
+class PlanCache:
+    """Shape-keyed plans (workspaces, call lists, CUDA graphs) with a byte budget: least recently used plans are
+    dropped once the cached workspaces exceed `limit_bytes`.  The reference's callers produce one tensor
+    shape per utterance length -- solver.py:96-97 validates with gradients enabled on the unsegmented loader,
+    evaluate.py / separate.py see ~3000 distinct lengths -- and a training plan holds the saved activations of
+    every block (about 0.8 GB per utterance of 6 s at the paper configuration), so an unbounded cache runs out
+    of memory after a few dozen lengths.  The `keep` most recent plans always stay (the slots of one
+    pipelined call are in use at the same time).  An evicted plan that an autograd graph still references
+    lives until that graph is freed."""
+
+    def __init__(self, limit_bytes=None, keep=4):
+        from collections import OrderedDict
+        self.plans = OrderedDict()
+        self.bytes = {}
+        self.limit_bytes = limit_bytes      # None = a quarter of the device's memory, resolved at first use
+        self.keep = keep
+        self.evictions = 0
+
+    def __len__(self):
+        return len(self.plans)
+
+    def __contains__(self, key):
+        return key in self.plans
+
+    def values(self):
+        return self.plans.values()
+
+    def clear(self):
+        self.plans.clear()
+        self.bytes.clear()
+
+    def get(self, key):
+        plan = self.plans.get(key)
+        if plan is not None:
+            self.plans.move_to_end(key)
+        return plan
+
+    def total_bytes(self):
+        return sum(self.bytes.values())
+
+    def put(self, key, plan, device):
+        if self.limit_bytes is None:
+            self.limit_bytes = torch.cuda.get_device_properties(device).total_memory // 4
+        self.plans[key] = plan
+        self.bytes[key] = _tensor_bytes(plan.__dict__, set())
+        total = self.total_bytes()
+        while total > self.limit_bytes and len(self.plans) > self.keep:
+            old, _ = self.plans.popitem(last=False)
+            total -= self.bytes.pop(old)
+            self.evictions += 1
+        return plan
+
+
 class _Prepared:
     """Weight-derived buffers: bf16 (hi, lo) splits with the preceding norm's affine folded in."""
 
@@ -172,6 +239,8 @@ class _Plan:
         self.calls = None
         self.param_ptrs = None
         self.graph = None
+        self.runs = 0
+        self.computed = self.drained = None     # events of the host-to-host pipeline (forward_host)
         self._keep = []
 
     def _gemm(self, **kw):
@@ -315,8 +384,12 @@ class _Plan:
         torch.cuda.synchronize(self.device)
         return [(k, f, b, evs[i].elapsed_time(evs[i + 1])) for i, (k, f, b) in enumerate(self.call_info)]
 
-    def run(self, use_graph):
-        if not use_graph:
+    def run(self, use_graph, capture_now=False):
+        """A shape is captured into a CUDA graph the SECOND time it runs (or at once with capture_now):
+        warm-up + capture cost three passes, which a length seen once (evaluate.py / separate.py over a corpus
+        of distinct utterance lengths) never earns back."""
+        self.runs += 1
+        if not use_graph or (self.graph is None and self.runs < 2 and not capture_now):
             self.launch()
             return
         if self.graph is None:
@@ -336,7 +409,7 @@ class SeparationEngine:
         _check_cfg(cfg)
         self.cfg = dict(cfg)
         self.prepared = {}
-        self.plans = {}
+        self.plans = PlanCache()
         self.micro_batch = 16
         self.use_graph = False
         # blocks with dilation <= this take the fused depthwise + pointwise kernel where the configuration
@@ -350,6 +423,7 @@ class SeparationEngine:
         # (residual update, decoder) and kernel tails overlap the other chain's tensor-bound GEMMs
         self.n_streams = 1
         self._streams = {}
+        self._host_slot = 0   # workspace slot of the next forward_host micro-batch (alternates across calls)
         self._staged = {}   # per device: aligned copies of unaligned (DataParallel replica) parameters
         self.launches = 0   # kernels of libctn_b200 launched by forward() so far
 
@@ -369,7 +443,7 @@ class SeparationEngine:
         prep.refresh(self.cfg, params)
         plan = self.plans.get(key)
         if plan is None:
-            plan = self.plans[key] = _Plan(self.cfg, M, T, device, self.fuse_max_dilation, self.fuse_update)
+            plan = self.plans.put(key, _Plan(self.cfg, M, T, device, self.fuse_max_dilation, self.fuse_update), device)
         ptrs = tuple(p.data_ptr() for p in params.values())
         if plan.calls is None or plan.param_ptrs != ptrs:
             plan.build(params, prep)
@@ -378,12 +452,17 @@ class SeparationEngine:
         return plan
 
     @torch.no_grad()
-    def forward_host(self, mixture, params, out=None):
+    def forward_host(self, mixture, params, out=None, join=True):
         """Bulk separation from HOST memory to HOST memory (BASELINE configs[3]): mixture is a CPU
         float32 [M, T] tensor (pinned for asynchronous copies), the result a pinned CPU [M, C, T] tensor.
         Micro-batch i+1 is copied in and micro-batch i-1 copied out on two copy streams while micro-batch
         i computes (two workspace slots), so PCIe time disappears behind the kernels instead of adding
-        to them.  Stream-ordered on the current stream: synchronise it before reading `out`."""
+        to them.  The slots alternate ACROSS calls as well and the per-slot events persist, so with
+        join=False consecutive calls pipeline: the copy-out of one call overlaps the compute of the next even
+        when a call is a single micro-batch (512 mixtures over 8 GPUs = one 64-utterance micro-batch per rank).
+        join=True: stream-ordered on the current stream (synchronise it before reading `out`).
+        join=False: returns (out, event); `out` is complete when the event, recorded on the copy-out stream,
+        has completed, and the caller must not reuse `mixture` / `out` before that."""
         if mixture.is_cuda or mixture.dim() != 2 or mixture.dtype != torch.float32:
             raise RuntimeError("mixture must be a CPU float32 [M, T] tensor (use forward() for CUDA tensors)")
         M, T = mixture.shape
@@ -396,17 +475,19 @@ class SeparationEngine:
         elif out.is_cuda or tuple(out.shape) != (M, cfg["C"], T) or out.dtype != torch.float32 or not out.is_contiguous():
             raise RuntimeError("out must be a contiguous CPU float32 [M, C, T] tensor")
         if M == 0:
-            return out
+            return out if join else (out, None)
         with torch.cuda.device(device):
             params = aligned_params(self._staged, params, device)
             mb = max(1, int(self.micro_batch))
             chunks = [(m0, min(M, m0 + mb)) for m0 in range(0, M, mb)]
-            plans = [self._plan(params, m1 - m0, T, device, slot=i % 2) for i, (m0, m1) in enumerate(chunks)]
+            first = self._host_slot
+            self._host_slot = (first + len(chunks)) % 2
+            plans = [self._plan(params, m1 - m0, T, device, slot=(first + i) % 2) for i, (m0, m1) in enumerate(chunks)]
             cur = torch.cuda.current_stream(device)
             if self.use_graph:
                 for plan in plans:
                     if plan.graph is None:
-                        plan.run(True)      # capture (and one replay) before the pipeline starts
+                        plan.run(True, capture_now=True)      # capture (and one replay) before the pipeline starts
             side = self._streams.setdefault(("io", device.index), [])
             while len(side) < 2:
                 side.append(torch.cuda.Stream(device=device))
@@ -414,24 +495,27 @@ class SeparationEngine:
             start = cur.record_event()
             s_in.wait_event(start)
             s_out.wait_event(start)
-            computed = {}    # plan -> event: its last compute has finished (mix may be overwritten)
-            drained = {}     # plan -> event: its last result has left the device (est may be overwritten)
+            last = None
             for (m0, m1), plan in zip(chunks, plans):
+                # plan.computed: its last compute has finished (mix may be overwritten);
+                # plan.drained: its last result has left the device (est may be overwritten)
                 with torch.cuda.stream(s_in):
-                    if plan in computed:
-                        s_in.wait_event(computed[plan])
+                    if plan.computed is not None:
+                        s_in.wait_event(plan.computed)
                     plan.mix.copy_(mixture[m0:m1], non_blocking=True)
                     loaded = s_in.record_event()
                 cur.wait_event(loaded)
-                if plan in drained:
-                    cur.wait_event(drained[plan])
+                if plan.drained is not None:
+                    cur.wait_event(plan.drained)
                 plan.run(self.use_graph)
                 self.launches += len(plan.calls)
-                computed[plan] = cur.record_event()
+                plan.computed = cur.record_event()
                 with torch.cuda.stream(s_out):
-                    s_out.wait_event(computed[plan])
+                    s_out.wait_event(plan.computed)
                     out[m0:m1].copy_(plan.est, non_blocking=True)
-                    drained[plan] = s_out.record_event()
+                    plan.drained = last = s_out.record_event()
+            if not join:
+                return out, last
             cur.wait_stream(s_out)
             cur.wait_stream(s_in)
         return out
@@ -459,6 +543,9 @@ class SeparationEngine:
                 for m0 in range(0, M, mb):
                     m1 = min(M, m0 + mb)
                     plan = self._plan(params, m1 - m0, T, device)
+                    if plan.drained is not None:      # an un-joined forward_host may still be copying est out
+                        torch.cuda.current_stream(device).wait_event(plan.drained)
+                        plan.drained = None
                     plan.mix.copy_(mixture[m0:m1])
                     plan.run(self.use_graph)
                     self.launches += len(plan.calls)
@@ -475,13 +562,16 @@ class SeparationEngine:
             if self.use_graph:
                 for plan in plans:
                     if plan.graph is None:
-                        plan.run(True)      # capture (and one replay) on the caller's stream
+                        plan.run(True, capture_now=True)      # capture (and one replay) on the caller's stream
             ready = cur.record_event()
             for i, ((m0, m1), plan) in enumerate(zip(chunks, plans)):
                 st = side[i % n_str]
                 if i < n_str:
                     st.wait_event(ready)
                 with torch.cuda.stream(st):
+                    if plan.drained is not None:
+                        st.wait_event(plan.drained)
+                        plan.drained = None
                     plan.mix.copy_(mixture[m0:m1])
                     plan.run(self.use_graph)
                     out[m0:m1].copy_(plan.est)

@@ -160,5 +160,9 @@ class FusedAdam(torch.optim.Optimizer):
                 self._table.data_ptr(), self._n_chunks, self._partials.data_ptr(),
                 float(self.max_norm) if self.max_norm is not None else 0.0, step_size, b1, b2, inv_sqrt_bias2,
                 g["eps"], g["weight_decay"], int(self.write_clipped_grad), self.total_norm.data_ptr(), nat.stream()))
+        # the kernel wrote the parameters through raw device pointers: bump their version counters, which is
+        # what the engines' prepared (bf16 split / norm-folded / transposed) weight copies are keyed on
+        # (_engine._Prepared.refresh), exactly as an in-place torch update would have
+        torch.autograd.graph.increment_version(ps)
         self._step_t += 1      # host tensor, as torch.optim.Adam keeps it by default
         return loss

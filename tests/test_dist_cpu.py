@@ -101,3 +101,34 @@ def test_shard_minibatch_partitions_dataset_items():
         assert max(sizes) - min(sizes) <= 1
     ev = _dist.shard_minibatch([mix, 8000], 2, 1)
     assert ev == [mix[3:], 8000]
+
+
+def _empty_worker(rank, world, port, out):
+    from ctn_b200 import _dist
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        torch.manual_seed(0)
+        model = torch.nn.Linear(5, 3)          # stands for the replica: only its parameter list matters here
+        n = sum(p.numel() for p in model.parameters())
+        lo, hi = _dist.shard_bounds(1, world, rank)      # one utterance, two ranks: rank 1 is empty
+        if hi > lo:
+            flat = torch.arange(n, dtype=torch.float32) + 1.0
+            _dist.reduce_flat_grad(flat, hi - lo, 1)
+        else:
+            flat = _dist.empty_shard_step(model)
+            assert all(p.grad is not None for p in model.parameters())
+            assert torch.equal(torch.cat([p.grad.flatten() for p in model.parameters()]), flat)
+        out[rank] = flat.tolist()
+    finally:
+        dist.destroy_process_group()
+
+
+def test_rank_with_an_empty_shard_joins_the_all_reduce():
+    """Fewer utterances than ranks: the empty rank contributes zeros to the one collective of the step and ends
+    with the global gradient, instead of leaving the other ranks waiting."""
+    world = 2
+    mgr = mp.Manager()
+    out = mgr.dict()
+    mp.spawn(_empty_worker, args=(world, _free_port(), out), nprocs=world, join=True)
+    assert out[0] == out[1] == [float(i + 1) for i in range(len(out[0]))]

@@ -116,6 +116,10 @@ CONFIGS = {
                              mask_nonlinear="relu"), 1, 48000),
     "cfg5_softmax_c3": (dict(N=512, L=16, B=128, H=512, P=3, X=8, R=3, C=3, norm_type="gLN", causal=False,
                              mask_nonlinear="softmax"), 2, 32000),
+    # BASELINE configs[2] at its stated size: one 60 s stream, K = 47 999 frames (the long-accumulation case;
+    # the fp64 oracle's activations are 200 MB each on the device)
+    "cfg3_causal_cln_60s": (dict(N=256, L=20, B=256, H=512, P=3, X=8, R=4, C=2, norm_type="cLN", causal=True,
+                                 mask_nonlinear="relu"), 1, 480000),
 }
 
 
@@ -175,6 +179,31 @@ def test_fused_depthwise_pointwise_path_matches_unfused(fuse):
     assert rel_l2(fused, fused_nou) < 2e-5          # the folded update re-splits x on the fly: same tolerance as against the unfused path
     assert torch.equal(fused, fused_g)
     assert rel_l2(fused[:1], ref) < WAVE_TOL / 10
+
+
+def test_utterances_inside_a_64_utterance_fused_micro_batch_match_the_oracle():
+    """BASELINE configs[3] runs 64-utterance micro-batches through the fused depthwise + pointwise kernel, whose
+    CTA pairs then own several tiles each and group the statistics' partial sums differently from a lone
+    utterance.  Direct comparison (not self-consistency) of utterances taken from the start, the middle and the
+    end of such a micro-batch with the fp64 oracle run on each of them alone (utterances are independent:
+    conv_tasnet.py:352-353 normalises per utterance)."""
+    cfg, _, T = CONFIGS["cfg1_paper_gln"]
+    p32 = O.random_params(*(cfg[k] for k in "NLBHPXRC"), cfg["causal"], seed=1234)
+    model = _build(cfg, p32)
+    eng = model.engine()
+    eng.micro_batch, eng.use_graph = 64, True
+    g = torch.Generator().manual_seed(2026)
+    mix = (0.1 * torch.randn(64, T, generator=g)).to(DEV)
+    p64 = {k: v.to(DEV).double() for k, v in p32.items()}
+    with torch.no_grad():
+        est = model(mix)
+        plan = eng._plan(model._params(), 64, T, mix.device)
+        assert all(plan.fused)                       # the path the bench times
+        for m in (0, 37, 63):
+            ref = O.forward(mix[m:m + 1].double(), p64, cfg)
+            err = rel_l2(est[m:m + 1], ref)
+            print("utterance", m, "of 64: rel_l2 vs fp64 oracle", err)
+            assert err < WAVE_TOL / 10
 
 
 def test_batched_equals_single_and_micro_batching():

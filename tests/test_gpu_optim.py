@@ -151,3 +151,53 @@ def test_gradients_as_views_of_a_moving_flat_buffer():
         o1.step()
         for a, b in zip(ours, ref):
             assert torch.allclose(a, b, rtol=2e-6, atol=2e-7), (it, a.shape, float((a - b).abs().max()))
+
+
+def test_fused_adam_trains_every_weight_like_torch_adam():
+    """The optimizer writes the parameters through raw device pointers; the engines' prepared weight copies
+    (bf16 splits with the norms folded in, transposed backward operands: ~95 % of the parameters) are keyed
+    on the tensors' version counters, so step() must advance them.  Two identical models, one stepped by
+    FusedAdam and one by clip_grad_norm_ + torch.optim.Adam (solver.py:183-186), must stay together on EVERY
+    tensor -- the 1x1 convolutions included -- and on the loss trajectory."""
+    import conv_tasnet
+    import pit_criterion
+    from ctn_b200.optim import FusedAdam
+    torch.manual_seed(0)
+    m1 = conv_tasnet.ConvTasNet(64, 16, 64, 128, 3, 3, 2, 2).to(DEV).train()
+    m2 = copy.deepcopy(m1)
+    o1 = FusedAdam(m1.parameters(), lr=1e-3, max_norm=5.0)
+    o2 = torch.optim.Adam(m2.parameters(), lr=1e-3)
+    g = torch.Generator().manual_seed(1)
+    src = (0.1 * torch.randn(3, 2, 4000, generator=g)).to(DEV)
+    mix = src.sum(1)
+    lens = torch.full((3,), 4000, dtype=torch.int64, device=DEV)
+    w0 = {k: v.detach().clone() for k, v in m1.state_dict().items()}
+    l1, l2 = [], []
+    for _ in range(4):
+        for model, opt, losses, clip in ((m1, o1, l1, False), (m2, o2, l2, True)):
+            est = model(mix)
+            loss, *_ = pit_criterion.cal_loss(src, est, lens)
+            opt.zero_grad()
+            loss.backward()
+            if clip:
+                torch.nn.utils.clip_grad_norm_(model.parameters(), 5.0)
+            opt.step()
+            losses.append(float(loss))
+    for a, b in zip(l1, l2):
+        assert abs(a - b) < 2e-3, (l1, l2)
+    # the losses move: a stale set of prepared weights would leave the 1x1 convolutions at their
+    # initial values inside the kernels and the two trajectories would part from step 2 on
+    assert abs(l1[-1] - l1[0]) > 1e-2
+    sd1, sd2 = m1.state_dict(), m2.state_dict()
+    for k in sd1:
+        # (norms, not maxima: Adam's m / sqrt(v) amplifies rounding differences of near-zero gradients)
+        step = float((sd2[k] - w0[k]).float().norm())
+        diff = float((sd1[k] - sd2[k]).float().norm())
+        assert diff <= 0.02 * step + 1e-7, (k, diff, step)
+    # and the forward really uses the updated 1x1 weights: same output as a fresh model loaded from them
+    m3 = conv_tasnet.ConvTasNet(64, 16, 64, 128, 3, 3, 2, 2).to(DEV).eval()
+    m3.load_state_dict(sd1)
+    with torch.no_grad():
+        e3 = m3(mix)
+        e1 = m1.eval()(mix)
+    assert float((e1 - e3).norm() / e3.norm()) < 1e-5

@@ -92,17 +92,30 @@ def test_gradients_demo_fixture_kink():
     assert rel_l2(flat, ref) < 2e-2
 
 
-def test_gradients_match_oracle_paper_config():
-    """cfg 2: paper model, batch 3 x 4 s, ragged lengths; oracle autograd in fp64 on the GPU."""
+GRAD_CONFIGS = {
+    # BASELINE configs[1]: paper model, batch 3 x 4 s, ragged lengths
+    "cfg2_paper": (dict(N=256, L=20, B=256, H=512, P=3, X=8, R=4, C=2, norm_type="gLN", causal=False,
+                        mask_nonlinear="relu"), 3, [32000, 24000, 16001]),
+    # BASELINE configs[4] at its stated size: N512 L16 B128 H512 X8 R3, C = 3 with the softmax mask, batch 8 x 4 s
+    # (pit_criterion.py:22 over six permutations; solver.py:183)
+    "cfg5_softmax_c3": (dict(N=512, L=16, B=128, H=512, P=3, X=8, R=3, C=3, norm_type="gLN", causal=False,
+                             mask_nonlinear="softmax"), 8, [32000, 32000, 31999, 24000, 32000, 16001, 32000, 20000]),
+}
+
+
+@pytest.mark.parametrize("name", list(GRAD_CONFIGS))
+def test_gradients_match_oracle_paper_config(name):
+    """Every parameter gradient at the BASELINE training configurations' full size against autograd over the
+    oracle in fp64 on the GPU."""
     import pit_criterion
-    cfg = dict(N=256, L=20, B=256, H=512, P=3, X=8, R=4, C=2, norm_type="gLN", causal=False, mask_nonlinear="relu")
-    M, T = 3, 32000
+    cfg, M, lens = GRAD_CONFIGS[name]
+    T = 32000
     p32 = O.random_params(*(cfg[k] for k in "NLBHPXRC"), cfg["causal"], seed=1234)
     model = _build(cfg, p32)
     g = torch.Generator().manual_seed(2025)
     src = (0.1 * torch.randn(M, cfg["C"], T, generator=g)).to(DEV)
     mix = src.sum(1)
-    lengths = torch.tensor([32000, 24000, 16001], device=DEV)
+    lengths = torch.tensor(lens, device=DEV)
     est = model(mix)
     loss, *_ = pit_criterion.cal_loss(src, est, lengths)
     loss.backward()
@@ -125,7 +138,7 @@ def test_gradients_match_oracle_paper_config():
             worst = (k, err)
     total = rel_l2(torch.cat(flat), torch.cat(flat_ref))
     slopes = rel_l2(torch.cat(sc), torch.cat(sc_ref))
-    print("paper cfg: loss", float(loss.detach()), "ref", float(loss_ref.detach()), "flat grad rel-L2", total,
+    print(name, ": loss", float(loss.detach()), "ref", float(loss_ref.detach()), "flat grad rel-L2", total,
           "worst tensor", worst, "slopes", slopes)
     assert total < 1e-3
     assert worst[1] < 5e-3
@@ -191,3 +204,56 @@ def test_backward_side_stream_overlap_is_bit_identical():
             loss.backward()
         grads.append(torch.cat([p.grad.flatten() for p in model.parameters()]).clone())
     assert torch.equal(grads[0], grads[1]) and torch.equal(grads[1], grads[2])
+
+
+def test_two_forwards_before_one_backward():
+    """Two micro-batches of the same shape whose losses are summed before a single backward (autograd lets the
+    reference do this): the second forward gets its own saved activations; the gradient is the sum of the two
+    separate gradients."""
+    import pit_criterion
+    cfg, z = load_golden("tc_small")
+    w = {k[2:]: v for k, v in z.items() if k.startswith("w:")}
+    mix, src, lens = z["mixture"].to(DEV), z["sources"].to(DEV), z["lengths"].to(DEV)
+    model = _build(cfg, w)
+    sep = []
+    for scale in (1.0, 0.5):
+        model.zero_grad()
+        loss, *_ = pit_criterion.cal_loss(src * scale, model(mix * scale), lens)
+        loss.backward()
+        sep.append(torch.cat([p.grad.flatten() for p in model.parameters()]).clone())
+    model.zero_grad()
+    l1, *_ = pit_criterion.cal_loss(src, model(mix), lens)
+    l2, *_ = pit_criterion.cal_loss(src * 0.5, model(mix * 0.5), lens)      # same (M, T): second activation set
+    (l1 + l2).backward()
+    both = torch.cat([p.grad.flatten() for p in model.parameters()])
+    assert rel_l2(both, sep[0] + sep[1]) < 1e-6
+    # a graph dropped without backward (solver.py:96-97 validates with gradients enabled) frees its set
+    eng = model.train_engine()
+    for _ in range(3 * eng.max_pending):
+        model(mix)
+    assert len(eng.plans) <= 2
+
+
+def test_plan_caches_are_bounded_over_many_lengths():
+    """One plan per distinct (M, T) -- solver.py:96-97 (validation, gradients enabled) and evaluate.py /
+    separate.py feed a new length per minibatch -- must not accumulate workspaces without bound."""
+    cfg, z = load_golden("tc_small")
+    w = {k[2:]: v for k, v in z.items() if k.startswith("w:")}
+    model = _build(cfg, w)
+    g = torch.Generator().manual_seed(4)
+    tr, inf = model.train_engine(), model.engine()
+    tr.plans.limit_bytes = inf.plans.limit_bytes = 64 << 20
+    seen = []
+    for i in range(24):
+        T = 3000 + 411 * i
+        mix = (0.1 * torch.randn(2, T, generator=g)).to(DEV)
+        est = model(mix)                              # training path: saved activations per plan
+        with torch.no_grad():
+            model.eval()(mix)
+            model.train()
+        del est
+        torch.cuda.synchronize()
+        seen.append(torch.cuda.memory_allocated())
+    assert tr.plans.evictions > 0 and inf.plans.evictions > 0
+    assert tr.plans.total_bytes() <= max(tr.plans.limit_bytes, max(tr.plans.bytes.values()) * tr.plans.keep)
+    assert max(seen[12:]) <= 1.5 * max(seen[:12]) + (64 << 20)
