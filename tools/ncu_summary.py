@@ -21,14 +21,26 @@ WANT = [
     "smsp__warp_issue_stalled_barrier_per_warp_active.pct", "smsp__warp_issue_stalled_membar_per_warp_active.pct",
     "smsp__warp_issue_stalled_short_scoreboard_per_warp_active.pct", "smsp__warp_issue_stalled_wait_per_warp_active.pct",
     "smsp__warp_issue_stalled_lg_throttle_per_warp_active.pct", "smsp__warp_issue_stalled_math_pipe_throttle_per_warp_active.pct",
-]
+    # the names this ncu (2025.2, sm_100) actually reports: tensor pipe (tcgen05 = the hmma sub-pipe) and warp stalls
+    "sm__pipe_tensor_cycles_active_realtime.avg.pct_of_peak_sustained_elapsed",
+    "sm__pipe_tensor_subpipe_hmma_cycles_active_realtime.avg",
+    "sm__inst_executed_pipe_tensor_subpipe_hmma.avg.pct_of_peak_sustained_active",
+    "sm__ops_path_tensor_op_hmma_src_bf16_dst_fp32_sparsity_off.avg.pct_of_peak_sustained_elapsed",
+    "sm__ops_path_tensor_op_hmma_src_bf16_dst_fp32_sparsity_off.sum.per_second",
+    "sm__mem_tensor_cycles_active.avg.pct_of_peak_sustained_elapsed",
+] + ["smsp__average_warps_issue_stalled_%s_per_issue_active.ratio" % r for r in (
+    "long_scoreboard", "short_scoreboard", "barrier", "membar", "wait", "sleeping", "lg_throttle", "mio_throttle",
+    "math_pipe_throttle", "tex_throttle", "dispatch_stall", "branch_resolving", "no_instruction", "not_selected",
+    "selected", "drain", "misc")]
 raw = subprocess.run(["ncu", "-i", sys.argv[1], "--page", "raw", "--csv"], capture_output=True, text=True).stdout
 rows = list(csv.reader(io.StringIO(raw)))
 hdr, units, data = rows[0], rows[1], rows[2:]
 idx = {h: i for i, h in enumerate(hdr)}
+for h, i in list(idx.items()):      # some columns carry a section prefix ("TPC.TriageCompute.sm__pipe_tensor_...")
+    idx.setdefault(h.split(".Triage")[-1].split(".", 1)[-1] if ".Triage" in h else h, i)
 print("# " + (sys.argv[2] if len(sys.argv) > 2 else sys.argv[1]))
 names = [r[idx["Kernel Name"]].split("(")[0].replace(", ", " ") for r in data]
 print("metric,unit," + ",".join("%s#%d" % (n, i) for i, n in enumerate(names)))
-for w in WANT:
+for w in dict.fromkeys(WANT):
     if w in idx:
         print("%s,%s,%s" % (w, units[idx[w]], ",".join(r[idx[w]].replace(",", "") for r in data)))

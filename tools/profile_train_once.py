@@ -11,6 +11,7 @@ if os.environ.get("CTN_CFG") == "cfg5":   # BASELINE configs[4]
     cfg = dict(N=512, L=16, B=128, H=512, P=3, X=8, R=3, C=3, norm_type="gLN", causal=False, mask_nonlinear="softmax")
 torch.manual_seed(0)
 model = conv_tasnet.ConvTasNet(**cfg).cuda().train()
+model.train_engine().use_graph = False      # plain launches: every kernel is its own ncu record
 src = 0.1 * torch.randn(M, cfg["C"], 32000, device="cuda"); mix = src.sum(1)
 lengths = torch.full((M,), 32000, device="cuda")
 for _ in range(steps):
