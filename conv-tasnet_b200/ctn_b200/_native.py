@@ -206,6 +206,11 @@ _SIGNATURES = {
                                     _vp, _vp, _vp]),
     "ctn_pit_reorder": (C.c_int, [_vp, _vp, _vp, C.c_int, C.c_int, C.c_int, _vp, _vp]),
     "ctn_bn_fold": (C.c_int, [_vp, _vp, _vp, _vp, C.c_float, C.c_int, _vp, _vp, _vp]),
+    "ctn_bn_tiles": (_i, [_ll]),
+    "ctn_bn_colsums": (_i, [_vp, _vp, _vp, _vp, _vp, _ll, _i, _vp, _vp, _vp]),
+    "ctn_bn_train_fold": (_i, [_vp, C.c_double, _vp, _vp, C.c_float, C.c_float, _i, _vp, _vp, _vp, _i, _vp, _vp, _vp,
+                               _vp, _vp]),
+    "ctn_bn_bwd_center": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, C.c_double, _i, _ll, _i, _vp, _vp, _vp]),
     "ctn_copy_table": (C.c_int, [_vp, C.c_int, C.c_longlong, _vp]),
     "ctn_pad_batch": (C.c_int, [_vp, _vp, _vp, C.c_int, C.c_int, C.c_int, C.c_float, _vp, _vp, _vp]),
     "ctn_remove_pad": (C.c_int, [_vp, _vp, C.c_int, C.c_int, C.c_int, _vp, _vp]),

@@ -377,6 +377,34 @@ int ctn_clip_adam(const ctn_opt_chunk* chunks_dev, int n_chunks, double* partial
 int ctn_bn_fold(const float* weight, const float* bias, const float* running_mean, const float* running_var, float eps,
                 int C, float* scale, float* shift, void* stream);
 
+/* ---- nn.BatchNorm1d in TRAINING mode (conv_tasnet.py:300-303; torch's batch_norm with training=True) --------
+ * Per channel c over all R = M*K rows of the batch (every frame of every utterance, padded or not):
+ *   mean[c], var[c] (biased) normalise;  running_mean / running_var move by `momentum` towards mean and the
+ *   UNBIASED variance; num_batches_tracked += 1.  The block kernels then take the folded affine
+ *   (scale = weight * rstd, shift = bias - mean * scale) in place of a gLN's (gamma, beta) with unit statistics.
+ *
+ * ctn_bn_colsums: column sums over the rows of x = PReLU(pre) (slope NULL = identity), pre fp32 [R, C]:
+ *   dy == NULL (forward):  sums[0][c] = sum x,   sums[1][c] = sum x*x
+ *   dy != NULL (backward): sums[0][c] = sum dy,  sums[1][c] = sum dy * xh,  xh = (x - mean[c]) * rstd[c]
+ * part: ctn_bn_tiles(R) * 2 * C floats of workspace; sums: 2 * C doubles (fixed-order reduction).  A data-parallel
+ * job sums `sums` over its ranks (one small all-reduce) before the next call, which makes utterance-sharded
+ * training equal to the single-process batch.
+ * ctn_bn_train_fold: statistics from sums / count (or from the running buffers when use_running != 0: eval-mode
+ *   BatchNorm inside a differentiated forward) -> scale, shift, mean, rstd [C]; updates the three buffers.
+ * ctn_bn_bwd_center: dy -= sums[0]/count + xh * sums[1]/count in place (center != 0: the two batch-mean terms
+ *   of the BatchNorm backward; the factor weight * rstd is applied by the consuming kernel as its "gamma"), and
+ *   d weight[c] = sums[1][c], d bias[c] = sums[0][c] (either may be NULL). */
+int ctn_bn_tiles(long long R);
+int ctn_bn_colsums(const float* dy, const float* pre, const float* slope, const float* mean, const float* rstd,
+                   long long R, int C, float* part, double* sums, void* stream);
+int ctn_bn_train_fold(const double* sums, double count, const float* weight, const float* bias, float eps,
+                      float momentum, int use_running, float* running_mean, float* running_var,
+                      long long* num_batches_tracked, int C, float* scale, float* shift, float* mean, float* rstd,
+                      void* stream);
+int ctn_bn_bwd_center(float* dy, const float* pre, const float* slope, const float* mean, const float* rstd,
+                      const double* sums, double count, int center, long long R, int C, float* dweight, float* dbias,
+                      void* stream);
+
 /* Table-driven device-to-device copies in one launch (state shift of the streaming separator,
  * ctn_b200/_stream.py: the frames a causal model's next chunk reaches back to).  items_dev: DEVICE array;
  * bytes must be a multiple of 4 and the pointers 4-byte aligned (16-byte aligned ranges move as 128-bit

@@ -44,3 +44,18 @@ print("metric,unit," + ",".join("%s#%d" % (n, i) for i, n in enumerate(names)))
 for w in dict.fromkeys(WANT):
     if w in idx:
         print("%s,%s,%s" % (w, units[idx[w]], ",".join(r[idx[w]].replace(",", "") for r in data)))
+# derived: tensor-pipe utilisation = cycles the (four per SM) tensor sub-pipes were active / (4 x elapsed SM cycles).
+# Cross-check on fb::dwpw_kernel: 0.455 x (148 SMs x 8192 dense bf16 flop/clk x 1.676 GHz) = 925 TFLOP/s =
+# the executed 3 x 54.3 GFLOP / 175 us.  (ncu's own pct_of_peak for this counter reads ~2 % for every
+# tcgen05 kernel: its denominator is not the tcgen05 rate.)
+ha, ce = "sm__pipe_tensor_subpipe_hmma_cycles_active_realtime.avg", "sm__cycles_elapsed.max"
+if ha in idx and ce in idx:
+    f = lambda v: float(v.replace(",", ""))
+    print("derived__tensor_pipe_utilisation,fraction,%s" % ",".join(
+        "%.4f" % (f(r[idx[ha]]) / (4.0 * f(r[idx[ce]]))) for r in data))
+    if "dram__bytes_read.sum" in idx:
+        print("derived__dram_GBps,GB/s,%s" % ",".join("%.1f" % (
+            (f(r[idx["dram__bytes_read.sum"]]) + f(r[idx["dram__bytes_write.sum"]])) *
+            {"byte": 1e-9, "Kbyte": 1e-6, "Mbyte": 1e-3, "Gbyte": 1.0}[units[idx["dram__bytes_read.sum"]]] /
+            (f(r[idx["gpu__time_duration.sum"]]) * {"ns": 1e-9, "us": 1e-6, "ms": 1e-3, "s": 1.0}[units[idx["gpu__time_duration.sum"]]])
+        ) for r in data))
