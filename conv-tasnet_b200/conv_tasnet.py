@@ -128,6 +128,19 @@ class ConvTasNet(nn.Module):
             self.__dict__["_param_slots"] = slots
         return {key: store[leaf] for key, store, leaf in slots}
 
+    def _bn_buffers(self):
+        """{state_dict key: tensor} of the BatchNorm1d buffers (running_mean, running_var, num_batches_tracked)."""
+        out = {}
+        for key, (_, kind) in param_spec(self.N, self.L, self.B, self.H, self.P, self.X, self.R, self.C, self.causal,
+                                         self.norm_type).items():
+            if kind.startswith("buf_"):
+                node = self
+                parts = key.split(".")
+                for part in parts[:-1]:
+                    node = node._modules[part]
+                out[key] = node._buffers[parts[-1]]
+        return out
+
     def engine(self):
         """The per-module kernel orchestrator (workspaces, prepared weights, CUDA graphs)."""
         eng = self.__dict__.get("_engine")
@@ -186,12 +199,13 @@ class ConvTasNet(nn.Module):
                 raise RuntimeError("parameter %s is %s on %s; float32 on %s is required (call model.cuda())"
                                    % (k, p.dtype, p.device, mixture.device))
         needs_grad = torch.is_grad_enabled() and (mixture.requires_grad or any(p.requires_grad for p in params.values()))
-        if is_bn(self.norm_type) and (self.training or needs_grad):
-            # nn.BatchNorm1d in training mode normalises with statistics over the whole batch and updates
-            # its running buffers (conv_tasnet.py:300-303); only the inference form is implemented
-            raise NotImplementedError("norm_type=%r (BatchNorm1d) is implemented for inference only: call "
-                                      "model.eval() and run under torch.no_grad()" % (self.norm_type,))
-        if needs_grad:
+        # nn.BatchNorm1d blocks (conv_tasnet.py:300-303) in train() mode normalise with the statistics of the
+        # whole batch and update their running buffers, with or without a graph: the training path does both
+        if needs_grad or (is_bn(self.norm_type) and self.training):
+            if getattr(self, "_is_replica", False) and is_bn(self.norm_type) and self.training:
+                raise NotImplementedError("BatchNorm1d training under torch.nn.DataParallel is not implemented: "
+                                          "use one process per GPU (ctn_b200._dist.attach), which also "
+                                          "synchronises the batch statistics")
             from ctn_b200 import _autograd
             return _autograd.separate(self, mixture, params)
         # the engine only takes addresses and version counters of the parameters (under no_grad): no detach

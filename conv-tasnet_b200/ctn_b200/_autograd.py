@@ -16,7 +16,10 @@ import torch
 
 from . import _native as nat
 from ._engine import _MASK, _NORM, PlanCache, _Prepared, _check_cfg, aligned_params
-from ._layout import block_keys, frame_geometry, param_spec
+from ._engine import BN_EPS
+from ._layout import block_keys, frame_geometry, is_bn, param_spec
+
+BN_MOMENTUM = 0.1   # nn.BatchNorm1d default (conv_tasnet.py:303 passes none)
 
 
 class _PreparedBwd:
@@ -55,7 +58,10 @@ class TrainPlan:
 
     def __init__(self, cfg, M, T, device, overlap=True):
         _check_cfg(cfg, training=True)
-        self.norm = _NORM[cfg["norm_type"]]
+        # BatchNorm1d blocks run through the gLN kernels with a per-channel affine and unit statistics (as in
+        # inference, _engine._Plan); csrc/bn_train.cu adds the batch statistics and the backward's mean terms
+        self.bn = is_bn(cfg["norm_type"])
+        self.norm = nat.NORM_GLN if self.bn else _NORM[cfg["norm_type"]]
         self.cfg, self.M, self.T, self.device = cfg, M, T, device
         self.overlap = bool(overlap)                 # weight gradients on a side stream (see _launch_backward)
         self.side_stream = torch.cuda.Stream(device=device) if overlap else None
@@ -121,15 +127,28 @@ class TrainPlan:
         self.wg_part = e(max(lib.ctn_wgrad_splits(Rr, i, j) * i * j for i, j in shapes), **f32)
         self.wg_part2 = e(lib.ctn_wgrad_splits(Rr, H, B) * H * B, **f32)
         # flat gradient buffer in state_dict order
-        self.spec = param_spec(N, L, B, H, cfg["P"], cfg["X"], cfg["R"], C_, cfg["causal"])
+        self.spec = param_spec(N, L, B, H, cfg["P"], cfg["X"], cfg["R"], C_, cfg["causal"], cfg["norm_type"])
         self.offsets, off = {}, 0
-        for key, (shape, _) in self.spec.items():
+        for key, (shape, kind) in self.spec.items():
+            if kind.startswith("buf_"):       # BatchNorm1d buffers carry no gradient
+                continue
             n = 1
             for s_ in shape:
                 n *= s_
             self.offsets[key] = (off, n, shape)
             off += n
         self.flat_grad = z(off, **f32)
+        if self.bn:
+            self.unit = z(M, 1, 2, **f32)
+            self.unit[:, 0, 1] = float(K * H)            # (sum, sumsq) = (0, count): mean 0, rstd 1
+            self.zero_stat = z(M, 1, 2, **f32)           # backward correction sums: none (bn_bwd_center did it)
+            self.zero_scal = z(M * max(self.bd_ctas), 4, **f32)
+            self.bn_part = e(lib.ctn_bn_tiles(Rr) * 2 * H, **f32)
+            self.bn_sums = z(2 * H, dtype=torch.float64, device=device)
+            # per block and norm: scale, shift (the kernels' "gamma, beta"), mean, rstd (the backward's xh)
+            self.bn_aff = [[tuple(e(H, **f32) for _ in range(4)) for _ in range(2)] for _ in range(NB)]
+            self.bn_w2 = [(e(B, H, **bf), e(B, H, **bf), e(B, **f32), e(B, **f32)) for _ in range(NB)]
+        self.bn_mode = None                              # (use running statistics, process group, global rows)
         self.fwd_calls = self.bwd_calls = None
         self.param_ptrs = None
         self._keep = []
@@ -194,7 +213,80 @@ class TrainPlan:
         return call
 
     # ------------------------------------------------------------- call lists
-    def build(self, params, prep, prep_b):
+    def _build_bn_forward_block(self, fwd, params, bufs, pb, i, xb, k, bn_count, use_running):
+        """conv1x1 -> [batch statistics of PReLU(a) -> fold] -> depthwise with the folded affine ->
+        [batch statistics of PReLU(d) -> fold -> W2 with the affine folded in] -> pointwise + residual."""
+        cfg, lib, tag = self.cfg, nat.lib(), self._tag
+        B, H, P, M, K = cfg["B"], cfg["H"], cfg["P"], self.M, self.K
+        Rr = M * K
+
+        def fold(j, aff):
+            g, b = params[k["g%d" % j]], params[k["b%d" % j]]
+            a = (self.bn_sums.data_ptr(), bn_count, g.data_ptr(), b.data_ptr(), BN_EPS, BN_MOMENTUM, int(use_running),
+                 bufs[k["rm%d" % j]].data_ptr(), bufs[k["rv%d" % j]].data_ptr(), bufs[k["nb%d" % j]].data_ptr(), H,
+                 aff[0].data_ptr(), aff[1].data_ptr(), aff[2].data_ptr(), aff[3].data_ptr())
+            return lambda s, a=a: lib.ctn_bn_train_fold(*a, s)
+
+        aff1, aff2 = self.bn_aff[i]
+        fwd.append(tag(self._gemm(Cin=B, Cout=H, a_hi=self.x_hl[i][0], a_lo=self.x_hl[i][1], w_hi=pb["w1"][0],
+                                  w_lo=pb["w1"][1], out_f32=self.a[i]),
+                       "fwd_gemm_conv1x1", 2.0 * Rr * B * H, Rr * (4.0 * B + 4.0 * H)))
+        if not use_running:
+            fwd.extend(self._bn_stats(None, self.a[i], params[k["a1"]], aff1))
+        fwd.append(fold(1, aff1))
+        d = nat.DwconvArgs()
+        d.M, d.K, d.H, d.P, d.dilation, d.causal = M, K, H, P, 2 ** xb, int(bool(cfg["causal"]))
+        d.inp, d.prelu_in = self.a[i].data_ptr(), params[k["a1"]].data_ptr()
+        d.gamma_in, d.beta_in = aff1[0].data_ptr(), aff1[1].data_ptr()
+        d.norm, d.in_stat, d.in_P = nat.NORM_GLN, self.unit.data_ptr(), 1
+        d.wd, d.prelu_out = params[k["wd"]].data_ptr(), params[k["a2"]].data_ptr()
+        d.out_pre = self.d[i].data_ptr()
+        d.out_hi, d.out_lo = self.q_hl[0].data_ptr(), self.q_hl[1].data_ptr()
+        d.out_stat = self.stat2[i].data_ptr()        # (the gLN partials the kernel writes are not used)
+        self._keep.append(d)
+        dw = lib.ctn_dwconv_fwd
+        fwd.append(tag(lambda s, ref=C.byref(d): dw(ref, s), "fwd_dwconv", 2.0 * Rr * H * P, 12.0 * Rr * H))
+        if not use_running:
+            fwd.extend(self._bn_stats(None, self.d[i], params[k["a2"]], aff2))
+        fwd.append(fold(2, aff2))
+        w2 = self.bn_w2[i]
+        a = (params[k["w2"]].data_ptr(), B, H, aff2[0].data_ptr(), aff2[1].data_ptr(), 0, w2[0].data_ptr(),
+             w2[1].data_ptr(), w2[2].data_ptr(), w2[3].data_ptr())
+        fwd.append(lambda s, a=a: lib.ctn_weight_prep(*a, s))
+        fwd.append(tag(self._gemm(Cin=H, Cout=B, a_hi=self.q_hl[0], a_lo=self.q_hl[1], w_hi=w2[0], w_lo=w2[1],
+                                  col_g=w2[2], col_bias=w2[3], in_norm=nat.NORM_GLN, in_stat=self.unit, in_P=1,
+                                  in_count=float(K) * H, resid=self.x, out_f32=self.x, out_hi=self.x_hl[i + 1][0],
+                                  out_lo=self.x_hl[i + 1][1]),
+                       "fwd_gemm_pointwise", 2.0 * Rr * B * H, Rr * (4.0 * H + 12.0 * B)))
+
+    def _bn_backward_norm(self, dy, pre, slope, aff, bn_count, use_running, key_w, key_b):
+        """BatchNorm backward around the gLN kernels: d weight = sum dy xh, d bias = sum dy (into the flat
+        gradient) and, with batch statistics, dy -= mean(dy) + xh mean(dy xh) in place."""
+        lib, Rr, H = nat.lib(), self.M * self.K, self.cfg["H"]
+        calls = self._bn_stats(dy, pre, slope, aff)
+        a = (dy.data_ptr(), pre.data_ptr(), slope.data_ptr(), aff[2].data_ptr(), aff[3].data_ptr(),
+             self.bn_sums.data_ptr(), bn_count, int(not use_running), Rr, H, self.grad_ptr(key_w), self.grad_ptr(key_b))
+        calls.append(self._tag(lambda s, a=a: lib.ctn_bn_bwd_center(*a, s), "bn_bwd_center", 4.0 * Rr * H, 12.0 * Rr * H))
+        return calls
+
+    def _bn_stats(self, dy, pre, slope, aff):
+        """Column sums over all rows (ctn_bn_colsums) and, in a data-parallel job, their sum over the ranks."""
+        lib, Rr, H = nat.lib(), self.M * self.K, self.cfg["H"]
+        a = (ptr_(dy), pre.data_ptr(), slope.data_ptr(), aff[2].data_ptr() if dy is not None else None,
+             aff[3].data_ptr() if dy is not None else None, Rr, H, self.bn_part.data_ptr(), self.bn_sums.data_ptr())
+        calls = [self._tag(lambda s, a=a: lib.ctn_bn_colsums(*a, s), "bn_colsums", 3.0 * Rr * H,
+                           (8.0 if dy is not None else 4.0) * Rr * H)]
+        group = self.bn_mode[1]
+        if group is not None:
+            import torch.distributed as dist
+
+            def allreduce(s, sums=self.bn_sums, group=group):
+                dist.all_reduce(sums, op=dist.ReduceOp.SUM, group=group)      # [2, H] fp64 on the current stream
+                return 0
+            calls.append(allreduce)
+        return calls
+
+    def build(self, params, prep, prep_b, bn_mode=(False, None, None), bn_buffers=None):
         cfg = self.cfg
         N, L, B, H, C_, P = cfg["N"], cfg["L"], cfg["B"], cfg["H"], cfg["C"], cfg["P"]
         M, K, T, NB = self.M, self.K, self.T, self.NB
@@ -204,6 +296,11 @@ class TrainPlan:
         tag, Rr = self._tag, M * K
         GLN = self.norm                      # the block norm (gLN or cLN)
         is_gln = self.norm == nat.NORM_GLN
+        bn = self.bn
+        self.bn_mode = bn_mode
+        if bn:
+            use_running, _, rows_global = bn_mode
+            bn_count = float(rows_global if rows_global else Rr)
         causal = int(bool(cfg["causal"]))
         U = params["encoder.conv1d_U.weight"]
         V = params["decoder.basis_signals.weight"]
@@ -226,9 +323,13 @@ class TrainPlan:
         i = 0
         for r in range(cfg["R"]):
             for xb in range(cfg["X"]):
-                k = block_keys(r, xb, cfg["causal"])
+                k = block_keys(r, xb, cfg["causal"], cfg["norm_type"])
                 blocks.append((i, xb, k))
                 pb = prep.blocks[i]
+                if bn:
+                    self._build_bn_forward_block(fwd, params, bn_buffers, pb, i, xb, k, bn_count, use_running)
+                    i += 1
+                    continue
                 fwd.append(tag(self._gemm(Cin=B, Cout=H, a_hi=self.x_hl[i][0], a_lo=self.x_hl[i][1], w_hi=pb["w1"][0],
                                           w_lo=pb["w1"][1], out_f32=self.a[i], out_stat=GLN,
                                           out_stat_buf=self.stat1[i], stat_prelu=params[k["a1"]]),
@@ -274,9 +375,16 @@ class TrainPlan:
         pn_cln = lib.ctn_bwd_prelu_norm_cln
         for (i, xb, k) in reversed(blocks):
             pb = prep_b.blocks[i]
-            P2 = self.P2s[xb]
-            a_ = (self.d[i].data_ptr(), params[k["a2"]].data_ptr(), params[k["g2"]].data_ptr(),
-                  params[k["b2"]].data_ptr(), GLN, self.stat2[i].data_ptr(), P2, M, K, H,
+            P2 = 1 if bn else self.P2s[xb]
+            if bn:      # the kernels' (gamma, beta) = the folded BatchNorm affine; statistics = unit
+                aff1, aff2 = self.bn_aff[i]
+                g1_, b1_, g2_, b2_ = aff1[0], aff1[1], aff2[0], aff2[1]
+                st1_, st2_, P1_ = self.unit, self.unit, 1
+            else:
+                g1_, b1_, g2_, b2_ = params[k["g1"]], params[k["b1"]], params[k["g2"]], params[k["b2"]]
+                st1_, st2_, P1_ = self.stat1[i], self.stat2[i], self.P1
+            a_ = (self.d[i].data_ptr(), params[k["a2"]].data_ptr(), g2_.data_ptr(),
+                  b2_.data_ptr(), GLN, st2_.data_ptr(), P2, M, K, H,
                   self.hl_H[0].data_ptr(), self.hl_H[1].data_ptr())
             bwd.append(_JOIN)     # the previous block's weight gradients read hl_H and the partial buffers
             # u is read by the weight-gradient GEMM only, so it is formed on the side stream as well: the fork
@@ -285,26 +393,37 @@ class TrainPlan:
             bwd.append(_FORK)
             bwd.append((_SIDE, tag(lambda s, a=a_: ns(*a, s), "bwd_norm_split", 4.0 * Rr * H, 8.0 * Rr * H)))   # u (hi, lo)
             bwd.append((_SIDE, call))
-            bwd.append(tag(self._gemm(Cin=B, Cout=H, a_hi=self.g_hl[0], a_lo=self.g_hl[1], w_hi=pb["w2t"][0],
-                                      w_lo=pb["w2t"][1], out_f32=self.du, out_stat=GLN, out_stat_buf=self.bstat,
-                                      bw_pre=self.d[i], bw_gamma=params[k["g2"]], bw_slope=params[k["a2"]],
-                                      bw_stat=self.stat2[i], bw_P=P2),                    # du = g W2 (+ S1, S2)
-                           "bwd_gemm_dgrad_pointwise", 2.0 * Rr * B * H, Rr * (4.0 * B + 8.0 * H)))
+            if bn:
+                bwd.append(tag(self._gemm(Cin=B, Cout=H, a_hi=self.g_hl[0], a_lo=self.g_hl[1], w_hi=pb["w2t"][0],
+                                          w_lo=pb["w2t"][1], out_f32=self.du),            # du = g W2
+                               "bwd_gemm_dgrad_pointwise", 2.0 * Rr * B * H, Rr * (4.0 * B + 4.0 * H)))
+                bwd.extend(self._bn_backward_norm(self.du, self.d[i], params[k["a2"]], aff2, bn_count, use_running,
+                                                  k["g2"], k["b2"]))
+            else:
+                bwd.append(tag(self._gemm(Cin=B, Cout=H, a_hi=self.g_hl[0], a_lo=self.g_hl[1], w_hi=pb["w2t"][0],
+                                          w_lo=pb["w2t"][1], out_f32=self.du, out_stat=GLN, out_stat_buf=self.bstat,
+                                          bw_pre=self.d[i], bw_gamma=params[k["g2"]], bw_slope=params[k["a2"]],
+                                          bw_stat=self.stat2[i], bw_P=P2),                    # du = g W2 (+ S1, S2)
+                               "bwd_gemm_dgrad_pointwise", 2.0 * Rr * B * H, Rr * (4.0 * B + 8.0 * H)))
             b = nat.BwdDwArgs()
             b.M, b.K, b.H, b.P, b.dilation, b.causal = M, K, H, P, 2 ** xb, causal
-            b.P1, b.P2, b.Pb = self.P1, P2, self.P1
+            b.P1, b.P2, b.Pb = P1_, P2, (1 if bn else self.P1)
             b.du, b.d, b.a = self.du.data_ptr(), self.d[i].data_ptr(), self.a[i].data_ptr()
-            b.stat1, b.stat2, b.bstat = self.stat1[i].data_ptr(), self.stat2[i].data_ptr(), self.bstat.data_ptr()
-            b.g1, b.b1, b.g2 = params[k["g1"]].data_ptr(), params[k["b1"]].data_ptr(), params[k["g2"]].data_ptr()
+            b.stat1, b.stat2 = st1_.data_ptr(), st2_.data_ptr()
+            b.bstat = self.zero_stat.data_ptr() if bn else self.bstat.data_ptr()
+            b.g1, b.b1, b.g2 = g1_.data_ptr(), b1_.data_ptr(), g2_.data_ptr()
             b.wd, b.slope1, b.slope2 = params[k["wd"]].data_ptr(), params[k["a1"]].data_ptr(), params[k["a2"]].data_ptr()
             b.dn1, b.chan_part, b.scal_part = self.dn1.data_ptr(), self.chan_part.data_ptr(), self.scal_part.data_ptr()
             b.norm = self.norm
             self._keep.append(b)
             bwd.append(tag(lambda s, ref=C.byref(b): bd(ref, s), "bwd_dwconv", 4.0 * Rr * H * P, 16.0 * Rr * H))
             bwd.append(_JOIN)     # dW2 has consumed u before da overwrites hl_H
+            if bn:
+                bwd.extend(self._bn_backward_norm(self.dn1, self.a[i], params[k["a1"]], aff1, bn_count, use_running,
+                                                  k["g1"], k["b1"]))
             if is_gln:
-                a_ = (self.dn1.data_ptr(), self.a[i].data_ptr(), self.stat1[i].data_ptr(), self.P1,
-                      self.scal_part.data_ptr(), self.bd_ctas[xb], params[k["g1"]].data_ptr(),
+                a_ = (self.dn1.data_ptr(), self.a[i].data_ptr(), st1_.data_ptr(), P1_,
+                      (self.zero_scal if bn else self.scal_part).data_ptr(), self.bd_ctas[xb], g1_.data_ptr(),
                       params[k["a1"]].data_ptr(), M, K, H, self.hl_H[0].data_ptr(), self.hl_H[1].data_ptr(),
                       self.alpha_part.data_ptr())
                 bwd.append(tag(lambda s, a=a_: pn(*a, s), "bwd_prelu_norm", 6.0 * Rr * H, 12.0 * Rr * H))   # da (hi, lo)
@@ -318,9 +437,11 @@ class TrainPlan:
             bwd.append((_SIDE, call))
             # every parameter gradient of the block in ONE reduction launch
             cp, cn, cs = self.chan_part, M * self.bd_rows[xb], (4 + P) * H
-            segs = [(cp, cn, cs, 0, H, 1, self.grad_ptr(k["g2"]), 1), (cp, cn, cs, H, H, 1, self.grad_ptr(k["b2"]), 1),
-                    (cp, cn, cs, 2 * H, H, 1, self.grad_ptr(k["g1"]), 1),
-                    (cp, cn, cs, 3 * H, H, 1, self.grad_ptr(k["b1"]), 1)]
+            # (BatchNorm: d weight / d bias of both norms come from ctn_bn_bwd_center, not from chan_part)
+            segs = [] if bn else [
+                (cp, cn, cs, 0, H, 1, self.grad_ptr(k["g2"]), 1), (cp, cn, cs, H, H, 1, self.grad_ptr(k["b2"]), 1),
+                (cp, cn, cs, 2 * H, H, 1, self.grad_ptr(k["g1"]), 1),
+                (cp, cn, cs, 3 * H, H, 1, self.grad_ptr(k["b1"]), 1)]
             segs += [(cp, cn, cs, (4 + j) * H, H, 1, self.grad_ptr(k["wd"]) + 4 * j, P) for j in range(P)]
             segs.append((self.scal_part, M * self.bd_ctas[xb], 4, 2, 1, 1, self.grad_ptr(k["a2"]), 1))
             segs.append((self.alpha_part, M * self.tiles_pn, 1, 0, 1, 1, self.grad_ptr(k["a1"]), 1))
@@ -438,6 +559,7 @@ class TrainPlan:
     def run_forward(self, use_graph):
         """mix -> est (static buffers).  Returns the number of kernels launched."""
         self.fwd_runs += 1
+        use_graph = use_graph and not (self.bn and self.bn_mode[1] is not None)   # all-reduces in the call list
         if not use_graph or (self.fwd_graph is None and self.fwd_runs < 2):
             self._launch_forward()     # a shape is captured the second time it is seen (see _engine._Plan.run)
         else:
@@ -449,6 +571,7 @@ class TrainPlan:
     def run_backward(self, use_graph):
         """g_est -> flat_grad (static buffers)."""
         self.bwd_runs += 1
+        use_graph = use_graph and not (self.bn and self.bn_mode[1] is not None)
         if not use_graph or (self.bwd_graph is None and self.bwd_runs < 2):
             self._launch_backward()
         else:
@@ -480,20 +603,20 @@ class TrainEngine:
         self.max_pending = 4           # activation sets per shape that may await their backward at one time
         self._staged = {}              # per device: aligned copies of DataParallel replica parameters
 
-    def plan(self, params, M, T, device):
+    def plan(self, params, M, T, device, bn_buffers=None, bn_running=False):
         """The plan of the first activation set of this shape that no live autograd graph is waiting on: a
         second forward before the first one's backward (two micro-batches whose losses are summed, or a
         train-mode forward whose graph is kept) gets its own saved activations, as autograd gives the
         reference; sets whose graph was dropped without a backward are reused."""
         for slot in range(self.max_pending):
-            plan = self._plan(params, M, T, device, slot)
+            plan = self._plan(params, M, T, device, slot, bn_buffers, bn_running)
             owner = plan.owner() if plan.owner is not None else None
             if owner is None or plan.done:
                 return plan
         raise RuntimeError("ConvTasNet.forward: %d forwards of shape (%d, %d) are awaiting backward; free their "
                            "graphs or raise train_engine().max_pending" % (self.max_pending, M, T))
 
-    def _plan(self, params, M, T, device, slot=0):
+    def _plan(self, params, M, T, device, slot=0, bn_buffers=None, bn_running=False):
         di = device.index
         if di not in self.prep:
             self.prep[di] = _Prepared(self.cfg, device)
@@ -507,8 +630,20 @@ class TrainEngine:
         if plan is None:
             plan = self.plans.put(key, TrainPlan(self.cfg, M, T, device, self.overlap_wgrad), device)
         ptrs = tuple(p.data_ptr() for p in params.values())
-        if plan.fwd_calls is None or plan.param_ptrs != ptrs:
-            plan.build(params, self.prep[di], self.prep_b[di])
+        bn_mode = (False, None, None)
+        if plan.bn:
+            # batch statistics span the GLOBAL batch: rows of all ranks (equal shards unless global_batch is set)
+            group = self.process_group
+            rows = None
+            if group is not None and not bn_running:
+                import torch.distributed as dist
+                n_global = self.global_batch if self.global_batch is not None else M * dist.get_world_size(group)
+                rows = n_global * plan.K
+            bn_mode = (bool(bn_running), None if bn_running else group, rows)
+            ptrs = ptrs + tuple(b.data_ptr() for b in bn_buffers.values())
+        if plan.fwd_calls is None or plan.param_ptrs != ptrs or plan.bn_mode != bn_mode:
+            plan.build(params, self.prep[di], self.prep_b[di], bn_mode, bn_buffers)
+            plan.param_ptrs = ptrs
         return plan
 
 
@@ -522,10 +657,13 @@ class _Separate(torch.autograd.Function):
         eng = model.train_engine()
         with torch.cuda.device(dev):
             params = aligned_params(eng._staged, params, dev)
-            plan = eng.plan(params, M, T, dev)
+            bufs = model._bn_buffers() if is_bn(model.norm_type) else None
+            plan = eng.plan(params, M, T, dev, bufs, bn_running=not model.training)
             plan.mix.copy_(mixture)
             eng.launches += plan.run_forward(eng.use_graph)
             est = plan.est.clone()
+            if bufs and model.training:     # the fold kernels updated the running statistics through raw pointers
+                torch.autograd.graph.increment_version(list(bufs.values()))
         plan.generation += 1
         plan.owner, plan.done = weakref.ref(ctx), False
         ctx.plan, ctx.generation, ctx.engine = plan, plan.generation, eng
@@ -552,6 +690,10 @@ class _Separate(torch.autograd.Function):
         return (None, None) + tuple(plan.grad_views(flat))
 
 
+def ptr_(t):
+    return None if t is None else t.data_ptr()
+
+
 def separate(model, mixture, params):
     if mixture.requires_grad:
         raise NotImplementedError("gradient with respect to the mixture is not implemented")
@@ -559,4 +701,12 @@ def separate(model, mixture, params):
         raise RuntimeError("mixture must be float32 [M, T]")
     if mixture.shape[1] < model.L:
         raise RuntimeError("Calculated output size is too small: T=%d < L=%d" % (mixture.shape[1], model.L))
-    return _Separate.apply(model, mixture, *params.values())
+    plist = [params[k] for k in model._keys]      # the parameters; BatchNorm1d buffers are not autograd inputs
+    if not torch.is_grad_enabled() or not any(p.requires_grad for p in plist):
+        # BatchNorm1d in train() mode without a graph (torch.no_grad): batch statistics + buffer update only
+        return _Separate.forward(_NoCtx(), model, mixture, *plist)
+    return _Separate.apply(model, mixture, *plist)
+
+
+class _NoCtx:
+    """Stands in for the autograd context when the training-mode forward runs without a graph."""

@@ -35,12 +35,8 @@ def _check_cfg(cfg, training=False):
     if training and nat.PRECISION != "bf16x3":
         raise RuntimeError("CTN_PRECISION=%s is an inference-only precision: gradients need the bf16 (hi, lo) "
                            "operands of the default mode" % nat.PRECISION)
-    if training and is_bn(cfg["norm_type"]):
-        # conv_tasnet.py:300-303 falls through to BatchNorm1d; its training-mode batch statistics couple
-        # the utterances of a batch, which the utterance-sharded design excludes.
-        # Inference with the running statistics is a per-channel affine and IS implemented (_Plan).
-        raise NotImplementedError("norm_type=%r (BatchNorm1d): training is not implemented, only inference"
-                                  % (cfg["norm_type"],))
+    # (any norm_type but gLN / cLN is nn.BatchNorm1d, conv_tasnet.py:300-303: inference folds the running
+    # statistics into a per-channel affine (_Plan); training uses batch statistics, csrc/bn_train.cu)
     if cfg["mask_nonlinear"] not in _MASK:
         raise ValueError("Unsupported mask non-linear function")  # conv_tasnet.py:208
 

@@ -23,7 +23,8 @@ def _free_port():
     return p
 
 
-def _worker(rank, world, port, M, out):
+def _worker(rank, world, port, M, out, norm="gLN"):
+    cfg = dict(CFG, norm_type=norm)
     import sys
     for p in (ROOT, PKG):
         if p not in sys.path:
@@ -38,9 +39,9 @@ def _worker(rank, world, port, M, out):
     dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
     try:
         torch.manual_seed(5)                       # same weights on every rank ...
-        ref_model = conv_tasnet.ConvTasNet(**CFG).to(dev).train()
+        ref_model = conv_tasnet.ConvTasNet(**cfg).to(dev).train()
         torch.manual_seed(6 + rank)                # ... but rank-dependent ones here: attach() must broadcast
-        model = conv_tasnet.ConvTasNet(**CFG).to(dev).train()
+        model = conv_tasnet.ConvTasNet(**cfg).to(dev).train()
         with torch.no_grad():
             if rank == 0:
                 model.load_state_dict(ref_model.state_dict())
@@ -65,7 +66,13 @@ def _worker(rank, world, port, M, out):
         mine = torch.cat([p.grad.flatten() for p in model.parameters()])
         gl = _dist.global_loss(loss, hi - lo, n_global)
         err = float((mine.double() - full.double()).norm() / full.double().norm())
-        out[rank] = (err, abs(float(gl) - float(loss_ref)))
+        # BatchNorm1d: the batch statistics were summed over the ranks, so the updated running buffers equal
+        # the single-process ones as well
+        berr = 0.0
+        for (ka, a), (kb, b) in zip(model.named_buffers(), ref_model.named_buffers()):
+            assert ka == kb
+            berr = max(berr, float((a.double() - b.double()).abs().max()))
+        out[rank] = (err, abs(float(gl) - float(loss_ref)), berr)
     finally:
         dist.destroy_process_group()
 
@@ -79,9 +86,27 @@ def test_two_rank_gradient_equals_single_process(M):
     out = mgr.dict()
     mp.spawn(_worker, args=(2, _free_port(), M, out), nprocs=2, join=True)
     for r in range(2):
-        err, dl = out[r]
+        err, dl, _ = out[r]
         assert err < 2e-5, (r, err)      # fp32 summation order differs between 1 and 2 shards
         assert dl < 1e-4
+
+
+@pytest.mark.parametrize("M", [4, 5])
+def test_two_rank_batchnorm_training_equals_single_process(M):
+    """norm_type="BN" (conv_tasnet.py:300-303): batch statistics couple the utterances, so the [2, H] column sums
+    of every norm are all-reduced across the ranks (forward and backward); two ranks with (un)equal shards
+    must reproduce the single-process gradient AND running statistics."""
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    import torch.multiprocessing as mp
+    mgr = mp.Manager()
+    out = mgr.dict()
+    mp.spawn(_worker, args=(2, _free_port(), M, out, "BN"), nprocs=2, join=True)
+    for r in range(2):
+        err, dl, berr = out[r]
+        assert err < 5e-5, (r, err)
+        assert dl < 1e-4
+        assert berr < 1e-6, (r, berr)
 
 
 def test_reference_dataparallel_wrapper():
