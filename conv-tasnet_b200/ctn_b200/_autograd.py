@@ -44,7 +44,7 @@ class _PreparedBwd:
             i = 0
             for r in range(cfg["R"]):
                 for x in range(cfg["X"]):
-                    k = block_keys(r, x, cfg["causal"])
+                    k = block_keys(r, x, cfg["causal"], cfg["norm_type"])
                     t.add(params[k["w1"]], H, B, None, None, 1, self.blocks[i]["w1t"])
                     t.add(params[k["w2"]], B, H, None, None, 1, self.blocks[i]["w2t"])
                     i += 1
@@ -480,6 +480,7 @@ class TrainPlan:
         self.bwd_calls = bwd
         self.param_ptrs = tuple(p.data_ptr() for p in params.values())
         self.fwd_graph = self.bwd_graph = None     # captured pointers may have changed
+        self.fwd_runs = self.bwd_runs = 0          # the next run of each direction is eager again (see _capture)
 
     def _launch_forward(self):
         s, check, lib = nat.stream(), nat.check, nat.lib()
@@ -549,7 +550,9 @@ class TrainPlan:
         return [(m[0], m[1], m[2], evs[i].elapsed_time(evs[i + 1])) for i, (_, m) in enumerate(seq)]
 
     def _capture(self, launch):
-        launch()                                   # warm-up outside capture (attribute setup, lazy loading)
+        # No warm-up launch here: a plan is captured on its SECOND run (run_forward / run_backward), so its first,
+        # eager run has already done the first-use set-up (kernel attributes, lazy module loading) -- and a
+        # BatchNorm training forward must execute exactly once per call, because it moves the running statistics.
         torch.cuda.synchronize(self.device)
         g = torch.cuda.CUDAGraph()
         with torch.cuda.graph(g, stream=nat.capture_stream(self.device), capture_error_mode="thread_local"):
@@ -619,7 +622,7 @@ class TrainEngine:
     def _plan(self, params, M, T, device, slot=0, bn_buffers=None, bn_running=False):
         di = device.index
         if di not in self.prep:
-            self.prep[di] = _Prepared(self.cfg, device)
+            self.prep[di] = _Prepared(self.cfg, device, fold_bn=False)
             self.prep_b[di] = _PreparedBwd(self.cfg, device)
         old = self.prep[di].fingerprint
         self.prep[di].refresh(self.cfg, params)

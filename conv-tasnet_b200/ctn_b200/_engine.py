@@ -126,7 +126,10 @@ class PlanCache:
 class _Prepared:
     """Weight-derived buffers: bf16 (hi, lo) splits with the preceding norm's affine folded in."""
 
-    def __init__(self, cfg, device):
+    def __init__(self, cfg, device, fold_bn=True):
+        # fold_bn: BatchNorm1d blocks fold their RUNNING statistics into w2 here (inference); the training plan
+        # folds batch statistics per step itself (TrainPlan.bn_w2) and passes False
+        self.fold_bn = fold_bn
         N, B, H, C = cfg["N"], cfg["B"], cfg["H"], cfg["C"]
         bf = dict(dtype=torch.bfloat16, device=device)
         f32 = dict(dtype=torch.float32, device=device)
@@ -137,7 +140,7 @@ class _Prepared:
                 w1=(torch.empty(H, B, **bf), torch.empty(H, B, **bf)),
                 w2=(torch.empty(B, H, **bf), torch.empty(B, H, **bf), torch.empty(B, **f32), torch.empty(B, **f32))))
         self.mask = (torch.empty(C * N, B, **bf), torch.empty(C * N, B, **bf))
-        if is_bn(cfg["norm_type"]):     # per block: (scale, shift) of both BatchNorm1d layers, folded from the
+        if is_bn(cfg["norm_type"]) and fold_bn:     # per block: (scale, shift) of both BatchNorm1d layers, folded from the
             for blk in self.blocks:     # running statistics by ctn_bn_fold
                 blk["bn1"] = (torch.empty(H, **f32), torch.empty(H, **f32))
                 blk["bn2"] = (torch.empty(H, **f32), torch.empty(H, **f32))
@@ -149,7 +152,7 @@ class _Prepared:
         if fp == self.fingerprint:
             return
         ptrs = tuple(p.data_ptr() for p in params.values())
-        bn = is_bn(cfg["norm_type"])
+        bn = is_bn(cfg["norm_type"]) and self.fold_bn
         if bn:
             lib, st, i = nat.lib(), nat.stream(), 0
             for r in range(cfg["R"]):

@@ -257,3 +257,34 @@ def test_plan_caches_are_bounded_over_many_lengths():
     assert tr.plans.evictions > 0 and inf.plans.evictions > 0
     assert tr.plans.total_bytes() <= max(tr.plans.limit_bytes, max(tr.plans.bytes.values()) * tr.plans.keep)
     assert max(seen[12:]) <= 1.5 * max(seen[:12]) + (64 << 20)
+
+
+@pytest.mark.parametrize("norm,causal", [("gLN", False), ("gLN", True), ("cLN", False), ("cLN", True)])
+def test_gradients_every_norm_and_padding_combination(norm, causal):
+    """chose_norm x causal (conv_tasnet.py:175-176, 292-303): the reference allows all four combinations; the
+    recorded fixtures only hold gLN non-causal and cLN causal.  Tensor-core sized model against autograd over the
+    oracle in fp64."""
+    import pit_criterion
+    cfg = dict(N=64, L=16, B=64, H=128, P=3, X=3, R=2, C=2, norm_type=norm, causal=causal, mask_nonlinear="relu")
+    p32 = O.random_params(*(cfg[k] for k in "NLBHPXRC"), cfg["causal"], seed=9)
+    model = _build(cfg, p32)
+    g = torch.Generator().manual_seed(10)
+    M, T = 3, 3000
+    src = (0.1 * torch.randn(M, 2, T, generator=g)).to(DEV)
+    mix = src.sum(1)
+    lengths = torch.tensor([T, 2500, T], device=DEV)
+    est = model(mix)
+    est0 = est.detach().clone()
+    loss, *_ = pit_criterion.cal_loss(src, est, lengths)
+    loss.backward()
+    p64 = {k: v.to(DEV).double().requires_grad_(True) for k, v in p32.items()}
+    est_ref = O.forward(mix.double(), p64, cfg)
+    loss_ref, *_ = O.cal_loss(src.double(), est_ref, lengths)
+    loss_ref.backward()
+    assert rel_l2(est0, est_ref) < 1e-4
+    errs = sorted(((rel_l2(p.grad, p64[k].grad), k) for k, p in model.named_parameters() if p.numel() > 1), reverse=True)
+    flat = torch.cat([p.grad.flatten().double() for _, p in model.named_parameters()])
+    flat_ref = torch.cat([p64[k].grad.flatten() for k, _ in model.named_parameters()])
+    print(norm, causal, "flat", rel_l2(flat, flat_ref), "worst", errs[:4])
+    assert rel_l2(flat, flat_ref) < 2e-3
+    assert errs[0][0] < 5e-3, errs[:4]
