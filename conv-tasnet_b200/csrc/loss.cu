@@ -248,3 +248,59 @@ extern "C" int ctn_pit_sisnr_bwd(const float* source, const float* estimate, con
     CTN_LAUNCH_CHECK("pit_bwd_kernel");
     return CTN_OK;
 }
+
+// ---- allocation-free variant of ctn_pit_sisnr_fwd ------------------------------------------------------------
+// No counterpart in the reference; added for callers that cannot call
+// cudaMalloc (code under CUDA-graph capture, tight serving loops, harnesses that forbid it).  The chunk partials
+// live in a file-scope __device__ array instead of a caller-provided workspace: CTN_PIT_STATIC_SCRATCH_DOUBLES
+// doubles = 512 KiB, held by every GPU that loads the library until the process exits.  In HOST code the array's
+// name is only a host-side stand-in, not a device address, so its address is resolved once per device with
+// cudaGetSymbolAddress (that device current) and cached.  Every call on a device shares the array: calls that
+// overlap on the GPU (different streams) race.  Nothing has to be cleared between calls: pit_sums_kernel
+// overwrites every partial slot that pit_finalize_kernel of the same call reads.
+#include <mutex>
+
+namespace ctn {
+static_assert(CTN_PIT_STATIC_SCRATCH_DOUBLES == 65536, "keep include/ctn_b200.h and the array in step");
+static __device__ __align__(256) double g_pit_static_scratch[CTN_PIT_STATIC_SCRATCH_DOUBLES];
+
+static int pit_static_scratch(double** out) {
+    static std::mutex mu;
+    static double* addr[kMaxDevices] = {};
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaGetDevice (ctn_pit_sisnr_fwd_static)");
+    if (dev < 0 || dev >= kMaxDevices) {
+        set_error("ctn_pit_sisnr_fwd_static: device %d outside [0, %d)", dev, kMaxDevices);
+        return CTN_ERR_UNSUPPORTED;
+    }
+    std::lock_guard<std::mutex> lock(mu);
+    if (addr[dev] == nullptr) {
+        void* p = nullptr;
+        e = cudaGetSymbolAddress(&p, g_pit_static_scratch);
+        if (e != cudaSuccess) return cuda_fail(e, "cudaGetSymbolAddress(g_pit_static_scratch)");
+        addr[dev] = static_cast<double*>(p);
+    }
+    *out = addr[dev];
+    return CTN_OK;
+}
+}  // namespace ctn
+
+extern "C" int ctn_pit_sisnr_fwd_static(const float* source, float* estimate, const long long* lengths, int B, int C,
+                                        int T, const long long* perms, int nperm, float* max_snr, long long* max_idx,
+                                        float* loss, float* pair_snr, float* coef, void* stream) {
+    using namespace ctn;
+    CTN_REQUIRE(B > 0 && T > 0 && nperm > 0, "ctn_pit_sisnr_fwd_static: bad shape");
+    CTN_REQUIRE(C >= 1 && C <= kLossMaxC, "ctn_pit_sisnr_fwd_static: C=%d outside [1, %d]", C, kLossMaxC);
+    const long long need = static_cast<long long>(B) * ceil_div(T, kLossChunk) * (5 * C + C * C);
+    if (need > CTN_PIT_STATIC_SCRATCH_DOUBLES) {
+        set_error("ctn_pit_sisnr_fwd_static: B=%d C=%d T=%d needs %lld doubles of scratch, the static array holds %d; "
+                  "use ctn_pit_sisnr_fwd with a caller-provided workspace", B, C, T, need, CTN_PIT_STATIC_SCRATCH_DOUBLES);
+        return CTN_ERR_UNSUPPORTED;
+    }
+    double* scratch = nullptr;
+    const int rc = pit_static_scratch(&scratch);
+    if (rc != CTN_OK) return rc;
+    return ctn_pit_sisnr_fwd(source, estimate, lengths, B, C, T, perms, nperm, scratch, max_snr, max_idx, loss, pair_snr,
+                             coef, stream);
+}

@@ -204,6 +204,8 @@ _SIGNATURES = {
     "ctn_pit_workspace_doubles": (C.c_int, [C.c_int, C.c_int, C.c_int]),
     "ctn_pit_sisnr_fwd": (C.c_int, [_vp, _vp, _vp, C.c_int, C.c_int, C.c_int, _vp, C.c_int, _vp, _vp, _vp, _vp,
                                     _vp, _vp, _vp]),
+    "ctn_pit_sisnr_fwd_static": (C.c_int, [_vp, _vp, _vp, C.c_int, C.c_int, C.c_int, _vp, C.c_int, _vp, _vp, _vp, _vp,
+                                           _vp, _vp]),
     "ctn_pit_reorder": (C.c_int, [_vp, _vp, _vp, C.c_int, C.c_int, C.c_int, _vp, _vp]),
     "ctn_bn_fold": (C.c_int, [_vp, _vp, _vp, _vp, C.c_float, C.c_int, _vp, _vp, _vp]),
     "ctn_bn_tiles": (_i, [_ll]),

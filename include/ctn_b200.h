@@ -223,6 +223,21 @@ int ctn_pit_sisnr_fwd(const float* source, float* estimate, const long long* len
                       const long long* perms, int nperm, double* workspace, float* max_snr, long long* max_idx,
                       float* loss, float* pair_snr, float* coef, void* stream);
 
+/* ctn_pit_sisnr_fwd without the caller-provided workspace, for callers that cannot allocate device memory (code
+ * under CUDA-graph capture, tight serving loops, harnesses that forbid cudaMalloc).  It has NO counterpart in the
+ * reference.  Same arguments, outputs and in-place masking
+ * side effect as ctn_pit_sisnr_fwd; the chunk partials go to a static __device__ array inside the library of
+ * CTN_PIT_STATIC_SCRATCH_DOUBLES doubles (512 KiB, held by every GPU that loads the library until the process
+ * exits).  Shapes with ctn_pit_workspace_doubles(B, C, T) above that limit return CTN_ERR_UNSUPPORTED with a
+ * message naming the limit.  The call allocates nothing (no cudaMalloc / cudaFree, no allocating library routine).
+ * All calls on a device share the array: calls that overlap on the GPU (different streams) race; calls ordered
+ * on one stream are safe, and nothing needs clearing between them (every slot read is written first by the
+ * same call).  The device of the pointers must be current (its copy of the array is resolved on first use). */
+#define CTN_PIT_STATIC_SCRATCH_DOUBLES 65536
+int ctn_pit_sisnr_fwd_static(const float* source, float* estimate, const long long* lengths, int B, int C, int T,
+                             const long long* perms, int nperm, float* max_snr, long long* max_idx, float* loss,
+                             float* pair_snr, float* coef, void* stream);
+
 /* reorder_source (pit_criterion.py:79-98): out[b, c] = estimate[b, perms[max_idx[b]][c]]
  * (applies the permutation, not its inverse -- kept as in the reference). */
 int ctn_pit_reorder(const float* estimate, const long long* perms, const long long* max_idx, int B, int C, int T,
