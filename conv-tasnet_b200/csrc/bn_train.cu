@@ -55,7 +55,7 @@ __global__ void __launch_bounds__(kBnThreads) bn_colsums_kernel(const float* __r
 
 // sums[j][c] = sum over tiles of part[tile][j][c], fp64, fixed order.  One CTA per 32 columns of the [2C] row:
 // 8 warps walk interleaved tiles, then the 8 partials are added in warp order.
-__global__ void __launch_bounds__(256) bn_reduce_kernel(const float* __restrict__ part, int n_tiles, int C2,
+__global__ void __launch_bounds__(256) bn_reduce_kernel(const float* __restrict__ part, int n_tiles, int C2, double scale,
                                                         double* __restrict__ sums) {
     __shared__ double red[8][32];
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
@@ -69,7 +69,7 @@ __global__ void __launch_bounds__(256) bn_reduce_kernel(const float* __restrict_
         double tot = 0.0;
 #pragma unroll
         for (int i = 0; i < 8; ++i) tot += red[i][lane];
-        sums[col] = tot;
+        sums[col] = tot * scale;
     }
 }
 
@@ -139,7 +139,8 @@ __global__ void __launch_bounds__(kBnThreads) bn_bwd_center_kernel(float* __rest
 extern "C" int ctn_bn_tiles(long long R) { return static_cast<int>((R + ctn::kBnRows - 1) / ctn::kBnRows); }
 
 extern "C" int ctn_bn_colsums(const float* dy, const float* pre, const float* slope, const float* mean,
-                              const float* rstd, long long R, int C, float* part, double* sums, void* stream) {
+                              const float* rstd, long long R, int C, double scale, float* part, double* sums,
+                              void* stream) {
     using namespace ctn;
     CTN_REQUIRE(pre && part && sums, "ctn_bn_colsums: NULL pointer");
     CTN_REQUIRE(R > 0 && C > 0, "ctn_bn_colsums: bad shape");
@@ -151,7 +152,7 @@ extern "C" int ctn_bn_colsums(const float* dy, const float* pre, const float* sl
     else
         bn_colsums_kernel<0><<<tiles, kBnThreads, 0, st>>>(nullptr, pre, slope, nullptr, nullptr, R, C, part);
     CTN_LAUNCH_CHECK("bn_colsums_kernel");
-    bn_reduce_kernel<<<ceil_div(2 * C, 32), 256, 0, st>>>(part, tiles, 2 * C, sums);
+    bn_reduce_kernel<<<ceil_div(2 * C, 32), 256, 0, st>>>(part, tiles, 2 * C, scale, sums);
     CTN_LAUNCH_CHECK("bn_reduce_kernel");
     return CTN_OK;
 }

@@ -265,15 +265,23 @@ class TrainPlan:
         lib, Rr, H = nat.lib(), self.M * self.K, self.cfg["H"]
         calls = self._bn_stats(dy, pre, slope, aff)
         a = (dy.data_ptr(), pre.data_ptr(), slope.data_ptr(), aff[2].data_ptr(), aff[3].data_ptr(),
-             self.bn_sums.data_ptr(), bn_count, int(not use_running), Rr, H, self.grad_ptr(key_w), self.grad_ptr(key_b))
+             self.bn_sums.data_ptr(), bn_count * self._bn_weight(), int(not use_running), Rr, H, self.grad_ptr(key_w),
+             self.grad_ptr(key_b))
         calls.append(self._tag(lambda s, a=a: lib.ctn_bn_bwd_center(*a, s), "bn_bwd_center", 4.0 * Rr * H, 12.0 * Rr * H))
         return calls
+
+    def _bn_weight(self):
+        """n_local / n_global: the weight of this rank's local-mean loss in the global-mean loss."""
+        rows_global = self.bn_mode[2]
+        return float(self.M * self.K) / float(rows_global) if rows_global else 1.0
 
     def _bn_stats(self, dy, pre, slope, aff):
         """Column sums over all rows (ctn_bn_colsums) and, in a data-parallel job, their sum over the ranks."""
         lib, Rr, H = nat.lib(), self.M * self.K, self.cfg["H"]
+        # backward sums are weighted by this rank's share of the global batch (see include/ctn_b200.h)
+        w = self._bn_weight() if dy is not None else 1.0
         a = (ptr_(dy), pre.data_ptr(), slope.data_ptr(), aff[2].data_ptr() if dy is not None else None,
-             aff[3].data_ptr() if dy is not None else None, Rr, H, self.bn_part.data_ptr(), self.bn_sums.data_ptr())
+             aff[3].data_ptr() if dy is not None else None, Rr, H, w, self.bn_part.data_ptr(), self.bn_sums.data_ptr())
         calls = [self._tag(lambda s, a=a: lib.ctn_bn_colsums(*a, s), "bn_colsums", 3.0 * Rr * H,
                            (8.0 if dy is not None else 4.0) * Rr * H)]
         group = self.bn_mode[1]

@@ -209,7 +209,7 @@ _SIGNATURES = {
     "ctn_pit_reorder": (C.c_int, [_vp, _vp, _vp, C.c_int, C.c_int, C.c_int, _vp, _vp]),
     "ctn_bn_fold": (C.c_int, [_vp, _vp, _vp, _vp, C.c_float, C.c_int, _vp, _vp, _vp]),
     "ctn_bn_tiles": (_i, [_ll]),
-    "ctn_bn_colsums": (_i, [_vp, _vp, _vp, _vp, _vp, _ll, _i, _vp, _vp, _vp]),
+    "ctn_bn_colsums": (_i, [_vp, _vp, _vp, _vp, _vp, _ll, _i, C.c_double, _vp, _vp, _vp]),
     "ctn_bn_train_fold": (_i, [_vp, C.c_double, _vp, _vp, C.c_float, C.c_float, _i, _vp, _vp, _vp, _i, _vp, _vp, _vp,
                                _vp, _vp]),
     "ctn_bn_bwd_center": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, C.c_double, _i, _ll, _i, _vp, _vp, _vp]),

@@ -401,9 +401,13 @@ int ctn_bn_fold(const float* weight, const float* bias, const float* running_mea
  * ctn_bn_colsums: column sums over the rows of x = PReLU(pre) (slope NULL = identity), pre fp32 [R, C]:
  *   dy == NULL (forward):  sums[0][c] = sum x,   sums[1][c] = sum x*x
  *   dy != NULL (backward): sums[0][c] = sum dy,  sums[1][c] = sum dy * xh,  xh = (x - mean[c]) * rstd[c]
- * part: ctn_bn_tiles(R) * 2 * C floats of workspace; sums: 2 * C doubles (fixed-order reduction).  A data-parallel
- * job sums `sums` over its ranks (one small all-reduce) before the next call, which makes utterance-sharded
- * training equal to the single-process batch.
+ * Both rows are multiplied by `scale` (1 in the forward).  part: ctn_bn_tiles(R) * 2 * C floats of workspace; sums:
+ * 2 * C doubles (fixed-order reduction).  A data-parallel job sums `sums` over its ranks (one small all-reduce)
+ * before the next call, which makes utterance-sharded training equal to the single-process batch.  In the
+ * backward each rank differentiates its LOCAL mean loss, which enters the global loss with weight
+ * w = n_local / n_global (pit_criterion.py:22 over the whole batch): it passes scale = w, so that the all-reduced
+ * sums are those of the global loss, and count * w to ctn_bn_bwd_center, which brings the batch-mean terms back
+ * to local-loss units (the flat gradient is multiplied by w before its own all-reduce).
  * ctn_bn_train_fold: statistics from sums / count (or from the running buffers when use_running != 0: eval-mode
  *   BatchNorm inside a differentiated forward) -> scale, shift, mean, rstd [C]; updates the three buffers.
  * ctn_bn_bwd_center: dy -= sums[0]/count + xh * sums[1]/count in place (center != 0: the two batch-mean terms
@@ -411,7 +415,7 @@ int ctn_bn_fold(const float* weight, const float* bias, const float* running_mea
  *   d weight[c] = sums[1][c], d bias[c] = sums[0][c] (either may be NULL). */
 int ctn_bn_tiles(long long R);
 int ctn_bn_colsums(const float* dy, const float* pre, const float* slope, const float* mean, const float* rstd,
-                   long long R, int C, float* part, double* sums, void* stream);
+                   long long R, int C, double scale, float* part, double* sums, void* stream);
 int ctn_bn_train_fold(const double* sums, double count, const float* weight, const float* bias, float eps,
                       float momentum, int use_running, float* running_mean, float* running_var,
                       long long* num_batches_tracked, int C, float* scale, float* shift, float* mean, float* rstd,

@@ -24,7 +24,11 @@ def _free_port():
 
 
 def _worker(rank, world, port, M, out, norm="gLN"):
-    cfg = dict(CFG, norm_type=norm)
+    # BatchNorm: the kink-free variant (PReLU slopes 1, softmax mask).  Batch normalisation centres every channel on
+    # the PReLU kink, so a 1e-7 difference in summation order between 1 and 2 shards can flip the branch of an
+    # element and move the gradient by 1e-4 (tests/test_gpu_bn.py); without branch points the comparison is tight.
+    smooth = norm == "BN"
+    cfg = dict(CFG, norm_type=norm, mask_nonlinear="softmax" if smooth else "relu")
     import sys
     for p in (ROOT, PKG):
         if p not in sys.path:
@@ -43,6 +47,10 @@ def _worker(rank, world, port, M, out, norm="gLN"):
         torch.manual_seed(6 + rank)                # ... but rank-dependent ones here: attach() must broadcast
         model = conv_tasnet.ConvTasNet(**cfg).to(dev).train()
         with torch.no_grad():
+            if smooth:
+                for p in ref_model.parameters():
+                    if p.numel() == 1:
+                        p.fill_(1.0)
             if rank == 0:
                 model.load_state_dict(ref_model.state_dict())
         n_global = None if M % world == 0 else M
@@ -104,7 +112,7 @@ def test_two_rank_batchnorm_training_equals_single_process(M):
     mp.spawn(_worker, args=(2, _free_port(), M, out, "BN"), nprocs=2, join=True)
     for r in range(2):
         err, dl, berr = out[r]
-        assert err < 5e-5, (r, err)
+        assert err < 2e-5, (r, err)
         assert dl < 1e-4
         assert berr < 1e-6, (r, berr)
 
