@@ -13,6 +13,9 @@
 // (PReLU, statistics, 256-bit stores), 6-13 producers.  The producers are latency-bound, not
 // FMA-bound like fused_block.cu's, so they never leave their load stream to drain.
 #include <cuda.h>
+#include <stdlib.h>
+
+#include <type_traits>
 
 #include "common.cuh"
 #include "f32x2.cuh"
@@ -21,6 +24,8 @@
 namespace ctn {
 
 int make_tmap_bf16_kmajor(CUtensorMap* tm, const void* ptr, long long rows, int cols, int box_rows);  // gemm.cu
+int make_tmap_out(CUtensorMap* tm, const void* ptr, int M, int K, int C, bool f32);                     // gemm.cu
+int make_tmap_bf16_3d(CUtensorMap* tm, const void* ptr, int M, int K, int C, int box_rows);             // gemm.cu
 
 namespace c1 {
 
@@ -29,7 +34,7 @@ constexpr int kBN = 256;             // output columns per accumulator
 constexpr int kBK = 64;
 constexpr int kCin = 256;            // B: the whole reduction dimension is resident
 constexpr int kKB = kCin / kBK;      // 4 k-blocks = 4 resident A slots
-constexpr int kWSlots = 3;
+constexpr int kWSlots = 2;
 constexpr int kABytes = kBM * kBK * 2;           // one of hi / lo
 constexpr int kWBytes = (kBN / 2) * kBK * 2;     // this CTA's half of a weight k-block, one of hi / lo
 constexpr int kASlotBytes = 2 * kABytes;
@@ -38,50 +43,58 @@ constexpr int kTileBytes = kKB * kASlotBytes + kWSlots * kWSlotBytes;
 constexpr int kBarBytes = 256;
 constexpr int kColBytes = 2 * kCin * 4;          // col_g, col_bias of the previous pointwise conv
 constexpr int kMaxTiles = 32;                    // row tiles per CTA whose gLN-2 scale / shift are precomputed
-constexpr int kSmemBytes = kTileBytes + kBarBytes + kColBytes + kMaxTiles * 8;
 constexpr int kDrainWarps = 4;
+constexpr int kStgChunk = 32 * 32 * 4;           // one drained chunk: 32 frames x 32 columns of fp32
+constexpr int kStgBytes = kDrainWarps * 2 * kStgChunk;   // two per drain warp: the TMA store of one reads while the next fills
+constexpr int kSmemBytes = kTileBytes + kStgBytes + kBarBytes + kColBytes + kMaxTiles * 8;
 constexpr int kProdWarps = 8;
-constexpr int kThreads = 32 * (2 + kDrainWarps + kProdWarps);
-constexpr int kRows = kBM / (kProdWarps * 2);   // frames a producer thread handles per unit (a warp spans 2 frame groups)
+constexpr int kFirstProd = 2 + kDrainWarps;      // warps 0 TMA (weights), 1 MMA, 2-5 drain, 6-13 fix-up, 14 x in / out
+constexpr int kIoWarp = kFirstProd + kProdWarps;
+constexpr int kThreads = 32 * (kIoWarp + 1);
+constexpr int kRows = kBM / (kProdWarps * 2);   // frames a fix-up thread handles per unit (a warp spans 2 frame groups)
 
 struct Params {
     int K, Cout, n_tn, tiles_per_utt, row_tiles, items, groups;
-    __nv_bfloat16* x_hi;
-    __nv_bfloat16* x_lo;
     const float* y;
     const float2* in_stat;   // gLN-2 partials of the previous block
     int in_P;
     double in_count;
     const float* col_g;
     const float* col_bias;
-    float* a;                // out: PReLU(W1 x), fp32 [M*K, Cout]
     float2* out_stat;        // out: gLN-1 partials, ctn_gemm1x1 layout
     int out_P;
     const float* slope;
+    int dbg;   // CTN_C1_DBG experiment bits (0 in production): 1 no `a` stores, 2 no x stores, 4 no MMAs, 8 no y loads
 };
 
-struct Row {   // one frame's worth of a thread's inputs: 4 channels
-    uint2 hi, lo;
-    float4 y;
-};
-
+// The residual stream never passes through registers on its way in or out: the x-io thread TMA-loads the
+// (hi, lo) tiles of a k-block straight into the A slot (128B-swizzled, K-major: the tcgen05 operand layout) as
+// soon as the MMAs of the previous row tile have released it - up to a whole row tile ahead of its use -,
+// the fix-up warps rewrite the slot in place (x += sc y + cc, re-split), and the same thread TMA-stores the
+// slot back to the residual stream.  Only y goes through a register ring (16 rows = two units ahead).  The
+// LSU sees no global stores at all: `a` leaves through per-warp staging buffers and TMA stores as well.
 __global__ void __launch_bounds__(kThreads, 1)
-updc1_kernel(const __grid_constant__ CUtensorMap tm_w_hi, const __grid_constant__ CUtensorMap tm_w_lo, const Params p) {
+updc1_kernel(const __grid_constant__ CUtensorMap tm_w_hi, const __grid_constant__ CUtensorMap tm_w_lo,
+             const __grid_constant__ CUtensorMap tm_a, const __grid_constant__ CUtensorMap tm_x_hi,
+             const __grid_constant__ CUtensorMap tm_x_lo, const Params p) {
     const uint32_t rank = ptx::cluster_ctarank();
     const int worker = static_cast<int>(blockIdx.x >> 1);
     const int n_workers = static_cast<int>(gridDim.x >> 1);
     extern __shared__ __align__(1024) uint8_t smem[];
     if ((ptx::smem_u32(smem) & 1023u) != 0) __trap();
     uint8_t* wsm = smem + kKB * kASlotBytes;
-    uint64_t* afull_bar = reinterpret_cast<uint64_t*>(smem + kTileBytes);
-    uint64_t* aempty_bar = afull_bar + kKB;
-    uint64_t* wfull_bar = aempty_bar + kKB;
+    uint8_t* stg = smem + kTileBytes;
+    uint64_t* afull_bar = reinterpret_cast<uint64_t*>(smem + kTileBytes + kStgBytes);   // fixed-up A slot (leader's: both CTAs)
+    uint64_t* aempty_bar = afull_bar + kKB;     // slot released: MMAs of the last column tile + the x store have read it
+    uint64_t* araw_bar = aempty_bar + kKB;      // raw (hi, lo) tiles have landed
+    uint64_t* xdone_bar = araw_bar + kKB;       // all fix-up warps of this CTA have rewritten the slot
+    uint64_t* wfull_bar = xdone_bar + kKB;
     uint64_t* wempty_bar = wfull_bar + kWSlots;
     uint64_t* tfull_bar = wempty_bar + kWSlots;
     uint64_t* tempty_bar = tfull_bar + 2;
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 2);
-    float* colc = reinterpret_cast<float*>(smem + kTileBytes + kBarBytes);   // [2][kCin]
-    float2* tstat = reinterpret_cast<float2*>(smem + kTileBytes + kBarBytes + kColBytes);   // [kMaxTiles] (rstd, -rstd mean)
+    float* colc = reinterpret_cast<float*>(smem + kTileBytes + kStgBytes + kBarBytes);   // [2][kCin]
+    float2* tstat = reinterpret_cast<float2*>(smem + kTileBytes + kStgBytes + kBarBytes + kColBytes);   // [kMaxTiles] (rstd, -rstd mean)
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
@@ -92,9 +105,14 @@ updc1_kernel(const __grid_constant__ CUtensorMap tm_w_hi, const __grid_constant_
     if (warp == 0 && lane == 0) {
         ptx::prefetch_tmap(&tm_w_hi);
         ptx::prefetch_tmap(&tm_w_lo);
+        ptx::prefetch_tmap(&tm_a);
+        ptx::prefetch_tmap(&tm_x_hi);
+        ptx::prefetch_tmap(&tm_x_lo);
         for (int i = 0; i < kKB; ++i) {
-            ptx::mbar_init(afull_bar + i, 2 * kProdWarps);   // one arrival per producer warp, both CTAs
-            ptx::mbar_init(aempty_bar + i, 1);
+            ptx::mbar_init(afull_bar + i, 2 * kProdWarps);   // one arrival per fix-up warp, both CTAs
+            ptx::mbar_init(aempty_bar + i, 2);               // MMA commit + x store
+            ptx::mbar_init(araw_bar + i, 1);
+            ptx::mbar_init(xdone_bar + i, kProdWarps);
         }
         for (int i = 0; i < kWSlots; ++i) {
             ptx::mbar_init(wfull_bar + i, 1);
@@ -160,7 +178,7 @@ updc1_kernel(const __grid_constant__ CUtensorMap tm_w_hi, const __grid_constant_
                         const uint64_t w_hi = ptx::make_smem_desc(sw, 0, 1024, ptx::kLayoutSwizzle128B);
                         const uint64_t w_lo = ptx::make_smem_desc(sw + kWBytes, 0, 1024, ptx::kLayoutSwizzle128B);
 #pragma unroll
-                        for (int k = 0; k < kBK / 16; ++k) {
+                        for (int k = 0; k < ((p.dbg & 4) ? 0 : kBK / 16); ++k) {
                             const uint64_t adv = static_cast<uint64_t>((k * 16 * 2) >> 4);
                             ptx::umma_bf16_pair(d_tmem, a_hi + adv, w_hi + adv, idesc, (kb | k) != 0);
                             ptx::umma_bf16_pair(d_tmem, a_lo + adv, w_hi + adv, idesc, 1);
@@ -174,7 +192,40 @@ updc1_kernel(const __grid_constant__ CUtensorMap tm_w_hi, const __grid_constant_
                 }
             }
         }
-    } else if (warp < 2 + kDrainWarps) {
+    } else if (warp == kIoWarp) {
+        // ------------------------------------------------ x in / out (TMA)
+        // per row tile: the raw (hi, lo) tiles of the four k-blocks in, each as soon as its slot is free; then
+        // the rewritten slots out, each as soon as the fix-up warps are done with it.  Rows past the end of the
+        // utterance are zero-filled on the way in and clipped on the way out (3-D maps [M, K, C]).
+        if (lane == 0) {
+            for (int it = 0; it < n_tiles; ++it) {
+                const int rt = 2 * (worker + it * n_workers) + static_cast<int>(rank);
+                const bool tile_ok = rt < p.row_tiles;
+                const int m = tile_ok ? rt / p.tiles_per_utt : 0, tk = tile_ok ? rt % p.tiles_per_utt : 0;
+                const uint32_t ph = static_cast<uint32_t>(it) & 1u;
+                for (int kb = 0; kb < kKB; ++kb) {
+                    ptx::mbar_wait(aempty_bar + kb, ph ^ 1u);
+                    uint8_t* sl = smem + kb * kASlotBytes;
+                    ptx::mbar_expect_tx(araw_bar + kb, 2 * kABytes);
+                    // a pair's odd leftover row tile does not exist: coordinates past the last utterance (zero fill)
+                    ptx::tma_load_3d(sl, &tm_x_hi, araw_bar + kb, kb * kBK, tk * kBM, tile_ok ? m : 0x7fffff);
+                    ptx::tma_load_3d(sl + kABytes, &tm_x_lo, araw_bar + kb, kb * kBK, tk * kBM, tile_ok ? m : 0x7fffff);
+                }
+                for (int kb = 0; kb < kKB; ++kb) {
+                    ptx::mbar_wait(xdone_bar + kb, ph);
+                    if (tile_ok && !(p.dbg & 2)) {
+                        const uint32_t sl = ptx::smem_u32(smem + kb * kASlotBytes);
+                        ptx::tma_store_3d_addr(&tm_x_hi, sl, kb * kBK, tk * kBM, m);
+                        ptx::tma_store_3d_addr(&tm_x_lo, sl + kABytes, kb * kBK, tk * kBM, m);
+                        ptx::tma_store_commit();
+                    }
+                }
+                ptx::tma_store_wait_read<0>();   // the stores have read their slots: the next row tile may overwrite them
+                for (int kb = 0; kb < kKB; ++kb) ptx::mbar_arrive(aempty_bar + kb);
+            }
+            ptx::tma_store_wait_all<0>();
+        }
+    } else if (warp < kFirstProd) {
         // ------------------------------------------------------------- drainers
         // accumulator d (row tile it = d / n_tn, column tile tn = d % n_tn) -> PReLU -> statistics + a;
         // strictly in order, so the parity wait on a TMEM stage can never see a later accumulator
@@ -182,7 +233,8 @@ updc1_kernel(const __grid_constant__ CUtensorMap tm_w_hi, const __grid_constant_
         const uint32_t tempty_remote = ptx::mapa(ptx::smem_u32(tempty_bar), 0);
         const float slope = __ldg(p.slope);
         const int n_acc = n_tiles * p.n_tn;
-        int it = 0, tn = 0;
+        const uint32_t stg_base = ptx::smem_u32(stg) + static_cast<uint32_t>(warp - 2) * (2 * kStgChunk);
+        int it = 0, tn = 0, chunk = 0;
         for (int d = 0; d < n_acc; ++d) {
             const int as = d & 1;
             const int rt = 2 * (worker + it * n_workers) + static_cast<int>(rank);
@@ -190,22 +242,25 @@ updc1_kernel(const __grid_constant__ CUtensorMap tm_w_hi, const __grid_constant_
             const int m = tile_ok ? rt / p.tiles_per_utt : 0, tk = tile_ok ? rt % p.tiles_per_utt : 0;
             const int k = tk * kBM + ew * 32 + lane;
             const bool valid = tile_ok && k < p.K;
-            float* arow = p.a + (static_cast<long long>(m) * p.K + k) * p.Cout + tn * kBN;
             ptx::mbar_wait(tfull_bar + as, (d >> 1) & 1);
             ptx::tc_fence_after();
             float ls = 0.f, lss = 0.f;
+            const bool rows_ok = tile_ok && tk * kBM + ew * 32 < p.K;   // any of this warp's 32 frames exists
 #pragma unroll 1
-            for (int ci = 0; ci < kBN / 32; ++ci) {
+            for (int ci = 0; ci < kBN / 32; ++ci, ++chunk) {
                 uint32_t r[32];
                 ptx::tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(ew * 32) << 16) + as * kBN + ci * 32, r);
+                // the staging buffer about to be refilled: its previous TMA store (two chunks ago) must have read it
+                if (lane == 0) ptx::tma_store_wait_read<1>();
+                __syncwarp();
                 ptx::tmem_ld_wait();
-                if (valid) {
-                    float v[32];
+                float v[32];
 #pragma unroll
-                    for (int j = 0; j < 32; ++j) {
-                        const float t = __uint_as_float(r[j]);
-                        v[j] = fmaf(slope, fminf(t, 0.f), fmaxf(t, 0.f));   // PReLU
-                    }
+                for (int j = 0; j < 32; ++j) {
+                    const float t = __uint_as_float(r[j]);
+                    v[j] = fmaf(slope, fminf(t, 0.f), fmaxf(t, 0.f));   // PReLU
+                }
+                if (valid) {
                     float l0 = 0.f, l1 = 0.f, q0 = 0.f, q1 = 0.f;
 #pragma unroll
                     for (int j = 0; j < 32; j += 2) {
@@ -213,12 +268,21 @@ updc1_kernel(const __grid_constant__ CUtensorMap tm_w_hi, const __grid_constant_
                         q0 = fmaf(v[j], v[j], q0), q1 = fmaf(v[j + 1], v[j + 1], q1);
                     }
                     ls += l0 + l1, lss += q0 + q1;
+                }
+                // lane = frame: its 128 B row of the chunk, 16 B pieces XOR-swizzled with (row & 7) as the
+                // 128B-swizzled tensor map expects (also makes the warp's stores conflict-free)
+                const uint32_t sb = stg_base + static_cast<uint32_t>(chunk & 1) * kStgChunk + static_cast<uint32_t>(lane) * 128u;
 #pragma unroll
-                    for (int j = 0; j < 4; ++j)
-                        ptx::st_global_v8(arow + ci * 32 + 8 * j, __float_as_uint(v[8 * j]), __float_as_uint(v[8 * j + 1]),
-                                          __float_as_uint(v[8 * j + 2]), __float_as_uint(v[8 * j + 3]),
-                                          __float_as_uint(v[8 * j + 4]), __float_as_uint(v[8 * j + 5]),
-                                          __float_as_uint(v[8 * j + 6]), __float_as_uint(v[8 * j + 7]));
+                for (int j = 0; j < 8; ++j)
+                    ptx::st_shared_v4(sb + ((static_cast<uint32_t>(j) ^ (static_cast<uint32_t>(lane) & 7u)) << 4),
+                                      __float_as_uint(v[4 * j]), __float_as_uint(v[4 * j + 1]), __float_as_uint(v[4 * j + 2]),
+                                      __float_as_uint(v[4 * j + 3]));
+                ptx::fence_async_smem();
+                __syncwarp();
+                if (lane == 0 && rows_ok && !(p.dbg & 1)) {   // frames past K are clipped by the map
+                    ptx::tma_store_3d_addr(&tm_a, stg_base + static_cast<uint32_t>(chunk & 1) * kStgChunk, tn * kBN + ci * 32,
+                                           tk * kBM + ew * 32, m);
+                    ptx::tma_store_commit();
                 }
                 if ((ci & 3) == 3) {   // end of a 128-column group: one partial per (row tile, group, quarter)
                     const float ws = warp_sum(ls), wss = warp_sum(lss);
@@ -233,46 +297,43 @@ updc1_kernel(const __grid_constant__ CUtensorMap tm_w_hi, const __grid_constant_
             if (lane == 0) ptx::mbar_arrive_cluster(tempty_remote + as * 8);
             if (++tn == p.n_tn) tn = 0, ++it;
         }
+        if (lane == 0) ptx::tma_store_wait_all<0>();   // the staging buffers must outlive their stores
     } else {
-        // ------------------------------------------------------------ producers
-        // All eight warps fill one unit (row tile it, k-block kb: 128 frames x 64 channels) at a time;
-        // thread (quad, s) owns 4 channels of frames s*8 .. s*8+7.  While a row of the current unit is
-        // consumed, the same row of the NEXT unit is requested, so 8 rows (256 B) per thread are always
-        // in flight, also while the warp waits for its A slot to be released.
-        const int pt = (warp - 2 - kDrainWarps) * 32 + lane;   // 0 .. 255
+        // ------------------------------------------------------------ fix-up warps
+        // All eight warps rewrite one unit (row tile it, k-block kb: 128 frames x 64 channels) at a time;
+        // thread (quad, s) owns 4 channels of frames s*8 .. s*8+7.  x (hi, lo) is read from and written back
+        // to the A slot; y streams through a 16-row register ring: while a row of unit u is consumed, the
+        // same row of unit u + 2 is requested.
+        const int pt = (warp - kFirstProd) * 32 + lane;   // 0 .. 255
         const int quad = pt & 15, s = pt >> 4;
         const uint32_t full_remote = ptx::mapa(ptx::smem_u32(afull_bar), 0);
         const uint32_t row_off0 = static_cast<uint32_t>(s * kRows) * 128u;
         const uint32_t cs = static_cast<uint32_t>(quad >> 1) * 16u + static_cast<uint32_t>(quad & 1) * 8u;
         const f2_t neg1 = f2_pack(-1.f, -1.f);
 
-        auto ld_row = [&](long long off, bool ok) {
-            Row r;
-            r.hi = make_uint2(0u, 0u), r.lo = make_uint2(0u, 0u), r.y = make_float4(0.f, 0.f, 0.f, 0.f);
-            if (ok) {
-                asm volatile("ld.volatile.global.v2.b32 {%0, %1}, [%2];" : "=r"(r.hi.x), "=r"(r.hi.y) : "l"(p.x_hi + off) : "memory");
-                asm volatile("ld.volatile.global.v2.b32 {%0, %1}, [%2];" : "=r"(r.lo.x), "=r"(r.lo.y) : "l"(p.x_lo + off) : "memory");
+        auto ld_y = [&](long long off, bool ok) {
+            float4 r = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (ok && !(p.dbg & 8))
                 asm volatile("ld.volatile.global.v4.f32 {%0, %1, %2, %3}, [%4];"
-                             : "=f"(r.y.x), "=f"(r.y.y), "=f"(r.y.z), "=f"(r.y.w)
+                             : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w)
                              : "l"(p.y + off)
                              : "memory");
-            }
             return r;
         };
         struct Unit {
-            int m, nrows;
-            long long ox;      // element offset of (first row, first channel); x and y are both [M*K, 256]
+            int nrows;
+            long long oy;      // element offset of (first row, first channel) in y [M*K, 256]
         };
         auto unit = [&](int u) {
             Unit g;
             const int it = u >> 2, kb = u & 3;
             const int rt = 2 * (worker + it * n_workers) + static_cast<int>(rank);
             const bool ok = it < n_tiles && rt < p.row_tiles;
-            g.m = ok ? rt / p.tiles_per_utt : 0;
+            const int m = ok ? rt / p.tiles_per_utt : 0;
             const int tk = ok ? rt % p.tiles_per_utt : 0;
             const int k0 = tk * kBM + s * kRows;
             g.nrows = ok ? max(0, min(kRows, p.K - k0)) : 0;
-            g.ox = (static_cast<long long>(g.m) * p.K + k0) * kCin + kb * kBK + quad * 4;
+            g.oy = (static_cast<long long>(m) * p.K + k0) * kCin + kb * kBK + quad * 4;
             return g;
         };
 
@@ -280,27 +341,33 @@ updc1_kernel(const __grid_constant__ CUtensorMap tm_w_hi, const __grid_constant_
         // Consecutive row tiles of a CTA lie in different utterances (stride 2 * n_workers tiles), so the
         // statistics of the previous block change with every tile: finalise them up front, one tile per
         // warp, instead of a chain of dependent loads and fp64 math in front of every tile.
-        for (int t = warp - 2 - kDrainWarps; t < min(n_tiles, kMaxTiles); t += kProdWarps) {
+        for (int t = warp - kFirstProd; t < min(n_tiles, kMaxTiles); t += kProdWarps) {
             const int rt = 2 * (worker + t * n_workers) + static_cast<int>(rank);
             const int m = rt < p.row_tiles ? rt / p.tiles_per_utt : 0;
             const float2 st = gln_finalize_warp(p.in_stat + static_cast<long long>(m) * p.in_P, p.in_P, p.in_count);
             if (lane == 0) tstat[t] = make_float2(st.y, -st.y * st.x);
         }
         ptx::named_bar_sync(1, 32 * kProdWarps);
-        Unit nx = unit(0);
-        Row q[kRows];
+        float4 q[2][kRows];
+        Unit g0 = unit(0), g1 = unit(1);
 #pragma unroll
-        for (int t = 0; t < kRows; ++t) q[t] = ld_row(nx.ox + static_cast<long long>(t) * kCin, t < nx.nrows);
-        for (int u = 0; u < n_units; ++u) {
-            const Unit g = nx;
-            nx = unit(u + 1);
+        for (int t = 0; t < kRows; ++t) q[0][t] = ld_y(g0.oy + static_cast<long long>(t) * kCin, t < g0.nrows);
+#pragma unroll
+        for (int t = 0; t < kRows; ++t) q[1][t] = ld_y(g1.oy + static_cast<long long>(t) * kCin, t < g1.nrows);
+
+        // unit u with its y rows in ring half `par` (a compile-time index: the ring stays in registers)
+        auto do_unit = [&](int u, auto par_tag) {
+            constexpr int par = decltype(par_tag)::value;
+            const Unit nx = unit(u + 2);
             const int it = u >> 2, kb = u & 3;
             float sc, sh;
             if (it < kMaxTiles) {
                 const float2 st = tstat[it];
                 sc = st.x, sh = st.y;
             } else {
-                const float2 st = gln_finalize_warp(p.in_stat + static_cast<long long>(g.m) * p.in_P, p.in_P, p.in_count);
+                const int rt = 2 * (worker + it * n_workers) + static_cast<int>(rank);
+                const int m = rt < p.row_tiles ? rt / p.tiles_per_utt : 0;
+                const float2 st = gln_finalize_warp(p.in_stat + static_cast<long long>(m) * p.in_P, p.in_P, p.in_count);
                 sc = st.y, sh = -st.y * st.x;
             }
             const int c = kb * kBK + quad * 4;
@@ -309,40 +376,46 @@ updc1_kernel(const __grid_constant__ CUtensorMap tm_w_hi, const __grid_constant_
             const f2_t cc0 = f2_pack(fmaf(sh, cg.x, cb.x), fmaf(sh, cg.y, cb.y));
             const f2_t cc1 = f2_pack(fmaf(sh, cg.z, cb.z), fmaf(sh, cg.w, cb.w));
             const f2_t sc2 = f2_pack(sc, sc);
-            ptx::mbar_wait(aempty_bar + kb, (static_cast<uint32_t>(it) & 1u) ^ 1u);
+            ptx::mbar_wait(araw_bar + kb, static_cast<uint32_t>(it) & 1u);
             const uint32_t hi_base = ptx::smem_u32(smem + kb * kASlotBytes) + row_off0;
 #pragma unroll
             for (int o = 0; o < kRows; ++o) {
-                const Row r = q[o];
-                q[o] = ld_row(nx.ox + static_cast<long long>(o) * kCin, o < nx.nrows);
+                const uint32_t ad = ((hi_base + cs) ^ (static_cast<uint32_t>(o & 7) << 4)) + static_cast<uint32_t>(o) * 128u;
+                uint32_t xh0, xh1, xl0, xl1;
+                asm volatile("ld.shared.v2.b32 {%0, %1}, [%2];" : "=r"(xh0), "=r"(xh1) : "r"(ad) : "memory");
+                asm volatile("ld.shared.v2.b32 {%0, %1}, [%2];" : "=r"(xl0), "=r"(xl1) : "r"(ad + kABytes) : "memory");
+                const float4 yv = q[par][o];
                 // x = hi + lo (exact in fp32), x' = x + sc * y + cc
 #if CTN_OPERAND_FP16
                 float e0, e1, e2, e3, e4, e5, e6, e7;
-                op16_value2(r.hi.x, e0, e1), op16_value2(r.hi.y, e2, e3), op16_value2(r.lo.x, e4, e5), op16_value2(r.lo.y, e6, e7);
+                op16_value2(xh0, e0, e1), op16_value2(xh1, e2, e3), op16_value2(xl0, e4, e5), op16_value2(xl1, e6, e7);
                 const f2_t h0 = f2_pack(e0, e1), h1 = f2_pack(e2, e3), l0 = f2_pack(e4, e5), l1 = f2_pack(e6, e7);
 #else
-                const f2_t h0 = f2_pack(__uint_as_float(r.hi.x << 16), __uint_as_float(r.hi.x & 0xffff0000u));
-                const f2_t h1 = f2_pack(__uint_as_float(r.hi.y << 16), __uint_as_float(r.hi.y & 0xffff0000u));
-                const f2_t l0 = f2_pack(__uint_as_float(r.lo.x << 16), __uint_as_float(r.lo.x & 0xffff0000u));
-                const f2_t l1 = f2_pack(__uint_as_float(r.lo.y << 16), __uint_as_float(r.lo.y & 0xffff0000u));
+                const f2_t h0 = f2_pack(__uint_as_float(xh0 << 16), __uint_as_float(xh0 & 0xffff0000u));
+                const f2_t h1 = f2_pack(__uint_as_float(xh1 << 16), __uint_as_float(xh1 & 0xffff0000u));
+                const f2_t l0 = f2_pack(__uint_as_float(xl0 << 16), __uint_as_float(xl0 & 0xffff0000u));
+                const f2_t l1 = f2_pack(__uint_as_float(xl1 << 16), __uint_as_float(xl1 & 0xffff0000u));
 #endif
-                f2_t v0 = f2_add(f2_fma(sc2, f2_pack(r.y.x, r.y.y), cc0), f2_add(h0, l0));
-                f2_t v1 = f2_add(f2_fma(sc2, f2_pack(r.y.z, r.y.w), cc1), f2_add(h1, l1));
-                uint32_t nh[2] = {0u, 0u}, nl[2] = {0u, 0u};
-                if (o < g.nrows) {
-                    f2_split_bf16(v0, neg1, nh[0], nl[0]);
-                    f2_split_bf16(v1, neg1, nh[1], nl[1]);
-                    const long long off = g.ox + static_cast<long long>(o) * kCin;
-                    asm volatile("st.global.v2.b32 [%0], {%1, %2};" ::"l"(p.x_hi + off), "r"(nh[0]), "r"(nh[1]) : "memory");
-                    asm volatile("st.global.v2.b32 [%0], {%1, %2};" ::"l"(p.x_lo + off), "r"(nl[0]), "r"(nl[1]) : "memory");
-                }
-                const uint32_t ad = ((hi_base + cs) ^ (static_cast<uint32_t>(o & 7) << 4)) + static_cast<uint32_t>(o) * 128u;
-                asm volatile("st.volatile.shared.v2.b32 [%0], {%1, %2};" ::"r"(ad), "r"(nh[0]), "r"(nh[1]) : "memory");
-                asm volatile("st.volatile.shared.v2.b32 [%0], {%1, %2};" ::"r"(ad + kABytes), "r"(nl[0]), "r"(nl[1]) : "memory");
+                const f2_t v0 = f2_add(f2_fma(sc2, f2_pack(yv.x, yv.y), cc0), f2_add(h0, l0));
+                const f2_t v1 = f2_add(f2_fma(sc2, f2_pack(yv.z, yv.w), cc1), f2_add(h1, l1));
+                // refill AFTER the last use of the ring slot, so that the load targets the registers it frees
+                q[par][o] = ld_y(nx.oy + static_cast<long long>(o) * kCin, o < nx.nrows);
+                uint32_t nh0, nl0, nh1, nl1;
+                f2_split_bf16(v0, neg1, nh0, nl0);
+                f2_split_bf16(v1, neg1, nh1, nl1);
+                asm volatile("st.shared.v2.b32 [%0], {%1, %2};" ::"r"(ad), "r"(nh0), "r"(nh1) : "memory");
+                asm volatile("st.shared.v2.b32 [%0], {%1, %2};" ::"r"(ad + kABytes), "r"(nl0), "r"(nl1) : "memory");
             }
-            ptx::fence_async_smem();
+            ptx::fence_async_smem();      // generic-proxy stores -> visible to the tensor core and the TMA store
             __syncwarp();
-            if (lane == 0) ptx::mbar_arrive_cluster(full_remote + kb * 8);
+            if (lane == 0) {
+                ptx::mbar_arrive_cluster(full_remote + kb * 8);
+                ptx::mbar_arrive(xdone_bar + kb);
+            }
+        };
+        for (int u = 0; u < n_units; u += 2) {
+            do_unit(u, std::integral_constant<int, 0>{});
+            if (u + 1 < n_units) do_unit(u + 1, std::integral_constant<int, 1>{});
         }
     }
 
@@ -384,15 +457,23 @@ extern "C" int ctn_updc1_fwd(const ctn_updc1_args* args, void* stream_) {
     p.row_tiles = a.M * p.tiles_per_utt;
     p.items = ceil_div(p.row_tiles, 2);
     p.groups = ceil_div(a.H, CTN_COL_TILE);
-    p.x_hi = static_cast<__nv_bfloat16*>(a.x_hi), p.x_lo = static_cast<__nv_bfloat16*>(a.x_lo);
     p.y = a.y, p.in_stat = static_cast<const float2*>(a.in_stat), p.in_P = a.in_P, p.in_count = a.in_count;
-    p.col_g = a.col_g, p.col_bias = a.col_bias, p.a = a.a, p.out_stat = static_cast<float2*>(a.out_stat);
+    p.col_g = a.col_g, p.col_bias = a.col_bias, p.out_stat = static_cast<float2*>(a.out_stat);
     p.out_P = ctn_gemm_gln_partials(a.K, a.H);
     p.slope = a.slope;
+    {
+        const char* d = getenv("CTN_C1_DBG");
+        p.dbg = d ? atoi(d) : 0;
+    }
     CUtensorMap tw_hi, tw_lo;
     int rc;
     if ((rc = make_tmap_bf16_kmajor(&tw_hi, a.w_hi, a.H, a.B, c1::kBN / 2)) != CTN_OK) return rc;
     if ((rc = make_tmap_bf16_kmajor(&tw_lo, a.w_lo, a.H, a.B, c1::kBN / 2)) != CTN_OK) return rc;
+    CUtensorMap ta;   // [M, K, H] fp32, box 32 columns x 32 frames of one utterance, 128B swizzle
+    if ((rc = make_tmap_out(&ta, a.a, a.M, a.K, a.H, true)) != CTN_OK) return rc;
+    CUtensorMap tx_hi, tx_lo;   // [M, K, B] bf16, box 64 channels x 128 frames of one utterance, 128B swizzle (in and out)
+    if ((rc = make_tmap_bf16_3d(&tx_hi, a.x_hi, a.M, a.K, a.B, c1::kBM)) != CTN_OK) return rc;
+    if ((rc = make_tmap_bf16_3d(&tx_lo, a.x_lo, a.M, a.K, a.B, c1::kBM)) != CTN_OK) return rc;
     static bool attr_done[kMaxDevices] = {};
     bool& attr_set = attr_done[device_slot()];
     if (!attr_set) {
@@ -414,7 +495,7 @@ extern "C" int ctn_updc1_fwd(const ctn_updc1_args* args, void* stream_) {
     attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
-    cudaError_t e = cudaLaunchKernelEx(&cfg, c1::updc1_kernel, tw_hi, tw_lo, p);
+    cudaError_t e = cudaLaunchKernelEx(&cfg, c1::updc1_kernel, tw_hi, tw_lo, ta, tx_hi, tx_lo, p);
     if (e != cudaSuccess) return cuda_fail(e, "cudaLaunchKernelEx(updc1_kernel)");
     return CTN_OK;
 }

@@ -693,7 +693,7 @@ int make_tmap_bf16_kmajor(CUtensorMap* tm, const void* ptr, long long rows, int 
 
 // [M, K, C] row-major output, box = 32 columns x 32 frames of one utterance; rows past K are
 // clipped by the map, so a partial last row tile never touches the next utterance.
-static int make_tmap_out(CUtensorMap* tm, const void* ptr, int M, int K, int C, bool f32) {
+int make_tmap_out(CUtensorMap* tm, const void* ptr, int M, int K, int C, bool f32) {
     PFN_encodeTiled enc = get_encode_fn();
     if (!enc) {
         set_error("cuTensorMapEncodeTiled not available from the driver");
@@ -710,6 +710,28 @@ static int make_tmap_out(CUtensorMap* tm, const void* ptr, int M, int K, int C, 
                      CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) {
         set_error("cuTensorMapEncodeTiled(out) failed (%d) ptr=%p M=%d K=%d C=%d", static_cast<int>(r), ptr, M, K, C);
+        return CTN_ERR_CUDA;
+    }
+    return CTN_OK;
+}
+
+// bf16 [M, K, C] row-major, box = 64 channels x box_rows frames of ONE utterance, 128B swizzle: loads zero-fill
+// frames past K, stores clip them (a row tile never touches the next utterance).
+int make_tmap_bf16_3d(CUtensorMap* tm, const void* ptr, int M, int K, int C, int box_rows) {
+    PFN_encodeTiled enc = get_encode_fn();
+    if (!enc) {
+        set_error("cuTensorMapEncodeTiled not available from the driver");
+        return CTN_ERR_CUDA;
+    }
+    cuuint64_t dims[3] = {static_cast<cuuint64_t>(C), static_cast<cuuint64_t>(K), static_cast<cuuint64_t>(M)};
+    cuuint64_t strides[2] = {static_cast<cuuint64_t>(C) * 2, static_cast<cuuint64_t>(C) * 2 * K};
+    cuuint32_t box[3] = {static_cast<cuuint32_t>(kBK), static_cast<cuuint32_t>(box_rows), 1};
+    cuuint32_t estr[3] = {1, 1, 1};
+    CUresult r = enc(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(ptr), dims, strides, box, estr,
+                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) {
+        set_error("cuTensorMapEncodeTiled(3d) failed (%d) ptr=%p M=%d K=%d C=%d", static_cast<int>(r), ptr, M, K, C);
         return CTN_ERR_CUDA;
     }
     return CTN_OK;
