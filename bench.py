@@ -613,7 +613,7 @@ def main():
     ap.add_argument("--micro-batch", type=int, default=64)
     ap.add_argument("--fuse", type=int, default=1 << 30,
                     help="blocks with dilation <= this use the fused depthwise+pointwise kernel (0 = off)")
-    ap.add_argument("--fuse-update", type=int, default=0,
+    ap.add_argument("--fuse-update", type=int, default=1,
                     help="fold the deferred residual update into the next conv1x1 (ctn_updc1_fwd)")
     ap.add_argument("--graph", type=int, default=1)
     ap.add_argument("--streams", type=int, default=1,

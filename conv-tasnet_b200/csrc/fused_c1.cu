@@ -2,16 +2,24 @@
 //     x <- x + r y - r mu rowsum + W2 beta2         (gLN-2 of the PREVIOUS block, conv_tasnet.py:254-256, :237)
 //     a  = PReLU(W1 x),  (sum, sumsq) of a          (conv1x1 of THIS block, :217-218, statistics for :219)
 // ctn_dwpw_fwd leaves the previous block's pointwise product y un-normalised because gLN-2 needs the
-// statistics of the whole utterance; here they are complete.  SIMT producer warps read x (hi, lo)
-// and y, form the new x, write it back (the residual stream, 1 KB per frame) and store it
-// 128B-swizzled, K-major into the shared-memory slot the tcgen05 MMAs read as their A operand.  The
-// A tile (128 frames x 256 channels) stays resident while BOTH 256-column tiles of Cout = 512 are
-// multiplied, so it is produced once per row tile; only the weights stream (TMA, 3 slots).
-// Replaces ctn_resid_update + ctn_gemm1x1: 6 KB -> 5 KB per frame and block, one launch fewer.
+// statistics of the whole utterance; here they are complete.  Replaces ctn_resid_update + ctn_gemm1x1:
+// 6 KB -> 5 KB per frame and block, one launch fewer.
 //
-// CTA pair (cta_group::2), warps: 0 TMA (weights), 1 MMA issuer, 2-5 drain the TMEM accumulators
-// (PReLU, statistics, 256-bit stores), 6-13 producers.  The producers are latency-bound, not
-// FMA-bound like fused_block.cu's, so they never leave their load stream to drain.
+// CTA pair (cta_group::2); per CTA a row tile of 128 frames whose whole reduction dimension (B = 256: four
+// k-block slots of (hi, lo), 128 KB) stays resident while BOTH 256-column tiles of Cout = 512 are multiplied.
+// Nothing on the residual stream passes through the LSU as a global access:
+//   x in   one thread TMA-loads the (hi, lo) tiles of a k-block straight into its A slot (128B-swizzled,
+//          K-major: the tcgen05 operand layout) as soon as the MMAs of the previous row tile released it;
+//   fix-up eight warps rewrite the slot in place: x += sc y + cc, re-split; y streams through a 16-row
+//          register ring (two units ahead);
+//   x out  one thread TMA-stores the rewritten slot back to the residual stream (3-D maps clip at K);
+//   MMA    one thread, three MMAs per k-step, two TMEM accumulator stages; weights by TMA (2 slots);
+//   drain  four warps: TMEM -> PReLU -> statistics -> 4 KB staging buffer -> TMA store of `a`.
+// Measured per 64 utterances (tools/bench_updc1.py): 203 us against 99 + 155..162 us for the two kernels it
+// replaces; register-ring loads of x and 256-bit global stores (the first version) gave 243 us: the loads
+// of a latency-bound ring and the scattered stores queue behind each other in the LSU, and every load's
+// latency stretches to several microseconds once the stores saturate the memory system.
+// Warps: 0 TMA (weights), 1 MMA issuer, 2-5 drain, 6-13 fix-up, 14 x in, 15 x out.
 #include <cuda.h>
 #include <stdlib.h>
 
@@ -28,6 +36,20 @@ int make_tmap_out(CUtensorMap* tm, const void* ptr, int M, int K, int C, bool f3
 int make_tmap_bf16_3d(CUtensorMap* tm, const void* ptr, int M, int K, int C, int box_rows);             // gemm.cu
 
 namespace c1 {
+
+// -DCTN_TRACE=1 (experiment builds only): CTA 0 records clock64() at the pipeline events of each of its row tiles
+// in a device array that ctn_debug_trace_read() copies out (tools/bench_updc1.py prints the timeline).
+#if CTN_TRACE
+__device__ long long g_trace[64 * 32];
+#define C1_TRACE(it, ev)                                                              \
+    do {                                                                              \
+        if (blockIdx.x == 0 && (it) < 64) g_trace[(it) * 32 + (ev)] = clock64();      \
+    } while (0)
+#else
+#define C1_TRACE(it, ev) \
+    do {                 \
+    } while (0)
+#endif
 
 constexpr int kBM = 128;
 constexpr int kBN = 256;             // output columns per accumulator
@@ -48,9 +70,10 @@ constexpr int kStgChunk = 32 * 32 * 4;           // one drained chunk: 32 frames
 constexpr int kStgBytes = kDrainWarps * 2 * kStgChunk;   // two per drain warp: the TMA store of one reads while the next fills
 constexpr int kSmemBytes = kTileBytes + kStgBytes + kBarBytes + kColBytes + kMaxTiles * 8;
 constexpr int kProdWarps = 8;
-constexpr int kFirstProd = 2 + kDrainWarps;      // warps 0 TMA (weights), 1 MMA, 2-5 drain, 6-13 fix-up, 14 x in / out
-constexpr int kIoWarp = kFirstProd + kProdWarps;
-constexpr int kThreads = 32 * (kIoWarp + 1);
+constexpr int kFirstProd = 2 + kDrainWarps;      // warps 0 TMA (weights), 1 MMA, 2-5 drain, 6-13 fix-up, 14 x in, 15 x out
+constexpr int kInWarp = kFirstProd + kProdWarps;
+constexpr int kOutWarp = kInWarp + 1;
+constexpr int kThreads = 32 * (kOutWarp + 1);
 constexpr int kRows = kBM / (kProdWarps * 2);   // frames a fix-up thread handles per unit (a warp spans 2 frame groups)
 
 struct Params {
@@ -140,16 +163,15 @@ updc1_kernel(const __grid_constant__ CUtensorMap tm_w_hi, const __grid_constant_
             uint32_t phase = 0;
             const uint32_t fb0 = ptx::mapa(ptx::smem_u32(wfull_bar), 0);
             for (int it = 0; it < n_tiles; ++it) {
-                for (int tn = 0; tn < p.n_tn; ++tn) {
-                    for (int kb = 0; kb < kKB; ++kb) {
-                        ptx::mbar_wait(wempty_bar + slot, phase ^ 1);
-                        uint8_t* st = wsm + slot * kWSlotBytes;
-                        if (rank == 0) ptx::mbar_expect_tx(wfull_bar + slot, 4 * kWBytes);
-                        const int n0 = tn * kBN + static_cast<int>(rank) * (kBN / 2);
-                        ptx::tma_load_2d_pair(st, &tm_w_hi, fb0 + slot * 8, kb * kBK, n0);
-                        ptx::tma_load_2d_pair(st + kWBytes, &tm_w_lo, fb0 + slot * 8, kb * kBK, n0);
-                        if (++slot == kWSlots) slot = 0, phase ^= 1;
-                    }
+                for (int step = 0; step < p.n_tn * kKB; ++step) {
+                    const int tn = step / kKB, kb = step % kKB;
+                    ptx::mbar_wait(wempty_bar + slot, phase ^ 1);
+                    uint8_t* st = wsm + slot * kWSlotBytes;
+                    if (rank == 0) ptx::mbar_expect_tx(wfull_bar + slot, 4 * kWBytes);
+                    const int n0 = tn * kBN + static_cast<int>(rank) * (kBN / 2);
+                    ptx::tma_load_2d_pair(st, &tm_w_hi, fb0 + slot * 8, kb * kBK, n0);
+                    ptx::tma_load_2d_pair(st + kWBytes, &tm_w_lo, fb0 + slot * 8, kb * kBK, n0);
+                    if (++slot == kWSlots) slot = 0, phase ^= 1;
                 }
             }
         }
@@ -159,58 +181,71 @@ updc1_kernel(const __grid_constant__ CUtensorMap tm_w_hi, const __grid_constant_
             constexpr uint32_t idesc = ptx::make_idesc_bf16(2 * kBM, kBN, 0, 0);
             int wslot = 0;
             uint32_t wph = 0;
-            int d = 0;   // accumulator counter
             for (int it = 0; it < n_tiles; ++it) {
                 const uint32_t aph = it & 1;
-                for (int tn = 0; tn < p.n_tn; ++tn, ++d) {
+                for (int step = 0; step < p.n_tn * kKB; ++step) {
+                    const int tn = step / kKB, kb = step % kKB;
+                    const int d = it * p.n_tn + tn;   // accumulator number: TMEM stage d & 1
                     const int as = d & 1;
-                    ptx::mbar_wait(tempty_bar + as, ((d >> 1) & 1) ^ 1);
-                    ptx::tc_fence_after();
-                    const uint32_t d_tmem = tmem_base + as * kBN;
-                    for (int kb = 0; kb < kKB; ++kb) {
-                        ptx::mbar_wait(wfull_bar + wslot, wph);
-                        if (tn == 0) ptx::mbar_wait(afull_bar + kb, aph);
+                    if (kb == 0) {                    // first MMA into this stage: its previous contents must be drained
+                        ptx::mbar_wait(tempty_bar + as, ((d >> 1) & 1) ^ 1);
                         ptx::tc_fence_after();
-                        const uint32_t sa = ptx::smem_u32(smem + kb * kASlotBytes);
-                        const uint32_t sw = ptx::smem_u32(wsm + wslot * kWSlotBytes);
-                        const uint64_t a_hi = ptx::make_smem_desc(sa, 0, 1024, ptx::kLayoutSwizzle128B);
-                        const uint64_t a_lo = ptx::make_smem_desc(sa + kABytes, 0, 1024, ptx::kLayoutSwizzle128B);
-                        const uint64_t w_hi = ptx::make_smem_desc(sw, 0, 1024, ptx::kLayoutSwizzle128B);
-                        const uint64_t w_lo = ptx::make_smem_desc(sw + kWBytes, 0, 1024, ptx::kLayoutSwizzle128B);
-#pragma unroll
-                        for (int k = 0; k < ((p.dbg & 4) ? 0 : kBK / 16); ++k) {
-                            const uint64_t adv = static_cast<uint64_t>((k * 16 * 2) >> 4);
-                            ptx::umma_bf16_pair(d_tmem, a_hi + adv, w_hi + adv, idesc, (kb | k) != 0);
-                            ptx::umma_bf16_pair(d_tmem, a_lo + adv, w_hi + adv, idesc, 1);
-                            ptx::umma_bf16_pair(d_tmem, a_hi + adv, w_lo + adv, idesc, 1);
-                        }
-                        ptx::umma_commit_pair(wempty_bar + wslot, 3);
-                        if (tn == p.n_tn - 1) ptx::umma_commit_pair(aempty_bar + kb, 3);   // last use of the A slot
-                        if (kb == kKB - 1) ptx::umma_commit_pair(tfull_bar + as, 3);
-                        if (++wslot == kWSlots) wslot = 0, wph ^= 1;
                     }
+                    const uint32_t d_tmem = tmem_base + as * kBN;
+                    ptx::mbar_wait(wfull_bar + wslot, wph);
+                    if (tn == 0) ptx::mbar_wait(afull_bar + kb, aph);
+                    ptx::tc_fence_after();
+                    const uint32_t sa = ptx::smem_u32(smem + kb * kASlotBytes);
+                    const uint32_t sw = ptx::smem_u32(wsm + wslot * kWSlotBytes);
+                    const uint64_t a_hi = ptx::make_smem_desc(sa, 0, 1024, ptx::kLayoutSwizzle128B);
+                    const uint64_t a_lo = ptx::make_smem_desc(sa + kABytes, 0, 1024, ptx::kLayoutSwizzle128B);
+                    const uint64_t w_hi = ptx::make_smem_desc(sw, 0, 1024, ptx::kLayoutSwizzle128B);
+                    const uint64_t w_lo = ptx::make_smem_desc(sw + kWBytes, 0, 1024, ptx::kLayoutSwizzle128B);
+#pragma unroll
+                    for (int k = 0; k < ((p.dbg & 4) ? 0 : kBK / 16); ++k) {
+                        const uint64_t adv = static_cast<uint64_t>((k * 16 * 2) >> 4);
+                        ptx::umma_bf16_pair(d_tmem, a_hi + adv, w_hi + adv, idesc, (kb | k) != 0);
+                        ptx::umma_bf16_pair(d_tmem, a_lo + adv, w_hi + adv, idesc, 1);
+                        ptx::umma_bf16_pair(d_tmem, a_hi + adv, w_lo + adv, idesc, 1);
+                    }
+                    C1_TRACE(it, 16 + step);
+                    ptx::umma_commit_pair(wempty_bar + wslot, 3);
+                    if (tn == p.n_tn - 1) ptx::umma_commit_pair(aempty_bar + kb, 3);   // last use of the A slot
+                    if (kb == kKB - 1) ptx::umma_commit_pair(tfull_bar + as, 3);
+                    if (++wslot == kWSlots) wslot = 0, wph ^= 1;
                 }
             }
         }
-    } else if (warp == kIoWarp) {
-        // ------------------------------------------------ x in / out (TMA)
-        // per row tile: the raw (hi, lo) tiles of the four k-blocks in, each as soon as its slot is free; then
-        // the rewritten slots out, each as soon as the fix-up warps are done with it.  Rows past the end of the
-        // utterance are zero-filled on the way in and clipped on the way out (3-D maps [M, K, C]).
+    } else if (warp == kInWarp) {
+        // ------------------------------------------------ x in (TMA): the raw (hi, lo) tiles of a k-block, as soon
+        // as its slot is free.  Rows past the end of the utterance are zero-filled (3-D map [M, K, C]).
+        if (lane == 0) {
+            for (int it = 0; it < n_tiles; ++it) {
+                const int rt = 2 * (worker + it * n_workers) + static_cast<int>(rank);
+                const bool tile_ok = rt < p.row_tiles;
+                // a pair's odd leftover row tile does not exist: coordinates past the last utterance (zero fill)
+                const int m = tile_ok ? rt / p.tiles_per_utt : 0x7fffff, tk = tile_ok ? rt % p.tiles_per_utt : 0;
+                const uint32_t ph = static_cast<uint32_t>(it) & 1u;
+                for (int kb = 0; kb < kKB; ++kb) {
+                    ptx::mbar_wait(aempty_bar + kb, ph ^ 1u);
+                    uint8_t* sl = smem + kb * kASlotBytes;
+                    ptx::mbar_expect_tx(araw_bar + kb, 2 * kABytes);
+                    ptx::tma_load_3d(sl, &tm_x_hi, araw_bar + kb, kb * kBK, tk * kBM, m);
+                    ptx::tma_load_3d(sl + kABytes, &tm_x_lo, araw_bar + kb, kb * kBK, tk * kBM, m);
+                    C1_TRACE(it, kb);
+                }
+            }
+        }
+    } else if (warp == kOutWarp) {
+        // ------------------------------------------------ x out (TMA): the rewritten slots, as soon as the fix-up
+        // warps are done with them; frames past the end of the utterance are clipped by the map.  A slot is
+        // released (together with the MMAs' commit) once the store has read it.
         if (lane == 0) {
             for (int it = 0; it < n_tiles; ++it) {
                 const int rt = 2 * (worker + it * n_workers) + static_cast<int>(rank);
                 const bool tile_ok = rt < p.row_tiles;
                 const int m = tile_ok ? rt / p.tiles_per_utt : 0, tk = tile_ok ? rt % p.tiles_per_utt : 0;
                 const uint32_t ph = static_cast<uint32_t>(it) & 1u;
-                for (int kb = 0; kb < kKB; ++kb) {
-                    ptx::mbar_wait(aempty_bar + kb, ph ^ 1u);
-                    uint8_t* sl = smem + kb * kASlotBytes;
-                    ptx::mbar_expect_tx(araw_bar + kb, 2 * kABytes);
-                    // a pair's odd leftover row tile does not exist: coordinates past the last utterance (zero fill)
-                    ptx::tma_load_3d(sl, &tm_x_hi, araw_bar + kb, kb * kBK, tk * kBM, tile_ok ? m : 0x7fffff);
-                    ptx::tma_load_3d(sl + kABytes, &tm_x_lo, araw_bar + kb, kb * kBK, tk * kBM, tile_ok ? m : 0x7fffff);
-                }
                 for (int kb = 0; kb < kKB; ++kb) {
                     ptx::mbar_wait(xdone_bar + kb, ph);
                     if (tile_ok && !(p.dbg & 2)) {
@@ -219,9 +254,13 @@ updc1_kernel(const __grid_constant__ CUtensorMap tm_w_hi, const __grid_constant_
                         ptx::tma_store_3d_addr(&tm_x_lo, sl + kABytes, kb * kBK, tk * kBM, m);
                         ptx::tma_store_commit();
                     }
+                    C1_TRACE(it, 12 + kb);
+                    if (kb & 1) {
+                        ptx::tma_store_wait_read<0>();
+                        ptx::mbar_arrive(aempty_bar + kb - 1);
+                        ptx::mbar_arrive(aempty_bar + kb);
+                    }
                 }
-                ptx::tma_store_wait_read<0>();   // the stores have read their slots: the next row tile may overwrite them
-                for (int kb = 0; kb < kKB; ++kb) ptx::mbar_arrive(aempty_bar + kb);
             }
             ptx::tma_store_wait_all<0>();
         }
@@ -244,6 +283,7 @@ updc1_kernel(const __grid_constant__ CUtensorMap tm_w_hi, const __grid_constant_
             const bool valid = tile_ok && k < p.K;
             ptx::mbar_wait(tfull_bar + as, (d >> 1) & 1);
             ptx::tc_fence_after();
+            if (warp == 2 && lane == 0) C1_TRACE(it, 24 + 2 * tn);
             float ls = 0.f, lss = 0.f;
             const bool rows_ok = tile_ok && tk * kBM + ew * 32 < p.K;   // any of this warp's 32 frames exists
 #pragma unroll 1
@@ -295,6 +335,7 @@ updc1_kernel(const __grid_constant__ CUtensorMap tm_w_hi, const __grid_constant_
             ptx::tc_fence_before();
             __syncwarp();
             if (lane == 0) ptx::mbar_arrive_cluster(tempty_remote + as * 8);
+            if (warp == 2 && lane == 0) C1_TRACE(it, 25 + 2 * tn);
             if (++tn == p.n_tn) tn = 0, ++it;
         }
         if (lane == 0) ptx::tma_store_wait_all<0>();   // the staging buffers must outlive their stores
@@ -377,6 +418,7 @@ updc1_kernel(const __grid_constant__ CUtensorMap tm_w_hi, const __grid_constant_
             const f2_t cc1 = f2_pack(fmaf(sh, cg.z, cb.z), fmaf(sh, cg.w, cb.w));
             const f2_t sc2 = f2_pack(sc, sc);
             ptx::mbar_wait(araw_bar + kb, static_cast<uint32_t>(it) & 1u);
+            if (pt == 0) C1_TRACE(it, 4 + kb);
             const uint32_t hi_base = ptx::smem_u32(smem + kb * kASlotBytes) + row_off0;
 #pragma unroll
             for (int o = 0; o < kRows; ++o) {
@@ -412,6 +454,7 @@ updc1_kernel(const __grid_constant__ CUtensorMap tm_w_hi, const __grid_constant_
                 ptx::mbar_arrive_cluster(full_remote + kb * 8);
                 ptx::mbar_arrive(xdone_bar + kb);
             }
+            if (pt == 0) C1_TRACE(it, 8 + kb);
         };
         for (int u = 0; u < n_units; u += 2) {
             do_unit(u, std::integral_constant<int, 0>{});
@@ -431,6 +474,12 @@ updc1_kernel(const __grid_constant__ CUtensorMap tm_w_hi, const __grid_constant_
 }  // namespace ctn
 
 using namespace ctn;
+
+#if CTN_TRACE
+extern "C" int ctn_debug_trace_read(long long* host, int n) {
+    return cudaMemcpyFromSymbol(host, c1::g_trace, sizeof(long long) * n) == cudaSuccess ? CTN_OK : CTN_ERR_CUDA;
+}
+#endif
 
 extern "C" int ctn_updc1_supported(int B, int H, int norm) {
     return norm == CTN_NORM_GLN && B == c1::kCin && H >= c1::kBN && H <= 4 * c1::kBN && H % c1::kBN == 0;
@@ -474,6 +523,7 @@ extern "C" int ctn_updc1_fwd(const ctn_updc1_args* args, void* stream_) {
     CUtensorMap tx_hi, tx_lo;   // [M, K, B] bf16, box 64 channels x 128 frames of one utterance, 128B swizzle (in and out)
     if ((rc = make_tmap_bf16_3d(&tx_hi, a.x_hi, a.M, a.K, a.B, c1::kBM)) != CTN_OK) return rc;
     if ((rc = make_tmap_bf16_3d(&tx_lo, a.x_lo, a.M, a.K, a.B, c1::kBM)) != CTN_OK) return rc;
+
     static bool attr_done[kMaxDevices] = {};
     bool& attr_set = attr_done[device_slot()];
     if (!attr_set) {

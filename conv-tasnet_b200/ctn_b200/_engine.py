@@ -415,8 +415,8 @@ class SeparationEngine:
         # allows it (0 = never; the default covers every dilation)
         self.fuse_max_dilation = 1 << 30
         # after a fused block, fold its deferred residual update into the next block's conv1x1
-        # (ctn_updc1_fwd).  Parity-green but not faster than ctn_resid_update + ctn_gemm1x1 yet
-        self.fuse_update = False
+        # (ctn_updc1_fwd: 203 us per 64 utterances against 99 + 158 for ctn_resid_update + ctn_gemm1x1)
+        self.fuse_update = True
         # micro-batches in flight: with n > 1, consecutive micro-batches (independent utterances, separate
         # workspaces) are issued round-robin on n side streams, so one chain's HBM-bound kernels
         # (residual update, decoder) and kernel tails overlap the other chain's tensor-bound GEMMs

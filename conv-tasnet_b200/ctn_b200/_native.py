@@ -20,6 +20,9 @@ PRECISION = os.environ.get("CTN_PRECISION", "bf16x3")
 if PRECISION not in _FORMATS:
     raise RuntimeError("CTN_PRECISION=%r: expected one of %s" % (PRECISION, sorted(_FORMATS)))
 _LIB_PATH = os.path.join(os.path.dirname(_HERE), _FORMATS[PRECISION][0])
+if os.environ.get("CTN_ALLOW_EXPERIMENT_BUILD") == "1" and os.environ.get("CTN_LIB_FILE"):
+    # A/B runs of experiment builds (build_native.py with CTN_LIB_NAME / NVCC_FLAGS): never the product path
+    _LIB_PATH = os.path.join(os.path.dirname(_HERE), os.environ["CTN_LIB_FILE"])
 
 NORM_NONE, NORM_GLN, NORM_CLN = 0, 1, 2
 MASK_RELU, MASK_SOFTMAX = 0, 1

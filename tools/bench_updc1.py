@@ -18,8 +18,8 @@ torch.manual_seed(0)
 R = M * K
 NITER = int(os.environ.get("CTN_NITER", "20"))
 DBGS = [int(x) for x in os.environ.get("CTN_DBGS", "0").split(",")]
-x_hi = torch.randn(R, B, device=dev).to(torch.bfloat16)
-x_lo = (torch.randn(R, B, device=dev) * 1e-3).to(torch.bfloat16)
+x_hi = torch.randn(2 * R, B, device=dev).to(torch.bfloat16)
+x_lo = (torch.randn(2 * R, B, device=dev) * 1e-3).to(torch.bfloat16)
 y = torch.randn(R, B, device=dev) * 0.01
 g2, b2 = 1 + 0.3 * torch.randn(H, device=dev), torch.randn(H, device=dev)
 W2 = torch.randn(B, H, device=dev) * 0.05
@@ -67,3 +67,20 @@ g.a_hi, g.a_lo, g.w_hi, g.w_lo = x_hi.data_ptr(), x_lo.data_ptr(), w_hi.data_ptr
 g.out_f32, g.out_stat, g.out_stat_buf, g.stat_prelu, g.store_prelu = a.data_ptr(), nat.NORM_GLN, st1.data_ptr(), slope.data_ptr(), 1
 us_g = timeit(lambda: nat.check(lib.ctn_gemm1x1(C.byref(g), s)))
 print("unfused M=%d: update %7.1f + conv1x1 %7.1f = %7.1f us" % (M, us_u, us_g, us_u + us_g), flush=True)
+
+if os.environ.get("CTN_TRACE") == "1":
+    import numpy as np
+    for dbg in DBGS:
+        os.environ["CTN_C1_DBG"] = str(dbg)
+        nat.check(lib.ctn_updc1_fwd(C.byref(u), s))
+        torch.cuda.synchronize()
+        buf = np.zeros(64 * 32, dtype=np.int64)
+        lib.ctn_debug_trace_read.argtypes = [C.c_void_p, C.c_int]
+        lib.ctn_debug_trace_read(buf.ctypes.data, buf.size)
+        t = buf.reshape(64, 32)
+        t0 = t[0][t[0] > 0].min()
+        names = ["ld0", "ld1", "ld2", "ld3", "raw0", "raw1", "raw2", "raw3", "fix0", "fix1", "fix2", "fix3", "st0", "st1", "st2",
+                 "st3", "m0", "m1", "m2", "m3", "m4", "m5", "m6", "m7", "d0s", "d0e", "d1s", "d1e"]
+        print("trace dbg", dbg, "(cycles since the first event, CTA 0, row tiles 0-11)")
+        for it in range(12):
+            print(it, " ".join("%s=%d" % (n, (t[it][i] - t0) // 10 * 10) for i, n in enumerate(names) if t[it][i] > 0))

@@ -15,7 +15,7 @@ cfg = dict(N=256, L=20, B=256, H=512, P=3, X=8, R=4, C=2, norm_type="gLN", causa
 torch.manual_seed(0)
 model = conv_tasnet.ConvTasNet(**cfg).cuda().eval()
 model.engine().micro_batch = M
-model.engine().fuse_update = os.environ.get("CTN_FUSE_UPDATE", "0") == "1"
+model.engine().fuse_update = os.environ.get("CTN_FUSE_UPDATE", "1") == "1"
 mix = 0.1 * torch.randn(M, 32000, device="cuda")
 with torch.no_grad():
     for _ in range(passes):
