@@ -62,6 +62,11 @@ constexpr int kPartialsPerTile = kProdWarps;
 struct Params {
     int K, H, d, c0;                 // frames, channels, dilation, taps before the output frame
     int w, w_log2, jspan, n_ig, tiles_per_utt, row_tiles, items;
+    // the producers' index arithmetic runs once per unit on the critical path of a 3-warp-per-scheduler kernel:
+    // no integer division there (20-30 dependent instructions each) - powers of two by shift, the rest by
+    // multiplication with a rounded-up reciprocal (exact for the operand ranges asserted on the host)
+    int d_log2, n_ig_log2, nkb;
+    uint32_t tpu_magic, nkb_magic;
     int in_P, out_P;
     const float* a;
     const float* prelu_in;
@@ -74,12 +79,16 @@ struct Params {
     float2* out_stat;
 };
 
+// x / divisor for 0 <= x < 2^20 with magic = ceil(2^32 / divisor), 2 <= divisor <= 2^12; magic = 0 stands for divisor 1
+__device__ __forceinline__ int div_magic(int x, uint32_t magic) {
+    return magic == 0u ? x : static_cast<int>(__umulhi(static_cast<uint32_t>(x), magic));
+}
 // frame of tile row r of tile tt (may be >= K: the row does not exist)
 __device__ __forceinline__ int tile_phase(const Params& p, int tt, int s) {
-    return (tt % p.n_ig) * p.w + (s & (p.w - 1));
+    return (tt & (p.n_ig - 1)) * p.w + (s & (p.w - 1));
 }
 __device__ __forceinline__ int tile_j0(const Params& p, int tt, int s) {
-    return (tt / p.n_ig) * p.jspan + (s >> p.w_log2) * kRowsPerThread;
+    return (tt >> p.n_ig_log2) * p.jspan + (s >> p.w_log2) * kRowsPerThread;
 }
 
 // kPreact: the input is already PReLU(conv1x1 output) (ctn_gemm1x1 with store_prelu), prelu_in is unused
@@ -102,7 +111,7 @@ dwpw_kernel(const __grid_constant__ CUtensorMap tm_w_hi, const __grid_constant__
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
-    const int nkb = p.H / kBK;
+    const int nkb = p.nkb;
     // per-channel constants of the producers: gamma, beta and the three taps, [5][H]
     float2* tstat = reinterpret_cast<float2*>(smem + kTileBytes + kBarBytes + kStgBytes);   // [kMaxTiles] (mean, rstd)
     float* cst = reinterpret_cast<float*>(smem + kTileBytes + kBarBytes + kStgBytes + kMaxTiles * 8);
@@ -236,11 +245,12 @@ dwpw_kernel(const __grid_constant__ CUtensorMap tm_w_hi, const __grid_constant__
             Tile T;
             const int rt = 2 * item + static_cast<int>(rank);
             const bool ok = item < p.items && rt < p.row_tiles;
-            m = ok ? rt / p.tiles_per_utt : 0;
-            tt = ok ? rt % p.tiles_per_utt : -1;
+            const int mq = div_magic(rt, p.tpu_magic);
+            m = ok ? mq : 0;
+            tt = ok ? rt - mq * p.tiles_per_utt : -1;
             const int ph = tile_phase(p, max(tt, 0), s);
             const int j0 = tile_j0(p, max(tt, 0), s);
-            const int J = ph < p.K ? (p.K - ph + p.d - 1) / p.d : 0;   // frames of this phase
+            const int J = ph < p.K ? (p.K - ph + p.d - 1) >> p.d_log2 : 0;   // frames of this phase
             T.n = ok ? max(0, min(kRowsPerThread, J - j0)) : 0;
             const int r0 = j0 - p.c0;                                  // sequence index of window row t = 0
             T.lo = max(0, -r0);
@@ -269,7 +279,8 @@ dwpw_kernel(const __grid_constant__ CUtensorMap tm_w_hi, const __grid_constant__
             const uint32_t aphase = (d >> 1) & 1;
             const int rt = 2 * (worker + d * n_workers) + static_cast<int>(rank);
             const bool tile_ok = rt < p.row_tiles;
-            const int m = tile_ok ? rt / p.tiles_per_utt : 0, tt = tile_ok ? rt % p.tiles_per_utt : 0;
+            const int mq = div_magic(rt, p.tpu_magic);
+            const int m = tile_ok ? mq : 0, tt = tile_ok ? rt - mq * p.tiles_per_utt : 0;
             const int r = ew * 32 + lane;
             const int sr = r >> 4;
             const int frame = tile_phase(p, tt, sr) + p.d * (tile_j0(p, tt, sr) + (r & 15));
@@ -306,8 +317,9 @@ dwpw_kernel(const __grid_constant__ CUtensorMap tm_w_hi, const __grid_constant__
         auto zero_stats = [&](int it_lo, int it_hi) {
             for (int t = it_lo; t < it_hi; ++t) {
                 const int rt = 2 * (worker + t * n_workers) + static_cast<int>(rank);
+                const int mq = div_magic(rt, p.tpu_magic);
                 if (lane == 0 && rt < p.row_tiles)
-                    p.out_stat[static_cast<long long>(rt / p.tiles_per_utt) * p.out_P + (rt % p.tiles_per_utt) * kPartialsPerTile + pw] =
+                    p.out_stat[static_cast<long long>(mq) * p.out_P + (rt - mq * p.tiles_per_utt) * kPartialsPerTile + pw] =
                         make_float2(0.f, 0.f);
             }
         };
@@ -326,7 +338,7 @@ dwpw_kernel(const __grid_constant__ CUtensorMap tm_w_hi, const __grid_constant__
         // loads and fp64 math in front of every tile of every group.
         for (int t = pw; t < min(n_tiles, kMaxTiles); t += kProdWarps) {
             const int rt = 2 * (worker + t * n_workers) + static_cast<int>(rank);
-            const int mt = rt < p.row_tiles ? rt / p.tiles_per_utt : 0;
+            const int mt = rt < p.row_tiles ? div_magic(rt, p.tpu_magic) : 0;
             const float2 st = gln_finalize_warp(p.in_stat + static_cast<long long>(mt) * p.in_P, p.in_P,
                                                 static_cast<double>(p.K) * p.H);
             if (lane == 0) tstat[t] = st;
@@ -335,8 +347,9 @@ dwpw_kernel(const __grid_constant__ CUtensorMap tm_w_hi, const __grid_constant__
         float4 q[kRing];
         if (grp < n_units) {   // rows 0 .. 8 of the group's first unit
             int m0, tt0;
-            const Tile T0 = tile_setup(worker + (grp / nkb) * n_workers, m0, tt0);
-            const float* b0 = T0.base + (grp % nkb) * kBK;
+            const int it0 = div_magic(grp, p.nkb_magic);
+            const Tile T0 = tile_setup(worker + it0 * n_workers, m0, tt0);
+            const float* b0 = T0.base + (grp - it0 * nkb) * kBK;
 #pragma unroll
             for (int t = 0; t < kRing; ++t) {
                 q[t] = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -344,7 +357,7 @@ dwpw_kernel(const __grid_constant__ CUtensorMap tm_w_hi, const __grid_constant__
             }
         }
         for (int u = grp; u < n_units; u += 3) {
-            const int it = u / nkb, kb = u - it * nkb;
+            const int it = div_magic(u, p.nkb_magic), kb = u - it * nkb;
             if (it != cur_it) {
                 if (cur_it >= 0) flush_stats();
                 zero_stats(cur_it + 1, it);
@@ -365,7 +378,7 @@ dwpw_kernel(const __grid_constant__ CUtensorMap tm_w_hi, const __grid_constant__
             const uint32_t phase = static_cast<uint32_t>(u / nslots) & 1u;
             // the unit whose first rows replace this one's in the ring as they are consumed
             const int un = u + 3;
-            const int itn = un / nkb, kbn = un - itn * nkb;
+            const int itn = div_magic(un, p.nkb_magic), kbn = un - itn * nkb;
             Tile Tn = T;
             if (itn != it) {
                 int mn_, ttn;
@@ -597,6 +610,16 @@ extern "C" int ctn_dwpw_fwd(const ctn_dwpw_args* args, void* stream_) {
     p.w = g.w, p.w_log2 = g.w_log2, p.jspan = g.jspan, p.n_ig = g.n_ig, p.tiles_per_utt = g.tiles_per_utt;
     p.row_tiles = a.M * g.tiles_per_utt;
     p.items = ceil_div(p.row_tiles, 2);
+    p.nkb = a.H / fb::kBK;
+    p.d_log2 = p.n_ig_log2 = 0;
+    while ((1 << p.d_log2) < a.dilation) ++p.d_log2;
+    while ((1 << p.n_ig_log2) < g.n_ig) ++p.n_ig_log2;
+    p.tpu_magic = g.tiles_per_utt == 1 ? 0u : static_cast<uint32_t>(((1ull << 32) + g.tiles_per_utt - 1) / g.tiles_per_utt);
+    p.nkb_magic = p.nkb == 1 ? 0u : static_cast<uint32_t>(((1ull << 32) + p.nkb - 1) / p.nkb);
+    // div_magic is exact while x * (magic * divisor - 2^32) < 2^32; here divisors <= 2^12 and x < 2^20: row tile
+    // numbers, and unit numbers of one CTA (< row_tiles / sm_count * nkb, nkb <= 18 by the shared-memory bound on H)
+    CTN_REQUIRE(g.tiles_per_utt <= 4096 && p.nkb <= 64 && p.row_tiles + 2 * sm_count() < (1 << 20),
+                "ctn_dwpw_fwd: batch too large for the tile index arithmetic (M=%d K=%d)", a.M, a.K);
     p.in_P = a.in_P, p.out_P = g.tiles_per_utt * fb::kPartialsPerTile;
     p.a = a.a, p.prelu_in = a.prelu_in, p.gamma_in = a.gamma_in, p.beta_in = a.beta_in;
     p.in_stat = static_cast<const float2*>(a.in_stat);

@@ -90,6 +90,10 @@ __device__ __forceinline__ void cp_async_16(void* smem_dst, const void* gmem_src
 __device__ __forceinline__ void prefetch_l2_bulk(const void* gmem, uint32_t bytes) {
     asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(gmem), "r"(bytes) : "memory");
 }
+// one cache line -> L2, fire and forget: no register, no scoreboard (look-ahead beyond a register ring)
+__device__ __forceinline__ void prefetch_l2(const void* gmem) {
+    asm volatile("prefetch.global.L2 [%0];" ::"l"(gmem) : "memory");
+}
 __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
 
 __device__ __forceinline__ void tma_store_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
