@@ -50,7 +50,9 @@ constexpr int kASlotBytes = 2 * kABytes;
 constexpr int kWSlotBytes = 2 * kWBytes;
 constexpr int kTileBytes = kASlots * kASlotBytes + kWSlots * kWSlotBytes;
 constexpr int kProdWarps = 12;       // three groups of four warps; they also drain TMEM
-constexpr int kThreads = 64 + 32 * kProdWarps;
+constexpr int kCtrlWarps = 4;        // one warpgroup: 0 TMA, 1 MMA, 2-3 idle (they only hand their registers over)
+constexpr int kThreads = 32 * (kCtrlWarps + kProdWarps);
+constexpr int kCtrlRegs = 56, kProdRegs = 152;   // per scheduler partition: 1 control + 3 producer warps <= 512 x 32 registers
 constexpr int kBarBytes = 256;
 constexpr int kStgBytes = 0;
 constexpr int kMaxTiles = 32;        // row tiles per CTA whose gLN-1 (mean, rstd) are precomputed
@@ -151,6 +153,8 @@ dwpw_kernel(const __grid_constant__ CUtensorMap tm_w_hi, const __grid_constant__
     // conv1x1 GEMM, writes activations and statistics); wait for it before reading those
     ptx::grid_dep_sync();
 
+    if (warp < kCtrlWarps) {
+    ptx::setmaxnreg_dec<kCtrlRegs>();
     if (warp == 0) {
         // ------------------------------------------------ TMA producer (weights only)
         if (lane == 0) {
@@ -210,7 +214,9 @@ dwpw_kernel(const __grid_constant__ CUtensorMap tm_w_hi, const __grid_constant__
                 }
             }
         }
+    }
     } else {
+        ptx::setmaxnreg_inc<kProdRegs>();
         // ---------------------------------------------------- q producers (which also drain TMEM)
         // Three groups of four warps; the CTA's units (tile, k-block) are dealt round-robin, unit u to
         // group u % 3, which therefore always fills stage u % 3.  Thread (quad, s) of a group owns four
@@ -219,7 +225,7 @@ dwpw_kernel(const __grid_constant__ CUtensorMap tm_w_hi, const __grid_constant__
         // loads are in flight all the time.  Interior units (all 18 rows inside the utterance) take a
         // path without any predicate.  There are no epilogue warps: the four warps of group d % 3
         // (one per TMEM lane quarter) drain the accumulator of tile d between two of their units.
-        const int pw = warp - 2;                               // 0 .. 11
+        const int pw = warp - kCtrlWarps;                      // 0 .. 11
         const int grp = pw >> 2;
         const int pt = (pw & 3) * 32 + lane;                   // 0 .. 127 within the group
         const int quad = pt & 15, s = pt >> 4;

@@ -78,6 +78,7 @@ constexpr int kRows = kBM / (kProdWarps * 2);   // frames a fix-up thread handle
 
 struct Params {
     int K, Cout, n_tn, tiles_per_utt, row_tiles, items, groups;
+    uint32_t tpu_magic;      // ceil(2^32 / tiles_per_utt) (0: one tile per utterance): no integer division per unit
     const float* y;
     const float2* in_stat;   // gLN-2 partials of the previous block
     int in_P;
@@ -370,8 +371,9 @@ updc1_kernel(const __grid_constant__ CUtensorMap tm_w_hi, const __grid_constant_
             const int it = u >> 2, kb = u & 3;
             const int rt = 2 * (worker + it * n_workers) + static_cast<int>(rank);
             const bool ok = it < n_tiles && rt < p.row_tiles;
-            const int m = ok ? rt / p.tiles_per_utt : 0;
-            const int tk = ok ? rt % p.tiles_per_utt : 0;
+            const int mq = p.tpu_magic == 0u ? rt : static_cast<int>(__umulhi(static_cast<uint32_t>(rt), p.tpu_magic));
+            const int m = ok ? mq : 0;
+            const int tk = ok ? rt - mq * p.tiles_per_utt : 0;
             const int k0 = tk * kBM + s * kRows;
             g.nrows = ok ? max(0, min(kRows, p.K - k0)) : 0;
             g.oy = (static_cast<long long>(m) * p.K + k0) * kCin + kb * kBK + quad * 4;
@@ -505,6 +507,10 @@ extern "C" int ctn_updc1_fwd(const ctn_updc1_args* args, void* stream_) {
     p.tiles_per_utt = ceil_div(a.K, c1::kBM);
     p.row_tiles = a.M * p.tiles_per_utt;
     p.items = ceil_div(p.row_tiles, 2);
+    // exact for row tile numbers < 2^20 and at most 2^12 tiles per utterance (see fused_block.cu: div_magic)
+    CTN_REQUIRE(p.tiles_per_utt <= 4096 && p.row_tiles + 2 * sm_count() < (1 << 20),
+                "ctn_updc1_fwd: batch too large for the tile index arithmetic (M=%d K=%d)", a.M, a.K);
+    p.tpu_magic = p.tiles_per_utt == 1 ? 0u : static_cast<uint32_t>(((1ull << 32) + p.tiles_per_utt - 1) / p.tiles_per_utt);
     p.groups = ceil_div(a.H, CTN_COL_TILE);
     p.y = a.y, p.in_stat = static_cast<const float2*>(a.in_stat), p.in_P = a.in_P, p.in_count = a.in_count;
     p.col_g = a.col_g, p.col_bias = a.col_bias, p.out_stat = static_cast<float2*>(a.out_stat);

@@ -1,1 +1,2 @@
-timeout 600 python -m pytest tests/test_gpu_kernels.py tests/test_gpu_model.py -m gpu -x -q 2>&1 | tail -3
+timeout 600 python -m pytest tests/test_gpu_kernels.py -m gpu -x -q -k "fused_depthwise" 2>&1 | tail -2
+CTN_DILS=1,8,128 timeout 200 python tools/bench_fused.py 64 2>&1 | grep dwpw
