@@ -349,11 +349,26 @@ class _Plan:
                                 in_P=1 if self.bn else self.P2s[xb],
                                 in_count=float(K) * H, resid_hi=self.x_hl[0], resid_lo=self.x_hl[1],
                                 out_hi=self.x_hl[0], out_lo=self.x_hl[1]))
-        if pending is not None:
-            emit_update(pending)
-        calls.append(self._gemm(Cin=B, Cout=C_ * N, a_hi=self.x_hl[0], a_lo=self.x_hl[1], w_hi=prep.mask[0],
-                                w_lo=prep.mask[1], out_f32=self.score))
-        info.append(("gemm_mask", 2.0 * Rr * B * C_ * N, 4.0 * Rr * B + 4.0 * Rr * C_ * N))
+        if pending is not None and use_c1 and bool(lib.ctn_updc1_supported(B, C_ * N, self.norm)):
+            # the mask conv has the shape of a conv1x1 (B -> C N channels): the last block's deferred update rides in
+            # it as well (PReLU slope 1 = identity; its gLN statistics go to a scratch buffer nobody reads)
+            c = nat.Updc1Args()
+            c.M, c.K, c.B, c.H = M, K, B, C_ * N
+            c.x_hi, c.x_lo, c.y = self.x_hl[0].data_ptr(), self.x_hl[1].data_ptr(), self.y.data_ptr()
+            c.in_stat, c.in_P, c.in_count = pending["stat"].data_ptr(), pending["P"], float(K) * H
+            c.col_g, c.col_bias = pending["g"].data_ptr(), pending["b"].data_ptr()
+            c.w_hi, c.w_lo = prep.mask[0].data_ptr(), prep.mask[1].data_ptr()
+            self.stat_mask = torch.zeros(M, lib.ctn_gemm_gln_partials(K, C_ * N), 2, dtype=torch.float32, device=self.device)
+            c.a, c.out_stat, c.slope = self.score.data_ptr(), self.stat_mask.data_ptr(), self.one.data_ptr()
+            self._keep.append(c)
+            emit("gemm_update_mask", 2.0 * Rr * B * C_ * N + 2.0 * Rr * B, 12.0 * Rr * B + 4.0 * Rr * C_ * N,
+                 lambda s, ref=C.byref(c): uc1(ref, s))
+        else:
+            if pending is not None:
+                emit_update(pending)
+            calls.append(self._gemm(Cin=B, Cout=C_ * N, a_hi=self.x_hl[0], a_lo=self.x_hl[1], w_hi=prep.mask[0],
+                                    w_lo=prep.mask[1], out_f32=self.score))
+            info.append(("gemm_mask", 2.0 * Rr * B * C_ * N, 4.0 * Rr * B + 4.0 * Rr * C_ * N))
         info.append(("decoder", 2.0 * Rr * C_ * N * L, 4.0 * Rr * N * (C_ + 1) + 4.0 * M * C_ * T))
         dec = lib.ctn_decoder_fwd
         a = (self.score.data_ptr(), self.w.data_ptr(), V.data_ptr(), M, K, N, L, C_, T,
@@ -431,6 +446,9 @@ class SeparationEngine:
         the fused path also has 3 per block: conv1x1, depthwise+pointwise, residual update; with
         fuse_update the update rides in the next block's conv1x1: 2 per block + 1)."""
         n = self.cfg["R"] * self.cfg["X"]
+        plans = list(self.plans.values())
+        if plans and plans[-1].calls is not None:
+            return len(plans[-1].calls)
         return 4 + (2 * n + 1 if self.fuse_update and self.fuse_max_dilation >= 2 ** (self.cfg["X"] - 1) else 3 * n)
 
     def _plan(self, params, M, T, device, slot=0):
