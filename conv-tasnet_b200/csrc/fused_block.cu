@@ -294,16 +294,25 @@ dwpw_kernel(const __grid_constant__ CUtensorMap tm_w_hi, const __grid_constant__
             float* yrow = p.y + (static_cast<long long>(m) * p.K + frame) * kBN;
             ptx::mbar_wait(tfull_bar + as, aphase);
             ptx::tc_fence_after();
+            // 16-column pieces in two alternating register sets: the TMEM load of piece h + 1 is in flight while
+            // piece h is stored, and a set is reloaded only one piece after its stores were issued (the loads'
+            // write-after-read wait on the stores' operands was the drain's main stall)
+            const uint32_t tsrc = tmem_base + (static_cast<uint32_t>(ew * 32) << 16) + as * kBN;
+            uint32_t va[16], vb[16];
+            ptx::tmem_ld_32x16(tsrc, va);
 #pragma unroll 1
-            for (int ci = 0; ci < kBN / 32; ++ci) {
-                uint32_t v[32];
-                ptx::tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(ew * 32) << 16) + as * kBN + ci * 32, v);
+            for (int h = 0; h < kBN / 16; h += 2) {
                 ptx::tmem_ld_wait();
+                ptx::tmem_ld_32x16(tsrc + (h + 1) * 16, vb);
                 if (valid) {
-#pragma unroll
-                    for (int j = 0; j < 4; ++j)
-                        ptx::st_global_v8(yrow + ci * 32 + 8 * j, v[8 * j], v[8 * j + 1], v[8 * j + 2], v[8 * j + 3],
-                                          v[8 * j + 4], v[8 * j + 5], v[8 * j + 6], v[8 * j + 7]);
+                    ptx::st_global_v8(yrow + h * 16, va[0], va[1], va[2], va[3], va[4], va[5], va[6], va[7]);
+                    ptx::st_global_v8(yrow + h * 16 + 8, va[8], va[9], va[10], va[11], va[12], va[13], va[14], va[15]);
+                }
+                ptx::tmem_ld_wait();
+                if (h + 2 < kBN / 16) ptx::tmem_ld_32x16(tsrc + (h + 2) * 16, va);
+                if (valid) {
+                    ptx::st_global_v8(yrow + (h + 1) * 16, vb[0], vb[1], vb[2], vb[3], vb[4], vb[5], vb[6], vb[7]);
+                    ptx::st_global_v8(yrow + (h + 1) * 16 + 8, vb[8], vb[9], vb[10], vb[11], vb[12], vb[13], vb[14], vb[15]);
                 }
             }
             ptx::tc_fence_before();
