@@ -184,6 +184,7 @@ class _Prepared:
 
 class _Plan:
     """Static workspaces + call list for one (M, T) on one device."""
+    FUSE_UPDATE_MIN_ROWS = 8192     # frames (M * K) from which the update rides in the next conv1x1
 
     def __init__(self, cfg, M, T, device, fuse_max_dilation=0, fuse_update=False):
         self.cfg, self.M, self.T, self.device = cfg, M, T, device
@@ -285,7 +286,11 @@ class _Plan:
                  pend["P"], float(K) * H, pend["g"].data_ptr(), pend["b"].data_ptr(), M, K, B)
             emit("resid_update", 2.0 * Rr * B, 12.0 * Rr * B, lambda s, u=u: upd(*u, s))
 
-        use_c1 = self.fuse_update and self.norm == nat.NORM_GLN and bool(lib.ctn_updc1_supported(B, H, self.norm))
+        # (a row tile per CTA and both column tiles in sequence: below ~3 utterances of 4 s the grid of ctn_updc1_fwd
+        # is a fraction of the GPU and the two plain kernels are quicker: 1.14 against 1.26 ms at M = 1, 1.46 against
+        # 1.36 ms at M = 3, tools/exp_small_batch.py)
+        use_c1 = (self.fuse_update and self.norm == nat.NORM_GLN and bool(lib.ctn_updc1_supported(B, H, self.norm))
+                  and M * K >= self.FUSE_UPDATE_MIN_ROWS)
         pending = None    # deferred gLN-2 + residual of the previous (fused) block
         i = 0
         for r in range(cfg["R"]):

@@ -18,11 +18,12 @@ validate)
   tail -c 600 $O/${tag}_bench_n1.err; cut -c1-400 $O/${tag}_bench_n1.json
   ;;
 ncu)
-  # forward, one 64-utterance micro-batch, 2 passes of 100 launches (enc, bott, 32 x (conv1x1, dwpw, update), mask, dec)
+  # forward, one 64-utterance micro-batch, 2 passes of 67 launches (enc, bott, conv1x1, 31 x (dwpw, update+conv1x1), dwpw,
+  # update+mask, dec)
   timeout 300 python tools/profile_forward.py 64 2 > $O/${tag}_plain_fwd.log 2>&1 &&
-  ncu --metrics gpu__time_duration.sum --clock-control none -s 100 -c 100 --csv --log-file $O/${tag}_launches_fwd.csv \
+  ncu --metrics gpu__time_duration.sum --clock-control none -s 67 -c 67 --csv --log-file $O/${tag}_launches_fwd.csv \
       python tools/profile_forward.py 64 2 > $O/${tag}_ncu_fwd_list.log 2>&1
-  for k in dwpw_kernel:33:2 gemm_tc_kernel:36:2 resid_update:33:1 encoder_fwd:1:1 decoder_fwd:1:1; do
+  for k in dwpw_kernel:33:2 updc1_kernel:33:2 gemm_tc_kernel:2:2 encoder_fwd:1:1 decoder_fwd:1:1; do
     IFS=: read name skip cnt <<< "$k"
     ncu --set full --clock-control none --import-source on -k regex:$name -s $skip -c $cnt -o $O/${tag}_prof_fwd_$name -f \
         python tools/profile_forward.py 64 2 > $O/${tag}_ncu_fwd_$name.log 2>&1
