@@ -619,7 +619,7 @@ def main():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--micro-batch", type=int, default=64)
+    ap.add_argument("--micro-batch", type=int, default=128)
     ap.add_argument("--fuse", type=int, default=1 << 30,
                     help="blocks with dilation <= this use the fused depthwise+pointwise kernel (0 = off)")
     ap.add_argument("--fuse-update", type=int, default=1,

@@ -28,7 +28,10 @@ constexpr int kBmAhead = 4;   // rows loaded ahead of use
 // 148 SMs, i.e. two rounds (51 us per launch for 25 us of work).  Small CTAs fill the 1776 warp slots
 // evenly: backward 6.0 -> 5.2 ms at batch 3, 18.6 -> 16.5 ms at batch 16.
 constexpr int kBmWarps = 4;
-constexpr int kBmCtasPerSm = 3;
+#ifndef CTN_BM_CTAS
+#define CTN_BM_CTAS 3
+#endif
+constexpr int kBmCtasPerSm = CTN_BM_CTAS;
 
 struct BwdMarchParams {
     int K, H, dil, c0, P1, P2, Pb, NS, units, groups, chan_rows, ctas, upw;

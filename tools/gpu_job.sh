@@ -1,7 +1,7 @@
 #!/bin/bash
 # The GPU-side jobs of a round, one entry point:  gpurun --timeout S -- 'bash tools/gpu_job.sh <job> [tag]'
 #   validate   pytest -m gpu, smoke, both bench arms (no profiler)
-#   ncu        validate-lite (plain runs) && launch lists + --set full captures of the hot kernels (forward mb64, train batch 3)
+#   ncu        validate-lite (plain runs) && launch lists + --set full captures of the hot kernels (forward mb128, train batch 3)
 #   sanitize   compute-sanitizer memcheck over the small-fixture GPU tests (racecheck: job "racecheck")
 #   multi      the 2-GPU NCCL tests + 2-rank bench (needs gpurun --gpus 2)
 # Everything is written under gpurun_out/<tag>_*; summaries are made HERE afterwards (tools/ncu_summary.py ...).
@@ -18,15 +18,15 @@ validate)
   tail -c 600 $O/${tag}_bench_n1.err; cut -c1-400 $O/${tag}_bench_n1.json
   ;;
 ncu)
-  # forward, one 64-utterance micro-batch, 2 passes of 67 launches (enc, bott, conv1x1, 31 x (dwpw, update+conv1x1), dwpw,
+  # forward, one 128-utterance micro-batch, 2 passes of 67 launches (enc, bott, conv1x1, 31 x (dwpw, update+conv1x1), dwpw,
   # update+mask, dec)
-  timeout 300 python tools/profile_forward.py 64 2 > $O/${tag}_plain_fwd.log 2>&1 &&
+  timeout 300 python tools/profile_forward.py 128 2 > $O/${tag}_plain_fwd.log 2>&1 &&
   ncu --metrics gpu__time_duration.sum --clock-control none -s 67 -c 67 --csv --log-file $O/${tag}_launches_fwd.csv \
-      python tools/profile_forward.py 64 2 > $O/${tag}_ncu_fwd_list.log 2>&1
+      python tools/profile_forward.py 128 2 > $O/${tag}_ncu_fwd_list.log 2>&1
   for k in dwpw_kernel:33:2 updc1_kernel:33:2 gemm_tc_kernel:2:2 encoder_fwd:1:1 decoder_fwd:1:1; do
     IFS=: read name skip cnt <<< "$k"
     ncu --set full --clock-control none --import-source on -k regex:$name -s $skip -c $cnt -o $O/${tag}_prof_fwd_$name -f \
-        python tools/profile_forward.py 64 2 > $O/${tag}_ncu_fwd_$name.log 2>&1
+        python tools/profile_forward.py 128 2 > $O/${tag}_ncu_fwd_$name.log 2>&1
   done
   # training, batch 3 (BASELINE configs[1]), 2 steps; the second step's launches
   timeout 300 python tools/profile_train_once.py 3 2 > $O/${tag}_plain_train.log 2>&1 &&
