@@ -168,10 +168,11 @@ updc1_kernel(const __grid_constant__ CUtensorMap tm_w_hi, const __grid_constant_
                     const int tn = step / kKB, kb = step % kKB;
                     ptx::mbar_wait(wempty_bar + slot, phase ^ 1);
                     uint8_t* st = wsm + slot * kWSlotBytes;
-                    if (rank == 0) ptx::mbar_expect_tx(wfull_bar + slot, 4 * kWBytes);
+                    // (the lo tiles are read by the correction MMAs only: not loaded by one-MMA builds)
+                    if (rank == 0) ptx::mbar_expect_tx(wfull_bar + slot, (CTN_MMA_TERMS == 3 ? 4 : 2) * kWBytes);
                     const int n0 = tn * kBN + static_cast<int>(rank) * (kBN / 2);
                     ptx::tma_load_2d_pair(st, &tm_w_hi, fb0 + slot * 8, kb * kBK, n0);
-                    ptx::tma_load_2d_pair(st + kWBytes, &tm_w_lo, fb0 + slot * 8, kb * kBK, n0);
+                    if (CTN_MMA_TERMS == 3) ptx::tma_load_2d_pair(st + kWBytes, &tm_w_lo, fb0 + slot * 8, kb * kBK, n0);
                     if (++slot == kWSlots) slot = 0, phase ^= 1;
                 }
             }
@@ -206,8 +207,10 @@ updc1_kernel(const __grid_constant__ CUtensorMap tm_w_hi, const __grid_constant_
                     for (int k = 0; k < ((p.dbg & 4) ? 0 : kBK / 16); ++k) {
                         const uint64_t adv = static_cast<uint64_t>((k * 16 * 2) >> 4);
                         ptx::umma_bf16_pair(d_tmem, a_hi + adv, w_hi + adv, idesc, (kb | k) != 0);
-                        ptx::umma_bf16_pair(d_tmem, a_lo + adv, w_hi + adv, idesc, 1);
-                        ptx::umma_bf16_pair(d_tmem, a_hi + adv, w_lo + adv, idesc, 1);
+                        if (CTN_MMA_TERMS == 3) {
+                            ptx::umma_bf16_pair(d_tmem, a_lo + adv, w_hi + adv, idesc, 1);
+                            ptx::umma_bf16_pair(d_tmem, a_hi + adv, w_lo + adv, idesc, 1);
+                        }
                     }
                     C1_TRACE(it, 16 + step);
                     ptx::umma_commit_pair(wempty_bar + wslot, 3);
