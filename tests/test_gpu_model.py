@@ -181,6 +181,28 @@ def test_fused_depthwise_pointwise_path_matches_unfused(fuse):
     assert rel_l2(fused[:1], ref) < WAVE_TOL / 10
 
 
+def test_deferred_update_path_is_chosen_by_batch_size():
+    """From 8192 frames up the deferred gLN-2 + residual of a fused block rides in the next conv1x1 and, after the
+    last block, in the mask conv (ctn_updc1_fwd: two kernels per block); smaller batches keep ctn_resid_update (its
+    grid would be a fraction of the GPU).  Both call lists give the same waveforms to rounding."""
+    cfg, _, T = CONFIGS["cfg1_paper_gln"]
+    p32 = O.random_params(*(cfg[k] for k in "NLBHPXRC"), cfg["causal"], seed=5)
+    model = _build(cfg, p32)
+    eng = model.engine()
+    nb = cfg["R"] * cfg["X"]
+    g = torch.Generator().manual_seed(6)
+    mix = (0.1 * torch.randn(3, T, generator=g)).to(DEV)
+    with torch.no_grad():
+        big = model(mix)
+        kinds3 = [k for k, _, _ in eng._plan(model._params(), 3, T, mix.device).call_info]
+        small = model(mix[:1])
+        kinds1 = [k for k, _, _ in eng._plan(model._params(), 1, T, mix.device).call_info]
+    assert kinds3.count("gemm_update_conv1x1") == nb - 1 and kinds3.count("gemm_update_mask") == 1
+    assert "resid_update" not in kinds3 and len(kinds3) == 2 * nb + 4
+    assert kinds1.count("resid_update") == nb and "gemm_update_conv1x1" not in kinds1 and len(kinds1) == 3 * nb + 4
+    assert rel_l2(big[:1], small) < 2e-5
+
+
 def test_utterances_inside_a_64_utterance_fused_micro_batch_match_the_oracle():
     """BASELINE configs[3] runs 64-utterance micro-batches through the fused depthwise + pointwise kernel, whose
     CTA pairs then own several tiles each and group the statistics' partial sums differently from a lone

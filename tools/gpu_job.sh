@@ -18,10 +18,10 @@ validate)
   tail -c 600 $O/${tag}_bench_n1.err; cut -c1-400 $O/${tag}_bench_n1.json
   ;;
 ncu)
-  # forward, one 128-utterance micro-batch, 2 passes of 67 launches (enc, bott, conv1x1, 31 x (dwpw, update+conv1x1), dwpw,
+  # forward, one 128-utterance micro-batch, 2 passes of 68 launches (enc, bott, conv1x1, 31 x (dwpw, update+conv1x1), dwpw,
   # update+mask, dec)
   timeout 300 python tools/profile_forward.py 128 2 > $O/${tag}_plain_fwd.log 2>&1 &&
-  ncu --metrics gpu__time_duration.sum --clock-control none -s 67 -c 67 --csv --log-file $O/${tag}_launches_fwd.csv \
+  ncu --metrics gpu__time_duration.sum --clock-control none -s 68 -c 68 --csv --log-file $O/${tag}_launches_fwd.csv \
       python tools/profile_forward.py 128 2 > $O/${tag}_ncu_fwd_list.log 2>&1
   for k in dwpw_kernel:33:2 updc1_kernel:33:2 gemm_tc_kernel:2:2 encoder_fwd:1:1 decoder_fwd:1:1; do
     IFS=: read name skip cnt <<< "$k"
