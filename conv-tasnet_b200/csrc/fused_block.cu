@@ -79,6 +79,7 @@ struct Params {
     const float* prelu_out;
     float* y;
     float2* out_stat;
+    float* d_out;   // training: depthwise output before the second PReLU (kStoreD instantiations)
 };
 
 // x / divisor for 0 <= x < 2^20 with magic = ceil(2^32 / divisor), 2 <= divisor <= 2^12; magic = 0 stands for divisor 1
@@ -94,7 +95,8 @@ __device__ __forceinline__ int tile_j0(const Params& p, int tt, int s) {
 }
 
 // kPreact: the input is already PReLU(conv1x1 output) (ctn_gemm1x1 with store_prelu), prelu_in is unused
-template <bool kPreact>
+// kStoreD: the depthwise output before the second PReLU is also written to d_out (the training forward)
+template <bool kPreact, bool kStoreD = false>
 __global__ void __launch_bounds__(kThreads, 1)
 dwpw_kernel(const __grid_constant__ CUtensorMap tm_w_hi, const __grid_constant__ CUtensorMap tm_w_lo, const Params p) {
     const uint32_t rank = ptx::cluster_ctarank();
@@ -434,6 +436,7 @@ dwpw_kernel(const __grid_constant__ CUtensorMap tm_w_hi, const __grid_constant__
             ptx::mbar_wait(aempty_bar + aslot, phase ^ 1);
             const uint32_t hi_base = ptx::smem_u32(smem + aslot * kASlotBytes) + row_off0;
 
+            float* dptr = kStoreD ? p.d_out + (T.base - p.a) + kb * kBK : nullptr;
             auto unit = [&](auto fast_tag) {
                 constexpr bool kFast = decltype(fast_tag)::value;
                 // row t -> pv = PReLU(v) (interior) or n1 = A pv + B, zero outside the utterance
@@ -470,12 +473,14 @@ dwpw_kernel(const __grid_constant__ CUtensorMap tm_w_hi, const __grid_constant__
                 for (int o = 0; o < kRowsPerThread; ++o) {
                     xform(o + 2, x2);
                     uint32_t h[2], l[2];
+                    float dv[4];
 #pragma unroll
                     for (int i = 0; i < 2; ++i) {
                         const f2_t acc = kFast ? f2_fma(w2[i], x2[i], f2_fma(w1[i], x1[i], f2_fma(w0[i], x0[i], Bc[i])))
                                                : f2_fma(w2[i], x2[i], f2_fma(w1[i], x1[i], f2_mul(w0[i], x0[i])));
                         float c0, c1;
                         f2_unpack(acc, c0, c1);
+                        if (kStoreD) dv[2 * i] = c0, dv[2 * i + 1] = c1;
                         f2_t qq = f2_fma(a2m1, f2_pack(fminf(c0, 0.f), fminf(c1, 0.f)), acc);   // PReLU
                         if (!kFast && o >= T.n) qq = 0ull;
                         ls[i] = f2_add(ls[i], qq);
@@ -483,6 +488,8 @@ dwpw_kernel(const __grid_constant__ CUtensorMap tm_w_hi, const __grid_constant__
                         f2_split_bf16(qq, neg1, h[i], l[i]);
                         x0[i] = x1[i], x1[i] = x2[i];
                     }
+                    if (kStoreD && (kFast || o < T.n))   // output o = sequence row c0 + o of the window that starts at T.base
+                        *reinterpret_cast<float4*>(dptr + (p.c0 + o) * strd) = make_float4(dv[0], dv[1], dv[2], dv[3]);
                     // row 16 s + o of the tile: 128 B rows, the 16 B chunk index XOR (row & 7) = XOR (o & 7).
                     // hi_base is 1024-aligned, so the XOR can be applied to the whole address.
                     const uint32_t ad = ((hi_base + cs) ^ (static_cast<uint32_t>(o & 7) << 4)) + static_cast<uint32_t>(o) * 128u;
@@ -644,13 +651,16 @@ extern "C" int ctn_dwpw_fwd(const ctn_dwpw_args* args, void* stream_) {
     if ((rc = make_tmap_bf16_kmajor(&tw_hi, a.w_hi, a.B, a.H, fb::kBN / 2)) != CTN_OK) return rc;
     if ((rc = make_tmap_bf16_kmajor(&tw_lo, a.w_lo, a.B, a.H, fb::kBN / 2)) != CTN_OK) return rc;
     const bool preact = a.prelu_in == nullptr;
-    auto kern = preact ? fb::dwpw_kernel<true> : fb::dwpw_kernel<false>;
-    static bool attr_done[kMaxDevices][2] = {};
-    bool* attr_set = attr_done[device_slot()];
-    if (!attr_set[preact]) {
+    p.d_out = a.d_out;
+    CTN_REQUIRE(a.d_out == nullptr || (!preact && aligned16(a.d_out)),
+                "ctn_dwpw_fwd: d_out (training) goes with prelu_in and must be 16-byte aligned");
+    auto kern = a.d_out ? fb::dwpw_kernel<false, true> : preact ? fb::dwpw_kernel<true> : fb::dwpw_kernel<false>;
+    static bool attr_done[kMaxDevices][3] = {};
+    bool* attr_set = attr_done[device_slot()] + (a.d_out ? 2 : 0);
+    if (!attr_set[a.d_out ? 0 : preact]) {
         cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, fb::kSmemMax);
         if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(dwpw_kernel)");
-        attr_set[preact] = true;
+        attr_set[a.d_out ? 0 : preact] = true;
     }
     const int workers_max = sm_count() / 2;
     const int workers = p.items < workers_max ? p.items : workers_max;

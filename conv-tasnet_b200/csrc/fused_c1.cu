@@ -88,6 +88,7 @@ struct Params {
     float2* out_stat;        // out: gLN-1 partials, ctn_gemm1x1 layout
     int out_P;
     const float* slope;
+    int store_raw;           // `a` leaves before the PReLU (training); the statistics are those of PReLU(a)
     int dbg;   // CTN_C1_DBG experiment bits (0 in production): 1 no `a` stores, 2 no x stores, 4 no MMAs, 8 no y loads
 };
 
@@ -100,7 +101,8 @@ struct Params {
 __global__ void __launch_bounds__(kThreads, 1)
 updc1_kernel(const __grid_constant__ CUtensorMap tm_w_hi, const __grid_constant__ CUtensorMap tm_w_lo,
              const __grid_constant__ CUtensorMap tm_a, const __grid_constant__ CUtensorMap tm_x_hi,
-             const __grid_constant__ CUtensorMap tm_x_lo, const Params p) {
+             const __grid_constant__ CUtensorMap tm_x_lo, const __grid_constant__ CUtensorMap tm_xo_hi,
+             const __grid_constant__ CUtensorMap tm_xo_lo, const Params p) {
     const uint32_t rank = ptx::cluster_ctarank();
     const int worker = static_cast<int>(blockIdx.x >> 1);
     const int n_workers = static_cast<int>(gridDim.x >> 1);
@@ -132,6 +134,8 @@ updc1_kernel(const __grid_constant__ CUtensorMap tm_w_hi, const __grid_constant_
         ptx::prefetch_tmap(&tm_a);
         ptx::prefetch_tmap(&tm_x_hi);
         ptx::prefetch_tmap(&tm_x_lo);
+        ptx::prefetch_tmap(&tm_xo_hi);
+        ptx::prefetch_tmap(&tm_xo_lo);
         for (int i = 0; i < kKB; ++i) {
             ptx::mbar_init(afull_bar + i, 2 * kProdWarps);   // one arrival per fix-up warp, both CTAs
             ptx::mbar_init(aempty_bar + i, 2);               // MMA commit + x store
@@ -254,8 +258,8 @@ updc1_kernel(const __grid_constant__ CUtensorMap tm_w_hi, const __grid_constant_
                     ptx::mbar_wait(xdone_bar + kb, ph);
                     if (tile_ok && !(p.dbg & 2)) {
                         const uint32_t sl = ptx::smem_u32(smem + kb * kASlotBytes);
-                        ptx::tma_store_3d_addr(&tm_x_hi, sl, kb * kBK, tk * kBM, m);
-                        ptx::tma_store_3d_addr(&tm_x_lo, sl + kABytes, kb * kBK, tk * kBM, m);
+                        ptx::tma_store_3d_addr(&tm_xo_hi, sl, kb * kBK, tk * kBM, m);
+                        ptx::tma_store_3d_addr(&tm_xo_lo, sl + kABytes, kb * kBK, tk * kBM, m);
                         ptx::tma_store_commit();
                     }
                     C1_TRACE(it, 12 + kb);
@@ -304,6 +308,7 @@ updc1_kernel(const __grid_constant__ CUtensorMap tm_w_hi, const __grid_constant_
                     const float t = __uint_as_float(r[j]);
                     v[j] = fmaf(slope, fminf(t, 0.f), fmaxf(t, 0.f));   // PReLU
                 }
+                const bool raw = p.store_raw != 0;
                 if (valid) {
                     float l0 = 0.f, l1 = 0.f, q0 = 0.f, q1 = 0.f;
 #pragma unroll
@@ -319,8 +324,9 @@ updc1_kernel(const __grid_constant__ CUtensorMap tm_w_hi, const __grid_constant_
 #pragma unroll
                 for (int j = 0; j < 8; ++j)
                     ptx::st_shared_v4(sb + ((static_cast<uint32_t>(j) ^ (static_cast<uint32_t>(lane) & 7u)) << 4),
-                                      __float_as_uint(v[4 * j]), __float_as_uint(v[4 * j + 1]), __float_as_uint(v[4 * j + 2]),
-                                      __float_as_uint(v[4 * j + 3]));
+                                      raw ? r[4 * j] : __float_as_uint(v[4 * j]), raw ? r[4 * j + 1] : __float_as_uint(v[4 * j + 1]),
+                                      raw ? r[4 * j + 2] : __float_as_uint(v[4 * j + 2]),
+                                      raw ? r[4 * j + 3] : __float_as_uint(v[4 * j + 3]));
                 ptx::fence_async_smem();
                 __syncwarp();
                 if (lane == 0 && rows_ok && !(p.dbg & 1)) {   // frames past K are clipped by the map
@@ -519,6 +525,7 @@ extern "C" int ctn_updc1_fwd(const ctn_updc1_args* args, void* stream_) {
     p.col_g = a.col_g, p.col_bias = a.col_bias, p.out_stat = static_cast<float2*>(a.out_stat);
     p.out_P = ctn_gemm_gln_partials(a.K, a.H);
     p.slope = a.slope;
+    p.store_raw = a.store_raw;
     {
         const char* d = getenv("CTN_C1_DBG");
         p.dbg = d ? atoi(d) : 0;
@@ -532,6 +539,13 @@ extern "C" int ctn_updc1_fwd(const ctn_updc1_args* args, void* stream_) {
     CUtensorMap tx_hi, tx_lo;   // [M, K, B] bf16, box 64 channels x 128 frames of one utterance, 128B swizzle (in and out)
     if ((rc = make_tmap_bf16_3d(&tx_hi, a.x_hi, a.M, a.K, a.B, c1::kBM)) != CTN_OK) return rc;
     if ((rc = make_tmap_bf16_3d(&tx_lo, a.x_lo, a.M, a.K, a.B, c1::kBM)) != CTN_OK) return rc;
+    CTN_REQUIRE((a.x_out_hi == nullptr) == (a.x_out_lo == nullptr), "ctn_updc1_fwd: x_out_hi / x_out_lo go together");
+    CUtensorMap txo_hi = tx_hi, txo_lo = tx_lo;   // in place unless an output pair is given
+    if (a.x_out_hi != nullptr) {
+        CTN_REQUIRE(aligned(a.x_out_hi, 16) && aligned(a.x_out_lo, 16), "ctn_updc1_fwd: x_out must be 16-byte aligned");
+        if ((rc = make_tmap_bf16_3d(&txo_hi, a.x_out_hi, a.M, a.K, a.B, c1::kBM)) != CTN_OK) return rc;
+        if ((rc = make_tmap_bf16_3d(&txo_lo, a.x_out_lo, a.M, a.K, a.B, c1::kBM)) != CTN_OK) return rc;
+    }
 
     static bool attr_done[kMaxDevices] = {};
     bool& attr_set = attr_done[device_slot()];
@@ -554,7 +568,7 @@ extern "C" int ctn_updc1_fwd(const ctn_updc1_args* args, void* stream_) {
     attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
-    cudaError_t e = cudaLaunchKernelEx(&cfg, c1::updc1_kernel, tw_hi, tw_lo, ta, tx_hi, tx_lo, p);
+    cudaError_t e = cudaLaunchKernelEx(&cfg, c1::updc1_kernel, tw_hi, tw_lo, ta, tx_hi, tx_lo, txo_hi, txo_lo, p);
     if (e != cudaSuccess) return cuda_fail(e, "cudaLaunchKernelEx(updc1_kernel)");
     return CTN_OK;
 }

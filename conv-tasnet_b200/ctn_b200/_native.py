@@ -63,7 +63,7 @@ class DwpwArgs(C.Structure):
     _fields_ = [
         ("M", C.c_int), ("K", C.c_int), ("H", C.c_int), ("B", C.c_int), ("dilation", C.c_int), ("causal", C.c_int),
         ("a", _vp), ("prelu_in", _vp), ("gamma_in", _vp), ("beta_in", _vp), ("in_stat", _vp), ("in_P", C.c_int),
-        ("wd", _vp), ("prelu_out", _vp), ("w_hi", _vp), ("w_lo", _vp), ("y", _vp), ("out_stat", _vp),
+        ("wd", _vp), ("prelu_out", _vp), ("w_hi", _vp), ("w_lo", _vp), ("y", _vp), ("out_stat", _vp), ("d_out", _vp),
     ]
 
 
@@ -73,6 +73,7 @@ class Updc1Args(C.Structure):
         ("M", C.c_int), ("K", C.c_int), ("B", C.c_int), ("H", C.c_int),
         ("x_hi", _vp), ("x_lo", _vp), ("y", _vp), ("in_stat", _vp), ("in_P", C.c_int), ("in_count", C.c_double),
         ("col_g", _vp), ("col_bias", _vp), ("w_hi", _vp), ("w_lo", _vp), ("a", _vp), ("out_stat", _vp), ("slope", _vp),
+        ("x_out_hi", _vp), ("x_out_lo", _vp), ("store_raw", C.c_int),
     ]
 
 

@@ -176,6 +176,8 @@ typedef struct ctn_dwpw_args {
     const void *w_hi, *w_lo;/* pointwise weight with gamma-2 folded (ctn_weight_prep), [B, H]  */
     float* y;               /* out: (W2 diag gamma2) q, fp32 [M*K, B]: NOT yet normalised      */
     void* out_stat;         /* out: float2 [M, ctn_dwpw_partials(K, dilation)] partials of q   */
+    float* d_out;           /* out (training, NULL otherwise): the depthwise output BEFORE the
+                               second PReLU, fp32 [M*K, H], which autograd saves for :253-254   */
 } ctn_dwpw_args;
 
 /* Inference fast path of one TemporalBlock's middle: first PReLU + gLN-1 + depthwise conv +
@@ -356,6 +358,10 @@ typedef struct ctn_updc1_args {
     float* a;                /* out: PReLU(W1 x), fp32 [M*K, H]                                       */
     void* out_stat;          /* out: float2 [M, ctn_gemm_gln_partials(K, H)] gLN-1 partials of a      */
     const float* slope;      /* slope of this block's first PReLU (device scalar)                     */
+    void *x_out_hi, *x_out_lo; /* training (NULL: in place): the updated residual stream goes HERE, the input
+                                  pair stays intact (autograd saves every block's input for dW1)       */
+    int store_raw;           /* training: `a` = W1 x BEFORE the PReLU (its backward needs the sign and
+                                the value); the statistics are those of PReLU(a) either way            */
 } ctn_updc1_args;
 
 /* ctn_resid_update of block b-1 fused into the conv1x1 of block b (conv_tasnet.py:254-256, :237 then

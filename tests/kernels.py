@@ -93,8 +93,9 @@ def dwconv(M, K, a, a1, g1, b1, norm, in_stat, in_P, wd, a2, dilation, causal, w
     return pre, hi, lo, st
 
 
-def dwpw(M, K, a, a1, g1, b1, in_stat, in_P, wd, a2, w_hi, w_lo, dilation, causal):
-    """ctn_dwpw_fwd: returns (y [M*K, B] raw product, gLN-2 partials [M, P, 2])"""
+def dwpw(M, K, a, a1, g1, b1, in_stat, in_P, wd, a2, w_hi, w_lo, dilation, causal, want_d=False):
+    """ctn_dwpw_fwd: returns (y [M*K, B] raw product, gLN-2 partials [M, P, 2]) (+ the depthwise output before the
+    second PReLU with want_d, the training forward's extra output)"""
     R, H = a.shape
     B = w_hi.shape[0]
     dev = a.device
@@ -107,8 +108,10 @@ def dwpw(M, K, a, a1, g1, b1, in_stat, in_P, wd, a2, w_hi, w_lo, dilation, causa
     y = torch.full((R, B), float("nan"), device=dev)
     st = torch.full((M, lib.ctn_dwpw_partials(K, dilation), 2), float("nan"), device=dev)
     d.y, d.out_stat = y.data_ptr(), st.data_ptr()
+    dout = torch.full((R, H), float("nan"), device=dev) if want_d else None
+    d.d_out = nat.ptr(dout)
     nat.check(lib.ctn_dwpw_fwd(C.byref(d), nat.stream()))
-    return y, st
+    return (y, st, dout) if want_d else (y, st)
 
 
 def resid_update(x_hi, x_lo, y, stat, count, col_g, col_bias, M, K):
@@ -117,8 +120,9 @@ def resid_update(x_hi, x_lo, y, stat, count, col_g, col_bias, M, K):
                                          float(count), col_g.data_ptr(), col_bias.data_ptr(), M, K, B, nat.stream()))
 
 
-def updc1(M, K, x_hi, x_lo, y, stat, count, col_g, col_bias, w_hi, w_lo, slope):
-    """ctn_updc1_fwd: updates (x_hi, x_lo) in place; returns (a [M*K, H], gLN-1 partials)"""
+def updc1(M, K, x_hi, x_lo, y, stat, count, col_g, col_bias, w_hi, w_lo, slope, x_out=None, store_raw=False):
+    """ctn_updc1_fwd: updates (x_hi, x_lo) in place (or writes the pair x_out, leaving the input intact); returns
+    (a [M*K, H] = PReLU(W1 x), or W1 x with store_raw, gLN-1 partials)"""
     B = y.shape[1]
     H = w_hi.shape[0]
     lib = nat.lib()
@@ -130,6 +134,9 @@ def updc1(M, K, x_hi, x_lo, y, stat, count, col_g, col_bias, w_hi, w_lo, slope):
     a = torch.full((M * K, H), float("nan"), device=y.device)
     st = torch.full((M, lib.ctn_gemm_gln_partials(K, H), 2), float("nan"), device=y.device)
     u.a, u.out_stat, u.slope = a.data_ptr(), st.data_ptr(), slope.data_ptr()
+    if x_out is not None:
+        u.x_out_hi, u.x_out_lo = x_out[0].data_ptr(), x_out[1].data_ptr()
+    u.store_raw = int(store_raw)
     nat.check(lib.ctn_updc1_fwd(C.byref(u), nat.stream()))
     return a, st
 

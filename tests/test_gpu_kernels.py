@@ -288,6 +288,57 @@ def test_fused_update_conv1x1(K, M, H):
     assert rel_l2(a, a_ref) < 2e-5
 
 
+@pytest.mark.parametrize("K,M,H", [(700, 2, 512), (3199, 3, 512), (129, 4, 256)])
+def test_fused_update_conv1x1_training_outputs(K, M, H):
+    """The training forward's variant of ctn_updc1_fwd: the updated residual stream goes to a second pair (the input
+    pair, which autograd saves for dW1, stays intact) and `a` leaves BEFORE the PReLU; statistics as before."""
+    B = 256
+    x = _rand(M * K, B, seed=70)
+    y = _rand(M * K, B, seed=71, scale=0.7)
+    g2, b2 = 1.0 + 0.3 * _rand(512, seed=72), _rand(512, seed=73)
+    _, _, col_g, col_bias = Kn.weight_prep(_rand(B, 512, seed=74, scale=0.05), g2, b2)
+    stat = torch.rand(M, 7, 2, device=DEV) * 100 + 50
+    count = float(K) * 512
+    stat[:, :, 1] = stat[:, :, 0] ** 2 / (count / 7) * 3.0 + 10.0
+    w_hi, w_lo, _, _ = Kn.weight_prep(_rand(H, B, seed=75, scale=0.06))
+    slope = torch.tensor([0.25], device=DEV)
+    x_hi, x_lo = Kn.split_hl(x)
+    r_hi, r_lo = x_hi.clone(), x_lo.clone()
+    a_ref, st_ref = Kn.updc1(M, K, r_hi, r_lo, y, stat, count, col_g, col_bias, w_hi, w_lo, slope)     # in place, PReLU'd
+    o_hi = torch.full_like(x_hi, float("nan"))
+    o_lo = torch.full_like(x_lo, float("nan"))
+    keep_hi, keep_lo = x_hi.clone(), x_lo.clone()
+    a_raw, st = Kn.updc1(M, K, x_hi, x_lo, y, stat, count, col_g, col_bias, w_hi, w_lo, slope, x_out=(o_hi, o_lo),
+                         store_raw=True)
+    assert torch.equal(x_hi, keep_hi) and torch.equal(x_lo, keep_lo)       # the input pair is untouched
+    assert torch.equal(o_hi, r_hi) and torch.equal(o_lo, r_lo)             # same update, other destination
+    assert torch.equal(F.prelu(a_raw, slope), a_ref)                       # same product, PReLU not applied
+    assert (a_raw < 0).any()
+    assert torch.equal(st, st_ref)
+
+
+@pytest.mark.parametrize("dil,causal", [(1, False), (8, True), (128, False)])
+def test_fused_depthwise_pointwise_saves_the_depthwise_output(dil, causal):
+    """d_out of ctn_dwpw_fwd (training) = the depthwise output before the second PReLU, as ctn_dwconv_fwd's out_pre."""
+    H, K, M, B, P = 512, 700, 3, 256, 3
+    a = Kn.to_rows(_rand(M, H, K, seed=80))
+    a1 = torch.tensor([0.25], device=DEV)
+    a2 = torch.tensor([0.1], device=DEV)
+    g1, b1 = 1.0 + 0.3 * _rand(H, seed=81), _rand(H, seed=82)
+    wd = _rand(H, 1, P, seed=83, scale=0.5)
+    w_hi, w_lo, _, _ = Kn.weight_prep(_rand(B, H, seed=84, scale=0.05), 1.0 + 0.3 * _rand(H, seed=85), _rand(H, seed=86))
+    pa = F.prelu(a, a1).view(M, K * H)
+    parts = torch.zeros(M, 3, 2, device=DEV)
+    parts[:, 0, 0] = pa.double().sum(1).float()
+    parts[:, 2, 1] = (pa.double() ** 2).sum(1).float()
+    y, st, d = Kn.dwpw(M, K, a, a1, g1, b1, parts, 3, wd, a2, w_hi, w_lo, dil, causal, want_d=True)
+    y0, st0 = Kn.dwpw(M, K, a, a1, g1, b1, parts, 3, wd, a2, w_hi, w_lo, dil, causal)
+    assert torch.equal(y, y0) and torch.equal(st, st0)                    # the extra store changes nothing else
+    pre, _, _, _ = Kn.dwconv(M, K, a, a1, g1, b1, nat.NORM_GLN, parts, 3, wd, a2, dil, causal)
+    assert not torch.isnan(d).any()
+    assert rel_l2(d, pre) < 2e-6
+
+
 def test_dwconv_rejects_length_changing_config():
     """P=2 non-causal changes the length; the reference crashes at the residual add"""
     H, K, M = 4, 10, 1
