@@ -15,7 +15,7 @@ import weakref
 import torch
 
 from . import _native as nat
-from ._engine import _MASK, _NORM, PlanCache, _Prepared, _check_cfg, aligned_params
+from ._engine import _MASK, _NORM, PlanCache, _Plan, _Prepared, _check_cfg, aligned_params
 from ._engine import BN_EPS
 from ._layout import block_keys, frame_geometry, is_bn, param_spec
 
@@ -55,6 +55,8 @@ class _PreparedBwd:
 
 class TrainPlan:
     """Workspaces and call lists of one (M, T) training step on one device."""
+
+    fuse_forward = True     # class-wide switch (tests compare both forward routes)
 
     def __init__(self, cfg, M, T, device, overlap=True):
         _check_cfg(cfg, training=True)
@@ -96,6 +98,20 @@ class TrainPlan:
             self.stat1 = [z(Rr, self.P1, 2, **f32) for _ in range(NB)]
             self.stat2 = [z(Rr, 2, **f32) for _ in range(NB)]
         self.score = e(Rr, C_ * N, **f32)
+        # Forward through the inference kernels (ctn_updc1_fwd + ctn_dwpw_fwd, two launches per block instead of
+        # three): gLN models whose shapes those kernels cover, from 8192 frames up (below, the plain
+        # kernels are as quick).  They save what autograd needs: every block's input pair (out-of-place update), a
+        # before the PReLU, and the depthwise output before the second PReLU.
+        self.fused_fwd = (self.fuse_forward and not self.bn and self.norm == nat.NORM_GLN and Rr >= _Plan.FUSE_UPDATE_MIN_ROWS
+                          and bool(lib.ctn_updc1_supported(B, H, self.norm))
+                          and bool(lib.ctn_updc1_supported(B, C_ * N, self.norm))
+                          and all(bool(lib.ctn_dwpw_supported(H, B, cfg["P"], 2 ** x, self.norm)) for x in range(cfg["X"])))
+        if self.fused_fwd:
+            self.y = e(Rr, B, **f32)
+            self.P2s = [lib.ctn_dwpw_partials(K, 2 ** x) for x in range(cfg["X"])]     # the fused kernel's partial layout
+            self.stat2 = [z(M, max(self.P2s), 2, **f32) for _ in range(NB)]
+            self.stat_mask = z(M, lib.ctn_gemm_gln_partials(K, C_ * N), 2, **f32)
+            self.one = torch.ones(1, **f32)
         # backward
         self.ds_hl = (e(Rr, C_ * N, **bf), e(Rr, C_ * N, **bf))
         self.dw_dec = e(Rr, N, **f32)
@@ -294,6 +310,55 @@ class TrainPlan:
             calls.append(allreduce)
         return calls
 
+    def _updc1(self, x_in, x_out, i_prev, w2_prev, w, Cout, out, out_stat, slope, kind):
+        """x_out = x_in + deferred gLN-2 + residual of block i_prev (whose raw pointwise product is self.y);
+        out = W x_out (before the PReLU: autograd needs it raw) with the gLN statistics of PReLU(out)."""
+        cfg, M, K = self.cfg, self.M, self.K
+        B, H = cfg["B"], cfg["H"]
+        Rr = M * K
+        c = nat.Updc1Args()
+        c.M, c.K, c.B, c.H = M, K, B, Cout
+        c.x_hi, c.x_lo, c.y = x_in[0].data_ptr(), x_in[1].data_ptr(), self.y.data_ptr()
+        c.x_out_hi, c.x_out_lo, c.store_raw = x_out[0].data_ptr(), x_out[1].data_ptr(), 1
+        c.in_stat, c.in_P, c.in_count = self.stat2[i_prev].data_ptr(), self.P2s[i_prev % cfg["X"]], float(K) * H
+        c.col_g, c.col_bias = w2_prev[2].data_ptr(), w2_prev[3].data_ptr()
+        c.w_hi, c.w_lo = w[0].data_ptr(), w[1].data_ptr()
+        c.a, c.out_stat, c.slope = out.data_ptr(), out_stat.data_ptr(), slope.data_ptr()
+        self._keep.append(c)
+        fn = nat.lib().ctn_updc1_fwd
+        return self._tag(lambda s, ref=C.byref(c): fn(ref, s), kind, 2.0 * Rr * B * Cout + 2.0 * Rr * B,
+                         Rr * (12.0 * B + 4.0 * Cout))
+
+    def _build_fused_forward_block(self, fwd, params, prep, i, xb, k):
+        """Block i through the inference kernels: [deferred update of block i-1 +] conv1x1 (a before the PReLU,
+        statistics of PReLU(a)), then PReLU / gLN-1 / depthwise / PReLU straight into the pointwise GEMM, whose raw
+        product y and gLN-2 partials the NEXT block's (or the mask conv's) update consumes.  Saved for the backward:
+        x_hl[i], a[i], d[i], stat1[i], stat2[i] - what the three-kernel route saves."""
+        cfg, M, K, tag = self.cfg, self.M, self.K, self._tag
+        B, H, P = cfg["B"], cfg["H"], cfg["P"]
+        Rr = M * K
+        pb = prep.blocks[i]
+        if i == 0:      # the bottleneck wrote x_hl[0]: plain conv1x1
+            fwd.append(tag(self._gemm(Cin=B, Cout=H, a_hi=self.x_hl[0][0], a_lo=self.x_hl[0][1], w_hi=pb["w1"][0],
+                                      w_lo=pb["w1"][1], out_f32=self.a[0], out_stat=self.norm,
+                                      out_stat_buf=self.stat1[0], stat_prelu=params[k["a1"]]),
+                           "fwd_gemm_conv1x1", 2.0 * Rr * B * H, Rr * (4.0 * B + 4.0 * H)))
+        else:
+            fwd.append(self._updc1(self.x_hl[i - 1], self.x_hl[i], i - 1, prep.blocks[i - 1]["w2"], pb["w1"], H, self.a[i],
+                                   self.stat1[i], params[k["a1"]], "fwd_gemm_update_conv1x1"))
+        f = nat.DwpwArgs()
+        f.M, f.K, f.H, f.B, f.dilation, f.causal = M, K, H, B, 2 ** xb, int(bool(cfg["causal"]))
+        f.a, f.prelu_in = self.a[i].data_ptr(), params[k["a1"]].data_ptr()
+        f.gamma_in, f.beta_in = params[k["g1"]].data_ptr(), params[k["b1"]].data_ptr()
+        f.in_stat, f.in_P = self.stat1[i].data_ptr(), self.P1
+        f.wd, f.prelu_out = params[k["wd"]].data_ptr(), params[k["a2"]].data_ptr()
+        f.w_hi, f.w_lo = pb["w2"][0].data_ptr(), pb["w2"][1].data_ptr()
+        f.y, f.out_stat, f.d_out = self.y.data_ptr(), self.stat2[i].data_ptr(), self.d[i].data_ptr()
+        self._keep.append(f)
+        fn = nat.lib().ctn_dwpw_fwd
+        fwd.append(tag(lambda s, ref=C.byref(f): fn(ref, s), "fwd_gemm_dwpw_fused", 2.0 * Rr * B * H + 2.0 * Rr * H * P,
+                       Rr * (8.0 * H + 4.0 * B)))
+
     def build(self, params, prep, prep_b, bn_mode=(False, None, None), bn_buffers=None):
         cfg = self.cfg
         N, L, B, H, C_, P = cfg["N"], cfg["L"], cfg["B"], cfg["H"], cfg["C"], cfg["P"]
@@ -338,6 +403,10 @@ class TrainPlan:
                     self._build_bn_forward_block(fwd, params, bn_buffers, pb, i, xb, k, bn_count, use_running)
                     i += 1
                     continue
+                if self.fused_fwd:
+                    self._build_fused_forward_block(fwd, params, prep, i, xb, k)
+                    i += 1
+                    continue
                 fwd.append(tag(self._gemm(Cin=B, Cout=H, a_hi=self.x_hl[i][0], a_lo=self.x_hl[i][1], w_hi=pb["w1"][0],
                                           w_lo=pb["w1"][1], out_f32=self.a[i], out_stat=GLN,
                                           out_stat_buf=self.stat1[i], stat_prelu=params[k["a1"]]),
@@ -359,9 +428,13 @@ class TrainPlan:
                                           out_f32=self.x, out_hi=self.x_hl[i + 1][0], out_lo=self.x_hl[i + 1][1]),
                                "fwd_gemm_pointwise", 2.0 * Rr * B * H, Rr * (4.0 * H + 12.0 * B)))
                 i += 1
-        fwd.append(tag(self._gemm(Cin=B, Cout=C_ * N, a_hi=self.x_hl[NB][0], a_lo=self.x_hl[NB][1], w_hi=prep.mask[0],
-                                  w_lo=prep.mask[1], out_f32=self.score),
-                       "fwd_gemm_mask", 2.0 * Rr * B * C_ * N, Rr * (4.0 * B + 4.0 * C_ * N)))
+        if self.fused_fwd:     # the last block's deferred update rides in the mask conv (PReLU slope 1 = identity)
+            fwd.append(self._updc1(self.x_hl[NB - 1], self.x_hl[NB], NB - 1, prep.blocks[NB - 1]["w2"], prep.mask, C_ * N,
+                                   self.score, self.stat_mask, self.one, "fwd_gemm_update_mask"))
+        else:
+            fwd.append(tag(self._gemm(Cin=B, Cout=C_ * N, a_hi=self.x_hl[NB][0], a_lo=self.x_hl[NB][1], w_hi=prep.mask[0],
+                                      w_lo=prep.mask[1], out_f32=self.score),
+                           "fwd_gemm_mask", 2.0 * Rr * B * C_ * N, Rr * (4.0 * B + 4.0 * C_ * N)))
         self.fwd_calls = fwd
         self.dec_args = (self.score.data_ptr(), self.w.data_ptr(), V.data_ptr(), M, K, N, L, C_, T,
                          _MASK[cfg["mask_nonlinear"]])

@@ -145,6 +145,39 @@ def test_gradients_match_oracle_paper_config(name):
     assert slopes < 5e-3
 
 
+def test_fused_training_forward_matches_the_three_kernel_route():
+    """From 8192 frames up a gLN training forward runs through the inference kernels (ctn_updc1_fwd with an out-of-place
+    update and a before the PReLU, ctn_dwpw_fwd saving the depthwise output): same estimates and gradients as the
+    three-kernel route to rounding, and the route is the one the plan reports."""
+    import pit_criterion
+    from ctn_b200._autograd import TrainPlan
+    cfg, M, lens = GRAD_CONFIGS["cfg2_paper_gln"] if "cfg2_paper_gln" in GRAD_CONFIGS else list(GRAD_CONFIGS.values())[0]
+    T = 32000
+    p32 = O.random_params(*(cfg[k] for k in "NLBHPXRC"), cfg["causal"], seed=99)
+    g = torch.Generator().manual_seed(100)
+    src = (0.1 * torch.randn(M, cfg["C"], T, generator=g)).to(DEV)
+    mix = src.sum(1)
+    lengths = torch.tensor(lens, device=DEV)
+    out = {}
+    try:
+        for fused in (True, False):
+            TrainPlan.fuse_forward = fused
+            model = _build(cfg, p32)
+            est = model(mix)
+            plan = next(iter(model.train_engine().plans.values()))
+            assert plan.fused_fwd == fused
+            kinds = [plan.meta[c][0] for c in plan.fwd_calls if c in plan.meta]
+            assert ("fwd_gemm_dwpw_fused" in kinds) == fused and ("fwd_dwconv" in kinds) == (not fused)
+            loss, *_ = pit_criterion.cal_loss(src, est, lengths)
+            loss.backward()
+            out[fused] = (est.detach().clone(), float(loss), torch.cat([p.grad.flatten() for p in model.parameters()]))
+    finally:
+        TrainPlan.fuse_forward = True
+    assert rel_l2(out[True][0], out[False][0]) < 5e-5
+    assert abs(out[True][1] - out[False][1]) < 1e-3
+    assert rel_l2(out[True][2], out[False][2]) < 1e-3
+
+
 def test_training_step_reduces_loss_and_is_deterministic():
     import pit_criterion
     cfg, z = load_golden("tc_small")
