@@ -292,7 +292,7 @@ def _roofs(acc, pk, traffic, names, how):
         tensor = "gemm" in k or "wgrad" in k
         # c1::updc1_kernel moves 5 KB per frame (x, y in; x, a out) for one 256 x 512 product: its limiter is the
         # memory system (profiles/r2), so it is held against the HBM roofline; its tensor figures ride along
-        if k.startswith("gemm_update"):
+        if k.startswith("gemm_update") or k.startswith("fwd_gemm_update"):
             ach = a[1] / a[2] / 1e6
             fl = a[0] / a[2] / 1e9
             r = {"bound": "hbm", "achieved": ach, "peak": pk["hbm"], "unit": "GB/s", "frac": ach / pk["hbm"],
@@ -522,7 +522,10 @@ def _precision():
 
 TRAIN_NAMES = {"fwd_gemm_conv1x1": "gemm_tc_kernel (conv1x1 + PReLU statistics)",
                "fwd_gemm_pointwise": "gemm_tc_kernel (pointwise + folded gLN + residual)",
-               "fwd_dwconv": "dwconv_march_kernel", "bwd_wgrad": "wgrad_tc_kernel (MN-major tcgen05 weight gradient)",
+               "fwd_dwconv": "dwconv_march_kernel",
+               "fwd_gemm_dwpw_fused": "fb::dwpw_kernel<false, true> (depthwise producers + pointwise GEMM, saves d)",
+               "fwd_gemm_update_conv1x1": "c1::updc1_kernel (out-of-place residual update + conv1x1, a before the PReLU)",
+               "fwd_gemm_update_mask": "c1::updc1_kernel (residual update + mask conv)", "bwd_wgrad": "wgrad_tc_kernel (MN-major tcgen05 weight gradient)",
                "bwd_gemm_dgrad_pointwise": "gemm_tc_kernel (dgrad of pointwise + norm-backward sums)",
                "bwd_gemm_dgrad_conv1x1": "gemm_tc_kernel (dgrad of conv1x1 + residual)",
                "bwd_dwconv": "bwd_dw_march_kernel", "bwd_prelu_norm": "bwd_prelu_norm_kernel",

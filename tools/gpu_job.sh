@@ -32,7 +32,7 @@ ncu)
   timeout 300 python tools/profile_train_once.py 3 2 > $O/${tag}_plain_train.log 2>&1 &&
   ncu --metrics gpu__time_duration.sum --clock-control none --csv --log-file $O/${tag}_launches_train.csv \
       python tools/profile_train_once.py 3 2 > $O/${tag}_ncu_train_list.log 2>&1
-  for k in wgrad_tc_kernel:70:2 gemm_tc_kernel:210:4 bwd_dw_march:34:1 dwconv_march:34:1; do
+  for k in wgrad_tc_kernel:70:2 gemm_tc_kernel:80:4 bwd_dw_march:34:1 dwpw_kernel:34:1 updc1_kernel:34:1; do
     IFS=: read name skip cnt <<< "$k"
     ncu --set full --clock-control none --import-source on -k regex:$name -s $skip -c $cnt -o $O/${tag}_prof_train_$name -f \
         python tools/profile_train_once.py 3 2 > $O/${tag}_ncu_train_$name.log 2>&1

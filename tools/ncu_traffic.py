@@ -20,7 +20,8 @@ KIND = {  # (section, substring of the kernel name) -> bench.py kernel kind
     "forward": [("dwpw_kernel", "gemm_dwpw_fused"), ("gemm_tc_kernel<256, 1, 0>", "gemm_conv1x1"),
                 ("updc1_kernel", "gemm_update_conv1x1"), ("resid_update", "resid_update"),
                 ("encoder_fwd", "encoder"), ("decoder_fwd", "decoder")],
-    "train": [("wgrad_tc_kernel", "bwd_wgrad"), ("bwd_dw_march", "bwd_dwconv"), ("dwconv_march", "fwd_dwconv")],
+    "train": [("wgrad_tc_kernel", "bwd_wgrad"), ("bwd_dw_march", "bwd_dwconv"), ("dwconv_march", "fwd_dwconv"),
+              ("dwpw_kernel", "fwd_gemm_dwpw_fused"), ("updc1_kernel", "fwd_gemm_update_conv1x1")],
 }
 
 
