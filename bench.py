@@ -309,7 +309,7 @@ def _roofs(acc, pk, traffic, names, how):
             ach = a[1] / a[2] / 1e6
             r = {"bound": "hbm", "achieved": ach, "peak": pk["hbm"], "unit": "GB/s", "frac": ach / pk["hbm"],
                  "peak_source": pk["source"] + " (copy bandwidth)"}
-        r.update({"kernel": names.get(k, k), "avg_launch_ms": a[2] / n, "launches_per_step": n,
+        r.update({"kernel": names.get(k, k), "avg_launch_ms": a[2] / n, "launches_per_pass": n,
                   "algorithmic_bytes_per_launch": a[1] / n, "share_of_step": a[2] / tot_ms, "traffic": traffic.get(k)})
         roofs[k] = r
     dom = max(roofs, key=lambda k: roofs[k]["share_of_step"])
@@ -471,6 +471,8 @@ def run_b200(args):
         tot_ms = sum(a[2] for a in acc.values())
         breakdown = {k: {"launches": a[3] // reps, "ms": a[2] / reps, "share": a[2] / tot_ms,
                          "tflops": a[0] / a[2] / 1e9, "gbs": a[1] / a[2] / 1e6} for k, a in acc.items()}
+        for a in acc.values():          # per pass of one micro-batch
+            a[0], a[1], a[2], a[3] = a[0] / reps, a[1] / reps, a[2] / reps, a[3] // reps
         roof = _roofs(acc, pk, _traffic("forward", mb), FWD_NAMES,
                       "dominant kernel by share of the step; CUDA events around every launch of one %d-utterance "
                       "micro-batch pass, %d repeats; traffic from profiles/r2/ncu_traffic.json when it was captured "

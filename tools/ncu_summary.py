@@ -54,8 +54,9 @@ if ha in idx and ce in idx:
     print("derived__tensor_pipe_utilisation,fraction,%s" % ",".join(
         "%.4f" % (f(r[idx[ha]]) / (4.0 * f(r[idx[ce]]))) for r in data))
     if "dram__bytes_read.sum" in idx:
+        ub = {"byte": 1e-9, "Kbyte": 1e-6, "Mbyte": 1e-3, "Gbyte": 1.0}
+        ut = {"ns": 1e-9, "us": 1e-6, "ms": 1e-3, "s": 1.0}
+        gb = lambda r, m: f(r[idx[m]]) * ub[units[idx[m]]]      # each column carries its own unit
         print("derived__dram_GBps,GB/s,%s" % ",".join("%.1f" % (
-            (f(r[idx["dram__bytes_read.sum"]]) + f(r[idx["dram__bytes_write.sum"]])) *
-            {"byte": 1e-9, "Kbyte": 1e-6, "Mbyte": 1e-3, "Gbyte": 1.0}[units[idx["dram__bytes_read.sum"]]] /
-            (f(r[idx["gpu__time_duration.sum"]]) * {"ns": 1e-9, "us": 1e-6, "ms": 1e-3, "s": 1.0}[units[idx["gpu__time_duration.sum"]]])
-        ) for r in data))
+            (gb(r, "dram__bytes_read.sum") + gb(r, "dram__bytes_write.sum")) /
+            (f(r[idx["gpu__time_duration.sum"]]) * ut[units[idx["gpu__time_duration.sum"]]])) for r in data))
