@@ -1,5 +1,5 @@
-python bench.py --steps 10 --warmup 3 --no-cpu 2>/dev/null | python -c "
-import json,sys
-d=json.loads(sys.stdin.read().strip().splitlines()[-1]); print(round(d['value']), d['clocks']['sm_mhz'])
-t=d['train_step']; print('train', t['ms_per_step'], t['gpu_launches_per_step'], t.get('serial_kernel_ms'))
-for k,v in sorted(t['kernel_breakdown'].items(), key=lambda kv:-kv[1]['ms']): print('   ',k,v['launches'],round(v['ms']*1e3/v['launches'],1),'us',round(v['share'],3))"
+timeout 600 python -m pytest tests/test_gpu_kernels.py -m gpu -x -q -k "fused_depthwise" 2>&1 | tail -2
+for i in 1 2; do
+CTN_DILS=1,8,128 timeout 200 python tools/bench_fused.py 64 2>&1 | grep dwpw
+CTN_ALLOW_EXPERIMENT_BUILD=1 CTN_LIB_FILE=libctn_exp.so CTN_DILS=1,8,128 timeout 200 python tools/bench_fused.py 64 2>&1 | grep dwpw
+done
