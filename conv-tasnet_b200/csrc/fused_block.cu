@@ -35,13 +35,18 @@
 namespace ctn {
 
 int make_tmap_bf16_kmajor(CUtensorMap* tm, const void* ptr, long long rows, int cols, int box_rows);  // gemm.cu
+int make_tmap_phase_f32(CUtensorMap* tm, const void* ptr, int M, int K, int C, int d, int box_j);       // gemm.cu
 
 namespace fb {
 
 constexpr int kBM = 128;             // tile rows = TMEM lanes
 constexpr int kBN = 256;             // output channels (B) per tile = whole pointwise output
 constexpr int kBK = 64;              // channels per k-block = one 128 B swizzle atom of bf16
-constexpr int kASlots = 4;           // produced A units in flight: more than producer groups, so a group never
+#ifndef CTN_FB_TMA_DRAIN
+#define CTN_FB_TMA_DRAIN 1
+#endif
+constexpr bool kTmaDrain = CTN_FB_TMA_DRAIN != 0;   // y of full row groups leaves through staging + TMA tensor stores
+constexpr int kASlots = kTmaDrain ? 3 : 4;           // produced A units in flight: more than producer groups, so a group never
                                      // waits for the MMAs to consume its own previous unit
 constexpr int kWSlots = 2;           // weight k-blocks in flight (TMA, L2-resident)
 constexpr int kABytes = kBM * kBK * 2;           // one of hi / lo
@@ -54,7 +59,8 @@ constexpr int kCtrlWarps = 4;        // one warpgroup: 0 TMA, 1 MMA, 2-3 idle (t
 constexpr int kThreads = 32 * (kCtrlWarps + kProdWarps);
 constexpr int kCtrlRegs = 56, kProdRegs = 152;   // per scheduler partition: 1 control + 3 producer warps <= 512 x 32 registers
 constexpr int kBarBytes = 256;
-constexpr int kStgBytes = 0;
+constexpr int kStgWarp = 32 * 128;      // one 32-column chunk of a warp's 32 rows
+constexpr int kStgBytes = kTmaDrain ? 12 * kStgWarp : 0;
 constexpr int kMaxTiles = 32;        // row tiles per CTA whose gLN-1 (mean, rstd) are precomputed
 constexpr int kSmemFixed = kTileBytes + kBarBytes + kStgBytes + kMaxTiles * 8;   // + 20 H bytes of per-channel constants
 constexpr int kSmemMax = 232448;
@@ -98,14 +104,15 @@ __device__ __forceinline__ int tile_j0(const Params& p, int tt, int s) {
 // kStoreD: the depthwise output before the second PReLU is also written to d_out (the training forward)
 template <bool kPreact, bool kStoreD = false>
 __global__ void __launch_bounds__(kThreads, 1)
-dwpw_kernel(const __grid_constant__ CUtensorMap tm_w_hi, const __grid_constant__ CUtensorMap tm_w_lo, const Params p) {
+dwpw_kernel(const __grid_constant__ CUtensorMap tm_w_hi, const __grid_constant__ CUtensorMap tm_w_lo,
+            const __grid_constant__ CUtensorMap tm_y, const Params p) {
     const uint32_t rank = ptx::cluster_ctarank();
     const int worker = static_cast<int>(blockIdx.x >> 1);
     const int n_workers = static_cast<int>(gridDim.x >> 1);
     extern __shared__ __align__(1024) uint8_t smem[];
     if ((ptx::smem_u32(smem) & 1023u) != 0) __trap();
     uint8_t* wsm = smem + kASlots * kASlotBytes;                // weight slots follow the A slots
-    uint64_t* afull_bar = reinterpret_cast<uint64_t*>(smem + kTileBytes);
+    uint64_t* afull_bar = reinterpret_cast<uint64_t*>(smem + kTileBytes + kStgBytes);
     uint64_t* aempty_bar = afull_bar + kASlots;
     uint64_t* wfull_bar = aempty_bar + kASlots;
     uint64_t* wempty_bar = wfull_bar + kWSlots;
@@ -117,6 +124,7 @@ dwpw_kernel(const __grid_constant__ CUtensorMap tm_w_hi, const __grid_constant__
     const int lane = threadIdx.x & 31;
     const int nkb = p.nkb;
     // per-channel constants of the producers: gamma, beta and the three taps, [5][H]
+    uint8_t* stg_smem = smem + kTileBytes;                      // [12 warps][32 rows][128 B] (TMA drain), 1024-aligned
     float2* tstat = reinterpret_cast<float2*>(smem + kTileBytes + kBarBytes + kStgBytes);   // [kMaxTiles] (mean, rstd)
     float* cst = reinterpret_cast<float*>(smem + kTileBytes + kBarBytes + kStgBytes + kMaxTiles * 8);
     for (int i = threadIdx.x; i < p.H; i += kThreads) {
@@ -130,6 +138,7 @@ dwpw_kernel(const __grid_constant__ CUtensorMap tm_w_hi, const __grid_constant__
     if (warp == 0 && lane == 0) {
         ptx::prefetch_tmap(&tm_w_hi);
         ptx::prefetch_tmap(&tm_w_lo);
+        ptx::prefetch_tmap(&tm_y);
         for (int i = 0; i < kASlots; ++i) {
             ptx::mbar_init(afull_bar + i, 2 * 4);   // one arrival per producer warp of the filling group, both CTAs
             ptx::mbar_init(aempty_bar + i, 1);
@@ -296,6 +305,38 @@ dwpw_kernel(const __grid_constant__ CUtensorMap tm_w_hi, const __grid_constant__
             float* yrow = p.y + (static_cast<long long>(m) * p.K + frame) * kBN;
             ptx::mbar_wait(tfull_bar + as, aphase);
             ptx::tc_fence_after();
+            const uint32_t tsrc = tmem_base + (static_cast<uint32_t>(ew * 32) << 16) + as * kBN;
+            const bool full = __all_sync(0xffffffffu, valid);
+            if (kTmaDrain && full) {
+                // All 32 rows exist: the warp stages a 32-column chunk (lane = row, 16 B pieces XOR-swizzled with the
+                // row as the 128B-swizzled map expects: conflict-free) and lane 0 hands it to the async proxy as two
+                // tensor stores, one per 16-frame run of a dilation phase.  Shared-memory stores release their
+                // operands at once; the register path's 256-bit global stores held theirs until the LSU had taken
+                // them, and the next TMEM load's write-after-read wait was the producers' largest single stall.
+                const uint32_t buf = ptx::smem_u32(stg_smem) + static_cast<uint32_t>(pw) * kStgWarp;
+                const uint32_t srow = buf + static_cast<uint32_t>(lane) * 128u;
+                const int ph_l = tile_phase(p, tt, sr), j_l = tile_j0(p, tt, sr);
+                const int ph1 = __shfl_sync(0xffffffffu, ph_l, 16), j1 = __shfl_sync(0xffffffffu, j_l, 16);
+#pragma unroll 1
+                for (int ci = 0; ci < kBN / 32; ++ci) {
+                    uint32_t v[32];
+                    ptx::tmem_ld_32x32(tsrc + ci * 32, v);
+                    if (lane == 0) ptx::tma_store_wait_read<0>();   // the previous chunk's stores have read the buffer
+                    __syncwarp();
+                    ptx::tmem_ld_wait();
+#pragma unroll
+                    for (int j = 0; j < 8; ++j)
+                        ptx::st_shared_v4(srow + ((static_cast<uint32_t>(j) ^ (static_cast<uint32_t>(lane) & 7u)) << 4), v[4 * j],
+                                          v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+                    ptx::fence_async_smem();
+                    __syncwarp();
+                    if (lane == 0) {
+                        ptx::tma_store_4d_addr(&tm_y, buf, ci * 32, ph_l, j_l, m);
+                        ptx::tma_store_4d_addr(&tm_y, buf + 2048u, ci * 32, ph1, j1, m);
+                        ptx::tma_store_commit();
+                    }
+                }
+            } else {
             // 16-column pieces in two alternating register sets: the TMEM load of piece h + 1 is in flight while
             // piece h is stored, and a set is reloaded only one piece after its stores were issued (the loads'
             // write-after-read wait on the stores' operands was the drain's main stall)
@@ -316,6 +357,7 @@ dwpw_kernel(const __grid_constant__ CUtensorMap tm_w_hi, const __grid_constant__
                     ptx::st_global_v8(yrow + (h + 1) * 16, vb[0], vb[1], vb[2], vb[3], vb[4], vb[5], vb[6], vb[7]);
                     ptx::st_global_v8(yrow + (h + 1) * 16 + 8, vb[8], vb[9], vb[10], vb[11], vb[12], vb[13], vb[14], vb[15]);
                 }
+            }
             }
             ptx::tc_fence_before();
             __syncwarp();
@@ -515,6 +557,7 @@ dwpw_kernel(const __grid_constant__ CUtensorMap tm_w_hi, const __grid_constant__
             drain(next_drain);
             next_drain += 3;
         }
+        if (kTmaDrain && lane == 0) ptx::tma_store_wait_all<0>();   // the staging buffers must outlive their stores
     }
 
     ptx::tc_fence_before();
@@ -650,6 +693,8 @@ extern "C" int ctn_dwpw_fwd(const ctn_dwpw_args* args, void* stream_) {
     int rc;
     if ((rc = make_tmap_bf16_kmajor(&tw_hi, a.w_hi, a.B, a.H, fb::kBN / 2)) != CTN_OK) return rc;
     if ((rc = make_tmap_bf16_kmajor(&tw_lo, a.w_lo, a.B, a.H, fb::kBN / 2)) != CTN_OK) return rc;
+    CUtensorMap ty;
+    if ((rc = make_tmap_phase_f32(&ty, a.y, a.M, a.K, a.B, a.dilation, fb::kRowsPerThread)) != CTN_OK) return rc;
     const bool preact = a.prelu_in == nullptr;
     p.d_out = a.d_out;
     CTN_REQUIRE(a.d_out == nullptr || (!preact && aligned16(a.d_out)),
@@ -678,7 +723,7 @@ extern "C" int ctn_dwpw_fwd(const ctn_dwpw_args* args, void* stream_) {
     attr[1].val.programmaticStreamSerializationAllowed = pdl_allowed(stream, static_cast<long long>(a.M) * a.K);
     cfg.attrs = attr;
     cfg.numAttrs = 2;
-    cudaError_t e = cudaLaunchKernelEx(&cfg, kern, tw_hi, tw_lo, p);
+    cudaError_t e = cudaLaunchKernelEx(&cfg, kern, tw_hi, tw_lo, ty, p);
     if (e != cudaSuccess) return cuda_fail(e, "cudaLaunchKernelEx(dwpw_kernel)");
     return CTN_OK;
 }

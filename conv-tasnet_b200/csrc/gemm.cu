@@ -737,6 +737,31 @@ int make_tmap_bf16_3d(CUtensorMap* tm, const void* ptr, int M, int K, int C, int
     return CTN_OK;
 }
 
+// fp32 [M, K, C] seen by dilation phase: dims (C, d, ceil(K / d), M), element (c, ph, j, m) = frame j d + ph of
+// utterance m; box = 32 columns x 1 phase x box_j frames of that phase, 128B swizzle.  Stores only, and only for boxes
+// whose frames all exist: a (ph, j) with j d + ph >= K aliases the next utterance and is NOT clipped by the map.
+int make_tmap_phase_f32(CUtensorMap* tm, const void* ptr, int M, int K, int C, int d, int box_j) {
+    PFN_encodeTiled enc = get_encode_fn();
+    if (!enc) {
+        set_error("cuTensorMapEncodeTiled not available from the driver");
+        return CTN_ERR_CUDA;
+    }
+    const cuuint64_t row = static_cast<cuuint64_t>(C) * 4;
+    cuuint64_t dims[4] = {static_cast<cuuint64_t>(C), static_cast<cuuint64_t>(d), static_cast<cuuint64_t>((K + d - 1) / d),
+                          static_cast<cuuint64_t>(M)};
+    cuuint64_t strides[3] = {row, row * d, row * K};
+    cuuint32_t box[4] = {32, 1, static_cast<cuuint32_t>(box_j), 1};
+    cuuint32_t estr[4] = {1, 1, 1, 1};
+    CUresult r = enc(tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, const_cast<void*>(ptr), dims, strides, box, estr,
+                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_NONE,
+                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) {
+        set_error("cuTensorMapEncodeTiled(phase) failed (%d) ptr=%p M=%d K=%d C=%d d=%d", static_cast<int>(r), ptr, M, K, C, d);
+        return CTN_ERR_CUDA;
+    }
+    return CTN_OK;
+}
+
 template <int BN, bool PAIR, int EPI>
 static int launch_tc(const ctn_gemm_args& a, const EpiParams& ep, cudaStream_t stream) {
     using Cfg = TcCfg<BN, PAIR>;
