@@ -97,6 +97,7 @@ struct NormSplitParams {
 #define CTN_NS_TILE 16
 #endif
 constexpr int kNsTile = CTN_NS_TILE;
+constexpr int kNsPre = 8;   // vectors per thread requested up front: a 16-frame tile of 512 channels in float4s
 
 template <int VEC>
 __global__ void __launch_bounds__(kBwThreads) norm_split_kernel(const NormSplitParams p) {
@@ -104,15 +105,26 @@ __global__ void __launch_bounds__(kBwThreads) norm_split_kernel(const NormSplitP
     const int m = blockIdx.y, k0 = blockIdx.x * kNsTile;
     const int nk = min(kNsTile, p.K - k0);
     const bool gln = p.norm == CTN_NORM_GLN;
+    const int CV = (p.C + VEC - 1) / VEC;
+    const long long row0 = static_cast<long long>(m) * p.K + k0;
+    // the tile's first kNsPre vectors per thread are requested before the statistics are finalised: the kernel
+    // is one round trip to memory long, and the partial sums' round trip would otherwise come in front of it
+    V<VEC> xs[kNsPre];
+#pragma unroll
+    for (int j = 0; j < kNsPre; ++j) {
+        const int i = threadIdx.x + j * kBwThreads;
+        if (i < nk * CV) {
+            const int r = i / CV, c = (i - r * CV) * VEC;
+            xs[j].load(p.in + (row0 + r) * p.C + c);
+        }
+    }
     if (gln && threadIdx.x < 32) {
         const float2 st = gln_finalize_warp(p.stat + static_cast<long long>(m) * p.P, p.P, p.count);
         if (threadIdx.x == 0) st_s[0] = st.x, st_s[1] = st.y;
     }
     __syncthreads();
     const float slope = p.slope ? __ldg(p.slope) : 1.f;
-    const int CV = (p.C + VEC - 1) / VEC;
-    const long long row0 = static_cast<long long>(m) * p.K + k0;
-    for (int i = threadIdx.x; i < nk * CV; i += kBwThreads) {
+    auto emit = [&](int i, const V<VEC>& x) {
         const int r = i / CV, c = (i - r * CV) * VEC;
         const long long row = row0 + r;
         float mu = st_s[0], rs = st_s[1];
@@ -120,14 +132,24 @@ __global__ void __launch_bounds__(kBwThreads) norm_split_kernel(const NormSplitP
             const float2 st = __ldg(p.stat + row);
             mu = st.x, rs = st.y;
         }
-        V<VEC> x, g, b;
-        x.load(p.in + row * p.C + c);
+        V<VEC> g, b;
         g.load(p.gamma + c);
         b.load(p.beta + c);
         float o[VEC];
 #pragma unroll
         for (int j = 0; j < VEC; ++j) o[j] = fmaf(g.v[j], (prelu(x.v[j], slope) - mu) * rs, b.v[j]);
         store_hl<VEC>(p.out_hi + row * p.C + c, p.out_lo + row * p.C + c, o);
+    };
+#pragma unroll
+    for (int j = 0; j < kNsPre; ++j) {
+        const int i = threadIdx.x + j * kBwThreads;
+        if (i < nk * CV) emit(i, xs[j]);
+    }
+    for (int i = threadIdx.x + kNsPre * kBwThreads; i < nk * CV; i += kBwThreads) {
+        const int r = i / CV, c = (i - r * CV) * VEC;
+        V<VEC> x;
+        x.load(p.in + (row0 + r) * p.C + c);
+        emit(i, x);
     }
 }
 
@@ -375,6 +397,18 @@ __global__ void __launch_bounds__(kBwThreads) bwd_prelu_norm_kernel(const BwdPnP
     const int m = blockIdx.y, k0 = blockIdx.x * kNsTile;
     const int nk = min(kNsTile, p.K - k0);
     const double n = static_cast<double>(p.K) * H;
+    const int CV = (H + VEC - 1) / VEC;
+    const long long row0 = static_cast<long long>(m) * p.K + k0;
+    V<VEC> dns[kNsPre / 2], avs[kNsPre / 2];   // requested before the sums are finalised, as in norm_split
+#pragma unroll
+    for (int j = 0; j < kNsPre / 2; ++j) {
+        const int i = threadIdx.x + j * kBwThreads;
+        if (i < nk * CV) {
+            const int r = i / CV, c = (i - r * CV) * VEC;
+            dns[j].load(p.dn1 + (row0 + r) * H + c);
+            avs[j].load(p.a + (row0 + r) * H + c);
+        }
+    }
     if (threadIdx.x < 32) {
         const float2 s1 = gln_finalize_warp(p.stat1 + static_cast<long long>(m) * p.P1, p.P1, n);
         double a = 0.0, b = 0.0;
@@ -388,15 +422,11 @@ __global__ void __launch_bounds__(kBwThreads) bwd_prelu_norm_kernel(const BwdPnP
     __syncthreads();
     const float mu1 = sh[0], r1 = sh[1], m1 = sh[2], m2 = sh[3];
     const float al1 = __ldg(p.slope1);
-    const int CV = (H + VEC - 1) / VEC;
-    const long long row0 = static_cast<long long>(m) * p.K + k0;
     float da1[1] = {0.f};
-    for (int i = threadIdx.x; i < nk * CV; i += kBwThreads) {
+    auto emit = [&](int i, const V<VEC>& dn, const V<VEC>& av) {
         const int r = i / CV, c = (i - r * CV) * VEC;
         const long long row = row0 + r;
-        V<VEC> dn, av, g;
-        dn.load(p.dn1 + row * H + c);
-        av.load(p.a + row * H + c);
+        V<VEC> g;
         g.load(p.g1 + c);
         float o[VEC];
 #pragma unroll
@@ -407,6 +437,18 @@ __global__ void __launch_bounds__(kBwThreads) bwd_prelu_norm_kernel(const BwdPnP
             if (!(av.v[j] > 0.f)) da1[0] = fmaf(dp, av.v[j], da1[0]);
         }
         store_hl<VEC>(p.da_hi + row * H + c, p.da_lo + row * H + c, o);
+    };
+#pragma unroll
+    for (int j = 0; j < kNsPre / 2; ++j) {
+        const int i = threadIdx.x + j * kBwThreads;
+        if (i < nk * CV) emit(i, dns[j], avs[j]);
+    }
+    for (int i = threadIdx.x + (kNsPre / 2) * kBwThreads; i < nk * CV; i += kBwThreads) {
+        const int r = i / CV, c = (i - r * CV) * VEC;
+        V<VEC> dn, av;
+        dn.load(p.dn1 + (row0 + r) * H + c);
+        av.load(p.a + (row0 + r) * H + c);
+        emit(i, dn, av);
     }
     block_sum<1>(da1, red);
     if (threadIdx.x == 0) p.alpha_part[static_cast<long long>(m) * gridDim.x + blockIdx.x] = da1[0];
@@ -805,10 +847,15 @@ extern "C" int ctn_bwd_dwconv(const ctn_bwd_dw_args* args, void* stream) {
         q.g1 = a.g1, q.b1 = a.b1, q.g2 = a.g2, q.wd = a.wd, q.slope1 = a.slope1, q.slope2 = a.slope2;
         q.dn1 = a.dn1, q.chan_part = a.chan_part, q.scal_part = a.scal_part;
         dim3 grid(q.ctas, a.M);
+        static const bool attr_ok = [] {
+            return cudaFuncSetAttribute(bwd_dw_march_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, kBmSmemBytes) == cudaSuccess &&
+                   cudaFuncSetAttribute(bwd_dw_march_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, kBmSmemBytes) == cudaSuccess;
+        }();
+        CTN_REQUIRE(attr_ok, "ctn_bwd_dwconv: cannot reserve the row ring in shared memory");
         if (a.causal)
-            bwd_dw_march_kernel<2><<<grid, kBmWarps * 32, 0, static_cast<cudaStream_t>(stream)>>>(q);
+            bwd_dw_march_kernel<2><<<grid, kBmWarps * 32, kBmSmemBytes, static_cast<cudaStream_t>(stream)>>>(q);
         else
-            bwd_dw_march_kernel<1><<<grid, kBmWarps * 32, 0, static_cast<cudaStream_t>(stream)>>>(q);
+            bwd_dw_march_kernel<1><<<grid, kBmWarps * 32, kBmSmemBytes, static_cast<cudaStream_t>(stream)>>>(q);
         CTN_LAUNCH_CHECK("bwd_dw_march_kernel");
         return CTN_OK;
     }

@@ -17,11 +17,26 @@
 #pragma once
 #include "common.cuh"
 #include "f32x2.cuh"
+#include "ptx.cuh"
 
 namespace ctn {
 
 constexpr int kBmUnits = 4;   // most (phase, 32-frame segment) units a warp accumulates before writing partials
-constexpr int kBmAhead = 4;   // rows loaded ahead of use
+#ifndef CTN_BM_RING
+#define CTN_BM_RING 8
+#endif
+// Rows in flight per thread.  They wait in a shared-memory ring filled by 16-byte asynchronous copies (LDGSTS), each
+// thread copying and reading back only its own slots: no barrier, no registers held by loads in flight.  The 4-row
+// register ring this replaces (48 registers; every first use of a loaded row was a scoreboard stall, 45 % of the
+// kernel's samples at batch 3) could not be deepened under the 168-register bound of three CTAs per SM.
+constexpr int kBmAhead = CTN_BM_RING;
+static_assert((kBmAhead & (kBmAhead - 1)) == 0 && kBmAhead >= 4, "ring depth: a power of two");
+constexpr int kBmSmemBytes = kBmAhead * 3 * 4 * 32 * 16;   // [slot][du, d, a][thread] float4
+template <int N>
+__device__ __forceinline__ void bm_wait_group() {
+    asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
+}
+__device__ __forceinline__ void bm_commit_group() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 // CTA shape: 4 warps, 3 CTAs per SM (168 registers per thread under that bound, a few spilled values).
 // The 8-warp, one-per-SM shape (204 registers) it replaces left a third of the register file idle and,
 // worse, quantised badly: at the reference's batch of 3 x 4 s the 1200 warps of work made 150 CTAs for
@@ -84,22 +99,59 @@ __device__ __forceinline__ void block_sum2_double(double& s, double& ss, double*
 template <int C0>
 __global__ void __launch_bounds__(kBmWarps * 32, kBmCtasPerSm)
 bwd_dw_march_kernel(const BwdMarchParams p) {
-    __shared__ double fin_s[2 * kBmWarps];
+    __shared__ double fin_s[6 * kBmWarps];
     __shared__ float red_s[3 * kBmWarps];
+    extern __shared__ __align__(16) float4 ring_s[];   // [kBmAhead][3][kBmWarps * 32]
     const int m = blockIdx.y;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int H = p.H, d = p.dil;
     const double cnt = static_cast<double>(p.K) * H;
-    const float2 st1 = gln_finalize_block(p.stat1 + static_cast<long long>(m) * p.P1, p.P1, cnt, fin_s);
-    __syncthreads();
-    const float2 st2 = gln_finalize_block(p.stat2 + static_cast<long long>(m) * p.P2, p.P2, cnt, fin_s);
-    __syncthreads();
-    double bs = 0.0, bss = 0.0;
-    for (int i = threadIdx.x; i < p.Pb; i += blockDim.x) {
-        const float2 t = __ldg(p.bstat + static_cast<long long>(m) * p.Pb + i);
-        bs += t.x, bss += t.y;
+    // The three sets of partials (norm-1 and norm-2 statistics, the dgrad epilogue's backward sums) are fetched
+    // together and reduced with one barrier: three block reductions in a row were a tenth of the kernel at batch 3.
+    // Same summation order as gln_finalize_block.
+    double acc[6] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
+    {
+        const float2* src[3] = {p.stat1 + static_cast<long long>(m) * p.P1, p.stat2 + static_cast<long long>(m) * p.P2,
+                                p.bstat + static_cast<long long>(m) * p.Pb};
+        const int cnts[3] = {p.P1, p.P2, p.Pb};
+        constexpr int kT = kBmWarps * 32;
+        float2 v[3][3];
+#pragma unroll
+        for (int q = 0; q < 3; ++q)
+#pragma unroll
+            for (int r = 0; r < 3; ++r) {
+                const int i = threadIdx.x + r * kT;
+                v[q][r] = i < cnts[q] ? __ldg(src[q] + i) : make_float2(0.f, 0.f);
+            }
+#pragma unroll
+        for (int q = 0; q < 3; ++q) {
+#pragma unroll
+            for (int r = 0; r < 3; ++r) acc[2 * q] += static_cast<double>(v[q][r].x), acc[2 * q + 1] += static_cast<double>(v[q][r].y);
+            for (int i = threadIdx.x + 3 * kT; i < cnts[q]; i += kT) {
+                const float2 t = __ldg(src[q] + i);
+                acc[2 * q] += static_cast<double>(t.x), acc[2 * q + 1] += static_cast<double>(t.y);
+            }
+        }
+#pragma unroll
+        for (int q = 0; q < 6; ++q) {
+            acc[q] = warp_sum(acc[q]);
+            if ((threadIdx.x & 31) == 0) fin_s[q * kBmWarps + (threadIdx.x >> 5)] = acc[q];
+        }
+        __syncthreads();
+#pragma unroll
+        for (int q = 0; q < 6; ++q) {
+            acc[q] = 0.0;
+            for (int i = 0; i < kBmWarps; ++i) acc[q] += fin_s[q * kBmWarps + i];
+        }
     }
-    block_sum2_double(bs, bss, fin_s);
+    auto mean_rstd = [&](double sum, double sumsq) {
+        const double mean = sum / cnt;
+        double var = sumsq / cnt - mean * mean;
+        var = var > 0.0 ? var : 0.0;
+        return make_float2(static_cast<float>(mean), static_cast<float>(1.0 / sqrt(var + 1e-8)));
+    };
+    const float2 st1 = mean_rstd(acc[0], acc[1]), st2 = mean_rstd(acc[2], acc[3]);
+    const double bs = acc[4], bss = acc[5];
     const float mu1 = st1.x, r1 = st1.y, mu2 = st2.x, r2 = st2.y;
     const float m1 = static_cast<float>(bs / cnt), m2 = static_cast<float>(bss / cnt);
     const float al1 = __ldg(p.slope1), al2 = __ldg(p.slope2);
@@ -154,31 +206,36 @@ bwd_dw_march_kernel(const BwdMarchParams p) {
             const int L = n + 2 * C0;            // loaded rows
             const long long off0 = (ubase + ph + static_cast<long long>(i0) * d) * H + c;   // may precede the buffer
             auto valid = [&](int s) { return s < L && i0 + s >= 0 && i0 + s < J; };
-            float4 qdu[kBmAhead], qd[kBmAhead], qa[kBmAhead];
-            auto load = [&](int s, int slot) {
-                const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
-                qdu[slot] = z, qd[slot] = z, qa[slot] = z;
+            // one commit group per row (empty for rows that do not exist), so that the group count is uniform
+            float4* mine = ring_s + threadIdx.x;
+            auto load = [&](int s) {
                 if (valid(s)) {
                     const long long o = off0 + s * strd;
-                    qdu[slot] = *reinterpret_cast<const float4*>(p.du + o);
-                    qd[slot] = *reinterpret_cast<const float4*>(p.d + o);
-                    qa[slot] = *reinterpret_cast<const float4*>(p.a + o);
+                    float4* dst = mine + (s & (kBmAhead - 1)) * (3 * kBmWarps * 32);
+                    ptx::cp_async_16(dst, p.du + o);
+                    ptx::cp_async_16(dst + kBmWarps * 32, p.d + o);
+                    ptx::cp_async_16(dst + 2 * kBmWarps * 32, p.a + o);
                 }
+                bm_commit_group();
             };
 #pragma unroll
-            for (int s = 0; s < kBmAhead; ++s) load(s, s);
+            for (int s = 0; s < kBmAhead; ++s) load(s);
             f2_t dd0[2] = {zero, zero}, dd1[2] = {zero, zero}, dd2[2];
             f2_t n0[2] = {zero, zero}, n1[2] = {zero, zero}, n2[2];
             f2_t h0[2] = {zero, zero}, h1[2] = {zero, zero}, h2[2];
-            for (int sb = 0; sb < L; sb += kBmAhead) {
+            constexpr int kUnroll = 3;      // the three-row windows rotate by renaming
+            for (int sb = 0; sb < L; sb += kUnroll) {
 #pragma unroll
-                for (int u = 0; u < kBmAhead; ++u) {
+                for (int u = 0; u < kUnroll; ++u) {
                     const int s = sb + u;
                     if (s < L) {
                         const bool ok = valid(s);
                         const bool centre = s >= C0 && s < C0 + n;
-                        const float4 vdu = qdu[u], vd = qd[u], va = qa[u];
-                        load(s + kBmAhead, u);
+                        bm_wait_group<kBmAhead - 1>();          // row s has landed
+                        const float4* src = mine + (s & (kBmAhead - 1)) * (3 * kBmWarps * 32);
+                        float4 vdu, vd, va;
+                        if (ok) vdu = src[0], vd = src[kBmWarps * 32], va = src[2 * kBmWarps * 32];
+                        load(s + kBmAhead);                     // refills the slot just read (same thread, program order)
                         if (ok) {
                             const f2_t du2[2] = {f2_pack(vdu.x, vdu.y), f2_pack(vdu.z, vdu.w)};
                             const f2_t d2[2] = {f2_pack(vd.x, vd.y), f2_pack(vd.z, vd.w)};

@@ -46,7 +46,13 @@ constexpr int kBK = 64;              // channels per k-block = one 128 B swizzle
 #define CTN_FB_TMA_DRAIN 1
 #endif
 constexpr bool kTmaDrain = CTN_FB_TMA_DRAIN != 0;   // y of full row groups leaves through staging + TMA tensor stores
-constexpr int kASlots = kTmaDrain ? 3 : 4;           // produced A units in flight: more than producer groups, so a group never
+#ifndef CTN_FB_CST_GLOBAL
+#define CTN_FB_CST_GLOBAL 1
+#endif
+// per-channel constants (gamma, beta, taps) read through L1 at the start of a unit instead of from a shared-memory copy:
+// together with staging buffers per (TMEM stage, lane quarter) this leaves room for the fourth A slot next to the TMA drain
+constexpr bool kCstGlobal = CTN_FB_CST_GLOBAL != 0;
+constexpr int kASlots = (kTmaDrain && !kCstGlobal) ? 3 : 4;           // produced A units in flight: more than producer groups, so a group never
                                      // waits for the MMAs to consume its own previous unit
 constexpr int kWSlots = 2;           // weight k-blocks in flight (TMA, L2-resident)
 constexpr int kABytes = kBM * kBK * 2;           // one of hi / lo
@@ -60,7 +66,8 @@ constexpr int kThreads = 32 * (kCtrlWarps + kProdWarps);
 constexpr int kCtrlRegs = 56, kProdRegs = 152;   // per scheduler partition: 1 control + 3 producer warps <= 512 x 32 registers
 constexpr int kBarBytes = 256;
 constexpr int kStgWarp = 32 * 128;      // one 32-column chunk of a warp's 32 rows
-constexpr int kStgBytes = kTmaDrain ? 12 * kStgWarp : 0;
+constexpr int kStgBufs = kCstGlobal ? 8 : 12;   // per (TMEM stage, lane quarter): two tiles drain at once at most / per warp
+constexpr int kStgBytes = kTmaDrain ? kStgBufs * kStgWarp : 0;
 constexpr int kMaxTiles = 32;        // row tiles per CTA whose gLN-1 (mean, rstd) are precomputed
 constexpr int kSmemFixed = kTileBytes + kBarBytes + kStgBytes + kMaxTiles * 8;   // + 20 H bytes of per-channel constants
 constexpr int kSmemMax = 232448;
@@ -127,7 +134,7 @@ dwpw_kernel(const __grid_constant__ CUtensorMap tm_w_hi, const __grid_constant__
     uint8_t* stg_smem = smem + kTileBytes;                      // [12 warps][32 rows][128 B] (TMA drain), 1024-aligned
     float2* tstat = reinterpret_cast<float2*>(smem + kTileBytes + kBarBytes + kStgBytes);   // [kMaxTiles] (mean, rstd)
     float* cst = reinterpret_cast<float*>(smem + kTileBytes + kBarBytes + kStgBytes + kMaxTiles * 8);
-    for (int i = threadIdx.x; i < p.H; i += kThreads) {
+    for (int i = threadIdx.x; i < (kCstGlobal ? 0 : p.H); i += kThreads) {
         cst[i] = __ldg(p.gamma_in + i);
         cst[p.H + i] = __ldg(p.beta_in + i);
         cst[2 * p.H + i] = __ldg(p.wd + 3 * i);
@@ -313,7 +320,7 @@ dwpw_kernel(const __grid_constant__ CUtensorMap tm_w_hi, const __grid_constant__
                 // tensor stores, one per 16-frame run of a dilation phase.  Shared-memory stores release their
                 // operands at once; the register path's 256-bit global stores held theirs until the LSU had taken
                 // them, and the next TMEM load's write-after-read wait was the producers' largest single stall.
-                const uint32_t buf = ptx::smem_u32(stg_smem) + static_cast<uint32_t>(pw) * kStgWarp;
+                const uint32_t buf = ptx::smem_u32(stg_smem) + static_cast<uint32_t>(kCstGlobal ? as * 4 + ew : pw) * kStgWarp;
                 const uint32_t srow = buf + static_cast<uint32_t>(lane) * 128u;
                 const int ph_l = tile_phase(p, tt, sr), j_l = tile_j0(p, tt, sr);
                 const int ph1 = __shfl_sync(0xffffffffu, ph_l, 16), j1 = __shfl_sync(0xffffffffu, j_l, 16);
@@ -336,6 +343,9 @@ dwpw_kernel(const __grid_constant__ CUtensorMap tm_w_hi, const __grid_constant__
                         ptx::tma_store_commit();
                     }
                 }
+                // the buffer belongs to (TMEM stage, lane quarter): the warp that drains the stage next is another
+                // group's, and the release of the stage below is what orders its writes after these reads
+                if (kCstGlobal && lane == 0) ptx::tma_store_wait_read<0>();
             } else {
             // 16-column pieces in two alternating register sets: the TMEM load of piece h + 1 is in flight while
             // piece h is stored, and a set is reloaded only one piece after its stores were issued (the loads'
@@ -453,11 +463,24 @@ dwpw_kernel(const __grid_constant__ CUtensorMap tm_w_hi, const __grid_constant__
             // boundary units keep n1 = A pv + B explicit, because the zero padding applies to n1.
             f2_t A[2], Bc[2], w0[2], w1[2], w2[2];
             {
-                const float4 g = *reinterpret_cast<const float4*>(cst + c);
-                const float4 b = *reinterpret_cast<const float4*>(cst + p.H + c);
-                const float4 u0 = *reinterpret_cast<const float4*>(cst + 2 * p.H + c);
-                const float4 u1 = *reinterpret_cast<const float4*>(cst + 3 * p.H + c);
-                const float4 u2 = *reinterpret_cast<const float4*>(cst + 4 * p.H + c);
+                float4 g, b, u0, u1, u2;
+                if (kCstGlobal) {
+                    g = __ldg(reinterpret_cast<const float4*>(p.gamma_in + c));
+                    b = __ldg(reinterpret_cast<const float4*>(p.beta_in + c));
+                    // wd is [H, 3]: the taps of channels c .. c + 3 are twelve consecutive floats
+                    const float4 t0 = __ldg(reinterpret_cast<const float4*>(p.wd + 3 * c));
+                    const float4 t1 = __ldg(reinterpret_cast<const float4*>(p.wd + 3 * c + 4));
+                    const float4 t2 = __ldg(reinterpret_cast<const float4*>(p.wd + 3 * c + 8));
+                    u0 = make_float4(t0.x, t0.w, t1.z, t2.y);
+                    u1 = make_float4(t0.y, t1.x, t1.w, t2.z);
+                    u2 = make_float4(t0.z, t1.y, t2.x, t2.w);
+                } else {
+                    g = *reinterpret_cast<const float4*>(cst + c);
+                    b = *reinterpret_cast<const float4*>(cst + p.H + c);
+                    u0 = *reinterpret_cast<const float4*>(cst + 2 * p.H + c);
+                    u1 = *reinterpret_cast<const float4*>(cst + 3 * p.H + c);
+                    u2 = *reinterpret_cast<const float4*>(cst + 4 * p.H + c);
+                }
                 const float Af[4] = {g.x * rstd, g.y * rstd, g.z * rstd, g.w * rstd};
                 const float Bf[4] = {b.x - Af[0] * mean, b.y - Af[1] * mean, b.z - Af[2] * mean, b.w - Af[3] * mean};
                 // f[3 ch + t]: tap t of channel ch
@@ -649,7 +672,7 @@ extern "C" int ctn_dwpw_partials(int K, int dilation) {
 
 extern "C" int ctn_dwpw_supported(int H, int B, int P, int dilation, int norm) {
     return norm == CTN_NORM_GLN && P == 3 && B == fb::kBN && H % fb::kBK == 0 && H >= fb::kBK &&
-           fb::kSmemFixed + 20 * H <= fb::kSmemMax && dilation > 0 &&
+           fb::kSmemFixed + (fb::kCstGlobal ? 0 : 20 * H) <= fb::kSmemMax && dilation > 0 &&
            (dilation & (dilation - 1)) == 0;
 }
 
@@ -712,7 +735,7 @@ extern "C" int ctn_dwpw_fwd(const ctn_dwpw_args* args, void* stream_) {
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(2 * workers, 1, 1);
     cfg.blockDim = dim3(fb::kThreads, 1, 1);
-    cfg.dynamicSmemBytes = (fb::kSmemFixed + 20 * a.H);
+    cfg.dynamicSmemBytes = fb::kSmemFixed + (fb::kCstGlobal ? 0 : 20 * a.H);
     cfg.stream = stream;
     cudaLaunchAttribute attr[2];
     attr[0].id = cudaLaunchAttributeClusterDimension;

@@ -1,5 +1,12 @@
-timeout 900 python -m pytest tests/test_gpu_kernels.py tests/test_gpu_model.py tests/test_gpu_properties.py tests/test_gpu_train.py tests/test_gpu_bn.py -m gpu -x -q 2>&1 | tail -3
-python bench.py --steps 8 --warmup 3 --no-cpu 2>/dev/null | python -c "
+O=gpurun_out
+python -m pytest tests/test_gpu_train.py tests/test_gpu_kernels.py -q -m gpu -x 2>&1 | tail -4
+export CTN_ALLOW_EXPERIMENT_BUILD=1
+for r in 1 2; do
+for l in libctn_base.so libctn_b200.so; do
+echo "== $l run $r"; CTN_LIB_FILE=$l python bench.py --steps 4 --warmup 3 2>&1 | tail -1 | python -c "
 import json,sys
-d=json.loads(sys.stdin.read().strip().splitlines()[-1]); print(round(d['value']), round(d['e2e']['value']), d['clocks']['sm_mhz'], d['train_step']['ms_per_step'])
-for k,v in d['kernel_breakdown'].items(): print('   ',k,v['launches'],round(v['ms']*1e3/v['launches'],1),'us')"
+d=json.loads(sys.stdin.read()); t=d['train_step']
+print('fwd', round(d['value']), 'train ms', round(t['ms_per_step'],3), 'serial', round(t['serial_kernel_ms'],3))
+for k in t.get('all_kernels', t.get('kernels', []))[:12]: print('   ', k)
+"
+done; done
