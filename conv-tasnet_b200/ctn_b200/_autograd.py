@@ -117,7 +117,11 @@ class TrainPlan:
         self.dw_dec = e(Rr, N, **f32)
         self.g = e(Rr, B, **f32)
         self.g_hl = (e(Rr, B, **bf), e(Rr, B, **bf))
-        self.hl_H = (e(Rr, H, **bf), e(Rr, H, **bf))       # u (hi, lo), later da (hi, lo)
+        # The weight-gradient GEMMs and the per-block reduction run on a side stream, up to two blocks behind the
+        # dgrad chain (_launch_backward): what the chain writes and they read exists twice, by block parity.
+        self.g_hl = (self.g_hl, (e(Rr, B, **bf), e(Rr, B, **bf)))
+        self.hl_H = ((e(Rr, H, **bf), e(Rr, H, **bf)), (e(Rr, H, **bf), e(Rr, H, **bf)))   # da (hi, lo)
+        self.u_hl = (e(Rr, H, **bf), e(Rr, H, **bf))       # u (hi, lo): written and read on the side stream only
         self.du = e(Rr, H, **f32)
         self.dn1 = e(Rr, H, **f32)
         self.bstat = z(M if self.norm == nat.NORM_GLN else Rr, self.P1, 2, **f32)
@@ -129,10 +133,10 @@ class TrainPlan:
             lib.ctn_bwd_dw_layout(M, K, H, cfg["P"], 2 ** x, self.norm, C.byref(ctas), C.byref(rows))
             self.bd_ctas.append(ctas.value)
             self.bd_rows.append(rows.value)
-        self.chan_part = e(M * max(self.bd_rows), (4 + cfg["P"]) * H, **f32)
-        self.scal_part = e(M * max(self.bd_ctas), 4, **f32)
+        self.chan_part = [e(M * max(self.bd_rows), (4 + cfg["P"]) * H, **f32) for _ in range(2)]
+        self.scal_part = [e(M * max(self.bd_ctas), 4, **f32) for _ in range(2)]
         self.tiles_pn = lib.ctn_bwd_prelu_norm_tiles(K)
-        self.alpha_part = e(M * self.tiles_pn, **f32)
+        self.alpha_part = [e(M * self.tiles_pn, **f32) for _ in range(2)]
         self.tiles_db = lib.ctn_decoder_bwd_tiles(K)
         self.dV_part = e(M * self.tiles_db, L * N, **f32)
         self.tiles_cb = lib.ctn_cln_bwd_tiles(K)
@@ -450,12 +454,22 @@ class TrainPlan:
             (self.dV_part, M * self.tiles_db, L * N, 0, L * N, 1, self.grad_ptr("decoder.basis_signals.weight"), 1),
             seg_mask]))
         bwd.append(tag(self._gemm(Cin=C_ * N, Cout=B, a_hi=self.ds_hl[0], a_lo=self.ds_hl[1], w_hi=prep_b.mask_t[0],
-                                  w_lo=prep_b.mask_t[1], out_f32=self.g, out_hi=self.g_hl[0], out_lo=self.g_hl[1]),
+                                  w_lo=prep_b.mask_t[1], out_f32=self.g, out_hi=self.g_hl[0][0], out_lo=self.g_hl[0][1]),
                        "bwd_gemm_mask_dgrad", 2.0 * Rr * B * C_ * N, Rr * (4.0 * C_ * N + 8.0 * B)))
         ns, bd, pn = lib.ctn_norm_split, lib.ctn_bwd_dwconv, lib.ctn_bwd_prelu_norm
         pn_cln = lib.ctn_bwd_prelu_norm_cln
-        for (i, xb, k) in reversed(blocks):
+        # Side-stream schedule (see _launch_backward).  Block number j of the backward, parity p = j & 1:
+        #   side: u = norm_split(d) -> dW2 = g^T u  [mark w2:j] ... dW1 = da^T x -> reduction of the block  [mark blk:j]
+        #   main: dgrad (du = g W2) -> [wait blk:j-2] depthwise backward -> prelu/norm backward (da) -> [wait w2:j-1]
+        #         dgrad (g' = da W1 + g)
+        # g (hi, lo) alternates between two pairs (dW2 of block j reads the pair that block j+1's last GEMM rewrites),
+        # da and the partial buffers of the main-stream kernels likewise; u and the GEMM partials are touched by the
+        # side stream only.
+        for j, (i, xb, k) in enumerate(reversed(blocks)):
             pb = prep_b.blocks[i]
+            par = j & 1
+            g_in, g_out, da_hl = self.g_hl[par], self.g_hl[par ^ 1], self.hl_H[par]
+            chan_part, scal_part, alpha_part = self.chan_part[par], self.scal_part[par], self.alpha_part[par]
             P2 = 1 if bn else self.P2s[xb]
             if bn:      # the kernels' (gamma, beta) = the folded BatchNorm affine; statistics = unit
                 aff1, aff2 = self.bn_aff[i]
@@ -466,26 +480,25 @@ class TrainPlan:
                 st1_, st2_, P1_ = self.stat1[i], self.stat2[i], self.P1
             a_ = (self.d[i].data_ptr(), params[k["a2"]].data_ptr(), g2_.data_ptr(),
                   b2_.data_ptr(), GLN, st2_.data_ptr(), P2, M, K, H,
-                  self.hl_H[0].data_ptr(), self.hl_H[1].data_ptr())
-            bwd.append(_JOIN)     # the previous block's weight gradients read hl_H and the partial buffers
-            # u is read by the weight-gradient GEMM only, so it is formed on the side stream as well: the fork
-            # orders it behind the previous block's last dgrad GEMM, which reads hl_H (as da)
-            call, seg_w2 = self._wgrad(self.g_hl, self.hl_H, B, H, k["w2"])              # dW2 = g^T u
-            bwd.append(_FORK)
+                  self.u_hl[0].data_ptr(), self.u_hl[1].data_ptr())
+            call, seg_w2 = self._wgrad(g_in, self.u_hl, B, H, k["w2"])              # dW2 = g^T u
+            bwd.append(_FORK)     # g (hi, lo) of this block is complete
             bwd.append((_SIDE, tag(lambda s, a=a_: ns(*a, s), "bwd_norm_split", 4.0 * Rr * H, 8.0 * Rr * H)))   # u (hi, lo)
             bwd.append((_SIDE, call))
+            bwd.append(_Mark("w2:%d" % j))
             if bn:
-                bwd.append(tag(self._gemm(Cin=B, Cout=H, a_hi=self.g_hl[0], a_lo=self.g_hl[1], w_hi=pb["w2t"][0],
+                bwd.append(tag(self._gemm(Cin=B, Cout=H, a_hi=g_in[0], a_lo=g_in[1], w_hi=pb["w2t"][0],
                                           w_lo=pb["w2t"][1], out_f32=self.du),            # du = g W2
                                "bwd_gemm_dgrad_pointwise", 2.0 * Rr * B * H, Rr * (4.0 * B + 4.0 * H)))
                 bwd.extend(self._bn_backward_norm(self.du, self.d[i], params[k["a2"]], aff2, bn_count, use_running,
                                                   k["g2"], k["b2"]))
             else:
-                bwd.append(tag(self._gemm(Cin=B, Cout=H, a_hi=self.g_hl[0], a_lo=self.g_hl[1], w_hi=pb["w2t"][0],
+                bwd.append(tag(self._gemm(Cin=B, Cout=H, a_hi=g_in[0], a_lo=g_in[1], w_hi=pb["w2t"][0],
                                           w_lo=pb["w2t"][1], out_f32=self.du, out_stat=GLN, out_stat_buf=self.bstat,
                                           bw_pre=self.d[i], bw_gamma=params[k["g2"]], bw_slope=params[k["a2"]],
                                           bw_stat=self.stat2[i], bw_P=P2),                    # du = g W2 (+ S1, S2)
                                "bwd_gemm_dgrad_pointwise", 2.0 * Rr * B * H, Rr * (4.0 * B + 8.0 * H)))
+            bwd.append(_Wait("blk:%d" % (j - 2)))   # its dW1 read this parity's da, its reduction this parity's partials
             b = nat.BwdDwArgs()
             b.M, b.K, b.H, b.P, b.dilation, b.causal = M, K, H, P, 2 ** xb, causal
             b.P1, b.P2, b.Pb = P1_, P2, (1 if bn else self.P1)
@@ -494,55 +507,57 @@ class TrainPlan:
             b.bstat = self.zero_stat.data_ptr() if bn else self.bstat.data_ptr()
             b.g1, b.b1, b.g2 = g1_.data_ptr(), b1_.data_ptr(), g2_.data_ptr()
             b.wd, b.slope1, b.slope2 = params[k["wd"]].data_ptr(), params[k["a1"]].data_ptr(), params[k["a2"]].data_ptr()
-            b.dn1, b.chan_part, b.scal_part = self.dn1.data_ptr(), self.chan_part.data_ptr(), self.scal_part.data_ptr()
+            b.dn1, b.chan_part, b.scal_part = self.dn1.data_ptr(), chan_part.data_ptr(), scal_part.data_ptr()
             b.norm = self.norm
             self._keep.append(b)
             bwd.append(tag(lambda s, ref=C.byref(b): bd(ref, s), "bwd_dwconv", 4.0 * Rr * H * P, 16.0 * Rr * H))
-            bwd.append(_JOIN)     # dW2 has consumed u before da overwrites hl_H
             if bn:
                 bwd.extend(self._bn_backward_norm(self.dn1, self.a[i], params[k["a1"]], aff1, bn_count, use_running,
                                                   k["g1"], k["b1"]))
             if is_gln:
                 a_ = (self.dn1.data_ptr(), self.a[i].data_ptr(), st1_.data_ptr(), P1_,
-                      (self.zero_scal if bn else self.scal_part).data_ptr(), self.bd_ctas[xb], g1_.data_ptr(),
-                      params[k["a1"]].data_ptr(), M, K, H, self.hl_H[0].data_ptr(), self.hl_H[1].data_ptr(),
-                      self.alpha_part.data_ptr())
+                      (self.zero_scal if bn else scal_part).data_ptr(), self.bd_ctas[xb], g1_.data_ptr(),
+                      params[k["a1"]].data_ptr(), M, K, H, da_hl[0].data_ptr(), da_hl[1].data_ptr(),
+                      alpha_part.data_ptr())
                 bwd.append(tag(lambda s, a=a_: pn(*a, s), "bwd_prelu_norm", 6.0 * Rr * H, 12.0 * Rr * H))   # da (hi, lo)
             else:
                 a_ = (self.dn1.data_ptr(), self.a[i].data_ptr(), self.stat1[i].data_ptr(), self.P1,
                       params[k["g1"]].data_ptr(), params[k["a1"]].data_ptr(), M, K, H,
-                      self.hl_H[0].data_ptr(), self.hl_H[1].data_ptr(), self.alpha_part.data_ptr())
+                      da_hl[0].data_ptr(), da_hl[1].data_ptr(), alpha_part.data_ptr())
                 bwd.append(tag(lambda s, a=a_: pn_cln(*a, s), "bwd_prelu_norm", 6.0 * Rr * H, 12.0 * Rr * H))
-            call, seg_w1 = self._wgrad(self.hl_H, self.x_hl[i], H, B, k["w1"], self.wg_part2)   # dW1 = da^T x
+            call, seg_w1 = self._wgrad(da_hl, self.x_hl[i], H, B, k["w1"], self.wg_part2)   # dW1 = da^T x
             bwd.append(_FORK)
             bwd.append((_SIDE, call))
             # every parameter gradient of the block in ONE reduction launch
-            cp, cn, cs = self.chan_part, M * self.bd_rows[xb], (4 + P) * H
+            cp, cn, cs = chan_part, M * self.bd_rows[xb], (4 + P) * H
             # (BatchNorm: d weight / d bias of both norms come from ctn_bn_bwd_center, not from chan_part)
             segs = [] if bn else [
                 (cp, cn, cs, 0, H, 1, self.grad_ptr(k["g2"]), 1), (cp, cn, cs, H, H, 1, self.grad_ptr(k["b2"]), 1),
                 (cp, cn, cs, 2 * H, H, 1, self.grad_ptr(k["g1"]), 1),
                 (cp, cn, cs, 3 * H, H, 1, self.grad_ptr(k["b1"]), 1)]
-            segs += [(cp, cn, cs, (4 + j) * H, H, 1, self.grad_ptr(k["wd"]) + 4 * j, P) for j in range(P)]
-            segs.append((self.scal_part, M * self.bd_ctas[xb], 4, 2, 1, 1, self.grad_ptr(k["a2"]), 1))
-            segs.append((self.alpha_part, M * self.tiles_pn, 1, 0, 1, 1, self.grad_ptr(k["a1"]), 1))
+            segs += [(cp, cn, cs, (4 + jj) * H, H, 1, self.grad_ptr(k["wd"]) + 4 * jj, P) for jj in range(P)]
+            segs.append((scal_part, M * self.bd_ctas[xb], 4, 2, 1, 1, self.grad_ptr(k["a2"]), 1))
+            segs.append((alpha_part, M * self.tiles_pn, 1, 0, 1, 1, self.grad_ptr(k["a1"]), 1))
             if len(segs) + 2 <= nat.MAX_SEG:
                 bwd.append((_SIDE, self._reduce_multi(segs + [seg_w2, seg_w1])))
             else:                                   # P > 3
                 bwd.append((_SIDE, self._reduce_multi(segs[:nat.MAX_SEG])))
                 bwd.append((_SIDE, self._reduce_multi(segs[nat.MAX_SEG:] + [seg_w2, seg_w1])))
-            bwd.append(tag(self._gemm(Cin=H, Cout=B, a_hi=self.hl_H[0], a_lo=self.hl_H[1], w_hi=pb["w1t"][0],
-                                      w_lo=pb["w1t"][1], resid=self.g, out_f32=self.g, out_hi=self.g_hl[0],
-                                      out_lo=self.g_hl[1]),                               # g = da W1 + g
+            bwd.append(_Mark("blk:%d" % j))
+            bwd.append(_Wait("w2:%d" % (j - 1)))    # it read the pair that is rewritten now
+            bwd.append(tag(self._gemm(Cin=H, Cout=B, a_hi=da_hl[0], a_lo=da_hl[1], w_hi=pb["w1t"][0],
+                                      w_lo=pb["w1t"][1], resid=self.g, out_f32=self.g, out_hi=g_out[0],
+                                      out_lo=g_out[1]),                               # g = da W1 + g
                            "bwd_gemm_dgrad_conv1x1", 2.0 * Rr * B * H, Rr * (4.0 * H + 12.0 * B)))
+        g_fin = self.g_hl[len(blocks) & 1]
         # bottleneck + leading cLN + encoder
         bwd.append(_JOIN)
         a_ = (self.w.data_ptr(), None, g0.data_ptr(), b0.data_ptr(), nat.NORM_CLN, self.rowstat0.data_ptr(), 1,
               M, K, N, self.w_hl[0].data_ptr(), self.w_hl[1].data_ptr())
         bwd.append(tag(lambda s, a=a_: ns(*a, s), "bwd_norm_split", 4.0 * Rr * N, 8.0 * Rr * N))   # n0 (hi, lo) over w_hl
-        call, seg_wb = self._wgrad(self.g_hl, self.w_hl, B, N, "separator.network.1.weight")
+        call, seg_wb = self._wgrad(g_fin, self.w_hl, B, N, "separator.network.1.weight")
         bwd.append(call)
-        bwd.append(tag(self._gemm(Cin=B, Cout=N, a_hi=self.g_hl[0], a_lo=self.g_hl[1], w_hi=prep_b.bott_t[0],
+        bwd.append(tag(self._gemm(Cin=B, Cout=N, a_hi=g_fin[0], a_lo=g_fin[1], w_hi=prep_b.bott_t[0],
                                   w_lo=prep_b.bott_t[1], out_f32=self.dn0),
                        "bwd_gemm_dgrad_bottleneck", 2.0 * Rr * B * N, Rr * (4.0 * B + 4.0 * N)))
         cb = lib.ctn_cln_bwd
@@ -578,7 +593,7 @@ class TrainPlan:
         check(lib.ctn_decoder_bwd(self.g_est.data_ptr(), *self.dec_bwd_args, s))
         if not self.overlap:
             for c in self.bwd_calls:
-                if c is _FORK or c is _JOIN:
+                if _is_marker(c):
                     continue
                 check((c[1] if isinstance(c, tuple) else c)(s))
             return
@@ -586,6 +601,7 @@ class TrainPlan:
         side = self.side_stream
         side_ptr = side.cuda_stream
         pending = False     # side work issued since the last join
+        marks = {}          # name -> event recorded on the side stream
         for c in self.bwd_calls:
             if c is _FORK:
                 ev = torch.cuda.Event()
@@ -597,6 +613,15 @@ class TrainPlan:
                     ev.record(side)
                     main.wait_event(ev)
                     pending = False
+                marks.clear()
+            elif isinstance(c, _Mark):
+                ev = torch.cuda.Event()
+                ev.record(side)
+                marks[c.name] = ev
+            elif isinstance(c, _Wait):
+                ev = marks.pop(c.name, None)
+                if ev is not None:
+                    main.wait_event(ev)
             elif isinstance(c, tuple):
                 check(c[1](side_ptr))
                 pending = True
@@ -618,7 +643,7 @@ class TrainPlan:
         seq.append((lambda st: lib.ctn_decoder_fwd(*self.dec_args, self.est.data_ptr(), st), dec_meta))
         seq.append((lambda st: lib.ctn_decoder_bwd(self.est.data_ptr(), *self.dec_bwd_args, st), decb_meta))
         for c in self.bwd_calls:
-            if c is _FORK or c is _JOIN:
+            if _is_marker(c):
                 continue
             c = c[1] if isinstance(c, tuple) else c
             seq.append((c, self.meta.get(c, ("other", 0.0, 0.0))))
@@ -662,10 +687,24 @@ class TrainPlan:
             if self.bwd_graph is None:
                 self.bwd_graph = self._capture(self._launch_backward)
             self.bwd_graph.replay()
-        return sum(1 for c in self.bwd_calls if c is not _FORK and c is not _JOIN) + 1
+        return sum(1 for c in self.bwd_calls if not _is_marker(c)) + 1
 
 
 _FORK, _JOIN, _SIDE = "fork", "join", "side"   # markers in TrainPlan.bwd_calls
+
+
+class _Mark:
+    """bwd_calls marker: the side stream has finished everything issued to it so far (named)."""
+    def __init__(self, name):
+        self.name = name
+
+
+class _Wait(_Mark):
+    """bwd_calls marker: the main stream waits for the _Mark of that name (no-op if there is none)."""
+
+
+def _is_marker(c):
+    return c is _FORK or c is _JOIN or isinstance(c, _Mark)
 
 
 class TrainEngine:

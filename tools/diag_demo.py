@@ -60,7 +60,7 @@ print("dscore", rel_l2(hl(plan.ds_hl), fm(keep["score"].grad)))
 print("g (d x_blk+1 if STOP else x0)", rel_l2(plan.g, fm(keep["x%d" % (BLK + 1 if STOP >= 0 else 0)].grad)))
 print("du block0", rel_l2(plan.du, fm(keep["u%d" % BLK].grad)))
 print("dn1 block0", rel_l2(plan.dn1, fm(keep["n1_%d" % BLK].grad)))
-print("da block0 (hl_H)", rel_l2(hl(plan.hl_H), fm(keep["a%d" % BLK].grad)))
+print("da block0 (hl_H)", rel_l2(hl(plan.hl_H[(len(plan.a) - 1 - BLK) & 1]), fm(keep["a%d" % BLK].grad)))
 print("dn0", rel_l2(plan.dn0, fm(keep["n0"].grad)))
 print("fwd a", rel_l2(plan.a[BLK], fm(keep["a%d" % BLK])), "d", rel_l2(plan.d[BLK], fm(keep["d%d" % BLK])))
 print("du ours", plan.du.tolist()); print("du ref", fm(keep["u%d" % BLK].grad).tolist())
