@@ -805,6 +805,8 @@ extern "C" int ctn_norm_split(const float* in, const float* prelu_slope, const f
 
 static bool bwd_use_march(int H, int P, int norm) { return P == 3 && H % 4 == 0 && norm != CTN_NORM_CLN; }
 
+extern "C" int ctn_bwd_dw_emits_u(int H, int P, int norm) { return bwd_use_march(H, P, norm) ? 1 : 0; }
+
 extern "C" int ctn_bwd_dw_layout(int M, int K, int H, int P, int dilation, int norm, int* ctas, int* chan_rows) {
     if (bwd_use_march(H, P, norm) && dilation > 0) {
         int NS, units, groups, n_ctas;
@@ -847,18 +849,20 @@ extern "C" int ctn_bwd_dwconv(const ctn_bwd_dw_args* args, void* stream) {
         q.g1 = a.g1, q.b1 = a.b1, q.g2 = a.g2, q.wd = a.wd, q.slope1 = a.slope1, q.slope2 = a.slope2;
         q.dn1 = a.dn1, q.chan_part = a.chan_part, q.scal_part = a.scal_part;
         dim3 grid(q.ctas, a.M);
-        static const bool attr_ok = [] {
-            return cudaFuncSetAttribute(bwd_dw_march_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, kBmSmemBytes) == cudaSuccess &&
-                   cudaFuncSetAttribute(bwd_dw_march_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, kBmSmemBytes) == cudaSuccess;
-        }();
-        CTN_REQUIRE(attr_ok, "ctn_bwd_dwconv: cannot reserve the row ring in shared memory");
-        if (a.causal)
-            bwd_dw_march_kernel<2><<<grid, kBmWarps * 32, kBmSmemBytes, static_cast<cudaStream_t>(stream)>>>(q);
-        else
-            bwd_dw_march_kernel<1><<<grid, kBmWarps * 32, kBmSmemBytes, static_cast<cudaStream_t>(stream)>>>(q);
+        const bool emit_u = a.u_hi != nullptr;
+        CTN_REQUIRE(!emit_u || (a.u_lo && a.b2 && al16(a.u_hi) && al16(a.u_lo) && al16(a.b2)),
+                    "ctn_bwd_dwconv: u_hi, u_lo and b2 go together, 16-byte aligned");
+        q.b2 = a.b2, q.u_hi = static_cast<__nv_bfloat16*>(a.u_hi), q.u_lo = static_cast<__nv_bfloat16*>(a.u_lo);
+        void (*kern)(const BwdMarchParams) =
+            a.causal ? (emit_u ? bwd_dw_march_kernel<2, true> : bwd_dw_march_kernel<2, false>)
+                     : (emit_u ? bwd_dw_march_kernel<1, true> : bwd_dw_march_kernel<1, false>);
+        CTN_REQUIRE(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kBmSmemBytes) == cudaSuccess,
+                    "ctn_bwd_dwconv: cannot reserve the row ring in shared memory");
+        kern<<<grid, kBmWarps * 32, kBmSmemBytes, static_cast<cudaStream_t>(stream)>>>(q);
         CTN_LAUNCH_CHECK("bwd_dw_march_kernel");
         return CTN_OK;
     }
+    CTN_REQUIRE(a.u_hi == nullptr && a.u_lo == nullptr, "ctn_bwd_dwconv: u is not written for this shape / norm (ctn_bwd_dw_emits_u)");
     BwdDwParams p;
     p.K = a.K, p.H = a.H, p.P = a.P, p.dil = a.dilation, p.causal = a.causal;
     p.P1 = a.P1, p.P2 = a.P2, p.Pb = a.Pb, p.cln = a.norm == CTN_NORM_CLN;

@@ -65,6 +65,9 @@ struct BwdMarchParams {
     float* dn1;
     float* chan_part;   // [M * chan_rows][7 * H]: dg2, db2, dg1, db1, dwd[0..3)
     float* scal_part;   // [M * ctas][4]: S1', S2', d a2, 0
+    const float* b2;    // EMIT_U: u = g2 qh + b2 as bf16 (hi, lo), rows of the unit's centre only
+    __nv_bfloat16* u_hi;
+    __nv_bfloat16* u_lo;
 };
 
 // units per utterance, warp groups (= partial rows) per utterance, CTAs per utterance
@@ -96,7 +99,7 @@ __device__ __forceinline__ void block_sum2_double(double& s, double& ss, double*
     __syncthreads();   // red may be reused
 }
 
-template <int C0>
+template <int C0, bool EMIT_U>
 __global__ void __launch_bounds__(kBmWarps * 32, kBmCtasPerSm)
 bwd_dw_march_kernel(const BwdMarchParams p) {
     __shared__ double fin_s[6 * kBmWarps];
@@ -174,6 +177,11 @@ bwd_dw_march_kernel(const BwdMarchParams p) {
         const f2_t r2p = f2_pack(r2, r2), nmu2r2 = f2_pack(-mu2 * r2, -mu2 * r2);
         const f2_t nm1r2 = f2_pack(-m1 * r2, -m1 * r2), nm2r2 = f2_pack(-m2 * r2, -m2 * r2);
         f2_t g1p[2], b1p[2], g2p[2], w0[2], w1[2], w2[2];
+        f2_t b2p[2] = {zero, zero};
+        if (EMIT_U) {
+            const float4 b2v = *reinterpret_cast<const float4*>(p.b2 + c);
+            b2p[0] = f2_pack(b2v.x, b2v.y), b2p[1] = f2_pack(b2v.z, b2v.w);
+        }
         {
             const float4 g1v = *reinterpret_cast<const float4*>(p.g1 + c);
             const float4 b1v = *reinterpret_cast<const float4*>(p.b1 + c);
@@ -241,6 +249,7 @@ bwd_dw_march_kernel(const BwdMarchParams p) {
                             const f2_t d2[2] = {f2_pack(vd.x, vd.y), f2_pack(vd.z, vd.w)};
                             const f2_t a2v[2] = {f2_pack(va.x, va.y), f2_pack(va.z, va.w)};
                             const float dsc[4] = {vd.x, vd.y, vd.z, vd.w};
+                            uint32_t uh[2], ul[2];
 #pragma unroll
                             for (int i = 0; i < 2; ++i) {
                                 f2_t mx, mn;
@@ -253,6 +262,11 @@ bwd_dw_march_kernel(const BwdMarchParams p) {
                                     dg2[i] = f2_fma(du2[i], qh, dg2[i]);
                                     db2[i] = f2_add(db2[i], du2[i]);
                                     sA2[i] = f2_fma(dq, mn, sA2[i]);
+                                    if (EMIT_U) {
+                                        float u0, u1;
+                                        f2_unpack(f2_fma(g2p[i], qh, b2p[i]), u0, u1);
+                                        split_pack2(u0, u1, uh[i], ul[i]);
+                                    }
                                 }
                                 const f2_t fac = f2_pack(dsc[2 * i] > 0.f ? 1.f : al2, dsc[2 * i + 1] > 0.f ? 1.f : al2);
                                 dd2[i] = f2_mul(dq, fac);
@@ -261,6 +275,11 @@ bwd_dw_march_kernel(const BwdMarchParams p) {
                                 const f2_t pa = f2_fma(a1p, amn, amx);
                                 h2[i] = f2_fma(pa, r1p, nmu1r1);
                                 n2[i] = f2_fma(g1p[i], h2[i], b1p[i]);
+                            }
+                            if (EMIT_U && centre) {
+                                const long long o = off0 + s * strd;
+                                *reinterpret_cast<uint2*>(p.u_hi + o) = make_uint2(uh[0], uh[1]);
+                                *reinterpret_cast<uint2*>(p.u_lo + o) = make_uint2(ul[0], ul[1]);
                             }
                         } else {
                             dd2[0] = zero, dd2[1] = zero, n2[0] = zero, n2[1] = zero, h2[0] = zero, h2[1] = zero;

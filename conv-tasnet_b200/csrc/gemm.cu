@@ -876,7 +876,13 @@ extern "C" int ctn_gemm1x1(const ctn_gemm_args* args, void* stream_) {
         // 256-wide tiles halve the re-reads of the activation tile but need enough tiles to fill the SMs
         const long long tiles256 = static_cast<long long>(a.M) * ep.tiles_per_utt * ceil_div(a.Cout, 256);
         const int mode = a.force_simt >> 1;   // test hook: 1 = single-CTA kernels only, 2 = pair kernel
-        const bool pair = a.Cout % 256 == 0 && mode != 1 && (mode == 2 || tiles256 >= 2ll * sm_count());
+        // ... or few enough that every CTA pair gets at most one 256 x 256 item where 128 x 128 tiles would need a
+        // second round for a handful of tiles (the reference's batch of 3 x 4 s: 150 tiles of a 256-column output
+        // for 148 SMs; training step 3.92 -> 3.83 ms backward)
+        const long long row_tiles_ = static_cast<long long>(a.M) * ep.tiles_per_utt;
+        const bool one_round = (row_tiles_ + 1) / 2 * ceil_div(a.Cout, 256) <= sm_count() / 2 &&
+                               row_tiles_ * ceil_div(a.Cout, 128) > sm_count();
+        const bool pair = a.Cout % 256 == 0 && mode != 1 && (mode == 2 || tiles256 >= 2ll * sm_count() || one_round);
         const bool affine = a.col_g != nullptr || a.col_bias != nullptr || a.in_norm != CTN_NORM_NONE ||
                             a.resid != nullptr || a.resid_hi != nullptr;
         if (a.bw_pre != nullptr)

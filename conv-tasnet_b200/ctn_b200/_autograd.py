@@ -121,7 +121,10 @@ class TrainPlan:
         # dgrad chain (_launch_backward): what the chain writes and they read exists twice, by block parity.
         self.g_hl = (self.g_hl, (e(Rr, B, **bf), e(Rr, B, **bf)))
         self.hl_H = ((e(Rr, H, **bf), e(Rr, H, **bf)), (e(Rr, H, **bf), e(Rr, H, **bf)))   # da (hi, lo)
-        self.u_hl = (e(Rr, H, **bf), e(Rr, H, **bf))       # u (hi, lo): written and read on the side stream only
+        # u (hi, lo), the operand of dW2: written by the depthwise backward where it can (emit_u), else by
+        # ctn_norm_split on the side stream
+        self.emit_u = bool(lib.ctn_bwd_dw_emits_u(H, cfg["P"], self.norm))
+        self.u_hl = [(e(Rr, H, **bf), e(Rr, H, **bf)) for _ in range(2 if self.emit_u else 1)]
         self.du = e(Rr, H, **f32)
         self.dn1 = e(Rr, H, **f32)
         self.bstat = z(M if self.norm == nat.NORM_GLN else Rr, self.P1, 2, **f32)
@@ -459,12 +462,12 @@ class TrainPlan:
         ns, bd, pn = lib.ctn_norm_split, lib.ctn_bwd_dwconv, lib.ctn_bwd_prelu_norm
         pn_cln = lib.ctn_bwd_prelu_norm_cln
         # Side-stream schedule (see _launch_backward).  Block number j of the backward, parity p = j & 1:
-        #   side: u = norm_split(d) -> dW2 = g^T u  [mark w2:j] ... dW1 = da^T x -> reduction of the block  [mark blk:j]
-        #   main: dgrad (du = g W2) -> [wait blk:j-2] depthwise backward -> prelu/norm backward (da) -> [wait w2:j-1]
-        #         dgrad (g' = da W1 + g)
+        #   main: dgrad (du = g W2) -> [wait blk:j-2] depthwise backward (also writes u) -> prelu/norm backward (da)
+        #         -> [wait w2:j-1] dgrad (g' = da W1 + g)
+        #   side, forked behind da: dW2 = g^T u  [mark w2:j] -> dW1 = da^T x -> reduction of the block  [mark blk:j]
         # g (hi, lo) alternates between two pairs (dW2 of block j reads the pair that block j+1's last GEMM rewrites),
-        # da and the partial buffers of the main-stream kernels likewise; u and the GEMM partials are touched by the
-        # side stream only.
+        # u, da and the partial buffers of the main-stream kernels likewise; the GEMM partials are touched by the side
+        # stream only.  (cLN, P != 3: u comes from ctn_norm_split on the side stream, forked at the top of the block.)
         for j, (i, xb, k) in enumerate(reversed(blocks)):
             pb = prep_b.blocks[i]
             par = j & 1
@@ -478,14 +481,15 @@ class TrainPlan:
             else:
                 g1_, b1_, g2_, b2_ = params[k["g1"]], params[k["b1"]], params[k["g2"]], params[k["b2"]]
                 st1_, st2_, P1_ = self.stat1[i], self.stat2[i], self.P1
-            a_ = (self.d[i].data_ptr(), params[k["a2"]].data_ptr(), g2_.data_ptr(),
-                  b2_.data_ptr(), GLN, st2_.data_ptr(), P2, M, K, H,
-                  self.u_hl[0].data_ptr(), self.u_hl[1].data_ptr())
-            call, seg_w2 = self._wgrad(g_in, self.u_hl, B, H, k["w2"])              # dW2 = g^T u
-            bwd.append(_FORK)     # g (hi, lo) of this block is complete
-            bwd.append((_SIDE, tag(lambda s, a=a_: ns(*a, s), "bwd_norm_split", 4.0 * Rr * H, 8.0 * Rr * H)))   # u (hi, lo)
-            bwd.append((_SIDE, call))
-            bwd.append(_Mark("w2:%d" % j))
+            u_hl = self.u_hl[par if self.emit_u else 0]
+            call_w2, seg_w2 = self._wgrad(g_in, u_hl, B, H, k["w2"])              # dW2 = g^T u
+            if not self.emit_u:
+                a_ = (self.d[i].data_ptr(), params[k["a2"]].data_ptr(), g2_.data_ptr(),
+                      b2_.data_ptr(), GLN, st2_.data_ptr(), P2, M, K, H, u_hl[0].data_ptr(), u_hl[1].data_ptr())
+                bwd.append(_FORK)     # g (hi, lo) of this block is complete
+                bwd.append((_SIDE, tag(lambda s, a=a_: ns(*a, s), "bwd_norm_split", 4.0 * Rr * H, 8.0 * Rr * H)))   # u (hi, lo)
+                bwd.append((_SIDE, call_w2))
+                bwd.append(_Mark("w2:%d" % j))
             if bn:
                 bwd.append(tag(self._gemm(Cin=B, Cout=H, a_hi=g_in[0], a_lo=g_in[1], w_hi=pb["w2t"][0],
                                           w_lo=pb["w2t"][1], out_f32=self.du),            # du = g W2
@@ -509,8 +513,11 @@ class TrainPlan:
             b.wd, b.slope1, b.slope2 = params[k["wd"]].data_ptr(), params[k["a1"]].data_ptr(), params[k["a2"]].data_ptr()
             b.dn1, b.chan_part, b.scal_part = self.dn1.data_ptr(), chan_part.data_ptr(), scal_part.data_ptr()
             b.norm = self.norm
+            if self.emit_u:     # u of this parity was last read by dW2 two blocks ago: behind the wait above
+                b.b2, b.u_hi, b.u_lo = b2_.data_ptr(), u_hl[0].data_ptr(), u_hl[1].data_ptr()
             self._keep.append(b)
-            bwd.append(tag(lambda s, ref=C.byref(b): bd(ref, s), "bwd_dwconv", 4.0 * Rr * H * P, 16.0 * Rr * H))
+            bwd.append(tag(lambda s, ref=C.byref(b): bd(ref, s), "bwd_dwconv", 4.0 * Rr * H * P,
+                           (20.0 if self.emit_u else 16.0) * Rr * H))
             if bn:
                 bwd.extend(self._bn_backward_norm(self.dn1, self.a[i], params[k["a1"]], aff1, bn_count, use_running,
                                                   k["g1"], k["b1"]))
@@ -527,6 +534,9 @@ class TrainPlan:
                 bwd.append(tag(lambda s, a=a_: pn_cln(*a, s), "bwd_prelu_norm", 6.0 * Rr * H, 12.0 * Rr * H))
             call, seg_w1 = self._wgrad(da_hl, self.x_hl[i], H, B, k["w1"], self.wg_part2)   # dW1 = da^T x
             bwd.append(_FORK)
+            if self.emit_u:
+                bwd.append((_SIDE, call_w2))
+                bwd.append(_Mark("w2:%d" % j))
             bwd.append((_SIDE, call))
             # every parameter gradient of the block in ONE reduction launch
             cp, cn, cs = chan_part, M * self.bd_rows[xb], (4 + P) * H

@@ -90,6 +90,7 @@ class BwdDwArgs(C.Structure):
         ("du", _vp), ("d", _vp), ("a", _vp), ("stat1", _vp), ("stat2", _vp), ("bstat", _vp),
         ("g1", _vp), ("b1", _vp), ("g2", _vp), ("wd", _vp), ("slope1", _vp), ("slope2", _vp),
         ("dn1", _vp), ("chan_part", _vp), ("scal_part", _vp), ("norm", C.c_int),
+        ("b2", _vp), ("u_hi", _vp), ("u_lo", _vp),
     ]
 
 
@@ -195,6 +196,7 @@ _SIGNATURES = {
     "ctn_wgrad": (_i, [_vp, _vp, _vp, _vp, _ll, _i, _i, _vp, _i, _vp]),
     "ctn_bwd_dw_layout": (_i, [_i, _i, _i, _i, _i, _i, C.POINTER(_i), C.POINTER(_i)]),
     "ctn_bwd_dwconv": (_i, [C.POINTER(BwdDwArgs), _vp]),
+    "ctn_bwd_dw_emits_u": (_i, [_i, _i, _i]),
     "ctn_bwd_prelu_norm_tiles": (_i, [_i]),
     "ctn_bwd_prelu_norm": (_i, [_vp, _vp, _vp, _i, _vp, _i, _vp, _vp, _i, _i, _i, _vp, _vp, _vp, _vp]),
     "ctn_bwd_prelu_norm_cln": (_i, [_vp, _vp, _vp, _i, _vp, _vp, _i, _i, _i, _vp, _vp, _vp, _vp]),
@@ -282,7 +284,10 @@ def capture_stream(device):
     process that drives several (torch.nn.DataParallel)."""
     st = _capture_streams.get(device.index)
     if st is None:
-        st = _capture_streams[device.index] = torch.cuda.Stream(device=device)
+        # high priority: kernel nodes inherit it, so in a captured training backward the dgrad chain's CTAs are placed
+        # before those of the weight-gradient kernels that share the graph from a default-priority side stream
+        # (backward 3.89 -> 3.61 ms at batch 3)
+        st = _capture_streams[device.index] = torch.cuda.Stream(device=device, priority=-1)
     return st
 
 

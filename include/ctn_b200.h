@@ -284,6 +284,12 @@ typedef struct ctn_bwd_dw_args {
     int norm;              /* CTN_NORM_GLN (0 is read as gLN) or CTN_NORM_CLN.  cLN: stat1 / bstat are
                             * per-frame column-group partials [M*K, P1] / [M*K, Pb], stat2 is the
                             * per-frame (mean, rstd) [M*K]; scal_part[.][0..1] are not produced          */
+    /* Optional: u = g2 * qh + b2 (the pointwise convolution's input, the operand of dW2 = g^T u) as bf16
+     * (hi, lo) [M*K, H] -- what ctn_norm_split makes of d -- written while d is in registers anyway.  All three
+     * NULL: not written.  Only where ctn_bwd_dw_emits_u() says so; an error elsewhere.                          */
+    const float* b2;
+    void* u_hi;
+    void* u_lo;
 } ctn_bwd_dw_args;
 
 /* gLN-2 backward + PReLU-2 backward + depthwise backward (input and weight grads) +
@@ -292,6 +298,8 @@ typedef struct ctn_bwd_dw_args {
  * rows of chan_part. */
 int ctn_bwd_dw_layout(int M, int K, int H, int P, int dilation, int norm, int* ctas, int* chan_rows);
 int ctn_bwd_dwconv(const ctn_bwd_dw_args* args, void* stream);
+/* 1 if ctn_bwd_dwconv can also write u (hi, lo) for this shape and norm (P = 3, H % 4 == 0, not cLN). */
+int ctn_bwd_dw_emits_u(int H, int P, int norm);
 
 /* gLN-1 input gradient + PReLU-1 backward: da (hi, lo) [M*K, H] and per-CTA d slope1 partials
  * [M * ctn_bwd_prelu_norm_tiles(K)]. */

@@ -70,8 +70,18 @@ def test_block_backward_chain(H, K, M, dil, causal):
     b.g1, b.b1, b.g2 = (t.data_ptr() for t in prm)
     b.wd, b.slope1, b.slope2 = wd_f.data_ptr(), a1_f.data_ptr(), a2_f.data_ptr()
     b.dn1, b.chan_part, b.scal_part = dn1.data_ptr(), chan.data_ptr(), scal.data_ptr()
+    # where the marching kernel runs it can also write u = gLN-2(prelu(d)) (hi, lo), the operand of dW2
+    emits_u = bool(lib.ctn_bwd_dw_emits_u(H, P, nat.NORM_GLN))
+    assert emits_u == (H % 4 == 0)
+    if emits_u:
+        b2_f = f(b2).view(-1)
+        u_hi = torch.full((M * K, H), float("nan"), dtype=torch.bfloat16, device=DEV)
+        u_lo = torch.full_like(u_hi, float("nan"))
+        b.b2, b.u_hi, b.u_lo = b2_f.data_ptr(), u_hi.data_ptr(), u_lo.data_ptr()
     nat.check(lib.ctn_bwd_dwconv(C.byref(b), nat.stream()))
     assert not torch.isnan(dn1).any() and not torch.isnan(chan).any() and not torch.isnan(scal).any()
+    if emits_u:
+        assert rel_l2(u_hi.double() + u_lo.double(), Kn.to_rows(u.detach().float())) < 2e-5
     tol = 2e-4
     assert rel_l2(dn1, Kn.to_rows(n1.grad.float())) < tol
     cs = chan.double().sum(0).view(4 + P, H)
@@ -91,3 +101,27 @@ def test_block_backward_chain(H, K, M, dil, causal):
                                      alpha.data_ptr(), nat.stream()))
     assert rel_l2(da_hi.double() + da_lo.double(), Kn.to_rows(a.grad.float())) < tol
     assert rel_l2(alpha.double().sum(), a1.grad) < 5 * tol
+
+
+def test_u_output_is_refused_where_the_kernel_cannot_write_it():
+    """cLN blocks take the row-per-thread kernel, which has no u output: asking for one is an error, not a no-op."""
+    from ctn_b200 import _native as nat
+    lib = nat.lib()
+    M, K, H, P = 1, 8, 8, 3
+    assert lib.ctn_bwd_dw_emits_u(H, P, nat.NORM_CLN) == 0 and lib.ctn_bwd_dw_emits_u(H, 5, nat.NORM_GLN) == 0
+    z = lambda *s: torch.zeros(*s, device=DEV)
+    bufs = dict(du=z(M * K, H), d=z(M * K, H), a=z(M * K, H), stat1=z(M * K, 1, 2), stat2=z(M * K, 2), bstat=z(M * K, 1, 2),
+                g1=z(H), b1=z(H), g2=z(H), wd=z(H, P), slope1=z(1), slope2=z(1), dn1=z(M * K, H))
+    tiles, rows = C.c_int(), C.c_int()
+    lib.ctn_bwd_dw_layout(M, K, H, P, 1, nat.NORM_CLN, C.byref(tiles), C.byref(rows))
+    bufs["chan_part"], bufs["scal_part"] = z(M * rows.value, (4 + P) * H), z(M * tiles.value, 4)
+    u = torch.zeros(M * K, H, dtype=torch.bfloat16, device=DEV)
+    b = nat.BwdDwArgs()
+    b.M, b.K, b.H, b.P, b.dilation, b.causal, b.norm = M, K, H, P, 1, 0, nat.NORM_CLN
+    b.P1, b.P2, b.Pb = 1, 1, 1
+    for k, v in bufs.items():
+        setattr(b, k, v.data_ptr())
+    assert lib.ctn_bwd_dwconv(C.byref(b), nat.stream()) == 0
+    b.b2, b.u_hi, b.u_lo = bufs["g2"].data_ptr(), u.data_ptr(), u.data_ptr()
+    assert lib.ctn_bwd_dwconv(C.byref(b), nat.stream()) != 0
+    assert b"ctn_bwd_dw_emits_u" in lib.ctn_last_error()

@@ -11,6 +11,7 @@ cfg = dict(N=256, L=20, B=256, H=512, P=3, X=8, R=4, C=2, norm_type="gLN", causa
 torch.manual_seed(0)
 dev = torch.device("cuda")
 model = conv_tasnet.ConvTasNet(**cfg).to(dev).train()
+model.train_engine().overlap_wgrad = bool(int(os.environ.get("CTN_OVERLAP", "1")))
 opt = FusedAdam(model.parameters(), lr=1e-3, max_norm=5.0)
 h_src = (0.1 * torch.randn(M, 2, T)).pin_memory(); h_mix = h_src.sum(1).pin_memory()
 lengths = torch.full((M,), T, dtype=torch.int64, device=dev)
