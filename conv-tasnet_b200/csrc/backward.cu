@@ -616,14 +616,20 @@ constexpr int kDbTile = 32;
 constexpr int kDbMaxC = 8;
 constexpr int kDbMaxL = 64;
 
+// LT: the filter length as a compile-time constant (0 = run-time L).  With it the per-thread basis column and its
+// gradient (2 L floats) live in registers; indexed by a run-time bound they were local-memory arrays, read and
+// written in the innermost loop (109 -> 4x us per launch at 3 x 4 s).
+template <int LT>
 __global__ void __launch_bounds__(kBwThreads)
 decoder_bwd_kernel(const float* __restrict__ gest, const float* __restrict__ score, const float* __restrict__ w,
                    const float* __restrict__ V, int K, int N, int L, int C, int T, int softmax,
                    __nv_bfloat16* __restrict__ ds_hi, __nv_bfloat16* __restrict__ ds_lo, float* __restrict__ dw,
                    float* __restrict__ dV_part) {
     extern __shared__ float db_smem[];
+    if (LT) L = LT;
     const int hop = L / 2;
     const int CL = C * L;
+    constexpr int kLA = LT ? LT : kDbMaxL;
     float* df = db_smem;  // [kDbTile][C][L]
     const int m = blockIdx.y, k0 = blockIdx.x * kDbTile;
     const int nk = min(kDbTile, K - k0);
@@ -635,19 +641,33 @@ decoder_bwd_kernel(const float* __restrict__ gest, const float* __restrict__ sco
     __syncthreads();
     float* part = dV_part + (static_cast<long long>(m) * gridDim.x + blockIdx.x) * L * N;
     for (int n = threadIdx.x; n < N; n += blockDim.x) {
-        float Vn[kDbMaxL], dVn[kDbMaxL];
-#pragma unroll 4
-        for (int l = 0; l < L; ++l) Vn[l] = V[l * N + n], dVn[l] = 0.f;
+        float Vn[kLA], dVn[kLA];
+#pragma unroll
+        for (int l = 0; l < kLA; ++l)
+            if (l < L) Vn[l] = V[l * N + n], dVn[l] = 0.f;
+        // the next frame's mixture weight and scores are requested before this frame's arithmetic
+        float wv_nx = 0.f, sc_nx[kDbMaxC];
+        auto fetch = [&](int r) {
+            const long long row = static_cast<long long>(m) * K + k0 + r;
+            wv_nx = w[row * N + n];
+#pragma unroll
+            for (int c = 0; c < kDbMaxC; ++c)
+                if (c < C) sc_nx[c] = score[row * (static_cast<long long>(C) * N) + c * N + n];
+        };
+        if (nk > 0) fetch(0);
         for (int r = 0; r < nk; ++r) {
             const long long row = static_cast<long long>(m) * K + k0 + r;
-            const float wv = w[row * N + n];
-            const float* srow = score + row * (static_cast<long long>(C) * N);
+            const float wv = wv_nx;
             float mask[kDbMaxC], dsw[kDbMaxC];
+#pragma unroll
+            for (int c = 0; c < kDbMaxC; ++c)
+                if (c < C) mask[c] = sc_nx[c];   // raw score; relu applied below
+            if (r + 1 < nk) fetch(r + 1);
             if (softmax) {
                 float mx = -INFINITY;
 #pragma unroll
                 for (int c = 0; c < kDbMaxC; ++c)
-                    if (c < C) mask[c] = srow[c * N + n], mx = fmaxf(mx, mask[c]);
+                    if (c < C) mx = fmaxf(mx, mask[c]);
                 float den = 0.f;
 #pragma unroll
                 for (int c = 0; c < kDbMaxC; ++c)
@@ -656,10 +676,6 @@ decoder_bwd_kernel(const float* __restrict__ gest, const float* __restrict__ sco
 #pragma unroll
                 for (int c = 0; c < kDbMaxC; ++c)
                     if (c < C) mask[c] *= inv;
-            } else {
-#pragma unroll
-                for (int c = 0; c < kDbMaxC; ++c)
-                    if (c < C) mask[c] = srow[c * N + n];   // raw score; relu applied below
             }
             float dwn = 0.f, dot = 0.f;
 #pragma unroll
@@ -669,9 +685,12 @@ decoder_bwd_kernel(const float* __restrict__ gest, const float* __restrict__ sco
                 const float mk = softmax ? mask[c] : fmaxf(mask[c], 0.f);
                 const float sw = mk * wv;
                 float acc = 0.f;
-                for (int l = 0; l < L; ++l) {
-                    acc = fmaf(f[l], Vn[l], acc);
-                    dVn[l] = fmaf(f[l], sw, dVn[l]);
+#pragma unroll
+                for (int l = 0; l < kLA; ++l) {
+                    if (l < L) {
+                        acc = fmaf(f[l], Vn[l], acc);
+                        dVn[l] = fmaf(f[l], sw, dVn[l]);
+                    }
                 }
                 dwn = fmaf(acc, mk, dwn);
                 dsw[c] = acc * wv;              // d mask_c
@@ -690,7 +709,9 @@ decoder_bwd_kernel(const float* __restrict__ gest, const float* __restrict__ sco
                 ds_hi[o] = h, ds_lo[o] = lo;
             }
         }
-        for (int l = 0; l < L; ++l) part[l * N + n] = dVn[l];
+#pragma unroll
+        for (int l = 0; l < kLA; ++l)
+            if (l < L) part[l * N + n] = dVn[l];
     }
 }
 
@@ -751,10 +772,13 @@ cln_bwd_kernel(const float* __restrict__ dn0, const float* __restrict__ w, const
 // ---------------------------------------------------------------------------------------
 constexpr int kEwTile = 64;
 
+template <int LT>   // filter length at compile time (0 = run-time L): the accumulators stay in registers
 __global__ void __launch_bounds__(kBwThreads)
 encoder_wgrad_kernel(const float* __restrict__ dpre, const float* __restrict__ mixture, int T, int K, int N, int L,
                      float* __restrict__ dU_part) {
     extern __shared__ float ew_smem[];
+    if (LT) L = LT;
+    constexpr int kLA = LT ? LT : kDbMaxL;
     const int hop = L / 2;
     const int m = blockIdx.y, k0 = blockIdx.x * kEwTile;
     const int nk = min(kEwTile, K - k0);
@@ -764,15 +788,27 @@ encoder_wgrad_kernel(const float* __restrict__ dpre, const float* __restrict__ m
     __syncthreads();
     float* part = dU_part + (static_cast<long long>(m) * gridDim.x + blockIdx.x) * N * L;
     for (int n = threadIdx.x; n < N; n += blockDim.x) {
-        float acc[kDbMaxL];
-#pragma unroll 4
-        for (int l = 0; l < L; ++l) acc[l] = 0.f;
-        for (int r = 0; r < nk; ++r) {
-            const float g = dpre[(static_cast<long long>(m) * K + k0 + r) * N + n];
-            const float* x = ew_smem + r * hop;
-            for (int l = 0; l < L; ++l) acc[l] = fmaf(g, x[l], acc[l]);
+        float acc[kLA];
+#pragma unroll
+        for (int l = 0; l < kLA; ++l) acc[l] = 0.f;
+        const float* gp = dpre + (static_cast<long long>(m) * K + k0) * N + n;
+        for (int r0 = 0; r0 < nk; r0 += 4) {       // four frames' gradients requested together
+            float g[4];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) g[j] = r0 + j < nk ? gp[static_cast<long long>(r0 + j) * N] : 0.f;
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                if (r0 + j < nk) {
+                    const float* x = ew_smem + (r0 + j) * hop;
+#pragma unroll
+                    for (int l = 0; l < kLA; ++l)
+                        if (l < L) acc[l] = fmaf(g[j], x[l], acc[l]);
+                }
+            }
         }
-        for (int l = 0; l < L; ++l) part[n * L + l] = acc[l];
+#pragma unroll
+        for (int l = 0; l < kLA; ++l)
+            if (l < L) part[n * L + l] = acc[l];
     }
 }
 
@@ -963,7 +999,9 @@ extern "C" int ctn_decoder_bwd(const float* grad_est, const float* score, const 
     const size_t smem = static_cast<size_t>(kDbTile) * C * L * sizeof(float);
     CTN_REQUIRE(smem <= 48 * 1024, "ctn_decoder_bwd: C*L too large");
     dim3 grid(ceil_div(K, kDbTile), M);
-    decoder_bwd_kernel<<<grid, kBwThreads, smem, static_cast<cudaStream_t>(stream)>>>(
+    auto kern = L == 20 ? decoder_bwd_kernel<20> : L == 16 ? decoder_bwd_kernel<16> : L == 40 ? decoder_bwd_kernel<40>
+                                                                                                 : decoder_bwd_kernel<0>;
+    kern<<<grid, kBwThreads, smem, static_cast<cudaStream_t>(stream)>>>(
         grad_est, score, w, V, K, N, L, C, T, mask_nonlinear == CTN_MASK_SOFTMAX,
         static_cast<__nv_bfloat16*>(dscore_hi), static_cast<__nv_bfloat16*>(dscore_lo), dw, dV_part);
     CTN_LAUNCH_CHECK("decoder_bwd_kernel");
@@ -1000,7 +1038,9 @@ extern "C" int ctn_encoder_wgrad(const float* dpre, const float* mixture, int M,
     const int K = (T - L) / hop + 1;
     const size_t smem = static_cast<size_t>((kEwTile - 1) * hop + L) * sizeof(float);
     dim3 grid(ceil_div(K, kEwTile), M);
-    encoder_wgrad_kernel<<<grid, kBwThreads, smem, static_cast<cudaStream_t>(stream)>>>(dpre, mixture, T, K, N, L,
+    auto kern = L == 20 ? encoder_wgrad_kernel<20> : L == 16 ? encoder_wgrad_kernel<16> : L == 40 ? encoder_wgrad_kernel<40>
+                                                                                                       : encoder_wgrad_kernel<0>;
+    kern<<<grid, kBwThreads, smem, static_cast<cudaStream_t>(stream)>>>(dpre, mixture, T, K, N, L,
                                                                                         dU_part);
     CTN_LAUNCH_CHECK("encoder_wgrad_kernel");
     return CTN_OK;
