@@ -437,6 +437,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tm_a_hi, const __grid_constan
             const int krow0 = tk * kBM + ew * 32;            // first frame of this warp's 32 rows
             const bool store_ok = tile_ok && krow0 < ep.K && !(ep.dbg & 2);  // rows past K: clipped by the map
             float ra[4][8], rb[4][8];                        // side input of even / odd chunks
+            float rc3[4][8];                                 // kDeep: a third buffer, the prefetch runs two chunks ahead
+            constexpr bool kDeep = kBw && !PAIR;             // (single-CTA kernel: small problems, latency-bound epilogue)
             auto load_aux = [&](float (&dst)[4][8], int ci) {
                 if (!valid || col0 + ci * 32 >= ep.Cout || (ep.dbg & 32)) return;
                 if (aux != nullptr) {
@@ -452,6 +454,14 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tm_a_hi, const __grid_constan
                 }
             };
             if (kAffine || kBw) load_aux(ra, 0);
+            if constexpr (kDeep) load_aux(rb, 1);
+            if (kBw && valid && grp_ok) {
+                // the saved pre-activation comes from DRAM (written a whole forward pass ago): bring the lane's other
+                // three lines of this tile into L2 while the MMAs run; the register prefetch is only one chunk deep
+#pragma unroll
+                for (int ci = 1; ci < 4; ++ci)
+                    if (col0 + ci * 32 < ep.Cout) ptx::prefetch_l2(aux + grow * ep.Cout + col0 + ci * 32);
+            }
             ptx::mbar_wait(tfull_bar + as, aphase);
             ptx::tc_fence_after();
             float ls[4] = {0.f, 0.f, 0.f, 0.f}, lss[4] = {0.f, 0.f, 0.f, 0.f};
@@ -466,14 +476,17 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tm_a_hi, const __grid_constan
                             for (int j = 0; j < 32; ++j) r[j] = j + lane;
                         } else
                         ptx::tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(ew * 32) << 16) + as * BN + cgrp * 128 + ci * 32, r);
-                        if ((kAffine || kBw) && ci < 3) {
+                        if constexpr (kDeep) {          // buffers ra, rb, rc3 in turn: chunk ci + 2 -> buffer (ci + 2) % 3
+                            if (ci == 0) load_aux(rc3, 2);
+                            if (ci == 1) load_aux(ra, 3);
+                        } else if ((kAffine || kBw) && ci < 3) {
                             if (ci & 1) load_aux(ra, ci + 1); else load_aux(rb, ci + 1);
                         }
                         ptx::tmem_ld_wait();
                         float v[32];
 #pragma unroll
                         for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
-                        const float (&rc)[4][8] = (ci & 1) ? rb : ra;
+                        const float (&rc)[4][8] = kDeep ? ((ci == 1) ? rb : ((ci == 2) ? rc3 : ra)) : ((ci & 1) ? rb : ra);
                         const float* cs = col_s + cgrp * 128 + ci * 32;
                         if (kAffine) {
 #pragma unroll
