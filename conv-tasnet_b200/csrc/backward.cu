@@ -389,8 +389,10 @@ struct BwdPnParams {
     float* alpha_part;       // [M * gridDim.x]
 };
 
+constexpr int kPnPre = 2;     // vector pairs (dn1, a) per thread requested ahead of the statistics: what 51 registers hold
+// five CTAs per SM: at 3 x 4 s the 600 CTAs of a launch are then resident at once (66 registers made it two waves)
 template <int VEC>
-__global__ void __launch_bounds__(kBwThreads) bwd_prelu_norm_kernel(const BwdPnParams p) {
+__global__ void __launch_bounds__(kBwThreads, 5) bwd_prelu_norm_kernel(const BwdPnParams p) {
     __shared__ float sh[4];
     __shared__ float red[8];
     const int H = p.H;
@@ -399,9 +401,9 @@ __global__ void __launch_bounds__(kBwThreads) bwd_prelu_norm_kernel(const BwdPnP
     const double n = static_cast<double>(p.K) * H;
     const int CV = (H + VEC - 1) / VEC;
     const long long row0 = static_cast<long long>(m) * p.K + k0;
-    V<VEC> dns[kNsPre / 2], avs[kNsPre / 2];   // requested before the sums are finalised, as in norm_split
+    V<VEC> dns[kPnPre], avs[kPnPre];   // requested before the sums are finalised, as in norm_split
 #pragma unroll
-    for (int j = 0; j < kNsPre / 2; ++j) {
+    for (int j = 0; j < kPnPre; ++j) {
         const int i = threadIdx.x + j * kBwThreads;
         if (i < nk * CV) {
             const int r = i / CV, c = (i - r * CV) * VEC;
@@ -439,11 +441,11 @@ __global__ void __launch_bounds__(kBwThreads) bwd_prelu_norm_kernel(const BwdPnP
         store_hl<VEC>(p.da_hi + row * H + c, p.da_lo + row * H + c, o);
     };
 #pragma unroll
-    for (int j = 0; j < kNsPre / 2; ++j) {
+    for (int j = 0; j < kPnPre; ++j) {
         const int i = threadIdx.x + j * kBwThreads;
         if (i < nk * CV) emit(i, dns[j], avs[j]);
     }
-    for (int i = threadIdx.x + (kNsPre / 2) * kBwThreads; i < nk * CV; i += kBwThreads) {
+    for (int i = threadIdx.x + (kPnPre) * kBwThreads; i < nk * CV; i += kBwThreads) {
         const int r = i / CV, c = (i - r * CV) * VEC;
         V<VEC> dn, av;
         dn.load(p.dn1 + (row0 + r) * H + c);
