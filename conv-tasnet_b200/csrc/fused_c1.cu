@@ -124,6 +124,7 @@ updc1_kernel(const __grid_constant__ CUtensorMap tm_w_hi, const __grid_constant_
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
+    if (threadIdx.x == 0) C1_TRACE(0, 28);     // kernel entry
     for (int i = threadIdx.x; i < kCin; i += kThreads) {
         colc[i] = __ldg(p.col_g + i);
         colc[kCin + i] = __ldg(p.col_bias + i);
@@ -478,6 +479,7 @@ updc1_kernel(const __grid_constant__ CUtensorMap tm_w_hi, const __grid_constant_
     if (warp == 1) {
         ptx::tc_fence_after();
         ptx::tmem_dealloc_pair(tmem_base, 2 * kBN);
+        if (lane == 0) C1_TRACE(0, 29);        // kernel exit
     }
 }
 

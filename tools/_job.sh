@@ -1,2 +1,2 @@
-export CTN_ALLOW_EXPERIMENT_BUILD=1
-for r in 1 2; do for l in libctn_b200.so libctn_expb.so libctn_expc.so; do echo $l; CTN_LIB_FILE=$l python tools/profile_step_phases.py 3 | egrep "bwd"; done; done
+export CTN_ALLOW_EXPERIMENT_BUILD=1 CTN_LIB_FILE=libctn_exp.so CTN_TRACE=1
+python tools/bench_updc1.py 3 2>&1 | grep -v "^[0-9]* $" | cut -c1-700

@@ -80,7 +80,7 @@ if os.environ.get("CTN_TRACE") == "1":
         t = buf.reshape(64, 32)
         t0 = t[0][t[0] > 0].min()
         names = ["ld0", "ld1", "ld2", "ld3", "raw0", "raw1", "raw2", "raw3", "fix0", "fix1", "fix2", "fix3", "st0", "st1", "st2",
-                 "st3", "m0", "m1", "m2", "m3", "m4", "m5", "m6", "m7", "d0s", "d0e", "d1s", "d1e"]
+                 "st3", "m0", "m1", "m2", "m3", "m4", "m5", "m6", "m7", "d0s", "d0e", "d1s", "d1e", "entry", "exit"]
         print("trace dbg", dbg, "(cycles since the first event, CTA 0, row tiles 0-11)")
         for it in range(12):
             print(it, " ".join("%s=%d" % (n, (t[it][i] - t0) // 10 * 10) for i, n in enumerate(names) if t[it][i] > 0))

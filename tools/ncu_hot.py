@@ -3,9 +3,11 @@ import csv, io, subprocess, sys
 raw = subprocess.run(["ncu", "-i", sys.argv[1], "--page", "source", "--csv", "--print-source", "sass"], capture_output=True, text=True).stdout
 rows = list(csv.reader(io.StringIO(raw)))
 hi = [i for i, r in enumerate(rows) if r and r[0] == "Address"]
-h = rows[hi[0]]
+import os
+KI = int(os.environ.get("NCU_KERNEL", "0"))      # which kernel of the report (NCU_KERNEL=1: the second launch captured)
+h = rows[hi[KI]]
 ci = {n: i for i, n in enumerate(h)}
-body = [r for r in rows[hi[0] + 1:(hi[1] - 1 if len(hi) > 1 else None)] if len(r) > 10]
+body = [r for r in rows[hi[KI] + 1:(hi[KI + 1] - 1 if len(hi) > KI + 1 else None)] if len(r) > 10]
 tot = sum(int(r[ci["# Samples"]] or 0) for r in body)
 print("total samples", tot, "instructions", len(body))
 stalls = [n for n in h if n.startswith("stall_") and "Not Issued" not in n]
