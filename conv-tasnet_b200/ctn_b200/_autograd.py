@@ -596,9 +596,11 @@ class TrainPlan:
 
     def _launch_backward(self):
         """The dgrad chain runs on the current stream; weight-gradient GEMMs and the per-block parameter
-        reduction (results needed only at the end of the step) run on a side stream between _FORK (side
-        waits for main) and _JOIN (main waits for side) markers, so they fill the SMs the chain's
-        kernels leave idle at small batch.  With overlap off everything runs in list order on one stream."""
+        reduction (results needed only at the end of the step) run on a side stream, so they fill the SMs the
+        chain's kernels leave idle at small batch.  Markers in bwd_calls: _FORK (side waits for everything issued
+        to main so far), _Mark(name) (an event on the side stream), _Wait(name) (main waits for that event, if
+        any), _JOIN (main waits for all side work).  With overlap off everything runs in list order on one stream
+        (the list order is a valid serial order)."""
         s, check, lib = nat.stream(), nat.check, nat.lib()
         check(lib.ctn_decoder_bwd(self.g_est.data_ptr(), *self.dec_bwd_args, s))
         if not self.overlap:
