@@ -514,9 +514,14 @@ class SeparationEngine:
             while len(side) < 2:
                 side.append(torch.cuda.Stream(device=device))
             s_in, s_out = side
-            start = cur.record_event()
-            s_in.wait_event(start)
-            s_out.wait_event(start)
+            if join:
+                # stream-ordered call: the copies start behind whatever the caller has queued on its stream
+                start = cur.record_event()
+                s_in.wait_event(start)
+                s_out.wait_event(start)
+            # join=False (pipelined calls): the copy-in only waits for its own slot's last compute (plan.computed), so it
+            # runs under the PREVIOUS call's kernels - with one micro-batch per call (8 GPUs x 64 mixtures) the wait on the
+            # caller's stream above would put every call's 8 MB copy-in in front of its compute
             last = None
             for (m0, m1), plan in zip(chunks, plans):
                 # plan.computed: its last compute has finished (mix may be overwritten);
